@@ -1,0 +1,88 @@
+"""ctypes binding of ``libgnnx_sm100.so`` -- the only way the package reaches the GPU kernels.
+
+Prototypes are parsed from ``include/gnnx.h`` so the Python side can never drift from the C ABI.
+There is no CPU fallback: if the shared library is missing or a call fails, a ``RuntimeError`` is
+raised (the product path must fail loudly, never silently degrade).
+"""
+
+from __future__ import annotations
+
+import ctypes
+import re
+from pathlib import Path
+from typing import Dict, List, Tuple
+
+_HERE = Path(__file__).resolve().parent
+HEADER = _HERE.parent / "include" / "gnnx.h"
+LIB_PATH = _HERE / "libgnnx_sm100.so"
+
+_SCALARS = {
+    "int64_t": ctypes.c_int64, "int32_t": ctypes.c_int32, "int": ctypes.c_int,
+    "size_t": ctypes.c_size_t, "float": ctypes.c_float,
+}
+_PROTO = re.compile(r"GNNX_API\s+(const\s+char\s*\*|int|size_t)\s+(gnnx_\w+)\s*\(([^;]*?)\)\s*;", re.S)
+
+
+def parse_header(path: Path = HEADER) -> Dict[str, Tuple[object, List[object]]]:
+    """Return ``{name: (restype, [argtypes])}`` for every ``GNNX_API`` prototype in the header."""
+    text = re.sub(r"/\*.*?\*/", "", path.read_text(), flags=re.S)
+    out: Dict[str, Tuple[object, List[object]]] = {}
+    for ret, name, args in _PROTO.findall(text):
+        ret = ret.replace(" ", "")
+        restype = ctypes.c_char_p if ret.startswith("constchar") else _SCALARS[ret]
+        argtypes: List[object] = []
+        args = args.strip()
+        if args and args != "void":
+            for a in args.split(","):
+                a = a.strip()
+                if "*" in a:
+                    argtypes.append(ctypes.c_void_p)
+                else:
+                    ctype = a.replace("const", "").split()[0]
+                    argtypes.append(_SCALARS[ctype])
+        out[name] = (restype, argtypes)
+    return out
+
+
+class GnnxError(RuntimeError):
+    pass
+
+
+class _Lib:
+    def __init__(self):
+        if not LIB_PATH.exists():
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m gnnepcsaft_b200.build` "
+                "(there is no CPU or PyTorch fallback for the gnnx kernels)")
+        self._dll = ctypes.CDLL(str(LIB_PATH))
+        self.protos = parse_header()
+        for name, (restype, argtypes) in self.protos.items():
+            fn = getattr(self._dll, name)          # AttributeError if the .so lacks a declared symbol
+            fn.restype, fn.argtypes = restype, argtypes
+        abi = self._dll.gnnx_abi_version()
+        if abi != 1:
+            raise RuntimeError(f"libgnnx_sm100.so ABI {abi} does not match the Python layer (1)")
+
+    def last_error(self) -> str:
+        msg = self._dll.gnnx_last_error()
+        return msg.decode() if msg else ""
+
+    def call(self, name: str, *args):
+        """Call an ``int``-returning entry point and raise on a non-zero code."""
+        rc = getattr(self._dll, name)(*args)
+        if rc != 0:
+            raise GnnxError(f"{name} failed with code {rc}: {self.last_error()}")
+
+    def query(self, name: str, *args) -> int:
+        """Call a ``size_t``-returning ``*_workspace_bytes`` entry point."""
+        return int(getattr(self._dll, name)(*args))
+
+
+_LIB = None
+
+
+def lib() -> _Lib:
+    global _LIB
+    if _LIB is None:
+        _LIB = _Lib()
+    return _LIB

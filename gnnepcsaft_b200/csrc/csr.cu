@@ -1,0 +1,366 @@
+// Batch collator: dst-sorted CSR + src-sorted view + degree histogram + packed-store collation.
+// Integer-only, bit-exact with argsort(stable)/bincount.  HBM-bound integer
+// work: histogram -> scan -> atomic placement -> per-row sort of edge ids (rows are tiny, and
+// sorting unique ids makes the atomic placement order irrelevant => deterministic).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace gnnx {
+
+static thread_local char g_err[512] = "";
+int set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+// ------------------------------------------------------------------ histogram
+template <typename IdxT>
+__global__ void k_hist(const IdxT* __restrict__ src, const IdxT* __restrict__ dst, int E, int N,
+                       int* __restrict__ cnt_dst, int* __restrict__ cnt_src, int* __restrict__ err) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
+        long long s = (long long)src[e], d = (long long)dst[e];
+        if (s < 0 || s >= N || d < 0 || d >= N) { *err = 1; continue; }
+        atomicAdd(&cnt_dst[d + 1], 1);
+        atomicAdd(&cnt_src[s + 1], 1);
+    }
+}
+
+// ------------------------------------------------------------------ scan (3-phase, 2 arrays via blockIdx.y)
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;                     // 2048 elements per block
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ int block_scan_inclusive(int v, int* smem_warp) {
+    // inclusive scan of one int per thread across the block (256 threads = 8 warps)
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    if (lane == 31) smem_warp[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        int s = lane < (kScanThreads / 32) ? smem_warp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane < (kScanThreads / 32)) smem_warp[lane] = s;
+    }
+    __syncthreads();
+    if (w > 0) v += smem_warp[w - 1];
+    __syncthreads();
+    return v;
+}
+
+__global__ void k_scan_tiles(int* __restrict__ a0, int* __restrict__ a1, int n, int* __restrict__ sums, int ntiles) {
+    __shared__ int sw[32];
+    int* a = blockIdx.y ? a1 : a0;
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int v[kScanItems];
+    int t = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        v[i] = (base + i < n) ? a[base + i] : 0;
+        t += v[i];
+        v[i] = t;
+    }
+    int incl = block_scan_inclusive(t, sw);
+    int excl = incl - t;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i)
+        if (base + i < n) a[base + i] = v[i] + excl;
+    if (threadIdx.x == kScanThreads - 1) sums[blockIdx.y * ntiles + blockIdx.x] = incl;
+}
+
+__global__ void k_scan_sums(int* __restrict__ sums, int ntiles) {
+    // one block per array; sequential over chunks of kScanThreads with a running carry
+    __shared__ int sw[32];
+    __shared__ int carry_s;
+    int* s = sums + blockIdx.x * ntiles;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < ntiles; base += kScanThreads) {
+        int i = base + threadIdx.x;
+        int v = i < ntiles ? s[i] : 0;
+        int incl = block_scan_inclusive(v, sw);
+        int carry = carry_s;
+        if (i < ntiles) s[i] = incl - v + carry;   // exclusive prefix of tile sums
+        __syncthreads();
+        if (threadIdx.x == kScanThreads - 1) carry_s = carry + incl;
+        __syncthreads();
+    }
+}
+
+__global__ void k_scan_add(int* __restrict__ a0, int* __restrict__ a1, int n, const int* __restrict__ sums, int ntiles) {
+    int* a = blockIdx.y ? a1 : a0;
+    int add = sums[blockIdx.y * ntiles + blockIdx.x];
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i)
+        if (base + i < n) a[base + i] += add;
+}
+
+// ------------------------------------------------------------------ placement + per-row sort
+template <typename IdxT>
+__global__ void k_place(const IdxT* __restrict__ src, const IdxT* __restrict__ dst, int E, int N,
+                        const int* __restrict__ rowptr, const int* __restrict__ colptr,
+                        int* __restrict__ fill_dst, int* __restrict__ fill_src,
+                        int* __restrict__ tmp_dst, int* __restrict__ tmp_src) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
+        long long s = (long long)src[e], d = (long long)dst[e];
+        if (s < 0 || s >= N || d < 0 || d >= N) continue;
+        tmp_dst[rowptr[d] + atomicAdd(&fill_dst[d], 1)] = e;
+        tmp_src[colptr[s] + atomicAdd(&fill_src[s], 1)] = e;
+    }
+}
+
+__device__ void sort_ids(int* a, int n) {
+    if (n <= 32) {                               // insertion sort: rows of molecular graphs have <= 6 entries
+        for (int i = 1; i < n; ++i) {
+            int v = a[i], j = i - 1;
+            while (j >= 0 && a[j] > v) { a[j + 1] = a[j]; --j; }
+            a[j + 1] = v;
+        }
+        return;
+    }
+    // heap sort for hub rows (any degree, in place)
+    for (int start = n / 2 - 1; start >= 0; --start) {
+        int root = start;
+        for (;;) {
+            int child = 2 * root + 1;
+            if (child >= n) break;
+            if (child + 1 < n && a[child] < a[child + 1]) ++child;
+            if (a[root] >= a[child]) break;
+            int t = a[root]; a[root] = a[child]; a[child] = t;
+            root = child;
+        }
+    }
+    for (int end = n - 1; end > 0; --end) {
+        int t = a[0]; a[0] = a[end]; a[end] = t;
+        int root = 0;
+        for (;;) {
+            int child = 2 * root + 1;
+            if (child >= end) break;
+            if (child + 1 < end && a[child] < a[child + 1]) ++child;
+            if (a[root] >= a[child]) break;
+            int t2 = a[root]; a[root] = a[child]; a[child] = t2;
+            root = child;
+        }
+    }
+}
+
+template <typename IdxT>
+__global__ void k_sort_rows_dst(const IdxT* __restrict__ src, int N, const int* __restrict__ rowptr,
+                                int* __restrict__ tmp_dst, int* __restrict__ csr_src,
+                                int* __restrict__ csr_eid, int* __restrict__ pos_of_eid) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        int b = rowptr[i], n = rowptr[i + 1] - b;
+        sort_ids(tmp_dst + b, n);
+        for (int k = 0; k < n; ++k) {
+            int e = tmp_dst[b + k];
+            csr_eid[b + k] = e;
+            csr_src[b + k] = (int)src[e];
+            pos_of_eid[e] = b + k;
+        }
+    }
+}
+
+template <typename IdxT>
+__global__ void k_sort_rows_src(const IdxT* __restrict__ dst, int N, const int* __restrict__ colptr,
+                                int* __restrict__ tmp_src, const int* __restrict__ pos_of_eid,
+                                int* __restrict__ csc_pos, int* __restrict__ csc_dst) {
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < N; j += gridDim.x * blockDim.x) {
+        int b = colptr[j], n = colptr[j + 1] - b;
+        sort_ids(tmp_src + b, n);
+        for (int k = 0; k < n; ++k) {
+            int e = tmp_src[b + k];
+            csc_pos[b + k] = pos_of_eid[e];
+            csc_dst[b + k] = (int)dst[e];
+        }
+    }
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+template <typename IdxT>
+static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t E64, int32_t* rowptr,
+                          int32_t* csr_src, int32_t* csr_eid, int32_t* pos_of_eid, int32_t* colptr,
+                          int32_t* csc_pos, int32_t* csc_dst, int32_t* err_flag, void* ws, size_t ws_bytes,
+                          void* stream_) {
+    GNNX_REQUIRE(N64 >= 0 && E64 >= 0 && N64 < (1ll << 31) - 1 && E64 < (1ll << 31) - 1, "csr_build: N/E out of int32 range");
+    GNNX_REQUIRE(rowptr && colptr && err_flag, "csr_build: null output");
+    GNNX_REQUIRE(ws_bytes >= gnnx_csr_workspace_bytes(N64, E64), "csr_build: workspace too small");
+    cudaStream_t st = as_stream(stream_);
+    int N = (int)N64, E = (int)E64;
+    int n1 = N + 1;
+    int ntiles = ceil_div(n1, kScanTile);
+    char* w = (char*)ws;
+    int* fill_dst = (int*)w; w += align256(sizeof(int) * (size_t)n1);
+    int* fill_src = (int*)w; w += align256(sizeof(int) * (size_t)n1);
+    int* tmp_dst = (int*)w;  w += align256(sizeof(int) * (size_t)(E > 0 ? E : 1));
+    int* tmp_src = (int*)w;  w += align256(sizeof(int) * (size_t)(E > 0 ? E : 1));
+    int* sums = (int*)w;
+
+    GNNX_CUDA(cudaMemsetAsync(rowptr, 0, sizeof(int) * (size_t)n1, st));
+    GNNX_CUDA(cudaMemsetAsync(colptr, 0, sizeof(int) * (size_t)n1, st));
+    GNNX_CUDA(cudaMemsetAsync(fill_dst, 0, sizeof(int) * (size_t)n1, st));
+    GNNX_CUDA(cudaMemsetAsync(fill_src, 0, sizeof(int) * (size_t)n1, st));
+    GNNX_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
+    int eb = E > 0 ? min(ceil_div(E, 256), kNumSMs * 16) : 0;
+    if (E > 0) k_hist<IdxT><<<eb, 256, 0, st>>>(src, dst, E, N, rowptr, colptr, err_flag);
+    k_scan_tiles<<<dim3(ntiles, 2), kScanThreads, 0, st>>>(rowptr, colptr, n1, sums, ntiles);
+    k_scan_sums<<<2, kScanThreads, 0, st>>>(sums, ntiles);
+    k_scan_add<<<dim3(ntiles, 2), kScanThreads, 0, st>>>(rowptr, colptr, n1, sums, ntiles);
+    if (E > 0) {
+        k_place<IdxT><<<eb, 256, 0, st>>>(src, dst, E, N, rowptr, colptr, fill_dst, fill_src, tmp_dst, tmp_src);
+        int nb = min(ceil_div(N, 128), kNumSMs * 16);
+        k_sort_rows_dst<IdxT><<<nb, 128, 0, st>>>(src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
+        k_sort_rows_src<IdxT><<<nb, 128, 0, st>>>(dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
+    }
+    return check_launch("csr_build");
+}
+
+// ------------------------------------------------------------------ degree histogram / graph_ptr / misc
+__global__ void k_degree_hist(const int* __restrict__ rowptr, int N, unsigned long long* __restrict__ hist,
+                              int nbins, int* __restrict__ maxdeg) {
+    extern __shared__ int sh[];   // nbins counters + 1 max
+    for (int i = threadIdx.x; i <= nbins; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        int d = rowptr[i + 1] - rowptr[i];
+        atomicAdd(&sh[min(d, nbins - 1)], 1);
+        atomicMax(&sh[nbins], d);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nbins; i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
+    if (threadIdx.x == 0) atomicMax(maxdeg, sh[nbins]);
+}
+
+__global__ void k_graph_ptr(const int64_t* __restrict__ batch, int N, int G, int* __restrict__ gp) {
+    for (int n = blockIdx.x * blockDim.x + threadIdx.x; n <= N; n += gridDim.x * blockDim.x) {
+        long long prev = n == 0 ? -1 : batch[n - 1];
+        long long cur = n == N ? (long long)G : batch[n];
+        if (cur > G) cur = G;
+        for (long long g = prev + 1; g <= cur; ++g) gp[g] = n;   // also fills empty graphs
+    }
+}
+
+__global__ void k_narrow(const int64_t* __restrict__ in, long long count, uint8_t* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
+        out[i] = (uint8_t)in[i];
+}
+
+__global__ void k_edge_codes(const uint8_t* __restrict__ ea, const int* __restrict__ eid, int E, uint8_t* __restrict__ codes) {
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < E; p += gridDim.x * blockDim.x) {
+        const uint8_t* a = ea + 3ll * eid[p];
+        codes[p] = (uint8_t)((a[0] * 6 + a[1]) * 2 + a[2]);
+    }
+}
+
+// one warp per selected molecule: copy its node / edge records to the batch, adding offsets
+__global__ void k_collate_packed(const uint8_t* __restrict__ sx, const int16_t* __restrict__ ssrc,
+                                 const int16_t* __restrict__ sdst, const uint8_t* __restrict__ sea,
+                                 const int64_t* __restrict__ snp, const int64_t* __restrict__ sep,
+                                 const int64_t* __restrict__ gids, int G, const int64_t* __restrict__ noff,
+                                 const int64_t* __restrict__ eoff, uint8_t* __restrict__ ox,
+                                 int* __restrict__ osrc, int* __restrict__ odst, uint8_t* __restrict__ oea,
+                                 int* __restrict__ obatch) {
+    int lane = threadIdx.x & 31;
+    int warps_per_block = blockDim.x >> 5;
+    for (int g = blockIdx.x * warps_per_block + (threadIdx.x >> 5); g < G; g += gridDim.x * warps_per_block) {
+        long long id = gids[g];
+        long long nb = snp[id], nn = snp[id + 1] - nb;
+        long long ebeg = sep[id], ne = sep[id + 1] - ebeg;
+        long long no = noff[g], eo = eoff[g];
+        for (long long t = lane; t < nn * 9; t += 32) ox[no * 9 + t] = sx[nb * 9 + t];
+        for (long long t = lane; t < nn; t += 32) obatch[no + t] = g;
+        for (long long t = lane; t < ne; t += 32) {
+            osrc[eo + t] = (int)ssrc[ebeg + t] + (int)no;
+            odst[eo + t] = (int)sdst[ebeg + t] + (int)no;
+        }
+        for (long long t = lane; t < ne * 3; t += 32) oea[eo * 3 + t] = sea[ebeg * 3 + t];
+    }
+}
+
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+int gnnx_abi_version(void) { return GNNX_ABI_VERSION; }
+const char* gnnx_last_error(void) { return gnnx::g_err; }
+
+size_t gnnx_csr_workspace_bytes(int64_t N, int64_t E) {
+    size_t n1 = (size_t)N + 1, e = (size_t)(E > 0 ? E : 1);
+    size_t ntiles = (n1 + kScanTile - 1) / kScanTile;
+    return 2 * align256(4 * n1) + 2 * align256(4 * e) + align256(4 * 2 * ntiles) + 256;
+}
+
+int gnnx_csr_build_i64(const int64_t* edge_index, int64_t N, int64_t E, int32_t* rowptr, int32_t* csr_src,
+                       int32_t* csr_eid, int32_t* pos_of_eid, int32_t* colptr, int32_t* csc_pos,
+                       int32_t* csc_dst, int32_t* err_flag, void* ws, size_t ws_bytes, void* stream) {
+    return csr_build_impl<int64_t>(edge_index, edge_index + E, N, E, rowptr, csr_src, csr_eid, pos_of_eid,
+                                   colptr, csc_pos, csc_dst, err_flag, ws, ws_bytes, stream);
+}
+
+int gnnx_csr_build_i32(const int32_t* src, const int32_t* dst, int64_t N, int64_t E, int32_t* rowptr,
+                       int32_t* csr_src, int32_t* csr_eid, int32_t* pos_of_eid, int32_t* colptr,
+                       int32_t* csc_pos, int32_t* csc_dst, int32_t* err_flag, void* ws, size_t ws_bytes,
+                       void* stream) {
+    return csr_build_impl<int32_t>(src, dst, N, E, rowptr, csr_src, csr_eid, pos_of_eid, colptr, csc_pos,
+                                   csc_dst, err_flag, ws, ws_bytes, stream);
+}
+
+int gnnx_degree_hist(const int32_t* rowptr, int64_t N, int64_t* hist, int32_t nbins, int32_t* max_degree,
+                     void* stream) {
+    GNNX_REQUIRE(nbins >= 1 && nbins <= 4096, "degree_hist: nbins must be in [1,4096]");
+    if (N == 0) return GNNX_OK;
+    int nb = min(ceil_div(N, 256), kNumSMs * 4);
+    k_degree_hist<<<nb, 256, sizeof(int) * (nbins + 1), as_stream(stream)>>>(
+        rowptr, (int)N, (unsigned long long*)hist, nbins, max_degree);
+    return check_launch("degree_hist");
+}
+
+int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream) {
+    GNNX_REQUIRE(N >= 0 && G >= 0, "graph_ptr: negative size");
+    int nb = min(ceil_div(N + 1, 256), kNumSMs * 8);
+    k_graph_ptr<<<nb, 256, 0, as_stream(stream)>>>(batch, (int)N, (int)G, graph_ptr);
+    return check_launch("graph_ptr_from_batch");
+}
+
+int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream) {
+    if (count == 0) return GNNX_OK;
+    int nb = min(ceil_div(count, 256), kNumSMs * 16);
+    k_narrow<<<nb, 256, 0, as_stream(stream)>>>(in, count, out);
+    return check_launch("narrow_i64_u8");
+}
+
+int gnnx_edge_codes(const uint8_t* ea, const int32_t* csr_eid, int64_t E, uint8_t* codes, void* stream) {
+    if (E == 0) return GNNX_OK;
+    int nb = min(ceil_div(E, 256), kNumSMs * 16);
+    k_edge_codes<<<nb, 256, 0, as_stream(stream)>>>(ea, csr_eid, (int)E, codes);
+    return check_launch("edge_codes");
+}
+
+int gnnx_collate_packed(const uint8_t* sx, const int16_t* ssrc, const int16_t* sdst, const uint8_t* sea,
+                        const int64_t* snp, const int64_t* sep, const int64_t* gids, int64_t G,
+                        const int64_t* noff, const int64_t* eoff, uint8_t* ox, int32_t* osrc, int32_t* odst,
+                        uint8_t* oea, int32_t* obatch, void* stream) {
+    if (G == 0) return GNNX_OK;
+    int nb = min(ceil_div(G, 8), kNumSMs * 8);
+    k_collate_packed<<<nb, 256, 0, as_stream(stream)>>>(sx, ssrc, sdst, sea, snp, sep, gids, (int)G, noff, eoff,
+                                                        ox, osrc, odst, oea, obatch);
+    return check_launch("collate_packed");
+}
+
+}  // extern "C"

@@ -1,0 +1,129 @@
+// OGB AtomEncoder / BondEncoder embedding sums: out[r] = sum_k table[off_k + idx[r,k]].
+// Forward: one warp per row, float4 over the hidden dim, table (<= 174 rows) stays in L1/L2.
+// Backward: deterministic, atomic-free: every (column, feature) pair is owned by one thread that
+// walks its row chunk in order and accumulates into a shared-memory table slab; chunk partials
+// are then summed in chunk order.
+#include "common.cuh"
+
+namespace gnnx {
+
+__global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, const int* __restrict__ offsets,
+                            const float* __restrict__ table, int H, float* __restrict__ out) {
+    int lane = threadIdx.x & 31;
+    int wpb = blockDim.x >> 5;
+    for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += gridDim.x * wpb) {
+        int my = lane < K ? offsets[lane] + (int)idx[(long long)r * K + lane] : 0;
+        for (int c = lane * 4; c < H; c += 128) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < K; ++k) {
+                int tr = __shfl_sync(0xffffffffu, my, k);
+                float4 v = ldg4(table + (long long)tr * H + c);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            stg4(out + (long long)r * H + c, acc);
+        }
+    }
+}
+
+constexpr int kEmbSlab = 32;   // columns per CTA in the backward
+
+// grid: (ceil(H/32), nchunks); block: (32, K).  smem: table_rows * 32 floats.
+__global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, int K,
+                                    const int* __restrict__ offsets, int table_rows,
+                                    const float* __restrict__ dout, int H, int rows_per_chunk,
+                                    float* __restrict__ partial) {
+    extern __shared__ float tab[];
+    int c = blockIdx.x * kEmbSlab + threadIdx.x;
+    int k = threadIdx.y;
+    int tid = threadIdx.y * 32 + threadIdx.x, nthreads = blockDim.x * blockDim.y;
+    for (int i = tid; i < table_rows * kEmbSlab; i += nthreads) tab[i] = 0.f;
+    __syncthreads();
+    int r0 = blockIdx.y * rows_per_chunk;
+    int r1 = min(rows, r0 + rows_per_chunk);
+    int off = offsets[k];
+    if (c < H) {
+        int r = r0;
+        for (; r + 4 <= r1; r += 4) {       // 4 independent loads in flight, then ordered updates
+            float v0 = __ldg(dout + (long long)(r + 0) * H + c);
+            float v1 = __ldg(dout + (long long)(r + 1) * H + c);
+            float v2 = __ldg(dout + (long long)(r + 2) * H + c);
+            float v3 = __ldg(dout + (long long)(r + 3) * H + c);
+            int i0 = off + idx[(long long)(r + 0) * K + k];
+            int i1 = off + idx[(long long)(r + 1) * K + k];
+            int i2 = off + idx[(long long)(r + 2) * K + k];
+            int i3 = off + idx[(long long)(r + 3) * K + k];
+            tab[i0 * kEmbSlab + threadIdx.x] += v0;
+            tab[i1 * kEmbSlab + threadIdx.x] += v1;
+            tab[i2 * kEmbSlab + threadIdx.x] += v2;
+            tab[i3 * kEmbSlab + threadIdx.x] += v3;
+        }
+        for (; r < r1; ++r) {
+            float v = __ldg(dout + (long long)r * H + c);
+            tab[(off + idx[(long long)r * K + k]) * kEmbSlab + threadIdx.x] += v;
+        }
+    }
+    __syncthreads();
+    // feature k owns table rows [offsets[k], offsets[k+1]) exclusively, so the slab is race-free
+    float* dst = partial + (long long)blockIdx.y * table_rows * H;
+    for (int i = tid; i < table_rows * kEmbSlab; i += nthreads) {
+        int tr = i / kEmbSlab, cc = blockIdx.x * kEmbSlab + (i % kEmbSlab);
+        if (cc < H) dst[(long long)tr * H + cc] = tab[i];
+    }
+}
+
+__global__ void k_reduce_partials(const float* __restrict__ partial, int nchunks, long long count,
+                                  float* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * count + i];
+        out[i] = s;
+    }
+}
+
+static int embed_chunks(int64_t rows, int32_t H) {
+    int slabs = ceil_div(H, kEmbSlab);
+    int target = max(1, (kNumSMs * 6) / slabs);
+    int by_rows = max(1, (int)((rows + 255) / 256));    // at least ~256 rows per chunk
+    return min(target, by_rows);
+}
+
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_t* offsets, const float* table,
+                       int32_t H, float* out, void* stream) {
+    GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_fwd: num_features must be in [1,32]");
+    GNNX_REQUIRE(H % 4 == 0, "embed_sum_fwd: hidden must be a multiple of 4");
+    if (rows == 0) return GNNX_OK;
+    int nb = min(ceil_div(rows, 8), kNumSMs * 8);
+    k_embed_fwd<<<nb, 256, 0, as_stream(stream)>>>(idx, (int)rows, K, offsets, table, H, out);
+    return check_launch("embed_sum_fwd");
+}
+
+size_t gnnx_embed_sum_bwd_workspace_bytes(int64_t rows, int32_t table_rows, int32_t H) {
+    return (size_t)embed_chunks(rows, H) * table_rows * H * sizeof(float);
+}
+
+int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_t* offsets, int32_t table_rows,
+                       const float* dout, int32_t H, float* dtable, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_bwd: num_features must be in [1,32]");
+    GNNX_REQUIRE(ws_bytes >= gnnx_embed_sum_bwd_workspace_bytes(rows, table_rows, H), "embed_sum_bwd: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    long long count = (long long)table_rows * H;
+    if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(dtable, 0, count * sizeof(float), st)); return GNNX_OK; }
+    int nchunks = embed_chunks(rows, H);
+    int rpc = ceil_div(rows, nchunks);
+    size_t smem = (size_t)table_rows * kEmbSlab * sizeof(float);
+    GNNX_REQUIRE(smem <= 200 * 1024, "embed_sum_bwd: table too large for the shared-memory slab");
+    if (smem > 48 * 1024)
+        GNNX_CUDA(cudaFuncSetAttribute(k_embed_bwd_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_embed_bwd_partial<<<dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st>>>(
+        idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws);
+    k_reduce_partials<<<min(ceil_div(count, 256), kNumSMs * 8), 256, 0, st>>>((const float*)ws, nchunks, count, dtable);
+    return check_launch("embed_sum_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,45 @@
+// gnnx_gemm: precision dispatch for the dense transforms (Linear layers of PNAConv / GATv2Conv / head).
+//   GNNX_PREC_FP32 -> CUDA-core fp32 kernel (gemm_simt.cu), the rel-1e-5 parity tier.
+//   GNNX_PREC_TF32 / GNNX_PREC_BF16 -> tcgen05 + TMEM kernels (gemm_tc.cu); shapes the tensor-core
+//   kernel does not cover (tiny or unaligned: the 60-row bond tables, the num_para-wide head output)
+//   run on the fp32 kernel, which is at least as accurate.
+#include "common.cuh"
+
+namespace gnnx {
+size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K);
+int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
+              int64_t N, int64_t K, const float* bias, int flags, void* ws, size_t ws_bytes, cudaStream_t st);
+bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
+                  const void* B, const void* C, int precision);
+size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision);
+int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
+            int64_t N, int64_t K, const float* bias, int flags, int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, int32_t tb, int32_t precision) {
+    size_t s = simt_workspace_bytes(M, N, K);
+    if (precision != GNNX_PREC_FP32) {
+        size_t t = tc_workspace_bytes(M, N, K, ta, tb, precision);
+        if (t > s) s = t;
+    }
+    return s;
+}
+
+int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
+              int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, int32_t precision, void* ws,
+              size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
+    GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
+    if (M == 0 || N == 0) return GNNX_OK;
+    GNNX_REQUIRE(A && B && C, "gemm: null operand");
+    cudaStream_t st = as_stream(stream);
+    if (precision != GNNX_PREC_FP32 && tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision))
+        return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, precision, ws, ws_bytes, st);
+    return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, ws, ws_bytes, st);
+}
+
+}  // extern "C"

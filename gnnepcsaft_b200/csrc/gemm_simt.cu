@@ -1,0 +1,222 @@
+// fp32 CUDA-core GEMM (GNNX_PREC_FP32): the parity tier for the Linear layers (rel 1e-5 against the
+// fp32 oracle) and the fallback for shapes the tcgen05 path does not take (tiny / unaligned).
+// 128x128x8 tiles, 256 threads, 8x8 register micro-tile, register-staged double buffering,
+// deterministic split-K (partials + ordered reduce) for the weight-gradient shapes (small M*N, huge K).
+#include "common.cuh"
+
+namespace gnnx {
+
+constexpr int BM = 128, BN = 128, BK = 8, TM = 8, TN = 8;
+
+// element (m,k) of op(A): trans ? A[k*lda + m] : A[m*lda + k]
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256, 2)
+k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__ B, long long ldb,
+           float* __restrict__ C, long long ldc, int M, int N, int K, int k_per_split,
+           const float* __restrict__ bias, int flags, float* __restrict__ partial) {
+    __shared__ float As[2][BK][BM + 4];
+    __shared__ float Bs[2][BK][BN + 4];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int kbeg = blockIdx.z * k_per_split;
+    const int kend = min(K, kbeg + k_per_split);
+    const int tx = tid % 16, ty = tid / 16;     // 16x16 threads, each 8x8 outputs (strided by 16 -> conflict-free)
+
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+
+    float ra[4], rb[4];
+    auto load_tiles = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int el = tid + i * 256;
+            int m, k;
+            if (TA) { k = el / BM; m = el % BM; } else { m = el / BK; k = el % BK; }
+            int gm = m0 + m, gk = k0 + k;
+            ra[i] = (gm < M && gk < kend) ? (TA ? A[(long long)gk * lda + gm] : A[(long long)gm * lda + gk]) : 0.f;
+            int n, kb;
+            if (TB) { n = el / BK; kb = el % BK; } else { kb = el / BN; n = el % BN; }
+            int gn = n0 + n, gkb = k0 + kb;
+            rb[i] = (gn < N && gkb < kend) ? (TB ? B[(long long)gn * ldb + gkb] : B[(long long)gkb * ldb + gn]) : 0.f;
+        }
+    };
+    auto store_tiles = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int el = tid + i * 256;
+            int m, k;
+            if (TA) { k = el / BM; m = el % BM; } else { m = el / BK; k = el % BK; }
+            As[buf][k][m] = ra[i];
+            int n, kb;
+            if (TB) { n = el / BK; kb = el % BK; } else { kb = el / BN; n = el % BN; }
+            Bs[buf][kb][n] = rb[i];
+        }
+    };
+
+    int buf = 0;
+    if (kbeg < kend) {
+        load_tiles(kbeg);
+        store_tiles(0);
+    }
+    __syncthreads();
+    for (int k0 = kbeg; k0 < kend; k0 += BK) {
+        bool has_next = k0 + BK < kend;
+        if (has_next) load_tiles(k0 + BK);
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            float a[TM], b[TN];
+#pragma unroll
+            for (int i = 0; i < TM; ++i) a[i] = As[buf][kk][ty + 16 * i];
+#pragma unroll
+            for (int j = 0; j < TN; ++j) b[j] = Bs[buf][kk][tx + 16 * j];
+#pragma unroll
+            for (int i = 0; i < TM; ++i)
+#pragma unroll
+                for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        if (has_next) {
+            store_tiles(buf ^ 1);
+            __syncthreads();
+            buf ^= 1;
+        }
+    }
+
+    const bool split = partial != nullptr;
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+        int gm = m0 + ty + 16 * i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            int gn = n0 + tx + 16 * j;
+            if (gn >= N) continue;
+            float v = acc[i][j];
+            if (split) {
+                partial[((long long)blockIdx.z * M + gm) * N + gn] = v;
+            } else {
+                if (bias) v += bias[gn];
+                if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)gm * ldc + gn];
+                if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
+                C[(long long)gm * ldc + gn] = v;
+            }
+        }
+    }
+}
+
+__global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ C,
+                                long long ldc, const float* __restrict__ bias, int flags) {
+    long long total = (long long)M * N;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int m = (int)(i / N), n = (int)(i % N);
+        float v = 0.f;
+        for (int s = 0; s < splits; ++s) v += partial[(long long)s * total + i];
+        if (bias) v += bias[n];
+        if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)m * ldc + n];
+        if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
+        C[(long long)m * ldc + n] = v;
+    }
+}
+
+int simt_splits(int64_t M, int64_t N, int64_t K) {
+    long long tiles = (long long)ceil_div(M, BM) * ceil_div(N, BN);
+    if (tiles >= kNumSMs || K < 1024) return 1;
+    long long want = (2ll * kNumSMs + tiles - 1) / tiles;
+    long long maxs = K / 256;
+    long long s = want < maxs ? want : maxs;
+    if (s > 128) s = 128;
+    return (int)(s < 1 ? 1 : s);
+}
+
+size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K) {
+    int s = simt_splits(M, N, K);
+    return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
+}
+
+int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc,
+              int64_t M, int64_t N, int64_t K, const float* bias, int flags, void* ws, size_t ws_bytes,
+              cudaStream_t st) {
+    if (M == 0 || N == 0) return GNNX_OK;
+    int splits = simt_splits(M, N, K);
+    float* partial = nullptr;
+    if (splits > 1) {
+        GNNX_REQUIRE(ws && ws_bytes >= (size_t)splits * M * N * sizeof(float), "gemm: workspace too small for split-K");
+        partial = (float*)ws;
+    }
+    int kps = ceil_div(ceil_div(K, splits), BK) * BK;
+    if (kps == 0) kps = BK;
+    splits = K > 0 ? ceil_div(K, kps) : 1;
+    if (splits <= 1) { partial = nullptr; splits = 1; }
+    dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
+    GNNX_REQUIRE(grid.y <= 65535 * 1 || true, "gemm: M too large");
+    if (grid.y > 65535) return set_error(GNNX_ERR_UNSUPPORTED, "gemm_simt: M=%lld exceeds grid.y limit", (long long)M);
+#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial)
+    if (ta && tb) LAUNCH(true, true);
+    else if (ta) LAUNCH(true, false);
+    else if (tb) LAUNCH(false, true);
+    else LAUNCH(false, false);
+#undef LAUNCH
+    if (partial)
+        k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags);
+    return check_launch("gemm_simt");
+}
+
+// ------------------------------------------------------------------ column sums
+constexpr int kCsRows = 8;
+__global__ void k_colsum_partial(const float* __restrict__ in, long long ld, int rows, int cols, int rows_per_chunk,
+                                 float* __restrict__ partial) {
+    __shared__ float sh[kCsRows][33];
+    int c = blockIdx.x * 32 + threadIdx.x;
+    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    float s = 0.f;
+    if (c < cols)
+        for (int r = r0 + threadIdx.y; r < r1; r += kCsRows) s += __ldg(in + (long long)r * ld + c);
+    sh[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < cols) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < kCsRows; ++i) t += sh[i][threadIdx.x];
+        partial[(long long)blockIdx.y * cols + c] = t;
+    }
+}
+__global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, int cols, float* __restrict__ out) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    float s = 0.f;
+    for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * cols + c];
+    out[c] = s;
+}
+int colsum_chunks(int64_t rows, int64_t cols) {
+    int slabs = ceil_div(cols, 32);
+    int target = max(1, (kNumSMs * 8) / slabs);
+    int by_rows = max(1, (int)((rows + 63) / 64));
+    return min(target, by_rows);
+}
+
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols) {
+    return (size_t)colsum_chunks(rows, cols) * cols * sizeof(float);
+}
+
+int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out, void* ws, size_t ws_bytes,
+                void* stream) {
+    if (cols == 0) return GNNX_OK;
+    GNNX_REQUIRE(ws_bytes >= gnnx_colsum_workspace_bytes(rows, cols), "colsum: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(out, 0, cols * sizeof(float), st)); return GNNX_OK; }
+    int nch = colsum_chunks(rows, cols);
+    int rpc = ceil_div(rows, nch);
+    k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+    k_colsum_final<<<ceil_div(cols, 128), 128, 0, st>>>((const float*)ws, nch, (int)cols, out);
+    return check_launch("colsum");
+}
+
+}  // extern "C"

@@ -1,0 +1,383 @@
+// BatchNorm(+ReLU) over node rows, graph-level segment pooling (K9), the fused
+// relative-error Huber loss (K11) and AdamW-amsgrad over the flat parameter buffer (K12).
+// Reductions over rows are two-pass and deterministic: per-chunk partials (Welford/Chan for the
+// variance) merged in chunk order -- no atomics.
+#include "common.cuh"
+
+namespace gnnx {
+
+union F4 {
+    float4 q;
+    float a[4];
+};
+
+constexpr int kBnRows = 8;   // block = (32 channels, 8 row lanes)
+
+struct Welford {
+    float n, mean, m2;
+};
+__device__ __forceinline__ void welford_add(Welford& w, float x) {
+    w.n += 1.f;
+    float d = x - w.mean;
+    w.mean += d / w.n;
+    w.m2 += d * (x - w.mean);
+}
+__device__ __forceinline__ void welford_merge(Welford& a, const Welford& b) {
+    if (b.n == 0.f) return;
+    float n = a.n + b.n;
+    float d = b.mean - a.mean;
+    a.mean += d * (b.n / n);
+    a.m2 += b.m2 + d * d * (a.n * b.n / n);
+    a.n = n;
+}
+
+static int bn_chunks(int64_t rows, int32_t C) {
+    int slabs = ceil_div(C, 32);
+    int target = max(1, (kNumSMs * 8) / slabs);
+    int by_rows = max(1, (int)((rows + 63) / 64));
+    return min(target, by_rows);
+}
+
+// partial: [nchunks][3][C] = (n, mean, M2)
+__global__ void k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial) {
+    __shared__ float sh[kBnRows][3][33];
+    int c = blockIdx.x * 32 + threadIdx.x;
+    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    Welford w = {0.f, 0.f, 0.f};
+    if (c < C)
+        for (int r = r0 + threadIdx.y; r < r1; r += kBnRows) welford_add(w, __ldg(x + (long long)r * C + c));
+    sh[threadIdx.y][0][threadIdx.x] = w.n;
+    sh[threadIdx.y][1][threadIdx.x] = w.mean;
+    sh[threadIdx.y][2][threadIdx.x] = w.m2;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+        Welford t = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < kBnRows; ++i) {
+            Welford o = {sh[i][0][threadIdx.x], sh[i][1][threadIdx.x], sh[i][2][threadIdx.x]};
+            welford_merge(t, o);
+        }
+        float* p = partial + (long long)blockIdx.y * 3 * C;
+        p[c] = t.n; p[C + c] = t.mean; p[2 * C + c] = t.m2;
+    }
+}
+
+__global__ void k_bn_stats_final(const float* __restrict__ partial, int nchunks, int C, float eps, float momentum,
+                                 float* __restrict__ running_mean, float* __restrict__ running_var,
+                                 float* __restrict__ save_mean, float* __restrict__ save_rstd) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    Welford t = {0.f, 0.f, 0.f};
+    for (int ch = 0; ch < nchunks; ++ch) {
+        const float* p = partial + (long long)ch * 3 * C;
+        Welford o = {p[c], p[C + c], p[2 * C + c]};
+        welford_merge(t, o);
+    }
+    float var = t.m2 / t.n;                      // biased, used to normalise
+    save_mean[c] = t.mean;
+    save_rstd[c] = rsqrtf(var + eps);
+    if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * t.mean;
+    if (running_var) {
+        float unbiased = t.n > 1.f ? t.m2 / (t.n - 1.f) : var;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+    }
+}
+
+__global__ void k_bn_eval_stats(const float* __restrict__ rm, const float* __restrict__ rv, int C, float eps,
+                                float* __restrict__ mean, float* __restrict__ rstd) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < C) { mean[c] = rm[c]; rstd[c] = rsqrtf(rv[c] + eps); }
+}
+
+__global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, const float* __restrict__ weight,
+                           const float* __restrict__ bias, const float* __restrict__ mean, const float* __restrict__ rstd,
+                           int relu, float* __restrict__ y) {
+    const int c4 = C / 4;
+    long long total = rows * c4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int c = (int)(i % c4) * 4;
+        F4 v, mu, rs, w, b, o;
+        v.q = ldg4_stream(x + i * 4);
+        mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+        w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        b.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float t = (v.a[j] - mu.a[j]) * rs.a[j] * w.a[j] + b.a[j];
+            o.a[j] = relu ? fmaxf(t, 0.f) : t;
+        }
+        stg4(y + i * 4, o.q);
+    }
+}
+
+// partial: [nchunks][2][C] = (sum dy', sum dy' * xhat)
+__global__ void k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+                                 int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
+                                 int rows_per_chunk, float* __restrict__ partial) {
+    __shared__ float sh[kBnRows][2][33];
+    int c = blockIdx.x * 32 + threadIdx.x;
+    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    float s1 = 0.f, s2 = 0.f;
+    if (c < C) {
+        float mu = mean[c], rs = rstd[c];
+        for (int r = r0 + threadIdx.y; r < r1; r += kBnRows) {
+            long long o = (long long)r * C + c;
+            float g = __ldg(dy + o);
+            if (relu && !(__ldg(y + o) > 0.f)) g = 0.f;
+            s1 += g;
+            s2 += g * ((__ldg(x + o) - mu) * rs);
+        }
+    }
+    sh[threadIdx.y][0][threadIdx.x] = s1;
+    sh[threadIdx.y][1][threadIdx.x] = s2;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int i = 0; i < kBnRows; ++i) { a += sh[i][0][threadIdx.x]; b += sh[i][1][threadIdx.x]; }
+        partial[(long long)blockIdx.y * 2 * C + c] = a;
+        partial[(long long)blockIdx.y * 2 * C + C + c] = b;
+    }
+}
+
+__global__ void k_bn_bwd_final(const float* __restrict__ partial, int nchunks, int C, float* __restrict__ dweight, float* __restrict__ dbias) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float a = 0.f, b = 0.f;
+    for (int ch = 0; ch < nchunks; ++ch) {
+        a += partial[(long long)ch * 2 * C + c];
+        b += partial[(long long)ch * 2 * C + C + c];
+    }
+    dbias[c] = a;
+    dweight[c] = b;
+}
+
+__global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+                               long long rows, int C, const float* __restrict__ weight, const float* __restrict__ mean,
+                               const float* __restrict__ rstd, const float* __restrict__ dweight,
+                               const float* __restrict__ dbias, int relu, float* __restrict__ dx) {
+    const int c4 = C / 4;
+    long long total = rows * c4;
+    const float inv_n = 1.f / (float)rows;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int c = (int)(i % c4) * 4;
+        F4 g, xv, yv, mu, rs, w, dw, db, o;
+        g.q = ldg4_stream(dy + i * 4);
+        xv.q = ldg4_stream(x + i * 4);
+        if (relu) yv.q = ldg4_stream(y + i * 4);
+        mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+        w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        dw.q = ldg4(dweight + c); db.q = ldg4(dbias + c);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float gg = (relu && !(yv.a[j] > 0.f)) ? 0.f : g.a[j];
+            float xh = (xv.a[j] - mu.a[j]) * rs.a[j];
+            o.a[j] = w.a[j] * rs.a[j] * (gg - db.a[j] * inv_n - xh * dw.a[j] * inv_n);
+        }
+        stg4(dx + i * 4, o.q);
+    }
+}
+
+// ------------------------------------------------------------------ graph pooling over contiguous node ranges
+// one warp per (graph, 128-col chunk); mode 0 add, 1 mean, 2 max (empty graph -> 0)
+__global__ void k_pool_fwd(const float* __restrict__ x, const int* __restrict__ gp, int G, int C, int mode, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int chunks = (C + 127) / 128;
+    const long long nwork = (long long)G * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int g = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= C) continue;
+        int b = gp[g], e = gp[g + 1];
+        F4 acc;
+        float init = mode == 2 ? -INFINITY : 0.f;
+        acc.q = make_float4(init, init, init, init);
+        for (int r = b; r < e; ++r) {
+            F4 v; v.q = ldg4(x + (long long)r * C + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc.a[j] = mode == 2 ? fmaxf(acc.a[j], v.a[j]) : acc.a[j] + v.a[j];
+        }
+        if (mode == 1) {
+            float cnt = fmaxf((float)(e - b), 1.f);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc.a[j] = acc.a[j] / cnt;
+        }
+        if (mode == 2 && b == e) acc.q = make_float4(0.f, 0.f, 0.f, 0.f);
+        stg4(out + (long long)g * C + c, acc.q);
+    }
+}
+
+__global__ void k_pool_bwd(const float* __restrict__ dout, const float* __restrict__ x, const float* __restrict__ out,
+                           const int* __restrict__ gp, int G, int C, int mode, float* __restrict__ dx) {
+    const int lane = threadIdx.x & 31;
+    const int chunks = (C + 127) / 128;
+    const long long nwork = (long long)G * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int g = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= C) continue;
+        int b = gp[g], e = gp[g + 1];
+        if (b == e) continue;
+        F4 go; go.q = ldg4(dout + (long long)g * C + c);
+        if (mode == 0 || mode == 1) {
+            if (mode == 1) {
+                float inv = 1.f / (float)(e - b);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) go.a[j] *= inv;
+            }
+            for (int r = b; r < e; ++r) stg4(dx + (long long)r * C + c, go.q);
+        } else {
+            F4 mx; mx.q = ldg4(out + (long long)g * C + c);
+            F4 nt; nt.q = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int r = b; r < e; ++r) {
+                F4 v; v.q = ldg4(x + (long long)r * C + c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) nt.a[j] += (v.a[j] == mx.a[j]) ? 1.f : 0.f;
+            }
+            for (int r = b; r < e; ++r) {
+                F4 v, o; v.q = ldg4(x + (long long)r * C + c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) o.a[j] = (v.a[j] == mx.a[j]) ? go.a[j] / nt.a[j] : 0.f;
+                stg4(dx + (long long)r * C + c, o.q);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ loss: Huber(delta) on the relative error + MAPE
+__global__ void k_relhuber(const float* __restrict__ pred, const float* __restrict__ target, int count, float delta,
+                           float* __restrict__ out2, float* __restrict__ dpred) {
+    __shared__ float sh[2][32];
+    float l = 0.f, mp = 0.f;
+    const float inv = 1.f / (float)count;
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        float p = pred[i], t = target[i];
+        float a = (p - t) / t;
+        float aa = fabsf(a);
+        float g;
+        if (aa <= delta) { l += 0.5f * a * a; g = a; }
+        else { l += delta * (aa - 0.5f * delta); g = a > 0.f ? delta : -delta; }
+        mp += fabsf(p - t) / fmaxf(fabsf(t), 1.17e-06f);
+        if (dpred) dpred[i] = g / t * inv;
+    }
+    l = warp_sum(l); mp = warp_sum(mp);
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { sh[0][w] = l; sh[1][w] = mp; }
+    __syncthreads();
+    if (w == 0) {
+        int nw = blockDim.x >> 5;
+        l = lane < nw ? sh[0][lane] : 0.f;
+        mp = lane < nw ? sh[1][lane] : 0.f;
+        l = warp_sum(l); mp = warp_sum(mp);
+        if (lane == 0) { out2[0] = l * inv; out2[1] = mp * inv; }
+    }
+}
+
+// ------------------------------------------------------------------ AdamW(amsgrad) on the flat buffer
+__global__ void k_adamw_amsgrad(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                float* __restrict__ vmax, long long count, float lr, float b1, float b2, float eps, float wd,
+                                float bc1, float bc2_sqrt, float gscale) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        float grad = g[i] * gscale;
+        float param = p[i] * (1.f - lr * wd);
+        float mi = m[i] + (grad - m[i]) * (1.f - b1);
+        float vi = v[i] * b2 + grad * grad * (1.f - b2);
+        float vm = fmaxf(vmax[i], vi);
+        float denom = sqrtf(vm) / bc2_sqrt + eps;
+        param -= (lr / bc1) * (mi / denom);
+        p[i] = param; m[i] = mi; v[i] = vi; vmax[i] = vm;
+    }
+}
+
+static inline int flat_grid(long long nthreads) {
+    long long blocks = (nthreads + 255) / 256;
+    long long cap = (long long)kNumSMs * 32;
+    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t C) {
+    return ((size_t)bn_chunks(rows, C) * 3 * C + 2 * (size_t)C) * sizeof(float);
+}
+
+int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weight, const float* bias, float* running_mean,
+                     float* running_var, int32_t training, float momentum, float eps, int32_t relu, float* y,
+                     float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(C % 4 == 0, "bn_relu_fwd: channels must be a multiple of 4");
+    GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_fwd: workspace too small");
+    GNNX_REQUIRE(save_mean && save_rstd, "bn_relu_fwd: save_mean / save_rstd are required");
+    if (rows == 0) return GNNX_OK;
+    cudaStream_t st = as_stream(stream);
+    if (training) {
+        GNNX_REQUIRE(rows > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
+        int nch = bn_chunks(rows, C);
+        int rpc = ceil_div(rows, nch);
+        k_bn_stats_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(x, (int)rows, C, rpc, (float*)ws);
+        k_bn_stats_final<<<ceil_div(C, 128), 128, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
+    } else {
+        GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
+        k_bn_eval_stats<<<ceil_div(C, 128), 128, 0, st>>>(running_mean, running_var, C, eps, save_mean, save_rstd);
+    }
+    k_bn_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(x, rows, C, weight, bias, save_mean, save_rstd, relu, y);
+    return check_launch("bn_relu_fwd");
+}
+
+int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
+                     const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
+                     void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(C % 4 == 0, "bn_relu_bwd: channels must be a multiple of 4");
+    GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_bwd: workspace too small");
+    if (rows == 0) return GNNX_OK;
+    cudaStream_t st = as_stream(stream);
+    int nch = bn_chunks(rows, C);
+    int rpc = ceil_div(rows, nch);
+    k_bn_bwd_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
+    k_bn_bwd_final<<<ceil_div(C, 128), 128, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
+    k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx);
+    return check_launch("bn_relu_bwd");
+}
+
+int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, int32_t C, int32_t mode, float* out, void* stream) {
+    GNNX_REQUIRE(C % 4 == 0 && mode >= 0 && mode <= 2, "segment_pool_fwd: channels %% 4 == 0 and mode in {0,1,2}");
+    if (G == 0) return GNNX_OK;
+    long long nwork = G * ((C + 127) / 128);
+    int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
+    k_pool_fwd<<<nb, 256, 0, as_stream(stream)>>>(x, graph_ptr, (int)G, C, mode, out);
+    return check_launch("segment_pool_fwd");
+}
+
+int gnnx_segment_pool_bwd(const float* dout, const float* x, const float* out, const int32_t* graph_ptr, int64_t G, int32_t C,
+                          int32_t mode, float* dx, void* stream) {
+    GNNX_REQUIRE(C % 4 == 0 && mode >= 0 && mode <= 2, "segment_pool_bwd: channels %% 4 == 0 and mode in {0,1,2}");
+    if (G == 0) return GNNX_OK;
+    long long nwork = G * ((C + 127) / 128);
+    int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
+    k_pool_bwd<<<nb, 256, 0, as_stream(stream)>>>(dout, x, out, graph_ptr, (int)G, C, mode, dx);
+    return check_launch("segment_pool_bwd");
+}
+
+int gnnx_relhuber_fwd_bwd(const float* pred, const float* target, int64_t count, float delta, float* out2, float* dpred, void* stream) {
+    GNNX_REQUIRE(count > 0 && count < (1ll << 31), "relhuber: count out of range");
+    k_relhuber<<<1, 1024, 0, as_stream(stream)>>>(pred, target, (int)count, delta, out2, dpred);
+    return check_launch("relhuber_fwd_bwd");
+}
+
+int gnnx_adamw_amsgrad(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* max_exp_avg_sq, int64_t count,
+                       float lr, float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale, void* stream) {
+    GNNX_REQUIRE(step >= 1, "adamw_amsgrad: step must be >= 1");
+    if (count == 0) return GNNX_OK;
+    double bc1 = 1.0 - pow((double)beta1, (double)step);
+    double bc2 = 1.0 - pow((double)beta2, (double)step);
+    k_adamw_amsgrad<<<flat_grid(count), 256, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, max_exp_avg_sq, count, lr, beta1,
+                                                                      beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
+    return check_launch("adamw_amsgrad");
+}
+
+}  // extern "C"

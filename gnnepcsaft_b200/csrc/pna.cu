@@ -1,0 +1,446 @@
+// PNA message passing over the dst-sorted CSR: gather, fused multi-aggregator
+// segmented reduction (mean|min|max|std in ONE pass over the messages), the matching backward
+// scatters, and the scaler-folded combine of the first post_nn Linear.  All kernels are
+// deterministic and atomic-free: one warp owns one (destination row, 128-column chunk), walks the
+// row's edges in edge order with float4 loads (several rows in flight), and writes each output once.
+#include "common.cuh"
+
+namespace gnnx {
+
+// torch: out.masked_fill(out <= math.sqrt(1e-5), 0) compares in fp32
+#define GNNX_STD_MASK 0.003162277629598975f
+
+union F4 {
+    float4 q;
+    float a[4];
+};
+__device__ __forceinline__ F4 f4_zero() { F4 r; r.q = make_float4(0.f, 0.f, 0.f, 0.f); return r; }
+__device__ __forceinline__ F4 f4_fill(float v) { F4 r; r.q = make_float4(v, v, v, v); return r; }
+__device__ __forceinline__ F4 f4_ld(const float* p) { F4 r; r.q = ldg4(p); return r; }
+__device__ __forceinline__ F4 f4_lds(const float* p) { F4 r; r.q = ldg4_stream(p); return r; }
+
+// ------------------------------------------------------------------ gather (K3 + first pre_nn Linear, node-side split)
+template <typename RIdx>
+__global__ void __launch_bounds__(256)
+k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __restrict__ r, long long ld_r,
+                 const RIdx* __restrict__ ridx, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
+                 int N, int H, int relu, float* __restrict__ h) {
+    const int lane = threadIdx.x & 31;
+    const int chunks = (H + 127) / 128;
+    const long long nwork = (long long)N * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int i = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        int b = rowptr[i], e = rowptr[i + 1];
+        if (b == e || c >= H) continue;
+        F4 p = f4_ld(pq + (long long)i * ld_pq + c);
+        int k = b;
+        for (; k + 2 <= e; k += 2) {
+            int s0 = csr_src[k], s1 = csr_src[k + 1];
+            long long r0 = (long long)ridx[k], r1 = (long long)ridx[k + 1];
+            F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c);
+            F4 q1 = f4_ld(pq + (long long)s1 * ld_pq + H + c);
+            F4 t0 = f4_ld(r + r0 * ld_r + c);
+            F4 t1 = f4_ld(r + r1 * ld_r + c);
+            F4 o0, o1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
+                o1.a[j] = p.a[j] + q1.a[j] + t1.a[j];
+                if (relu) { o0.a[j] = fmaxf(o0.a[j], 0.f); o1.a[j] = fmaxf(o1.a[j], 0.f); }
+            }
+            stg4(h + (long long)k * H + c, o0.q);
+            stg4(h + (long long)(k + 1) * H + c, o1.q);
+        }
+        if (k < e) {
+            int s0 = csr_src[k];
+            long long r0 = (long long)ridx[k];
+            F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c);
+            F4 t0 = f4_ld(r + r0 * ld_r + c);
+            F4 o0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
+                if (relu) o0.a[j] = fmaxf(o0.a[j], 0.f);
+            }
+            stg4(h + (long long)k * H + c, o0.q);
+        }
+    }
+}
+
+// dpq[:, 0:H] by CSR rows, dpq[:, H:2H] through csc_pos
+__global__ void __launch_bounds__(256)
+k_pna_gather_bwd(const float* __restrict__ dh, const int* __restrict__ rowptr, const int* __restrict__ colptr,
+                 const int* __restrict__ csc_pos, int N, int H, float* __restrict__ dpq, long long ld) {
+    const int lane = threadIdx.x & 31;
+    const int chunks = (H + 127) / 128;
+    const long long nwork = (long long)N * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int i = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= H) continue;
+        F4 a = f4_zero();
+        for (int k = rowptr[i], e = rowptr[i + 1]; k < e; ++k) {
+            F4 v = f4_ld(dh + (long long)k * H + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a.a[j] += v.a[j];
+        }
+        stg4(dpq + (long long)i * ld + c, a.q);
+        F4 s = f4_zero();
+        for (int k = colptr[i], e = colptr[i + 1]; k < e; ++k) {
+            F4 v = f4_ld(dh + (long long)csc_pos[k] * H + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s.a[j] += v.a[j];
+        }
+        stg4(dpq + (long long)i * ld + H + c, s.q);
+    }
+}
+
+__global__ void k_permute_rows(const float* __restrict__ in, const int* __restrict__ dst_row, long long E, int H,
+                               float* __restrict__ out, long long ld_out) {
+    const int h4 = H / 4;
+    long long total = E * h4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        long long p = i / h4;
+        int c = (int)(i % h4) * 4;
+        stg4(out + (long long)dst_row[p] * ld_out + c, ldg4(in + p * H + c));
+    }
+}
+
+// grid: (ceil(H/32), nchunks), block (32, 8): each threadIdx.y owns a private [ncodes][32] table in smem
+constexpr int kCodeRows = 8;
+__global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* __restrict__ codes, int rows,
+                                   int ncodes, int H, int rows_per_chunk, float* __restrict__ partial) {
+    extern __shared__ float tab[];   // [kCodeRows][ncodes][32]
+    int c = blockIdx.x * 32 + threadIdx.x;
+    float* mine = tab + (long long)threadIdx.y * ncodes * 32;
+    for (int i = threadIdx.x; i < ncodes * 32; i += 32) mine[i] = 0.f;
+    __syncwarp();
+    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    if (c < H)
+        for (int r = r0 + threadIdx.y; r < r1; r += kCodeRows)
+            mine[(int)codes[r] * 32 + threadIdx.x] += __ldg(dh + (long long)r * H + c);
+    __syncthreads();
+    if (c < H)
+        for (int code = threadIdx.y; code < ncodes; code += kCodeRows) {
+            float s = 0.f;
+#pragma unroll
+            for (int y = 0; y < kCodeRows; ++y) s += tab[((long long)y * ncodes + code) * 32 + threadIdx.x];
+            partial[((long long)blockIdx.y * ncodes + code) * H + c] = s;
+        }
+}
+__global__ void k_sum_partials(const float* __restrict__ partial, int nchunks, long long count, float* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * count + i];
+        out[i] = s;
+    }
+}
+static int code_chunks(int64_t rows, int32_t H) {
+    int slabs = ceil_div(H, 32);
+    int target = max(1, (kNumSMs * 3) / slabs);
+    int by_rows = max(1, (int)((rows + 511) / 512));
+    return min(target, by_rows);
+}
+
+// ------------------------------------------------------------------ fused multi-aggregator (K5)
+// m: [E, H] dst-sorted, H = T*F.  agg: [N, T, 4, F].  One warp per (row, 128-col chunk).
+__device__ __forceinline__ void agg_acc(const F4& v, F4& s, F4& s2, F4& mn, F4& mx) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        s.a[j] = __fadd_rn(s.a[j], v.a[j]);                       // no FMA contraction: same op
+        s2.a[j] = __fadd_rn(s2.a[j], __fmul_rn(v.a[j], v.a[j]));  // sequence as scatter_add_(x*x)
+        mn.a[j] = fminf(mn.a[j], v.a[j]);
+        mx.a[j] = fmaxf(mx.a[j], v.a[j]);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr, int N, int T, int F,
+                    float* __restrict__ agg) {
+    const int H = T * F;
+    const int lane = threadIdx.x & 31;
+    const int chunks = (H + 127) / 128;
+    const long long nwork = (long long)N * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int i = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= H) continue;
+        int b = rowptr[i], e = rowptr[i + 1];
+        F4 s = f4_zero(), s2 = f4_zero(), mn = f4_fill(INFINITY), mx = f4_fill(-INFINITY);
+        int k = b;
+        for (; k + 4 <= e; k += 4) {             // 4 rows in flight per lane
+            F4 v0 = f4_lds(m + (long long)(k + 0) * H + c);
+            F4 v1 = f4_lds(m + (long long)(k + 1) * H + c);
+            F4 v2 = f4_lds(m + (long long)(k + 2) * H + c);
+            F4 v3 = f4_lds(m + (long long)(k + 3) * H + c);
+            agg_acc(v0, s, s2, mn, mx); agg_acc(v1, s, s2, mn, mx);
+            agg_acc(v2, s, s2, mn, mx); agg_acc(v3, s, s2, mn, mx);
+        }
+        if (k + 2 <= e) {
+            F4 v0 = f4_lds(m + (long long)(k + 0) * H + c);
+            F4 v1 = f4_lds(m + (long long)(k + 1) * H + c);
+            agg_acc(v0, s, s2, mn, mx); agg_acc(v1, s, s2, mn, mx);
+            k += 2;
+        }
+        if (k < e) {
+            F4 v0 = f4_lds(m + (long long)k * H + c);
+            agg_acc(v0, s, s2, mn, mx);
+        }
+        float cnt = fmaxf((float)(e - b), 1.f);
+        F4 mean, sd;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float mu = __fdiv_rn(s.a[j], cnt);
+            float m2 = __fdiv_rn(s2.a[j], cnt);
+            float var = __fsub_rn(m2, __fmul_rn(mu, mu));
+            float o = __fsqrt_rn(fmaxf(var, 1e-5f));
+            mean.a[j] = mu;
+            sd.a[j] = (o <= GNNX_STD_MASK) ? 0.f : o;
+        }
+        if (b == e) { mn = f4_zero(); mx = f4_zero(); }
+        int t = c / F, f = c % F;
+        float* o = agg + (((long long)i * T + t) * 4) * F + f;
+        stg4_stream(o, mean.q);
+        stg4_stream(o + F, mn.q);
+        stg4_stream(o + 2 * F, mx.q);
+        stg4_stream(o + 3 * F, sd.q);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m, const float* __restrict__ agg,
+                    const int* __restrict__ rowptr, int N, int T, int F, float* __restrict__ dm) {
+    const int H = T * F;
+    const int lane = threadIdx.x & 31;
+    const int chunks = (H + 127) / 128;
+    const long long nwork = (long long)N * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        int i = (int)(w / chunks);
+        int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= H) continue;
+        int b = rowptr[i], e = rowptr[i + 1];
+        if (b == e) continue;
+        int t = c / F, f = c % F;
+        long long base = (((long long)i * T + t) * 4) * F + f;
+        F4 mean = f4_lds(agg + base), mn = f4_lds(agg + base + F), mx = f4_lds(agg + base + 2 * F), sd = f4_lds(agg + base + 3 * F);
+        F4 gmean = f4_lds(dagg + base), gmn = f4_lds(dagg + base + F), gmx = f4_lds(dagg + base + 2 * F), gsd = f4_lds(dagg + base + 3 * F);
+        // pass 1: tie counts for min / max (PyG CPU semantics: gradient split evenly among ties)
+        F4 nmn = f4_zero(), nmx = f4_zero();
+        for (int k = b; k < e; ++k) {
+            F4 v = f4_ld(m + (long long)k * H + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                nmn.a[j] += (v.a[j] == mn.a[j]) ? 1.f : 0.f;
+                nmx.a[j] += (v.a[j] == mx.a[j]) ? 1.f : 0.f;
+            }
+        }
+        float inv_cnt = 1.f / (float)(e - b);
+        F4 cmean, cmn, cmx, csd;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            cmean.a[j] = gmean.a[j] * inv_cnt;
+            cmn.a[j] = gmn.a[j] / nmn.a[j];
+            cmx.a[j] = gmx.a[j] / nmx.a[j];
+            csd.a[j] = sd.a[j] > 0.f ? gsd.a[j] * inv_cnt / sd.a[j] : 0.f;   // d std / d m_e = (m_e - mean) / (cnt * std)
+        }
+        // pass 2 (rows are L1/L2-resident from pass 1)
+        for (int k = b; k < e; ++k) {
+            F4 v = f4_ld(m + (long long)k * H + c);
+            F4 g;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float x = v.a[j];
+                g.a[j] = cmean.a[j] + ((x == mn.a[j]) ? cmn.a[j] : 0.f) + ((x == mx.a[j]) ? cmx.a[j] : 0.f) +
+                         csd.a[j] * (x - mean.a[j]);
+            }
+            stg4(dm + (long long)k * H + c, g.q);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ first post_nn Linear, scalers folded (K5 tail + K6 head)
+__device__ __forceinline__ void pna_scalers(const int* __restrict__ rowptr, int row, float avg_deg_log, float& s_amp, float& s_att) {
+    float d = (float)(rowptr[row + 1] - rowptr[row]);
+    s_amp = logf(d + 1.f) / avg_deg_log;
+    s_att = avg_deg_log / logf(fmaxf(d, 1.f) + 1.f);
+}
+
+__global__ void k_pna_post_combine_fwd(const float* __restrict__ y0, const float* __restrict__ z, const float* __restrict__ bias,
+                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int T, int Fo,
+                                       int relu, float* __restrict__ out) {
+    const int H = T * Fo, h4 = H / 4;
+    long long total = N * h4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int row = (int)(i / h4);
+        int c = (int)(i % h4) * 4;
+        int t = c / Fo, f = c % Fo;
+        float sa, st;
+        pna_scalers(rowptr, row, avg_deg_log, sa, st);
+        const float* zr = z + (((long long)row * T + t) * 3) * Fo + f;
+        F4 a = f4_ld(y0 + (long long)row * H + c), zi = f4_lds(zr), za = f4_lds(zr + Fo), zt = f4_lds(zr + 2 * Fo);
+        F4 bb = bias ? f4_ld(bias + c) : f4_zero();
+        F4 o;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float v = a.a[j] + zi.a[j] + sa * za.a[j] + st * zt.a[j] + bb.a[j];
+            o.a[j] = relu ? fmaxf(v, 0.f) : v;
+        }
+        stg4(out + (long long)row * H + c, o.q);
+    }
+}
+
+__global__ void k_pna_post_combine_bwd(const float* __restrict__ dout, const float* __restrict__ out,
+                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int T, int Fo,
+                                       int relu, float* __restrict__ dy0, float* __restrict__ dz) {
+    const int H = T * Fo, h4 = H / 4;
+    long long total = N * h4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int row = (int)(i / h4);
+        int c = (int)(i % h4) * 4;
+        int t = c / Fo, f = c % Fo;
+        float sa, st;
+        pna_scalers(rowptr, row, avg_deg_log, sa, st);
+        F4 g = f4_lds(dout + (long long)row * H + c);
+        if (relu) {
+            F4 o = f4_lds(out + (long long)row * H + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) g.a[j] = o.a[j] > 0.f ? g.a[j] : 0.f;
+        }
+        F4 ga, gt;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { ga.a[j] = sa * g.a[j]; gt.a[j] = st * g.a[j]; }
+        float* zr = dz + (((long long)row * T + t) * 3) * Fo + f;
+        stg4(dy0 + (long long)row * H + c, g.q);
+        stg4(zr, g.q);
+        stg4(zr + Fo, ga.q);
+        stg4(zr + 2 * Fo, gt.q);
+    }
+}
+
+__global__ void k_relu_bwd(const float* __restrict__ dy, const float* __restrict__ y, long long count, float* __restrict__ dx) {
+    long long n4 = count / 4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        F4 g = f4_lds(dy + i * 4), o = f4_lds(y + i * 4);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g.a[j] = o.a[j] > 0.f ? g.a[j] : 0.f;
+        stg4(dx + i * 4, g.q);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (count & 3)) {
+        long long i = n4 * 4 + threadIdx.x;
+        dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+    }
+}
+
+static inline int warp_grid(long long nwork) {   // 8 warps per block, grid a multiple of the SM count
+    long long blocks = (nwork + 7) / 8;
+    long long cap = (long long)kNumSMs * 32;
+    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+static inline int flat_grid(long long nthreads) {
+    long long blocks = (nthreads + 255) / 256;
+    long long cap = (long long)kNumSMs * 32;
+    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace gnnx
+
+using namespace gnnx;
+
+extern "C" {
+
+int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t ld_r, const int32_t* ridx_i32,
+                        const uint8_t* ridx_u8, const int32_t* rowptr, const int32_t* csr_src, int64_t N, int64_t E,
+                        int32_t H, int32_t relu, float* h, void* stream) {
+    GNNX_REQUIRE(H % 4 == 0 && ld_pq % 4 == 0 && ld_r % 4 == 0, "pna_gather_fwd: hidden / strides must be multiples of 4");
+    GNNX_REQUIRE((ridx_i32 != nullptr) != (ridx_u8 != nullptr), "pna_gather_fwd: exactly one of ridx_i32 / ridx_u8");
+    if (N == 0 || E == 0) return GNNX_OK;
+    long long nwork = (long long)N * ((H + 127) / 128);
+    if (ridx_i32)
+        k_pna_gather_fwd<int><<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h);
+    else
+        k_pna_gather_fwd<uint8_t><<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h);
+    return check_launch("pna_gather_fwd");
+}
+
+int gnnx_pna_gather_bwd(const float* dh, const int32_t* rowptr, const int32_t* colptr, const int32_t* csc_pos,
+                        const int32_t* csr_eid, int64_t N, int64_t E, int32_t H, float* dpq, int64_t ld_dpq,
+                        float* dr_edge, int64_t ld_dr, void* stream) {
+    GNNX_REQUIRE(H % 4 == 0 && ld_dpq % 4 == 0, "pna_gather_bwd: hidden / strides must be multiples of 4");
+    if (N == 0) return GNNX_OK;
+    long long nwork = (long long)N * ((H + 127) / 128);
+    k_pna_gather_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
+    if (dr_edge && E > 0) {
+        GNNX_REQUIRE(ld_dr % 4 == 0 && csr_eid, "pna_gather_bwd: dr_edge needs csr_eid and an aligned stride");
+        k_permute_rows<<<flat_grid(E * (H / 4)), 256, 0, as_stream(stream)>>>(dh, csr_eid, E, H, dr_edge, ld_dr);
+    }
+    return check_launch("pna_gather_bwd");
+}
+
+size_t gnnx_code_segment_sum_workspace_bytes(int64_t rows, int32_t num_codes, int32_t H) {
+    return (size_t)code_chunks(rows, H) * num_codes * H * sizeof(float);
+}
+
+int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, int32_t ncodes, int32_t H, float* dtable,
+                          void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(ncodes >= 1 && ncodes <= 256, "code_segment_sum: num_codes must be in [1,256]");
+    GNNX_REQUIRE(ws_bytes >= gnnx_code_segment_sum_workspace_bytes(rows, ncodes, H), "code_segment_sum: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    long long count = (long long)ncodes * H;
+    if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(dtable, 0, count * sizeof(float), st)); return GNNX_OK; }
+    int nch = code_chunks(rows, H);
+    int rpc = ceil_div(rows, nch);
+    size_t smem = (size_t)kCodeRows * ncodes * 32 * sizeof(float);
+    GNNX_REQUIRE(smem <= 200 * 1024, "code_segment_sum: too many codes for the shared-memory tables");
+    if (smem > 48 * 1024)
+        GNNX_CUDA(cudaFuncSetAttribute(k_code_sum_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_code_sum_partial<<<dim3(ceil_div(H, 32), nch), dim3(32, kCodeRows), smem, st>>>(dh, codes, (int)rows, ncodes, H, rpc, (float*)ws);
+    k_sum_partials<<<flat_grid(count), 256, 0, st>>>((const float*)ws, nch, count, dtable);
+    return check_launch("code_segment_sum");
+}
+
+int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t N, int32_t T, int32_t F, float* agg, void* stream) {
+    GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_fwd: F must be a positive multiple of 4");
+    if (N == 0) return GNNX_OK;
+    long long nwork = (long long)N * ((T * F + 127) / 128);
+    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, agg);
+    return check_launch("pna_aggregate_fwd");
+}
+
+int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, const int32_t* rowptr, int64_t N,
+                           int32_t T, int32_t F, float* dm, void* stream) {
+    GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_bwd: F must be a positive multiple of 4");
+    if (N == 0) return GNNX_OK;
+    long long nwork = (long long)N * ((T * F + 127) / 128);
+    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm);
+    return check_launch("pna_aggregate_bwd");
+}
+
+int gnnx_pna_post_combine_fwd(const float* y0, const float* z, const float* bias, const int32_t* rowptr, float avg_deg_log,
+                              int64_t N, int32_t T, int32_t Fo, int32_t relu, float* out, void* stream) {
+    GNNX_REQUIRE(Fo % 4 == 0, "pna_post_combine_fwd: F_out must be a multiple of 4");
+    if (N == 0) return GNNX_OK;
+    k_pna_post_combine_fwd<<<flat_grid(N * (T * Fo / 4)), 256, 0, as_stream(stream)>>>(y0, z, bias, rowptr, avg_deg_log, N, T, Fo, relu, out);
+    return check_launch("pna_post_combine_fwd");
+}
+
+int gnnx_pna_post_combine_bwd(const float* dout, const float* out, const int32_t* rowptr, float avg_deg_log, int64_t N,
+                              int32_t T, int32_t Fo, int32_t relu, float* dy0, float* dz, void* stream) {
+    GNNX_REQUIRE(Fo % 4 == 0, "pna_post_combine_bwd: F_out must be a multiple of 4");
+    if (N == 0) return GNNX_OK;
+    k_pna_post_combine_bwd<<<flat_grid(N * (T * Fo / 4)), 256, 0, as_stream(stream)>>>(dout, out, rowptr, avg_deg_log, N, T, Fo, relu, dy0, dz);
+    return check_launch("pna_post_combine_bwd");
+}
+
+int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream) {
+    if (count == 0) return GNNX_OK;
+    GNNX_REQUIRE(((uintptr_t)dy % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)dx % 16 == 0), "relu_bwd: pointers must be 16-byte aligned");
+    k_relu_bwd<<<flat_grid(count / 4 + 1), 256, 0, as_stream(stream)>>>(dy, y, count, dx);
+    return check_launch("relu_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,383 @@
+"""Tensor-level wrappers over the C ABI (``include/gnnx.h``).
+
+Every function validates device / dtype / contiguity in Python, allocates outputs and workspaces
+with torch (plumbing only), and launches on torch's current CUDA stream.  No function here has a
+CPU path: a CPU tensor raises.
+"""
+
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from ._lib import lib
+
+PREC_FP32, PREC_TF32, PREC_BF16 = 0, 1, 2
+GEMM_RELU, GEMM_ACCUMULATE = 1, 2
+_PRECISIONS = {"fp32": PREC_FP32, "highest": PREC_FP32, "tf32": PREC_TF32, "high": PREC_TF32,
+               "bf16": PREC_BF16, "medium": PREC_BF16}
+
+_default_precision = PREC_FP32
+
+
+def set_matmul_precision(name: str) -> None:
+    """Mirror of ``torch.set_float32_matmul_precision`` for the gnnx Linear layers
+    (reference: train/train.py:54 uses "medium"; parity tests use "highest")."""
+    global _default_precision
+    _default_precision = _PRECISIONS[name]
+
+
+def get_matmul_precision() -> int:
+    return _default_precision
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: Tensor, dtype, name: str) -> Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"gnnx: `{name}` must be a CUDA tensor (no CPU fallback exists)")
+    if t.dtype != dtype:
+        raise TypeError(f"gnnx: `{name}` must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"gnnx: `{name}` must be contiguous")
+    return t
+
+
+def _p(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _ws(nbytes: int, device) -> Tuple[Optional[Tensor], int]:
+    if nbytes == 0:
+        return None, 0
+    t = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    return t, nbytes
+
+
+# ------------------------------------------------------------------ collator
+def csr_build(edge_index: Optional[Tensor], num_nodes: int, src32: Optional[Tensor] = None,
+              dst32: Optional[Tensor] = None):
+    """dst-sorted CSR + src-sorted view.  Pass either int64 ``edge_index`` [2,E] or int32 src/dst."""
+    L = lib()
+    if edge_index is not None:
+        _chk(edge_index, torch.int64, "edge_index")
+        if edge_index.dim() != 2 or edge_index.shape[0] != 2:
+            raise ValueError("gnnx: edge_index must be [2, E]")
+        E, dev = edge_index.shape[1], edge_index.device
+    else:
+        _chk(src32, torch.int32, "src"); _chk(dst32, torch.int32, "dst")
+        E, dev = src32.numel(), src32.device
+    i32 = dict(dtype=torch.int32, device=dev)
+    rowptr, colptr = torch.empty(num_nodes + 1, **i32), torch.empty(num_nodes + 1, **i32)
+    csr_src, csr_eid, pos = torch.empty(E, **i32), torch.empty(E, **i32), torch.empty(E, **i32)
+    csc_pos, csc_dst = torch.empty(E, **i32), torch.empty(E, **i32)
+    err = torch.empty(1, **i32)
+    ws, nb = _ws(L.query("gnnx_csr_workspace_bytes", num_nodes, E), dev)
+    if edge_index is not None:
+        L.call("gnnx_csr_build_i64", edge_index.data_ptr(), num_nodes, E, rowptr.data_ptr(), csr_src.data_ptr(),
+               csr_eid.data_ptr(), pos.data_ptr(), colptr.data_ptr(), csc_pos.data_ptr(), csc_dst.data_ptr(),
+               err.data_ptr(), _p(ws), nb, _stream())
+    else:
+        L.call("gnnx_csr_build_i32", src32.data_ptr(), dst32.data_ptr(), num_nodes, E, rowptr.data_ptr(),
+               csr_src.data_ptr(), csr_eid.data_ptr(), pos.data_ptr(), colptr.data_ptr(), csc_pos.data_ptr(),
+               csc_dst.data_ptr(), err.data_ptr(), _p(ws), nb, _stream())
+    return rowptr, csr_src, csr_eid, pos, colptr, csc_pos, csc_dst, err
+
+
+def degree_hist(rowptr: Tensor, hist: Tensor, max_degree: Tensor) -> None:
+    _chk(rowptr, torch.int32, "rowptr"); _chk(hist, torch.int64, "hist"); _chk(max_degree, torch.int32, "max_degree")
+    lib().call("gnnx_degree_hist", rowptr.data_ptr(), rowptr.numel() - 1, hist.data_ptr(), hist.numel(),
+               max_degree.data_ptr(), _stream())
+
+
+def graph_ptr_from_batch(batch: Tensor, num_graphs: int) -> Tensor:
+    _chk(batch, torch.int64, "batch")
+    gp = torch.empty(num_graphs + 1, dtype=torch.int32, device=batch.device)
+    lib().call("gnnx_graph_ptr_from_batch", batch.data_ptr(), batch.numel(), num_graphs, gp.data_ptr(), _stream())
+    return gp
+
+
+def narrow_u8(t: Tensor) -> Tensor:
+    _chk(t, torch.int64, "features")
+    out = torch.empty(t.shape, dtype=torch.uint8, device=t.device)
+    lib().call("gnnx_narrow_i64_u8", t.data_ptr(), t.numel(), out.data_ptr(), _stream())
+    return out
+
+
+def edge_codes(edge_attr_u8: Tensor, csr_eid: Tensor) -> Tensor:
+    _chk(edge_attr_u8, torch.uint8, "edge_attr_u8"); _chk(csr_eid, torch.int32, "csr_eid")
+    E = csr_eid.numel()
+    codes = torch.empty(E, dtype=torch.uint8, device=csr_eid.device)
+    lib().call("gnnx_edge_codes", edge_attr_u8.data_ptr(), csr_eid.data_ptr(), E, codes.data_ptr(), _stream())
+    return codes
+
+
+def collate_packed(store, graph_ids: Tensor, node_off: Tensor, edge_off: Tensor, N: int, E: int):
+    """``store`` is a ``DeviceGraphStore``; returns x_u8 [N,9], src32, dst32, edge_attr_u8 [E,3], batch32 [N]."""
+    dev = graph_ids.device
+    _chk(graph_ids, torch.int64, "graph_ids"); _chk(node_off, torch.int64, "node_off"); _chk(edge_off, torch.int64, "edge_off")
+    G = graph_ids.numel()
+    x = torch.empty((N, 9), dtype=torch.uint8, device=dev)
+    src, dst = torch.empty(E, dtype=torch.int32, device=dev), torch.empty(E, dtype=torch.int32, device=dev)
+    ea = torch.empty((E, 3), dtype=torch.uint8, device=dev)
+    batch = torch.empty(N, dtype=torch.int32, device=dev)
+    lib().call("gnnx_collate_packed", store.x.data_ptr(), store.src.data_ptr(), store.dst.data_ptr(),
+               store.edge_attr.data_ptr(), store.node_ptr.data_ptr(), store.edge_ptr.data_ptr(), graph_ids.data_ptr(), G,
+               node_off.data_ptr(), edge_off.data_ptr(), x.data_ptr(), src.data_ptr(), dst.data_ptr(), ea.data_ptr(),
+               batch.data_ptr(), _stream())
+    return x, src, dst, ea, batch
+
+
+# ------------------------------------------------------------------ embeddings
+def embed_sum_fwd(idx_u8: Tensor, offsets: Tensor, table: Tensor) -> Tensor:
+    _chk(idx_u8, torch.uint8, "idx"); _chk(offsets, torch.int32, "offsets"); _chk(table, torch.float32, "table")
+    rows, K = idx_u8.shape
+    H = table.shape[1]
+    out = torch.empty((rows, H), dtype=torch.float32, device=table.device)
+    lib().call("gnnx_embed_sum_fwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table.data_ptr(), H, out.data_ptr(), _stream())
+    return out
+
+
+def embed_sum_bwd(idx_u8: Tensor, offsets: Tensor, table_rows: int, dout: Tensor) -> Tensor:
+    _chk(idx_u8, torch.uint8, "idx"); _chk(dout, torch.float32, "dout")
+    rows, K = idx_u8.shape
+    H = dout.shape[1]
+    dtable = torch.empty((table_rows, H), dtype=torch.float32, device=dout.device)
+    ws, nb = _ws(lib().query("gnnx_embed_sum_bwd_workspace_bytes", rows, table_rows, H), dout.device)
+    lib().call("gnnx_embed_sum_bwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table_rows, dout.data_ptr(), H,
+               dtable.data_ptr(), _p(ws), nb, _stream())
+    return dtable
+
+
+# ------------------------------------------------------------------ dense transforms
+def _ld(t: Tensor) -> int:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError("gnnx: GEMM operands must be 2-D with unit inner stride")
+    return t.stride(0) if t.shape[0] > 1 else max(t.stride(0), t.shape[1])
+
+
+def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, bias: Optional[Tensor] = None,
+         relu: bool = False, out: Optional[Tensor] = None, accumulate: bool = False,
+         precision: Optional[int] = None) -> Tensor:
+    """``out = act(op(a) @ op(b) + bias)``; ``a``/``b``/``out`` may be column slices (row stride = ld)."""
+    for t, n in ((a, "a"), (b, "b")):
+        if not t.is_cuda or t.dtype != torch.float32:
+            raise RuntimeError(f"gnnx.gemm: `{n}` must be a CUDA float32 tensor (no CPU fallback exists)")
+    M, K = (a.shape[1], a.shape[0]) if trans_a else (a.shape[0], a.shape[1])
+    Kb, N = (b.shape[1], b.shape[0]) if trans_b else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise ValueError(f"gnnx.gemm: inner dimensions differ ({K} vs {Kb})")
+    if out is None:
+        if accumulate:
+            raise ValueError("gnnx.gemm: accumulate needs `out`")
+        out = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    elif out.shape != (M, N) or out.dtype != torch.float32 or not out.is_cuda:
+        raise ValueError("gnnx.gemm: bad `out`")
+    if bias is not None:
+        _chk(bias, torch.float32, "bias")
+    prec = _default_precision if precision is None else precision
+    flags = (GEMM_RELU if relu else 0) | (GEMM_ACCUMULATE if accumulate else 0)
+    L = lib()
+    ws, nb = _ws(L.query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
+    L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),
+           M, N, K, _p(bias), flags, prec, _p(ws), nb, _stream())
+    return out
+
+
+def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    if not x.is_cuda or x.dtype != torch.float32:
+        raise RuntimeError("gnnx.colsum: needs a CUDA float32 tensor")
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty(cols, dtype=torch.float32, device=x.device)
+    ws, nb = _ws(lib().query("gnnx_colsum_workspace_bytes", rows, cols), x.device)
+    lib().call("gnnx_colsum", x.data_ptr(), _ld(x), rows, cols, out.data_ptr(), _p(ws), nb, _stream())
+    return out
+
+
+# ------------------------------------------------------------------ PNA
+def pna_gather_fwd(pq: Tensor, r: Tensor, ridx: Tensor, rowptr: Tensor, csr_src: Tensor, relu: bool) -> Tensor:
+    _chk(pq, torch.float32, "pq"); _chk(r, torch.float32, "r")
+    N, H = pq.shape[0], pq.shape[1] // 2
+    E = csr_src.numel()
+    h = torch.empty((E, H), dtype=torch.float32, device=pq.device)
+    i32 = ridx.data_ptr() if ridx.dtype == torch.int32 else None
+    u8 = ridx.data_ptr() if ridx.dtype == torch.uint8 else None
+    lib().call("gnnx_pna_gather_fwd", pq.data_ptr(), pq.stride(0), r.data_ptr(), r.stride(0), i32, u8, rowptr.data_ptr(),
+               csr_src.data_ptr(), N, E, H, int(relu), h.data_ptr(), _stream())
+    return h
+
+
+def pna_gather_bwd(dh: Tensor, g, want_dr_edge: bool):
+    _chk(dh, torch.float32, "dh")
+    E, H = dh.shape
+    dpq = torch.empty((g.num_nodes, 2 * H), dtype=torch.float32, device=dh.device)
+    dr = torch.empty((E, H), dtype=torch.float32, device=dh.device) if want_dr_edge else None
+    lib().call("gnnx_pna_gather_bwd", dh.data_ptr(), g.rowptr.data_ptr(), g.colptr.data_ptr(), g.csc_pos.data_ptr(),
+               g.csr_eid.data_ptr(), g.num_nodes, E, H, dpq.data_ptr(), 2 * H, _p(dr), H, _stream())
+    return dpq, dr
+
+
+def code_segment_sum(dh: Tensor, codes: Tensor, num_codes: int) -> Tensor:
+    _chk(dh, torch.float32, "dh"); _chk(codes, torch.uint8, "codes")
+    rows, H = dh.shape
+    out = torch.empty((num_codes, H), dtype=torch.float32, device=dh.device)
+    ws, nb = _ws(lib().query("gnnx_code_segment_sum_workspace_bytes", rows, num_codes, H), dh.device)
+    lib().call("gnnx_code_segment_sum", dh.data_ptr(), codes.data_ptr(), rows, num_codes, H, out.data_ptr(), _p(ws), nb, _stream())
+    return out
+
+
+def pna_aggregate_fwd(m: Tensor, rowptr: Tensor, towers: int) -> Tensor:
+    _chk(m, torch.float32, "m"); _chk(rowptr, torch.int32, "rowptr")
+    N, H = rowptr.numel() - 1, m.shape[1]
+    agg = torch.empty((N, 4 * H), dtype=torch.float32, device=m.device)
+    lib().call("gnnx_pna_aggregate_fwd", m.data_ptr(), rowptr.data_ptr(), N, towers, H // towers, agg.data_ptr(), _stream())
+    return agg
+
+
+def pna_aggregate_bwd(dagg: Tensor, m: Tensor, agg: Tensor, rowptr: Tensor, towers: int) -> Tensor:
+    _chk(dagg, torch.float32, "dagg"); _chk(m, torch.float32, "m"); _chk(agg, torch.float32, "agg")
+    N, H = rowptr.numel() - 1, m.shape[1]
+    dm = torch.empty_like(m)
+    lib().call("gnnx_pna_aggregate_bwd", dagg.data_ptr(), m.data_ptr(), agg.data_ptr(), rowptr.data_ptr(), N, towers,
+               H // towers, dm.data_ptr(), _stream())
+    return dm
+
+
+def pna_post_combine_fwd(y0: Tensor, z: Tensor, bias: Optional[Tensor], rowptr: Tensor, avg_deg_log: float,
+                         towers: int, relu: bool) -> Tensor:
+    _chk(y0, torch.float32, "y0"); _chk(z, torch.float32, "z")
+    N, H = y0.shape
+    out = torch.empty_like(y0)
+    lib().call("gnnx_pna_post_combine_fwd", y0.data_ptr(), z.data_ptr(), _p(bias), rowptr.data_ptr(), float(avg_deg_log),
+               N, towers, H // towers, int(relu), out.data_ptr(), _stream())
+    return out
+
+
+def pna_post_combine_bwd(dout: Tensor, out: Tensor, rowptr: Tensor, avg_deg_log: float, towers: int, relu: bool):
+    _chk(dout, torch.float32, "dout"); _chk(out, torch.float32, "out")
+    N, H = dout.shape
+    dy0 = torch.empty_like(dout)
+    dz = torch.empty((N, 3 * H), dtype=torch.float32, device=dout.device)
+    lib().call("gnnx_pna_post_combine_bwd", dout.data_ptr(), out.data_ptr(), rowptr.data_ptr(), float(avg_deg_log), N,
+               towers, H // towers, int(relu), dy0.data_ptr(), dz.data_ptr(), _stream())
+    return dy0, dz
+
+
+def relu_bwd(dy: Tensor, y: Tensor) -> Tensor:
+    _chk(dy, torch.float32, "dy"); _chk(y, torch.float32, "y")
+    dx = torch.empty_like(dy)
+    lib().call("gnnx_relu_bwd", dy.data_ptr(), y.data_ptr(), dy.numel(), dx.data_ptr(), _stream())
+    return dx
+
+
+# ------------------------------------------------------------------ batch norm / pooling
+def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bool, momentum: float, eps: float,
+                relu: bool):
+    _chk(x, torch.float32, "x")
+    rows, C = x.shape
+    y = torch.empty_like(x)
+    mean = torch.empty(C, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+    ws, nb = _ws(lib().query("gnnx_bn_workspace_bytes", rows, C), x.device)
+    lib().call("gnnx_bn_relu_fwd", x.data_ptr(), rows, C, _p(weight), _p(bias), _p(running_mean), _p(running_var),
+               int(training), float(momentum), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+               _p(ws), nb, _stream())
+    return y, mean, rstd
+
+
+def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Tensor, relu: bool):
+    _chk(dy, torch.float32, "dy")
+    rows, C = x.shape
+    dx = torch.empty_like(x)
+    dw = torch.empty(C, dtype=torch.float32, device=x.device)
+    db = torch.empty(C, dtype=torch.float32, device=x.device)
+    ws, nb = _ws(lib().query("gnnx_bn_workspace_bytes", rows, C), x.device)
+    lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, _p(weight), mean.data_ptr(),
+               rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
+    return dx, dw, db
+
+
+POOL_MODES = {"add": 0, "sum": 0, "mean": 1, "max": 2}
+
+
+def segment_pool_fwd(x: Tensor, graph_ptr: Tensor, mode: int) -> Tensor:
+    _chk(x, torch.float32, "x"); _chk(graph_ptr, torch.int32, "graph_ptr")
+    G, C = graph_ptr.numel() - 1, x.shape[1]
+    out = torch.empty((G, C), dtype=torch.float32, device=x.device)
+    lib().call("gnnx_segment_pool_fwd", x.data_ptr(), graph_ptr.data_ptr(), G, C, mode, out.data_ptr(), _stream())
+    return out
+
+
+def segment_pool_bwd(dout: Tensor, x: Tensor, out: Tensor, graph_ptr: Tensor, mode: int) -> Tensor:
+    _chk(dout, torch.float32, "dout")
+    G, C = graph_ptr.numel() - 1, x.shape[1]
+    dx = torch.zeros_like(x) if G == 0 else torch.empty_like(x)
+    lib().call("gnnx_segment_pool_bwd", dout.data_ptr(), x.data_ptr(), out.data_ptr(), graph_ptr.data_ptr(), G, C, mode,
+               dx.data_ptr(), _stream())
+    return dx
+
+
+# ------------------------------------------------------------------ GATv2
+def gatv2_fwd(xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, bias: Optional[Tensor], g, heads: int, c: int,
+              slope: float, self_loops: bool):
+    _chk(xlr, torch.float32, "xlr"); _chk(e, torch.float32, "e"); _chk(att, torch.float32, "att")
+    N, E, H = g.num_nodes, g.num_edges, heads * c
+    out = torch.empty((N, H), dtype=torch.float32, device=xlr.device)
+    alpha = torch.empty((E + N, heads), dtype=torch.float32, device=xlr.device)
+    i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
+    u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
+    lib().call("gnnx_gatv2_fwd", xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, att.data_ptr(), _p(bias),
+               g.rowptr.data_ptr(), g.csr_src.data_ptr(), N, E, heads, c, float(slope), int(self_loops), out.data_ptr(),
+               alpha.data_ptr(), _stream())
+    return out, alpha
+
+
+def gatv2_bwd(dout: Tensor, xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, alpha: Tensor, g, heads: int, c: int,
+              slope: float, self_loops: bool):
+    _chk(dout, torch.float32, "dout")
+    N, E, H = g.num_nodes, g.num_edges, heads * c
+    dev = dout.device
+    dxlr = torch.empty((N, 2 * H), dtype=torch.float32, device=dev)
+    datt = torch.empty(H, dtype=torch.float32, device=dev)
+    ds = torch.empty((E + N, H), dtype=torch.float32, device=dev)
+    i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
+    u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
+    ws, nb = _ws(lib().query("gnnx_gatv2_bwd_workspace_bytes", N, E, heads, c), dev)
+    lib().call("gnnx_gatv2_bwd", dout.data_ptr(), xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, att.data_ptr(),
+               alpha.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(), g.colptr.data_ptr(), g.csc_pos.data_ptr(),
+               g.csc_dst.data_ptr(), N, E, heads, c, float(slope), int(self_loops), dxlr.data_ptr(), datt.data_ptr(),
+               ds.data_ptr(), _p(ws), nb, _stream())
+    return dxlr, datt, ds
+
+
+def gatv2_edge_grad(ds: Tensor, g, hidden: int, self_loops: bool, original_order: bool) -> Tensor:
+    E = g.num_edges
+    de = torch.zeros((E, hidden), dtype=torch.float32, device=ds.device)
+    lib().call("gnnx_gatv2_edge_grad", ds.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(),
+               g.csr_eid.data_ptr() if original_order else None, g.num_nodes, E, hidden, int(self_loops), de.data_ptr(),
+               _stream())
+    return de
+
+
+# ------------------------------------------------------------------ loss / optimizer tail
+def relhuber_fwd_bwd(pred: Tensor, target: Tensor, delta: float = 0.01, want_grad: bool = True):
+    _chk(pred, torch.float32, "pred"); _chk(target, torch.float32, "target")
+    out2 = torch.empty(2, dtype=torch.float32, device=pred.device)
+    dpred = torch.empty_like(pred) if want_grad else None
+    lib().call("gnnx_relhuber_fwd_bwd", pred.data_ptr(), target.data_ptr(), pred.numel(), float(delta), out2.data_ptr(),
+               _p(dpred), _stream())
+    return out2, dpred
+
+
+def adamw_amsgrad_(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, max_exp_avg_sq: Tensor, *, lr: float,
+                   beta1: float, beta2: float, eps: float, weight_decay: float, step: int, grad_scale: float = 1.0) -> None:
+    for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq"), (max_exp_avg_sq, "max_exp_avg_sq")):
+        _chk(t, torch.float32, n)
+    lib().call("gnnx_adamw_amsgrad", param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+               max_exp_avg_sq.data_ptr(), param.numel(), float(lr), float(beta1), float(beta2), float(eps),
+               float(weight_decay), int(step), float(grad_scale), _stream())

@@ -1,0 +1,254 @@
+/* gnnx.h -- C ABI of libgnnx_sm100.so: the B200 (sm_100a) message-passing hot path of
+ * wildsonbbl/gnnepcsaft (PyG PNAConv / GATv2Conv gather-transform-scatter, batch-norm,
+ * graph pooling, OGB embedding sums, and the batch collator), forward and backward.
+ *
+ * Conventions (every entry point):
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless marked "host";
+ *   - no allocation and no ownership transfer inside the library: the caller passes outputs
+ *     and, where needed, a workspace sized by the matching gnnx_*_workspace_bytes();
+ *   - stream-ordered and asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - returns GNNX_OK (0), a positive cudaError_t, or a negative GNNX_ERR_* code;
+ *     gnnx_last_error() returns a thread-local message for the last non-zero return;
+ *   - feature matrices are row-major fp32; index arrays are int32 on the device
+ *     (the reference's int64 tensors are narrowed by the collator entry points).
+ *
+ * The reference has no FFI of its own for this path: it is a Python duck-typed module
+ * interface over torch_geometric / ogb (gnnepcsaft/train/models.py:175-184, 205-219,
+ * 441-495, 587-595).  Each group below names the reference call it stands behind; the
+ * ctypes binding a maintainer would add is shown in INTEGRATION.md.
+ */
+#ifndef GNNX_H_
+#define GNNX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define GNNX_API __attribute__((visibility("default")))
+#else
+#define GNNX_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNNX_OK 0
+#define GNNX_ERR_INVALID (-1)     /* bad argument (shape, alignment, null pointer) */
+#define GNNX_ERR_UNSUPPORTED (-2) /* configuration outside the compiled envelope */
+#define GNNX_ERR_WORKSPACE (-3)   /* workspace too small */
+
+#define GNNX_ABI_VERSION 1
+
+GNNX_API int gnnx_abi_version(void);
+GNNX_API const char* gnnx_last_error(void);
+
+/* ------------------------------------------------------------------ collator (integer) */
+/* Replaces: PyG Batch.from_data_list + the unordered COO scatter indexing
+ * (gnnepcsaft/train/train.py:59-75) and torch_geometric.utils.degree / calc_deg
+ * (gnnepcsaft/train/utils.py:37-60).  Results are bit-exact with
+ * argsort(edge_index[1], stable=True) / bincount. */
+
+GNNX_API size_t gnnx_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges);
+
+/* edge_index: int64 [2,E] (row 0 = source j, row 1 = destination i), PyG COO order.
+ * Outputs (all int32):
+ *   rowptr[N+1], csr_src[E], csr_eid[E]  dst-sorted CSR; csr_eid = original edge id
+ *   pos_of_eid[E]                        slot of original edge e in the dst-sorted order
+ *   colptr[N+1], csc_pos[E], csc_dst[E]  src-sorted view: dst-sorted slot / destination of
+ *                                        each edge, grouped by source (backward scatter)
+ *   err_flag[1]                          set to 1 if any endpoint is outside [0,N)        */
+GNNX_API int gnnx_csr_build_i64(const int64_t* edge_index, int64_t num_nodes, int64_t num_edges,
+                       int32_t* rowptr, int32_t* csr_src, int32_t* csr_eid, int32_t* pos_of_eid,
+                       int32_t* colptr, int32_t* csc_pos, int32_t* csc_dst, int32_t* err_flag,
+                       void* workspace, size_t workspace_bytes, void* stream);
+/* Same, from separate int32 src / dst arrays (the packed-store collator's output). */
+GNNX_API int gnnx_csr_build_i32(const int32_t* src, const int32_t* dst, int64_t num_nodes, int64_t num_edges,
+                       int32_t* rowptr, int32_t* csr_src, int32_t* csr_eid, int32_t* pos_of_eid,
+                       int32_t* colptr, int32_t* csc_pos, int32_t* csc_dst, int32_t* err_flag,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* hist[d] += #nodes with in-degree d (d clamped to nbins-1); max_degree[0] = max(max_degree[0], max d).
+ * Accumulates, so a dataset histogram (calc_deg) is a loop of calls over batches. */
+GNNX_API int gnnx_degree_hist(const int32_t* rowptr, int64_t num_nodes, int64_t* hist, int32_t nbins,
+                     int32_t* max_degree, void* stream);
+
+/* graph_ptr[G+1] from the sorted, non-decreasing int64 `batch` vector (PyG Batch.batch). */
+GNNX_API int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t num_nodes, int64_t num_graphs,
+                              int32_t* graph_ptr, void* stream);
+
+/* Narrow int64 categorical features [rows, K] to uint8 (vocabularies are <= 119). */
+GNNX_API int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream);
+
+/* Bond-type code per dst-sorted slot: code = (a0*6 + a1)*2 + a2 in [0,60) from uint8 [E,3]
+ * edge attributes in original edge order and csr_eid. */
+GNNX_API int gnnx_edge_codes(const uint8_t* edge_attr_u8, const int32_t* csr_eid, int64_t num_edges,
+                    uint8_t* codes, void* stream);
+
+/* Device-side block-diagonal collation of G molecules picked from a packed, device-resident
+ * store (uint8 features, int16 graph-local endpoints).  graph_ids[G] selects molecules;
+ * out_node_off[G+1] / out_edge_off[G+1] are the exclusive scans of their node / edge counts.
+ * Produces exactly Batch.from_data_list's x / edge_index / edge_attr / batch, narrowed. */
+GNNX_API int gnnx_collate_packed(const uint8_t* store_x, const int16_t* store_src, const int16_t* store_dst,
+                        const uint8_t* store_edge_attr, const int64_t* store_node_ptr,
+                        const int64_t* store_edge_ptr, const int64_t* graph_ids, int64_t num_graphs,
+                        const int64_t* out_node_off, const int64_t* out_edge_off,
+                        uint8_t* out_x, int32_t* out_src, int32_t* out_dst, uint8_t* out_edge_attr,
+                        int32_t* out_batch, void* stream);
+
+/* --------------------------------------------------------------- OGB embedding sums (K1) */
+/* Replaces ogb AtomEncoder / BondEncoder.forward (models.py:175-176, 205-206):
+ * out[r,:] = sum_k table[offset[k] + idx[r,k], :], accumulated in k order.
+ * idx is uint8 [rows,K]; table is the row-concatenation of the K embedding weights. */
+GNNX_API int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t num_features, const int32_t* offsets,
+                       const float* table, int32_t hidden, float* out, void* stream);
+GNNX_API size_t gnnx_embed_sum_bwd_workspace_bytes(int64_t rows, int32_t table_rows, int32_t hidden);
+/* dtable[table_rows, hidden] = sum over rows (deterministic, atomic-free). */
+GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_features, const int32_t* offsets,
+                       int32_t table_rows, const float* dout, int32_t hidden, float* dtable,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ dense transforms (d) */
+/* C[M,N] = epilogue( op(A) * op(B) ) for the Linear layers inside PNAConv / GATv2Conv / the
+ * MLP head (torch.nn.Linear semantics: y = x W^T + b with W [out,in]).
+ *   trans_a = 0: A is [M,K] row-major (lda);  1: A is stored [K,M] (lda) and used transposed
+ *   trans_b = 0: B is [K,N] row-major (ldb);  1: B is stored [N,K] (ldb)  (Linear forward)
+ *   bias: optional [N]; flags: GNNX_GEMM_RELU applies max(.,0); GNNX_GEMM_ACCUMULATE adds the
+ *   previous contents of C.  precision: GNNX_PREC_* below.
+ * Split-K (deterministic two-pass) is chosen internally when M*N is small and K large;
+ * workspace may be null when gnnx_gemm_workspace_bytes() returns 0. */
+#define GNNX_GEMM_RELU 1
+#define GNNX_GEMM_ACCUMULATE 2
+#define GNNX_PREC_FP32 0 /* CUDA-core fp32 FMA (parity tier, rel 1e-5)              */
+#define GNNX_PREC_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM             */
+#define GNNX_PREC_BF16 2 /* tcgen05 kind::f16 on bf16-rounded operands, fp32 accum  */
+GNNX_API size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t trans_a, int32_t trans_b,
+                                 int32_t precision);
+GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float* B, int64_t ldb, int32_t trans_b,
+              float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags,
+              int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
+GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);
+GNNX_API int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out,
+                void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ PNA message passing */
+/* Replaces the gather + first pre_nn Linear of PNAConv.message (PyG; called from
+ * models.py:211-216).  With pq = x [W_dst ; W_src]^T computed node-side, for every
+ * dst-sorted slot p:  h[p,:] = act( pq[dst_p, 0:H] + pq[src_p, H:2H] + r[ridx_p, :] )
+ * where r is either the per-edge term in ORIGINAL edge order (ridx = csr_eid) or a 60-row
+ * bond-type table (ridx = codes, uint8).  Exactly one of ridx_i32 / ridx_u8 is non-null.
+ * relu != 0 applies the ReLU that follows the first Linear when pre_layers > 1. */
+GNNX_API int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t ld_r,
+                        const int32_t* ridx_i32, const uint8_t* ridx_u8,
+                        const int32_t* rowptr, const int32_t* csr_src, int64_t num_nodes,
+                        int64_t num_edges, int32_t hidden, int32_t relu, float* h, void* stream);
+/* Backward of the gather: dh is [E,H] in dst-sorted order (already masked by ReLU').
+ *   dpq[i, 0:H]  = sum_{p in row i} dh[p]           (segment sum, CSR)
+ *   dpq[j, H:2H] = sum_{edges with src j} dh[pos]   (segment sum through csc_pos)
+ *   dr_edge[csr_eid[p], :] = dh[p]                  (only if dr_edge != null)          */
+GNNX_API int gnnx_pna_gather_bwd(const float* dh, const int32_t* rowptr, const int32_t* colptr,
+                        const int32_t* csc_pos, const int32_t* csr_eid, int64_t num_nodes,
+                        int64_t num_edges, int32_t hidden, float* dpq, int64_t ld_dpq,
+                        float* dr_edge, int64_t ld_dr, void* stream);
+/* dtable[c,:] = sum_{p: codes[p]==c} dh[p,:]  (gradient of the 60-row bond-type table). */
+GNNX_API size_t gnnx_code_segment_sum_workspace_bytes(int64_t rows, int32_t num_codes, int32_t hidden);
+GNNX_API int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, int32_t num_codes,
+                          int32_t hidden, float* dtable, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
+/* Replaces DegreeScalerAggregation(MultiAggregation[mean,min,max,std]) (models.py:443-449):
+ * one pass over the dst-sorted messages m [E, T*F]; agg is [N, T, 4, F] = PyG's [N,T,4F]
+ * ordering (mean|min|max|std per tower); empty rows give 0 for all four.  The degree
+ * scalers are NOT applied here: they are folded into the consumer (gnnx_pna_post_combine). */
+GNNX_API int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t num_nodes, int32_t towers,
+                           int32_t f, float* agg, void* stream);
+/* dm[p] from dagg [N,T,4,F]; min/max gradients are split evenly among tied extrema and
+ * std has zero gradient where it was clamped to 0 (PyG CPU semantics). */
+GNNX_API int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, const int32_t* rowptr,
+                           int64_t num_nodes, int32_t towers, int32_t f, float* dm, void* stream);
+
+/* First post_nn Linear with the scalers folded in.  z is [N, T, 3, F_out] holding
+ * agg[:,t] W_id^T | agg[:,t] W_amp^T | agg[:,t] W_att^T, y0 is [N, T*F_out] = x W_x^T:
+ *   out = act( y0 + z_id + s_amp(d_i) z_amp + s_att(d_i) z_att + bias ),
+ *   s_amp = log(d+1)/avg_deg_log,  s_att = avg_deg_log / log(max(d,1)+1),  d = in-degree. */
+GNNX_API int gnnx_pna_post_combine_fwd(const float* y0, const float* z, const float* bias, const int32_t* rowptr,
+                              float avg_deg_log, int64_t num_nodes, int32_t towers, int32_t f_out,
+                              int32_t relu, float* out, void* stream);
+/* dy0 = dout*mask, dz = (dy0, s_amp dy0, s_att dy0); mask = (out > 0) when relu. */
+GNNX_API int gnnx_pna_post_combine_bwd(const float* dout, const float* out, const int32_t* rowptr,
+                              float avg_deg_log, int64_t num_nodes, int32_t towers, int32_t f_out,
+                              int32_t relu, float* dy0, float* dz, void* stream);
+
+/* dx = dy * (y > 0) elementwise (ReLU backward between Linear layers). */
+GNNX_API int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream);
+
+/* ------------------------------------------------------------------ batch norm + ReLU (K8) */
+/* Replaces torch_geometric.nn.BatchNorm / BatchNorm1d + F.relu (models.py:184, 212-213).
+ * Training: batch statistics over all rows (biased variance to normalise), running stats
+ * updated with the unbiased variance and `momentum`; eval: running stats.
+ * save_mean / save_rstd [C] are written in training mode for the backward. */
+GNNX_API size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t channels);
+GNNX_API int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t channels, const float* weight,
+                     const float* bias, float* running_mean, float* running_var, int32_t training,
+                     float momentum, float eps, int32_t relu, float* y, float* save_mean,
+                     float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
+/* dx, dweight, dbias from dy; y is the forward output (used for the ReLU mask), x the input. */
+GNNX_API int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t channels,
+                     const float* weight, const float* save_mean, const float* save_rstd,
+                     int32_t relu, float* dx, float* dweight, float* dbias, void* workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ graph pooling (K9) */
+/* Replaces aggr.{Sum,Mean,Max}Aggregation()(x, batch) (models.py:218-219, 587-595) over the
+ * contiguous node ranges graph_ptr[g]..graph_ptr[g+1].  mode: 0 add, 1 mean, 2 max. */
+GNNX_API int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t num_graphs,
+                          int32_t channels, int32_t mode, float* out, void* stream);
+GNNX_API int gnnx_segment_pool_bwd(const float* dout, const float* x, const float* out, const int32_t* graph_ptr,
+                          int64_t num_graphs, int32_t channels, int32_t mode, float* dx, void* stream);
+
+/* ------------------------------------------------------------------ GATv2 attention (K7) */
+/* Replaces GATv2Conv's edge_update + segment softmax + propagate (PyG; models.py:487-495).
+ * xlr is [N, 2*H] = [lin_l(x) | lin_r(x)], H = heads*C.  e is the lin_edge term: per-edge
+ * [E,H] in original order (eidx = csr_eid) or a table indexed by codes.  self_loops != 0 adds
+ * the i->i edge whose edge term is the mean of the incoming e rows (fill_value='mean' through
+ * the bias-free lin_edge); edges with src == dst are dropped first (remove_self_loops).
+ * alpha is [E + N, heads] (dst-sorted slots, then loop slots) and is saved for the backward. */
+GNNX_API int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t* eidx_i32,
+                   const uint8_t* eidx_u8, const float* att, const float* bias, const int32_t* rowptr,
+                   const int32_t* csr_src, int64_t num_nodes, int64_t num_edges, int32_t heads,
+                   int32_t c, float negative_slope, int32_t self_loops, float* out, float* alpha,
+                   void* stream);
+/* Backward.  Outputs: dxlr [N,2H] (fully written), datt [heads*C], ds [E+N, H] = gradient
+ * at the pre-activation s (dst-sorted slots then loop slots); the caller derives d(lin_edge)
+ * from ds.  workspace: gnnx_gatv2_bwd_workspace_bytes(). */
+GNNX_API size_t gnnx_gatv2_bwd_workspace_bytes(int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c);
+GNNX_API int gnnx_gatv2_bwd(const float* dout, const float* xlr, const float* e, int64_t ld_e,
+                   const int32_t* eidx_i32, const uint8_t* eidx_u8, const float* att,
+                   const float* alpha, const int32_t* rowptr, const int32_t* csr_src,
+                   const int32_t* colptr, const int32_t* csc_pos, const int32_t* csc_dst,
+                   int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float negative_slope,
+                   int32_t self_loops, float* dxlr, float* datt, float* ds, void* workspace,
+                   size_t workspace_bytes, void* stream);
+/* de rows for the edge term from ds: de[slot] = ds[slot] + ds[loop(dst)] / deg(dst) (the loop's
+ * mean fan-out), written in ORIGINAL edge order when csr_eid != null, else dst-sorted. */
+GNNX_API int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* csr_src,
+                         const int32_t* csr_eid, int64_t num_nodes, int64_t num_edges, int32_t hidden,
+                         int32_t self_loops, float* de, void* stream);
+
+/* ------------------------------------------------------------------ loss + optimizer tail */
+/* Relative-error Huber(delta) + MAPE of GNNePCSAFTL.training_step (models.py:89-92), fused
+ * forward + gradient: out[0] = loss, out[1] = mape, dpred = d loss / d pred. */
+GNNX_API int gnnx_relhuber_fwd_bwd(const float* pred, const float* target, int64_t count, float delta,
+                          float* out2, float* dpred, void* stream);
+/* AdamW(amsgrad=True) over a flat fp32 parameter buffer (models.py:49-55); grad_scale folds the
+ * 1/world_size of the data-parallel mean. step >= 1. */
+GNNX_API int gnnx_adamw_amsgrad(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                       float* max_exp_avg_sq, int64_t count, float lr, float beta1, float beta2,
+                       float eps, float weight_decay, int32_t step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNNX_H_ */

@@ -1,0 +1,520 @@
+"""Pure-torch CPU restatement of the PyG / ogb modules the reference's hot path uses.
+
+TEST INFRASTRUCTURE ONLY -- see ``oracle/__init__.py``.  *parity unpinned*: there
+is no reference-side golden vector for this path; this file restates the
+published pure-torch semantics of ``torch_geometric`` (2.6.x / 2.7, the era the
+reference's ``requirements.txt:12`` resolves to) and ``ogb`` 1.3.6
+(``gnnepcsaft/data/ogb_utils.py:3``), assembled exactly as the reference
+assembles them in ``gnnepcsaft/train/models.py:159-254, 441-495, 587-595``.
+
+Every function cites the reference call site it backs (paths relative to
+``/root/reference``) and the SURVEY.md §8(c) rule (R1..R10) it implements.
+State-dict key names follow PyG so checkpoints are interchangeable with the
+product modules (``gnnepcsaft_b200.nn``).
+"""
+
+from __future__ import annotations
+
+import math
+from typing import Any, List, Optional, Sequence, Union
+
+import torch
+import torch.nn.functional as F
+from torch import Tensor
+from torch.nn import BatchNorm1d, Dropout, Embedding, Linear, Module, ModuleList, Parameter, ReLU, Sequential
+
+# ogb.utils.features.get_atom_feature_dims() / get_bond_feature_dims();
+# vocabulary sizes are the lengths of the lists in gnnepcsaft/data/ogb_utils.py:8-34.
+ATOM_FEATURE_DIMS = (119, 5, 12, 12, 10, 6, 6, 2, 2)
+BOND_FEATURE_DIMS = (5, 6, 2)
+
+
+# --------------------------------------------------------------------------- R1
+class Graph:
+    """Minimal stand-in for ``torch_geometric.data.Data`` (gnnepcsaft/data/graph.py:40-52)."""
+
+    def __init__(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, **attrs: Tensor):
+        self.x, self.edge_index, self.edge_attr = x, edge_index, edge_attr
+        self.batch: Optional[Tensor] = None
+        for k, v in attrs.items():
+            setattr(self, k, v)
+        self._attr_names = tuple(attrs)
+
+    @property
+    def num_nodes(self) -> int:
+        return int(self.x.shape[0])
+
+
+def collate(graphs: Sequence[Graph]) -> Graph:
+    """R1 -- ``Batch.from_data_list`` as used by the PyG DataLoader (train/train.py:59-75).
+
+    Block-diagonal batching: ``x``/``edge_attr`` concatenated on dim 0, ``edge_index``
+    concatenated on dim 1 with a per-graph node offset, ``batch`` / ``ptr`` built from the
+    node counts, graph-level ``[1,k]`` attributes stacked to ``[G,k]``.  Edge order is the
+    input order (OGB bond order, data/ogb_utils.py:125-129).
+    """
+    n = torch.tensor([g.num_nodes for g in graphs], dtype=torch.long)
+    ptr = torch.zeros(len(graphs) + 1, dtype=torch.long)
+    ptr[1:] = torch.cumsum(n, 0)
+    x = torch.cat([g.x for g in graphs], 0)
+    edge_attr = torch.cat([g.edge_attr for g in graphs], 0)
+    edge_index = torch.cat([g.edge_index + int(off) for g, off in zip(graphs, ptr[:-1])], 1)
+    out = Graph(x, edge_index, edge_attr)
+    out.batch = torch.repeat_interleave(torch.arange(len(graphs)), n)
+    out.ptr = ptr
+    names = graphs[0]._attr_names if graphs else ()
+    for k in names:
+        setattr(out, k, torch.cat([getattr(g, k) for g in graphs], 0))
+    out._attr_names = tuple(names)
+    return out
+
+
+# --------------------------------------------------------------------------- R2
+def degree(index: Tensor, num_nodes: int, dtype=torch.long) -> Tensor:
+    """R2 -- ``torch_geometric.utils.degree`` (train/utils.py:52, 58)."""
+    out = torch.zeros(num_nodes, dtype=dtype)
+    return out.scatter_add_(0, index, torch.ones(index.numel(), dtype=dtype))
+
+
+def calc_deg(graphs: Sequence[Graph]) -> List[int]:
+    """R2 -- dataset in-degree histogram, gnnepcsaft/train/utils.py:37-60."""
+    max_degree = -1
+    for g in graphs:
+        d = degree(g.edge_index[1], g.num_nodes)
+        max_degree = max(max_degree, int(d.max()))
+    deg = torch.zeros(max_degree + 1, dtype=torch.long)
+    for g in graphs:
+        d = degree(g.edge_index[1], g.num_nodes)
+        deg += torch.bincount(d, minlength=deg.numel())
+    return deg.tolist()
+
+
+def csr_reference(edge_index: Tensor, num_nodes: int):
+    """R2 -- the dst-sorted CSR the GPU collator must reproduce bit-exactly.
+
+    ``perm`` = stable argsort of the destination row, ``rowptr`` = exclusive scan of the
+    in-degree; also the src-sorted (CSC) permutation used by the backward scatter.
+    """
+    src, dst = edge_index[0], edge_index[1]
+    perm = torch.sort(dst, stable=True).indices
+    rowptr = torch.zeros(num_nodes + 1, dtype=torch.long)
+    rowptr[1:] = torch.cumsum(torch.bincount(dst, minlength=num_nodes), 0)
+    perm_src = torch.sort(src, stable=True).indices
+    colptr = torch.zeros(num_nodes + 1, dtype=torch.long)
+    colptr[1:] = torch.cumsum(torch.bincount(src, minlength=num_nodes), 0)
+    return {
+        "rowptr": rowptr, "eid": perm, "src": src[perm],
+        "colptr": colptr, "eid_by_src": perm_src, "dst_by_src": dst[perm_src],
+        "in_degree": rowptr[1:] - rowptr[:-1],
+    }
+
+
+# --------------------------------------------------------------------------- R3
+def _broadcast(index: Tensor, ref: Tensor) -> Tensor:
+    size = [-1] + [1] * (ref.dim() - 1)
+    return index.view(size).expand_as(ref)
+
+
+def scatter(src: Tensor, index: Tensor, dim_size: int, reduce: str) -> Tensor:
+    """R3 -- ``torch_geometric.utils.scatter`` along dim 0, pure-torch backend.
+
+    ``min``/``max`` use ``scatter_reduce_(include_self=False)`` on a zero tensor: empty
+    segments stay 0 and the backward splits the gradient evenly among tied extrema.
+    """
+    size = [dim_size] + list(src.shape[1:])
+    if reduce in ("sum", "add"):
+        return src.new_zeros(size).scatter_add_(0, _broadcast(index, src), src)
+    if reduce == "mean":
+        count = src.new_zeros(dim_size).scatter_add_(0, index, src.new_ones(src.shape[0]))
+        count = count.clamp(min=1)
+        out = src.new_zeros(size).scatter_add_(0, _broadcast(index, src), src)
+        return out / count.view([-1] + [1] * (src.dim() - 1))
+    if reduce in ("min", "max"):
+        return src.new_zeros(size).scatter_reduce_(
+            0, _broadcast(index, src), src, reduce="a" + reduce, include_self=False)
+    raise ValueError(reduce)
+
+
+# --------------------------------------------------------------------------- R8
+def segment_softmax(src: Tensor, index: Tensor, num_nodes: int) -> Tensor:
+    """R8 -- ``torch_geometric.utils.softmax`` (used inside GATv2Conv.edge_update)."""
+    src_max = scatter(src.detach(), index, num_nodes, "max")
+    out = (src - src_max.index_select(0, index)).exp()
+    out_sum = scatter(out, index, num_nodes, "sum") + 1e-16
+    return out / out_sum.index_select(0, index)
+
+
+# --------------------------------------------------------------------------- R4
+class SumAggregation(Module):
+    """``gnn.aggr.SumAggregation`` (models.py:594); ``forward(x, index)``; ``dim_size`` = max+1."""
+
+    reduce = "sum"
+
+    def forward(self, x: Tensor, index: Tensor, dim_size: Optional[int] = None) -> Tensor:
+        if dim_size is None:
+            dim_size = int(index.max()) + 1 if index.numel() > 0 else 0
+        return scatter(x, index, dim_size, self.reduce)
+
+
+class MeanAggregation(SumAggregation):
+    """``gnn.aggr.MeanAggregation`` (models.py:590)."""
+    reduce = "mean"
+
+
+class MaxAggregation(SumAggregation):
+    """``gnn.aggr.MaxAggregation`` (models.py:592)."""
+    reduce = "max"
+
+
+class MinAggregation(SumAggregation):
+    reduce = "min"
+
+
+def var_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
+    """R4 -- ``VarAggregation(semi_grad=False)``: mean(x*x) - mean(x)**2."""
+    mean = scatter(x, index, dim_size, "mean")
+    mean_2 = scatter(x * x, index, dim_size, "mean")
+    return mean_2 - mean * mean
+
+
+def std_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
+    """R4 -- ``StdAggregation``: clamp(1e-5).sqrt() then zero-fill at/below sqrt(1e-5)."""
+    var = var_aggregation(x, index, dim_size)
+    out = var.clamp(min=1e-5).sqrt()
+    return out.masked_fill(out <= math.sqrt(1e-5), 0.0)
+
+
+_AGGRS = {
+    "mean": lambda x, i, n: scatter(x, i, n, "mean"),
+    "min": lambda x, i, n: scatter(x, i, n, "min"),
+    "max": lambda x, i, n: scatter(x, i, n, "max"),
+    "sum": lambda x, i, n: scatter(x, i, n, "sum"),
+    "var": var_aggregation,
+    "std": std_aggregation,
+}
+
+
+# --------------------------------------------------------------------------- R5
+class DegreeScalerAggregation(Module):
+    """R5 -- ``torch_geometric.nn.aggr.DegreeScalerAggregation`` (train_norm=False).
+
+    Built by PNAConv from the aggregator / scaler lists of models.py:443-444 and the
+    dataset histogram ``deg`` (models.py:451, train/utils.py:37-60).
+    """
+
+    def __init__(self, aggr: Sequence[str], scaler: Sequence[str], deg: Tensor):
+        super().__init__()
+        self.aggr_names, self.scaler = list(aggr), list(scaler)
+        deg = deg.to(torch.float)
+        num_nodes = int(deg.sum())
+        bin_degree = torch.arange(deg.numel())
+        self.init_avg_deg_lin = float((bin_degree * deg).sum()) / num_nodes
+        self.init_avg_deg_log = float(((bin_degree + 1).log() * deg).sum()) / num_nodes
+        self.register_buffer("avg_deg_lin", torch.full((1,), self.init_avg_deg_lin))
+        self.register_buffer("avg_deg_log", torch.full((1,), self.init_avg_deg_log))
+
+    def forward(self, x: Tensor, index: Tensor, dim_size: int) -> Tensor:
+        out = torch.cat([_AGGRS[a](x, index, dim_size) for a in self.aggr_names], dim=-1)
+        deg = degree(index, dim_size, dtype=out.dtype).view([-1] + [1] * (out.dim() - 1))
+        outs = []
+        for scaler in self.scaler:
+            if scaler == "identity":
+                o = out
+            elif scaler == "amplification":
+                o = out * (torch.log(deg + 1) / self.avg_deg_log)
+            elif scaler == "attenuation":
+                o = out * (self.avg_deg_log / torch.log(deg.clamp(min=1) + 1))
+            elif scaler == "linear":
+                o = out * (deg / self.avg_deg_lin)
+            elif scaler == "inverse_linear":
+                o = out * (self.avg_deg_lin / deg.clamp(min=1))
+            else:
+                raise ValueError(f"Unknown scaler '{scaler}'")
+            outs.append(o)
+        return torch.cat(outs, dim=-1) if len(outs) > 1 else outs[0]
+
+
+# --------------------------------------------------------------------------- R6
+class PNAConv(Module):
+    """R6 -- ``gnn.PNAConv`` as instantiated at gnnepcsaft/train/models.py:445-457."""
+
+    def __init__(self, in_channels: int, out_channels: int, aggregators: Sequence[str],
+                 scalers: Sequence[str], deg: Tensor, edge_dim: Optional[int] = None,
+                 towers: int = 1, pre_layers: int = 1, post_layers: int = 1,
+                 divide_input: bool = False):
+        super().__init__()
+        if divide_input:
+            assert in_channels % towers == 0
+        assert out_channels % towers == 0
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.towers, self.divide_input, self.edge_dim = towers, divide_input, edge_dim
+        self.F_in = in_channels // towers if divide_input else in_channels
+        self.F_out = out_channels // towers
+        self.aggr_module = DegreeScalerAggregation(aggregators, scalers, deg)
+        if edge_dim is not None:
+            self.edge_encoder = Linear(edge_dim, self.F_in)
+        self.pre_nns, self.post_nns = ModuleList(), ModuleList()
+        for _ in range(towers):
+            mods: List[Module] = [Linear((3 if edge_dim else 2) * self.F_in, self.F_in)]
+            for _ in range(pre_layers - 1):
+                mods += [ReLU(), Linear(self.F_in, self.F_in)]
+            self.pre_nns.append(Sequential(*mods))
+            k_in = (len(aggregators) * len(scalers) + 1) * self.F_in
+            mods = [Linear(k_in, self.F_out)]
+            for _ in range(post_layers - 1):
+                mods += [ReLU(), Linear(self.F_out, self.F_out)]
+            self.post_nns.append(Sequential(*mods))
+        self.lin = Linear(out_channels, out_channels)
+
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Optional[Tensor] = None) -> Tensor:
+        n = x.shape[0]
+        if self.divide_input:
+            xv = x.view(-1, self.towers, self.F_in)
+        else:
+            xv = x.view(-1, 1, self.F_in).repeat(1, self.towers, 1)
+        x_j, x_i = xv[edge_index[0]], xv[edge_index[1]]
+        if edge_attr is not None:
+            e = self.edge_encoder(edge_attr).view(-1, 1, self.F_in).repeat(1, self.towers, 1)
+            h = torch.cat([x_i, x_j, e], dim=-1)
+        else:
+            h = torch.cat([x_i, x_j], dim=-1)
+        m = torch.stack([nn(h[:, i]) for i, nn in enumerate(self.pre_nns)], dim=1)
+        out = self.aggr_module(m, edge_index[1], n)
+        out = torch.cat([xv, out], dim=-1)
+        out = torch.cat([nn(out[:, i]) for i, nn in enumerate(self.post_nns)], dim=1)
+        return self.lin(out)
+
+
+# --------------------------------------------------------------------------- R7
+def remove_self_loops(edge_index: Tensor, edge_attr: Optional[Tensor]):
+    mask = edge_index[0] != edge_index[1]
+    return edge_index[:, mask], (None if edge_attr is None else edge_attr[mask])
+
+
+def add_self_loops_mean(edge_index: Tensor, edge_attr: Optional[Tensor], num_nodes: int):
+    """``add_self_loops(fill_value='mean')``: loop features = mean of incoming edge features."""
+    loop = torch.arange(num_nodes, dtype=edge_index.dtype).unsqueeze(0).repeat(2, 1)
+    if edge_attr is not None:
+        loop_attr = scatter(edge_attr, edge_index[1], num_nodes, "mean")
+        edge_attr = torch.cat([edge_attr, loop_attr], 0)
+    return torch.cat([edge_index, loop], 1), edge_attr
+
+
+class GATv2Conv(Module):
+    """R7 -- ``gnn.GATv2Conv`` as instantiated at gnnepcsaft/train/models.py:487-495."""
+
+    def __init__(self, in_channels: int, out_channels: int, heads: int = 1, concat: bool = True,
+                 negative_slope: float = 0.2, dropout: float = 0.0, add_self_loops: bool = True,
+                 edge_dim: Optional[int] = None, bias: bool = True):
+        super().__init__()
+        self.in_channels, self.out_channels, self.heads = in_channels, out_channels, heads
+        self.concat, self.negative_slope, self.dropout = concat, negative_slope, dropout
+        self.add_self_loops, self.edge_dim = add_self_loops, edge_dim
+        self.lin_l = Linear(in_channels, heads * out_channels, bias=bias)
+        self.lin_r = Linear(in_channels, heads * out_channels, bias=bias)
+        self.att = Parameter(torch.empty(1, heads, out_channels))
+        self.lin_edge = Linear(edge_dim, heads * out_channels, bias=False) if edge_dim is not None else None
+        self.bias = Parameter(torch.empty(heads * out_channels if concat else out_channels)) if bias else None
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for lin in (self.lin_l, self.lin_r, self.lin_edge):
+            if lin is not None:
+                torch.nn.init.xavier_uniform_(lin.weight)  # PyG: weight_initializer='glorot'
+                if lin.bias is not None:
+                    torch.nn.init.zeros_(lin.bias)
+        torch.nn.init.xavier_uniform_(self.att)
+        if self.bias is not None:
+            torch.nn.init.zeros_(self.bias)
+
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Optional[Tensor] = None) -> Tensor:
+        h, c, n = self.heads, self.out_channels, x.shape[0]
+        x_l = self.lin_l(x).view(-1, h, c)
+        x_r = self.lin_r(x).view(-1, h, c)
+        if self.add_self_loops:
+            edge_index, edge_attr = remove_self_loops(edge_index, edge_attr)
+            edge_index, edge_attr = add_self_loops_mean(edge_index, edge_attr, n)
+        src, dst = edge_index[0], edge_index[1]
+        s = x_r[dst] + x_l[src]                       # x_i + x_j
+        if edge_attr is not None:
+            s = s + self.lin_edge(edge_attr).view(-1, h, c)
+        s = F.leaky_relu(s, self.negative_slope)
+        alpha = (s * self.att).sum(dim=-1)
+        alpha = segment_softmax(alpha, dst, n)
+        alpha = F.dropout(alpha, p=self.dropout, training=self.training)
+        out = scatter(x_l[src] * alpha.unsqueeze(-1), dst, n, "sum")
+        out = out.view(-1, h * c) if self.concat else out.mean(dim=1)
+        if self.bias is not None:
+            out = out + self.bias
+        return out
+
+
+class TransformerConv(Module):
+    """``gnn.TransformerConv`` as instantiated at gnnepcsaft/train/models.py:497-510
+    (concat=True, beta=False, root_weight=True, bias=True) -- SURVEY §8(f) rank 1."""
+
+    def __init__(self, in_channels: int, out_channels: int, heads: int = 1, concat: bool = True,
+                 dropout: float = 0.0, edge_dim: Optional[int] = None):
+        super().__init__()
+        self.in_channels, self.out_channels, self.heads = in_channels, out_channels, heads
+        self.concat, self.dropout, self.edge_dim = concat, dropout, edge_dim
+        self.lin_key = Linear(in_channels, heads * out_channels)
+        self.lin_query = Linear(in_channels, heads * out_channels)
+        self.lin_value = Linear(in_channels, heads * out_channels)
+        self.lin_edge = Linear(edge_dim, heads * out_channels, bias=False) if edge_dim is not None else None
+        self.lin_skip = Linear(in_channels, heads * out_channels if concat else out_channels)
+
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Optional[Tensor] = None) -> Tensor:
+        h, c, n = self.heads, self.out_channels, x.shape[0]
+        q = self.lin_query(x).view(-1, h, c)
+        k = self.lin_key(x).view(-1, h, c)
+        v = self.lin_value(x).view(-1, h, c)
+        src, dst = edge_index[0], edge_index[1]
+        k_j, v_j, q_i = k[src], v[src], q[dst]
+        if self.lin_edge is not None:
+            e = self.lin_edge(edge_attr).view(-1, h, c)
+            k_j = k_j + e
+        alpha = (q_i * k_j).sum(dim=-1) / math.sqrt(c)
+        alpha = segment_softmax(alpha, dst, n)
+        alpha = F.dropout(alpha, p=self.dropout, training=self.training)
+        out = v_j
+        if self.lin_edge is not None:
+            out = out + e
+        out = scatter(out * alpha.view(-1, h, 1), dst, n, "sum")
+        out = out.view(-1, h * c) if self.concat else out.mean(dim=1)
+        return out + self.lin_skip(x)
+
+
+# --------------------------------------------------------------------------- R9
+class BatchNorm(Module):
+    """R9 -- ``torch_geometric.nn.BatchNorm`` (models.py:184): wraps BatchNorm1d as ``.module``."""
+
+    def __init__(self, in_channels: int, eps: float = 1e-5, momentum: float = 0.1):
+        super().__init__()
+        self.module = BatchNorm1d(in_channels, eps, momentum)
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self.module(x)
+
+
+# --------------------------------------------------------------------------- R10
+class _FeatureEncoder(Module):
+    list_name = ""
+    dims: Sequence[int] = ()
+
+    def __init__(self, emb_dim: int):
+        super().__init__()
+        embs = ModuleList()
+        for d in self.dims:
+            emb = Embedding(d, emb_dim)
+            torch.nn.init.xavier_uniform_(emb.weight.data)
+            embs.append(emb)
+        setattr(self, self.list_name, embs)
+
+    def forward(self, x: Tensor) -> Tensor:
+        out: Union[int, Tensor] = 0
+        for i in range(x.shape[1]):
+            out = out + getattr(self, self.list_name)[i](x[:, i])
+        return out
+
+
+class AtomEncoder(_FeatureEncoder):
+    """R10 -- ``ogb.graphproppred.mol_encoder.AtomEncoder`` (models.py:175, 205)."""
+    list_name, dims = "atom_embedding_list", ATOM_FEATURE_DIMS
+
+
+class BondEncoder(_FeatureEncoder):
+    """R10 -- ``ogb.graphproppred.mol_encoder.BondEncoder`` (models.py:176, 206)."""
+    list_name, dims = "bond_embedding_list", BOND_FEATURE_DIMS
+
+
+# ------------------------------------------------------------------ model (L2)
+def get_conv(config: dict) -> Module:
+    """gnnepcsaft/train/models.py:441-584 restricted to the convs any config uses."""
+    aggregators = ["mean", "min", "max", "std"]
+    scalers = ["identity", "amplification", "attenuation"]
+    if config["conv"] == "PNA":
+        return PNAConv(config["hidden_dim"], config["hidden_dim"], aggregators, scalers,
+                       torch.tensor(config["deg"], dtype=torch.long), edge_dim=config["hidden_dim"],
+                       towers=config["towers"], pre_layers=config["pre_layers"],
+                       post_layers=config["post_layers"], divide_input=True)
+    if config["conv"] == "GATv2":
+        assert config["hidden_dim"] % config["heads"] == 0, "hidden_dim must be divisible by heads"
+        return GATv2Conv(config["hidden_dim"], config["hidden_dim"] // config["heads"],
+                         heads=config["heads"], concat=True, dropout=config["dropout"],
+                         edge_dim=config["hidden_dim"], add_self_loops=config["add_self_loops"])
+    if config["conv"] == "Transformer":
+        assert config["hidden_dim"] % config["heads"] == 0, "hidden_dim must be divisible by heads"
+        return TransformerConv(config["hidden_dim"], config["hidden_dim"] // config["heads"],
+                               heads=config["heads"], concat=True, dropout=config["dropout"],
+                               edge_dim=config["hidden_dim"])
+    raise ValueError(f"Unsupported convolution: {config['conv']}.")
+
+
+def get_global_pool(config: dict) -> Module:
+    """gnnepcsaft/train/models.py:587-595."""
+    if config["global_pool"] == "mean":
+        return MeanAggregation()
+    if config["global_pool"] == "max":
+        return MaxAggregation()
+    if config["global_pool"] == "add":
+        return SumAggregation()
+    raise ValueError(f"Unsupported global pooling: {config['global_pool']}.")
+
+
+class GNNePCSAFT(Module):
+    """gnnepcsaft/train/models.py:159-254, module for module."""
+
+    def __init__(self, config: dict):
+        super().__init__()
+        self.convs, self.batch_norms = ModuleList(), ModuleList()
+        self.lower_bounds = torch.tensor([1.0, 1.9, 50.0, -1 * math.log10(0.9), math.log10(200.0)])
+        self.upper_bounds = torch.tensor([25.0, 4.5, 550.0, -1 * math.log10(0.0001), math.log10(5000.0)])
+        self.num_para = config["num_para"]
+        self.node_embed = AtomEncoder(config["hidden_dim"])
+        self.edge_embed = BondEncoder(config["hidden_dim"])
+        self.dropout = Dropout(p=config["dropout"])
+        self.global_pool = get_global_pool(config)
+        self.global_pool_type = config["global_pool"]
+        for _ in range(config["propagation_depth"]):
+            self.convs.append(get_conv(config))
+            self.batch_norms.append(BatchNorm(config["hidden_dim"]))
+        h = config["hidden_dim"]
+        self.mlp = Sequential(
+            Linear(h, h // 2), BatchNorm1d(h // 2), ReLU(),
+            Linear(h // 2, h // 4), BatchNorm1d(h // 4), ReLU(),
+            Linear(h // 4, config["num_para"]),
+        )
+
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Optional[Tensor]) -> Tensor:
+        x = self.node_embed(x)
+        edge_attr = self.edge_embed(edge_attr)
+        for conv, batch_norm in zip(self.convs, self.batch_norms):
+            x = self.dropout(x)
+            x = F.relu(batch_norm(conv(x=x, edge_index=edge_index, edge_attr=edge_attr)))
+        if batch is not None:
+            x = self.global_pool(x, batch)
+        elif self.global_pool_type == "mean":
+            x = x.mean(dim=0, keepdim=True)
+        elif self.global_pool_type == "max":
+            x = x.max(dim=0, keepdim=True).values
+        elif self.global_pool_type == "add":
+            x = x.sum(dim=0, keepdim=True)
+        return self.mlp(x)
+
+    def pred_with_bounds(self, data: Any) -> Tensor:
+        x, edge_index, edge_attr, batch = data.x, data.edge_index, data.edge_attr, data.batch
+        if isinstance(x, Tensor) and isinstance(edge_index, Tensor) and isinstance(edge_attr, Tensor):
+            params = self.forward(x, edge_index, edge_attr, batch)
+            sl = slice(0, 3) if self.num_para == 3 else slice(3, None)
+            return params.clip(self.lower_bounds[sl].to(x.device), self.upper_bounds[sl].to(x.device))
+        raise ValueError("Invalid input data")
+
+
+def training_loss(pred: Tensor, target: Tensor):
+    """Loss of ``GNNePCSAFTL.training_step`` (models.py:89-92): Huber(delta=0.01) on the
+    relative error, plus the logged MAPE (torchmetrics semantics: mean(|p-t| / max(|t|, 1.17e-06)))."""
+    ape = (pred - target) / target
+    loss = F.huber_loss(ape, torch.zeros_like(ape), delta=0.01)
+    mape = ((pred - target).abs() / target.abs().clamp(min=1.17e-06)).mean()
+    return loss, mape
