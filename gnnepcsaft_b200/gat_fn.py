@@ -1,0 +1,68 @@
+"""GATv2Conv forward / backward as one autograd node over the gnnx kernels."""
+
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+
+from . import ops
+from .functional import _c
+
+
+class GATMeta:
+    __slots__ = ("g", "codes", "heads", "c", "slope", "self_loops")
+
+    def __init__(self, g, codes, heads, c, slope, self_loops):
+        self.g, self.codes, self.heads, self.c, self.slope, self.self_loops = g, codes, heads, c, slope, self_loops
+
+
+class GATv2ConvFn(Function):
+    """params: lin_l.weight, lin_l.bias, lin_r.weight, lin_r.bias, lin_edge.weight, att, bias."""
+
+    @staticmethod
+    def forward(ctx, x, efeat, meta: GATMeta, wl, bl, wr, br, wedge, att, bias):
+        g, heads, c = meta.g, meta.heads, meta.c
+        H = heads * c
+        N = x.shape[0]
+        x, efeat = _c(x), _c(efeat)
+        xlr = torch.empty((N, 2 * H), dtype=torch.float32, device=x.device)
+        ops.gemm(x, wl, trans_b=True, bias=bl, out=xlr[:, :H])
+        ops.gemm(x, wr, trans_b=True, bias=br, out=xlr[:, H:])
+        e = ops.gemm(efeat, wedge, trans_b=True)                  # [E or 60, H], lin_edge has no bias
+        eidx = meta.codes if meta.codes is not None else g.csr_eid
+        att_flat = att.reshape(-1)
+        out, alpha = ops.gatv2_fwd(xlr, e, eidx, att_flat, bias, g, heads, c, meta.slope, meta.self_loops)
+        ctx.meta = meta
+        ctx.has = (bl is not None, br is not None, bias is not None)
+        ctx.save_for_backward(x, efeat, xlr, e, alpha, wl, wr, wedge, att)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dout):
+        meta: GATMeta = ctx.meta
+        g, heads, c = meta.g, meta.heads, meta.c
+        H = heads * c
+        x, efeat, xlr, e, alpha, wl, wr, wedge, att = ctx.saved_tensors
+        dout = _c(dout)
+        eidx = meta.codes if meta.codes is not None else g.csr_eid
+        dxlr, datt, ds = ops.gatv2_bwd(dout, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
+                                       meta.self_loops)
+        dl, dr = dxlr[:, :H], dxlr[:, H:]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.gemm(dl, wl)
+            ops.gemm(dr, wr, out=dx, accumulate=True)
+        dwl = ops.gemm(dl, x, trans_a=True)
+        dwr = ops.gemm(dr, x, trans_a=True)
+        dbl = ops.colsum(dl) if ctx.has[0] else None
+        dbr = ops.colsum(dr) if ctx.has[1] else None
+        dbias = ops.colsum(dout) if ctx.has[2] else None
+        table = meta.codes is not None
+        de = ops.gatv2_edge_grad(ds, g, H, meta.self_loops, original_order=not table)
+        if table:
+            de = ops.code_segment_sum(de, meta.codes, efeat.shape[0])
+        dwedge = ops.gemm(de, efeat, trans_a=True)
+        defeat = ops.gemm(de, wedge) if ctx.needs_input_grad[1] else None
+        return dx, defeat, None, dwl, dbl, dwr, dbr, dwedge, datt.view_as(att), dbias

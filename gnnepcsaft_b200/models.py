@@ -1,0 +1,137 @@
+"""Drop-in ``GNNePCSAFT`` (reference: gnnepcsaft/train/models.py:159-254, 441-606).
+
+Same config keys, submodule / state-dict names, ``forward(x, edge_index, edge_attr, batch)`` and
+``pred_with_bounds(data)`` as the reference model; the body runs on the gnnx sm_100a kernels:
+the CSR is built once per batch, bond features are kept factored (60-row table + codes), and
+BatchNorm + ReLU are one kernel per layer.
+"""
+
+from __future__ import annotations
+
+import math
+from typing import Any, Optional, Union
+
+import torch
+import torch.nn.functional as F
+from torch import Tensor
+from torch.nn import BatchNorm1d, Dropout, Linear, Module, ModuleList, ReLU, Sequential
+
+from . import functional as Fn
+from . import nn as gnn
+from . import ops
+from .graph import Batch, batch_from_reference_tensors
+
+
+def get_conv(config: dict) -> Module:
+    """Conv factory, reference models.py:441-584 (the convs any file in ``configs/`` selects)."""
+    aggregators = ["mean", "min", "max", "std"]
+    scalers = ["identity", "amplification", "attenuation"]
+    if config["conv"] == "PNA":
+        return gnn.PNAConv(
+            in_channels=config["hidden_dim"], out_channels=config["hidden_dim"], aggregators=aggregators,
+            scalers=scalers, deg=torch.tensor(config["deg"], dtype=torch.long), edge_dim=config["hidden_dim"],
+            towers=config["towers"], pre_layers=config["pre_layers"], post_layers=config["post_layers"],
+            divide_input=True)
+    if config["conv"] == "GATv2":
+        assert config["hidden_dim"] % config["heads"] == 0, "hidden_dim must be divisible by heads"
+        return gnn.GATv2Conv(
+            in_channels=config["hidden_dim"], out_channels=config["hidden_dim"] // config["heads"],
+            heads=config["heads"], concat=True, dropout=config["dropout"], edge_dim=config["hidden_dim"],
+            add_self_loops=config["add_self_loops"])
+    raise ValueError(f"Unsupported convolution: {config['conv']}.")
+
+
+def get_global_pool(config: dict) -> Module:
+    """Pool factory, reference models.py:587-595."""
+    if config["global_pool"] == "mean":
+        return gnn.MeanAggregation()
+    if config["global_pool"] == "max":
+        return gnn.MaxAggregation()
+    if config["global_pool"] == "add":
+        return gnn.SumAggregation()
+    raise ValueError(f"Unsupported global pooling: {config['global_pool']}.")
+
+
+class GNNePCSAFT(Module):
+    """Graph neural network to predict PC-SAFT parameters (reference models.py:159-254)."""
+
+    def __init__(self, config: dict):
+        super().__init__()
+        self.convs = ModuleList()
+        self.batch_norms = ModuleList()
+        self.lower_bounds = torch.tensor([1.0, 1.9, 50.0, -1 * math.log10(0.9), math.log10(200.0)])
+        self.upper_bounds = torch.tensor([25.0, 4.5, 550.0, -1 * math.log10(0.0001), math.log10(5000.0)])
+        self.num_para = config["num_para"]
+        self.node_embed = gnn.AtomEncoder(config["hidden_dim"])
+        self.edge_embed = gnn.BondEncoder(config["hidden_dim"])
+        self.dropout = Dropout(p=config["dropout"])
+        self.global_pool = get_global_pool(config)
+        self.global_pool_type = config["global_pool"]
+        for _ in range(config["propagation_depth"]):
+            self.convs.append(get_conv(config))
+            self.batch_norms.append(gnn.BatchNorm(config["hidden_dim"]))
+        h = config["hidden_dim"]
+        self.mlp = Sequential(
+            Linear(h, h // 2), BatchNorm1d(h // 2), ReLU(),
+            Linear(h // 2, h // 4), BatchNorm1d(h // 4), ReLU(),
+            Linear(h // 4, config["num_para"]),
+        )
+        self._bounds_dev = None
+
+    # -- reference signature -------------------------------------------------------------
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Union[Tensor, None],
+                num_graphs: Optional[int] = None) -> Tensor:
+        """Forward pass of the model (same inputs / output as the reference's ``forward``)."""
+        if not x.is_cuda:
+            raise RuntimeError("GNNePCSAFT (gnnx): inputs must be CUDA tensors; there is no CPU fallback")
+        b = batch_from_reference_tensors(x.contiguous(), edge_index.contiguous(), edge_attr.contiguous(), batch,
+                                         num_graphs)
+        return self.forward_batch(b)
+
+    # -- fast path: everything prebuilt on the device --------------------------------------
+    def forward_batch(self, b: Batch) -> Tensor:
+        g = b.index
+        x_idx = b.x if b.x.dtype == torch.uint8 else ops.narrow_u8(b.x)
+        ea_u8 = b.edge_attr if b.edge_attr.dtype == torch.uint8 else ops.narrow_u8(b.edge_attr)
+        x = self.node_embed(x_idx)
+        edges = self.edge_embed.forward_table(ops.edge_codes(ea_u8.contiguous(), g.csr_eid))
+        for conv, batch_norm in zip(self.convs, self.batch_norms):
+            x = self.dropout(x)
+            x = batch_norm(conv(x, b.edge_index, edges, index=g), relu=True)
+        if b.batch is not None or b.graph_ptr is not None:
+            x = self.global_pool(x, ptr=b.graph_ptr)
+        else:
+            n = x.shape[0]
+            ptr = torch.tensor([0, n], dtype=torch.int32, device=x.device)
+            x = Fn.segment_pool(x, ptr, self.global_pool_type)
+        return self._head(x)
+
+    def _head(self, x: Tensor) -> Tensor:
+        m = self.mlp
+        x = Fn.batch_norm(Fn.linear(x, m[0].weight, m[0].bias), m[1], relu=True)
+        x = Fn.batch_norm(Fn.linear(x, m[3].weight, m[3].bias), m[4], relu=True)
+        return Fn.linear(x, m[6].weight, m[6].bias)
+
+    def pred_with_bounds(self, data: Any) -> Tensor:
+        """Forward pass of the model with bounds (reference models.py:229-254)."""
+        if isinstance(data, Batch) and data.index is not None:
+            params = self.forward_batch(data)
+            dev = params.device
+        else:
+            x, edge_index, edge_attr, batch = data.x, data.edge_index, data.edge_attr, getattr(data, "batch", None)
+            if not (isinstance(x, Tensor) and isinstance(edge_index, Tensor) and isinstance(edge_attr, Tensor)):
+                raise ValueError("Invalid input data")
+            params = self.forward(x, edge_index, edge_attr, batch, getattr(data, "num_graphs", None))
+            dev = x.device
+        if self._bounds_dev is None or self._bounds_dev[0].device != dev:
+            sl = slice(0, 3) if self.num_para == 3 else slice(3, None)
+            self._bounds_dev = (self.lower_bounds[sl].to(dev), self.upper_bounds[sl].to(dev))
+        return params.clip(self._bounds_dev[0], self._bounds_dev[1])
+
+
+def create_model(config: dict, deg: list) -> GNNePCSAFT:
+    """Reference ``create_model`` (models.py:598-606) without the Lightning wrapper."""
+    config["deg"] = deg
+    if config.get("model", "gnn").lower() == "gnn":
+        return GNNePCSAFT(config)
+    raise ValueError(f"Unsupported model: {config['model']}.")
