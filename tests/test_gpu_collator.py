@@ -1,0 +1,94 @@
+"""GPU collator parity (integer work: BIT-EXACT against the oracle)."""
+import numpy as np
+import pytest
+import torch
+
+from gnnepcsaft_b200 import graph, ops, synth
+from oracle import pyg_restated as O
+from tests.util import make_batch, oracle_graphs
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _check_csr(ei: torch.Tensor, n: int):
+    g = graph.GraphIndex.build(ei.to(DEV), n, check=True)
+    torch.cuda.synchronize()
+    ref = O.csr_reference(ei, n)
+    assert torch.equal(g.rowptr.cpu().long(), ref["rowptr"])
+    assert torch.equal(g.csr_eid.cpu().long(), ref["eid"])
+    assert torch.equal(g.csr_src.cpu().long(), ref["src"])
+    assert torch.equal(g.colptr.cpu().long(), ref["colptr"])
+    pos = torch.empty(ei.shape[1], dtype=torch.long)
+    pos[ref["eid"]] = torch.arange(ei.shape[1])
+    assert torch.equal(g.pos_of_eid.cpu().long(), pos)
+    assert torch.equal(g.csc_pos.cpu().long(), pos[ref["eid_by_src"]])
+    assert torch.equal(g.csc_dst.cpu().long(), ref["dst_by_src"])
+    assert torch.equal(g.in_degree.cpu().long(), ref["in_degree"])
+    return g
+
+
+def test_csr_molecular_batch_bit_exact():
+    _, b = make_batch(256, seed=11)
+    _check_csr(b["edge_index"], b["x"].shape[0])
+
+
+@pytest.mark.parametrize("n,e,seed", [(1, 0, 0), (7, 0, 1), (5, 40, 2), (1000, 5000, 3), (300, 40000, 4), (70000, 150000, 5)])
+def test_csr_random_multigraph_bit_exact(n, e, seed):
+    """Random COO with duplicates, self loops, isolated nodes and hub rows (> 32 entries: heap-sort path)."""
+    gen = torch.Generator().manual_seed(seed)
+    ei = torch.randint(0, n, (2, e), generator=gen)
+    if e > 100:
+        ei[1, : e // 3] = 0                      # one hub destination
+    _check_csr(ei, n)
+
+
+def test_csr_rejects_out_of_range():
+    ei = torch.tensor([[0, 1, 5], [1, 0, 2]])
+    with pytest.raises(IndexError):
+        graph.GraphIndex.build(ei.to(DEV), 3, check=True)
+
+
+def test_degree_histogram_equals_calc_deg():
+    graphs, b = make_batch(200, seed=5)
+    g = graph.GraphIndex.build(b["edge_index"].to(DEV), b["x"].shape[0])
+    hist, mx = graph.calc_deg_from_index(g)
+    ref = O.calc_deg(oracle_graphs(graphs))
+    assert hist[: int(mx.item()) + 1].tolist() == ref
+    assert int(hist.sum()) == b["x"].shape[0]
+
+
+def test_graph_ptr_from_batch():
+    _, b = make_batch(100, seed=6)
+    gp = ops.graph_ptr_from_batch(b["batch"].to(DEV), 100).cpu().long()
+    ref = torch.zeros(101, dtype=torch.long)
+    ref[1:] = torch.cumsum(torch.bincount(b["batch"], minlength=100), 0)
+    assert torch.equal(gp, ref)
+
+
+def test_packed_store_collate_equals_pyg_collate():
+    graphs = synth.make_graphs(300, 21, 1, 30, 0.1)
+    store = graph.DeviceGraphStore(synth.pack(graphs), DEV)
+    ids = np.random.default_rng(0).permutation(300)[:128]
+    b = store.collate(ids)
+    ref = O.collate([oracle_graphs(graphs)[i] for i in ids])
+    assert torch.equal(b.x.cpu().long(), ref.x)
+    assert torch.equal(torch.stack([b._src32, b._dst32]).cpu().long(), ref.edge_index)
+    assert torch.equal(b.edge_attr.cpu().long(), ref.edge_attr)
+    assert torch.equal(b.batch.cpu().long(), ref.batch)
+    assert torch.equal(b.graph_ptr.cpu().long(), ref.ptr)
+    assert torch.equal(b.para.cpu(), ref.para)
+    csr = O.csr_reference(ref.edge_index, ref.num_nodes)
+    assert torch.equal(b.index.csr_eid.cpu().long(), csr["eid"])
+    assert store.calc_deg(100) == O.calc_deg(oracle_graphs(graphs))
+
+
+def test_edge_codes_and_narrow():
+    _, b = make_batch(64, seed=8)
+    ea = b["edge_attr"]
+    g = graph.GraphIndex.build(b["edge_index"].to(DEV), b["x"].shape[0])
+    ea8 = ops.narrow_u8(ea.to(DEV))
+    assert torch.equal(ea8.cpu().long(), ea)
+    codes = ops.edge_codes(ea8, g.csr_eid).cpu().long()
+    sorted_ea = ea[g.csr_eid.cpu().long()]
+    assert torch.equal(codes, (sorted_ea[:, 0] * 6 + sorted_ea[:, 1]) * 2 + sorted_ea[:, 2])

@@ -1,0 +1,189 @@
+"""Per-kernel parity against the CPU oracle on identical seeded inputs.
+
+Tolerance (north_star): fp32 outputs and gradients within rel 1e-5 (atol 1e-6 for near-zero entries) of the
+fp32 oracle run at matmul precision "highest"; the gnnx GEMMs run at GNNX_PREC_FP32 here.
+"""
+import math
+
+import pytest
+import torch
+
+from gnnepcsaft_b200 import functional as Fn
+from gnnepcsaft_b200 import graph, nn as gnn, ops
+from oracle import pyg_restated as O
+from tests.util import assert_close, make_batch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+RTOL, ATOL = 1e-5, 1e-6
+
+
+@pytest.fixture(autouse=True)
+def _precision():
+    torch.set_float32_matmul_precision("highest")
+    ops.set_matmul_precision("fp32")
+    torch.manual_seed(0)
+
+
+# ------------------------------------------------------------------ GEMM
+@pytest.mark.parametrize("M,N,K", [(1, 1, 1), (60, 64, 64), (257, 130, 70), (1000, 256, 256), (4096, 3, 64), (128, 768, 1024)])
+@pytest.mark.parametrize("ta,tb", [(False, True), (False, False), (True, False), (True, True)])
+def test_gemm_fp32(M, N, K, ta, tb):
+    a = torch.randn((K, M) if ta else (M, K))
+    b = torch.randn((N, K) if tb else (K, N))
+    bias = torch.randn(N)
+    ref = (a.t() if ta else a).double() @ (b.t() if tb else b).double() + bias.double()
+    out = ops.gemm(a.to(DEV), b.to(DEV), trans_a=ta, trans_b=tb, bias=bias.to(DEV))
+    assert_close(out, ref, RTOL, ATOL, f"gemm {M}x{N}x{K}")
+    out2 = ops.gemm(a.to(DEV), b.to(DEV), trans_a=ta, trans_b=tb, bias=bias.to(DEV), relu=True)
+    assert_close(out2, ref.clamp(min=0), RTOL, ATOL, "gemm+relu")
+
+
+def test_gemm_splitk_weight_gradient_shape_and_slices():
+    rows = 30000
+    dy, x = torch.randn(rows, 96), torch.randn(rows, 200)
+    ref = dy.double().t() @ x[:, 40:168].double()
+    dw = torch.zeros(96, 300, device=DEV)
+    ops.gemm(dy.to(DEV), x.to(DEV)[:, 40:168], trans_a=True, out=dw[:, 100:228])       # strided A/B/C views
+    assert_close(dw[:, 100:228], ref, RTOL, ATOL, "split-K dW")
+    assert float(dw[:, :100].abs().sum()) == 0.0 and float(dw[:, 228:].abs().sum()) == 0.0
+    ops.gemm(dy.to(DEV), x.to(DEV)[:, 40:168], trans_a=True, out=dw[:, 100:228], accumulate=True)
+    assert_close(dw[:, 100:228], 2 * ref, RTOL, ATOL, "split-K accumulate")
+    a1 = ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True)
+    a2 = ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True)
+    assert torch.equal(a1, a2)                                                          # deterministic
+
+
+def test_colsum():
+    x = torch.randn(50001, 70)
+    assert_close(ops.colsum(x.to(DEV)), x.double().sum(0), RTOL, ATOL, "colsum")
+    assert_close(ops.colsum(x.to(DEV)[:, 3:40]), x[:, 3:40].double().sum(0), RTOL, ATOL, "colsum slice")
+
+
+# ------------------------------------------------------------------ embeddings
+@pytest.mark.parametrize("H", [64, 256])
+def test_atom_bond_encoder_fwd_bwd(H):
+    _, b = make_batch(64, seed=3)
+    for cls_o, cls_p, key in ((O.AtomEncoder, gnn.AtomEncoder, "x"), (O.BondEncoder, gnn.BondEncoder, "edge_attr")):
+        mo = cls_o(H)
+        mp = cls_p(H).to(DEV)
+        mp.load_state_dict(mo.state_dict())
+        out_o = mo(b[key])
+        out_p = mp(b[key].to(DEV))
+        assert torch.equal(out_p.cpu(), out_o), "embedding sums are order-exact"
+        w = torch.randn_like(out_o)
+        (out_o * w).sum().backward()
+        (out_p * w.to(DEV)).sum().backward()
+        for (n, po), (_, pp) in zip(mo.named_parameters(), mp.named_parameters()):
+            assert_close(pp.grad, po.grad, RTOL, ATOL, f"{key} d{n}")
+
+
+def test_bond_table_matches_dense_encoder():
+    _, b = make_batch(32, seed=4)
+    enc = gnn.BondEncoder(64).to(DEV)
+    g = graph.GraphIndex.build(b["edge_index"].to(DEV), b["x"].shape[0])
+    dense = enc(b["edge_attr"].to(DEV))
+    et = enc.forward_table(ops.edge_codes(ops.narrow_u8(b["edge_attr"].to(DEV)), g.csr_eid))
+    assert_close(et.table[et.codes.long()], dense[g.csr_eid.long()], 1e-6, 1e-7, "bond table")
+
+
+# ------------------------------------------------------------------ PNA aggregation
+@pytest.mark.parametrize("T,F", [(1, 64), (1, 256), (4, 16), (8, 32), (2, 12)])
+def test_pna_aggregate_fwd_bwd(T, F):
+    _, b = make_batch(48, seed=9)
+    ei, N = b["edge_index"], b["x"].shape[0]
+    E, H = ei.shape[1], T * F
+    g = graph.GraphIndex.build(ei.to(DEV), N)
+    perm = g.csr_eid.cpu().long()
+    m = torch.randn(E, H)
+    m[::7] = m[1::7][: m[::7].shape[0]]                    # plant exact ties between neighbouring messages
+    m_o = m.clone().requires_grad_(True)
+    mv = m_o.view(E, T, F)
+    ref = torch.cat([O._AGGRS[a](mv, ei[1], N) for a in ("mean", "min", "max", "std")], -1)   # [N,T,4F]
+    m_sorted = m[perm].contiguous().to(DEV)
+    agg = ops.pna_aggregate_fwd(m_sorted, g.rowptr, T)
+    assert_close(agg.view(N, T, 4 * F), ref, RTOL, ATOL, "aggregate fwd")
+    w = torch.randn_like(ref)
+    (ref * w).sum().backward()
+    dm = ops.pna_aggregate_bwd(w.reshape(N, -1).contiguous().to(DEV), m_sorted, agg, g.rowptr, T)
+    dm_orig = torch.empty_like(m)
+    dm_orig[perm] = dm.cpu()
+    assert_close(dm_orig, m_o.grad, RTOL, ATOL, "aggregate bwd")
+
+
+def test_pna_aggregate_in_degree_one_std_is_zero():
+    ei = torch.tensor([[0, 1], [1, 0]])
+    g = graph.GraphIndex.build(ei.to(DEV), 3)
+    m = torch.randn(2, 8, device=DEV)
+    agg = ops.pna_aggregate_fwd(m, g.rowptr, 1).view(3, 4, 8)
+    assert float(agg[:, 3].abs().sum()) == 0.0 and float(agg[2].abs().sum()) == 0.0
+    assert torch.equal(agg[0, 0], m[0]) and torch.equal(agg[0, 1], m[0]) and torch.equal(agg[0, 2], m[0])
+
+
+# ------------------------------------------------------------------ BatchNorm / pooling / loss / optimizer
+@pytest.mark.parametrize("rows,C,relu", [(800, 64, True), (5000, 256, True), (33, 32, False)])
+def test_batchnorm_relu_fwd_bwd(rows, C, relu):
+    x = torch.randn(rows, C) * 3 + 1.5
+    bo = O.BatchNorm(C)
+    with torch.no_grad():
+        bo.module.weight.uniform_(0.5, 1.5); bo.module.bias.normal_()
+    bp = gnn.BatchNorm(C).to(DEV)
+    bp.load_state_dict(bo.state_dict())
+    xo = x.clone().requires_grad_(True)
+    xp = x.clone().to(DEV).requires_grad_(True)
+    yo = bo(xo)
+    yo = torch.relu(yo) if relu else yo
+    yp = bp(xp, relu=relu)
+    assert_close(yp, yo, RTOL, ATOL, "bn fwd")
+    w = torch.randn_like(yo)
+    (yo * w).sum().backward(); (yp * w.to(DEV)).sum().backward()
+    assert_close(xp.grad, xo.grad, RTOL, ATOL, "bn dx")
+    assert_close(bp.module.weight.grad, bo.module.weight.grad, RTOL, ATOL, "bn dweight")
+    assert_close(bp.module.bias.grad, bo.module.bias.grad, RTOL, ATOL, "bn dbias")
+    assert_close(bp.module.running_mean, bo.module.running_mean, RTOL, ATOL, "running_mean")
+    assert_close(bp.module.running_var, bo.module.running_var, RTOL, ATOL, "running_var")
+    assert int(bp.module.num_batches_tracked) == 1
+    bo.eval(); bp.eval()
+    assert_close(bp(x.to(DEV)), bo(x), RTOL, ATOL, "bn eval")
+
+
+@pytest.mark.parametrize("mode,cls_o,cls_p", [("add", O.SumAggregation, gnn.SumAggregation), ("mean", O.MeanAggregation, gnn.MeanAggregation),
+                                               ("max", O.MaxAggregation, gnn.MaxAggregation)])
+def test_global_pool_fwd_bwd(mode, cls_o, cls_p):
+    _, b = make_batch(40, seed=2)
+    N = b["x"].shape[0]
+    x = torch.randn(N, 64).round(decimals=1)             # rounding plants ties for max
+    xo, xp = x.clone().requires_grad_(True), x.clone().to(DEV).requires_grad_(True)
+    yo, yp = cls_o()(xo, b["batch"]), cls_p()(xp, b["batch"].to(DEV))
+    assert_close(yp, yo, RTOL, ATOL, f"pool {mode} fwd")
+    w = torch.randn_like(yo)
+    (yo * w).sum().backward(); (yp * w.to(DEV)).sum().backward()
+    assert_close(xp.grad, xo.grad, RTOL, ATOL, f"pool {mode} bwd")
+
+
+def test_relhuber_loss_and_grad():
+    pred = (torch.rand(500, 3) * 5 + 1).requires_grad_(True)
+    target = torch.rand(500, 3) * 5 + 1
+    with torch.no_grad():
+        pred[:100] = target[:100] * (1 + 0.004 * torch.randn(100, 3))   # inside the quadratic zone
+    loss, mape = O.training_loss(pred, target)
+    loss.backward()
+    out2, dpred = ops.relhuber_fwd_bwd(pred.detach().to(DEV), target.to(DEV), 0.01)
+    assert_close(out2[0], loss, RTOL, 1e-9, "loss")
+    assert_close(out2[1], mape, RTOL, 1e-9, "mape")
+    assert_close(dpred, pred.grad, RTOL, 1e-10, "dloss/dpred")
+
+
+def test_adamw_amsgrad_matches_torch():
+    p = torch.randn(10007)
+    po = p.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([po], lr=1e-3, weight_decay=1e-2, amsgrad=True, eps=1e-5)
+    pp = p.clone().to(DEV)
+    m, v, vm = torch.zeros_like(pp), torch.zeros_like(pp), torch.zeros_like(pp)
+    for step in range(1, 6):
+        g = torch.randn(10007)
+        po.grad = g.clone()
+        opt.step()
+        ops.adamw_amsgrad_(pp, (g * 4).to(DEV), m, v, vm, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-5, weight_decay=1e-2,
+                           step=step, grad_scale=0.25)
+    assert_close(pp, po, 1e-6, 1e-7, "adamw")
