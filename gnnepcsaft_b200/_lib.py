@@ -20,7 +20,7 @@ _SCALARS = {
     "int64_t": ctypes.c_int64, "int32_t": ctypes.c_int32, "int": ctypes.c_int,
     "size_t": ctypes.c_size_t, "float": ctypes.c_float,
 }
-_PROTO = re.compile(r"GNNX_API\s+(const\s+char\s*\*|int|size_t)\s+(gnnx_\w+)\s*\(([^;]*?)\)\s*;", re.S)
+_PROTO = re.compile(r"GNNX_API\s+(const\s+char\s*\*|int64_t|int|size_t)\s+(gnnx_\w+)\s*\(([^;]*?)\)\s*;", re.S)
 
 
 def parse_header(path: Path = HEADER) -> Dict[str, Tuple[object, List[object]]]:
@@ -72,6 +72,10 @@ class _Lib:
         rc = getattr(self._dll, name)(*args)
         if rc != 0:
             raise GnnxError(f"{name} failed with code {rc}: {self.last_error()}")
+
+    def launch_count(self) -> int:
+        """Kernels launched by libgnnx so far in this process."""
+        return int(self._dll.gnnx_launch_count())
 
     def query(self, name: str, *args) -> int:
         """Call a ``size_t``-returning ``*_workspace_bytes`` entry point."""

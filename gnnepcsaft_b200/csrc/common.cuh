@@ -11,7 +11,11 @@ namespace gnnx {
 // Thread-local last-error message, read through gnnx_last_error().
 int set_error(int code, const char* fmt, ...);
 
-inline int check_launch(const char* what) {
+// Number of kernels this library has launched (read through gnnx_launch_count()).
+void count_launches(int n);
+
+inline int check_launch(const char* what, int kernels = 1) {
+    count_launches(kernels);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error((int)e, "%s: %s", what, cudaGetErrorString(e));
     return GNNX_OK;

@@ -10,6 +10,8 @@
 namespace gnnx {
 
 static thread_local char g_err[512] = "";
+static unsigned long long g_launches = 0;
+void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
 int set_error(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -225,7 +227,7 @@ static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t
         k_sort_rows_dst<IdxT><<<nb, 128, 0, st>>>(src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
         k_sort_rows_src<IdxT><<<nb, 128, 0, st>>>(dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
     }
-    return check_launch("csr_build");
+    return check_launch("csr_build", E > 0 ? 7 : 3);
 }
 
 // ------------------------------------------------------------------ degree histogram / graph_ptr / misc
@@ -299,6 +301,7 @@ extern "C" {
 
 int gnnx_abi_version(void) { return GNNX_ABI_VERSION; }
 const char* gnnx_last_error(void) { return gnnx::g_err; }
+int64_t gnnx_launch_count(void) { return (int64_t)__atomic_load_n(&gnnx::g_launches, __ATOMIC_RELAXED); }
 
 size_t gnnx_csr_workspace_bytes(int64_t N, int64_t E) {
     size_t n1 = (size_t)N + 1, e = (size_t)(E > 0 ? E : 1);

@@ -123,7 +123,7 @@ int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
     k_embed_bwd_partial<<<dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st>>>(
         idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws);
     k_reduce_partials<<<min(ceil_div(count, 256), kNumSMs * 8), 256, 0, st>>>((const float*)ws, nchunks, count, dtable);
-    return check_launch("embed_sum_bwd");
+    return check_launch("embed_sum_bwd", 2);
 }
 
 }  // extern "C"

@@ -453,7 +453,7 @@ int gnnx_gatv2_bwd(const float* dout, const float* xlr, const float* e, int64_t 
     GAT_DISPATCH_NQ(H, CALL);
 #undef CALL
     k_sum_rows<<<ceil_div(H, 128), 128, 0, st>>>((const float*)ws, grid, H, datt);
-    return check_launch("gatv2_bwd");
+    return check_launch("gatv2_bwd", 3);
 }
 
 int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* csr_src, const int32_t* csr_eid, int64_t N,

@@ -160,7 +160,7 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
 #undef LAUNCH
     if (partial)
         k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags);
-    return check_launch("gemm_simt");
+    return check_launch("gemm_simt", partial ? 2 : 1);
 }
 
 // ------------------------------------------------------------------ column sums
@@ -216,7 +216,7 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
     int rpc = ceil_div(rows, nch);
     k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
     k_colsum_final<<<ceil_div(cols, 128), 128, 0, st>>>((const float*)ws, nch, (int)cols, out);
-    return check_launch("colsum");
+    return check_launch("colsum", 2);
 }
 
 }  // extern "C"

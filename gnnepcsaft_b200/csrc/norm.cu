@@ -326,7 +326,7 @@ int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weigh
         k_bn_eval_stats<<<ceil_div(C, 128), 128, 0, st>>>(running_mean, running_var, C, eps, save_mean, save_rstd);
     }
     k_bn_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(x, rows, C, weight, bias, save_mean, save_rstd, relu, y);
-    return check_launch("bn_relu_fwd");
+    return check_launch("bn_relu_fwd", training ? 3 : 2);
 }
 
 int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
@@ -341,7 +341,7 @@ int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t ro
     k_bn_bwd_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
     k_bn_bwd_final<<<ceil_div(C, 128), 128, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
     k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx);
-    return check_launch("bn_relu_bwd");
+    return check_launch("bn_relu_bwd", 3);
 }
 
 int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, int32_t C, int32_t mode, float* out, void* stream) {

@@ -378,7 +378,7 @@ int gnnx_pna_gather_bwd(const float* dh, const int32_t* rowptr, const int32_t* c
         GNNX_REQUIRE(ld_dr % 4 == 0 && csr_eid, "pna_gather_bwd: dr_edge needs csr_eid and an aligned stride");
         k_permute_rows<<<flat_grid(E * (H / 4)), 256, 0, as_stream(stream)>>>(dh, csr_eid, E, H, dr_edge, ld_dr);
     }
-    return check_launch("pna_gather_bwd");
+    return check_launch("pna_gather_bwd", (dr_edge && E > 0) ? 2 : 1);
 }
 
 size_t gnnx_code_segment_sum_workspace_bytes(int64_t rows, int32_t num_codes, int32_t H) {
@@ -400,7 +400,7 @@ int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, i
         GNNX_CUDA(cudaFuncSetAttribute(k_code_sum_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_code_sum_partial<<<dim3(ceil_div(H, 32), nch), dim3(32, kCodeRows), smem, st>>>(dh, codes, (int)rows, ncodes, H, rpc, (float*)ws);
     k_sum_partials<<<flat_grid(count), 256, 0, st>>>((const float*)ws, nch, count, dtable);
-    return check_launch("code_segment_sum");
+    return check_launch("code_segment_sum", 2);
 }
 
 int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t N, int32_t T, int32_t F, float* agg, void* stream) {

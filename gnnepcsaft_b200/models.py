@@ -121,7 +121,7 @@ class GNNePCSAFT(Module):
             x, edge_index, edge_attr, batch = data.x, data.edge_index, data.edge_attr, getattr(data, "batch", None)
             if not (isinstance(x, Tensor) and isinstance(edge_index, Tensor) and isinstance(edge_attr, Tensor)):
                 raise ValueError("Invalid input data")
-            params = self.forward(x, edge_index, edge_attr, batch, getattr(data, "num_graphs", None))
+            params = self.forward(x, edge_index, edge_attr, batch, getattr(data, "num_graphs", None) or None)
             dev = x.device
         if self._bounds_dev is None or self._bounds_dev[0].device != dev:
             sl = slice(0, 3) if self.num_para == 3 else slice(3, None)

@@ -21,6 +21,12 @@ from . import ops
 from .functional import _c
 
 
+# Debug taps: when set to a list, every PNAConv forward appends dict(agg [N, T*4*F], m [E, T*F] dst-sorted, g)
+# (tests read which Std entries were zero-masked and which messages were the min / max of their row).
+CAPTURE_AGG = None
+CAPTURE_BWD = None
+
+
 class PNAMeta:
     """Non-tensor arguments of one PNAConv call."""
 
@@ -100,6 +106,8 @@ class PNAConvFn(Function):
         hs = _tower_chain_fwd(h, pre, T, F, 1)
         m = hs[-1]
         agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
+        if CAPTURE_AGG is not None:
+            CAPTURE_AGG.append(dict(agg=agg, m=m, g=g))
         y0 = torch.empty((N, Ho), dtype=torch.float32, device=dev)
         z = torch.empty((N, 3 * Ho), dtype=torch.float32, device=dev)
         for t in range(T):
@@ -163,6 +171,8 @@ class PNAConvFn(Function):
             grads[id(bp)] = db0[t * Fo:(t + 1) * Fo] if T > 1 else db0
         # aggregators
         dm = ops.pna_aggregate_bwd(dagg, hs[-1], agg, g.rowptr, T)
+        if CAPTURE_BWD is not None:
+            CAPTURE_BWD.append(dict(dagg=dagg, dm=dm, m=hs[-1], agg=agg, dz=dz, dy0=dy0, d_post=d))
         # pre layers 1.. (reverse) -> gradient at h (after the first layer's activation)
         dh = _tower_chain_bwd(dm, hs, pre, T, F, 1, grads)
         if meta.pre_layers > 1:

@@ -1,0 +1,103 @@
+"""Training step for the hot path: forward, relative-error Huber loss, backward, (one NCCL all-reduce of the flat
+gradient), AdamW-amsgrad -- the body of ``GNNePCSAFTL.training_step`` + ``configure_optimizers``
+(reference: gnnepcsaft/train/models.py:47-108) without the Lightning shell.
+
+Data parallelism: one process per GPU, graphs sharded by rank, per-rank BatchNorm statistics
+(the reference's DDP does not use SyncBN), and exactly ONE all-reduce per step over a single contiguous fp32
+gradient buffer; the 1/world_size of the mean is folded into the optimizer kernel.
+"""
+
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+from torch import Tensor
+
+from . import ops
+from .graph import Batch
+
+
+class FlatParameters:
+    """Re-homes every parameter (and its gradient) of ``model`` into one contiguous fp32 buffer each."""
+
+    def __init__(self, model: torch.nn.Module):
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        if not self.params:
+            raise ValueError("model has no trainable parameters")
+        dev = self.params[0].device
+        sizes = [p.numel() for p in self.params]
+        # keep every view 16-byte aligned so vectorised kernels can run on parameter slices
+        self.offsets, off = [], 0
+        for n in sizes:
+            self.offsets.append(off)
+            off += (n + 3) // 4 * 4
+        self.numel = off
+        self.data = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(off, dtype=torch.float32, device=dev)
+        for p, o in zip(self.params, self.offsets):
+            n = p.numel()
+            self.data[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.data[o:o + n].view(p.shape)
+            p.grad = self.grad[o:o + n].view(p.shape)
+
+    def zero_grad(self) -> None:
+        self.grad.zero_()
+        for p, o in zip(self.params, self.offsets):       # autograd may have swapped .grad for a fresh tensor
+            g = p.grad
+            if g is None or g.data_ptr() != self.grad.data_ptr() + 4 * o:
+                p.grad = self.grad[o:o + p.numel()].view(p.shape)
+
+
+def cosine_warm_restarts_lr(base_lr: float, epoch: int, t_0: int, t_mult: int = 2, eta_min: float = 1e-6) -> float:
+    """``CosineAnnealingWarmRestarts(T_0=warmup_steps, T_mult=2, eta_min=1e-6)`` as a scalar (models.py:66-74)."""
+    t_i, t_cur = t_0, epoch
+    while t_cur >= t_i:
+        t_cur -= t_i
+        t_i *= t_mult
+    return eta_min + (base_lr - eta_min) * (1 + math.cos(math.pi * t_cur / t_i)) / 2
+
+
+class Trainer:
+    """One object per rank.  ``step(batch)`` runs a full training step and returns a device tensor
+    ``[loss, mape]`` (no host sync inside)."""
+
+    def __init__(self, model: torch.nn.Module, lr: float = 1e-3, weight_decay: float = 1e-2, betas=(0.9, 0.999),
+                 eps: float = 1e-5, target: str = "para", huber_delta: float = 0.01,
+                 process_group: Optional[dist.ProcessGroup] = None, distributed: Optional[bool] = None):
+        self.model = model
+        self.flat = FlatParameters(model)
+        self.lr, self.weight_decay, self.betas, self.eps = lr, weight_decay, betas, eps
+        self.target, self.huber_delta = target, huber_delta
+        self.exp_avg = torch.zeros_like(self.flat.data)
+        self.exp_avg_sq = torch.zeros_like(self.flat.data)
+        self.max_exp_avg_sq = torch.zeros_like(self.flat.data)
+        self.step_count = 0
+        self.pg = process_group
+        self.distributed = dist.is_initialized() if distributed is None else distributed
+        self.world = dist.get_world_size(self.pg) if self.distributed else 1
+        if self.distributed:                                  # identical replicas to start from
+            dist.broadcast(self.flat.data, src=0, group=self.pg)
+
+    def forward_backward(self, batch: Batch) -> Tensor:
+        self.flat.zero_grad()
+        pred = self.model.forward_batch(batch)
+        target = getattr(batch, self.target)
+        out2, dpred = ops.relhuber_fwd_bwd(pred.detach().contiguous(), target.contiguous(), self.huber_delta)
+        pred.backward(dpred)
+        return out2
+
+    def optimizer_step(self) -> None:
+        if self.distributed and self.world > 1:
+            dist.all_reduce(self.flat.grad, op=dist.ReduceOp.SUM, group=self.pg)   # the single collective of the step
+        self.step_count += 1
+        ops.adamw_amsgrad_(self.flat.data, self.flat.grad, self.exp_avg, self.exp_avg_sq, self.max_exp_avg_sq,
+                           lr=self.lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
+                           weight_decay=self.weight_decay, step=self.step_count, grad_scale=1.0 / self.world)
+
+    def step(self, batch: Batch) -> Tensor:
+        out2 = self.forward_backward(batch)
+        self.optimizer_step()
+        return out2

@@ -42,6 +42,8 @@ extern "C" {
 
 GNNX_API int gnnx_abi_version(void);
 GNNX_API const char* gnnx_last_error(void);
+/* Total number of CUDA kernels launched by this library in this process (monotonic). */
+GNNX_API int64_t gnnx_launch_count(void);
 
 /* ------------------------------------------------------------------ collator (integer) */
 /* Replaces: PyG Batch.from_data_list + the unordered COO scatter indexing

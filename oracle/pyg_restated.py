@@ -110,6 +110,42 @@ def csr_reference(edge_index: Tensor, num_nodes: int):
 
 
 # --------------------------------------------------------------------------- R3
+# Test hook for the min/max routing discontinuity (SURVEY 8(c) "exact-tie detection"): d max / d x_e jumps between
+# candidates when two messages of a segment are within rounding of each other, so two correct fp32 implementations
+# whose inputs differ in the last bits can route the gradient to different edges.  When EXTREMUM_SELECT is a
+# non-empty list, successive scatter(min|max) calls take WHICH elements receive the gradient from it (teacher
+# forcing the implementation under test) and record in EXTREMUM_BAND_VIOLATIONS every forced element whose own
+# value is further than EXTREMUM_BAND * max|src| from the oracle's own extremum.  Forward values are untouched.
+EXTREMUM_SELECT = None
+EXTREMUM_BAND = 1e-4
+EXTREMUM_BAND_VIOLATIONS = []
+
+
+class _ForcedExtremum(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, index, dim_size, reduce, select):
+        size = [dim_size] + list(src.shape[1:])
+        idx = _broadcast(index, src)
+        out = src.new_zeros(size).scatter_reduce_(0, idx, src, reduce="a" + reduce, include_self=False)
+        select = select.to(src.device).view_as(src)
+        own = src == out.index_select(0, index)
+        differ = select != own
+        if bool(differ.any()):
+            gap = (src - out.index_select(0, index)).abs()[differ & select]
+            scale = float(src.abs().max())
+            worst = float(gap.max()) / scale if gap.numel() else 0.0
+            EXTREMUM_BAND_VIOLATIONS.append((int(differ.sum()), int((gap > EXTREMUM_BAND * scale).sum()), worst))
+        ctx.save_for_backward(index, select)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad):
+        index, select = ctx.saved_tensors
+        sel = select.to(grad.dtype)
+        cnt = torch.zeros_like(grad).scatter_add_(0, _broadcast(index, sel), sel).clamp(min=1)
+        return sel * (grad / cnt).index_select(0, index), None, None, None, None
+
+
 def _broadcast(index: Tensor, ref: Tensor) -> Tensor:
     size = [-1] + [1] * (ref.dim() - 1)
     return index.view(size).expand_as(ref)
@@ -130,6 +166,8 @@ def scatter(src: Tensor, index: Tensor, dim_size: int, reduce: str) -> Tensor:
         out = src.new_zeros(size).scatter_add_(0, _broadcast(index, src), src)
         return out / count.view([-1] + [1] * (src.dim() - 1))
     if reduce in ("min", "max"):
+        if EXTREMUM_SELECT:
+            return _ForcedExtremum.apply(src, index, dim_size, reduce, EXTREMUM_SELECT.pop(0))
         return src.new_zeros(size).scatter_reduce_(
             0, _broadcast(index, src), src, reduce="a" + reduce, include_self=False)
     raise ValueError(reduce)
@@ -177,11 +215,30 @@ def var_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
     return mean_2 - mean * mean
 
 
+# Test hook for the Std discontinuity (SURVEY 8(c) "exclusion band"): StdAggregation jumps from 0 to sqrt(1e-5) at
+# var = 1e-5, and fp32 evaluates var = E[x^2] - E[x]^2 with an absolute error of ~1e-9, so two correct fp32
+# implementations whose inputs differ in the last bit can land on different sides of the threshold.  When
+# STD_MASKS is a list, successive std_aggregation calls take their zero-mask from it (teacher forcing the branch
+# the implementation under test took) and record in STD_BAND_VIOLATIONS every forced entry whose own var is NOT
+# within the relative band STD_BAND of the threshold -- those would be genuine disagreements, not rounding.
+STD_MASKS = None
+STD_BAND = 2e-3
+STD_BAND_VIOLATIONS = []
+
+
 def std_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
     """R4 -- ``StdAggregation``: clamp(1e-5).sqrt() then zero-fill at/below sqrt(1e-5)."""
     var = var_aggregation(x, index, dim_size)
     out = var.clamp(min=1e-5).sqrt()
-    return out.masked_fill(out <= math.sqrt(1e-5), 0.0)
+    own_mask = out <= math.sqrt(1e-5)
+    if STD_MASKS is None:
+        return out.masked_fill(own_mask, 0.0)
+    forced = STD_MASKS.pop(0).to(own_mask.device).view_as(own_mask)
+    differ = forced != own_mask
+    if bool(differ.any()):
+        rel = (var.detach()[differ].double() - 1e-5).abs() / 1e-5
+        STD_BAND_VIOLATIONS.append((int(differ.sum()), int((rel > STD_BAND).sum()), float(rel.max())))
+    return var.clamp(min=1e-12).sqrt().masked_fill(forced, 0.0)
 
 
 _AGGRS = {

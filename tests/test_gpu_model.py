@@ -1,7 +1,11 @@
 """Conv-layer and whole-model parity (forward + every gradient) against the CPU oracle.
 
-Tolerance: rel 1e-5 / atol 1e-6 per element for single layers; whole models (3 conv layers + BN + head,
-fp32 rounding compounds through ~25 dependent GEMMs) are held to rel 1e-4 on gradients, 1e-5 on outputs.
+Tolerance: single layers -- outputs rel 1e-5 / atol 1e-6 (normwise floor, see tests/util.py), gradients rel 1e-4
+elementwise AND "as accurate as the fp32 oracle is against its own fp64 run" (factor 4).  Whole models (3 conv
+layers + BN + head: fp32 rounding compounds through ~25 dependent GEMMs) use the same two bounds.  StdAggregation
+is discontinuous at var = 1e-5 (jump 0 -> 3.2e-3); entries within fp32 rounding of that threshold are
+teacher-forced to the CUDA path's branch and the test asserts every such entry really is inside the band
+(tests/util.py:branches_from) -- SURVEY 8(c)'s "exclusion band", applied without dropping any entry.
 """
 import copy
 
@@ -9,9 +13,9 @@ import pytest
 import torch
 
 import gnnepcsaft_b200 as G
-from gnnepcsaft_b200 import graph, nn as gnn, ops
+from gnnepcsaft_b200 import graph, nn as gnn, ops, pna_fn
 from oracle import pyg_restated as O
-from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_close, deg_hist, make_batch
+from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_as_accurate, assert_close, deg_hist, make_batch, branches_from
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -26,31 +30,54 @@ def _precision():
     torch.manual_seed(0)
 
 
-def _grads_close(mp, mo, rtol, atol):
-    po = dict(mo.named_parameters())
+def _ref_err(r32, r64):
+    return float((r32.detach().double() - r64.detach()).abs().max()) if r32.numel() else 0.0
+
+
+def _grads_close(mp, mo, mo64, rtol):
+    """Every parameter gradient: as accurate as the fp32 oracle is against its own fp64 run (normwise, factor 4), and
+    elementwise within rtol of the fp32 oracle with an absolute floor of max(1e-5 * global gradient scale, 4 x the
+    fp32 oracle's own error) -- biases that feed a BatchNorm have a true-zero gradient and are judged on that floor."""
+    po, po64 = dict(mo.named_parameters()), dict(mo64.named_parameters())
+    gmax = max(float(p.grad.abs().max()) for p in mo64.parameters())
     for n, p in mp.named_parameters():
         assert p.grad is not None, f"no grad for {n}"
-        assert_close(p.grad, po[n].grad, rtol, atol, f"d{n}")
+        assert_as_accurate(p.grad, po[n].grad, po64[n].grad, f"d{n}", min_scale=1e-2 * gmax)
+        assert_close(p.grad, po[n].grad, rtol, max(1e-5 * gmax, 4 * _ref_err(po[n].grad, po64[n].grad)), f"d{n}")
 
 
 def _conv_pair(make_o, make_p, b, H, seed=0):
     torch.manual_seed(seed)
     co = make_o()
+    co64 = copy.deepcopy(co).double()
     cp = make_p().to(DEV)
     cp.load_state_dict(co.state_dict())
     N, E = b["x"].shape[0], b["edge_index"].shape[1]
     x, ea = torch.randn(N, H), torch.randn(E, H)
     xo, eo = x.clone().requires_grad_(True), ea.clone().requires_grad_(True)
+    x64, e64 = x.double().requires_grad_(True), ea.double().requires_grad_(True)
     xp, ep = x.clone().to(DEV).requires_grad_(True), ea.clone().to(DEV).requires_grad_(True)
-    yo = co(xo, b["edge_index"], eo)
-    yp = cp(xp, b["edge_index"].to(DEV), ep)
+    pna_fn.CAPTURE_AGG = []
+    try:
+        yp = cp(xp, b["edge_index"].to(DEV), ep)
+        aggs = list(pna_fn.CAPTURE_AGG)
+    finally:
+        pna_fn.CAPTURE_AGG = None
+    towers = getattr(cp, "towers", 1)
+    with branches_from(aggs, towers):
+        yo = co(xo, b["edge_index"], eo)
+    with branches_from(aggs, towers):
+        y64 = co64(x64, b["edge_index"], e64)
+    assert_as_accurate(yp, yo, y64, "conv fwd")
     assert_close(yp, yo, 1e-5, 1e-6, "conv fwd")
     w = torch.randn_like(yo)
     (yo * w).sum().backward()
+    (y64 * w.double()).sum().backward()
     (yp * w.to(DEV)).sum().backward()
-    assert_close(xp.grad, xo.grad, 1e-5, 1e-6, "dx")
-    assert_close(ep.grad, eo.grad, 1e-5, 1e-6, "dedge_attr")
-    _grads_close(cp, co, 1e-5, 1e-6)
+    for got, r32, r64, what in ((xp.grad, xo.grad, x64.grad, "dx"), (ep.grad, eo.grad, e64.grad, "dedge_attr")):
+        assert_as_accurate(got, r32, r64, what)
+        assert_close(got, r32, 1e-4, max(1e-6, 4 * _ref_err(r32, r64)), what)
+    _grads_close(cp, co, co64, 1e-4)
 
 
 @pytest.mark.parametrize("H,T,pre,post", [(64, 1, 2, 4), (64, 4, 1, 1), (128, 8, 3, 2), (256, 1, 2, 4), (48, 2, 4, 3)])
@@ -86,19 +113,33 @@ def _model_pair(cfg, graphs):
                                         (dict(PNA_CFG1, towers=4, pre_layers=1, post_layers=2, global_pool="mean"), "para"),
                                         (dict(GAT_CFG_SMALL, heads=8, global_pool="max"), "assoc")])
 def test_whole_model_training_step_parity(cfg, target):
-    """BASELINE cfg1: fwd + loss + bwd on 32 synthetic ~25-atom graphs, every parameter gradient checked."""
+    """BASELINE cfg1: fwd + loss + bwd on 32 synthetic ~25-atom graphs, every parameter gradient checked.
+
+    Bar: the CUDA path must sit as close to the fp64 oracle as the fp32 oracle does (factor 4, normwise), and
+    within rel 1e-4 (normwise floor 0.1) of the fp32 oracle elementwise; the loss within rel 1e-5."""
     graphs, b = make_batch(32, seed=1234)
     mo, mp = _model_pair(cfg, graphs)
-    mo.train(); mp.train()
-    po = mo(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
-    pp = mp(b["x"].to(DEV), b["edge_index"].to(DEV), b["edge_attr"].to(DEV), b["batch"].to(DEV))
-    assert_close(pp, po, 1e-5, 1e-6, "model fwd")
+    mo64 = copy.deepcopy(mo).double()
+    mo.train(); mp.train(); mo64.train()
+    pna_fn.CAPTURE_AGG = []
+    try:
+        pp = mp(b["x"].to(DEV), b["edge_index"].to(DEV), b["edge_attr"].to(DEV), b["batch"].to(DEV))
+        aggs = list(pna_fn.CAPTURE_AGG)
+    finally:
+        pna_fn.CAPTURE_AGG = None
+    with branches_from(aggs, cfg["towers"]):
+        po = mo(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
+    with branches_from(aggs, cfg["towers"]):
+        p64 = mo64(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
+    assert_as_accurate(pp, po, p64, "model fwd")
+    assert_close(pp, po, 1e-4, 1e-6, "model fwd")
     lo, _ = O.training_loss(po, b[target])
-    lo.backward()
+    l64, _ = O.training_loss(p64, b[target].double())
+    lo.backward(); l64.backward()
     out2, dpred = ops.relhuber_fwd_bwd(pp.detach().contiguous(), b[target].to(DEV))
     assert_close(out2[0], lo, 1e-5, 1e-9, "loss")
     pp.backward(dpred)
-    _grads_close(mp, mo, 1e-4, 1e-7)
+    _grads_close(mp, mo, mo64, 1e-4)
     sp = mp.state_dict()
     for n, bo in mo.state_dict().items():
         if "running_" in n:
