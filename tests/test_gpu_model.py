@@ -143,7 +143,7 @@ def test_whole_model_training_step_parity(cfg, target):
     sp = mp.state_dict()
     for n, bo in mo.state_dict().items():
         if "running_" in n:
-            assert_close(sp[n], bo, 1e-5, 1e-6, f"buffer {n}")
+            assert_close(sp[n], bo, 1e-4, 1e-6, f"buffer {n}")
 
 
 def test_eval_pred_with_bounds_and_single_graph_path():
