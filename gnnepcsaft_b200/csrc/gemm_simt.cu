@@ -120,6 +120,16 @@ __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, i
     }
 }
 
+// Ordered (deterministic) sum of `splits` partial [M,N] products + bias / accumulate / ReLU; shared with gemm_tc.cu.
+int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
+                         int flags, cudaStream_t st) {
+    long long total = (long long)M * N;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    k_splitk_reduce<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, ldc, bias, flags);
+    return check_launch("splitk_reduce");
+}
+
 int simt_splits(int64_t M, int64_t N, int64_t K) {
     long long tiles = (long long)ceil_div(M, BM) * ceil_div(N, BN);
     if (tiles >= kNumSMs || K < 1024) return 1;

@@ -1,16 +1,422 @@
-// tcgen05 + TMEM GEMM for the dense transforms (placeholder until the kernel lands: reports
-// "not supported" so every shape runs on the fp32 kernel).
+// tcgen05 + TMEM + TMA GEMMs (kind::tf32, fp32 in HBM, fp32 accumulate) for the dense transforms of the
+// hot path: the Linear layers inside PNAConv / GATv2Conv / the MLP head and their dX / dW products.
+//
+// Two kernels, both warp-specialised (warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
+// epilogue, one per TMEM lane quadrant), fed by 128-byte-swizzled TMA boxes straight from the fp32
+// tensors (no conversion pass: the tensor map's TFLOAT32 type rounds on load) through a 3-stage mbarrier ring:
+//
+//   k_gemm_tf32_rows   C[M,N] = A[M,K] * op(B)      A K-major.  op(B) = B^T with B [N,K] (Linear forward,
+//                      K-major) or B [K,N] (dX = dY W, MN-major B descriptor).  One CTA owns 256 rows
+//                      (two 128x256 accumulators = all 512 TMEM columns) so every B stage is used twice and
+//                      A is read exactly once; persistent over row blocks, N tiles innermost (A stays in L2).
+//   k_gemm_tf32_red    C[Mo,No] = A[R,Mo]^T * B[R,No]  (dW = dY^T X): both operands MN-major, the reduction
+//                      runs over the R rows; grid = output tiles x row splits, partials reduced by a
+//                      deterministic second pass (no atomics).
+//
+// At the hot path's shapes (K = 256..1024, N = 256..768, M = 1e5..2e5 rows of fp32) these products are
+// HBM/L2-bound, not tensor-bound: see DESIGN.md for the roofline of each.
+#include <cudaTypedefs.h>
+
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace gnnx {
 
-bool tc_supported(int64_t, int64_t, int64_t, int, int, int64_t, int64_t, int64_t, const void*, const void*, const void*, int) {
-    return false;
+int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
+                         int flags, cudaStream_t st);
+
+namespace tc {
+
+constexpr int kStages = 3;
+constexpr int kThreads = 192;
+constexpr int kBK = 32;                         // fp32 per k-block = one 128-byte swizzle row
+constexpr int kAStage = 256 * 128;              // 32 KB: 256 rows x 128 B (rows kernel) / 8 chunks x 32 k x 128 B (red kernel)
+constexpr int kBStage = 256 * 128;              // 32 KB
+constexpr int kStageBytes = kAStage + kBStage;  // 64 KB
+constexpr int kEpiPitch = 36;                   // floats; 144-byte rows keep float4 staging conflict-free
+constexpr int kEpiBytes = 4 * 32 * kEpiPitch * 4;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + 128;
+constexpr int kTmemCols = 512;
+
+struct Smem {
+    uint8_t* base;      // 1024-aligned
+    __device__ uint32_t a(int s) const { return smem_u32(base + s * kStageBytes); }
+    __device__ uint32_t b(int s) const { return smem_u32(base + s * kStageBytes + kAStage); }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages * kStageBytes) + q * 32 * kEpiPitch; }
+    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStages * kStageBytes + kEpiBytes); }
+    __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }
+    __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStages + s); }
+    __device__ uint32_t tmem_full() const { return smem_u32(bars() + 2 * kStages); }
+    __device__ uint32_t tmem_empty() const { return smem_u32(bars() + 2 * kStages + 1); }
+    __device__ uint32_t* tmem_ptr() const { return reinterpret_cast<uint32_t*>(bars() + 2 * kStages + 2); }
+};
+
+__device__ __forceinline__ Smem carve_smem(uint8_t* raw) {
+    Smem s;
+    s.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023));
+    return s;
 }
-size_t tc_workspace_bytes(int64_t, int64_t, int64_t, int, int, int) { return 0; }
-int gemm_tc(const float*, int64_t, int, const float*, int64_t, int, float*, int64_t, int64_t, int64_t, int64_t, const float*,
-            int, int, void*, size_t, cudaStream_t) {
-    return set_error(GNNX_ERR_UNSUPPORTED, "gemm_tc: tensor-core path not built");
+
+// Common prologue: barriers, TMEM allocation (all 512 columns: one CTA per SM by shared-memory footprint).
+__device__ __forceinline__ uint32_t prologue(const Smem& sm, int warp) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(sm.full(s), 1);
+            mbar_init(sm.empty(s), 1);
+        }
+        mbar_init(sm.tmem_full(), 1);
+        mbar_init(sm.tmem_empty(), 4);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(sm.tmem_ptr()), kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    return *sm.tmem_ptr();
+}
+
+// Epilogue of one 128-row accumulator: TMEM -> registers -> per-warp smem transpose -> coalesced float4 rows.
+// Thread t of quadrant q holds accumulator row q*32+t; after the transpose 8 lanes cover one 128-byte row segment.
+__device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, int q, int lane, float* __restrict__ C,
+                                            long long ldc, long long row0, long long row_end, int col0, int col_end,
+                                            int ncols, const float* __restrict__ bias, int flags) {
+    float* st = sm.epi(q);
+    for (int c = 0; c < ncols; c += 32) {
+        float v[32];
+        tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(st + lane * kEpiPitch + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        const int cc = (lane & 7) * 4;
+        const int gcol = col0 + c + cc;
+        if (gcol < col_end) {
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bias) bv = __ldg(reinterpret_cast<const float4*>(bias + gcol));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + (lane >> 3);
+                const long long grow = row0 + q * 32 + r;
+                if (grow < row_end) {
+                    float4 o = *reinterpret_cast<const float4*>(st + r * kEpiPitch + cc);
+                    o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                    float* dst = C + grow * ldc + gcol;
+                    if (flags & GNNX_GEMM_ACCUMULATE) {
+                        float4 p = *reinterpret_cast<const float4*>(dst);
+                        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+                    }
+                    if (flags & GNNX_GEMM_RELU) {
+                        o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+                    }
+                    *reinterpret_cast<float4*>(dst) = o;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------ C[M,N] = A[M,K] * op(B)
+template <bool kBMN>
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
+                 long long ldc, int M, int N, int K, int BN, const float* __restrict__ bias, int flags) {
+    extern __shared__ uint8_t smem_raw[];
+    const Smem sm = carve_smem(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t tmem_base = prologue(sm, warp);
+
+    const int n_tiles = (N + BN - 1) / BN;
+    const int m_tiles = (M + 255) / 256;
+    const int tiles = n_tiles * m_tiles;
+    const int KB = (K + kBK - 1) / kBK;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = kAStage + (uint32_t)BN * 128u;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.empty(stage), phase ^ 1);
+                    mbar_expect_tx(sm.full(stage), tx);
+                    tma_load_2d(sm.a(stage), &tmA, sm.full(stage), kb * kBK, m0);
+                    if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK, n0 / 32);
+                    else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, BN, 0, kBMN ? 1 : 0);
+            int stage = 0;
+            uint32_t phase = 0, tphase = 0;
+            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+                const int m0 = (t / n_tiles) * 256;
+                const int halves = (m0 + 128 < M) ? 2 : 1;
+                mbar_wait(sm.tmem_empty(), tphase ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.full(stage), phase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < kBK / 8; ++k) {
+                        const uint64_t bdesc = kBMN ? make_smem_desc(sm.b(stage) + k * 1024, 32 * 128, 512, kLayoutSw128B32)
+                                                    : make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        for (int h = 0; h < halves; ++h) {
+                            const uint64_t adesc = make_smem_desc(sm.a(stage) + h * (128 * 128) + k * 32, 16, 1024, kLayoutSw128);
+                            mma_tf32(tmem_base + h * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+                        }
+                    }
+                    mma_commit(sm.empty(stage));
+                    if (kb == KB - 1) mma_commit(sm.tmem_full());
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                tphase ^= 1;
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t tphase = 0;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
+            const int halves = (m0 + 128 < M) ? 2 : 1;
+            mbar_wait(sm.tmem_full(), tphase);
+            tc_fence_after();
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
+            for (int h = 0; h < halves; ++h)
+                epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sm.tmem_empty());
+            tphase ^= 1;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------ partial[z][Mo,No] = A[rows_z, Mo]^T * B[rows_z, No]
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ partial,
+                int Mo, int No, int R, int rows_per_split, int BM, int BN) {
+    extern __shared__ uint8_t smem_raw[];
+    const Smem sm = carve_smem(smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t tmem_base = prologue(sm, warp);
+
+    const int n_tiles = (No + BN - 1) / BN;
+    const int m0 = (blockIdx.x / n_tiles) * BM, n0 = (blockIdx.x % n_tiles) * BN;
+    const int r_begin = blockIdx.y * rows_per_split;
+    const int r_end = min(R, r_begin + rows_per_split);
+    const int RB = (r_end - r_begin + kBK - 1) / kBK;
+    const int halves = BM / 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = (uint32_t)(BM + BN) * 128u;
+            for (int rb = 0; rb < RB; ++rb) {
+                mbar_wait(sm.empty(stage), phase ^ 1);
+                mbar_expect_tx(sm.full(stage), tx);
+                tma_load_3d(sm.a(stage), &tmA, sm.full(stage), 0, r_begin + rb * kBK, m0 / 32);
+                tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, r_begin + rb * kBK, n0 / 32);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && RB > 0) {
+            const uint32_t idesc = make_idesc_tf32(128, BN, 1, 1);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int rb = 0; rb < RB; ++rb) {
+                mbar_wait(sm.full(stage), phase);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < kBK / 8; ++k) {
+                    const uint64_t bdesc = make_smem_desc(sm.b(stage) + k * 1024, 32 * 128, 512, kLayoutSw128B32);
+                    for (int h = 0; h < halves; ++h) {
+                        const uint64_t adesc = make_smem_desc(sm.a(stage) + h * (4 * 32 * 128) + k * 1024, 32 * 128, 512, kLayoutSw128B32);
+                        mma_tf32(tmem_base + h * 256, adesc, bdesc, idesc, (rb | k) ? 1u : 0u);
+                    }
+                }
+                mma_commit(sm.empty(stage));
+                if (rb == RB - 1) mma_commit(sm.tmem_full());
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        float* out = partial + (long long)blockIdx.y * Mo * No;
+        if (RB > 0) {
+            mbar_wait(sm.tmem_full(), 0);
+            tc_fence_after();
+            const int ncols = min(BN, No - n0);
+            for (int h = 0; h < halves; ++h)
+                epilogue_acc(sm, tmem_base + h * 256, q, lane, out, No, (long long)m0 + h * 128, Mo, n0, No, ncols, nullptr, 0);
+        } else {                                   // empty row range: this split contributes zeros
+            for (int h = 0; h < halves; ++h)
+                for (int r = q * 32 + lane; r < 128; r += 128) {
+                    const int grow = m0 + h * 128 + r;
+                    if (grow < Mo)
+                        for (int c = n0; c < min(No, n0 + BN); ++c) out[(long long)grow * No + c] = 0.f;
+                }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    }
+    return fn;
+}
+
+static CUtensorMapDataType tma_dtype() {
+    static int f32 = -1;
+    if (f32 < 0) {
+        const char* e = getenv("GNNX_TMA_F32");      // diagnostic: raw fp32 bits (MMA truncates) instead of round-to-tf32
+        f32 = (e && e[0] == '1') ? 1 : 0;
+    }
+    return f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32;
+}
+
+// K-major view of a row-major [rows, cols] fp32 matrix: box = 32 floats x box_rows rows.
+static int make_map_kmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = encode_fn()(m, tma_dtype(), 2, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (K-major) failed: %d", (int)r);
+}
+// MN-major view of a row-major [rows, cols] fp32 matrix (cols % 32 == 0): dims (32, rows, cols/32) so that one
+// box lands as [chunk][k row][32 floats] = the canonical MN-major operand layout of tf32 (128B swizzle, 32B atoms).
+static int make_map_mnmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_chunks) {
+    cuuint64_t dims[3] = {32, (cuuint64_t)rows, (cuuint64_t)(cols / 32)};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 4, 128};
+    cuuint32_t box[3] = {32, 32, (cuuint32_t)box_chunks};
+    cuuint32_t es[3] = {1, 1, 1};
+    CUresult r = encode_fn()(m, tma_dtype(), 3, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (MN-major) failed: %d", (int)r);
+}
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+struct RedPlan {
+    int BM, BN, tiles, splits, rows_per_split;
+};
+static RedPlan red_plan(int64_t Mo, int64_t No, int64_t R) {
+    RedPlan p;
+    p.BM = Mo > 128 ? 256 : 128;
+    p.BN = (int)(No < 256 ? No : 256);
+    p.tiles = ceil_div(Mo, p.BM) * ceil_div(No, p.BN);
+    int want = kNumSMs / p.tiles;
+    if (want < 1) want = 1;
+    int64_t max_splits = (R + 255) / 256;                 // at least 256 rows per split
+    if (max_splits < 1) max_splits = 1;
+    int splits = (int)(want < max_splits ? want : max_splits);
+    int rps = ceil_div(ceil_div(R, splits), kBK) * kBK;
+    if (rps < kBK) rps = kBK;
+    p.rows_per_split = rps;
+    p.splits = R > 0 ? ceil_div(R, rps) : 1;
+    return p;
+}
+
+}  // namespace tc
+
+using namespace tc;
+
+bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
+                  const void* B, const void* C, int precision) {
+    (void)precision;
+    if (!encode_fn()) return false;
+    if (!aligned16(A) || !aligned16(B) || !aligned16(C)) return false;
+    if ((lda & 3) || (ldb & 3) || (ldc & 3)) return false;
+    if (M > 0x7fffffff || N > 0x7fffffff || K > 0x7fffffff) return false;
+    if (!ta) {
+        if (M < 64 || N < 16 || K < 8 || (N & 3)) return false;
+        if (tb) return true;                               // C = A B^T, both K-major
+        return (N % 32) == 0;                              // C = A B, B [K,N] as an MN-major operand
+    }
+    if (tb) return false;                                  // A^T B^T: not on the hot path
+    return M >= 32 && N >= 32 && (M % 32) == 0 && (N % 32) == 0 && K >= 256;
+}
+
+size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision) {
+    (void)precision;
+    if (ta && !tb) {
+        RedPlan p = red_plan(M, N, K);
+        return (size_t)p.splits * M * N * sizeof(float);
+    }
+    return 0;
+}
+
+int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
+            int64_t N, int64_t K, const float* bias, int flags, int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
+    (void)precision;
+    static bool attr_done = false;
+    if (!attr_done) {
+        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_done = true;
+    }
+    CUtensorMap mA, mB;
+    if (!ta) {
+        int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
+        if (make_map_kmajor(&mA, A, M, K, lda, 256)) return GNNX_ERR_INVALID;
+        if (tb) {
+            if (make_map_kmajor(&mB, B, N, K, ldb, BN)) return GNNX_ERR_INVALID;
+        } else {
+            if (make_map_mnmajor(&mB, B, K, N, ldb, BN / 32)) return GNNX_ERR_INVALID;
+        }
+        int tiles = ceil_div(M, 256) * ceil_div(N, BN);
+        int grid = tiles < kNumSMs ? tiles : kNumSMs;
+        if (tb)
+            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags);
+        else
+            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags);
+        return check_launch("gemm_tf32_rows");
+    }
+    // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
+    RedPlan p = red_plan(M, N, K);
+    GNNX_REQUIRE(ws && ws_bytes >= (size_t)p.splits * M * N * sizeof(float), "gemm_tc: workspace too small for the row-split partials");
+    if (make_map_mnmajor(&mA, A, K, M, lda, p.BM / 32)) return GNNX_ERR_INVALID;
+    if (make_map_mnmajor(&mB, B, K, N, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
+    k_gemm_tf32_red<<<dim3(p.tiles, p.splits), kThreads, kSmemBytes, st>>>(mA, mB, (float*)ws, (int)M, (int)N, (int)K,
+                                                                          p.rows_per_split, p.BM, p.BN);
+    int rc = check_launch("gemm_tf32_red");
+    if (rc) return rc;
+    return splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, st);
 }
 
 }  // namespace gnnx

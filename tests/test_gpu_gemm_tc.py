@@ -1,0 +1,105 @@
+"""tcgen05 (kind::tf32) GEMM kernels against an fp64 product of the same operands.
+
+Tolerance (stated separately from the fp32 tier, north_star): operands are rounded to tf32 (10-bit mantissa,
+unit roundoff 2^-11) and accumulated in fp32, so |C - C64| <= ~2 * 2^-11 * (|A| |B|) elementwise; the test
+bounds the error by 3 * 2^-11 * (|A| @ |B|).  The layouts under test are the three the hot path uses:
+A K-major x B K-major (Linear forward), A K-major x B MN-major (dX = dY W) and both MN-major (dW = dY^T X).
+"""
+import pytest
+import torch
+
+from gnnepcsaft_b200 import ops
+from gnnepcsaft_b200._lib import lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+U_TF32 = 2.0 ** -11
+
+
+def _check(out, a64, b64, extra64=None, relu=False, what=""):
+    ref = a64 @ b64
+    if extra64 is not None:
+        ref = ref + extra64
+    bound = 3 * U_TF32 * (a64.abs() @ b64.abs()) + 1e-6
+    if relu:
+        ref = ref.clamp(min=0)
+    err = (out.double().cpu() - ref).abs()
+    assert bool(torch.isfinite(out).all()), f"{what}: non-finite"
+    worst = float((err / bound).max())
+    assert worst <= 1.0, f"{what}: error/bound = {worst:.3g} (max abs err {float(err.max()):.3g})"
+    # and it must really be a tf32-class result, not garbage that happens to be small: relative Frobenius error
+    rel = float(err.norm() / ref.norm().clamp(min=1e-30))
+    assert rel < 2e-3, f"{what}: relative Frobenius error {rel:.3g}"
+
+
+@pytest.fixture(autouse=True)
+def _prec():
+    ops.set_matmul_precision("tf32")
+    torch.manual_seed(0)
+    yield
+    ops.set_matmul_precision("fp32")
+
+
+def _tc_taken(fn):
+    """Run fn and assert it launched kernels (the tensor-core path counts 1 launch for rows, 2 for the reduction)."""
+    n0 = lib().launch_count()
+    out = fn()
+    assert lib().launch_count() > n0
+    return out
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 256), (300, 256, 256), (1000, 768, 1024), (4096, 128, 256), (257, 64, 96),
+                                   (5000, 48, 40), (100000, 256, 256), (777, 320, 72)])
+def test_linear_forward_layout(M, N, K):
+    a, w, bias = torch.randn(M, K), torch.randn(N, K), torch.randn(N)
+    out = _tc_taken(lambda: ops.gemm(a.to(DEV), w.to(DEV), trans_b=True, bias=bias.to(DEV)))
+    _check(out, a.double(), w.double().t(), bias.double(), what=f"NT {M}x{N}x{K}")
+    out = ops.gemm(a.to(DEV), w.to(DEV), trans_b=True, bias=bias.to(DEV), relu=True)
+    _check(out, a.double(), w.double().t(), bias.double(), relu=True, what=f"NT+relu {M}x{N}x{K}")
+
+
+def test_forward_strided_views_and_accumulate():
+    M = 3000
+    x = torch.randn(M, 1024)
+    w = torch.randn(256, 1300)
+    out = torch.randn(M, 768)
+    ref_prev = out[:, 256:512].double().clone()
+    xd, wd, od = x.to(DEV), w.to(DEV), out.to(DEV)
+    ops.gemm(xd[:, 256:768], wd[:, 260:772], trans_b=True, out=od[:, 256:512], accumulate=True)
+    _check(od[:, 256:512], x[:, 256:768].double(), w[:, 260:772].double().t(), ref_prev, what="strided accumulate")
+    assert torch.equal(od[:, :256].cpu(), out[:, :256]) and torch.equal(od[:, 512:].cpu(), out[:, 512:])
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 256, 256), (3000, 1024, 768), (4096, 64, 128), (100000, 256, 256), (513, 96, 200)])
+def test_dx_layout(M, N, K):
+    dy, w = torch.randn(M, K), torch.randn(K, N)          # dX = dY @ W, W is [out=K, in=N] row-major
+    out = _tc_taken(lambda: ops.gemm(dy.to(DEV), w.to(DEV)))
+    _check(out, dy.double(), w.double(), what=f"NN {M}x{N}x{K}")
+
+
+@pytest.mark.parametrize("Mo,No,R", [(256, 256, 5000), (768, 1024, 3001), (128, 256, 4096), (256, 128, 100000), (64, 96, 777),
+                                     (384, 288, 2000)])
+def test_dw_layout(Mo, No, R):
+    dy, x = torch.randn(R, Mo), torch.randn(R, No)
+    out = _tc_taken(lambda: ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True))
+    _check(out, dy.double().t(), x.double(), what=f"TN {Mo}x{No}x{R}")
+    again = ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True)
+    assert torch.equal(out, again), "dW must be deterministic (ordered split reduction, no atomics)"
+
+
+def test_dw_strided_accumulate():
+    R = 20000
+    dy, x = torch.randn(R, 768), torch.randn(R, 1024)
+    dw = torch.randn(256, 1300)
+    prev = dw[:, 100:356].double().clone()
+    dwd = dw.to(DEV)
+    ops.gemm(dy.to(DEV)[:, 256:512], x.to(DEV)[:, 512:768], trans_a=True, out=dwd[:, 100:356], accumulate=True)
+    _check(dwd[:, 100:356], dy[:, 256:512].double().t(), x[:, 512:768].double(), prev, what="dW strided accumulate")
+    assert torch.equal(dwd[:, :100].cpu(), dw[:, :100]) and torch.equal(dwd[:, 356:].cpu(), dw[:, 356:])
+
+
+def test_small_or_unaligned_shapes_fall_back_to_fp32_kernel():
+    a, w = torch.randn(60, 13), torch.randn(64, 13)        # the 60-row bond table product: SIMT path, fp32-exact class
+    out = ops.gemm(a.to(DEV), w.to(DEV), trans_b=True)
+    ref = a.double() @ w.double().t()
+    assert float((out.double().cpu() - ref).abs().max()) < 1e-4
