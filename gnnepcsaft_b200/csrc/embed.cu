@@ -13,14 +13,18 @@ __global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, co
     int wpb = blockDim.x >> 5;
     for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += gridDim.x * wpb) {
         int my = lane < K ? offsets[lane] + (int)idx[(long long)r * K + lane] : 0;
-        for (int c = lane * 4; c < H; c += 128) {
+        for (int c0 = 0; c0 < H; c0 += 128) {          // warp-uniform trip count: every lane takes part in the shuffles
+            const int c = c0 + lane * 4;
+            const bool active = c < H;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int k = 0; k < K; ++k) {
                 int tr = __shfl_sync(0xffffffffu, my, k);
-                float4 v = ldg4(table + (long long)tr * H + c);
-                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+                if (active) {
+                    float4 v = ldg4(table + (long long)tr * H + c);
+                    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+                }
             }
-            stg4(out + (long long)r * H + c, acc);
+            if (active) stg4(out + (long long)r * H + c, acc);
         }
     }
 }

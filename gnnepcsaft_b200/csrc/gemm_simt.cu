@@ -13,7 +13,8 @@ template <bool TA, bool TB>
 __global__ void __launch_bounds__(256, 2)
 k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__ B, long long ldb,
            float* __restrict__ C, long long ldc, int M, int N, int K, int k_per_split,
-           const float* __restrict__ bias, int flags, float* __restrict__ partial) {
+           const float* __restrict__ bias, int flags, float* __restrict__ partial,
+           const float* __restrict__ mask, long long ldm) {
     __shared__ float As[2][BK][BM + 4];
     __shared__ float Bs[2][BK][BN + 4];
     const int tid = threadIdx.x;
@@ -99,6 +100,7 @@ k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__
             } else {
                 if (bias) v += bias[gn];
                 if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)gm * ldc + gn];
+                if (mask && !(mask[(long long)gm * ldm + gn] > 0.f)) v = 0.f;
                 if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
                 C[(long long)gm * ldc + gn] = v;
             }
@@ -107,14 +109,24 @@ k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__
 }
 
 __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ C,
-                                long long ldc, const float* __restrict__ bias, int flags) {
+                                long long ldc, const float* __restrict__ bias, int flags, const float* __restrict__ mask,
+                                long long ldm) {
     long long total = (long long)M * N;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int m = (int)(i / N), n = (int)(i % N);
         float v = 0.f;
-        for (int s = 0; s < splits; ++s) v += partial[(long long)s * total + i];
+        int s = 0;
+        for (; s + 8 <= splits; s += 8) {          // 8 independent loads in flight, summed in split order
+            float t[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[j] = __ldcs(partial + (long long)(s + j) * total + i);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v += t[j];
+        }
+        for (; s < splits; ++s) v += __ldcs(partial + (long long)s * total + i);
         if (bias) v += bias[n];
         if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)m * ldc + n];
+        if (mask && !(mask[(long long)m * ldm + n] > 0.f)) v = 0.f;
         if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
         C[(long long)m * ldc + n] = v;
     }
@@ -122,11 +134,11 @@ __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, i
 
 // Ordered (deterministic) sum of `splits` partial [M,N] products + bias / accumulate / ReLU; shared with gemm_tc.cu.
 int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
-                         int flags, cudaStream_t st) {
+                         int flags, const float* mask, long long ldm, cudaStream_t st) {
     long long total = (long long)M * N;
     int blocks = (int)((total + 255) / 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    k_splitk_reduce<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, ldc, bias, flags);
+    k_splitk_reduce<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, ldc, bias, flags, mask, ldm);
     return check_launch("splitk_reduce");
 }
 
@@ -146,8 +158,8 @@ size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K) {
 }
 
 int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc,
-              int64_t M, int64_t N, int64_t K, const float* bias, int flags, void* ws, size_t ws_bytes,
-              cudaStream_t st) {
+              int64_t M, int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, void* ws,
+              size_t ws_bytes, cudaStream_t st) {
     if (M == 0 || N == 0) return GNNX_OK;
     int splits = simt_splits(M, N, K);
     float* partial = nullptr;
@@ -162,14 +174,14 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
     GNNX_REQUIRE(grid.y <= 65535 * 1 || true, "gemm: M too large");
     if (grid.y > 65535) return set_error(GNNX_ERR_UNSUPPORTED, "gemm_simt: M=%lld exceeds grid.y limit", (long long)M);
-#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial)
+#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial, mask, ldm)
     if (ta && tb) LAUNCH(true, true);
     else if (ta) LAUNCH(true, false);
     else if (tb) LAUNCH(false, true);
     else LAUNCH(false, false);
 #undef LAUNCH
     if (partial)
-        k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags);
+        k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
     return check_launch("gemm_simt", partial ? 2 : 1);
 }
 

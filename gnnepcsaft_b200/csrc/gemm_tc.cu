@@ -23,7 +23,7 @@
 namespace gnnx {
 
 int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
-                         int flags, cudaStream_t st);
+                         int flags, const float* mask, long long ldm, cudaStream_t st);
 
 namespace tc {
 
@@ -79,9 +79,31 @@ __device__ __forceinline__ uint32_t prologue(const Smem& sm, int warp) {
 // Thread t of quadrant q holds accumulator row q*32+t; after the transpose 8 lanes cover one 128-byte row segment.
 __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, int q, int lane, float* __restrict__ C,
                                             long long ldc, long long row0, long long row_end, int col0, int col_end,
-                                            int ncols, const float* __restrict__ bias, int flags) {
+                                            int ncols, const float* __restrict__ bias, int flags,
+                                            const float* __restrict__ mask, long long ldm) {
     float* st = sm.epi(q);
+    const int cc = (lane & 7) * 4;
+    const bool acc = (flags & GNNX_GEMM_ACCUMULATE) != 0;
     for (int c = 0; c < ncols; c += 32) {
+        const int gcol = col0 + c + cc;
+        const bool col_ok = gcol < col_end;
+        // previous C (accumulate) and the ReLU mask rows are fetched BEFORE the TMEM load so that the 8 independent
+        // global loads of this chunk overlap it (a load issued after a store to C cannot be hoisted by the compiler).
+        float4 prev[8], mk[8];
+        if (acc && col_ok) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const long long grow = row0 + q * 32 + i * 4 + (lane >> 3);
+                prev[i] = grow < row_end ? *reinterpret_cast<const float4*>(C + grow * ldc + gcol) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        if (mask && col_ok) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const long long grow = row0 + q * 32 + i * 4 + (lane >> 3);
+                mk[i] = grow < row_end ? __ldcs(reinterpret_cast<const float4*>(mask + grow * ldm + gcol)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
         float v[32];
         tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
         tmem_ld_wait();
@@ -89,9 +111,7 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
         for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(st + lane * kEpiPitch + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         __syncwarp();
-        const int cc = (lane & 7) * 4;
-        const int gcol = col0 + c + cc;
-        if (gcol < col_end) {
+        if (col_ok) {
             float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
             if (bias) bv = __ldg(reinterpret_cast<const float4*>(bias + gcol));
 #pragma unroll
@@ -101,15 +121,15 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
                 if (grow < row_end) {
                     float4 o = *reinterpret_cast<const float4*>(st + r * kEpiPitch + cc);
                     o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
-                    float* dst = C + grow * ldc + gcol;
-                    if (flags & GNNX_GEMM_ACCUMULATE) {
-                        float4 p = *reinterpret_cast<const float4*>(dst);
-                        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+                    if (acc) { o.x += prev[i].x; o.y += prev[i].y; o.z += prev[i].z; o.w += prev[i].w; }
+                    if (mask) {
+                        o.x = mk[i].x > 0.f ? o.x : 0.f; o.y = mk[i].y > 0.f ? o.y : 0.f;
+                        o.z = mk[i].z > 0.f ? o.z : 0.f; o.w = mk[i].w > 0.f ? o.w : 0.f;
                     }
                     if (flags & GNNX_GEMM_RELU) {
                         o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
                     }
-                    *reinterpret_cast<float4*>(dst) = o;
+                    *reinterpret_cast<float4*>(C + grow * ldc + gcol) = o;
                 }
             }
         }
@@ -121,7 +141,8 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
 template <bool kBMN>
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
-                 long long ldc, int M, int N, int K, int BN, const float* __restrict__ bias, int flags) {
+                 long long ldc, int M, int N, int K, int BN, const float* __restrict__ bias, int flags,
+                 const float* __restrict__ mask, long long ldm) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -190,7 +211,7 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             for (int h = 0; h < halves; ++h)
-                epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags);
+                epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(sm.tmem_empty());
@@ -265,7 +286,7 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             tc_fence_after();
             const int ncols = min(BN, No - n0);
             for (int h = 0; h < halves; ++h)
-                epilogue_acc(sm, tmem_base + h * 256, q, lane, out, No, (long long)m0 + h * 128, Mo, n0, No, ncols, nullptr, 0);
+                epilogue_acc(sm, tmem_base + h * 256, q, lane, out, No, (long long)m0 + h * 128, Mo, n0, No, ncols, nullptr, 0, nullptr, 0);
         } else {                                   // empty row range: this split contributes zeros
             for (int h = 0; h < halves; ++h)
                 for (int r = q * 32 + lane; r < 128; r += 128) {
@@ -381,7 +402,8 @@ size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int p
 }
 
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
-            int64_t N, int64_t K, const float* bias, int flags, int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
+            int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, int precision, void* ws,
+            size_t ws_bytes, cudaStream_t st) {
     (void)precision;
     static bool attr_done = false;
     if (!attr_done) {
@@ -402,9 +424,9 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         int tiles = ceil_div(M, 256) * ceil_div(N, BN);
         int grid = tiles < kNumSMs ? tiles : kNumSMs;
         if (tb)
-            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags);
+            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
         else
-            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags);
+            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
         return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
@@ -416,7 +438,7 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
                                                                           p.rows_per_split, p.BM, p.BN);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
-    return splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, st);
+    return splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
 }
 
 }  // namespace gnnx

@@ -270,24 +270,23 @@ __device__ __forceinline__ void pna_scalers(const int* __restrict__ rowptr, int 
     s_att = avg_deg_log / logf(fmaxf(d, 1.f) + 1.f);
 }
 
-__global__ void k_pna_post_combine_fwd(const float* __restrict__ y0, const float* __restrict__ z, const float* __restrict__ bias,
-                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int T, int Fo,
-                                       int relu, float* __restrict__ out) {
-    const int H = T * Fo, h4 = H / 4;
+__global__ void k_pna_post_combine_fwd(const float* __restrict__ z, const float* __restrict__ bias,
+                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int H, int relu,
+                                       float* __restrict__ out) {
+    const int h4 = H / 4;
     long long total = N * h4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int row = (int)(i / h4);
         int c = (int)(i % h4) * 4;
-        int t = c / Fo, f = c % Fo;
         float sa, st;
         pna_scalers(rowptr, row, avg_deg_log, sa, st);
-        const float* zr = z + (((long long)row * T + t) * 3) * Fo + f;
-        F4 a = f4_ld(y0 + (long long)row * H + c), zi = f4_lds(zr), za = f4_lds(zr + Fo), zt = f4_lds(zr + 2 * Fo);
+        const float* zr = z + (long long)row * 3 * H + c;
+        F4 zi = f4_lds(zr), za = f4_lds(zr + H), zt = f4_lds(zr + 2 * H);
         F4 bb = bias ? f4_ld(bias + c) : f4_zero();
         F4 o;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float v = a.a[j] + zi.a[j] + sa * za.a[j] + st * zt.a[j] + bb.a[j];
+            float v = zi.a[j] + sa * za.a[j] + st * zt.a[j] + bb.a[j];
             o.a[j] = relu ? fmaxf(v, 0.f) : v;
         }
         stg4(out + (long long)row * H + c, o.q);
@@ -295,14 +294,13 @@ __global__ void k_pna_post_combine_fwd(const float* __restrict__ y0, const float
 }
 
 __global__ void k_pna_post_combine_bwd(const float* __restrict__ dout, const float* __restrict__ out,
-                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int T, int Fo,
-                                       int relu, float* __restrict__ dy0, float* __restrict__ dz) {
-    const int H = T * Fo, h4 = H / 4;
+                                       const int* __restrict__ rowptr, float avg_deg_log, long long N, int H, int relu,
+                                       float* __restrict__ dz) {
+    const int h4 = H / 4;
     long long total = N * h4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int row = (int)(i / h4);
         int c = (int)(i % h4) * 4;
-        int t = c / Fo, f = c % Fo;
         float sa, st;
         pna_scalers(rowptr, row, avg_deg_log, sa, st);
         F4 g = f4_lds(dout + (long long)row * H + c);
@@ -314,11 +312,10 @@ __global__ void k_pna_post_combine_bwd(const float* __restrict__ dout, const flo
         F4 ga, gt;
 #pragma unroll
         for (int j = 0; j < 4; ++j) { ga.a[j] = sa * g.a[j]; gt.a[j] = st * g.a[j]; }
-        float* zr = dz + (((long long)row * T + t) * 3) * Fo + f;
-        stg4(dy0 + (long long)row * H + c, g.q);
+        float* zr = dz + (long long)row * 3 * H + c;
         stg4(zr, g.q);
-        stg4(zr + Fo, ga.q);
-        stg4(zr + 2 * Fo, gt.q);
+        stg4(zr + H, ga.q);
+        stg4(zr + 2 * H, gt.q);
     }
 }
 
@@ -420,19 +417,19 @@ int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, 
     return check_launch("pna_aggregate_bwd");
 }
 
-int gnnx_pna_post_combine_fwd(const float* y0, const float* z, const float* bias, const int32_t* rowptr, float avg_deg_log,
-                              int64_t N, int32_t T, int32_t Fo, int32_t relu, float* out, void* stream) {
-    GNNX_REQUIRE(Fo % 4 == 0, "pna_post_combine_fwd: F_out must be a multiple of 4");
+int gnnx_pna_post_combine_fwd(const float* z, const float* bias, const int32_t* rowptr, float avg_deg_log, int64_t N,
+                              int32_t H, int32_t relu, float* out, void* stream) {
+    GNNX_REQUIRE(H % 4 == 0, "pna_post_combine_fwd: h_out must be a multiple of 4");
     if (N == 0) return GNNX_OK;
-    k_pna_post_combine_fwd<<<flat_grid(N * (T * Fo / 4)), 256, 0, as_stream(stream)>>>(y0, z, bias, rowptr, avg_deg_log, N, T, Fo, relu, out);
+    k_pna_post_combine_fwd<<<flat_grid(N * (H / 4)), 256, 0, as_stream(stream)>>>(z, bias, rowptr, avg_deg_log, N, H, relu, out);
     return check_launch("pna_post_combine_fwd");
 }
 
 int gnnx_pna_post_combine_bwd(const float* dout, const float* out, const int32_t* rowptr, float avg_deg_log, int64_t N,
-                              int32_t T, int32_t Fo, int32_t relu, float* dy0, float* dz, void* stream) {
-    GNNX_REQUIRE(Fo % 4 == 0, "pna_post_combine_bwd: F_out must be a multiple of 4");
+                              int32_t H, int32_t relu, float* dz, void* stream) {
+    GNNX_REQUIRE(H % 4 == 0, "pna_post_combine_bwd: h_out must be a multiple of 4");
     if (N == 0) return GNNX_OK;
-    k_pna_post_combine_bwd<<<flat_grid(N * (T * Fo / 4)), 256, 0, as_stream(stream)>>>(dout, out, rowptr, avg_deg_log, N, T, Fo, relu, dy0, dz);
+    k_pna_post_combine_bwd<<<flat_grid(N * (H / 4)), 256, 0, as_stream(stream)>>>(dout, out, rowptr, avg_deg_log, N, H, relu, dz);
     return check_launch("pna_post_combine_bwd");
 }
 

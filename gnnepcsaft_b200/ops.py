@@ -162,8 +162,9 @@ def _ld(t: Tensor) -> int:
 
 def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, bias: Optional[Tensor] = None,
          relu: bool = False, out: Optional[Tensor] = None, accumulate: bool = False,
-         precision: Optional[int] = None) -> Tensor:
-    """``out = act(op(a) @ op(b) + bias)``; ``a``/``b``/``out`` may be column slices (row stride = ld)."""
+         precision: Optional[int] = None, relu_mask: Optional[Tensor] = None) -> Tensor:
+    """``out = act(op(a) @ op(b) + bias)``; ``a``/``b``/``out`` may be column slices (row stride = ld).
+    ``relu_mask`` [M,N]: the result is zeroed where ``relu_mask <= 0`` (fused ReLU backward of the layer below)."""
     for t, n in ((a, "a"), (b, "b")):
         if not t.is_cuda or t.dtype != torch.float32:
             raise RuntimeError(f"gnnx.gemm: `{n}` must be a CUDA float32 tensor (no CPU fallback exists)")
@@ -179,12 +180,14 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
         raise ValueError("gnnx.gemm: bad `out`")
     if bias is not None:
         _chk(bias, torch.float32, "bias")
+    if relu_mask is not None and (relu_mask.shape != (M, N) or relu_mask.dtype != torch.float32 or not relu_mask.is_cuda):
+        raise ValueError("gnnx.gemm: bad `relu_mask`")
     prec = _default_precision if precision is None else precision
     flags = (GEMM_RELU if relu else 0) | (GEMM_ACCUMULATE if accumulate else 0)
     L = lib()
     ws, nb = _ws(L.query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
     L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),
-           M, N, K, _p(bias), flags, prec, _p(ws), nb, _stream())
+           M, N, K, _p(bias), flags, _p(relu_mask), 0 if relu_mask is None else _ld(relu_mask), prec, _p(ws), nb, _stream())
     return out
 
 
@@ -248,24 +251,23 @@ def pna_aggregate_bwd(dagg: Tensor, m: Tensor, agg: Tensor, rowptr: Tensor, towe
     return dm
 
 
-def pna_post_combine_fwd(y0: Tensor, z: Tensor, bias: Optional[Tensor], rowptr: Tensor, avg_deg_log: float,
-                         towers: int, relu: bool) -> Tensor:
-    _chk(y0, torch.float32, "y0"); _chk(z, torch.float32, "z")
-    N, H = y0.shape
-    out = torch.empty_like(y0)
-    lib().call("gnnx_pna_post_combine_fwd", y0.data_ptr(), z.data_ptr(), _p(bias), rowptr.data_ptr(), float(avg_deg_log),
-               N, towers, H // towers, int(relu), out.data_ptr(), _stream())
+def pna_post_combine_fwd(z: Tensor, bias: Optional[Tensor], rowptr: Tensor, avg_deg_log: float, relu: bool) -> Tensor:
+    """z [N, 3*Ho] = (identity | amplification | attenuation) partial products -> out [N, Ho]."""
+    _chk(z, torch.float32, "z")
+    N, H = z.shape[0], z.shape[1] // 3
+    out = torch.empty((N, H), dtype=torch.float32, device=z.device)
+    lib().call("gnnx_pna_post_combine_fwd", z.data_ptr(), _p(bias), rowptr.data_ptr(), float(avg_deg_log), N, H, int(relu),
+               out.data_ptr(), _stream())
     return out
 
 
-def pna_post_combine_bwd(dout: Tensor, out: Tensor, rowptr: Tensor, avg_deg_log: float, towers: int, relu: bool):
+def pna_post_combine_bwd(dout: Tensor, out: Tensor, rowptr: Tensor, avg_deg_log: float, relu: bool) -> Tensor:
     _chk(dout, torch.float32, "dout"); _chk(out, torch.float32, "out")
     N, H = dout.shape
-    dy0 = torch.empty_like(dout)
     dz = torch.empty((N, 3 * H), dtype=torch.float32, device=dout.device)
-    lib().call("gnnx_pna_post_combine_bwd", dout.data_ptr(), out.data_ptr(), rowptr.data_ptr(), float(avg_deg_log), N,
-               towers, H // towers, int(relu), dy0.data_ptr(), dz.data_ptr(), _stream())
-    return dy0, dz
+    lib().call("gnnx_pna_post_combine_bwd", dout.data_ptr(), out.data_ptr(), rowptr.data_ptr(), float(avg_deg_log), N, H,
+               int(relu), dz.data_ptr(), _stream())
+    return dz
 
 
 def relu_bwd(dy: Tensor, y: Tensor) -> Tensor:

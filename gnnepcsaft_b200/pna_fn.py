@@ -5,7 +5,11 @@ Restructurings relative to the PyG formulation, all algebraically ex
     so the [E, 3F] concat is never built and two of the three products run on N rows, not E;
   * the four aggregators are produced by ONE pass over the dst-sorted messages;
   * the degree scalers are per-row scalars, so (s * agg) W^T = s * (agg W^T): the [N, 12F] / [N, 13F]
-    concats are never built -- three K=4F products plus a fused combine replace the K=13F product.
+    concats are never built -- ONE product agg [N,4H] x Wz^T [4H, 3Ho] plus a fused combine replace the K=13F product;
+  * towers are folded into block-diagonal weights (built per call from the per-tower parameters, a few KB..MB):
+    every Linear of the layer is then ONE full-width GEMM whatever `towers` is.  These products are HBM-bound at
+    the hot path's shapes (DESIGN.md), so the zero blocks cost tensor-pipe flops, not time;
+  * the ReLU backward between Linear layers rides the dX product's epilogue (`relu_mask`).
 """
 
 from __future__ import annotations
@@ -46,80 +50,83 @@ def _split_params(meta: PNAMeta, params):
     return we, be, pre, post, wl, bl
 
 
-def _tower_chain_fwd(inp: Tensor, layers, towers: int, f: int, first: int) -> List[Tensor]:
-    """Per-tower Linear(+ReLU) layers ``first..`` applied to column blocks of ``inp``; returns all outputs."""
+def _bd(blocks: List[Tensor]) -> Tensor:
+    return blocks[0].contiguous() if len(blocks) == 1 else torch.block_diag(*blocks)
+
+
+def _cat(ts: List[Tensor], dim: int = 0) -> Tensor:
+    return ts[0].contiguous() if len(ts) == 1 else torch.cat(ts, dim)
+
+
+class _Packed:
+    """Block-diagonal / stacked views of the per-tower parameters (see module docstring)."""
+
+    def __init__(self, meta: PNAMeta, pre, post):
+        T, F = meta.towers, meta.f_in
+        w0 = [pre[t][0][0] for t in range(T)]
+        self.wpq = torch.cat([_bd([w[:, 0:F] for w in w0]), _bd([w[:, F:2 * F] for w in w0])], 0)      # [2H, H]
+        self.wr = _cat([w[:, 2 * F:3 * F] for w in w0])                                                # [H, F]
+        self.br = _cat([pre[t][0][1] for t in range(T)])
+        self.pre = [(_bd([pre[t][l][0] for t in range(T)]), _cat([pre[t][l][1] for t in range(T)]))
+                    for l in range(1, meta.pre_layers)]
+        wp = [post[t][0][0] for t in range(T)]
+        self.wx = _bd([w[:, 0:F] for w in wp])                                                         # [Ho, H]
+        self.wz = torch.cat([_bd([w[:, F + s * 4 * F:F + (s + 1) * 4 * F] for w in wp]) for s in range(3)], 0)  # [3Ho, 4H]
+        self.b0 = _cat([post[t][0][1] for t in range(T)])
+        self.post = [(_bd([post[t][l][0] for t in range(T)]), _cat([post[t][l][1] for t in range(T)]))
+                     for l in range(1, meta.post_layers)]
+
+
+def _chain_fwd(inp: Tensor, layers) -> List[Tensor]:
+    """Linear(+ReLU except after the last) layers; returns the input and every layer output."""
     outs = [inp]
-    n_layers = len(layers[0])
-    for l in range(first, n_layers):
-        cur = outs[-1]
-        nxt = torch.empty_like(cur)
-        for t in range(towers):
-            w, b = layers[t][l]
-            ops.gemm(cur[:, t * f:(t + 1) * f], w, trans_b=True, bias=b, relu=l < n_layers - 1,
-                     out=nxt[:, t * f:(t + 1) * f])
-        outs.append(nxt)
+    for i, (w, b) in enumerate(layers):
+        outs.append(ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=i < len(layers) - 1))
     return outs
 
 
-def _tower_chain_bwd(d_last: Tensor, acts: List[Tensor], layers, towers: int, f: int, first: int, grads: dict):
-    """Backward of ``_tower_chain_fwd``; ``d_last`` is the gradient at the last (un-activated) output.
-    Returns the gradient at ``acts[0]`` (before any mask for acts[0]'s own activation)."""
-    n_layers = len(layers[0])
-    d = d_last
-    for l in range(n_layers - 1, first - 1, -1):
-        y_in = acts[l - first]
-        if l < n_layers - 1:                       # this layer's output went through ReLU
-            d = ops.relu_bwd(d, acts[l - first + 1])
-        d_in = torch.empty_like(y_in)
-        for t in range(towers):
-            w, b = layers[t][l]
-            sl = slice(t * f, (t + 1) * f)
-            ops.gemm(d[:, sl], w, out=d_in[:, sl])
-            grads[id(w)] = ops.gemm(d[:, sl], y_in[:, sl], trans_a=True)
-            grads[id(b)] = ops.colsum(d[:, sl])
-        d = d_in
-    return d
+def _chain_bwd(d: Tensor, acts: List[Tensor], layers, mask_first: bool):
+    """Backward of ``_chain_fwd``.  ``acts[i]`` is the input of layer i; every ``acts[i]`` went through a ReLU, whose
+    backward is fused into the dX product -- for ``acts[0]`` only if ``mask_first``.  Returns (d at acts[0], dW, db)."""
+    dws, dbs = [None] * len(layers), [None] * len(layers)
+    for i in range(len(layers) - 1, -1, -1):
+        w, _ = layers[i]
+        dws[i] = ops.gemm(d, acts[i], trans_a=True)
+        dbs[i] = ops.colsum(d)
+        d = ops.gemm(d, w, relu_mask=acts[i] if (i > 0 or mask_first) else None)
+    return d, dws, dbs
+
+
+def _diag_blocks(m: Tensor, T: int) -> List[Tensor]:
+    r, c = m.shape[0] // T, m.shape[1] // T
+    return [m[t * r:(t + 1) * r, t * c:(t + 1) * c] for t in range(T)]
 
 
 class PNAConvFn(Function):
     @staticmethod
     def forward(ctx, x, efeat, meta: PNAMeta, *params):
         g, T, F, Fo = meta.g, meta.towers, meta.f_in, meta.f_out
-        H, Ho = T * F, T * Fo
-        N = x.shape[0]
+        Ho = T * Fo
         we, be, pre, post, wl, bl = _split_params(meta, params)
+        pk = _Packed(meta, pre, post)
         x = _c(x)
         efeat = _c(efeat)
-        dev = x.device
-        # edge term: edge_encoder, then the e' block of the first pre_nn Linear (+ its bias)
+        # edge term: edge_encoder, then the e' block of the first pre_nn Linear (+ its bias); 60 rows in table form
         e1 = ops.gemm(efeat, we, trans_b=True, bias=be)
-        pq = torch.empty((N, 2 * H), dtype=torch.float32, device=dev)
-        r = torch.empty((efeat.shape[0], H), dtype=torch.float32, device=dev)
-        for t in range(T):
-            w0, b0 = pre[t][0]
-            xt = x[:, t * F:(t + 1) * F]
-            ops.gemm(xt, w0[:, 0:F], trans_b=True, out=pq[:, t * F:(t + 1) * F])
-            ops.gemm(xt, w0[:, F:2 * F], trans_b=True, out=pq[:, H + t * F:H + (t + 1) * F])
-            ops.gemm(e1, w0[:, 2 * F:3 * F], trans_b=True, bias=b0, out=r[:, t * F:(t + 1) * F])
+        r = ops.gemm(e1, pk.wr, trans_b=True, bias=pk.br)
+        pq = ops.gemm(x, pk.wpq, trans_b=True)
         ridx = meta.codes if meta.codes is not None else g.csr_eid
         h = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=meta.pre_layers > 1)
-        hs = _tower_chain_fwd(h, pre, T, F, 1)
+        hs = _chain_fwd(h, pk.pre)
         m = hs[-1]
         agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
         if CAPTURE_AGG is not None:
             CAPTURE_AGG.append(dict(agg=agg, m=m, g=g))
-        y0 = torch.empty((N, Ho), dtype=torch.float32, device=dev)
-        z = torch.empty((N, 3 * Ho), dtype=torch.float32, device=dev)
-        for t in range(T):
-            wp, _ = post[t][0]
-            ops.gemm(x[:, t * F:(t + 1) * F], wp[:, 0:F], trans_b=True, out=y0[:, t * Fo:(t + 1) * Fo])
-            a_t = agg[:, t * 4 * F:(t + 1) * 4 * F]
-            for s in range(3):
-                ops.gemm(a_t, wp[:, F + s * 4 * F:F + (s + 1) * 4 * F], trans_b=True,
-                         out=z[:, (3 * t + s) * Fo:(3 * t + s + 1) * Fo])
-        bias0 = post[0][0][1] if T == 1 else torch.cat([post[t][0][1] for t in range(T)])
-        o = ops.pna_post_combine_fwd(y0, z, bias0, g.rowptr, meta.avg_deg_log, T, relu=meta.post_layers > 1)
-        os_ = _tower_chain_fwd(o, post, T, Fo, 1)
+        z = torch.empty((x.shape[0], 3 * Ho), dtype=torch.float32, device=x.device)
+        ops.gemm(agg, pk.wz, trans_b=True, out=z)
+        ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
+        o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
+        os_ = _chain_fwd(o, pk.post)
         out = ops.gemm(os_[-1], wl, trans_b=True, bias=bl)
         ctx.meta = meta
         ctx.n_hs, ctx.n_os = len(hs), len(os_)
@@ -138,66 +145,59 @@ class PNAConvFn(Function):
         os_ = list(saved[4 + ctx.n_hs:4 + ctx.n_hs + ctx.n_os])
         params = saved[4 + ctx.n_hs + ctx.n_os:]
         we, be, pre, post, wl, bl = _split_params(meta, params)
+        pk = _Packed(meta, pre, post)
         grads: dict = {}
         dout = _c(dout)
-        N = x.shape[0]
-        dev = x.device
 
         # lin
-        d = ops.gemm(dout, wl)
         grads[id(wl)] = ops.gemm(dout, os_[-1], trans_a=True)
         grads[id(bl)] = ops.colsum(dout)
-        # post layers 1.. (reverse) -> gradient at o (post-combine output)
-        d = _tower_chain_bwd(d, os_, post, T, Fo, 1, grads)
+        d = ops.gemm(dout, wl)
+        # post layers 1.. -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
+        d, dws, dbs = _chain_bwd(d, os_, pk.post, mask_first=False)
+        for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
+            for t, blk in enumerate(_diag_blocks(dw, T)):
+                grads[id(post[t][l][0])] = blk
+                grads[id(post[t][l][1])] = db[t * Fo:(t + 1) * Fo]
         # first post Linear with folded scalers
-        dy0, dz = ops.pna_post_combine_bwd(d, os_[0], g.rowptr, meta.avg_deg_log, T, relu=meta.post_layers > 1)
+        dz = ops.pna_post_combine_bwd(d, os_[0], g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
+        dy0 = dz[:, :Ho]
+        dwz = ops.gemm(dz, agg, trans_a=True)                   # [3Ho, 4H]
+        dwx = ops.gemm(dy0, x, trans_a=True)                    # [Ho, H]
         db0 = ops.colsum(dy0)
-        dx = torch.empty_like(x)
-        dagg = torch.empty_like(agg)
+        dagg = ops.gemm(dz, pk.wz)                              # [N, 4H]
         for t in range(T):
-            wp, bp = post[t][0]
-            dwp = torch.empty_like(wp)
-            xt = x[:, t * F:(t + 1) * F]
-            dy0_t = dy0[:, t * Fo:(t + 1) * Fo]
-            ops.gemm(dy0_t, wp[:, 0:F], out=dx[:, t * F:(t + 1) * F])
-            ops.gemm(dy0_t, xt, trans_a=True, out=dwp[:, 0:F])
-            a_t = agg[:, t * 4 * F:(t + 1) * 4 * F]
-            for s in range(3):
-                dz_ts = dz[:, (3 * t + s) * Fo:(3 * t + s + 1) * Fo]
-                w_s = wp[:, F + s * 4 * F:F + (s + 1) * 4 * F]
-                ops.gemm(dz_ts, w_s, out=dagg[:, t * 4 * F:(t + 1) * 4 * F], accumulate=s > 0)
-                ops.gemm(dz_ts, a_t, trans_a=True, out=dwp[:, F + s * 4 * F:F + (s + 1) * 4 * F])
-            grads[id(wp)] = dwp
-            grads[id(bp)] = db0[t * Fo:(t + 1) * Fo] if T > 1 else db0
+            cols = [dwx[t * Fo:(t + 1) * Fo, t * F:(t + 1) * F]]
+            cols += [dwz[s * Ho + t * Fo:s * Ho + (t + 1) * Fo, t * 4 * F:(t + 1) * 4 * F] for s in range(3)]
+            grads[id(post[t][0][0])] = torch.cat(cols, 1)
+            grads[id(post[t][0][1])] = db0[t * Fo:(t + 1) * Fo]
         # aggregators
         dm = ops.pna_aggregate_bwd(dagg, hs[-1], agg, g.rowptr, T)
         if CAPTURE_BWD is not None:
-            CAPTURE_BWD.append(dict(dagg=dagg, dm=dm, m=hs[-1], agg=agg, dz=dz, dy0=dy0, d_post=d))
-        # pre layers 1.. (reverse) -> gradient at h (after the first layer's activation)
-        dh = _tower_chain_bwd(dm, hs, pre, T, F, 1, grads)
-        if meta.pre_layers > 1:
-            dh = ops.relu_bwd(dh, hs[0])
+            CAPTURE_BWD.append(dict(dagg=dagg, dm=dm, m=hs[-1], agg=agg, dz=dz, d_post=d))
+        # pre layers 1.. -> gradient at the gather output (ReLU of the first layer fused into the last dX product)
+        dh, dws, dbs = _chain_bwd(dm, hs, pk.pre, mask_first=True)
+        for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
+            for t, blk in enumerate(_diag_blocks(dw, T)):
+                grads[id(pre[t][l][0])] = blk
+                grads[id(pre[t][l][1])] = db[t * F:(t + 1) * F]
         table = meta.codes is not None
         dpq, dr = ops.pna_gather_bwd(dh, g, want_dr_edge=not table)
         if table:
             dr = ops.code_segment_sum(dh, meta.codes, efeat.shape[0])
-        de1 = torch.empty_like(e1)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = ops.gemm(dpq, pk.wpq)
+            ops.gemm(dy0, pk.wx, out=dx, accumulate=True)
+        dwpq = ops.gemm(dpq, x, trans_a=True)                   # [2H, H]
+        dwr = ops.gemm(dr, e1, trans_a=True)                    # [H, F]
+        dbr = ops.colsum(dr)
         for t in range(T):
-            w0, b0 = pre[t][0]
-            dw0 = torch.empty_like(w0)
-            xt = x[:, t * F:(t + 1) * F]
-            dp_t = dpq[:, t * F:(t + 1) * F]
-            dq_t = dpq[:, H + t * F:H + (t + 1) * F]
-            dr_t = dr[:, t * F:(t + 1) * F]
-            ops.gemm(dp_t, w0[:, 0:F], out=dx[:, t * F:(t + 1) * F], accumulate=True)
-            ops.gemm(dq_t, w0[:, F:2 * F], out=dx[:, t * F:(t + 1) * F], accumulate=True)
-            ops.gemm(dp_t, xt, trans_a=True, out=dw0[:, 0:F])
-            ops.gemm(dq_t, xt, trans_a=True, out=dw0[:, F:2 * F])
-            ops.gemm(dr_t, e1, trans_a=True, out=dw0[:, 2 * F:3 * F])
-            ops.gemm(dr_t, w0[:, 2 * F:3 * F], out=de1, accumulate=t > 0)
-            grads[id(w0)] = dw0
-            grads[id(b0)] = ops.colsum(dr_t)
+            sl = slice(t * F, (t + 1) * F)
+            grads[id(pre[t][0][0])] = torch.cat([dwpq[sl, sl], dwpq[H + t * F:H + (t + 1) * F, sl], dwr[sl]], 1)
+            grads[id(pre[t][0][1])] = dbr[sl]
+        de1 = ops.gemm(dr, pk.wr)
         grads[id(we)] = ops.gemm(de1, efeat, trans_a=True)
         grads[id(be)] = ops.colsum(de1)
         defeat = ops.gemm(de1, we) if ctx.needs_input_grad[1] else None
-        return (dx if ctx.needs_input_grad[0] else None, defeat, None, *[grads.get(id(p)) for p in params])
+        return (dx, defeat, None, *[grads.get(id(p)) for p in params])

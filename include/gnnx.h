@@ -116,19 +116,22 @@ GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_fe
  *   trans_a = 0: A is [M,K] row-major (lda);  1: A is stored [K,M] (lda) and used transposed
  *   trans_b = 0: B is [K,N] row-major (ldb);  1: B is stored [N,K] (ldb)  (Linear forward)
  *   bias: optional [N]; flags: GNNX_GEMM_RELU applies max(.,0); GNNX_GEMM_ACCUMULATE adds the
- *   previous contents of C.  precision: GNNX_PREC_* below.
+ *   previous contents of C.  relu_mask: optional [M,N] (row stride ld_mask): the result is zeroed
+ *   where relu_mask <= 0 -- the ReLU backward of the layer BELOW fused into a dX product
+ *   (dX = (dY W) * (y_in > 0)).  precision: GNNX_PREC_* below.
  * Split-K (deterministic two-pass) is chosen internally when M*N is small and K large;
  * workspace may be null when gnnx_gemm_workspace_bytes() returns 0. */
 #define GNNX_GEMM_RELU 1
 #define GNNX_GEMM_ACCUMULATE 2
 #define GNNX_PREC_FP32 0 /* CUDA-core fp32 FMA (parity tier, rel 1e-5)              */
 #define GNNX_PREC_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM             */
-#define GNNX_PREC_BF16 2 /* tcgen05 kind::f16 on bf16-rounded operands, fp32 accum  */
+#define GNNX_PREC_BF16 2 /* the reference's "medium": served by the tf32 kernels (more precise) */
 GNNX_API size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t trans_a, int32_t trans_b,
                                  int32_t precision);
 GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float* B, int64_t ldb, int32_t trans_b,
               float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags,
-              int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
+              const float* relu_mask, int64_t ld_mask, int32_t precision, void* workspace, size_t workspace_bytes,
+              void* stream);
 
 /* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);
@@ -171,17 +174,16 @@ GNNX_API int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64
 GNNX_API int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, const int32_t* rowptr,
                            int64_t num_nodes, int32_t towers, int32_t f, float* dm, void* stream);
 
-/* First post_nn Linear with the scalers folded in.  z is [N, T, 3, F_out] holding
- * agg[:,t] W_id^T | agg[:,t] W_amp^T | agg[:,t] W_att^T, y0 is [N, T*F_out] = x W_x^T:
- *   out = act( y0 + z_id + s_amp(d_i) z_amp + s_att(d_i) z_att + bias ),
+/* First post_nn Linear with the scalers folded in.  z is [N, 3, Ho] (Ho = towers * F_out):
+ *   z[:,0] = x Wx^T + agg W_id^T,  z[:,1] = agg W_amp^T,  z[:,2] = agg W_att^T  (block-diagonal over towers),
+ *   out = act( z_id + s_amp(d_i) z_amp + s_att(d_i) z_att + bias ),
  *   s_amp = log(d+1)/avg_deg_log,  s_att = avg_deg_log / log(max(d,1)+1),  d = in-degree. */
-GNNX_API int gnnx_pna_post_combine_fwd(const float* y0, const float* z, const float* bias, const int32_t* rowptr,
-                              float avg_deg_log, int64_t num_nodes, int32_t towers, int32_t f_out,
-                              int32_t relu, float* out, void* stream);
-/* dy0 = dout*mask, dz = (dy0, s_amp dy0, s_att dy0); mask = (out > 0) when relu. */
+GNNX_API int gnnx_pna_post_combine_fwd(const float* z, const float* bias, const int32_t* rowptr, float avg_deg_log,
+                              int64_t num_nodes, int32_t h_out, int32_t relu, float* out, void* stream);
+/* dz [N,3,Ho] = (g, s_amp g, s_att g) with g = dout * (out > 0 if relu); dz[:,0] is also d(x Wx^T). */
 GNNX_API int gnnx_pna_post_combine_bwd(const float* dout, const float* out, const int32_t* rowptr,
-                              float avg_deg_log, int64_t num_nodes, int32_t towers, int32_t f_out,
-                              int32_t relu, float* dy0, float* dz, void* stream);
+                              float avg_deg_log, int64_t num_nodes, int32_t h_out, int32_t relu, float* dz,
+                              void* stream);
 
 /* dx = dy * (y > 0) elementwise (ReLU backward between Linear layers). */
 GNNX_API int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream);

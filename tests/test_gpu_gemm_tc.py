@@ -103,3 +103,22 @@ def test_small_or_unaligned_shapes_fall_back_to_fp32_kernel():
     out = ops.gemm(a.to(DEV), w.to(DEV), trans_b=True)
     ref = a.double() @ w.double().t()
     assert float((out.double().cpu() - ref).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("prec", ["tf32", "fp32"])
+def test_fused_relu_mask_and_accumulate(prec):
+    """dX = (dY W) * (y_in > 0) with the mask applied in the epilogue, alone and on top of accumulate."""
+    ops.set_matmul_precision(prec)
+    M, K, N = 3000, 256, 512
+    dy, w, y = torch.randn(M, K), torch.randn(K, N), torch.randn(M, N)
+    ref = (dy.double() @ w.double()) * (y.double() > 0)
+    out = ops.gemm(dy.to(DEV), w.to(DEV), relu_mask=y.to(DEV))
+    err = (out.double().cpu() - ref).abs()
+    bound = 3 * U_TF32 * (dy.double().abs() @ w.double().abs()) + 1e-6
+    assert float((err / bound).max()) <= 1.0
+    assert bool((out.cpu()[y <= 0] == 0).all())
+    prev = torch.randn(M, N)
+    out2 = prev.to(DEV).clone()
+    ops.gemm(dy.to(DEV), w.to(DEV), out=out2, accumulate=True, relu_mask=y.to(DEV))
+    ref2 = (dy.double() @ w.double() + prev.double()) * (y.double() > 0)
+    assert float(((out2.double().cpu() - ref2).abs() / bound).max()) <= 1.0

@@ -61,7 +61,7 @@ def test_colsum():
 
 
 # ------------------------------------------------------------------ embeddings
-@pytest.mark.parametrize("H", [64, 256])
+@pytest.mark.parametrize("H", [8, 32, 64, 200, 256, 512])
 def test_atom_bond_encoder_fwd_bwd(H):
     _, b = make_batch(64, seed=3)
     for cls_o, cls_p, key in ((O.AtomEncoder, gnn.AtomEncoder, "x"), (O.BondEncoder, gnn.BondEncoder, "edge_attr")):
