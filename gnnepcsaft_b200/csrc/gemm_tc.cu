@@ -33,8 +33,8 @@ constexpr int kBK = 32;                         // fp32 per k-block = one 128-by
 constexpr int kAStage = 256 * 128;              // 32 KB: 256 rows x 128 B (rows kernel) / 8 chunks x 32 k x 128 B (red kernel)
 constexpr int kBStage = 256 * 128;              // 32 KB
 constexpr int kStageBytes = kAStage + kBStage;  // 64 KB
-constexpr int kEpiPitch = 36;                   // floats; 144-byte rows keep float4 staging conflict-free
-constexpr int kEpiBytes = 4 * 32 * kEpiPitch * 4;
+constexpr int kEpiPitch = 36;                   // floats; 144-byte rows keep float4 staging conflict-free (register-store path)
+constexpr int kEpiBytes = 4 * 2 * 4096;         // per epilogue warp: two 32x32 fp32 TMA-store staging tiles (1024-B aligned)
 constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + 128;
 constexpr int kTmemCols = 512;
 
@@ -42,7 +42,7 @@ struct Smem {
     uint8_t* base;      // 1024-aligned
     __device__ uint32_t a(int s) const { return smem_u32(base + s * kStageBytes); }
     __device__ uint32_t b(int s) const { return smem_u32(base + s * kStageBytes + kAStage); }
-    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages * kStageBytes) + q * 32 * kEpiPitch; }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages * kStageBytes + q * 8192); }
     __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStages * kStageBytes + kEpiBytes); }
     __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }
     __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStages + s); }
@@ -84,6 +84,23 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
     float* st = sm.epi(q);
     const int cc = (lane & 7) * 4;
     const bool acc = (flags & GNNX_GEMM_ACCUMULATE) != 0;
+    const int dbg = (flags >> 8) & 3;            // GNNX_EPI_DEBUG experiments (wrong results for dbg >= 2)
+    if (dbg == 3) return;
+    if (dbg == 1 || dbg == 2) {
+        for (int c = 0; c < ncols; c += 32) {
+            float v[32];
+            tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+            tmem_ld_wait();
+            const long long grow = row0 + q * 32 + lane;
+            if (dbg == 1 && grow < row_end) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (col0 + c + 4 * j < col_end)
+                        *reinterpret_cast<float4*>(C + grow * ldc + col0 + c + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else if (v[0] == 123.456f) C[0] = v[1];
+        }
+        return;
+    }
     for (int c = 0; c < ncols; c += 32) {
         const int gcol = col0 + c + cc;
         const bool col_ok = gcol < col_end;
@@ -137,12 +154,54 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
     }
 }
 
+// Epilogue of one 128-row accumulator through TMA stores: TMEM -> registers (+bias, ReLU) -> 128B-swizzled 32x32 smem
+// tile -> cp.async.bulk.tensor store (or reduce-add when accumulating), two tiles in flight per warp.  The bulk
+// copy engine moves whole 128-byte rows, so four epilogue warps are enough to keep the SM's store path full; rows
+// and columns beyond the tensor bounds are clipped by the tensor map.  `it` counts this warp's staged tiles.
+__device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
+                                            int row0, int row_end, int col0, int ncols, const float* __restrict__ bias,
+                                            int col_end, int flags, uint32_t& it) {
+    uint8_t* stage = reinterpret_cast<uint8_t*>(sm.epi(q));
+    for (int c = 0; c < ncols; c += 32, ++it) {
+        float v[32];
+        tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
+        uint8_t* buf = stage + (it & 1) * 4096;
+        if (lane == 0) tma_store_wait_read<1>();          // the store that last read this buffer has drained it
+        __syncwarp();
+        tmem_ld_wait();
+        if (bias) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int gc = col0 + c + 4 * j;
+                if (gc < col_end) {
+                    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + gc));
+                    v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                }
+            }
+        }
+        if (flags & GNNX_GEMM_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            if (row0 + q * 32 < row_end && col0 + c < col_end)
+                tma_store_2d(tmC, smem_u32(buf), col0 + c, row0 + q * 32, (flags & GNNX_GEMM_ACCUMULATE) != 0);
+            tma_store_commit();
+        }
+    }
+}
+
 // ------------------------------------------------------------------ C[M,N] = A[M,K] * op(B)
 template <bool kBMN>
 __global__ void __launch_bounds__(kThreads, 1)
-k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ C,
-                 long long ldc, int M, int N, int K, int BN, const float* __restrict__ bias, int flags,
-                 const float* __restrict__ mask, long long ldm) {
+k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
+                 const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -203,20 +262,28 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else {
         const int q = warp & 3;
-        uint32_t tphase = 0;
+        uint32_t tphase = 0, it = 0;
+        // register-store path only where the epilogue must read global memory besides adding (ReLU mask / act(C + AB))
+        const bool use_tma = !mask && !((flags & GNNX_GEMM_ACCUMULATE) && (flags & GNNX_GEMM_RELU)) && ((flags >> 8) & 3) == 0;
+        if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
         for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
             const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
             const int halves = (m0 + 128 < M) ? 2 : 1;
             mbar_wait(sm.tmem_full(), tphase);
             tc_fence_after();
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
-            for (int h = 0; h < halves; ++h)
-                epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
+            for (int h = 0; h < halves; ++h) {
+                if (use_tma)
+                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it);
+                else
+                    epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(sm.tmem_empty());
             tphase ^= 1;
         }
+        if (use_tma && lane == 0) tma_store_wait_all();
     }
     tc_fence_before();
     __syncthreads();
@@ -228,8 +295,9 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // ------------------------------------------------------------------ partial[z][Mo,No] = A[rows_z, Mo]^T * B[rows_z, No]
 __global__ void __launch_bounds__(kThreads, 1)
-k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, float* __restrict__ partial,
-                int Mo, int No, int R, int rows_per_split, int BM, int BN) {
+k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmP, float* __restrict__ partial, int Mo, int No, int R,
+                int rows_per_split, int BM, int BN) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -285,8 +353,13 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             mbar_wait(sm.tmem_full(), 0);
             tc_fence_after();
             const int ncols = min(BN, No - n0);
+            uint32_t it = 0;
+            // tmP views the partials as [splits * Mo, No]; Mo and No are multiples of 32, so a 32x32 staging tile is
+            // either wholly inside this split's [Mo, No] block or skipped (row_end / col_end guards).
+            const int prow = blockIdx.y * Mo;
             for (int h = 0; h < halves; ++h)
-                epilogue_acc(sm, tmem_base + h * 256, q, lane, out, No, (long long)m0 + h * 128, Mo, n0, No, ncols, nullptr, 0, nullptr, 0);
+                epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmP, prow + m0 + h * 128, prow + Mo, n0, ncols, nullptr, No, 0, it);
+            if (lane == 0) tma_store_wait_all();
         } else {                                   // empty row range: this split contributes zeros
             for (int h = 0; h < halves; ++h)
                 for (int r = q * 32 + lane; r < 128; r += 128) {
@@ -348,6 +421,18 @@ static int make_map_mnmajor(CUtensorMap* m, const float* p, int64_t rows, int64_
     CUresult r = encode_fn()(m, tma_dtype(), 3, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                              CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (MN-major) failed: %d", (int)r);
+}
+
+// Store view of a row-major [rows, cols] fp32 matrix: 32x32 tiles, 128B swizzle (matches epilogue_tma's staging).
+static int make_map_store(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld) {
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(p), dims, strides, box, es,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (store) failed: %d", (int)r);
 }
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -412,7 +497,10 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_done = true;
     }
-    CUtensorMap mA, mB;
+    static int epi_dbg = -1;
+    if (epi_dbg < 0) { const char* e = getenv("GNNX_EPI_DEBUG"); epi_dbg = e ? atoi(e) & 3 : 0; }
+    flags |= epi_dbg << 8;
+    CUtensorMap mA, mB, mC;
     if (!ta) {
         int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
         if (make_map_kmajor(&mA, A, M, K, lda, 256)) return GNNX_ERR_INVALID;
@@ -421,12 +509,13 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         } else {
             if (make_map_mnmajor(&mB, B, K, N, ldb, BN / 32)) return GNNX_ERR_INVALID;
         }
+        if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
         int tiles = ceil_div(M, 256) * ceil_div(N, BN);
         int grid = tiles < kNumSMs ? tiles : kNumSMs;
         if (tb)
-            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
+            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
         else
-            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
+            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
         return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
@@ -434,7 +523,8 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     GNNX_REQUIRE(ws && ws_bytes >= (size_t)p.splits * M * N * sizeof(float), "gemm_tc: workspace too small for the row-split partials");
     if (make_map_mnmajor(&mA, A, K, M, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, K, N, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
-    k_gemm_tf32_red<<<dim3(p.tiles, p.splits), kThreads, kSmemBytes, st>>>(mA, mB, (float*)ws, (int)M, (int)N, (int)K,
+    if (make_map_store(&mC, (const float*)ws, (int64_t)p.splits * M, N, N)) return GNNX_ERR_INVALID;
+    k_gemm_tf32_red<<<dim3(p.tiles, p.splits), kThreads, kSmemBytes, st>>>(mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
                                                                           p.rows_per_split, p.BM, p.BN);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;

@@ -23,8 +23,30 @@ def timeit(fn, reps=10):
     return e0.elapsed_time(e1) / reps
 
 
+def single(M, N, K, layout):
+    """One shape, 3 launches: the target of an `ncu --set full` capture."""
+    dev = "cuda"
+    ops.set_matmul_precision("tf32")
+    a = torch.randn(M, K, device=dev)
+    w = torch.randn(N, K, device=dev)
+    wt = w.t().contiguous()
+    c = torch.empty(M, N, device=dev)
+    dy = torch.randn(M, N, device=dev)
+    for _ in range(3):
+        if layout == "NT":
+            ops.gemm(a, w, trans_b=True, out=c)
+        elif layout == "NN":
+            ops.gemm(a, wt, out=c)
+        else:
+            ops.gemm(dy, a, trans_a=True)
+    torch.cuda.synchronize()
+    print("ok")
+
+
 def main():
     dev = "cuda"
+    if len(sys.argv) > 1 and sys.argv[1] == "--single":
+        return single(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), sys.argv[5])
     ops.set_matmul_precision(sys.argv[1] if len(sys.argv) > 1 else "tf32")
     rows = [102400, 204800]
     shapes = [(256, 256), (256, 1024), (768, 1024), (1024, 256), (512, 256)]     # (N, K)
