@@ -208,7 +208,15 @@ __global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, i
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= cols) return;
     float s = 0.f;
-    for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * cols + c];
+    int ch = 0;
+    for (; ch + 8 <= nchunks; ch += 8) {           // 8 independent loads in flight, summed in chunk order
+        float t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = partial[(long long)(ch + j) * cols + c];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += t[j];
+    }
+    for (; ch < nchunks; ++ch) s += partial[(long long)ch * cols + c];
     out[c] = s;
 }
 int colsum_chunks(int64_t rows, int64_t cols) {
@@ -237,7 +245,7 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
     int nch = colsum_chunks(rows, cols);
     int rpc = ceil_div(rows, nch);
     k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
-    k_colsum_final<<<ceil_div(cols, 128), 128, 0, st>>>((const float*)ws, nch, (int)cols, out);
+    k_colsum_final<<<ceil_div(cols, 32), 32, 0, st>>>((const float*)ws, nch, (int)cols, out);
     return check_launch("colsum", 2);
 }
 

@@ -160,9 +160,20 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
 // and columns beyond the tensor bounds are clipped by the tensor map.  `it` counts this warp's staged tiles.
 __device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
                                             int row0, int row_end, int col0, int ncols, const float* __restrict__ bias,
-                                            int col_end, int flags, uint32_t& it) {
+                                            int col_end, int flags, uint32_t& it, const float* __restrict__ mask = nullptr,
+                                            long long ldm = 0) {
     uint8_t* stage = reinterpret_cast<uint8_t*>(sm.epi(q));
+    const long long grow = (long long)row0 + q * 32 + lane;
     for (int c = 0; c < ncols; c += 32, ++it) {
+        // ReLU mask of the layer below: this thread's row, 128 contiguous bytes, requested before the TMEM load
+        float4 mk[8];
+        if (mask) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                mk[j] = (grow < row_end && col0 + c + 4 * j < col_end)
+                            ? *reinterpret_cast<const float4*>(mask + grow * ldm + col0 + c + 4 * j)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         float v[32];
         tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
         uint8_t* buf = stage + (it & 1) * 4096;
@@ -177,6 +188,13 @@ __device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, 
                     const float4 b = __ldg(reinterpret_cast<const float4*>(bias + gc));
                     v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
                 }
+            }
+        }
+        if (mask) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                v[4 * j] = mk[j].x > 0.f ? v[4 * j] : 0.f; v[4 * j + 1] = mk[j].y > 0.f ? v[4 * j + 1] : 0.f;
+                v[4 * j + 2] = mk[j].z > 0.f ? v[4 * j + 2] : 0.f; v[4 * j + 3] = mk[j].w > 0.f ? v[4 * j + 3] : 0.f;
             }
         }
         if (flags & GNNX_GEMM_RELU) {
@@ -263,8 +281,8 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else {
         const int q = warp & 3;
         uint32_t tphase = 0, it = 0;
-        // register-store path only where the epilogue must read global memory besides adding (ReLU mask / act(C + AB))
-        const bool use_tma = !mask && !((flags & GNNX_GEMM_ACCUMULATE) && (flags & GNNX_GEMM_RELU)) && ((flags >> 8) & 3) == 0;
+        // register-store path only for act(C + AB): the epilogue must read C before it can apply the activation / mask
+        const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask)) && ((flags >> 8) & 3) == 0;
         if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
         for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
             const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
@@ -274,7 +292,7 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             for (int h = 0; h < halves; ++h) {
                 if (use_tma)
-                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it);
+                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it, mask, ldm);
                 else
                     epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
             }
@@ -469,12 +487,12 @@ bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, 
     if ((lda & 3) || (ldb & 3) || (ldc & 3)) return false;
     if (M > 0x7fffffff || N > 0x7fffffff || K > 0x7fffffff) return false;
     if (!ta) {
-        if (M < 64 || N < 16 || K < 8 || (N & 3)) return false;
+        if (M < 1 || N < 16 || K < 8 || (N & 3)) return false;
         if (tb) return true;                               // C = A B^T, both K-major
         return (N % 32) == 0;                              // C = A B, B [K,N] as an MN-major operand
     }
     if (tb) return false;                                  // A^T B^T: not on the hot path
-    return M >= 32 && N >= 32 && (M % 32) == 0 && (N % 32) == 0 && K >= 256;
+    return M >= 32 && N >= 32 && (M % 32) == 0 && (N % 32) == 0 && K >= 32;
 }
 
 size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision) {

@@ -62,17 +62,27 @@ __global__ void k_bn_stats_partial(const float* __restrict__ x, int rows, int C,
     }
 }
 
+// one warp per channel: lanes stride over the chunks, then a fixed shuffle tree merges the 32 lane partials
+// (deterministic: the merge order depends only on nchunks)
 __global__ void k_bn_stats_final(const float* __restrict__ partial, int nchunks, int C, float eps, float momentum,
                                  float* __restrict__ running_mean, float* __restrict__ running_var,
                                  float* __restrict__ save_mean, float* __restrict__ save_rstd) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    const int lane = threadIdx.x & 31;
+    const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (c >= C) return;                              // warp-uniform
     Welford t = {0.f, 0.f, 0.f};
-    for (int ch = 0; ch < nchunks; ++ch) {
+    for (int ch = lane; ch < nchunks; ch += 32) {
         const float* p = partial + (long long)ch * 3 * C;
         Welford o = {p[c], p[C + c], p[2 * C + c]};
         welford_merge(t, o);
     }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        Welford o = {__shfl_down_sync(0xffffffffu, t.n, off), __shfl_down_sync(0xffffffffu, t.mean, off),
+                     __shfl_down_sync(0xffffffffu, t.m2, off)};
+        welford_merge(t, o);
+    }
+    if (lane != 0) return;
     float var = t.m2 / t.n;                      // biased, used to normalise
     save_mean[c] = t.mean;
     save_rstd[c] = rsqrtf(var + eps);
@@ -144,7 +154,18 @@ __global__ void k_bn_bwd_final(const float* __restrict__ partial, int nchunks, i
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     float a = 0.f, b = 0.f;
-    for (int ch = 0; ch < nchunks; ++ch) {
+    int ch = 0;
+    for (; ch + 8 <= nchunks; ch += 8) {           // 16 independent loads in flight, summed in chunk order
+        float ta[8], tb[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            ta[j] = partial[(long long)(ch + j) * 2 * C + c];
+            tb[j] = partial[(long long)(ch + j) * 2 * C + C + c];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { a += ta[j]; b += tb[j]; }
+    }
+    for (; ch < nchunks; ++ch) {
         a += partial[(long long)ch * 2 * C + c];
         b += partial[(long long)ch * 2 * C + C + c];
     }
@@ -320,7 +341,7 @@ int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weigh
         int nch = bn_chunks(rows, C);
         int rpc = ceil_div(rows, nch);
         k_bn_stats_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(x, (int)rows, C, rpc, (float*)ws);
-        k_bn_stats_final<<<ceil_div(C, 128), 128, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
+        k_bn_stats_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
     } else {
         GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
         k_bn_eval_stats<<<ceil_div(C, 128), 128, 0, st>>>(running_mean, running_var, C, eps, save_mean, save_rstd);
@@ -339,7 +360,7 @@ int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t ro
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
     k_bn_bwd_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
-    k_bn_bwd_final<<<ceil_div(C, 128), 128, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
+    k_bn_bwd_final<<<ceil_div(C, 32), 32, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
     k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx);
     return check_launch("bn_relu_bwd", 3);
 }

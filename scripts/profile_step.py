@@ -39,11 +39,16 @@ def main():
     trainer.step(store.collate(ids))
     torch.cuda.synchronize()
     n0 = lib().launch_count()
+    import time
     torch.cuda.profiler.start()
+    t0 = time.perf_counter()
     for _ in range(args.steps):
         out = trainer.step(store.collate(ids))
+    t_host = time.perf_counter() - t0
     torch.cuda.synchronize()
+    t_all = time.perf_counter() - t0
     torch.cuda.profiler.stop()
+    print(f"host issue time {1e3 * t_host / args.steps:.2f} ms/step, wall {1e3 * t_all / args.steps:.2f} ms/step")
     print(f"steps={args.steps} gnnx_launches_per_step={(lib().launch_count() - n0) // args.steps} loss={float(out[0]):.6f}")
 
 
