@@ -11,8 +11,12 @@ of the flat gradient when N > 1), AdamW-amsgrad.  Prints ONE JSON line on rank 0
   value   graphs/s with the packed dataset already resident in HBM (device-timed, max over ranks)
   e2e     graphs/s through the reference-facing call model.forward(x, edge_index, edge_attr, batch) with the
           reference's int64 batch tensors in pinned HOST memory: H2D copy, step, D2H read of the loss, every step
-  roofline  the PNA multi-aggregator kernel (gnnx_pna_aggregate_fwd), timed alone with CUDA events against the
-          measured HBM copy bandwidth in MEASURED_PEAKS.json
+  roofline  the entry point with the largest share of the step (the tcgen05 tf32 GEMMs; HBM-bound with fp32 operands):
+          algorithmic bytes / CUDA-event time of its calls inside two extra full steps, against the measured HBM copy
+          bandwidth in MEASURED_PEAKS.json; `kernels` lists the same figure for the gather / scatter / norm kernels
+  dtype   tf32 = tcgen05 kind::tf32 products with fp32 accumulation and fp32 storage everywhere (the reference trains
+          with torch.set_float32_matmul_precision("medium"), i.e. bf16-class products: train/train.py:54);
+          --precision fp32 runs the CUDA-core parity tier
   cpu_baseline  the CPU oracle (pure-torch restatement of the reference's PyG path) on a bounded sample
 
 --impl reference times that CPU oracle as the reference arm (torch_geometric is not installable here or on the
@@ -167,6 +171,67 @@ def run_reference_arm(args, cfg, target):
     print(json.dumps(line), flush=True)
 
 
+
+# ------------------------------------------------------------------ roofline accounting
+def _algorithmic_bytes(name, a, N, E, H):
+    """Algorithmic HBM bytes (and flops) of one gnnx call; None for calls that are not tracked."""
+    if name == "gnnx_gemm":
+        M, Nn, K, flags, mask = a[8], a[9], a[10], a[12], a[13]
+        byts = 4.0 * (M * K + Nn * K + M * Nn)
+        if flags & 2:
+            byts += 4.0 * M * Nn
+        if mask:
+            byts += 4.0 * M * Nn
+        return byts, 2.0 * M * Nn * K
+    if name == "gnnx_pna_aggregate_fwd":          # read messages once, write the four aggregates (SURVEY 8d: 4EH + 16NH + 4N)
+        return 4.0 * E * H + 16.0 * N * H + 4.0 * N, 0.0
+    if name == "gnnx_pna_aggregate_bwd":          # SURVEY 8d: 8EH + 32NH
+        return 8.0 * E * H + 32.0 * N * H, 0.0
+    if name == "gnnx_pna_gather_fwd":             # unique node rows [N,2H] read, messages [E,H] written
+        return 8.0 * N * H + 4.0 * E * H + 5.0 * E, 0.0
+    if name == "gnnx_pna_gather_bwd":             # dh [E,H] read, dpq [N,2H] written
+        return 4.0 * E * H + 8.0 * N * H + 8.0 * E, 0.0
+    if name == "gnnx_pna_post_combine_fwd":
+        return 16.0 * N * H, 0.0
+    if name == "gnnx_pna_post_combine_bwd":
+        return 20.0 * N * H, 0.0
+    if name in ("gnnx_bn_relu_fwd", "gnnx_bn_relu_bwd"):
+        rows, C = a[1] if name.endswith("fwd") else a[3], a[2] if name.endswith("fwd") else a[4]
+        return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
+    if name == "gnnx_colsum":
+        return 4.0 * a[2] * a[3], 0.0
+    return None
+
+
+def summarise_roofline(records, N, E, H, peak, peak_src):
+    agg = {}
+    for name, a, ms in records:
+        r = _algorithmic_bytes(name, a, N, E, H)
+        if r is None:
+            continue
+        d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
+        d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]
+    total_ms = sum(ms for _, _, ms in records)
+    kernels = {}
+    for name, d in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
+        gbs = d["bytes"] / (d["ms"] / 1e3) / 1e9
+        k = {"calls": d["calls"], "ms_per_call": d["ms"] / d["calls"], "share_of_gnnx_time": d["ms"] / total_ms,
+             "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+        if d["flops"]:
+            k["achieved_TFLOPs"] = d["flops"] / (d["ms"] / 1e3) / 1e12
+        kernels[name] = k
+    top = max(agg.items(), key=lambda kv: kv[1]["ms"])
+    name, d = top
+    achieved = d["bytes"] / (d["ms"] / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": name + (" (tcgen05 tf32 k_gemm_tf32_rows / k_gemm_tf32_red)" if name == "gnnx_gemm" else ""),
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "bytes_per_launch": d["bytes"] / d["calls"], "ms_per_launch": d["ms"] / d["calls"], "launches_timed": d["calls"],
+                "peak_source": peak_src, "nodes": N, "edges": E,
+                "note": "algorithmic bytes of every call of the entry point / CUDA-event time of those calls inside 2 full "
+                        "training steps; fp32 operands make these products HBM-bound (DESIGN.md)"}
+    return roofline, kernels
+
+
 # ------------------------------------------------------------------ GPU arm
 def run_gpu_arm(args, cfg, target):
     import torch.distributed as dist
@@ -262,27 +327,17 @@ def run_gpu_arm(args, cfg, target):
     e2e_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     e2e_value = world * G / (e2e_ms / 1e3)
 
-    # ---- roofline of the dominant HBM kernel: the fused PNA multi-aggregator, timed alone on cfg2-sized tensors
+    # ---- roofline pass: 2 more steps of the SAME workload with CUDA events around every gnnx entry point (on the
+    # launching stream); algorithmic bytes per call from its shapes (DESIGN.md "Kernels and rooflines").
     b = store.collate(batch_ids[0])
     H = cfg["hidden_dim"]
     N, E = b.num_nodes, b.index.num_edges
-    m = torch.randn(E, H, device=dev)
-    for _ in range(3):
-        ops.pna_aggregate_fwd(m, b.index.rowptr, 1)
-    reps = 20
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(reps):
-        ops.pna_aggregate_fwd(m, b.index.rowptr, 1)
-    e1.record()
-    torch.cuda.synchronize()
-    agg_ms = e0.elapsed_time(e1) / reps
-    agg_bytes = 4 * E * H + 16 * N * H + 4 * (N + 1)
     peak, peak_src = _peaks()
-    achieved = agg_bytes / (agg_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_pna_aggregate_fwd", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "bytes_per_launch": agg_bytes, "ms_per_launch": agg_ms,
-                "peak_source": peak_src, "nodes": N, "edges": E}
+    lib().start_timing()
+    for i in range(2):
+        resident_step(i)
+    records = lib().stop_timing()
+    roofline, kernels = summarise_roofline(records, N, E, H, peak, peak_src)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -299,7 +354,7 @@ def run_gpu_arm(args, cfg, target):
     line = {
         "metric": "train molecular graphs/sec", "value": value, "unit": "graphs/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "bf16"}[args.precision],
+        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "tf32"}[args.precision],
         "data": "synthetic",
         "config": {"workload": WORKLOAD_NAMES[args.workload], "graphs_per_gpu": G, "global_batch": world * G,
                    "nodes_per_batch": N, "edges_per_batch": E, "parallelism": f"dp{world}",
@@ -311,6 +366,7 @@ def run_gpu_arm(args, cfg, target):
                                                  "from pinned host memory + loss.item()"},
         "gpu_launches": launches,
         "roofline": roofline,
+        "kernels": kernels,
         "cpu_baseline": cpu_baseline,
     }
     print(json.dumps(line), flush=True)
@@ -325,7 +381,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "bf16"])
+    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

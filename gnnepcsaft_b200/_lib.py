@@ -69,9 +69,34 @@ class _Lib:
 
     def call(self, name: str, *args):
         """Call an ``int``-returning entry point and raise on a non-zero code."""
+        if self._timing is not None:
+            return self._timed_call(name, args)
         rc = getattr(self._dll, name)(*args)
         if rc != 0:
             raise GnnxError(f"{name} failed with code {rc}: {self.last_error()}")
+
+    # -- optional per-entry-point device timing (bench.py's roofline pass): CUDA events on the launching stream
+    _timing = None
+
+    def start_timing(self) -> None:
+        self._timing = []
+
+    def stop_timing(self):
+        """Returns ``[(name, args, ms)]`` for every call since ``start_timing()`` (synchronises the device)."""
+        import torch
+        torch.cuda.synchronize()
+        rec, self._timing = self._timing, None
+        return [(n, a, e0.elapsed_time(e1)) for n, a, e0, e1 in rec]
+
+    def _timed_call(self, name: str, args):
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(self._dll, name)(*args)
+        e1.record()
+        if rc != 0:
+            raise GnnxError(f"{name} failed with code {rc}: {self.last_error()}")
+        self._timing.append((name, args, e0, e1))
 
     def launch_count(self) -> int:
         """Kernels launched by libgnnx so far in this process."""

@@ -51,6 +51,30 @@ class FlatParameters:
                 p.grad = self.grad[o:o + p.numel()].view(p.shape)
 
 
+def shard_range(num_items: int, rank: int, world: int):
+    """Contiguous, near-equal shard ``[lo, hi)`` of ``num_items`` for ``rank`` (graphs are independent units:
+    sharding needs no data-path collective)."""
+    base, rem = divmod(num_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def node_balanced_batches(node_counts, max_nodes: int, max_graphs: int):
+    """Greedy split of a graph sequence into consecutive batches of at most ``max_nodes`` nodes / ``max_graphs``
+    graphs (bulk screening mixes 1..100-atom molecules, so batches are sized by nodes, not by graph count).
+    Returns a list of ``(lo, hi)`` index ranges covering ``range(len(node_counts))`` in order."""
+    out, lo, acc = [], 0, 0
+    for i, n in enumerate(node_counts):
+        n = int(n)
+        if i > lo and (acc + n > max_nodes or i - lo >= max_graphs):
+            out.append((lo, i))
+            lo, acc = i, 0
+        acc += n
+    if lo < len(node_counts):
+        out.append((lo, len(node_counts)))
+    return out
+
+
 def cosine_warm_restarts_lr(base_lr: float, epoch: int, t_0: int, t_mult: int = 2, eta_min: float = 1e-6) -> float:
     """``CosineAnnealingWarmRestarts(T_0=warmup_steps, T_mult=2, eta_min=1e-6)`` as a scalar (models.py:66-74)."""
     t_i, t_cur = t_0, epoch
