@@ -77,7 +77,8 @@ __device__ __forceinline__ uint32_t prologue(const Smem& sm, int warp) {
 
 // Epilogue of one 128-row accumulator: TMEM -> registers -> per-warp smem transpose -> coalesced float4 rows.
 // Thread t of quadrant q holds accumulator row q*32+t; after the transpose 8 lanes cover one 128-byte row segment.
-__device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, int q, int lane, float* __restrict__ C,
+template <class SM>
+__device__ __forceinline__ void epilogue_acc(const SM& sm, uint32_t tmem_acc, int q, int lane, float* __restrict__ C,
                                             long long ldc, long long row0, long long row_end, int col0, int col_end,
                                             int ncols, const float* __restrict__ bias, int flags,
                                             const float* __restrict__ mask, long long ldm) {
@@ -158,7 +159,8 @@ __device__ __forceinline__ void epilogue_acc(const Smem& sm, uint32_t tmem_acc, 
 // tile -> cp.async.bulk.tensor store (or reduce-add when accumulating), two tiles in flight per warp.  The bulk
 // copy engine moves whole 128-byte rows, so four epilogue warps are enough to keep the SM's store path full; rows
 // and columns beyond the tensor bounds are clipped by the tensor map.  `it` counts this warp's staged tiles.
-__device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
+template <class SM>
+__device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
                                             int row0, int row_end, int col0, int ncols, const float* __restrict__ bias,
                                             int col_end, int flags, uint32_t& it, const float* __restrict__ mask = nullptr,
                                             long long ldm = 0) {
@@ -174,6 +176,13 @@ __device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, 
                             ? *reinterpret_cast<const float4*>(mask + grow * ldm + col0 + c + 4 * j)
                             : make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        float4 bv[8];
+        if (bias) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                bv[j] = (col0 + c + 4 * j < col_end) ? __ldg(reinterpret_cast<const float4*>(bias + col0 + c + 4 * j))
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         float v[32];
         tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
         uint8_t* buf = stage + (it & 1) * 4096;
@@ -183,11 +192,7 @@ __device__ __forceinline__ void epilogue_tma(const Smem& sm, uint32_t tmem_acc, 
         if (bias) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const int gc = col0 + c + 4 * j;
-                if (gc < col_end) {
-                    const float4 b = __ldg(reinterpret_cast<const float4*>(bias + gc));
-                    v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-                }
+                v[4 * j] += bv[j].x; v[4 * j + 1] += bv[j].y; v[4 * j + 2] += bv[j].z; v[4 * j + 3] += bv[j].w;
             }
         }
         if (mask) {
@@ -305,6 +310,146 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     tc_fence_before();
     __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------ C[M,N] = A[M,K] * op(B), version 2
+// 128 rows per CTA and tile (ONE 128 x BN accumulator = 256 TMEM columns), so the 512 columns hold two accumulators
+// and the epilogue of tile i overlaps the loads + MMAs of tile i+1; 4 stages x 48 KB.  With kCluster == 2 two CTAs
+// (a thread-block cluster, adjacent row tiles, same N tile) each load HALF of every weight stage and multicast it to
+// both, so the L2 traffic per output element equals that of a 256-row tile.  A stage is released to the producers of
+// BOTH CTAs by a multicast tcgen05.commit (empty barriers count kCluster arrivals).
+constexpr int kStages2 = 4;
+constexpr int kA2 = 128 * 128;                  // 16 KB
+constexpr int kB2 = 256 * 128;                  // 32 KB
+constexpr int kStage2 = kA2 + kB2;              // 48 KB
+constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes + 256;
+
+struct Smem2 {
+    uint8_t* base;
+    __device__ uint32_t a(int s) const { return smem_u32(base + s * kStage2); }
+    __device__ uint32_t b(int s) const { return smem_u32(base + s * kStage2 + kA2); }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages2 * kStage2 + q * 8192); }
+    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStages2 * kStage2 + kEpiBytes); }
+    __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }
+    __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStages2 + s); }
+    __device__ uint32_t tmem_full(int b) const { return smem_u32(bars() + 2 * kStages2 + b); }
+    __device__ uint32_t tmem_empty(int b) const { return smem_u32(bars() + 2 * kStages2 + 2 + b); }
+    __device__ uint32_t* tmem_ptr() const { return reinterpret_cast<uint32_t*>(bars() + 2 * kStages2 + 4); }
+};
+
+template <bool kBMN, int kCluster>
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
+                  const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm) {
+    extern __shared__ uint8_t smem_raw[];
+    Smem2 sm;
+    sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = kCluster > 1 ? (int)cluster_ctarank() : 0;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages2; ++s) {
+            mbar_init(sm.full(s), 1);
+            mbar_init(sm.empty(s), kCluster);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(sm.tmem_full(b), 1);
+            mbar_init(sm.tmem_empty(b), 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(sm.tmem_ptr()), kTmemCols);
+    tc_fence_before();
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();      // peers must see initialised barriers before any multicast
+    tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr();
+
+    const int n_tiles = (N + BN - 1) / BN;
+    const int m_groups = ((M + 127) / 128 + kCluster - 1) / kCluster;
+    const int work = n_tiles * m_groups;
+    const int cid = blockIdx.x / kCluster, ncl = gridDim.x / kCluster;
+    const int KB = (K + kBK - 1) / kBK;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = kA2 + (uint32_t)BN * 128u;
+            const int half = BN / 2;
+            for (int w = cid; w < work; w += ncl) {
+                const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.empty(stage), phase ^ 1);
+                    mbar_expect_tx(sm.full(stage), tx);
+                    tma_load_2d(sm.a(stage), &tmA, sm.full(stage), kb * kBK, m0);
+                    if (kCluster == 1) {
+                        if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK, n0 / 32);
+                        else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0);
+                    } else {
+                        if (kBMN) tma_load_3d_mc(sm.b(stage) + rank * (half / 32) * 4096, &tmB, sm.full(stage), 0, kb * kBK, n0 / 32 + rank * (half / 32), 3);
+                        else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kb * kBK, n0 + rank * half, 3);
+                    }
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, BN, 0, kBMN ? 1 : 0);
+            int stage = 0;
+            uint32_t phase = 0, i = 0;
+            for (int w = cid; w < work; w += ncl, ++i) {
+                const uint32_t buf = i & 1;
+                mbar_wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.full(stage), phase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < kBK / 8; ++k) {
+                        const uint64_t bdesc = kBMN ? make_smem_desc(sm.b(stage) + k * 1024, 32 * 128, 512, kLayoutSw128B32)
+                                                    : make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        const uint64_t adesc = make_smem_desc(sm.a(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        mma_tf32(tmem_base + buf * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    if (kCluster > 1) mma_commit_mc(sm.empty(stage), 3); else mma_commit(sm.empty(stage));
+                    if (kb == KB - 1) mma_commit(sm.tmem_full(buf));
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        uint32_t it = 0, i = 0;
+        const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask));
+        if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
+        for (int w = cid; w < work; w += ncl, ++i) {
+            const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
+            const uint32_t buf = i & 1;
+            mbar_wait(sm.tmem_full(buf), (i >> 1) & 1);
+            tc_fence_after();
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
+            if (m0 < M) {
+                if (use_tma)
+                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm);
+                else
+                    epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags & 0xff, mask, ldm);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sm.tmem_empty(buf));
+        }
+        if (use_tma && lane == 0) tma_store_wait_all();
+    }
+    tc_fence_before();
+    __syncwarp();                                                    // re-converge the single-lane role warps
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();      // no CTA may exit while its peer can still multicast into it
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -519,6 +664,51 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     if (epi_dbg < 0) { const char* e = getenv("GNNX_EPI_DEBUG"); epi_dbg = e ? atoi(e) & 3 : 0; }
     flags |= epi_dbg << 8;
     CUtensorMap mA, mB, mC;
+    static int use_v1 = -1;
+    if (use_v1 < 0) { const char* e = getenv("GNNX_GEMM_V1"); use_v1 = (e && e[0] == '1') ? 1 : 0; }
+    if (!ta && !use_v1) {
+        const int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
+        const int m_tiles = ceil_div(M, 128);
+        const int cluster = (m_tiles >= 2 && (tb ? (BN % 16 == 0) : (BN % 64 == 0))) ? 2 : 1;
+        if (make_map_kmajor(&mA, A, M, K, lda, 128)) return GNNX_ERR_INVALID;
+        if (tb) {
+            if (make_map_kmajor(&mB, B, N, K, ldb, BN / cluster)) return GNNX_ERR_INVALID;
+        } else {
+            if (make_map_mnmajor(&mB, B, K, N, ldb, BN / 32 / cluster)) return GNNX_ERR_INVALID;
+        }
+        if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
+        const int work = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
+        const int max_cl = kNumSMs / cluster;
+        const int ncl = work < max_cl ? work : max_cl;
+        static bool attr2 = false;
+        if (!attr2) {
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            attr2 = true;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(ncl * cluster);
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = kSmem2;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        const int Mi = (int)M, Ni = (int)N, Ki = (int)K;
+        const long long ldc_ = ldc, ldm_ = ldm;
+        cudaError_t e;
+        if (cluster == 2)
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_);
+        else
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_);
+        if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
+        return check_launch("gemm_tf32_rows2");
+    }
     if (!ta) {
         int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
         if (make_map_kmajor(&mA, A, M, K, lda, 256)) return GNNX_ERR_INVALID;
