@@ -47,7 +47,11 @@ WORKLOADS = {
     "cfg3": dict(conv="GATv2", hidden_dim=256, propagation_depth=7, dropout=0.0, global_pool="add", num_para=2,
                  towers=1, pre_layers=2, post_layers=4, heads=2, add_self_loops=True, model="gnn"),
 }
+WORKLOADS["cfg5"] = dict(WORKLOADS["cfg2"])            # bulk screening runs the (m, sigma, epsilon/k) PNA model in eval mode
+INFER_GRAPHS_PER_STEP = 16384
 WORKLOAD_NAMES = {
+    "cfg5": "bulk inference screening, PNA hidden 256 / 6 layers, eval + pred_with_bounds, synthetic molecules of 1..100 atoms, "
+            "16384 graphs per step per GPU, shards with no communication (BASELINE configs[4])",
     "cfg2": "PNA hidden 256, 6 layers, training step, 4096 synthetic ~25-atom OGB-featurised graphs per GPU (BASELINE configs[1])",
     "cfg3": "GATv2 hidden 256, heads 2, 7 layers, fwd+bwd+step, 4096 synthetic graphs per GPU (BASELINE configs[2])",
 }
@@ -374,6 +378,135 @@ def run_gpu_arm(args, cfg, target):
         dist.destroy_process_group()
 
 
+def run_infer_arm(args, cfg):
+    """BASELINE configs[4]: sharded bulk screening.  One step = one node-balanced batch of 16384 molecules per GPU."""
+    import torch.distributed as dist
+    from gnnepcsaft_b200 import create_model, graph, ops, synth
+    from gnnepcsaft_b200._lib import lib
+    from gnnepcsaft_b200.infer import BulkScreener
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the gnnx kernels have no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ops.set_matmul_precision(args.precision)
+    G = INFER_GRAPHS_PER_STEP
+    graphs = synth.make_inference_graphs(2 * G, seed=1234 + 4 + 1000 * rank)
+    store = graph.DeviceGraphStore(synth.pack(graphs), dev)
+    deg = store.calc_deg()
+    torch.manual_seed(0)
+    model = create_model(dict(cfg), deg).to(dev).eval()
+    scr = BulkScreener(model, store, 0, 1, max_nodes=1 << 21, max_graphs=G)
+    nb = len(scr.batches)
+    out = torch.empty((store.num_graphs, model.num_para), dtype=torch.float32, device=dev)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for i in range(args.warmup):
+        scr.run_batch(i % nb, out)
+    sync()
+    launches0 = lib().launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    done = 0
+    with ClockSampler(local) as clocks:
+        e0.record()
+        for i in range(args.steps):
+            lo, hi = scr.batches[i % nb]
+            scr.run_batch(i % nb, out)
+            done += hi - lo
+        e1.record()
+        sync()
+    launches = lib().launch_count() - launches0
+    ms_step = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    per_step = done / args.steps
+    value = world * per_step / (ms_step / 1e3)
+
+    # e2e: reference-facing pred_with_bounds(Data) on int64 host tensors, predictions read back to the host
+    host = []
+    for lo, hi in scr.batches:
+        x, ei, ea, bt, _, _ = synth.collate_numpy(graphs, lo, hi)
+        host.append(([torch.from_numpy(a).pin_memory() for a in (x, ei, ea, bt)], hi - lo))
+    h2d = sum(t.numel() * t.element_size() for t in host[0][0])
+    res = torch.empty((G, model.num_para), dtype=torch.float32).pin_memory()
+
+    def e2e_step(i):
+        (x, ei, ea, bt), g = host[i % nb]
+        data = graph.Batch(x=x.to(dev, non_blocking=True), edge_index=ei.to(dev, non_blocking=True),
+                           edge_attr=ea.to(dev, non_blocking=True), batch=bt.to(dev, non_blocking=True), num_graphs=g)
+        with torch.no_grad():
+            p = model.pred_with_bounds(data)
+        res[:g].copy_(p, non_blocking=False)               # D2H of the step's result
+        return g
+
+    for i in range(3):
+        e2e_step(i)
+    sync()
+    done = 0
+    e0.record()
+    for i in range(args.steps):
+        done += e2e_step(i)
+    e1.record()
+    sync()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    e2e_value = world * (done / args.steps) / (e2e_ms / 1e3)
+
+    b = store.collate(np.arange(*scr.batches[0]))
+    N, E, H = b.num_nodes, b.index.num_edges, cfg["hidden_dim"]
+    peak, peak_src = _peaks()
+    lib().start_timing()
+    for i in range(2):
+        scr.run_batch(i % nb, out)
+    roofline, kernels = summarise_roofline(lib().stop_timing(), N, E, H, peak, peak_src)
+    if rank == 0:
+        cpu_baseline = None
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import pyg_restated as O
+            threads = os.cpu_count() or 1
+            torch.set_num_threads(threads)
+            t = torch.from_numpy
+            og = [O.Graph(t(g.x), t(g.edge_index), t(g.edge_attr)) for g in graphs[:1024]]
+            mo = O.GNNePCSAFT(dict(cfg, deg=deg)).eval()
+            times = []
+            with torch.no_grad():
+                for i in range(4):
+                    t0 = time.perf_counter()
+                    mo.pred_with_bounds(O.collate(og[i * 256:(i + 1) * 256]))
+                    times.append(time.perf_counter() - t0)
+            cpu_baseline = {"value": 256 / float(np.mean(times[1:])), "unit": "graphs/s", "cores": threads, "kind": "port",
+                            "sample": f"256 molecules/step x 3 steps (1 warm-up): collate + eval forward + clip on the CPU oracle, {threads} threads"}
+        line = {
+            "metric": "infer molecular graphs/sec", "value": value, "unit": "graphs/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "tf32"}[args.precision], "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAMES["cfg5"], "graphs_per_step_per_gpu": per_step, "nodes_per_batch": N,
+                       "edges_per_batch": E, "parallelism": f"shard{world}", "l2": "inputs per step (GBs of activations) far exceed the 126 MB L2"},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_value, "unit": "graphs/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": int(per_step) * model.num_para * 4,
+                    "api": "GNNePCSAFT.pred_with_bounds(Data(x, edge_index, edge_attr, batch)) on int64 tensors from pinned host memory, predictions copied back"},
+            "gpu_launches": launches, "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu_baseline,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -389,6 +522,8 @@ def main():
     target = "para" if cfg["num_para"] == 3 else "assoc"
     if args.impl == "reference":
         run_reference_arm(args, cfg, target)
+    elif args.workload == "cfg5":
+        run_infer_arm(args, cfg)
     else:
         run_gpu_arm(args, cfg, target)
 

@@ -33,8 +33,12 @@ def get_matmul_precision() -> int:
     return _default_precision
 
 
+_raw_stream = torch._C._cuda_getCurrentRawStream
+
+
 def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+    # torch.cuda.current_stream() builds a Python Stream object (~15 us); the raw handle is what the C ABI wants
+    return _raw_stream(torch.cuda.current_device())
 
 
 def _chk(t: Tensor, dtype, name: str) -> Tensor:
@@ -51,11 +55,29 @@ def _p(t: Optional[Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+_WS_CACHE: dict = {}
+_WS_QUERY_CACHE: dict = {}
+
+
 def _ws(nbytes: int, device) -> Tuple[Optional[Tensor], int]:
+    """Scratch for one call.  Kernels of one stream run in order, so a single grow-only buffer per (device, stream)
+    is reused by every call instead of a fresh torch.empty each time."""
     if nbytes == 0:
         return None, 0
-    t = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
+    t = _WS_CACHE.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _WS_CACHE[key] = t
     return t, nbytes
+
+
+def _query(name: str, *args) -> int:
+    key = (name, args)
+    v = _WS_QUERY_CACHE.get(key)
+    if v is None:
+        v = _WS_QUERY_CACHE[key] = lib().query(name, *args)
+    return v
 
 
 # ------------------------------------------------------------------ collator
@@ -76,7 +98,7 @@ def csr_build(edge_index: Optional[Tensor], num_nodes: int, src32: Optional[Tens
     csr_src, csr_eid, pos = torch.empty(E, **i32), torch.empty(E, **i32), torch.empty(E, **i32)
     csc_pos, csc_dst = torch.empty(E, **i32), torch.empty(E, **i32)
     err = torch.empty(1, **i32)
-    ws, nb = _ws(L.query("gnnx_csr_workspace_bytes", num_nodes, E), dev)
+    ws, nb = _ws(_query("gnnx_csr_workspace_bytes", num_nodes, E), dev)
     if edge_index is not None:
         L.call("gnnx_csr_build_i64", edge_index.data_ptr(), num_nodes, E, rowptr.data_ptr(), csr_src.data_ptr(),
                csr_eid.data_ptr(), pos.data_ptr(), colptr.data_ptr(), csc_pos.data_ptr(), csc_dst.data_ptr(),
@@ -147,7 +169,7 @@ def embed_sum_bwd(idx_u8: Tensor, offsets: Tensor, table_rows: int, dout: Tensor
     rows, K = idx_u8.shape
     H = dout.shape[1]
     dtable = torch.empty((table_rows, H), dtype=torch.float32, device=dout.device)
-    ws, nb = _ws(lib().query("gnnx_embed_sum_bwd_workspace_bytes", rows, table_rows, H), dout.device)
+    ws, nb = _ws(_query("gnnx_embed_sum_bwd_workspace_bytes", rows, table_rows, H), dout.device)
     lib().call("gnnx_embed_sum_bwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table_rows, dout.data_ptr(), H,
                dtable.data_ptr(), _p(ws), nb, _stream())
     return dtable
@@ -185,7 +207,7 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
     prec = _default_precision if precision is None else precision
     flags = (GEMM_RELU if relu else 0) | (GEMM_ACCUMULATE if accumulate else 0)
     L = lib()
-    ws, nb = _ws(L.query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
+    ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
     L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),
            M, N, K, _p(bias), flags, _p(relu_mask), 0 if relu_mask is None else _ld(relu_mask), prec, _p(ws), nb, _stream())
     return out
@@ -197,7 +219,7 @@ def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
     rows, cols = x.shape
     if out is None:
         out = torch.empty(cols, dtype=torch.float32, device=x.device)
-    ws, nb = _ws(lib().query("gnnx_colsum_workspace_bytes", rows, cols), x.device)
+    ws, nb = _ws(_query("gnnx_colsum_workspace_bytes", rows, cols), x.device)
     lib().call("gnnx_colsum", x.data_ptr(), _ld(x), rows, cols, out.data_ptr(), _p(ws), nb, _stream())
     return out
 
@@ -229,7 +251,7 @@ def code_segment_sum(dh: Tensor, codes: Tensor, num_codes: int) -> Tensor:
     _chk(dh, torch.float32, "dh"); _chk(codes, torch.uint8, "codes")
     rows, H = dh.shape
     out = torch.empty((num_codes, H), dtype=torch.float32, device=dh.device)
-    ws, nb = _ws(lib().query("gnnx_code_segment_sum_workspace_bytes", rows, num_codes, H), dh.device)
+    ws, nb = _ws(_query("gnnx_code_segment_sum_workspace_bytes", rows, num_codes, H), dh.device)
     lib().call("gnnx_code_segment_sum", dh.data_ptr(), codes.data_ptr(), rows, num_codes, H, out.data_ptr(), _p(ws), nb, _stream())
     return out
 
@@ -285,7 +307,7 @@ def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bo
     y = torch.empty_like(x)
     mean = torch.empty(C, dtype=torch.float32, device=x.device)
     rstd = torch.empty(C, dtype=torch.float32, device=x.device)
-    ws, nb = _ws(lib().query("gnnx_bn_workspace_bytes", rows, C), x.device)
+    ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
     lib().call("gnnx_bn_relu_fwd", x.data_ptr(), rows, C, _p(weight), _p(bias), _p(running_mean), _p(running_var),
                int(training), float(momentum), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                _p(ws), nb, _stream())
@@ -298,7 +320,7 @@ def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Te
     dx = torch.empty_like(x)
     dw = torch.empty(C, dtype=torch.float32, device=x.device)
     db = torch.empty(C, dtype=torch.float32, device=x.device)
-    ws, nb = _ws(lib().query("gnnx_bn_workspace_bytes", rows, C), x.device)
+    ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
     lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, _p(weight), mean.data_ptr(),
                rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
     return dx, dw, db
@@ -349,7 +371,7 @@ def gatv2_bwd(dout: Tensor, xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, a
     ds = torch.empty((E + N, H), dtype=torch.float32, device=dev)
     i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
     u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
-    ws, nb = _ws(lib().query("gnnx_gatv2_bwd_workspace_bytes", N, E, heads, c), dev)
+    ws, nb = _ws(_query("gnnx_gatv2_bwd_workspace_bytes", N, E, heads, c), dev)
     lib().call("gnnx_gatv2_bwd", dout.data_ptr(), xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, att.data_ptr(),
                alpha.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(), g.colptr.data_ptr(), g.csc_pos.data_ptr(),
                g.csc_dst.data_ptr(), N, E, heads, c, float(slope), int(self_loops), dxlr.data_ptr(), datt.data_ptr(),

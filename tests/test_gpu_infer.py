@@ -1,0 +1,46 @@
+"""Bulk screening (BASELINE config 5): node-balanced batches, shards with no communication, eval-mode parity.
+
+Tolerance: fp32 tier, rel 1e-4 / atol 1e-5 against the CPU oracle's ``pred_with_bounds`` (eval mode: every graph is
+independent of its batch, so any batching must give the oracle's per-molecule answer)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+import gnnepcsaft_b200 as G
+from gnnepcsaft_b200 import graph, ops, synth
+from gnnepcsaft_b200.infer import BulkScreener
+from oracle import pyg_restated as O
+from tests.util import PNA_CFG1, assert_close, deg_hist
+
+pytestmark = pytest.mark.gpu
+
+
+def test_sharded_screening_matches_oracle_and_unsharded():
+    ops.set_matmul_precision("fp32")
+    torch.set_float32_matmul_precision("highest")
+    graphs = synth.make_inference_graphs(300, seed=11)
+    cfg = dict(PNA_CFG1, deg=deg_hist(graphs))
+    torch.manual_seed(3)
+    mo = O.GNNePCSAFT(cfg).eval()
+    with torch.no_grad():                              # non-trivial running statistics
+        for bn in list(mo.batch_norms) + [mo.mlp[1], mo.mlp[4]]:
+            m = bn.module if hasattr(bn, "module") else bn
+            m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.5, 1.5)
+    mp = G.GNNePCSAFT(copy.deepcopy(cfg)).cuda().eval()
+    mp.load_state_dict(mo.state_dict(), strict=True)
+    t = torch.from_numpy
+    with torch.no_grad():
+        ref = mo.pred_with_bounds(O.collate([O.Graph(t(g.x), t(g.edge_index), t(g.edge_attr)) for g in graphs]))
+    store = graph.DeviceGraphStore(synth.pack(graphs), torch.device("cuda", 0))
+    whole = BulkScreener(mp, store, max_nodes=2000, max_graphs=64)
+    assert len(whole.batches) > 5 and whole.batches[0][0] == 0 and whole.batches[-1][1] == 300
+    out = whole.run()
+    assert_close(out, ref, 1e-4, 1e-5, "screening vs oracle")
+    lo_b, hi_b = torch.tensor([1.0, 1.9, 50.0]), torch.tensor([25.0, 4.5, 550.0])
+    assert bool((out.cpu() >= lo_b).all()) and bool((out.cpu() <= hi_b).all())
+    parts = [BulkScreener(mp, store, r, 3, max_nodes=1500, max_graphs=50).run() for r in range(3)]
+    assert sum(p.shape[0] for p in parts) == 300
+    assert_close(torch.cat(parts), ref, 1e-4, 1e-5, "3 shards vs oracle")
+    assert not mp.training
