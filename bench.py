@@ -202,6 +202,14 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name in ("gnnx_bn_relu_fwd", "gnnx_bn_relu_bwd"):
         rows, C = a[1] if name.endswith("fwd") else a[3], a[2] if name.endswith("fwd") else a[4]
         return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
+    if name == "gnnx_gatv2_fwd":                  # xlr [N,2H] read once, x_l[src] per edge slot (+ self loops), out written, alpha written
+        n, e, heads, c = a[9], a[10], a[11], a[12]
+        h = heads * c
+        return 4.0 * (e + n) * h + 12.0 * n * h + 4.0 * (e + n) * heads, 0.0
+    if name == "gnnx_gatv2_bwd":                  # + dout, dxlr, ds [E+N, H]
+        n, e, heads, c = a[13], a[14], a[15], a[16]
+        h = heads * c
+        return 8.0 * (e + n) * h + 20.0 * n * h + 4.0 * (e + n) * heads, 0.0
     if name == "gnnx_colsum":
         return 4.0 * a[2] * a[3], 0.0
     return None

@@ -144,9 +144,9 @@ int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* 
 
 int simt_splits(int64_t M, int64_t N, int64_t K) {
     long long tiles = (long long)ceil_div(M, BM) * ceil_div(N, BN);
-    if (tiles >= kNumSMs || K < 1024) return 1;
+    if (tiles >= kNumSMs || K < 128) return 1;
     long long want = (2ll * kNumSMs + tiles - 1) / tiles;
-    long long maxs = K / 256;
+    long long maxs = K >= 1024 ? K / 256 : K / 32;       // small weight-space products are latency-bound: split deeper
     long long s = want < maxs ? want : maxs;
     if (s > 128) s = 128;
     return (int)(s < 1 ? 1 : s);
@@ -204,24 +204,48 @@ __global__ void k_colsum_partial(const float* __restrict__ in, long long ld, int
         partial[(long long)blockIdx.y * cols + c] = t;
     }
 }
+// float4 variant (cols % 4 == 0, 16-byte aligned rows): 64 column groups x 4 row lanes, 4 rows in flight per thread
+__global__ void __launch_bounds__(256)
+k_colsum_partial4(const float* __restrict__ in, long long ld, int rows, int cols, int rows_per_chunk, float* __restrict__ partial) {
+    __shared__ float sh[4][256 + 4];
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int c = (blockIdx.x * 64 + tx) * 4;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < cols) {
+        int r = r0 + ty;
+        for (; r + 12 < r1; r += 16) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = ldg4_stream(in + (long long)(r + 4 * u) * ld + c);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+        }
+        for (; r < r1; r += 4) {
+            float4 v = ldg4_stream(in + (long long)r * ld + c);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+    }
+    sh[ty][tx * 4 + 0] = s.x; sh[ty][tx * 4 + 1] = s.y; sh[ty][tx * 4 + 2] = s.z; sh[ty][tx * 4 + 3] = s.w;
+    __syncthreads();
+    const int cc = blockIdx.x * 256 + threadIdx.x;
+    if (cc < cols) partial[(long long)blockIdx.y * cols + cc] = (sh[0][threadIdx.x] + sh[1][threadIdx.x]) + (sh[2][threadIdx.x] + sh[3][threadIdx.x]);
+}
+
+// one warp per column: lanes stride over the chunks, then a fixed shuffle tree (deterministic)
 __global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, int cols, float* __restrict__ out) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= cols) return;
     float s = 0.f;
-    int ch = 0;
-    for (; ch + 8 <= nchunks; ch += 8) {           // 8 independent loads in flight, summed in chunk order
-        float t[8];
+    for (int ch = lane; ch < nchunks; ch += 32) s += partial[(long long)ch * cols + c];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) t[j] = partial[(long long)(ch + j) * cols + c];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s += t[j];
-    }
-    for (; ch < nchunks; ++ch) s += partial[(long long)ch * cols + c];
-    out[c] = s;
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+    if (lane == 0) out[c] = s;
 }
 int colsum_chunks(int64_t rows, int64_t cols) {
-    int slabs = ceil_div(cols, 32);
-    int target = max(1, (kNumSMs * 8) / slabs);
+    int slabs = ceil_div(cols, 256);
+    int target = max(1, (kNumSMs * 4) / slabs);
     int by_rows = max(1, (int)((rows + 63) / 64));
     return min(target, by_rows);
 }
@@ -244,8 +268,11 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
     if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(out, 0, cols * sizeof(float), st)); return GNNX_OK; }
     int nch = colsum_chunks(rows, cols);
     int rpc = ceil_div(rows, nch);
-    k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
-    k_colsum_final<<<ceil_div(cols, 32), 32, 0, st>>>((const float*)ws, nch, (int)cols, out);
+    if ((cols & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)in & 15) == 0)
+        k_colsum_partial4<<<dim3(ceil_div(cols, 256), nch), 256, 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+    else
+        k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+    k_colsum_final<<<ceil_div(cols, 8), 256, 0, st>>>((const float*)ws, nch, (int)cols, out);
     return check_launch("colsum", 2);
 }
 

@@ -165,16 +165,18 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
                                             int col_end, int flags, uint32_t& it, const float* __restrict__ mask = nullptr,
                                             long long ldm = 0) {
     uint8_t* stage = reinterpret_cast<uint8_t*>(sm.epi(q));
-    const long long grow = (long long)row0 + q * 32 + lane;
+    const int mr = lane >> 3, mj = lane & 7;            // coalesced mask mapping: 8 lanes cover one 128-byte row segment
     for (int c = 0; c < ncols; c += 32, ++it) {
-        // ReLU mask of the layer below: this thread's row, 128 contiguous bytes, requested before the TMEM load
+        // ReLU mask of the layer below, requested before the TMEM load: 4 full 128-byte rows per load instruction
         float4 mk[8];
         if (mask) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-                mk[j] = (grow < row_end && col0 + c + 4 * j < col_end)
-                            ? *reinterpret_cast<const float4*>(mask + grow * ldm + col0 + c + 4 * j)
+            for (int i = 0; i < 8; ++i) {
+                const long long gr = (long long)row0 + q * 32 + i * 4 + mr;
+                mk[i] = (gr < row_end && col0 + c + 4 * mj < col_end)
+                            ? __ldcs(reinterpret_cast<const float4*>(mask + gr * ldm + col0 + c + 4 * mj))
                             : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         }
         float4 bv[8];
         if (bias) {
@@ -195,13 +197,6 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
                 v[4 * j] += bv[j].x; v[4 * j + 1] += bv[j].y; v[4 * j + 2] += bv[j].z; v[4 * j + 3] += bv[j].w;
             }
         }
-        if (mask) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                v[4 * j] = mk[j].x > 0.f ? v[4 * j] : 0.f; v[4 * j + 1] = mk[j].y > 0.f ? v[4 * j + 1] : 0.f;
-                v[4 * j + 2] = mk[j].z > 0.f ? v[4 * j + 2] : 0.f; v[4 * j + 3] = mk[j].w > 0.f ? v[4 * j + 3] : 0.f;
-            }
-        }
         if (flags & GNNX_GEMM_RELU) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
@@ -209,6 +204,18 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
 #pragma unroll
         for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        if (mask) {                                      // second pass over the staged tile in the mask's (coalesced) mapping
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = i * 4 + mr;
+                float4* p = reinterpret_cast<float4*>(buf + r * 128 + ((mj ^ (r & 7)) << 4));
+                float4 o = *p;
+                o.x = mk[i].x > 0.f ? o.x : 0.f; o.y = mk[i].y > 0.f ? o.y : 0.f;
+                o.z = mk[i].z > 0.f ? o.z : 0.f; o.w = mk[i].w > 0.f ? o.w : 0.f;
+                *p = o;
+            }
+        }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {

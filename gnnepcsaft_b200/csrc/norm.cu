@@ -32,33 +32,63 @@ __device__ __forceinline__ void welford_merge(Welford& a, const Welford& b) {
 }
 
 static int bn_chunks(int64_t rows, int32_t C) {
-    int slabs = ceil_div(C, 32);
-    int target = max(1, (kNumSMs * 8) / slabs);
+    int slabs = ceil_div(C, 256);
+    int target = max(1, (kNumSMs * 4) / slabs);
     int by_rows = max(1, (int)((rows + 63) / 64));
     return min(target, by_rows);
 }
 
-// partial: [nchunks][3][C] = (n, mean, M2)
-__global__ void k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial) {
-    __shared__ float sh[kBnRows][3][33];
-    int c = blockIdx.x * 32 + threadIdx.x;
-    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
-    Welford w = {0.f, 0.f, 0.f};
-    if (c < C)
-        for (int r = r0 + threadIdx.y; r < r1; r += kBnRows) welford_add(w, __ldg(x + (long long)r * C + c));
-    sh[threadIdx.y][0][threadIdx.x] = w.n;
-    sh[threadIdx.y][1][threadIdx.x] = w.mean;
-    sh[threadIdx.y][2][threadIdx.x] = w.m2;
+// partial: [nchunks][3][C] = (n, mean, M2).  Block = 64 float4 column groups x 4 row lanes: a warp reads 512
+// contiguous bytes of a row, 4 rows in flight per thread.  Per thread the sums are taken about a pivot (the chunk's
+// first row), which keeps the single-pass variance as accurate as Welford's update without a division per element;
+// lanes and chunks are then merged with Chan's formula in a fixed order.
+__global__ void __launch_bounds__(256)
+k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial) {
+    __shared__ float sh[4][3][256 + 4];
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int c = (blockIdx.x * 64 + tx) * 4;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    F4 s, q, p;
+    s.q = q.q = p.q = make_float4(0.f, 0.f, 0.f, 0.f);
+    float n = 0.f;
+    if (c < C && r0 < r1) {
+        p.q = ldg4(x + (long long)r0 * C + c);
+        int r = r0 + ty;
+        for (; r + 12 < r1; r += 16) {
+            F4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u].q = ldg4_stream(x + (long long)(r + 4 * u) * C + c);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { float d = v[u].a[j] - p.a[j]; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+            n += 4.f;
+        }
+        for (; r < r1; r += 4) {
+            F4 v;
+            v.q = ldg4_stream(x + (long long)r * C + c);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { float d = v.a[j] - p.a[j]; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+            n += 1.f;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float mean = n > 0.f ? p.a[j] + s.a[j] / n : 0.f;
+        float m2 = n > 0.f ? fmaxf(q.a[j] - s.a[j] * s.a[j] / n, 0.f) : 0.f;
+        sh[ty][0][tx * 4 + j] = n; sh[ty][1][tx * 4 + j] = mean; sh[ty][2][tx * 4 + j] = m2;
+    }
     __syncthreads();
-    if (threadIdx.y == 0 && c < C) {
+    const int cc = blockIdx.x * 256 + threadIdx.x;
+    if (cc < C) {
         Welford t = {0.f, 0.f, 0.f};
 #pragma unroll
-        for (int i = 0; i < kBnRows; ++i) {
+        for (int i = 0; i < 4; ++i) {
             Welford o = {sh[i][0][threadIdx.x], sh[i][1][threadIdx.x], sh[i][2][threadIdx.x]};
             welford_merge(t, o);
         }
-        float* p = partial + (long long)blockIdx.y * 3 * C;
-        p[c] = t.n; p[C + c] = t.mean; p[2 * C + c] = t.m2;
+        float* pp = partial + (long long)blockIdx.y * 3 * C;
+        pp[cc] = t.n; pp[C + cc] = t.mean; pp[2 * C + cc] = t.m2;
     }
 }
 
@@ -120,57 +150,81 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
     }
 }
 
-// partial: [nchunks][2][C] = (sum dy', sum dy' * xhat)
-__global__ void k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
-                                 int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
-                                 int rows_per_chunk, float* __restrict__ partial) {
-    __shared__ float sh[kBnRows][2][33];
-    int c = blockIdx.x * 32 + threadIdx.x;
-    int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
-    float s1 = 0.f, s2 = 0.f;
+// partial: [nchunks][2][C] = (sum dy', sum dy' * xhat); same thread layout as k_bn_stats_partial
+__global__ void __launch_bounds__(256)
+k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
+                 int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
+                 int rows_per_chunk, float* __restrict__ partial) {
+    __shared__ float sh[4][2][256 + 4];
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int c = (blockIdx.x * 64 + tx) * 4;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    F4 s1, s2;
+    s1.q = s2.q = make_float4(0.f, 0.f, 0.f, 0.f);
     if (c < C) {
-        float mu = mean[c], rs = rstd[c];
-        for (int r = r0 + threadIdx.y; r < r1; r += kBnRows) {
+        F4 mu, rs;
+        mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+        int r = r0 + ty;
+        for (; r + 4 < r1; r += 8) {
+            F4 g[2], xv[2], yv[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                long long o = (long long)(r + 4 * u) * C + c;
+                g[u].q = ldg4_stream(dy + o);
+                xv[u].q = ldg4(x + o);
+                if (relu) yv[u].q = ldg4(y + o);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float gg = (relu && !(yv[u].a[j] > 0.f)) ? 0.f : g[u].a[j];
+                    s1.a[j] += gg;
+                    s2.a[j] = fmaf(gg, (xv[u].a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
+                }
+        }
+        for (; r < r1; r += 4) {
             long long o = (long long)r * C + c;
-            float g = __ldg(dy + o);
-            if (relu && !(__ldg(y + o) > 0.f)) g = 0.f;
-            s1 += g;
-            s2 += g * ((__ldg(x + o) - mu) * rs);
+            F4 g, xv, yv;
+            g.q = ldg4_stream(dy + o); xv.q = ldg4(x + o);
+            if (relu) yv.q = ldg4(y + o);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float gg = (relu && !(yv.a[j] > 0.f)) ? 0.f : g.a[j];
+                s1.a[j] += gg;
+                s2.a[j] = fmaf(gg, (xv.a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
+            }
         }
     }
-    sh[threadIdx.y][0][threadIdx.x] = s1;
-    sh[threadIdx.y][1][threadIdx.x] = s2;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { sh[ty][0][tx * 4 + j] = s1.a[j]; sh[ty][1][tx * 4 + j] = s2.a[j]; }
     __syncthreads();
-    if (threadIdx.y == 0 && c < C) {
+    const int cc = blockIdx.x * 256 + threadIdx.x;
+    if (cc < C) {
         float a = 0.f, b = 0.f;
 #pragma unroll
-        for (int i = 0; i < kBnRows; ++i) { a += sh[i][0][threadIdx.x]; b += sh[i][1][threadIdx.x]; }
-        partial[(long long)blockIdx.y * 2 * C + c] = a;
-        partial[(long long)blockIdx.y * 2 * C + C + c] = b;
+        for (int i = 0; i < 4; ++i) { a += sh[i][0][threadIdx.x]; b += sh[i][1][threadIdx.x]; }
+        partial[(long long)blockIdx.y * 2 * C + cc] = a;
+        partial[(long long)blockIdx.y * 2 * C + C + cc] = b;
     }
 }
 
+// one warp per channel: lanes stride over the chunks (each lane sums its chunks in order), then a fixed shuffle tree
 __global__ void k_bn_bwd_final(const float* __restrict__ partial, int nchunks, int C, float* __restrict__ dweight, float* __restrict__ dbias) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    const int lane = threadIdx.x & 31;
+    const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (c >= C) return;                              // warp-uniform
     float a = 0.f, b = 0.f;
-    int ch = 0;
-    for (; ch + 8 <= nchunks; ch += 8) {           // 16 independent loads in flight, summed in chunk order
-        float ta[8], tb[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            ta[j] = partial[(long long)(ch + j) * 2 * C + c];
-            tb[j] = partial[(long long)(ch + j) * 2 * C + C + c];
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { a += ta[j]; b += tb[j]; }
-    }
-    for (; ch < nchunks; ++ch) {
+    for (int ch = lane; ch < nchunks; ch += 32) {
         a += partial[(long long)ch * 2 * C + c];
         b += partial[(long long)ch * 2 * C + C + c];
     }
-    dbias[c] = a;
-    dweight[c] = b;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        a += __shfl_down_sync(0xffffffffu, a, off);
+        b += __shfl_down_sync(0xffffffffu, b, off);
+    }
+    if (lane == 0) { dbias[c] = a; dweight[c] = b; }
 }
 
 __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
@@ -340,7 +394,7 @@ int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weigh
         GNNX_REQUIRE(rows > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
         int nch = bn_chunks(rows, C);
         int rpc = ceil_div(rows, nch);
-        k_bn_stats_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(x, (int)rows, C, rpc, (float*)ws);
+        k_bn_stats_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(x, (int)rows, C, rpc, (float*)ws);
         k_bn_stats_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
     } else {
         GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
@@ -359,8 +413,8 @@ int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t ro
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
-    k_bn_bwd_partial<<<dim3(ceil_div(C, 32), nch), dim3(32, kBnRows), 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
-    k_bn_bwd_final<<<ceil_div(C, 32), 32, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
+    k_bn_bwd_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
+    k_bn_bwd_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
     k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx);
     return check_launch("bn_relu_bwd", 3);
 }

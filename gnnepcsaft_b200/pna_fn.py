@@ -9,7 +9,10 @@ Restructurings relative to the PyG formulation, all algebraically ex
   * towers are folded into block-diagonal weights (built per call from the per-tower parameters, a few KB..MB):
     every Linear of the layer is then ONE full-width GEMM whatever `towers` is.  These products are HBM-bound at
     the hot path's shapes (DESIGN.md), so the zero blocks cost tensor-pipe flops, not time;
-  * the ReLU backward between Linear layers rides the dX product's epilogue (`relu_mask`).
+  * the ReLU backward between Linear layers rides the dX product's epilogue (`relu_mask`);
+  * the last post_nn Linear has no activation before `lin`, so the two are applied as ONE Linear with
+    Wf = W_lin W_last, bf = W_lin b_last + b_lin (a 256^3 weight-space product per call); the chain rule back to
+    the two original parameters is exact (dW_lin = dWf W_last^T + dbf b_last^T, dW_last = W_lin^T dWf, ...).
 """
 
 from __future__ import annotations
@@ -77,12 +80,17 @@ class _Packed:
                      for l in range(1, meta.post_layers)]
 
 
-def _chain_fwd(inp: Tensor, layers) -> List[Tensor]:
-    """Linear(+ReLU except after the last) layers; returns the input and every layer output."""
+def _chain_fwd(inp: Tensor, layers, relu_last: bool = False) -> List[Tensor]:
+    """Linear + ReLU layers (no ReLU after the last unless ``relu_last``); returns the input and every layer output."""
     outs = [inp]
     for i, (w, b) in enumerate(layers):
-        outs.append(ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=i < len(layers) - 1))
+        outs.append(ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=relu_last or i < len(layers) - 1))
     return outs
+
+
+def _wprod(a: Tensor, b: Tensor, **kw) -> Tensor:
+    """Weight-space product (a few hundred rows): always on the fp32 kernel."""
+    return ops.gemm(a, b, precision=ops.PREC_FP32, **kw)
 
 
 def _chain_bwd(d: Tensor, acts: List[Tensor], layers, mask_first: bool):
@@ -126,8 +134,14 @@ class PNAConvFn(Function):
         ops.gemm(agg, pk.wz, trans_b=True, out=z)
         ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
         o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
-        os_ = _chain_fwd(o, pk.post)
-        out = ops.gemm(os_[-1], wl, trans_b=True, bias=bl)
+        if pk.post:                                   # fold the activation-free last post Linear into `lin`
+            w_last, b_last = pk.post[-1]
+            os_ = _chain_fwd(o, pk.post[:-1], relu_last=True)
+            wf = _wprod(wl, w_last)
+            bf = _wprod(wl, b_last.unsqueeze(1)).squeeze(1) + bl
+        else:
+            os_, wf, bf = [o], wl, bl
+        out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
         ctx.meta = meta
         ctx.n_hs, ctx.n_os = len(hs), len(os_)
         ctx.save_for_backward(x, efeat, e1, agg, *hs, *os_, *params)
@@ -149,12 +163,27 @@ class PNAConvFn(Function):
         grads: dict = {}
         dout = _c(dout)
 
-        # lin
-        grads[id(wl)] = ops.gemm(dout, os_[-1], trans_a=True)
-        grads[id(bl)] = ops.colsum(dout)
-        d = ops.gemm(dout, wl)
-        # post layers 1.. -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
-        d, dws, dbs = _chain_bwd(d, os_, pk.post, mask_first=False)
+        # lin (fused with the last post Linear when there is one)
+        dwf = ops.gemm(dout, os_[-1], trans_a=True)
+        dbf = ops.colsum(dout)
+        if pk.post:
+            w_last, b_last = pk.post[-1]
+            wf = _wprod(wl, w_last)
+            grads[id(wl)] = _wprod(dwf, w_last, trans_b=True) + torch.outer(dbf, b_last)
+            grads[id(bl)] = dbf
+            dw_last = _wprod(wl, dwf, trans_a=True)
+            db_last = _wprod(wl, dbf.unsqueeze(1), trans_a=True).squeeze(1)
+            l_last = meta.post_layers - 1
+            for t, blk in enumerate(_diag_blocks(dw_last, T)):
+                grads[id(post[t][l_last][0])] = blk
+                grads[id(post[t][l_last][1])] = db_last[t * Fo:(t + 1) * Fo]
+            # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
+            d = ops.gemm(dout, wf, relu_mask=os_[-1] if len(os_) > 1 else None)
+        else:
+            grads[id(wl)], grads[id(bl)] = dwf, dbf
+            d = ops.gemm(dout, wl)
+        # post layers 1..post-2 -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
+        d, dws, dbs = _chain_bwd(d, os_, pk.post[:-1], mask_first=False)
         for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
             for t, blk in enumerate(_diag_blocks(dw, T)):
                 grads[id(post[t][l][0])] = blk

@@ -5,7 +5,9 @@ elementwise AND "as accurate as the fp32 oracle is against its own fp64 run" (fa
 layers + BN + head: fp32 rounding compounds through ~25 dependent GEMMs) use the same two bounds.  StdAggregation
 is discontinuous at var = 1e-5 (jump 0 -> 3.2e-3); entries within fp32 rounding of that threshold are
 teacher-forced to the CUDA path's branch and the test asserts every such entry really is inside the band
-(tests/util.py:branches_from) -- SURVEY 8(c)'s "exclusion band", applied without dropping any entry.
+(tests/util.py:branches_from) -- SURVEY 8(c)'s "exclusion band", applied without dropping any entry.  The same
+holds for the ReLU behind each layer's BatchNorm in the whole-model tests: an activation within fp32 rounding of zero
+(about one per layer per 1e5 entries) takes the CUDA path's sign, and the test asserts it is inside that band.
 """
 import copy
 
@@ -37,12 +39,13 @@ def _ref_err(r32, r64):
 def _grads_close(mp, mo, mo64, rtol):
     """Every parameter gradient: as accurate as the fp32 oracle is against its own fp64 run (normwise, factor 4), and
     elementwise within rtol of the fp32 oracle with an absolute floor of max(1e-5 * global gradient scale, 4 x the
-    fp32 oracle's own error) -- biases that feed a BatchNorm have a true-zero gradient and are judged on that floor."""
+    fp32 oracle's own error) -- biases that feed a BatchNorm have a true-zero gradient and are judged on that floor
+    (normwise: 2e-6 * 5e-2 * gmax = 1e-7 * gmax, i.e. two fp32 ulps of the global gradient scale)."""
     po, po64 = dict(mo.named_parameters()), dict(mo64.named_parameters())
     gmax = max(float(p.grad.abs().max()) for p in mo64.parameters())
     for n, p in mp.named_parameters():
         assert p.grad is not None, f"no grad for {n}"
-        assert_as_accurate(p.grad, po[n].grad, po64[n].grad, f"d{n}", min_scale=1e-2 * gmax)
+        assert_as_accurate(p.grad, po[n].grad, po64[n].grad, f"d{n}", min_scale=5e-2 * gmax)
         assert_close(p.grad, po[n].grad, rtol, max(1e-5 * gmax, 4 * _ref_err(po[n].grad, po64[n].grad)), f"d{n}")
 
 
@@ -122,14 +125,18 @@ def test_whole_model_training_step_parity(cfg, target):
     mo64 = copy.deepcopy(mo).double()
     mo.train(); mp.train(); mo64.train()
     pna_fn.CAPTURE_AGG = []
+    relu_out = []
+    hooks = [bn.register_forward_hook(lambda _m, _i, out: relu_out.append(out.detach())) for bn in mp.batch_norms]
     try:
         pp = mp(b["x"].to(DEV), b["edge_index"].to(DEV), b["edge_attr"].to(DEV), b["batch"].to(DEV))
         aggs = list(pna_fn.CAPTURE_AGG)
     finally:
         pna_fn.CAPTURE_AGG = None
-    with branches_from(aggs, cfg["towers"]):
+        for h in hooks:
+            h.remove()
+    with branches_from(aggs, cfg["towers"], relu_out):
         po = mo(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
-    with branches_from(aggs, cfg["towers"]):
+    with branches_from(aggs, cfg["towers"], relu_out):
         p64 = mo64(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
     assert_as_accurate(pp, po, p64, "model fwd")
     assert_close(pp, po, 1e-4, 1e-6, "model fwd")

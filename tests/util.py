@@ -63,14 +63,18 @@ def assert_as_accurate(a, ref32, ref64, what="", factor=4.0, rel_floor=2e-6, min
 
 
 class branches_from:
-    """Context manager: make the oracle take, entry by entry, the branches the CUDA path took at the two
-    discontinuities of the PNA aggregators -- the Std zero-mask at var = 1e-5 and WHICH message of a row receives
-    the min / max gradient -- and verify afterwards that every entry where the two disagreed lies inside the
+    """Context manager: make the oracle take, entry by entry, the branches the CUDA path took at the
+    discontinuities of the path -- the Std zero-mask at var = 1e-5, WHICH message of a row receives the min / max
+    gradient, and (whole models) the sign of activations within rounding of the ReLU kink behind each BatchNorm --
+    and verify afterwards that every entry where the two disagreed lies inside the
     rounding band of its discontinuity (oracle/pyg_restated.py: STD_MASKS, EXTREMUM_SELECT).  No entry is dropped
     from the comparison.  Use one instance per oracle forward pass."""
 
-    def __init__(self, captured, towers):
+    def __init__(self, captured, towers, relu_outputs=()):
+        """``relu_outputs``: the CUDA model's per-layer BatchNorm+ReLU outputs (their > 0 pattern is forced onto the
+        oracle's ReLU behind each BatchNorm, oracle/pyg_restated.py: RELU_MASKS)."""
         self.std_masks, self.selects = [], []
+        self.relu_masks = [(y.detach() > 0).cpu() for y in relu_outputs]
         for c in captured:
             agg, m, g = c["agg"], c["m"], c["g"]
             n, e = agg.shape[0], m.shape[0]
@@ -88,18 +92,24 @@ class branches_from:
     def __enter__(self):
         O.STD_MASKS = [m.clone() for m in self.std_masks]
         O.EXTREMUM_SELECT = [m.clone() for m in self.selects]
+        O.RELU_MASKS = [m.clone() for m in self.relu_masks] if self.relu_masks else None
         O.STD_BAND_VIOLATIONS.clear()
         O.EXTREMUM_BAND_VIOLATIONS.clear()
+        O.RELU_BAND_VIOLATIONS.clear()
         return self
 
     def __exit__(self, *exc):
-        left = len(O.STD_MASKS) + len(O.EXTREMUM_SELECT)
+        left = len(O.STD_MASKS) + len(O.EXTREMUM_SELECT) + len(O.RELU_MASKS or ())
         O.STD_MASKS = None
         O.EXTREMUM_SELECT = None
+        O.RELU_MASKS = None
         if exc[0] is None:
             assert left == 0, "oracle made fewer aggregator calls than the CUDA path"
             bad = [v for v in O.STD_BAND_VIOLATIONS if v[1] > 0]
             assert not bad, f"Std mask disagreements outside the rounding band: {bad}"
             bad = [v for v in O.EXTREMUM_BAND_VIOLATIONS if v[1] > 0]
             assert not bad, f"min/max routing disagreements outside the rounding band: {bad}"
+            bad = [v for v in O.RELU_BAND_VIOLATIONS if v[1] > 0]
+            assert not bad, f"ReLU sign disagreements outside the rounding band: {bad}"
+            assert sum(v[0] for v in O.RELU_BAND_VIOLATIONS) <= 8, f"too many ReLU sign disagreements: {O.RELU_BAND_VIOLATIONS}"
         return False
