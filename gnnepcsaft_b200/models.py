@@ -38,6 +38,11 @@ def get_conv(config: dict) -> Module:
             in_channels=config["hidden_dim"], out_channels=config["hidden_dim"] // config["heads"],
             heads=config["heads"], concat=True, dropout=config["dropout"], edge_dim=config["hidden_dim"],
             add_self_loops=config["add_self_loops"])
+    if config["conv"] == "Transformer":
+        assert config["hidden_dim"] % config["heads"] == 0, "hidden_dim must be divisible by heads"
+        return gnn.TransformerConv(
+            in_channels=config["hidden_dim"], out_channels=config["hidden_dim"] // config["heads"],
+            heads=config["heads"], concat=True, dropout=config["dropout"], edge_dim=config["hidden_dim"])
     raise ValueError(f"Unsupported convolution: {config['conv']}.")
 
 

@@ -1,7 +1,7 @@
 """Drop-in modules for the PyG / ogb classes the reference model is built from.
 
 Same constructor arguments, ``forward`` signatures, error behaviour and state-dict key names as
-``torch_geometric.nn.{PNAConv, GATv2Conv, BatchNorm}``, ``torch_geometric.nn.aggr.{Sum,Mean,Max}Aggregation``
+``torch_geometric.nn.{PNAConv, GATv2Conv, TransformerConv, BatchNorm}``, ``torch_geometric.nn.aggr.{Sum,Mean,Max}Aggregation``
 and ``ogb.graphproppred.mol_encoder.{AtomEncoder, BondEncoder}`` as used at
 gnnepcsaft/train/models.py:175-184, 441-495, 587-595 -- backed by the sm_100a kernels of libgnnx.
 """
@@ -21,6 +21,7 @@ from .functional import EdgeTable
 from .gat_fn import GATMeta, GATv2ConvFn
 from .graph import GraphIndex, graph_index_for
 from .pna_fn import PNAConvFn, PNAMeta
+from .tconv_fn import TConvMeta, TransformerConvFn
 
 ATOM_FEATURE_DIMS = (119, 5, 12, 12, 10, 6, 6, 2, 2)   # gnnepcsaft/data/ogb_utils.py:9-23
 BOND_FEATURE_DIMS = (5, 6, 2)                           # gnnepcsaft/data/ogb_utils.py:24-33
@@ -286,3 +287,42 @@ class GATv2Conv(Module):
         meta = GATMeta(g, codes, self.heads, self.out_channels, self.negative_slope, self.add_self_loops)
         return GATv2ConvFn.apply(x, efeat, meta, self.lin_l.weight, self.lin_l.bias, self.lin_r.weight,
                                  self.lin_r.bias, self.lin_edge.weight, self.att, self.bias)
+
+
+# ------------------------------------------------------------------ TransformerConv
+class TransformerConv(Module):
+    """``torch_geometric.nn.TransformerConv`` as built by ``get_conv`` (models.py:497-510; the third conv of
+    configs/search_space.py:15): ``concat=True, beta=False, root_weight=True, bias=True`` with edge features."""
+
+    def __init__(self, in_channels: int, out_channels: int, heads: int = 1, concat: bool = True, beta: bool = False,
+                 dropout: float = 0.0, edge_dim: Optional[int] = None, bias: bool = True, root_weight: bool = True,
+                 **kwargs):
+        super().__init__()
+        if not concat or beta or not root_weight or not bias or edge_dim is None:
+            raise NotImplementedError("gnnx TransformerConv implements concat=True, beta=False, root_weight=True, "
+                                      "bias=True with edge features (gnnepcsaft/train/models.py:497-510)")
+        self.in_channels, self.out_channels, self.heads = in_channels, out_channels, heads
+        self.concat, self.beta, self.root_weight = concat, beta, root_weight
+        self.dropout, self.edge_dim = dropout, edge_dim
+        self.lin_key = Linear(in_channels, heads * out_channels)
+        self.lin_query = Linear(in_channels, heads * out_channels)
+        self.lin_value = Linear(in_channels, heads * out_channels)
+        self.lin_edge = Linear(edge_dim, heads * out_channels, bias=False)
+        self.lin_skip = Linear(in_channels, heads * out_channels, bias=bias)
+
+    def reset_parameters(self):
+        for lin in (self.lin_key, self.lin_query, self.lin_value, self.lin_edge, self.lin_skip):
+            lin.reset_parameters()
+
+    def forward(self, x: Tensor, edge_index: Optional[Tensor], edge_attr: Union[Tensor, EdgeTable, None] = None,
+                index: Optional[GraphIndex] = None) -> Tensor:
+        _require_cuda(x, "TransformerConv")
+        if x.dim() != 2 or x.shape[1] != self.in_channels:
+            raise ValueError(f"TransformerConv: x must be [N, {self.in_channels}], got {tuple(x.shape)}")
+        g = index if index is not None else graph_index_for(edge_index, x.shape[0])
+        efeat, codes = _resolve_edges(edge_attr, self.edge_dim, g, "TransformerConv")
+        p = self.dropout if self.training else 0.0           # F.dropout(alpha, p, training) inside the kernel
+        meta = TConvMeta(g, codes, self.heads, self.out_channels, p, ops.dropout_seed() if p > 0.0 else 0)
+        return TransformerConvFn.apply(x, efeat, meta, self.lin_query.weight, self.lin_query.bias, self.lin_key.weight,
+                                       self.lin_key.bias, self.lin_value.weight, self.lin_value.bias,
+                                       self.lin_edge.weight, self.lin_skip.weight, self.lin_skip.bias)

@@ -388,6 +388,52 @@ def gatv2_edge_grad(ds: Tensor, g, hidden: int, self_loops: bool, original_order
     return de
 
 
+# ------------------------------------------------------------------ TransformerConv
+def _eidx_ptrs(eidx: Tensor):
+    if eidx.dtype == torch.int32:
+        return eidx.data_ptr(), None
+    if eidx.dtype == torch.uint8:
+        return None, eidx.data_ptr()
+    raise ValueError("gnnx: edge-term index must be int32 (csr_eid) or uint8 (bond codes)")
+
+
+def dropout_seed() -> int:
+    """A fresh 63-bit seed for an in-kernel dropout draw, taken from torch's CPU generator (so ``torch.manual_seed``
+    makes runs repeatable) without touching the device."""
+    return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
+
+
+def tconv_fwd(qkv: Tensor, e: Tensor, eidx: Tensor, g, heads: int, c: int, skip_out: Tensor, dropout_p: float = 0.0,
+              seed: int = 0):
+    """``skip_out`` holds lin_skip(x) on entry and ``agg + lin_skip(x)`` on return; returns (agg, alpha)."""
+    _chk(qkv, torch.float32, "qkv"); _chk(e, torch.float32, "e"); _chk(skip_out, torch.float32, "skip_out")
+    N, E, H = g.num_nodes, g.num_edges, heads * c
+    agg = torch.empty((N, H), dtype=torch.float32, device=qkv.device)
+    alpha = torch.empty((E, heads), dtype=torch.float32, device=qkv.device)
+    i32, u8 = _eidx_ptrs(eidx)
+    lib().call("gnnx_tconv_fwd", qkv.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, g.rowptr.data_ptr(),
+               g.csr_src.data_ptr(), N, E, heads, c, float(dropout_p), int(seed), skip_out.data_ptr(), agg.data_ptr(),
+               skip_out.data_ptr(), alpha.data_ptr(), _stream())
+    return agg, alpha
+
+
+def tconv_bwd(dout: Tensor, qkv: Tensor, e: Tensor, eidx: Tensor, alpha: Tensor, agg: Tensor, g, heads: int, c: int,
+              original_order: bool, dropout_p: float = 0.0):
+    """Returns (dqkv [N,3H], de [E,H]); de rows in original edge order if ``original_order`` else dst-sorted."""
+    _chk(dout, torch.float32, "dout")
+    N, E, H = g.num_nodes, g.num_edges, heads * c
+    dev = dout.device
+    dqkv = torch.empty((N, 3 * H), dtype=torch.float32, device=dev)
+    ds = torch.empty((E, H), dtype=torch.float32, device=dev)
+    de = torch.empty((E, H), dtype=torch.float32, device=dev)
+    i32, u8 = _eidx_ptrs(eidx)
+    lib().call("gnnx_tconv_bwd", dout.data_ptr(), qkv.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, alpha.data_ptr(),
+               agg.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(), g.csr_eid.data_ptr() if original_order else None,
+               g.colptr.data_ptr(), g.csc_pos.data_ptr(), g.csc_dst.data_ptr(), N, E, heads, c, float(dropout_p),
+               dqkv.data_ptr(), ds.data_ptr(), de.data_ptr(), _stream())
+    return dqkv, de
+
+
 # ------------------------------------------------------------------ loss / optimizer tail
 def relhuber_fwd_bwd(pred: Tensor, target: Tensor, delta: float = 0.01, want_grad: bool = True):
     _chk(pred, torch.float32, "pred"); _chk(target, torch.float32, "target")

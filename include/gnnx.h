@@ -241,6 +241,30 @@ GNNX_API int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const 
                          const int32_t* csr_eid, int64_t num_nodes, int64_t num_edges, int32_t hidden,
                          int32_t self_loops, float* de, void* stream);
 
+/* ------------------------------------------------------------------ TransformerConv attention */
+/* Replaces TransformerConv's message + segment softmax + aggregate (PyG; models.py:497-510, the
+ * third conv of configs/search_space.py:15) with concat=True, beta=False, root_weight=True.
+ * qkv is [N, 3*H] = [lin_query(x) | lin_key(x) | lin_value(x)], H = heads*C; e is the bias-free
+ * lin_edge term, per edge in original order (eidx = csr_eid) or a table indexed by codes.
+ *   logit = <q_i, k_j + e>_h / sqrt(C);  alpha = segment softmax over dst;  agg_i = sum alpha (v_j + e)
+ * agg [N,H] is saved for the backward; out (optional) = agg + skip, and may alias skip.
+ * alpha is [E, heads] in dst-sorted slot order.  dropout_p > 0 applies F.dropout(alpha, p) (training
+ * mode): the draw for (slot, head) is a pure function of (seed, slot, head); alpha keeps the softmax
+ * value and records a dropped entry in its sign bit (stored negated). */
+GNNX_API int gnnx_tconv_fwd(const float* qkv, const float* e, int64_t ld_e, const int32_t* eidx_i32,
+                   const uint8_t* eidx_u8, const int32_t* rowptr, const int32_t* csr_src,
+                   int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float dropout_p,
+                   int64_t seed, const float* skip, float* agg, float* out, float* alpha, void* stream);
+/* Backward of the attention part (dout = gradient at agg).  Outputs: dqkv [N,3H] (fully written),
+ * ds [E,H] scratch (per-slot d k), de [E,H] = gradient at the edge term, rows in ORIGINAL edge
+ * order when csr_eid != null, else dst-sorted slots. */
+GNNX_API int gnnx_tconv_bwd(const float* dout, const float* qkv, const float* e, int64_t ld_e,
+                   const int32_t* eidx_i32, const uint8_t* eidx_u8, const float* alpha, const float* agg,
+                   const int32_t* rowptr, const int32_t* csr_src, const int32_t* csr_eid,
+                   const int32_t* colptr, const int32_t* csc_pos, const int32_t* csc_dst,
+                   int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float dropout_p,
+                   float* dqkv, float* ds, float* de, void* stream);
+
 /* ------------------------------------------------------------------ loss + optimizer tail */
 /* Relative-error Huber(delta) + MAPE of GNNePCSAFTL.training_step (models.py:89-92), fused
  * forward + gradient: out[0] = loss, out[1] = mape, dpred = d loss / d pred. */

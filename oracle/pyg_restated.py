@@ -398,12 +398,26 @@ class GATv2Conv(Module):
         s = F.leaky_relu(s, self.negative_slope)
         alpha = (s * self.att).sum(dim=-1)
         alpha = segment_softmax(alpha, dst, n)
-        alpha = F.dropout(alpha, p=self.dropout, training=self.training)
+        alpha = _attention_dropout(alpha, self.dropout, self.training)
         out = scatter(x_l[src] * alpha.unsqueeze(-1), dst, n, "sum")
         out = out.view(-1, h * c) if self.concat else out.mean(dim=1)
         if self.bias is not None:
             out = out + self.bias
         return out
+
+
+# Test hook for attention dropout: torch's RNG stream cannot be matched by another implementation, so when
+# DROPOUT_KEEP is a list, successive attention layers take their keep-mask ([E', heads] bool, edge order of the
+# oracle) from it instead of drawing one; the arithmetic (zero the dropped entries, scale the rest by 1/(1-p)) is
+# F.dropout's.
+DROPOUT_KEEP = None
+
+
+def _attention_dropout(alpha: Tensor, p: float, training: bool) -> Tensor:
+    if DROPOUT_KEEP is None or not training or p == 0.0:
+        return F.dropout(alpha, p=p, training=training)
+    keep = DROPOUT_KEEP.pop(0).to(alpha.device).view_as(alpha)
+    return alpha * keep.to(alpha.dtype) / (1.0 - p)
 
 
 class TransformerConv(Module):
@@ -433,7 +447,7 @@ class TransformerConv(Module):
             k_j = k_j + e
         alpha = (q_i * k_j).sum(dim=-1) / math.sqrt(c)
         alpha = segment_softmax(alpha, dst, n)
-        alpha = F.dropout(alpha, p=self.dropout, training=self.training)
+        alpha = _attention_dropout(alpha, self.dropout, self.training)
         out = v_j
         if self.lin_edge is not None:
             out = out + e

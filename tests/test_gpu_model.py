@@ -15,7 +15,7 @@ import pytest
 import torch
 
 import gnnepcsaft_b200 as G
-from gnnepcsaft_b200 import graph, nn as gnn, ops, pna_fn
+from gnnepcsaft_b200 import graph, nn as gnn, ops, pna_fn, tconv_fn
 from oracle import pyg_restated as O
 from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_as_accurate, assert_close, deg_hist, make_batch, branches_from
 
@@ -103,6 +103,78 @@ def test_gatv2conv_dense_edge_attr(H, heads, loops):
     _conv_pair(lambda: O.GATv2Conv(**kw), lambda: gnn.GATv2Conv(**kw), b, H)
 
 
+@pytest.mark.parametrize("H,heads", [(64, 2), (64, 8), (256, 2), (256, 1), (128, 4), (512, 2), (48, 3), (1024, 2)])
+def test_transformerconv_dense_edge_attr(H, heads):
+    """TransformerConv as built at models.py:497-510, forward + every gradient."""
+    _, b = make_batch(24, seed=33)
+    kw = dict(in_channels=H, out_channels=H // heads, heads=heads, concat=True, dropout=0.0, edge_dim=H)
+    _conv_pair(lambda: O.TransformerConv(**kw), lambda: gnn.TransformerConv(**kw), b, H)
+
+
+def _keep_mask_original_order(cap):
+    """[E, heads] keep-mask of a captured attention layer, permuted from dst-sorted slots to the input edge order."""
+    alpha, g = cap["alpha"], cap["g"]
+    keep = torch.empty_like(alpha, dtype=torch.bool)
+    keep[g.csr_eid.long()] = ~torch.signbit(alpha)
+    return keep.cpu()
+
+
+@pytest.mark.parametrize("H,heads,p", [(64, 2, 0.25), (256, 2, 0.25), (128, 8, 0.5)])
+def test_transformerconv_attention_dropout(H, heads, p):
+    """Training-mode attention dropout (configs/transformer_msigmae.py:40, dropout 0.25): the kernel's own draw is
+    replayed on the oracle (RNG streams cannot match), then forward and every gradient must agree; the draw is
+    repeatable under torch.manual_seed, differs between calls, and drops about p of the entries."""
+    _, b = make_batch(24, seed=34)
+    kw = dict(in_channels=H, out_channels=H // heads, heads=heads, concat=True, dropout=p, edge_dim=H)
+    torch.manual_seed(0)
+    co = O.TransformerConv(**kw)
+    co64 = copy.deepcopy(co).double()
+    cp = gnn.TransformerConv(**kw).to(DEV)
+    cp.load_state_dict(co.state_dict())
+    co.train(); co64.train(); cp.train()
+    N, E = b["x"].shape[0], b["edge_index"].shape[1]
+    x, ea = torch.randn(N, H), torch.randn(E, H)
+    xo, eo = x.clone().requires_grad_(True), ea.clone().requires_grad_(True)
+    x64, e64 = x.double().requires_grad_(True), ea.double().requires_grad_(True)
+    xp, ep = x.clone().to(DEV).requires_grad_(True), ea.clone().to(DEV).requires_grad_(True)
+    ei = b["edge_index"].to(DEV)
+    tconv_fn.CAPTURE_ALPHA = []
+    try:
+        torch.manual_seed(7)
+        yp = cp(xp, ei, ep)
+        torch.manual_seed(7)
+        yp_again = cp(xp.detach(), ei, ep.detach())
+        yp_other = cp(xp.detach(), ei, ep.detach())
+        caps = list(tconv_fn.CAPTURE_ALPHA)
+    finally:
+        tconv_fn.CAPTURE_ALPHA = None
+    assert torch.equal(yp.detach(), yp_again), "same seed must give the same draw"
+    assert not torch.equal(yp.detach(), yp_other), "successive calls must draw different masks"
+    keep = _keep_mask_original_order(caps[0])
+    frac = 1.0 - float(keep.float().mean())
+    assert abs(frac - p) < 0.05, f"dropped fraction {frac:.3f} vs p={p}"
+    try:
+        O.DROPOUT_KEEP = [keep.clone()]
+        yo = co(xo, b["edge_index"], eo)
+        O.DROPOUT_KEEP = [keep.clone()]
+        y64 = co64(x64, b["edge_index"], e64)
+    finally:
+        O.DROPOUT_KEEP = None
+    assert_as_accurate(yp, yo, y64, "conv fwd (dropout)")
+    assert_close(yp, yo, 1e-5, 1e-6, "conv fwd (dropout)")
+    w = torch.randn_like(yo)
+    (yo * w).sum().backward()
+    (y64 * w.double()).sum().backward()
+    (yp * w.to(DEV)).sum().backward()
+    for got, r32, r64, what in ((xp.grad, xo.grad, x64.grad, "dx"), (ep.grad, eo.grad, e64.grad, "dedge_attr")):
+        assert_as_accurate(got, r32, r64, what)
+        assert_close(got, r32, 1e-4, max(1e-6, 4 * _ref_err(r32, r64)), what)
+    _grads_close(cp, co, co64, 1e-4)
+    cp.eval()
+    with torch.no_grad():
+        assert torch.equal(cp(xp, ei, ep), cp(xp, ei, ep)), "eval mode must not drop anything"
+
+
 def _model_pair(cfg, graphs):
     cfg = dict(cfg, deg=deg_hist(graphs))
     torch.manual_seed(1)
@@ -114,7 +186,9 @@ def _model_pair(cfg, graphs):
 
 @pytest.mark.parametrize("cfg,target", [(PNA_CFG1, "para"), (GAT_CFG_SMALL, "assoc"),
                                         (dict(PNA_CFG1, towers=4, pre_layers=1, post_layers=2, global_pool="mean"), "para"),
-                                        (dict(GAT_CFG_SMALL, heads=8, global_pool="max"), "assoc")])
+                                        (dict(GAT_CFG_SMALL, heads=8, global_pool="max"), "assoc"),
+                                        (dict(GAT_CFG_SMALL, conv="Transformer", num_para=3), "para"),
+                                        (dict(GAT_CFG_SMALL, conv="Transformer", heads=4, global_pool="mean"), "assoc")])
 def test_whole_model_training_step_parity(cfg, target):
     """BASELINE cfg1: fwd + loss + bwd on 32 synthetic ~25-atom graphs, every parameter gradient checked.
 
