@@ -47,6 +47,8 @@ WORKLOADS = {
     "cfg3": dict(conv="GATv2", hidden_dim=256, propagation_depth=7, dropout=0.0, global_pool="add", num_para=2,
                  towers=1, pre_layers=2, post_layers=4, heads=2, add_self_loops=True, model="gnn"),
 }
+WORKLOADS["transformer"] = dict(conv="Transformer", hidden_dim=256, propagation_depth=6, dropout=0.0, global_pool="add",
+                                num_para=3, towers=1, pre_layers=2, post_layers=4, heads=2, add_self_loops=True, model="gnn")
 WORKLOADS["cfg5"] = dict(WORKLOADS["cfg2"])            # bulk screening runs the (m, sigma, epsilon/k) PNA model in eval mode
 INFER_GRAPHS_PER_STEP = 16384
 WORKLOAD_NAMES = {
@@ -54,6 +56,8 @@ WORKLOAD_NAMES = {
             "16384 graphs per step per GPU, shards with no communication (BASELINE configs[4])",
     "cfg2": "PNA hidden 256, 6 layers, training step, 4096 synthetic ~25-atom OGB-featurised graphs per GPU (BASELINE configs[1])",
     "cfg3": "GATv2 hidden 256, heads 2, 7 layers, fwd+bwd+step, 4096 synthetic graphs per GPU (BASELINE configs[2])",
+    "transformer": "TransformerConv hidden 256, heads 2, 6 layers (configs/transformer_msigmae.py shape, dropout 0), training "
+                   "step, 4096 synthetic graphs per GPU (SURVEY 8(f) rank 1)",
 }
 
 
@@ -207,9 +211,17 @@ def _algorithmic_bytes(name, a, N, E, H):
         h = heads * c
         return 4.0 * (e + n) * h + 12.0 * n * h + 4.0 * (e + n) * heads, 0.0
     if name == "gnnx_gatv2_bwd":                  # + dout, dxlr, ds [E+N, H]
-        n, e, heads, c = a[13], a[14], a[15], a[16]
+        n, e, heads, c = a[15], a[16], a[17], a[18]
         h = heads * c
-        return 8.0 * (e + n) * h + 20.0 * n * h + 4.0 * (e + n) * heads, 0.0
+        return 8.0 * (e + n) * h + 24.0 * n * h + 4.0 * (e + n) * heads, 0.0
+    if name == "gnnx_tconv_fwd":                  # qkv [N,3H] read, k_j+v_j per edge slot, skip read, agg + out written
+        n, e, heads, c = a[7], a[8], a[9], a[10]
+        h = heads * c
+        return 8.0 * e * h + 4.0 * n * h * (3 + 1 + 2) + 4.0 * e * heads, 0.0
+    if name == "gnnx_tconv_bwd":                  # + dout, agg read; dqkv [N,3H], ds and de [E,H] written, ds read back once
+        n, e, heads, c = a[14], a[15], a[16], a[17]
+        h = heads * c
+        return 8.0 * e * h + 12.0 * e * h + 4.0 * n * h * (3 + 2 + 3) + 4.0 * e * heads, 0.0
     if name == "gnnx_colsum":
         return 4.0 * a[2] * a[3], 0.0
     return None

@@ -1,354 +1,339 @@
 // GATv2 attention over the dst-sorted CSR: additive attention logits, segment
 // softmax over each destination (online, single gather of x_l[src] per edge), weighted aggregation,
 // self loops synthesised in-kernel (loop edge term = mean of the incoming edge terms, which equals
-// lin_edge(mean(edge_attr)) because lin_edge has no bias), and the matching backward.
-// One warp owns one destination row and all H = heads*C columns (NQ chunks of 128); C is a power of 2.
+// lin_edge(mean(edge_attr)) because lin_edge has no bias), attention dropout, and the matching backward.
+// One warp owns one (destination row, head group) pair (attn.cuh) and gathers two edges per iteration.
 // Deterministic and atomic-free: the only cross-row reduction (d att) goes through ordered partials.
-#include "common.cuh"
+#include "attn.cuh"
 
 namespace gnnx {
-
-union F4 {
-    float4 q;
-    float a[4];
-};
-__device__ __forceinline__ F4 g4(const float* p) { F4 r; r.q = ldg4(p); return r; }
-__device__ __forceinline__ F4 z4() { F4 r; r.q = make_float4(0.f, 0.f, 0.f, 0.f); return r; }
-
-// part[q] (per-lane partial dot products) -> logit of the head that owns columns (q*128 + lane*4 ..)
-template <int NQ>
-__device__ __forceinline__ void head_reduce(float (&part)[NQ], int C) {
-    if (C >= 128) {
-        const int qph = C >> 7;
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) part[q] = warp_sum(part[q]);
-        if (qph > 1) {
-            float tot[NQ];
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                float t = 0.f;
-#pragma unroll
-                for (int p = 0; p < NQ; ++p) t += (p / qph == q / qph) ? part[p] : 0.f;
-                tot[q] = t;
-            }
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) part[q] = tot[q];
-        }
-    } else {
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-            float v = part[q];
-            for (int o = C >> 3; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            part[q] = v;
-        }
-    }
-}
-
-// is this lane the writer for the head owning (q, lane)?  (first lane of the head's first chunk)
-__device__ __forceinline__ bool head_writer(int q, int lane, int C) {
-    int col = q * 128 + lane * 4;
-    return col % C == 0;
-}
 
 template <int NQ, typename EIdx>
 __global__ void __launch_bounds__(256)
 k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
             const float* __restrict__ att, const float* __restrict__ bias, const int* __restrict__ rowptr,
-            const int* __restrict__ csr_src, int N, int E, int heads, int C, float slope, int self_loops,
-            float* __restrict__ out, float* alpha) {
+            const int* __restrict__ csr_src, int N, int E, int heads, int C, int groups, float slope, int self_loops,
+            unsigned int drop_thr, float keep_scale, unsigned long long seed, float* __restrict__ out, float* alpha) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const long long ld = 2ll * H;
-    F4 av[NQ];
-#pragma unroll
-    for (int q = 0; q < NQ; ++q) {
-        int c = q * 128 + lane * 4;
-        av[q] = c < H ? g4(att + c) : z4();
-    }
-    for (int i = blockIdx.x * wpb + (threadIdx.x >> 5); i < N; i += gridDim.x * wpb) {
+    const long long nwork = (long long)N * groups;
+    const int hpw = (NQ > 1 || C >= 128) ? 1 : 128 / C;          // heads per warp
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        const int i = (int)(w / groups);
+        const int cb = (int)(w % groups) * 128 * NQ;
+        const int c0 = cb + lane * 4;
+        const bool act = c0 < H;
+        const int head = act ? c0 / C : 0;
+        const bool writer = act && (NQ > 1 ? lane == 0 : (c0 % C) == 0);
         const int b = rowptr[i], e = rowptr[i + 1];
-        F4 xr[NQ], acc[NQ], esum[NQ];
-        float mx[NQ], den[NQ];
+        F4 xr[NQ], av[NQ], acc[NQ], esum[NQ];
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-            int c = q * 128 + lane * 4;
-            xr[q] = c < H ? g4(xlr + (long long)i * ld + H + c) : z4();
+            const int c = c0 + 128 * q;
+            xr[q] = act ? g4(xlr + (long long)i * ld + H + c) : z4();
+            av[q] = act ? g4(att + c) : z4();
             acc[q] = z4(); esum[q] = z4();
-            mx[q] = -INFINITY; den[q] = 0.f;
         }
+        float mx = -INFINITY, den = 0.f;
         int cnt = 0;
-        const int nslots = (e - b) + (self_loops ? 1 : 0);
-        for (int t = 0; t < nslots; ++t) {
-            const bool is_loop = t == (e - b);
-            int src, slot;
-            if (is_loop) { src = i; slot = E + i; }
-            else {
-                slot = b + t; src = csr_src[slot];
-                if (self_loops && src == i) {            // remove_self_loops
-                    if (lane < heads) alpha[(long long)slot * heads + lane] = 0.f;
-                    continue;
+        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], int slot) {
+            float part = 0.f;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float s = xr[q].a[j] + xl[q].a[j] + ev[q].a[j];
+                    s = s > 0.f ? s : s * slope;
+                    part = fmaf(s, av[q].a[j], part);
                 }
-            }
-            F4 xl[NQ];
-            float part[NQ];
-            const float inv_cnt = 1.f / (float)max(cnt, 1);
+            const float lg = head_sum<NQ>(part, C);
+            if (writer) alpha[(long long)slot * heads + head] = lg;      // raw logit, normalised below
+            const float nm = fmaxf(mx, lg);
+            const float sc = expf(mx - nm);                              // exp(-inf) = 0 on the first edge
+            const float wgt = expf(lg - nm);
+            den = den * sc + wgt;
+            const float wk = (drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr)) ? wgt : 0.f;
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[q].a[j] = acc[q].a[j] * sc + wk * xl[q].a[j];
+            mx = nm;
+        };
+        for (int t = b; t < e; t += 2) {
+            const bool two = t + 1 < e;
+            const int s0 = csr_src[t], s1 = two ? csr_src[t + 1] : s0;
+            const long long r0 = (long long)eidx[t] * ld_e, r1 = two ? (long long)eidx[t + 1] * ld_e : r0;
+            F4 x0[NQ], e0[NQ], x1[NQ], e1[NQ];
 #pragma unroll
             for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                part[q] = 0.f;
-                xl[q] = z4();
-                if (c < H) {
-                    xl[q] = g4(xlr + (long long)src * ld + c);
-                    F4 ev;
-                    if (is_loop) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) ev.a[j] = esum[q].a[j] * inv_cnt;
-                    } else {
-                        ev = g4(ee + (long long)eidx[slot] * ld_e + c);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) esum[q].a[j] += ev.a[j];
-                    }
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        float s = xr[q].a[j] + xl[q].a[j] + ev.a[j];
-                        s = s > 0.f ? s : s * slope;
-                        part[q] = fmaf(s, av[q].a[j], part[q]);
-                    }
+                const int c = c0 + 128 * q;
+                if (act) {
+                    x0[q] = g4(xlr + (long long)s0 * ld + c);
+                    e0[q] = g4(ee + r0 + c);
+                    x1[q] = g4(xlr + (long long)s1 * ld + c);
+                    e1[q] = g4(ee + r1 + c);
+                } else {
+                    x0[q] = e0[q] = x1[q] = e1[q] = z4();
                 }
             }
-            if (!is_loop) ++cnt;
-            head_reduce<NQ>(part, C);
+            if (!(self_loops && s0 == i)) {                              // remove_self_loops
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                if (c < H) {
-                    float lg = part[q];
-                    if (head_writer(q, lane, C)) alpha[(long long)slot * heads + c / C] = lg;   // raw logit for now
-                    float nm = fmaxf(mx[q], lg);
-                    float sc = expf(mx[q] - nm);        // exp(-inf) = 0 on the first edge
-                    float w = expf(lg - nm);
-                    den[q] = den[q] * sc + w;
+                for (int q = 0; q < NQ; ++q)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[q].a[j] = acc[q].a[j] * sc + w * xl[q].a[j];
-                    mx[q] = nm;
-                }
+                    for (int j = 0; j < 4; ++j) esum[q].a[j] += e0[q].a[j];
+                ++cnt;
+                step(x0, e0, t);
+            }
+            if (two && !(self_loops && s1 == i)) {
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) esum[q].a[j] += e1[q].a[j];
+                ++cnt;
+                step(x1, e1, t + 1);
             }
         }
-        // normalise: out = acc / (den + 1e-16) + bias ; alpha = exp(lg - mx) / (den + 1e-16)
+        if (self_loops) {                                                // the i -> i edge, edge term = mean of the row's
+            const float inv_cnt = 1.f / (float)max(cnt, 1);
+            F4 xl[NQ], ev[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                xl[q] = act ? g4(xlr + (long long)i * ld + c0 + 128 * q) : z4();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) ev[q].a[j] = esum[q].a[j] * inv_cnt;
+            }
+            step(xl, ev, E + i);
+        }
+        // out = acc / (den + 1e-16) + bias
+        const float inv = 1.f / (den + 1e-16f);
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-            int c = q * 128 + lane * 4;
-            if (c < H) {
-                float inv = 1.f / (den[q] + 1e-16f);
+            const int c = c0 + 128 * q;
+            if (act) {
                 F4 o, bv = bias ? g4(bias + c) : z4();
 #pragma unroll
-                for (int j = 0; j < 4; ++j) o.a[j] = acc[q].a[j] * inv + bv.a[j];
+                for (int j = 0; j < 4; ++j) o.a[j] = acc[q].a[j] * (inv * keep_scale) + bv.a[j];
                 stg4(out + (long long)i * H + c, o.q);
-                if (head_writer(q, lane, C)) {
-                    int hd = c / C;
-                    for (int t = 0; t < nslots; ++t) {
-                        int slot = t == (e - b) ? E + i : b + t;
-                        if (t < (e - b) && self_loops && csr_src[slot] == i) continue;
-                        float* ap = alpha + (long long)slot * heads + hd;
-                        *ap = expf(*ap - mx[q]) * inv;
-                    }
-                }
+            }
+        }
+        // alpha = exp(logit - max) / (sum + 1e-16): lanes spread over the (slot, head) pairs of this group
+        __syncwarp();
+        const int nreal = e - b;
+        const int npairs = (nreal + (self_loops ? 1 : 0)) * hpw;
+        for (int base = 0; base < npairs; base += 32) {
+            const int idx = base + lane;
+            const int hl = idx % hpw, t = idx / hpw;
+            const int from = (hl * (C >> 2)) & 31;
+            const float hmx = __shfl_sync(0xffffffffu, mx, from), hinv = __shfl_sync(0xffffffffu, inv, from);
+            const int hd = cb / C + hl;
+            if (idx < npairs && hd < heads) {
+                const int slot = t < nreal ? b + t : E + i;
+                float* ap = alpha + (long long)slot * heads + hd;
+                if (t < nreal && self_loops && csr_src[slot] == i) { *ap = 0.f; continue; }     // removed self loop
+                const float a = expf(*ap - hmx) * hinv;
+                const bool keep = drop_thr == 0u || attn_keep(seed, (long long)slot * heads + hd, drop_thr);
+                *ap = keep ? a : -a;
             }
         }
     }
 }
 
-// Backward, destination side.  Writes ds rows (gradient at the pre-activation s) for every slot,
-// dxlr[:, H:2H] (= d x_r), and per-block partial sums of d att.
+// Backward, destination side.  Writes ds rows (gradient at the pre-activation s) for every slot, dxlr[:, H:2H]
+// (= d x_r), and per-warp partial sums of d att.  S_h = sum_e alpha'_e <dout_i, x_l[src_e]>_h is <dout_i, out_i - bias>_h.
+// A warp keeps one head group for its whole life (rows advance by total_warps / groups), so d att accumulates in registers.
 template <int NQ, typename EIdx>
 __global__ void __launch_bounds__(256)
-k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e,
-                const EIdx* __restrict__ eidx, const float* __restrict__ att, const float* __restrict__ alpha,
-                const int* __restrict__ rowptr, const int* __restrict__ csr_src, int N, int E, int heads, int C,
-                float slope, int self_loops, float* __restrict__ dxlr, float* __restrict__ ds,
-                float* __restrict__ datt_partial) {
-    extern __shared__ float sh_datt[];        // [warps][H]
+k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ bias,
+                const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
+                const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,
+                const int* __restrict__ csr_src, int N, int E, int heads, int C, int groups, float slope, int self_loops,
+                float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
     const int wpb = blockDim.x >> 5;
     const long long ld = 2ll * H;
-    F4 av[NQ], datt[NQ];
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);
+    const int row_stride = (gridDim.x * wpb) / groups;           // host guarantees divisibility
+    const int cb = (gw % groups) * 128 * NQ;
+    const int c0 = cb + lane * 4;
+    const bool act = c0 < H;
+    const int head = act ? c0 / C : 0;
+    F4 av[NQ], datt[NQ], bv[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-        int c = q * 128 + lane * 4;
-        av[q] = c < H ? g4(att + c) : z4();
+        const int c = c0 + 128 * q;
+        av[q] = act ? g4(att + c) : z4();
+        bv[q] = (act && bias) ? g4(bias + c) : z4();
         datt[q] = z4();
     }
-    for (int i = blockIdx.x * wpb + warp; i < N; i += gridDim.x * wpb) {
+    for (int i = gw / groups; i < N; i += row_stride) {
         const int b = rowptr[i], e = rowptr[i + 1];
-        const int nslots = (e - b) + (self_loops ? 1 : 0);
         F4 xr[NQ], go[NQ], dxr[NQ], esum[NQ];
-        float S[NQ];
+        float sp = 0.f;
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-            int c = q * 128 + lane * 4;
-            xr[q] = c < H ? g4(xlr + (long long)i * ld + H + c) : z4();
-            go[q] = c < H ? g4(dout + (long long)i * H + c) : z4();
+            const int c = c0 + 128 * q;
+            xr[q] = act ? g4(xlr + (long long)i * ld + H + c) : z4();
+            go[q] = act ? g4(dout + (long long)i * H + c) : z4();
+            const F4 o = act ? g4(out + (long long)i * H + c) : z4();
             dxr[q] = z4(); esum[q] = z4();
-            S[q] = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) sp = fmaf(go[q].a[j], o.a[j] - bv[q].a[j], sp);
         }
-        // pass 1: S_h = sum_e alpha_e * <dout_i, x_l[src_e]>_h
-        for (int t = 0; t < nslots; ++t) {
-            const bool is_loop = t == (e - b);
-            int slot = is_loop ? E + i : b + t;
-            int src = is_loop ? i : csr_src[slot];
-            if (!is_loop && self_loops && src == i) continue;
-            float part[NQ];
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                part[q] = 0.f;
-                if (c < H) {
-                    F4 xl = g4(xlr + (long long)src * ld + c);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) part[q] = fmaf(go[q].a[j], xl.a[j], part[q]);
-                }
-            }
-            head_reduce<NQ>(part, C);
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                if (c < H) S[q] += alpha[(long long)slot * heads + c / C] * part[q];
-            }
-        }
-        // pass 2: d logit, d s, accumulate d x_r / d att; loop slot last (needs the mean edge term)
+        const float S = head_sum<NQ>(sp, C);
         int cnt = 0;
-        for (int t = 0; t < nslots; ++t) {
-            const bool is_loop = t == (e - b);
-            int slot = is_loop ? E + i : b + t;
-            int src = is_loop ? i : csr_src[slot];
-            if (!is_loop && self_loops && src == i) {
+        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], float stored, int slot) {
+            float part = 0.f;
 #pragma unroll
-                for (int q = 0; q < NQ; ++q) {
-                    int c = q * 128 + lane * 4;
-                    if (c < H) stg4(ds + (long long)slot * H + c, make_float4(0.f, 0.f, 0.f, 0.f));
+            for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) part = fmaf(go[q].a[j], xl[q].a[j], part);
+            const float kf = attn_dropped(stored) ? 0.f : keep_scale;
+            const float dlg = fabsf(stored) * (kf * head_sum<NQ>(part, C) - S);
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                F4 d;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float s = xr[q].a[j] + xl[q].a[j] + ev[q].a[j];
+                    const float a = s > 0.f ? s : s * slope;
+                    datt[q].a[j] = fmaf(dlg, a, datt[q].a[j]);
+                    d.a[j] = dlg * av[q].a[j] * (s > 0.f ? 1.f : slope);
+                    dxr[q].a[j] += d.a[j];
                 }
-                continue;
+                if (act) stg4(ds + (long long)slot * H + c0 + 128 * q, d.q);
             }
+        };
+        auto zero_slot = [&](int slot) {
+#pragma unroll
+            for (int q = 0; q < NQ; ++q)
+                if (act) stg4(ds + (long long)slot * H + c0 + 128 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+        };
+        for (int t = b; t < e; t += 2) {
+            const bool two = t + 1 < e;
+            const int s0 = csr_src[t], s1 = two ? csr_src[t + 1] : s0;
+            const long long r0 = (long long)eidx[t] * ld_e, r1 = two ? (long long)eidx[t + 1] * ld_e : r0;
+            const float a0 = alpha[(long long)t * heads + head];
+            const float a1 = two ? alpha[(long long)(t + 1) * heads + head] : 0.f;
+            F4 x0[NQ], e0[NQ], x1[NQ], e1[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                const int c = c0 + 128 * q;
+                if (act) {
+                    x0[q] = g4(xlr + (long long)s0 * ld + c);
+                    e0[q] = g4(ee + r0 + c);
+                    x1[q] = g4(xlr + (long long)s1 * ld + c);
+                    e1[q] = g4(ee + r1 + c);
+                } else {
+                    x0[q] = e0[q] = x1[q] = e1[q] = z4();
+                }
+            }
+            if (!(self_loops && s0 == i)) {
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) esum[q].a[j] += e0[q].a[j];
+                ++cnt;
+                step(x0, e0, a0, t);
+            } else {
+                zero_slot(t);
+            }
+            if (two) {
+                if (!(self_loops && s1 == i)) {
+#pragma unroll
+                    for (int q = 0; q < NQ; ++q)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) esum[q].a[j] += e1[q].a[j];
+                    ++cnt;
+                    step(x1, e1, a1, t + 1);
+                } else {
+                    zero_slot(t + 1);
+                }
+            }
+        }
+        if (self_loops) {
             const float inv_cnt = 1.f / (float)max(cnt, 1);
-            F4 sv[NQ];
-            float part[NQ];
+            const float al = alpha[(long long)(E + i) * heads + head];
+            F4 xl[NQ], ev[NQ];
 #pragma unroll
             for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                part[q] = 0.f;
-                sv[q] = z4();
-                if (c < H) {
-                    F4 xl = g4(xlr + (long long)src * ld + c);
-                    F4 ev;
-                    if (is_loop) {
+                xl[q] = act ? g4(xlr + (long long)i * ld + c0 + 128 * q) : z4();
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) ev.a[j] = esum[q].a[j] * inv_cnt;
-                    } else {
-                        ev = g4(ee + (long long)eidx[slot] * ld_e + c);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) esum[q].a[j] += ev.a[j];
-                    }
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        sv[q].a[j] = xr[q].a[j] + xl.a[j] + ev.a[j];
-                        part[q] = fmaf(go[q].a[j], xl.a[j], part[q]);
-                    }
-                }
+                for (int j = 0; j < 4; ++j) ev[q].a[j] = esum[q].a[j] * inv_cnt;
             }
-            if (!is_loop) ++cnt;
-            head_reduce<NQ>(part, C);     // d alpha for this lane's heads
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                if (c < H) {
-                    float a = alpha[(long long)slot * heads + c / C];
-                    float dlg = a * (part[q] - S[q]);
-                    F4 d;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        float s = sv[q].a[j];
-                        float act = s > 0.f ? s : s * slope;
-                        datt[q].a[j] = fmaf(dlg, act, datt[q].a[j]);
-                        d.a[j] = dlg * av[q].a[j] * (s > 0.f ? 1.f : slope);
-                        dxr[q].a[j] += d.a[j];
-                    }
-                    stg4(ds + (long long)slot * H + c, d.q);
-                }
-            }
+            step(xl, ev, al, E + i);
         }
 #pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-            int c = q * 128 + lane * 4;
-            if (c < H) stg4(dxlr + (long long)i * ld + H + c, dxr[q].q);
-        }
+        for (int q = 0; q < NQ; ++q)
+            if (act) stg4(dxlr + (long long)i * ld + H + c0 + 128 * q, dxr[q].q);
     }
-    // ordered block reduction of d att
 #pragma unroll
-    for (int q = 0; q < NQ; ++q) {
-        int c = q * 128 + lane * 4;
-        if (c < H) stg4(sh_datt + warp * H + c, datt[q].q);
-    }
-    __syncthreads();
-    for (int c = threadIdx.x; c < H; c += blockDim.x) {
-        float s = 0.f;
-        for (int w = 0; w < wpb; ++w) s += sh_datt[w * H + c];
-        datt_partial[(long long)blockIdx.x * H + c] = s;
-    }
+    for (int q = 0; q < NQ; ++q)
+        stg4(datt_partial + (long long)gw * (128 * NQ) + q * 128 + lane * 4, datt[q].q);
 }
 
-// Backward, source side: dxlr[j, 0:H] = sum_{edges j->i} (ds[pos] + alpha[pos] * dout[i]) + loop term
-template <int NQ>
+// datt[c] = sum over the warps that owned column c's head group, in warp order; one warp per column
+__global__ void k_gatv2_datt_final(const float* __restrict__ partial, int total_warps, int groups, int width, int H,
+                                   float* __restrict__ datt) {
+    const int lane = threadIdx.x & 31;
+    const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (c >= H) return;
+    const int grp = c / width, off = c % width;
+    float s = 0.f;
+    for (int gw = grp + lane * groups; gw < total_warps; gw += 32 * groups) s += partial[(long long)gw * width + off];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) datt[c] = s;
+}
+
+// Backward, source side: dxlr[j, 0:H] = sum_{edges j->i} (ds[pos] + alpha'[pos] * dout[i]) + loop term.
+// Warp per (source row, 128-column chunk), two out-edges per iteration.
 __global__ void __launch_bounds__(256)
 k_gatv2_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, const float* __restrict__ alpha,
-                const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csr_dst_of_pos,
-                int N, int E, int heads, int C, int self_loops, float* __restrict__ dxlr) {
+                const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csc_dst, int N,
+                int E, int heads, int C, int self_loops, float keep_scale, float* __restrict__ dxlr) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
+    const int chunks = (H + 127) / 128;
     const long long ld = 2ll * H;
-    for (int j = blockIdx.x * wpb + (threadIdx.x >> 5); j < N; j += gridDim.x * wpb) {
-        F4 acc[NQ];
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) acc[q] = z4();
+    const long long nwork = (long long)N * chunks;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        const int j = (int)(w / chunks);
+        const int c = (int)(w % chunks) * 128 + lane * 4;
+        if (c >= H) continue;
+        const int head = c / C;
         const int b = colptr[j], e = colptr[j + 1];
-        const int nslots = (e - b) + (self_loops ? 1 : 0);
-        for (int t = 0; t < nslots; ++t) {
-            const bool is_loop = t == (e - b);
-            int pos, dst;
-            if (is_loop) { pos = E + j; dst = j; }
-            else {
-                pos = csc_pos[b + t]; dst = csr_dst_of_pos[b + t];
-                if (self_loops && dst == j) continue;
+        F4 acc = z4();
+        auto add = [&](int pos, int dst) {
+            const F4 d = g4(ds + (long long)pos * H + c), g = g4(dout + (long long)dst * H + c);
+            const float r = alpha[(long long)pos * heads + head];
+            const float a = attn_dropped(r) ? 0.f : r * keep_scale;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) acc.a[jj] += fmaf(a, g.a[jj], d.a[jj]);
+        };
+        for (int p = b; p < e; p += 2) {
+            const bool two = p + 1 < e;
+            const int p0 = csc_pos[p], d0 = csc_dst[p];
+            const int p1 = two ? csc_pos[p + 1] : p0, d1 = two ? csc_dst[p + 1] : d0;
+            const F4 x0 = g4(ds + (long long)p0 * H + c), g0 = g4(dout + (long long)d0 * H + c);
+            const F4 x1 = g4(ds + (long long)p1 * H + c), g1 = g4(dout + (long long)d1 * H + c);
+            const float r0 = alpha[(long long)p0 * heads + head], r1 = alpha[(long long)p1 * heads + head];
+            const float a0 = attn_dropped(r0) ? 0.f : r0 * keep_scale, a1 = attn_dropped(r1) ? 0.f : r1 * keep_scale;
+            if (!(self_loops && d0 == j)) {
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) acc.a[jj] += fmaf(a0, g0.a[jj], x0.a[jj]);
             }
+            if (two && !(self_loops && d1 == j)) {
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                int c = q * 128 + lane * 4;
-                if (c < H) {
-                    F4 d = g4(ds + (long long)pos * H + c);
-                    F4 g = g4(dout + (long long)dst * H + c);
-                    float a = alpha[(long long)pos * heads + c / C];
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) acc[q].a[jj] += d.a[jj] + a * g.a[jj];
-                }
+                for (int jj = 0; jj < 4; ++jj) acc.a[jj] += fmaf(a1, g1.a[jj], x1.a[jj]);
             }
         }
-#pragma unroll
-        for (int q = 0; q < NQ; ++q) {
-            int c = q * 128 + lane * 4;
-            if (c < H) stg4(dxlr + (long long)j * ld + c, acc[q].q);
-        }
+        if (self_loops) add(E + j, j);
+        stg4(dxlr + (long long)j * ld + c, acc.q);
     }
-}
-
-__global__ void k_sum_rows(const float* __restrict__ partial, int nrows, int H, float* __restrict__ out) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= H) return;
-    float s = 0.f;
-    for (int r = 0; r < nrows; ++r) s += partial[(long long)r * H + c];
-    out[c] = s;
 }
 
 // de[slot or eid] = ds[slot] + ds[loop(dst)] / deg(dst); warp per destination row
@@ -387,72 +372,81 @@ k_gatv2_edge_grad(const float* __restrict__ ds, const int* __restrict__ rowptr, 
     }
 }
 
-static int gat_grid(int64_t N) {
-    long long blocks = (N + 7) / 8;
-    long long cap = (long long)kNumSMs * 8;
-    return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
-}
-
-static bool pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
-
 }  // namespace gnnx
 
 using namespace gnnx;
 
-#define GAT_DISPATCH_NQ(H, CALL)                                              \
-    do {                                                                      \
-        int _nq = ((H) + 127) / 128;                                          \
-        if (_nq <= 1) { CALL(1); }                                            \
-        else if (_nq <= 2) { CALL(2); }                                       \
-        else if (_nq <= 4) { CALL(4); }                                       \
-        else { CALL(8); }                                                     \
+#define GAT_DISPATCH(S, CALL)                                                \
+    do {                                                                     \
+        if ((S).nq == 1) { CALL(1); }                                        \
+        else if ((S).nq == 2) { CALL(2); }                                   \
+        else if ((S).nq == 4) { CALL(4); }                                   \
+        else { CALL(8); }                                                    \
     } while (0)
+
+// destination-side backward grid: a multiple of `groups` blocks so that every warp keeps one head group
+static int gat_bwd_grid(int64_t N, int groups) {
+    long long blocks = ((long long)N * groups + 7) / 8;
+    long long cap = (long long)kNumSMs * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)((blocks + groups - 1) / groups * groups);
+}
 
 extern "C" {
 
 int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t* eidx_i32, const uint8_t* eidx_u8,
                    const float* att, const float* bias, const int32_t* rowptr, const int32_t* csr_src, int64_t N, int64_t E,
-                   int32_t heads, int32_t C, float slope, int32_t self_loops, float* out, float* alpha, void* stream) {
-    const int H = heads * C;
-    GNNX_REQUIRE(pow2(C) && C >= 4 && heads >= 1 && heads <= 32 && H <= 1024, "gatv2_fwd: need C a power of two >= 4, heads <= 32, heads*C <= 1024");
+                   int32_t heads, int32_t C, float slope, int32_t self_loops, float dropout_p, int64_t seed, float* out,
+                   float* alpha, void* stream) {
+    GNNX_REQUIRE(attn_shape_ok(heads, C), "gatv2_fwd: need C a power of two in [4, 1024] and heads*C <= 4096");
+    GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "gatv2_fwd: dropout_p must be in [0, 1)");
     GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_fwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ld_e % 4 == 0, "gatv2_fwd: ld_e must be a multiple of 4");
     if (N == 0) return GNNX_OK;
+    const AttnShape s = attn_shape(heads, C);
     cudaStream_t st = as_stream(stream);
-    int grid = gat_grid(N);
+    const int grid = attn_grid(N * s.groups);
+    const unsigned int thr = attn_drop_threshold(dropout_p);
+    const float ks = 1.0f / (1.0f - dropout_p);
+    const unsigned long long sd = (unsigned long long)seed;
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_fwd<NQ, int><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, slope, self_loops, out, alpha); \
-    else k_gatv2_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, slope, self_loops, out, alpha)
-    GAT_DISPATCH_NQ(H, CALL);
+    if (eidx_i32) k_gatv2_fwd<NQ, int><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
+    else k_gatv2_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, thr, ks, sd, out, alpha)
+    GAT_DISPATCH(s, CALL);
 #undef CALL
     return check_launch("gatv2_fwd");
 }
 
 size_t gnnx_gatv2_bwd_workspace_bytes(int64_t N, int64_t E, int32_t heads, int32_t C) {
     (void)E;
-    return (size_t)gat_grid(N) * heads * C * sizeof(float);
+    if (!attn_shape_ok(heads, C)) return 0;
+    const AttnShape s = attn_shape(heads, C);
+    return (size_t)gat_bwd_grid(N, s.groups) * 8 * 128 * s.nq * sizeof(float);
 }
 
-int gnnx_gatv2_bwd(const float* dout, const float* xlr, const float* e, int64_t ld_e, const int32_t* eidx_i32,
-                   const uint8_t* eidx_u8, const float* att, const float* alpha, const int32_t* rowptr, const int32_t* csr_src,
-                   const int32_t* colptr, const int32_t* csc_pos, const int32_t* csc_dst, int64_t N, int64_t E, int32_t heads,
-                   int32_t C, float slope, int32_t self_loops, float* dxlr, float* datt, float* ds, void* ws, size_t ws_bytes,
-                   void* stream) {
+int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const float* xlr, const float* e, int64_t ld_e,
+                   const int32_t* eidx_i32, const uint8_t* eidx_u8, const float* att, const float* alpha,
+                   const int32_t* rowptr, const int32_t* csr_src, const int32_t* colptr, const int32_t* csc_pos,
+                   const int32_t* csc_dst, int64_t N, int64_t E, int32_t heads, int32_t C, float slope, int32_t self_loops,
+                   float dropout_p, float* dxlr, float* datt, float* ds, void* ws, size_t ws_bytes, void* stream) {
     const int H = heads * C;
-    GNNX_REQUIRE(pow2(C) && C >= 4 && heads >= 1 && heads <= 32 && H <= 1024, "gatv2_bwd: need C a power of two >= 4, heads <= 32, heads*C <= 1024");
+    GNNX_REQUIRE(attn_shape_ok(heads, C), "gatv2_bwd: need C a power of two in [4, 1024] and heads*C <= 4096");
+    GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "gatv2_bwd: dropout_p must be in [0, 1)");
     GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_bwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ws_bytes >= gnnx_gatv2_bwd_workspace_bytes(N, E, heads, C), "gatv2_bwd: workspace too small");
     cudaStream_t st = as_stream(stream);
     if (N == 0) { GNNX_CUDA(cudaMemsetAsync(datt, 0, H * sizeof(float), st)); return GNNX_OK; }
-    int grid = gat_grid(N);
-    size_t smem = (size_t)8 * H * sizeof(float);
+    const AttnShape s = attn_shape(heads, C);
+    const int grid = gat_bwd_grid(N, s.groups);
+    const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_bwd_dst<NQ, int><<<grid, 256, smem, st>>>(dout, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, slope, self_loops, dxlr, ds, (float*)ws); \
-    else k_gatv2_bwd_dst<NQ, uint8_t><<<grid, 256, smem, st>>>(dout, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, slope, self_loops, dxlr, ds, (float*)ws); \
-    k_gatv2_bwd_src<NQ><<<grid, 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, self_loops, dxlr)
-    GAT_DISPATCH_NQ(H, CALL);
+    if (eidx_i32) k_gatv2_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
+    else k_gatv2_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
+    GAT_DISPATCH(s, CALL);
 #undef CALL
-    k_sum_rows<<<ceil_div(H, 128), 128, 0, st>>>((const float*)ws, grid, H, datt);
+    k_gatv2_bwd_src<<<attn_grid(N * ((H + 127) / 128)), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, self_loops, ks, dxlr);
+    k_gatv2_datt_final<<<ceil_div(H, 8), 256, 0, st>>>((const float*)ws, grid * 8, s.groups, 128 * s.nq, H, datt);
     return check_launch("gatv2_bwd", 3);
 }
 

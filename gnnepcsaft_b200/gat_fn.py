@@ -10,11 +10,17 @@ from . import ops
 from .functional import _c
 
 
-class GATMeta:
-    __slots__ = ("g", "codes", "heads", "c", "slope", "self_loops")
+# Debug tap: when set to a list, every forward appends dict(alpha [E + N, heads] -- dst-sorted slots then loop slots,
+# a negative sign marks an entry removed by attention dropout --, g) so tests can replay the draw on the oracle.
+CAPTURE_ALPHA = None
 
-    def __init__(self, g, codes, heads, c, slope, self_loops):
+
+class GATMeta:
+    __slots__ = ("g", "codes", "heads", "c", "slope", "self_loops", "dropout_p", "seed")
+
+    def __init__(self, g, codes, heads, c, slope, self_loops, dropout_p=0.0, seed=0):
         self.g, self.codes, self.heads, self.c, self.slope, self.self_loops = g, codes, heads, c, slope, self_loops
+        self.dropout_p, self.seed = dropout_p, seed
 
 
 class GATv2ConvFn(Function):
@@ -32,10 +38,13 @@ class GATv2ConvFn(Function):
         e = ops.gemm(efeat, wedge, trans_b=True)                  # [E or 60, H], lin_edge has no bias
         eidx = meta.codes if meta.codes is not None else g.csr_eid
         att_flat = att.reshape(-1)
-        out, alpha = ops.gatv2_fwd(xlr, e, eidx, att_flat, bias, g, heads, c, meta.slope, meta.self_loops)
+        out, alpha = ops.gatv2_fwd(xlr, e, eidx, att_flat, bias, g, heads, c, meta.slope, meta.self_loops,
+                                   meta.dropout_p, meta.seed)
+        if CAPTURE_ALPHA is not None:
+            CAPTURE_ALPHA.append(dict(alpha=alpha, g=g))
         ctx.meta = meta
         ctx.has = (bl is not None, br is not None, bias is not None)
-        ctx.save_for_backward(x, efeat, xlr, e, alpha, wl, wr, wedge, att)
+        ctx.save_for_backward(x, efeat, xlr, e, alpha, wl, wr, wedge, att, out, bias)
         return out
 
     @staticmethod
@@ -44,11 +53,11 @@ class GATv2ConvFn(Function):
         meta: GATMeta = ctx.meta
         g, heads, c = meta.g, meta.heads, meta.c
         H = heads * c
-        x, efeat, xlr, e, alpha, wl, wr, wedge, att = ctx.saved_tensors
+        x, efeat, xlr, e, alpha, wl, wr, wedge, att, out, bias = ctx.saved_tensors
         dout = _c(dout)
         eidx = meta.codes if meta.codes is not None else g.csr_eid
-        dxlr, datt, ds = ops.gatv2_bwd(dout, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
-                                       meta.self_loops)
+        dxlr, datt, ds = ops.gatv2_bwd(dout, out, bias, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
+                                       meta.self_loops, meta.dropout_p)
         dl, dr = dxlr[:, :H], dxlr[:, H:]
         dx = None
         if ctx.needs_input_grad[0]:

@@ -280,11 +280,11 @@ class GATv2Conv(Module):
         _require_cuda(x, "GATv2Conv")
         if x.dim() != 2 or x.shape[1] != self.in_channels:
             raise ValueError(f"GATv2Conv: x must be [N, {self.in_channels}], got {tuple(x.shape)}")
-        if self.training and self.dropout > 0.0:
-            raise NotImplementedError("gnnx GATv2Conv: attention dropout > 0 in training mode is not implemented yet")
         g = index if index is not None else graph_index_for(edge_index, x.shape[0])
         efeat, codes = _resolve_edges(edge_attr, self.edge_dim, g, "GATv2Conv")
-        meta = GATMeta(g, codes, self.heads, self.out_channels, self.negative_slope, self.add_self_loops)
+        p = self.dropout if self.training else 0.0           # F.dropout(alpha, p, training) inside the kernel
+        meta = GATMeta(g, codes, self.heads, self.out_channels, self.negative_slope, self.add_self_loops, p,
+                       ops.dropout_seed() if p > 0.0 else 0)
         return GATv2ConvFn.apply(x, efeat, meta, self.lin_l.weight, self.lin_l.bias, self.lin_r.weight,
                                  self.lin_r.bias, self.lin_edge.weight, self.att, self.bias)
 

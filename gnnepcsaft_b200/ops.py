@@ -348,7 +348,7 @@ def segment_pool_bwd(dout: Tensor, x: Tensor, out: Tensor, graph_ptr: Tensor, mo
 
 # ------------------------------------------------------------------ GATv2
 def gatv2_fwd(xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, bias: Optional[Tensor], g, heads: int, c: int,
-              slope: float, self_loops: bool):
+              slope: float, self_loops: bool, dropout_p: float = 0.0, seed: int = 0):
     _chk(xlr, torch.float32, "xlr"); _chk(e, torch.float32, "e"); _chk(att, torch.float32, "att")
     N, E, H = g.num_nodes, g.num_edges, heads * c
     out = torch.empty((N, H), dtype=torch.float32, device=xlr.device)
@@ -356,13 +356,13 @@ def gatv2_fwd(xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, bias: Optional[
     i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
     u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
     lib().call("gnnx_gatv2_fwd", xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, att.data_ptr(), _p(bias),
-               g.rowptr.data_ptr(), g.csr_src.data_ptr(), N, E, heads, c, float(slope), int(self_loops), out.data_ptr(),
-               alpha.data_ptr(), _stream())
+               g.rowptr.data_ptr(), g.csr_src.data_ptr(), N, E, heads, c, float(slope), int(self_loops), float(dropout_p),
+               int(seed), out.data_ptr(), alpha.data_ptr(), _stream())
     return out, alpha
 
 
-def gatv2_bwd(dout: Tensor, xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, alpha: Tensor, g, heads: int, c: int,
-              slope: float, self_loops: bool):
+def gatv2_bwd(dout: Tensor, out: Tensor, bias: Optional[Tensor], xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor,
+              alpha: Tensor, g, heads: int, c: int, slope: float, self_loops: bool, dropout_p: float = 0.0):
     _chk(dout, torch.float32, "dout")
     N, E, H = g.num_nodes, g.num_edges, heads * c
     dev = dout.device
@@ -372,10 +372,11 @@ def gatv2_bwd(dout: Tensor, xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, a
     i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
     u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
     ws, nb = _ws(_query("gnnx_gatv2_bwd_workspace_bytes", N, E, heads, c), dev)
-    lib().call("gnnx_gatv2_bwd", dout.data_ptr(), xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8, att.data_ptr(),
+    lib().call("gnnx_gatv2_bwd", dout.data_ptr(), out.data_ptr(), _p(bias), xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8,
+               att.data_ptr(),
                alpha.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(), g.colptr.data_ptr(), g.csc_pos.data_ptr(),
-               g.csc_dst.data_ptr(), N, E, heads, c, float(slope), int(self_loops), dxlr.data_ptr(), datt.data_ptr(),
-               ds.data_ptr(), _p(ws), nb, _stream())
+               g.csc_dst.data_ptr(), N, E, heads, c, float(slope), int(self_loops), float(dropout_p), dxlr.data_ptr(),
+               datt.data_ptr(), ds.data_ptr(), _p(ws), nb, _stream())
     return dxlr, datt, ds
 
 

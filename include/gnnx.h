@@ -218,23 +218,27 @@ GNNX_API int gnnx_segment_pool_bwd(const float* dout, const float* x, const floa
  * [E,H] in original order (eidx = csr_eid) or a table indexed by codes.  self_loops != 0 adds
  * the i->i edge whose edge term is the mean of the incoming e rows (fill_value='mean' through
  * the bias-free lin_edge); edges with src == dst are dropped first (remove_self_loops).
- * alpha is [E + N, heads] (dst-sorted slots, then loop slots) and is saved for the backward. */
+ * alpha is [E + N, heads] (dst-sorted slots, then loop slots) and is saved for the backward.
+ * dropout_p > 0 applies F.dropout(alpha, p) (training mode) with the draw of (slot, head) a pure
+ * function of (seed, slot, head); a dropped entry is recorded in alpha's sign bit (stored negated). */
 GNNX_API int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t* eidx_i32,
                    const uint8_t* eidx_u8, const float* att, const float* bias, const int32_t* rowptr,
                    const int32_t* csr_src, int64_t num_nodes, int64_t num_edges, int32_t heads,
-                   int32_t c, float negative_slope, int32_t self_loops, float* out, float* alpha,
-                   void* stream);
-/* Backward.  Outputs: dxlr [N,2H] (fully written), datt [heads*C], ds [E+N, H] = gradient
- * at the pre-activation s (dst-sorted slots then loop slots); the caller derives d(lin_edge)
- * from ds.  workspace: gnnx_gatv2_bwd_workspace_bytes(). */
+                   int32_t c, float negative_slope, int32_t self_loops, float dropout_p, int64_t seed,
+                   float* out, float* alpha, void* stream);
+/* Backward.  out / bias are the forward's output and bias (out - bias is the aggregate the
+ * softmax backward needs).  Outputs: dxlr [N,2H] (fully written), datt [heads*C], ds [E+N, H] =
+ * gradient at the pre-activation s (dst-sorted slots then loop slots); the caller derives
+ * d(lin_edge) from ds.  workspace: gnnx_gatv2_bwd_workspace_bytes(). */
 GNNX_API size_t gnnx_gatv2_bwd_workspace_bytes(int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c);
-GNNX_API int gnnx_gatv2_bwd(const float* dout, const float* xlr, const float* e, int64_t ld_e,
+GNNX_API int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const float* xlr,
+                   const float* e, int64_t ld_e,
                    const int32_t* eidx_i32, const uint8_t* eidx_u8, const float* att,
                    const float* alpha, const int32_t* rowptr, const int32_t* csr_src,
                    const int32_t* colptr, const int32_t* csc_pos, const int32_t* csc_dst,
                    int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float negative_slope,
-                   int32_t self_loops, float* dxlr, float* datt, float* ds, void* workspace,
-                   size_t workspace_bytes, void* stream);
+                   int32_t self_loops, float dropout_p, float* dxlr, float* datt, float* ds,
+                   void* workspace, size_t workspace_bytes, void* stream);
 /* de rows for the edge term from ds: de[slot] = ds[slot] + ds[loop(dst)] / deg(dst) (the loop's
  * mean fan-out), written in ORIGINAL edge order when csr_eid != null, else dst-sorted. */
 GNNX_API int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* csr_src,

@@ -15,7 +15,7 @@ import pytest
 import torch
 
 import gnnepcsaft_b200 as G
-from gnnepcsaft_b200 import graph, nn as gnn, ops, pna_fn, tconv_fn
+from gnnepcsaft_b200 import gat_fn, graph, nn as gnn, ops, pna_fn, tconv_fn
 from oracle import pyg_restated as O
 from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_as_accurate, assert_close, deg_hist, make_batch, branches_from
 
@@ -111,25 +111,35 @@ def test_transformerconv_dense_edge_attr(H, heads):
     _conv_pair(lambda: O.TransformerConv(**kw), lambda: gnn.TransformerConv(**kw), b, H)
 
 
-def _keep_mask_original_order(cap):
-    """[E, heads] keep-mask of a captured attention layer, permuted from dst-sorted slots to the input edge order."""
+def _keep_mask_original_order(cap, loops=False):
+    """Keep-mask of a captured attention layer in the oracle's edge order: the E real edges permuted from dst-sorted
+    slots back to input order, then (GATv2 with self loops) the N loop slots, which both sides append last."""
     alpha, g = cap["alpha"], cap["g"]
+    E = g.num_edges
     keep = torch.empty_like(alpha, dtype=torch.bool)
-    keep[g.csr_eid.long()] = ~torch.signbit(alpha)
-    return keep.cpu()
+    keep[g.csr_eid.long()] = ~torch.signbit(alpha[:E])
+    keep[E:] = ~torch.signbit(alpha[E:])
+    return (keep if loops else keep[:E]).cpu()           # without self loops the loop slots of alpha are unused
 
 
-@pytest.mark.parametrize("H,heads,p", [(64, 2, 0.25), (256, 2, 0.25), (128, 8, 0.5)])
-def test_transformerconv_attention_dropout(H, heads, p):
-    """Training-mode attention dropout (configs/transformer_msigmae.py:40, dropout 0.25): the kernel's own draw is
-    replayed on the oracle (RNG streams cannot match), then forward and every gradient must agree; the draw is
-    repeatable under torch.manual_seed, differs between calls, and drops about p of the entries."""
+@pytest.mark.parametrize("conv,H,heads,p", [("Transformer", 64, 2, 0.25), ("Transformer", 256, 2, 0.25),
+                                            ("Transformer", 128, 8, 0.5), ("GATv2", 64, 2, 0.25), ("GATv2", 256, 2, 0.25),
+                                            ("GATv2", 256, 1, 0.1), ("GATv2noloops", 128, 4, 0.5)])
+def test_attention_dropout(conv, H, heads, p):
+    """Training-mode attention dropout (configs/transformer_msigmae.py:40, gatv2_assoc_2.py:41: dropout 0.25): the
+    kernel's own draw is replayed on the oracle (RNG streams cannot match), then forward and every gradient must
+    agree; the draw is repeatable under torch.manual_seed, differs between calls, and drops about p of the entries."""
     _, b = make_batch(24, seed=34)
     kw = dict(in_channels=H, out_channels=H // heads, heads=heads, concat=True, dropout=p, edge_dim=H)
     torch.manual_seed(0)
-    co = O.TransformerConv(**kw)
+    if conv == "Transformer":
+        mod, make_o, make_p = tconv_fn, O.TransformerConv, gnn.TransformerConv
+    else:
+        kw["add_self_loops"] = conv == "GATv2"
+        mod, make_o, make_p = gat_fn, O.GATv2Conv, gnn.GATv2Conv
+    co = make_o(**kw)
     co64 = copy.deepcopy(co).double()
-    cp = gnn.TransformerConv(**kw).to(DEV)
+    cp = make_p(**kw).to(DEV)
     cp.load_state_dict(co.state_dict())
     co.train(); co64.train(); cp.train()
     N, E = b["x"].shape[0], b["edge_index"].shape[1]
@@ -138,19 +148,19 @@ def test_transformerconv_attention_dropout(H, heads, p):
     x64, e64 = x.double().requires_grad_(True), ea.double().requires_grad_(True)
     xp, ep = x.clone().to(DEV).requires_grad_(True), ea.clone().to(DEV).requires_grad_(True)
     ei = b["edge_index"].to(DEV)
-    tconv_fn.CAPTURE_ALPHA = []
+    mod.CAPTURE_ALPHA = []
     try:
         torch.manual_seed(7)
         yp = cp(xp, ei, ep)
         torch.manual_seed(7)
         yp_again = cp(xp.detach(), ei, ep.detach())
         yp_other = cp(xp.detach(), ei, ep.detach())
-        caps = list(tconv_fn.CAPTURE_ALPHA)
+        caps = list(mod.CAPTURE_ALPHA)
     finally:
-        tconv_fn.CAPTURE_ALPHA = None
+        mod.CAPTURE_ALPHA = None
     assert torch.equal(yp.detach(), yp_again), "same seed must give the same draw"
     assert not torch.equal(yp.detach(), yp_other), "successive calls must draw different masks"
-    keep = _keep_mask_original_order(caps[0])
+    keep = _keep_mask_original_order(caps[0], loops=conv == "GATv2")
     frac = 1.0 - float(keep.float().mean())
     assert abs(frac - p) < 0.05, f"dropped fraction {frac:.3f} vs p={p}"
     try:
