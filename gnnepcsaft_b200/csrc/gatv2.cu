@@ -9,7 +9,7 @@
 namespace gnnx {
 
 template <int NQ, typename EIdx>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
             const float* __restrict__ att, const float* __restrict__ bias, const int* __restrict__ rowptr,
             const int* __restrict__ csr_src, int N, int E, int heads, int C, int groups, float slope, int self_loops,
@@ -20,25 +20,40 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
     const long long ld = 2ll * H;
     const long long nwork = (long long)N * groups;
     const int hpw = (NQ > 1 || C >= 128) ? 1 : 128 / C;          // heads per warp
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+    const int lph = 32 / hpw;                                    // lanes per head
+    const int lih = lane & (lph - 1);                            // lane index inside its head
+    const long long wstride = (long long)gridDim.x * wpb;
+    long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5);
+    int nb = 0, ne = 0;
+    if (w < nwork) { const int i0 = (int)(w / groups); nb = rowptr[i0]; ne = rowptr[i0 + 1]; }
+    for (; w < nwork; w += wstride) {
         const int i = (int)(w / groups);
         const int cb = (int)(w % groups) * 128 * NQ;
         const int c0 = cb + lane * 4;
         const bool act = c0 < H;
         const int head = act ? c0 / C : 0;
         const bool writer = act && (NQ > 1 ? lane == 0 : (c0 % C) == 0);
-        const int b = rowptr[i], e = rowptr[i + 1];
-        F4 xr[NQ], av[NQ], acc[NQ], esum[NQ];
+        const int b = nb, e = ne;
+        if (w + wstride < nwork) {                               // next item's row bounds: latency hidden behind this item
+            const int in = (int)((w + wstride) / groups);
+            nb = rowptr[in]; ne = rowptr[in + 1];
+        }
+        const int nreal = e - b;
+        const int nslots = nreal + (self_loops ? 1 : 0);
+        const bool spill = nslots > lph;                         // logits kept in registers (lane t of a head <- slot t) unless
+        float mylg = 0.f;                                        // the row has more slots than a head has lanes
+        F4 xr[NQ], av[NQ], acc[NQ], esum[NQ], xself[NQ];
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
             const int c = c0 + 128 * q;
             xr[q] = act ? g4(xlr + (long long)i * ld + H + c) : z4();
+            xself[q] = (act && self_loops) ? g4(xlr + (long long)i * ld + c) : z4();
             av[q] = act ? g4(att + c) : z4();
             acc[q] = z4(); esum[q] = z4();
         }
         float mx = -INFINITY, den = 0.f;
         int cnt = 0;
-        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], int slot) {
+        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], int slot, int tt) {
             float part = 0.f;
 #pragma unroll
             for (int q = 0; q < NQ; ++q)
@@ -49,7 +64,8 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
                     part = fmaf(s, av[q].a[j], part);
                 }
             const float lg = head_sum<NQ>(part, C);
-            if (writer) alpha[(long long)slot * heads + head] = lg;      // raw logit, normalised below
+            if (spill) { if (writer) alpha[(long long)slot * heads + head] = lg; }      // raw logit, normalised below
+            else if (lih == tt) mylg = lg;
             const float nm = fmaxf(mx, lg);
             const float sc = expf(mx - nm);                              // exp(-inf) = 0 on the first edge
             const float wgt = expf(lg - nm);
@@ -84,27 +100,31 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
 #pragma unroll
                     for (int j = 0; j < 4; ++j) esum[q].a[j] += e0[q].a[j];
                 ++cnt;
-                step(x0, e0, t);
+                step(x0, e0, t, t - b);
+            } else if (!spill && lih == t - b) {
+                mylg = INFINITY;                                         // marks a removed edge: alpha = 0
             }
-            if (two && !(self_loops && s1 == i)) {
+            if (two) {
+                if (!(self_loops && s1 == i)) {
 #pragma unroll
-                for (int q = 0; q < NQ; ++q)
+                    for (int q = 0; q < NQ; ++q)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) esum[q].a[j] += e1[q].a[j];
-                ++cnt;
-                step(x1, e1, t + 1);
+                        for (int j = 0; j < 4; ++j) esum[q].a[j] += e1[q].a[j];
+                    ++cnt;
+                    step(x1, e1, t + 1, t + 1 - b);
+                } else if (!spill && lih == t + 1 - b) {
+                    mylg = INFINITY;
+                }
             }
         }
         if (self_loops) {                                                // the i -> i edge, edge term = mean of the row's
             const float inv_cnt = 1.f / (float)max(cnt, 1);
-            F4 xl[NQ], ev[NQ];
+            F4 ev[NQ];
 #pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                xl[q] = act ? g4(xlr + (long long)i * ld + c0 + 128 * q) : z4();
+            for (int q = 0; q < NQ; ++q)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) ev[q].a[j] = esum[q].a[j] * inv_cnt;
-            }
-            step(xl, ev, E + i);
+            step(xself, ev, E + i, nreal);
         }
         // out = acc / (den + 1e-16) + bias
         const float inv = 1.f / (den + 1e-16f);
@@ -118,10 +138,21 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
                 stg4(out + (long long)i * H + c, o.q);
             }
         }
-        // alpha = exp(logit - max) / (sum + 1e-16): lanes spread over the (slot, head) pairs of this group
-        __syncwarp();
-        const int nreal = e - b;
-        const int npairs = (nreal + (self_loops ? 1 : 0)) * hpw;
+        // alpha = exp(logit - max) / (sum + 1e-16), negated where attention dropout removed the entry
+        if (!spill) {
+            if (act && lih < nslots) {
+                const int slot = lih < nreal ? b + lih : E + i;
+                float a = 0.f;
+                if (mylg != INFINITY) {
+                    a = expf(mylg - mx) * inv;
+                    if (!(drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr))) a = -a;
+                }
+                alpha[(long long)slot * heads + head] = a;
+            }
+            continue;
+        }
+        __syncwarp();                                            // long rows: lanes spread over the (slot, head) pairs
+        const int npairs = nslots * hpw;
         for (int base = 0; base < npairs; base += 32) {
             const int idx = base + lane;
             const int hl = idx % hpw, t = idx / hpw;
@@ -144,7 +175,7 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
 // (= d x_r), and per-warp partial sums of d att.  S_h = sum_e alpha'_e <dout_i, x_l[src_e]>_h is <dout_i, out_i - bias>_h.
 // A warp keeps one head group for its whole life (rows advance by total_warps / groups), so d att accumulates in registers.
 template <int NQ, typename EIdx>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ bias,
                 const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
                 const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,

@@ -9,7 +9,7 @@
 namespace gnnx {
 
 template <int NQ, typename EIdx>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
             const int* __restrict__ rowptr, const int* __restrict__ csr_src, int N, int heads, int C, int groups,
             float scale, unsigned int drop_thr, float keep_scale, unsigned long long seed, const float* skip,
@@ -20,14 +20,27 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
     const long long ld = 3ll * H;
     const long long nwork = (long long)N * groups;
     const int hpw = (NQ > 1 || C >= 128) ? 1 : 128 / C;          // heads per warp
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+    const int lph = 32 / hpw;                                    // lanes per head
+    const int lih = lane & (lph - 1);                            // lane index inside its head
+    const long long wstride = (long long)gridDim.x * wpb;
+    long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5);
+    int nb = 0, ne = 0;
+    if (w < nwork) { const int i0 = (int)(w / groups); nb = rowptr[i0]; ne = rowptr[i0 + 1]; }
+    for (; w < nwork; w += wstride) {
         const int i = (int)(w / groups);
         const int cb = (int)(w % groups) * 128 * NQ;
         const int c0 = cb + lane * 4;
         const bool act = c0 < H;
         const int head = act ? c0 / C : 0;
         const bool writer = act && (NQ > 1 ? lane == 0 : (c0 % C) == 0);
-        const int b = rowptr[i], e = rowptr[i + 1];
+        const int b = nb, e = ne;
+        if (w + wstride < nwork) {                               // next item's row bounds: latency hidden behind this item
+            const int in = (int)((w + wstride) / groups);
+            nb = rowptr[in]; ne = rowptr[in + 1];
+        }
+        const int nslots = e - b;
+        const bool spill = nslots > lph;                         // logits stay in registers (lane t of a head <- slot t)
+        float mylg = 0.f;                                        // unless the row has more slots than a head has lanes
         F4 qv[NQ], acc[NQ];
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
@@ -44,7 +57,8 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
 #pragma unroll
                 for (int j = 0; j < 4; ++j) part = fmaf(qv[q].a[j], k[q].a[j] + ev[q].a[j], part);
             const float lg = head_sum<NQ>(part, C);
-            if (writer) alpha[(long long)slot * heads + head] = lg;      // raw logit, normalised below
+            if (spill) { if (writer) alpha[(long long)slot * heads + head] = lg; }      // raw logit, normalised below
+            else if (lih == slot - b) mylg = lg;
             const float nm = fmaxf(mx, lg);
             const float sc = expf(mx - nm);                              // exp(-inf) = 0 on the first edge
             const float wgt = expf(lg - nm);
@@ -96,9 +110,18 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
                 }
             }
         }
-        // alpha = exp(logit - max) / (sum + 1e-16): lanes spread over the (slot, head) pairs of this group
-        __syncwarp();
-        const int npairs = (e - b) * hpw;
+        // alpha = exp(logit - max) / (sum + 1e-16), negated where attention dropout removed the entry
+        if (!spill) {
+            if (act && lih < nslots) {
+                const int slot = b + lih;
+                float a = expf(mylg - mx) * inv;
+                if (!(drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr))) a = -a;
+                alpha[(long long)slot * heads + head] = a;
+            }
+            continue;
+        }
+        __syncwarp();                                            // long rows: lanes spread over the (slot, head) pairs
+        const int npairs = nslots * hpw;
         for (int base = 0; base < npairs; base += 32) {
             const int idx = base + lane;
             const int hl = idx % hpw, t = idx / hpw;
@@ -118,7 +141,7 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
 // Backward, destination side: dq rows, and per slot dk (= d logit * q / sqrt(C)) and the edge-term gradient
 // de = dk + alpha * dout_i.  S_h = sum_e alpha_e <dout_i, v_j + e_e>_h equals <dout_i, agg_i>_h, so no extra pass.
 template <int NQ, typename EIdx>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_tconv_bwd_dst(const float* __restrict__ dout, const float* __restrict__ qkv, const float* __restrict__ ee, long long ld_e,
                 const EIdx* __restrict__ eidx, const float* __restrict__ alpha, const float* __restrict__ agg,
                 const int* __restrict__ rowptr, const int* __restrict__ csr_src, const int* __restrict__ csr_eid, int N,
