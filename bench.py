@@ -209,19 +209,19 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name == "gnnx_gatv2_fwd":                  # xlr [N,2H] read once, x_l[src] per edge slot (+ self loops), out written, alpha written
         n, e, heads, c = a[9], a[10], a[11], a[12]
         h = heads * c
-        return 4.0 * (e + n) * h + 12.0 * n * h + 4.0 * (e + n) * heads, 0.0
-    if name == "gnnx_gatv2_bwd":                  # + dout, dxlr, ds [E+N, H]
+        return 4.0 * (e + n) * h + 8.0 * n * h + 4.0 * (e + n) * heads, 0.0          # SURVEY 8(d) B_gat with the 60-row table
+    if name == "gnnx_gatv2_bwd":                  # per slot: x_l[src] and dout[dst] gathers, ds written + read back; per node: dout, out, x_r, dxlr
         n, e, heads, c = a[15], a[16], a[17], a[18]
         h = heads * c
-        return 8.0 * (e + n) * h + 24.0 * n * h + 4.0 * (e + n) * heads, 0.0
-    if name == "gnnx_tconv_fwd":                  # qkv [N,3H] read, k_j+v_j per edge slot, skip read, agg + out written
+        return 16.0 * (e + n) * h + 20.0 * n * h + 8.0 * (e + n) * heads, 0.0
+    if name == "gnnx_tconv_fwd":                  # k_j, v_j gathered per edge slot; q, skip read and agg, out written per node
         n, e, heads, c = a[7], a[8], a[9], a[10]
         h = heads * c
-        return 8.0 * e * h + 4.0 * n * h * (3 + 1 + 2) + 4.0 * e * heads, 0.0
-    if name == "gnnx_tconv_bwd":                  # + dout, agg read; dqkv [N,3H], ds and de [E,H] written, ds read back once
+        return 8.0 * e * h + 16.0 * n * h + 4.0 * e * heads, 0.0
+    if name == "gnnx_tconv_bwd":                  # per slot: k_j, v_j, dout[dst] gathers, ds + de written, ds read back; per node: dout, q, agg, dqkv
         n, e, heads, c = a[14], a[15], a[16], a[17]
         h = heads * c
-        return 8.0 * e * h + 12.0 * e * h + 4.0 * n * h * (3 + 2 + 3) + 4.0 * e * heads, 0.0
+        return 24.0 * e * h + 24.0 * n * h + 8.0 * e * heads, 0.0
     if name == "gnnx_colsum":
         return 4.0 * a[2] * a[3], 0.0
     return None

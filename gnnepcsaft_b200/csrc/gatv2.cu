@@ -12,31 +12,29 @@ template <int NQ, typename EIdx>
 __global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
             const float* __restrict__ att, const float* __restrict__ bias, const int* __restrict__ rowptr,
-            const int* __restrict__ csr_src, int N, int E, int heads, int C, int groups, float slope, int self_loops,
-            unsigned int drop_thr, float keep_scale, unsigned long long seed, float* __restrict__ out, float* alpha) {
+            const int* __restrict__ csr_src, int N, int E, int heads, int C, int log2c, int groups, float slope,
+            int self_loops, unsigned int drop_thr, float keep_scale, unsigned long long seed, float* __restrict__ out, float* alpha) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const long long ld = 2ll * H;
-    const long long nwork = (long long)N * groups;
     const int hpw = (NQ > 1 || C >= 128) ? 1 : 128 / C;          // heads per warp
     const int lph = 32 / hpw;                                    // lanes per head
     const int lih = lane & (lph - 1);                            // lane index inside its head
-    const long long wstride = (long long)gridDim.x * wpb;
-    long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5);
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // this warp's head group never changes: no index
+    const int row_stride = (gridDim.x * wpb) / groups;           // division in the row loop (host: warps % groups == 0)
+    const int cb = (gw % groups) * 128 * NQ;
+    const int c0 = cb + lane * 4;
+    const bool act = c0 < H;
+    const int head = act ? c0 >> log2c : 0;
+    const bool writer = act && (NQ > 1 ? lane == 0 : (c0 & (C - 1)) == 0);
+    int i = gw / groups;
     int nb = 0, ne = 0;
-    if (w < nwork) { const int i0 = (int)(w / groups); nb = rowptr[i0]; ne = rowptr[i0 + 1]; }
-    for (; w < nwork; w += wstride) {
-        const int i = (int)(w / groups);
-        const int cb = (int)(w % groups) * 128 * NQ;
-        const int c0 = cb + lane * 4;
-        const bool act = c0 < H;
-        const int head = act ? c0 / C : 0;
-        const bool writer = act && (NQ > 1 ? lane == 0 : (c0 % C) == 0);
+    if (i < N) { nb = rowptr[i]; ne = rowptr[i + 1]; }
+    for (; i < N; i += row_stride) {
         const int b = nb, e = ne;
-        if (w + wstride < nwork) {                               // next item's row bounds: latency hidden behind this item
-            const int in = (int)((w + wstride) / groups);
-            nb = rowptr[in]; ne = rowptr[in + 1];
+        if (i + row_stride < N) {                                // next row's bounds: latency hidden behind this row
+            nb = rowptr[i + row_stride]; ne = rowptr[i + row_stride + 1];
         }
         const int nreal = e - b;
         const int nslots = nreal + (self_loops ? 1 : 0);
@@ -66,9 +64,11 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
             const float lg = head_sum<NQ>(part, C);
             if (spill) { if (writer) alpha[(long long)slot * heads + head] = lg; }      // raw logit, normalised below
             else if (lih == tt) mylg = lg;
+            const float dl = lg - mx;                                    // one of the two rescale factors is exp(0):
+            const float ex = expf(-fabsf(dl));                           // a single exp (dl = +inf on the first edge -> 0)
             const float nm = fmaxf(mx, lg);
-            const float sc = expf(mx - nm);                              // exp(-inf) = 0 on the first edge
-            const float wgt = expf(lg - nm);
+            const float sc = dl > 0.f ? ex : 1.f;
+            const float wgt = dl > 0.f ? 1.f : ex;
             den = den * sc + wgt;
             const float wk = (drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr)) ? wgt : 0.f;
 #pragma unroll
@@ -158,7 +158,7 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
             const int hl = idx % hpw, t = idx / hpw;
             const int from = (hl * (C >> 2)) & 31;
             const float hmx = __shfl_sync(0xffffffffu, mx, from), hinv = __shfl_sync(0xffffffffu, inv, from);
-            const int hd = cb / C + hl;
+            const int hd = (cb >> log2c) + hl;
             if (idx < npairs && hd < heads) {
                 const int slot = t < nreal ? b + t : E + i;
                 float* ap = alpha + (long long)slot * heads + hd;
@@ -179,8 +179,8 @@ __global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ bias,
                 const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
                 const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,
-                const int* __restrict__ csr_src, int N, int E, int heads, int C, int groups, float slope, int self_loops,
-                float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial) {
+                const int* __restrict__ csr_src, int N, int E, int heads, int C, int log2c, int groups, float slope,
+                int self_loops, float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -190,7 +190,7 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
     const int cb = (gw % groups) * 128 * NQ;
     const int c0 = cb + lane * 4;
     const bool act = c0 < H;
-    const int head = act ? c0 / C : 0;
+    const int head = act ? c0 >> log2c : 0;
     F4 av[NQ], datt[NQ], bv[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
@@ -324,18 +324,18 @@ __global__ void k_gatv2_datt_final(const float* __restrict__ partial, int total_
 __global__ void __launch_bounds__(256)
 k_gatv2_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, const float* __restrict__ alpha,
                 const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csc_dst, int N,
-                int E, int heads, int C, int self_loops, float keep_scale, float* __restrict__ dxlr) {
+                int E, int heads, int C, int log2c, int self_loops, float keep_scale, float* __restrict__ dxlr) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const int chunks = (H + 127) / 128;
     const long long ld = 2ll * H;
-    const long long nwork = (long long)N * chunks;
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
-        const int j = (int)(w / chunks);
-        const int c = (int)(w % chunks) * 128 + lane * 4;
-        if (c >= H) continue;
-        const int head = c / C;
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // fixed column chunk per warp, rows strided
+    const int row_stride = (gridDim.x * wpb) / chunks;           // host guarantees divisibility
+    const int c = (gw % chunks) * 128 + lane * 4;
+    if (c >= H) return;
+    const int head = c >> log2c;
+    for (int j = gw / chunks; j < N; j += row_stride) {
         const int b = colptr[j], e = colptr[j + 1];
         F4 acc = z4();
         auto add = [&](int pos, int dst) {
@@ -415,14 +415,7 @@ using namespace gnnx;
         else { CALL(8); }                                                    \
     } while (0)
 
-// destination-side backward grid: a multiple of `groups` blocks so that every warp keeps one head group
-static int gat_bwd_grid(int64_t N, int groups) {
-    long long blocks = ((long long)N * groups + 7) / 8;
-    long long cap = (long long)kNumSMs * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return (int)((blocks + groups - 1) / groups * groups);
-}
+static int gat_bwd_grid(int64_t N, int groups) { return attn_row_grid(N, groups, 8); }
 
 extern "C" {
 
@@ -437,13 +430,13 @@ int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t
     if (N == 0) return GNNX_OK;
     const AttnShape s = attn_shape(heads, C);
     cudaStream_t st = as_stream(stream);
-    const int grid = attn_grid(N * s.groups);
+    const int grid = attn_row_grid(N, s.groups, 16);
     const unsigned int thr = attn_drop_threshold(dropout_p);
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_fwd<NQ, int><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
-    else k_gatv2_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, thr, ks, sd, out, alpha)
+    if (eidx_i32) k_gatv2_fwd<NQ, int><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
+    else k_gatv2_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha)
     GAT_DISPATCH(s, CALL);
 #undef CALL
     return check_launch("gatv2_fwd");
@@ -472,11 +465,11 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     const int grid = gat_bwd_grid(N, s.groups);
     const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
-    else k_gatv2_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
+    if (eidx_i32) k_gatv2_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
+    else k_gatv2_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
     GAT_DISPATCH(s, CALL);
 #undef CALL
-    k_gatv2_bwd_src<<<attn_grid(N * ((H + 127) / 128)), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, self_loops, ks, dxlr);
+    k_gatv2_bwd_src<<<attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);
     k_gatv2_datt_final<<<ceil_div(H, 8), 256, 0, st>>>((const float*)ws, grid * 8, s.groups, 128 * s.nq, H, datt);
     return check_launch("gatv2_bwd", 3);
 }

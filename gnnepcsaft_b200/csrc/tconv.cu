@@ -11,32 +11,30 @@ namespace gnnx {
 template <int NQ, typename EIdx>
 __global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
-            const int* __restrict__ rowptr, const int* __restrict__ csr_src, int N, int heads, int C, int groups,
+            const int* __restrict__ rowptr, const int* __restrict__ csr_src, int N, int heads, int C, int log2c, int groups,
             float scale, unsigned int drop_thr, float keep_scale, unsigned long long seed, const float* skip,
             float* __restrict__ agg, float* out, float* alpha) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const long long ld = 3ll * H;
-    const long long nwork = (long long)N * groups;
     const int hpw = (NQ > 1 || C >= 128) ? 1 : 128 / C;          // heads per warp
     const int lph = 32 / hpw;                                    // lanes per head
     const int lih = lane & (lph - 1);                            // lane index inside its head
-    const long long wstride = (long long)gridDim.x * wpb;
-    long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5);
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // this warp's head group never changes: no index
+    const int row_stride = (gridDim.x * wpb) / groups;           // division in the row loop (host: warps % groups == 0)
+    const int cb = (gw % groups) * 128 * NQ;
+    const int c0 = cb + lane * 4;
+    const bool act = c0 < H;
+    const int head = act ? c0 >> log2c : 0;
+    const bool writer = act && (NQ > 1 ? lane == 0 : (c0 & (C - 1)) == 0);
+    int i = gw / groups;
     int nb = 0, ne = 0;
-    if (w < nwork) { const int i0 = (int)(w / groups); nb = rowptr[i0]; ne = rowptr[i0 + 1]; }
-    for (; w < nwork; w += wstride) {
-        const int i = (int)(w / groups);
-        const int cb = (int)(w % groups) * 128 * NQ;
-        const int c0 = cb + lane * 4;
-        const bool act = c0 < H;
-        const int head = act ? c0 / C : 0;
-        const bool writer = act && (NQ > 1 ? lane == 0 : (c0 % C) == 0);
+    if (i < N) { nb = rowptr[i]; ne = rowptr[i + 1]; }
+    for (; i < N; i += row_stride) {
         const int b = nb, e = ne;
-        if (w + wstride < nwork) {                               // next item's row bounds: latency hidden behind this item
-            const int in = (int)((w + wstride) / groups);
-            nb = rowptr[in]; ne = rowptr[in + 1];
+        if (i + row_stride < N) {                                // next row's bounds: latency hidden behind this row
+            nb = rowptr[i + row_stride]; ne = rowptr[i + row_stride + 1];
         }
         const int nslots = e - b;
         const bool spill = nslots > lph;                         // logits stay in registers (lane t of a head <- slot t)
@@ -59,9 +57,11 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
             const float lg = head_sum<NQ>(part, C);
             if (spill) { if (writer) alpha[(long long)slot * heads + head] = lg; }      // raw logit, normalised below
             else if (lih == slot - b) mylg = lg;
+            const float dl = lg - mx;                                    // one of the two rescale factors is exp(0):
+            const float ex = expf(-fabsf(dl));                           // a single exp (dl = +inf on the first edge -> 0)
             const float nm = fmaxf(mx, lg);
-            const float sc = expf(mx - nm);                              // exp(-inf) = 0 on the first edge
-            const float wgt = expf(lg - nm);
+            const float sc = dl > 0.f ? ex : 1.f;
+            const float wgt = dl > 0.f ? 1.f : ex;
             den = den * sc + wgt;
             const float wk = (drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr)) ? wgt : 0.f;
 #pragma unroll
@@ -127,7 +127,7 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
             const int hl = idx % hpw, t = idx / hpw;
             const int from = (hl * (C >> 2)) & 31;
             const float hmx = __shfl_sync(0xffffffffu, mx, from), hinv = __shfl_sync(0xffffffffu, inv, from);
-            const int hd = cb / C + hl;
+            const int hd = (cb >> log2c) + hl;
             if (idx < npairs && hd < heads) {
                 float* ap = alpha + (long long)(b + t) * heads + hd;
                 const float a = expf(*ap - hmx) * hinv;
@@ -145,20 +145,24 @@ __global__ void __launch_bounds__(256, NQ == 1 ? 4 : (NQ == 2 ? 2 : 1))
 k_tconv_bwd_dst(const float* __restrict__ dout, const float* __restrict__ qkv, const float* __restrict__ ee, long long ld_e,
                 const EIdx* __restrict__ eidx, const float* __restrict__ alpha, const float* __restrict__ agg,
                 const int* __restrict__ rowptr, const int* __restrict__ csr_src, const int* __restrict__ csr_eid, int N,
-                int heads, int C, int groups, float scale, float keep_scale, float* __restrict__ dqkv,
+                int heads, int C, int log2c, int groups, float scale, float keep_scale, float* __restrict__ dqkv,
                 float* __restrict__ ds, float* __restrict__ de) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const long long ld = 3ll * H;
-    const long long nwork = (long long)N * groups;
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
-        const int i = (int)(w / groups);
-        const int cb = (int)(w % groups) * 128 * NQ;
-        const int c0 = cb + lane * 4;
-        const bool act = c0 < H;
-        const int head = act ? c0 / C : 0;
-        const int b = rowptr[i], e = rowptr[i + 1];
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);
+    const int row_stride = (gridDim.x * wpb) / groups;           // host guarantees divisibility
+    const int cb = (gw % groups) * 128 * NQ;
+    const int c0 = cb + lane * 4;
+    const bool act = c0 < H;
+    const int head = act ? c0 >> log2c : 0;
+    int i = gw / groups;
+    int nb = 0, ne = 0;
+    if (i < N) { nb = rowptr[i]; ne = rowptr[i + 1]; }
+    for (; i < N; i += row_stride) {
+        const int b = nb, e = ne;
+        if (i + row_stride < N) { nb = rowptr[i + row_stride]; ne = rowptr[i + row_stride + 1]; }
         F4 go[NQ], qv[NQ], dq[NQ];
         float sp = 0.f;
 #pragma unroll
@@ -236,18 +240,18 @@ k_tconv_bwd_dst(const float* __restrict__ dout, const float* __restrict__ qkv, c
 __global__ void __launch_bounds__(256)
 k_tconv_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, const float* __restrict__ alpha,
                 const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csc_dst, int N,
-                int heads, int C, float keep_scale, float* __restrict__ dqkv) {
+                int heads, int C, int log2c, float keep_scale, float* __restrict__ dqkv) {
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     const int chunks = (H + 127) / 128;
     const long long ld = 3ll * H;
-    const long long nwork = (long long)N * chunks;
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
-        const int j = (int)(w / chunks);
-        const int c = (int)(w % chunks) * 128 + lane * 4;
-        if (c >= H) continue;
-        const int head = c / C;
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // fixed column chunk per warp, rows strided
+    const int row_stride = (gridDim.x * wpb) / chunks;           // host guarantees divisibility
+    const int c = (gw % chunks) * 128 + lane * 4;
+    if (c >= H) return;
+    const int head = c >> log2c;
+    for (int j = gw / chunks; j < N; j += row_stride) {
         const int b = colptr[j], e = colptr[j + 1];
         F4 dk = z4(), dv = z4();
         for (int p = b; p < e; p += 2) {
@@ -303,13 +307,13 @@ int gnnx_tconv_fwd(const float* qkv, const float* e, int64_t ld_e, const int32_t
     const AttnShape s = attn_shape(heads, C);
     const float scale = 1.0f / sqrtf((float)C);
     cudaStream_t st = as_stream(stream);
-    const int grid = attn_grid(N * s.groups);
+    const int grid = attn_row_grid(N, s.groups, 16);
     const unsigned int thr = attn_drop_threshold(dropout_p);
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
 #define CALL(NQ)                                                                                                          \
-    if (eidx_i32) k_tconv_fwd<NQ, int><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_i32, rowptr, csr_src, (int)N, heads, C, s.groups, scale, thr, ks, sd, skip, agg, out, alpha); \
-    else k_tconv_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_u8, rowptr, csr_src, (int)N, heads, C, s.groups, scale, thr, ks, sd, skip, agg, out, alpha)
+    if (eidx_i32) k_tconv_fwd<NQ, int><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_i32, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha); \
+    else k_tconv_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_u8, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha)
     TCONV_DISPATCH(s, CALL);
 #undef CALL
     return check_launch("tconv_fwd");
@@ -329,14 +333,14 @@ int gnnx_tconv_bwd(const float* dout, const float* qkv, const float* e, int64_t 
     const AttnShape s = attn_shape(heads, C);
     const float scale = 1.0f / sqrtf((float)C);
     cudaStream_t st = as_stream(stream);
-    const int grid = attn_grid(N * s.groups);
+    const int grid = attn_row_grid(N, s.groups, 16);
     const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                          \
-    if (eidx_i32) k_tconv_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_i32, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, s.groups, scale, ks, dqkv, ds, de); \
-    else k_tconv_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_u8, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, s.groups, scale, ks, dqkv, ds, de)
+    if (eidx_i32) k_tconv_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_i32, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de); \
+    else k_tconv_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_u8, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de)
     TCONV_DISPATCH(s, CALL);
 #undef CALL
-    k_tconv_bwd_src<<<attn_grid(N * ((s.H + 127) / 128)), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, heads, C, ks, dqkv);
+    k_tconv_bwd_src<<<attn_row_grid(N, (s.H + 127) / 128, 16), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, heads, C, ilog2(C), ks, dqkv);
     return check_launch("tconv_bwd", 2);
 }
 
