@@ -41,14 +41,28 @@ class FlatParameters:
             n = p.numel()
             self.data[o:o + n].copy_(p.data.reshape(-1))
             p.data = self.data[o:o + n].view(p.shape)
-            p.grad = self.grad[o:o + n].view(p.shape)
+        self.grad_views = [self.grad[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, self.offsets)]
 
     def zero_grad(self) -> None:
-        self.grad.zero_()
-        for p, o in zip(self.params, self.offsets):       # autograd may have swapped .grad for a fresh tensor
-            g = p.grad
-            if g is None or g.data_ptr() != self.grad.data_ptr() + 4 * o:
-                p.grad = self.grad[o:o + p.numel()].view(p.shape)
+        """Drop the per-parameter gradients: with ``.grad`` unset autograd hands each parameter the tensor the backward
+        produced (no per-parameter accumulation kernel); ``gather_grads`` then packs them into the flat buffer."""
+        for p in self.params:
+            p.grad = None
+
+    def gather_grads(self) -> None:
+        """Pack every ``p.grad`` into the flat gradient buffer with one multi-tensor copy; afterwards ``p.grad`` IS the
+        matching view of the flat buffer.  Parameters the backward did not reach get a zero gradient."""
+        src, dst = [], []
+        for p, v in zip(self.params, self.grad_views):
+            if p.grad is None:
+                v.zero_()
+            elif p.grad.data_ptr() != v.data_ptr():
+                src.append(p.grad.reshape(v.shape))
+                dst.append(v)
+        if src:
+            torch._foreach_copy_(dst, src)
+        for p, v in zip(self.params, self.grad_views):
+            p.grad = v
 
 
 def shard_range(num_items: int, rank: int, world: int):
@@ -111,6 +125,7 @@ class Trainer:
         target = getattr(batch, self.target)
         out2, dpred = ops.relhuber_fwd_bwd(pred.detach().contiguous(), target.contiguous(), self.huber_delta)
         pred.backward(dpred)
+        self.flat.gather_grads()
         return out2
 
     def optimizer_step(self) -> None:

@@ -37,6 +37,7 @@ def _worker(rank, world, port, out):
         lo, hi = shard_range(len(graphs), rank, world)
         flat.zero_grad()
         ((model(feats[lo:hi]) - tgt[lo:hi]) ** 2).sum().backward()
+        flat.gather_grads()
         assert all(p.grad.data_ptr() == flat.grad.data_ptr() + 4 * o for p, o in zip(flat.params, flat.offsets)), \
             "gradients must land in the flat buffer (one all-reduce, no bucketing)"
         dist.all_reduce(flat.grad, op=dist.ReduceOp.SUM)              # THE collective of a training step
@@ -65,6 +66,7 @@ def test_two_rank_sharded_gradient_equals_global_batch(tmp_path):
     tgt = torch.stack([torch.from_numpy(g.para[0]) for g in graphs])
     flat.zero_grad()
     ((model(feats) - tgt) ** 2).sum().backward()
+    flat.gather_grads()
     assert torch.allclose(got["grad"], flat.grad, rtol=1e-5, atol=1e-3 * float(flat.grad.abs().max()) * 1e-2)
     hist = np.zeros(16, np.int64)
     for g in graphs:
