@@ -189,7 +189,7 @@ def _algorithmic_bytes(name, a, N, E, H):
         if flags & 2:
             byts += 4.0 * M * Nn
         if mask:
-            byts += 4.0 * M * Nn
+            byts += (M * Nn / 8.0) if (flags & 4) else 4.0 * M * Nn      # packed (1 bit / element) or fp32 mask
         return byts, 2.0 * M * Nn * K
     if name == "gnnx_pna_aggregate_fwd":          # read messages once, write the four aggregates (4EH + 16NH + 4N)
         return 4.0 * E * H + 16.0 * N * H + 4.0 * N, 0.0

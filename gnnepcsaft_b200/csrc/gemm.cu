@@ -8,14 +8,14 @@
 namespace gnnx {
 size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K);
 int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
-              int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, void* ws, size_t ws_bytes,
-              cudaStream_t st);
+              int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
+              void* ws, size_t ws_bytes, cudaStream_t st);
 bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
                   const void* B, const void* C, int precision);
 size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision);
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
-            int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, int precision, void* ws,
-            size_t ws_bytes, cudaStream_t st);
+            int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
+            int precision, void* ws, size_t ws_bytes, cudaStream_t st);
 }  // namespace gnnx
 
 using namespace gnnx;
@@ -32,17 +32,22 @@ size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, in
 }
 
 int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
-              int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, const float* relu_mask, int64_t ld_mask,
-              int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+              int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, const void* relu_mask_v, int64_t ld_mask,
+              uint32_t* relu_bits_out, int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+    const float* relu_mask = static_cast<const float*>(relu_mask_v);      // uint32 words under GNNX_GEMM_MASK_BITS
     GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
     GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
     if (M == 0 || N == 0) return GNNX_OK;
     GNNX_REQUIRE(A && B && C, "gemm: null operand");
     cudaStream_t st = as_stream(stream);
-    const bool mask_ok = !relu_mask || (((uintptr_t)relu_mask & 15) == 0 && (ld_mask & 3) == 0);
+    const bool bits = (flags & GNNX_GEMM_MASK_BITS) != 0;
+    GNNX_REQUIRE(!bits || relu_mask, "gemm: GNNX_GEMM_MASK_BITS without a mask");
+    GNNX_REQUIRE(!bits || ld_mask >= (N + 31) / 32, "gemm: packed mask rows need at least ceil(N/32) words");
+    GNNX_REQUIRE(!(relu_bits_out && (flags & GNNX_GEMM_ACCUMULATE)), "gemm: relu_bits_out is not available with ACCUMULATE");
+    const bool mask_ok = !relu_mask || bits || (((uintptr_t)relu_mask & 15) == 0 && (ld_mask & 3) == 0);
     if (precision != GNNX_PREC_FP32 && mask_ok && tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision))
-        return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, precision, ws, ws_bytes, st);
-    return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, ws, ws_bytes, st);
+        return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, precision, ws, ws_bytes, st);
+    return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, ws, ws_bytes, st);
 }
 
 }  // extern "C"

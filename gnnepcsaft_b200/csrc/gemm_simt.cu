@@ -8,6 +8,13 @@ namespace gnnx {
 
 constexpr int BM = 128, BN = 128, BK = 8, TM = 8, TN = 8;
 
+// ReLU mask of the layer below: fp32 activations, or (GNNX_GEMM_MASK_BITS) one bit per element packed in uint32 words
+__device__ __forceinline__ bool mask_keeps(const float* __restrict__ mask, long long ldm, int flags, long long m, int n) {
+    if (flags & GNNX_GEMM_MASK_BITS)
+        return (reinterpret_cast<const uint32_t*>(mask)[m * ldm + (n >> 5)] >> (n & 31)) & 1u;
+    return mask[m * ldm + n] > 0.f;
+}
+
 // element (m,k) of op(A): trans ? A[k*lda + m] : A[m*lda + k]
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(256, 2)
@@ -100,7 +107,7 @@ k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__
             } else {
                 if (bias) v += bias[gn];
                 if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)gm * ldc + gn];
-                if (mask && !(mask[(long long)gm * ldm + gn] > 0.f)) v = 0.f;
+                if (mask && !mask_keeps(mask, ldm, flags, gm, gn)) v = 0.f;
                 if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
                 C[(long long)gm * ldc + gn] = v;
             }
@@ -126,7 +133,7 @@ __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, i
         for (; s < splits; ++s) v += __ldcs(partial + (long long)s * total + i);
         if (bias) v += bias[n];
         if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)m * ldc + n];
-        if (mask && !(mask[(long long)m * ldm + n] > 0.f)) v = 0.f;
+        if (mask && !mask_keeps(mask, ldm, flags, m, n)) v = 0.f;
         if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
         C[(long long)m * ldc + n] = v;
     }
@@ -157,9 +164,29 @@ size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K) {
     return s > 1 ? (size_t)s * M * N * sizeof(float) : 0;
 }
 
+// bits[r, w] = OR_j (C[r, 32 w + j] > 0) << j : the packed ReLU mask a forward product leaves for its backward
+__global__ void k_pack_relu_bits(const float* __restrict__ C, long long ldc, int M, int N, uint32_t* __restrict__ bits) {
+    const int words = (N + 31) / 32;
+    const long long total = (long long)M * words;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / words;
+        const int c0 = (int)(i % words) * 32;
+        uint32_t w = 0;
+        for (int j = 0; j < 32 && c0 + j < N; ++j) w |= (C[r * ldc + c0 + j] > 0.f ? 1u : 0u) << j;
+        bits[i] = w;
+    }
+}
+int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t* bits, cudaStream_t st) {
+    long long total = (long long)M * ((N + 31) / 32);
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    k_pack_relu_bits<<<blocks, 256, 0, st>>>(C, ldc, M, N, bits);
+    return check_launch("pack_relu_bits");
+}
+
 int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc,
-              int64_t M, int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, void* ws,
-              size_t ws_bytes, cudaStream_t st) {
+              int64_t M, int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm,
+              uint32_t* bits_out, void* ws, size_t ws_bytes, cudaStream_t st) {
     if (M == 0 || N == 0) return GNNX_OK;
     int splits = simt_splits(M, N, K);
     float* partial = nullptr;
@@ -182,7 +209,9 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
 #undef LAUNCH
     if (partial)
         k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
-    return check_launch("gemm_simt", partial ? 2 : 1);
+    int rc = check_launch("gemm_simt", partial ? 2 : 1);
+    if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
+    return rc;
 }
 
 // ------------------------------------------------------------------ column sums

@@ -24,6 +24,7 @@ namespace gnnx {
 
 int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
                          int flags, const float* mask, long long ldm, cudaStream_t st);
+int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t* bits, cudaStream_t st);
 
 namespace tc {
 
@@ -119,7 +120,13 @@ __device__ __forceinline__ void epilogue_acc(const SM& sm, uint32_t tmem_acc, in
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const long long grow = row0 + q * 32 + i * 4 + (lane >> 3);
-                mk[i] = grow < row_end ? __ldcs(reinterpret_cast<const float4*>(mask + grow * ldm + gcol)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (grow >= row_end) { mk[i] = make_float4(0.f, 0.f, 0.f, 0.f); continue; }
+                if (flags & GNNX_GEMM_MASK_BITS) {       // expand this lane's 4 bits to the fp32 form used below
+                    const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(mask) + grow * ldm + (gcol >> 5)) >> (gcol & 31);
+                    mk[i] = make_float4((float)(w & 1u), (float)((w >> 1) & 1u), (float)((w >> 2) & 1u), (float)((w >> 3) & 1u));
+                } else {
+                    mk[i] = __ldcs(reinterpret_cast<const float4*>(mask + grow * ldm + gcol));
+                }
             }
         }
         float v[32];
@@ -163,13 +170,20 @@ template <class SM>
 __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
                                             int row0, int row_end, int col0, int ncols, const float* __restrict__ bias,
                                             int col_end, int flags, uint32_t& it, const float* __restrict__ mask = nullptr,
-                                            long long ldm = 0) {
+                                            long long ldm = 0, uint32_t* __restrict__ bits_out = nullptr, long long ldbits = 0) {
     uint8_t* stage = reinterpret_cast<uint8_t*>(sm.epi(q));
     const int mr = lane >> 3, mj = lane & 7;            // coalesced mask mapping: 8 lanes cover one 128-byte row segment
+    const bool mbits = mask && (flags & GNNX_GEMM_MASK_BITS);
+    const long long myrow = (long long)row0 + q * 32 + lane;   // this thread's accumulator row
     for (int c = 0; c < ncols; c += 32, ++it) {
-        // ReLU mask of the layer below, requested before the TMEM load: 4 full 128-byte rows per load instruction
+        // ReLU mask of the layer below, requested before the TMEM load.  Packed: ONE word per thread covers its row's
+        // 32 columns of this chunk.  fp32: 4 full 128-byte rows per load instruction, applied on the staged tile.
         float4 mk[8];
-        if (mask) {
+        uint32_t mw = 0xffffffffu;
+        if (mbits) {
+            if (myrow < row_end && col0 + c < col_end)
+                mw = __ldg(reinterpret_cast<const uint32_t*>(mask) + myrow * ldm + ((col0 + c) >> 5));
+        } else if (mask) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const long long gr = (long long)row0 + q * 32 + i * 4 + mr;
@@ -201,10 +215,20 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
+        if (mbits) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = ((mw >> j) & 1u) ? v[j] : 0.f;
+        }
+        if (bits_out) {                                  // packed (C > 0) of this row's 32 columns, for the backward
+            uint32_t w = 0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) w |= (v[j] > 0.f ? 1u : 0u) << j;
+            if (myrow < row_end && col0 + c < col_end) bits_out[myrow * ldbits + ((col0 + c) >> 5)] = w;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        if (mask) {                                      // second pass over the staged tile in the mask's (coalesced) mapping
+        if (mask && !mbits) {                            // second pass over the staged tile in the mask's (coalesced) mapping
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -231,7 +255,8 @@ template <bool kBMN>
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
-                 const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm) {
+                 const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
+                 uint32_t* __restrict__ bits_out, long long ldbits) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -304,7 +329,7 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             for (int h = 0; h < halves; ++h) {
                 if (use_tma)
-                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it, mask, ldm);
+                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
                 else
                     epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
             }
@@ -352,7 +377,8 @@ template <bool kBMN, int kCluster>
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
-                  const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm) {
+                  const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
+                  uint32_t* __restrict__ bits_out, long long ldbits) {
     extern __shared__ uint8_t smem_raw[];
     Smem2 sm;
     sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -444,7 +470,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
                 if (use_tma)
-                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm);
+                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
                 else
                     epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags & 0xff, mask, ldm);
             }
@@ -657,8 +683,8 @@ size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int p
 }
 
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
-            int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, int precision, void* ws,
-            size_t ws_bytes, cudaStream_t st) {
+            int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
+            int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
     (void)precision;
     static bool attr_done = false;
     if (!attr_done) {
@@ -706,13 +732,14 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         cfg.attrs = at; cfg.numAttrs = 1;
         const int Mi = (int)M, Ni = (int)N, Ki = (int)K;
         const long long ldc_ = ldc, ldm_ = ldm;
+        const long long ldbits = (N + 31) / 32;          // packed masks are row-major: [M, ceil(N/32)] words
         cudaError_t e;
         if (cluster == 2)
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits);
         else
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits);
         if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
         return check_launch("gemm_tf32_rows2");
     }
@@ -728,9 +755,9 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         int tiles = ceil_div(M, 256) * ceil_div(N, BN);
         int grid = tiles < kNumSMs ? tiles : kNumSMs;
         if (tb)
-            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
+            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
         else
-            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm);
+            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
         return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
@@ -743,7 +770,9 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
                                                                           p.rows_per_split, p.BM, p.BN);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
-    return splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
+    rc = splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
+    if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
+    return rc;
 }
 
 }  // namespace gnnx

@@ -20,51 +20,57 @@ __device__ __forceinline__ F4 f4_ld(const float* p) { F4 r; r.q = ldg4(p); retur
 __device__ __forceinline__ F4 f4_lds(const float* p) { F4 r; r.q = ldg4_stream(p); return r; }
 
 // ------------------------------------------------------------------ gather (K3 + first pre_nn Linear, node-side split)
+// 8 lanes x 4 columns -> the uint32 word of packed (value > 0) bits for those 32 columns, on every lane of the group
+__device__ __forceinline__ uint32_t pack_relu_word(const F4& o, bool act, int lane) {
+    uint32_t v = 0;
+    if (act) v = ((o.a[0] > 0.f ? 1u : 0u) | (o.a[1] > 0.f ? 2u : 0u) | (o.a[2] > 0.f ? 4u : 0u) | (o.a[3] > 0.f ? 8u : 0u)) << (4 * (lane & 7));
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+
 template <typename RIdx>
 __global__ void __launch_bounds__(256)
 k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __restrict__ r, long long ld_r,
                  const RIdx* __restrict__ ridx, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
-                 int N, int H, int relu, float* __restrict__ h) {
+                 int N, int H, int relu, float* __restrict__ h, uint32_t* __restrict__ bits) {
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
-    const long long nwork = (long long)N * chunks;
+    const int words = (H + 31) / 32;
     const int wpb = blockDim.x >> 5;
-    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
-        int i = (int)(w / chunks);
-        int c = (int)(w % chunks) * 128 + lane * 4;
-        int b = rowptr[i], e = rowptr[i + 1];
-        if (b == e || c >= H) continue;
-        F4 p = f4_ld(pq + (long long)i * ld_pq + c);
-        int k = b;
-        for (; k + 2 <= e; k += 2) {
-            int s0 = csr_src[k], s1 = csr_src[k + 1];
-            long long r0 = (long long)ridx[k], r1 = (long long)ridx[k + 1];
-            F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c);
-            F4 q1 = f4_ld(pq + (long long)s1 * ld_pq + H + c);
-            F4 t0 = f4_ld(r + r0 * ld_r + c);
-            F4 t1 = f4_ld(r + r1 * ld_r + c);
-            F4 o0, o1;
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // fixed column chunk per warp, rows strided
+    const int row_stride = (gridDim.x * wpb) / chunks;           // host guarantees divisibility
+    const int c = (gw % chunks) * 128 + lane * 4;
+    const bool act = c < H;
+    for (int i = gw / chunks; i < N; i += row_stride) {
+        const int b = rowptr[i], e = rowptr[i + 1];
+        if (b == e) continue;
+        const F4 p = act ? f4_ld(pq + (long long)i * ld_pq + c) : f4_zero();
+        for (int k = b; k < e; k += 2) {
+            const bool two = k + 1 < e;
+            const int s0 = csr_src[k], s1 = two ? csr_src[k + 1] : s0;
+            const long long r0 = (long long)ridx[k], r1 = two ? (long long)ridx[k + 1] : r0;
+            F4 o0 = f4_zero(), o1 = f4_zero();
+            if (act) {
+                const F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c), q1 = f4_ld(pq + (long long)s1 * ld_pq + H + c);
+                const F4 t0 = f4_ld(r + r0 * ld_r + c), t1 = f4_ld(r + r1 * ld_r + c);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
-                o1.a[j] = p.a[j] + q1.a[j] + t1.a[j];
-                if (relu) { o0.a[j] = fmaxf(o0.a[j], 0.f); o1.a[j] = fmaxf(o1.a[j], 0.f); }
+                for (int j = 0; j < 4; ++j) {
+                    o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
+                    o1.a[j] = p.a[j] + q1.a[j] + t1.a[j];
+                    if (relu) { o0.a[j] = fmaxf(o0.a[j], 0.f); o1.a[j] = fmaxf(o1.a[j], 0.f); }
+                }
+                stg4(h + (long long)k * H + c, o0.q);
+                if (two) stg4(h + (long long)(k + 1) * H + c, o1.q);
             }
-            stg4(h + (long long)k * H + c, o0.q);
-            stg4(h + (long long)(k + 1) * H + c, o1.q);
-        }
-        if (k < e) {
-            int s0 = csr_src[k];
-            long long r0 = (long long)ridx[k];
-            F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c);
-            F4 t0 = f4_ld(r + r0 * ld_r + c);
-            F4 o0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
-                if (relu) o0.a[j] = fmaxf(o0.a[j], 0.f);
+            if (bits) {                                          // packed ReLU mask of the rows just written
+                const uint32_t w0 = pack_relu_word(o0, act, lane), w1 = pack_relu_word(o1, act, lane);
+                if (act && (lane & 7) == 0) {
+                    bits[(long long)k * words + (c >> 5)] = w0;
+                    if (two) bits[(long long)(k + 1) * words + (c >> 5)] = w1;
+                }
             }
-            stg4(h + (long long)k * H + c, o0.q);
         }
     }
 }
@@ -352,15 +358,17 @@ extern "C" {
 
 int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t ld_r, const int32_t* ridx_i32,
                         const uint8_t* ridx_u8, const int32_t* rowptr, const int32_t* csr_src, int64_t N, int64_t E,
-                        int32_t H, int32_t relu, float* h, void* stream) {
+                        int32_t H, int32_t relu, float* h, uint32_t* relu_bits_out, void* stream) {
     GNNX_REQUIRE(H % 4 == 0 && ld_pq % 4 == 0 && ld_r % 4 == 0, "pna_gather_fwd: hidden / strides must be multiples of 4");
     GNNX_REQUIRE((ridx_i32 != nullptr) != (ridx_u8 != nullptr), "pna_gather_fwd: exactly one of ridx_i32 / ridx_u8");
     if (N == 0 || E == 0) return GNNX_OK;
-    long long nwork = (long long)N * ((H + 127) / 128);
+    const int chunks = (H + 127) / 128;
+    int grid = warp_grid((long long)N * chunks);
+    grid = (grid + chunks - 1) / chunks * chunks;               // every warp keeps one column chunk
     if (ridx_i32)
-        k_pna_gather_fwd<int><<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h);
+        k_pna_gather_fwd<int><<<grid, 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
     else
-        k_pna_gather_fwd<uint8_t><<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h);
+        k_pna_gather_fwd<uint8_t><<<grid, 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
     return check_launch("pna_gather_fwd");
 }
 

@@ -15,7 +15,7 @@ from torch import Tensor
 from ._lib import lib
 
 PREC_FP32, PREC_TF32, PREC_BF16 = 0, 1, 2
-GEMM_RELU, GEMM_ACCUMULATE = 1, 2
+GEMM_RELU, GEMM_ACCUMULATE, GEMM_MASK_BITS = 1, 2, 4
 _PRECISIONS = {"fp32": PREC_FP32, "highest": PREC_FP32, "tf32": PREC_TF32, "high": PREC_TF32,
                "bf16": PREC_BF16, "medium": PREC_BF16}
 
@@ -184,9 +184,11 @@ def _ld(t: Tensor) -> int:
 
 def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, bias: Optional[Tensor] = None,
          relu: bool = False, out: Optional[Tensor] = None, accumulate: bool = False,
-         precision: Optional[int] = None, relu_mask: Optional[Tensor] = None) -> Tensor:
+         precision: Optional[int] = None, relu_mask: Optional[Tensor] = None, want_relu_bits: bool = False):
     """``out = act(op(a) @ op(b) + bias)``; ``a``/``b``/``out`` may be column slices (row stride = ld).
-    ``relu_mask`` [M,N]: the result is zeroed where ``relu_mask <= 0`` (fused ReLU backward of the layer below)."""
+    ``relu_mask`` [M,N]: the result is zeroed where ``relu_mask <= 0`` (fused ReLU backward of the layer below); an
+    int32 tensor is taken as the PACKED form (bit c%32 of word [r, c//32] set where the activation was
+    positive) -- int32 [M, ceil(N/32)].  ``want_relu_bits``: also return that packed mask of the result -> ``(out, bits)``."""
     for t, n in ((a, "a"), (b, "b")):
         if not t.is_cuda or t.dtype != torch.float32:
             raise RuntimeError(f"gnnx.gemm: `{n}` must be a CUDA float32 tensor (no CPU fallback exists)")
@@ -202,15 +204,28 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
         raise ValueError("gnnx.gemm: bad `out`")
     if bias is not None:
         _chk(bias, torch.float32, "bias")
-    if relu_mask is not None and (relu_mask.shape != (M, N) or relu_mask.dtype != torch.float32 or not relu_mask.is_cuda):
-        raise ValueError("gnnx.gemm: bad `relu_mask`")
-    prec = _default_precision if precision is None else precision
     flags = (GEMM_RELU if relu else 0) | (GEMM_ACCUMULATE if accumulate else 0)
+    words = (N + 31) // 32
+    ld_mask = 0
+    if relu_mask is not None:
+        if not relu_mask.is_cuda:
+            raise ValueError("gnnx.gemm: bad `relu_mask`")
+        if relu_mask.dtype == torch.int32:
+            if relu_mask.shape != (M, words) or not relu_mask.is_contiguous():
+                raise ValueError("gnnx.gemm: a packed `relu_mask` must be a contiguous int32 [M, ceil(N/32)]")
+            flags |= GEMM_MASK_BITS
+            ld_mask = words
+        elif relu_mask.shape != (M, N) or relu_mask.dtype != torch.float32:
+            raise ValueError("gnnx.gemm: bad `relu_mask`")
+        else:
+            ld_mask = _ld(relu_mask)
+    bits = torch.empty((M, words), dtype=torch.int32, device=a.device) if want_relu_bits else None
+    prec = _default_precision if precision is None else precision
     L = lib()
     ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
     L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),
-           M, N, K, _p(bias), flags, _p(relu_mask), 0 if relu_mask is None else _ld(relu_mask), prec, _p(ws), nb, _stream())
-    return out
+           M, N, K, _p(bias), flags, _p(relu_mask), ld_mask, _p(bits), prec, _p(ws), nb, _stream())
+    return (out, bits) if want_relu_bits else out
 
 
 def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
@@ -225,16 +240,18 @@ def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
 
 
 # ------------------------------------------------------------------ PNA
-def pna_gather_fwd(pq: Tensor, r: Tensor, ridx: Tensor, rowptr: Tensor, csr_src: Tensor, relu: bool) -> Tensor:
+def pna_gather_fwd(pq: Tensor, r: Tensor, ridx: Tensor, rowptr: Tensor, csr_src: Tensor, relu: bool,
+                   want_relu_bits: bool = False):
     _chk(pq, torch.float32, "pq"); _chk(r, torch.float32, "r")
     N, H = pq.shape[0], pq.shape[1] // 2
     E = csr_src.numel()
     h = torch.empty((E, H), dtype=torch.float32, device=pq.device)
+    bits = torch.empty((E, (H + 31) // 32), dtype=torch.int32, device=pq.device) if want_relu_bits else None
     i32 = ridx.data_ptr() if ridx.dtype == torch.int32 else None
     u8 = ridx.data_ptr() if ridx.dtype == torch.uint8 else None
     lib().call("gnnx_pna_gather_fwd", pq.data_ptr(), pq.stride(0), r.data_ptr(), r.stride(0), i32, u8, rowptr.data_ptr(),
-               csr_src.data_ptr(), N, E, H, int(relu), h.data_ptr(), _stream())
-    return h
+               csr_src.data_ptr(), N, E, H, int(relu), h.data_ptr(), _p(bits), _stream())
+    return (h, bits) if want_relu_bits else h
 
 
 def pna_gather_bwd(dh: Tensor, g, want_dr_edge: bool):

@@ -9,7 +9,8 @@ Restructurings relative to the PyG formulation, all algebraically ex
   * towers are folded into block-diagonal weights (built per call from the per-tower parameters, a few KB..MB):
     every Linear of the layer is then ONE full-width GEMM whatever `towers` is.  These products are HBM-bound at
     the hot path's shapes (DESIGN.md), so the zero blocks cost tensor-pipe flops, not time;
-  * the ReLU backward between Linear layers rides the dX product's epilogue (`relu_mask`);
+  * the ReLU backward between Linear layers rides the dX product's epilogue (`relu_mask`), fed by a 1-bit-per-element
+    mask that the forward product (or the gather kernel) packed from its own output;
   * the last post_nn Linear has no activation before `lin`, so the two are applied as ONE Linear with
     Wf = W_lin W_last, bf = W_lin b_last + b_lin (a 256^3 weight-space product per call); the chain rule back to
     the two original parameters is exact (dW_lin = dWf W_last^T + dbf b_last^T, dW_last = W_lin^T dWf, ...).
@@ -80,12 +81,18 @@ class _Packed:
                      for l in range(1, meta.post_layers)]
 
 
-def _chain_fwd(inp: Tensor, layers, relu_last: bool = False) -> List[Tensor]:
-    """Linear + ReLU layers (no ReLU after the last unless ``relu_last``); returns the input and every layer output."""
-    outs = [inp]
+def _chain_fwd(inp: Tensor, layers, relu_last: bool = False):
+    """Linear + ReLU layers (no ReLU after the last unless ``relu_last``); returns the input and every layer output,
+    and for every output the packed ReLU mask its backward needs (``None`` where no ReLU was applied)."""
+    outs, bits = [inp], [None]
     for i, (w, b) in enumerate(layers):
-        outs.append(ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=relu_last or i < len(layers) - 1))
-    return outs
+        relu = relu_last or i < len(layers) - 1
+        if relu:
+            o, m = ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=True, want_relu_bits=True)
+        else:
+            o, m = ops.gemm(outs[-1], w, trans_b=True, bias=b), None
+        outs.append(o); bits.append(m)
+    return outs, bits
 
 
 def _wprod(a: Tensor, b: Tensor, **kw) -> Tensor:
@@ -93,15 +100,16 @@ def _wprod(a: Tensor, b: Tensor, **kw) -> Tensor:
     return ops.gemm(a, b, precision=ops.PREC_FP32, **kw)
 
 
-def _chain_bwd(d: Tensor, acts: List[Tensor], layers, mask_first: bool):
-    """Backward of ``_chain_fwd``.  ``acts[i]`` is the input of layer i; every ``acts[i]`` went through a ReLU, whose
-    backward is fused into the dX product -- for ``acts[0]`` only if ``mask_first``.  Returns (d at acts[0], dW, db)."""
+def _chain_bwd(d: Tensor, acts: List[Tensor], masks, layers):
+    """Backward of ``_chain_fwd``.  ``acts[i]`` is the input of layer i and ``masks[i]`` the packed mask of the ReLU
+    it went through (``None``: no ReLU to undo here); that ReLU's backward is fused into the dX product.
+    Returns (d at acts[0], dW, db)."""
     dws, dbs = [None] * len(layers), [None] * len(layers)
     for i in range(len(layers) - 1, -1, -1):
         w, _ = layers[i]
         dws[i] = ops.gemm(d, acts[i], trans_a=True)
         dbs[i] = ops.colsum(d)
-        d = ops.gemm(d, w, relu_mask=acts[i] if (i > 0 or mask_first) else None)
+        d = ops.gemm(d, w, relu_mask=masks[i])
     return d, dws, dbs
 
 
@@ -124,8 +132,12 @@ class PNAConvFn(Function):
         r = ops.gemm(e1, pk.wr, trans_b=True, bias=pk.br)
         pq = ops.gemm(x, pk.wpq, trans_b=True)
         ridx = meta.codes if meta.codes is not None else g.csr_eid
-        h = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=meta.pre_layers > 1)
-        hs = _chain_fwd(h, pk.pre)
+        if meta.pre_layers > 1:
+            h, hbits = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=True, want_relu_bits=True)
+        else:
+            h, hbits = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=False), None
+        hs, hmasks = _chain_fwd(h, pk.pre)
+        hmasks[0] = hbits
         m = hs[-1]
         agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
         if CAPTURE_AGG is not None:
@@ -136,15 +148,17 @@ class PNAConvFn(Function):
         o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
         if pk.post:                                   # fold the activation-free last post Linear into `lin`
             w_last, b_last = pk.post[-1]
-            os_ = _chain_fwd(o, pk.post[:-1], relu_last=True)
+            os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True)
             wf = _wprod(wl, w_last)
             bf = _wprod(wl, b_last.unsqueeze(1)).squeeze(1) + bl
         else:
-            os_, wf, bf = [o], wl, bl
+            os_, omasks, wf, bf = [o], [None], wl, bl
         out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
         ctx.meta = meta
         ctx.n_hs, ctx.n_os = len(hs), len(os_)
-        ctx.save_for_backward(x, efeat, e1, agg, *hs, *os_, *params)
+        omasks[0] = None                               # the combine output's own ReLU is undone by combine_bwd
+        ctx.mask_slots = [m is not None for m in hmasks + omasks]
+        ctx.save_for_backward(x, efeat, e1, agg, *hs, *os_, *[m for m in hmasks + omasks if m is not None], *params)
         return out
 
     @staticmethod
@@ -157,7 +171,13 @@ class PNAConvFn(Function):
         x, efeat, e1, agg = saved[:4]
         hs = list(saved[4:4 + ctx.n_hs])
         os_ = list(saved[4 + ctx.n_hs:4 + ctx.n_hs + ctx.n_os])
-        params = saved[4 + ctx.n_hs + ctx.n_os:]
+        pos = 4 + ctx.n_hs + ctx.n_os
+        masks = []
+        for present in ctx.mask_slots:
+            masks.append(saved[pos] if present else None)
+            pos += int(present)
+        hmasks, omasks = masks[:ctx.n_hs], masks[ctx.n_hs:]
+        params = saved[pos:]
         we, be, pre, post, wl, bl = _split_params(meta, params)
         pk = _Packed(meta, pre, post)
         grads: dict = {}
@@ -178,12 +198,12 @@ class PNAConvFn(Function):
                 grads[id(post[t][l_last][0])] = blk
                 grads[id(post[t][l_last][1])] = db_last[t * Fo:(t + 1) * Fo]
             # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
-            d = ops.gemm(dout, wf, relu_mask=os_[-1] if len(os_) > 1 else None)
+            d = ops.gemm(dout, wf, relu_mask=omasks[-1])
         else:
             grads[id(wl)], grads[id(bl)] = dwf, dbf
             d = ops.gemm(dout, wl)
         # post layers 1..post-2 -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
-        d, dws, dbs = _chain_bwd(d, os_, pk.post[:-1], mask_first=False)
+        d, dws, dbs = _chain_bwd(d, os_, omasks, pk.post[:-1])
         for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
             for t, blk in enumerate(_diag_blocks(dw, T)):
                 grads[id(post[t][l][0])] = blk
@@ -205,7 +225,7 @@ class PNAConvFn(Function):
         if CAPTURE_BWD is not None:
             CAPTURE_BWD.append(dict(dagg=dagg, dm=dm, m=hs[-1], agg=agg, dz=dz, d_post=d))
         # pre layers 1.. -> gradient at the gather output (ReLU of the first layer fused into the last dX product)
-        dh, dws, dbs = _chain_bwd(dm, hs, pk.pre, mask_first=True)
+        dh, dws, dbs = _chain_bwd(dm, hs, hmasks, pk.pre)
         for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
             for t, blk in enumerate(_diag_blocks(dw, T)):
                 grads[id(pre[t][l][0])] = blk

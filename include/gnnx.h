@@ -118,11 +118,17 @@ GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_fe
  *   bias: optional [N]; flags: GNNX_GEMM_RELU applies max(.,0); GNNX_GEMM_ACCUMULATE adds the
  *   previous contents of C.  relu_mask: optional [M,N] (row stride ld_mask): the result is zeroed
  *   where relu_mask <= 0 -- the ReLU backward of the layer BELOW fused into a dX product
- *   (dX = (dY W) * (y_in > 0)).  precision: GNNX_PREC_* below.
+ *   (dX = (dY W) * (y_in > 0)).  With GNNX_GEMM_MASK_BITS the mask is PACKED instead: relu_mask
+ *   points to uint32 words, bit (c % 32) of word [r * ld_mask + c / 32] set where y_in[r,c] > 0
+ *   (1 bit instead of 4 bytes of mask traffic per element; a row's words share one 32-byte sector,
+ *   so the one-row-per-thread epilogue misses once per row and then hits L1).  relu_bits_out:
+ *   optional [M, ceil(N/32)] uint32 -- the same packing of (C > 0) for the result just computed,
+ *   written by a ReLU'd forward product for its own backward.  precision: GNNX_PREC_* below.
  * Split-K (deterministic two-pass) is chosen internally when M*N is small and K large;
  * workspace may be null when gnnx_gemm_workspace_bytes() returns 0. */
 #define GNNX_GEMM_RELU 1
 #define GNNX_GEMM_ACCUMULATE 2
+#define GNNX_GEMM_MASK_BITS 4
 #define GNNX_PREC_FP32 0 /* CUDA-core fp32 FMA (parity tier, rel 1e-5)              */
 #define GNNX_PREC_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM             */
 #define GNNX_PREC_BF16 2 /* the reference's "medium": served by the tf32 kernels (more precise) */
@@ -130,8 +136,8 @@ GNNX_API size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32
                                  int32_t precision);
 GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float* B, int64_t ldb, int32_t trans_b,
               float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags,
-              const float* relu_mask, int64_t ld_mask, int32_t precision, void* workspace, size_t workspace_bytes,
-              void* stream);
+              const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out, int32_t precision, void* workspace,
+              size_t workspace_bytes, void* stream);
 
 /* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);
@@ -144,11 +150,14 @@ GNNX_API int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols
  * dst-sorted slot p:  h[p,:] = act( pq[dst_p, 0:H] + pq[src_p, H:2H] + r[ridx_p, :] )
  * where r is either the per-edge term in ORIGINAL edge order (ridx = csr_eid) or a 60-row
  * bond-type table (ridx = codes, uint8).  Exactly one of ridx_i32 / ridx_u8 is non-null.
- * relu != 0 applies the ReLU that follows the first Linear when pre_layers > 1. */
+ * relu != 0 applies the ReLU that follows the first Linear when pre_layers > 1.
+ * relu_bits_out: optional [E, ceil(H/32)] uint32, the packed (h > 0) mask in the layout
+ * gnnx_gemm's GNNX_GEMM_MASK_BITS consumes (the backward of that ReLU rides a dX product). */
 GNNX_API int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t ld_r,
                         const int32_t* ridx_i32, const uint8_t* ridx_u8,
                         const int32_t* rowptr, const int32_t* csr_src, int64_t num_nodes,
-                        int64_t num_edges, int32_t hidden, int32_t relu, float* h, void* stream);
+                        int64_t num_edges, int32_t hidden, int32_t relu, float* h, uint32_t* relu_bits_out,
+                        void* stream);
 /* Backward of the gather: dh is [E,H] in dst-sorted order (already masked by ReLU').
  *   dpq[i, 0:H]  = sum_{p in row i} dh[p]           (segment sum, CSR)
  *   dpq[j, H:2H] = sum_{edges with src j} dh[pos]   (segment sum through csc_pos)

@@ -122,3 +122,40 @@ def test_fused_relu_mask_and_accumulate(prec):
     ops.gemm(dy.to(DEV), w.to(DEV), out=out2, accumulate=True, relu_mask=y.to(DEV))
     ref2 = (dy.double() @ w.double() + prev.double()) * (y.double() > 0)
     assert float(((out2.double().cpu() - ref2).abs() / bound).max()) <= 1.0
+
+
+def _pack_bits(y: torch.Tensor) -> torch.Tensor:
+    """Reference packing: bit c%32 of word [r, c//32] = (y[r, c] > 0); int32 words as the kernels store them."""
+    M, N = y.shape
+    words = (N + 31) // 32
+    pad = torch.zeros(M, words * 32, dtype=torch.bool)
+    pad[:, :N] = y > 0
+    w = (pad.view(M, words, 32).to(torch.int64) << torch.arange(32, dtype=torch.int64)).sum(-1)
+    return torch.where(w >= 2 ** 31, w - 2 ** 32, w).to(torch.int32)
+
+
+@pytest.mark.parametrize("prec", ["tf32", "fp32"])
+@pytest.mark.parametrize("M,K,N", [(3000, 256, 256), (1000, 64, 96), (333, 128, 512), (5000, 256, 48)])
+def test_packed_relu_bits_produced_and_consumed(prec, M, K, N):
+    """A ReLU'd forward product emits the 1-bit mask of its own output; the matching dX product consumes it
+    (GNNX_GEMM_MASK_BITS) and must equal the fp32-mask variant bit for bit."""
+    ops.set_matmul_precision(prec)
+    torch.manual_seed(M + N)
+    x, w, b = torch.randn(M, K), torch.randn(N, K) / K ** 0.5, torch.randn(N)
+    y, bits = ops.gemm(x.to(DEV), w.to(DEV), trans_b=True, bias=b.to(DEV), relu=True, want_relu_bits=True)
+    words = (N + 31) // 32
+    assert bits.shape == (M, words) and bits.dtype == torch.int32
+    want = _pack_bits(y.cpu())
+    valid = N - 32 * (words - 1)                       # bits past column N in the last word are don't-care
+    keep = torch.full((words,), -1, dtype=torch.int64)
+    keep[-1] = (1 << valid) - 1
+    assert torch.equal(bits.cpu().to(torch.int64) & keep, want.to(torch.int64) & keep), "packed mask differs from (y > 0)"
+    dy, w2 = torch.randn(M, K), torch.randn(K, N)
+    a = ops.gemm(dy.to(DEV), w2.to(DEV), relu_mask=y)
+    bq = ops.gemm(dy.to(DEV), w2.to(DEV), relu_mask=bits)
+    assert torch.equal(a, bq), "packed-mask dX differs from the fp32-mask dX"
+    prev = torch.randn(M, N)
+    o1, o2 = prev.to(DEV).clone(), prev.to(DEV).clone()
+    ops.gemm(dy.to(DEV), w2.to(DEV), out=o1, accumulate=True, relu_mask=y)
+    ops.gemm(dy.to(DEV), w2.to(DEV), out=o2, accumulate=True, relu_mask=bits)
+    assert torch.equal(o1, o2), "packed-mask accumulate variant differs"

@@ -211,3 +211,23 @@ def test_adamw_amsgrad_matches_torch():
         ops.adamw_amsgrad_(pp, (g * 4).to(DEV), m, v, vm, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-5, weight_decay=1e-2,
                            step=step, grad_scale=0.25)
     assert_close(pp, po, 1e-6, 1e-7, "adamw")
+
+
+@pytest.mark.parametrize("H", [32, 48, 128, 256, 320])
+def test_gather_packed_relu_bits(H):
+    """pna_gather_fwd's optional packed mask equals (h > 0) of the rows it wrote, for full and partial column chunks."""
+    _, b = make_batch(16, seed=11)
+    N, E = b["x"].shape[0], b["edge_index"].shape[1]
+    g = graph.graph_index_for(b["edge_index"].to(DEV), N)
+    torch.manual_seed(H)
+    pq, r = torch.randn(N, 2 * H, device=DEV), torch.randn(E, H, device=DEV)
+    h, bits = ops.pna_gather_fwd(pq, r, g.csr_eid, g.rowptr, g.csr_src, relu=True, want_relu_bits=True)
+    h0 = ops.pna_gather_fwd(pq, r, g.csr_eid, g.rowptr, g.csr_src, relu=True)
+    assert torch.equal(h, h0)
+    words = (H + 31) // 32
+    pad = torch.zeros(E, words * 32, dtype=torch.bool, device=DEV)
+    pad[:, :H] = h > 0
+    want = (pad.view(E, words, 32).to(torch.int64) << torch.arange(32, dtype=torch.int64, device=DEV)).sum(-1)
+    got = bits.to(torch.int64) & 0xFFFFFFFF
+    assert bits.shape == (E, words)
+    assert torch.equal(got, want)
