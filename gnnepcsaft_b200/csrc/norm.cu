@@ -456,3 +456,35 @@ int gnnx_adamw_amsgrad(float* param, const float* grad, float* exp_avg, float* e
 }
 
 }  // extern "C"
+
+namespace gnnx {
+// out[g] = [m, sigma, epsilon/k, kappa_AB, epsilon_AB/k, mu, n_a, n_b, MW]  (demo/utils.py:664-691)
+__global__ void k_assemble_params(const float* __restrict__ msigmae, const float* __restrict__ log10assoc,
+                                  const float* __restrict__ assoc, const float* __restrict__ munanb,
+                                  const float* __restrict__ mw, long long G, float* __restrict__ out) {
+    for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < G; g += (long long)gridDim.x * blockDim.x) {
+        float* o = out + g * 9;
+        o[0] = msigmae[g * 3]; o[1] = msigmae[g * 3 + 1]; o[2] = msigmae[g * 3 + 2];
+        if (log10assoc) {                            // 10 ** (pred * [-1, +1])
+            o[3] = exp10f(-log10assoc[g * 2]);
+            o[4] = exp10f(log10assoc[g * 2 + 1]);
+        } else {
+            o[3] = assoc ? assoc[g * 2] : 0.f;
+            o[4] = assoc ? assoc[g * 2 + 1] : 0.f;
+        }
+        o[5] = munanb[g * 3]; o[6] = munanb[g * 3 + 1]; o[7] = munanb[g * 3 + 2];
+        o[8] = mw[g];
+    }
+}
+}  // namespace gnnx
+
+extern "C" int gnnx_assemble_params(const float* msigmae, const float* log10assoc, const float* assoc, const float* munanb,
+                                    const float* mw, int64_t G, float* out9, void* stream) {
+    GNNX_REQUIRE(msigmae && munanb && mw && out9, "assemble_params: null operand");
+    GNNX_REQUIRE(!(log10assoc && assoc), "assemble_params: give the predicted log10 association pair OR known values, not both");
+    if (G == 0) return GNNX_OK;
+    long long blocks = (G + 255) / 256;
+    if (blocks > gnnx::kNumSMs * 8) blocks = gnnx::kNumSMs * 8;
+    gnnx::k_assemble_params<<<(int)blocks, 256, 0, gnnx::as_stream(stream)>>>(msigmae, log10assoc, assoc, munanb, mw, G, out9);
+    return gnnx::check_launch("assemble_params");
+}

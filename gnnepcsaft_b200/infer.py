@@ -16,6 +16,7 @@ import numpy as np
 import torch
 from torch import Tensor
 
+from . import ops
 from .graph import DeviceGraphStore
 from .train import node_balanced_batches, shard_range
 
@@ -55,3 +56,31 @@ class BulkScreener:
         finally:
             self.model.train(was_training)
         return out
+
+
+def screen_parameters(model_msigmae: torch.nn.Module, store: DeviceGraphStore, munanb: Tensor, mw: Tensor,
+                      model_assoc: Optional[torch.nn.Module] = None, assoc: Optional[Tensor] = None, rank: int = 0,
+                      world: int = 1, max_nodes: int = 1 << 20, max_graphs: int = 16384,
+                      out_path: Optional[str] = None) -> Tensor:
+    """Bulk-screening output stage (reference ``_get_model_params``, demo/utils.py:664-691, run
+    over a whole shard): both models' ``pred_with_bounds`` over this rank's graphs, then ONE kernel assembles the
+    9-vector ``[m, sigma, epsilon/k, kappa_AB, epsilon_AB/k, mu, n_a, n_b, MW]`` per molecule --
+    ``10 ** (pred * [-1, +1])`` for the association pair when ``model_assoc`` is given, the known ``assoc`` values (or
+    zeros) otherwise.  ``munanb`` [G,3] / ``mw`` [G] are the per-graph attributes of the WHOLE store (this rank's slice
+    is taken here).  With ``out_path`` the shard is also streamed to ``<out_path>.rank<r>.npy`` (one file per rank:
+    no communication)."""
+    if model_assoc is not None and assoc is not None:
+        raise ValueError("screen_parameters: give `model_assoc` or known `assoc` values, not both")
+    scr = BulkScreener(model_msigmae, store, rank, world, max_nodes, max_graphs)
+    msigmae = scr.run()
+    lo, hi = scr.lo, scr.hi
+    log10assoc = None
+    if model_assoc is not None:
+        log10assoc = BulkScreener(model_assoc, store, rank, world, max_nodes, max_graphs).run()
+    dev = store.device
+    out = ops.assemble_params(msigmae, munanb[lo:hi].to(dev, torch.float32).contiguous(),
+                              mw.reshape(-1)[lo:hi].to(dev, torch.float32).contiguous(), log10assoc=log10assoc,
+                              assoc=None if assoc is None else assoc[lo:hi].to(dev, torch.float32).contiguous())
+    if out_path is not None:
+        np.save(f"{out_path}.rank{rank}.npy", out.cpu().numpy())
+    return out

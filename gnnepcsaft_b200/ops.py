@@ -452,6 +452,25 @@ def tconv_bwd(dout: Tensor, qkv: Tensor, e: Tensor, eidx: Tensor, alpha: Tensor,
     return dqkv, de
 
 
+def assemble_params(msigmae: Tensor, munanb: Tensor, mw: Tensor, log10assoc: Optional[Tensor] = None,
+                    assoc: Optional[Tensor] = None) -> Tensor:
+    """``[G, 9]`` = [m, sigma, epsilon/k, kappa_AB, epsilon_AB/k, mu, n_a, n_b, MW] (demo/utils.py:664-691)."""
+    G = msigmae.shape[0]
+    for t, shape, n in ((msigmae, (G, 3), "msigmae"), (munanb, (G, 3), "munanb"), (mw.reshape(-1), (G,), "mw")):
+        _chk(t, torch.float32, n)
+        if tuple(t.shape) != shape:
+            raise ValueError(f"gnnx.assemble_params: `{n}` must be {shape}, got {tuple(t.shape)}")
+    for t, n in ((log10assoc, "log10assoc"), (assoc, "assoc")):
+        if t is not None:
+            _chk(t, torch.float32, n)
+            if tuple(t.shape) != (G, 2):
+                raise ValueError(f"gnnx.assemble_params: `{n}` must be ({G}, 2)")
+    out = torch.empty((G, 9), dtype=torch.float32, device=msigmae.device)
+    lib().call("gnnx_assemble_params", msigmae.data_ptr(), _p(log10assoc), _p(assoc), munanb.data_ptr(),
+               mw.reshape(-1).data_ptr(), G, out.data_ptr(), _stream())
+    return out
+
+
 # ------------------------------------------------------------------ loss / optimizer tail
 def relhuber_fwd_bwd(pred: Tensor, target: Tensor, delta: float = 0.01, want_grad: bool = True):
     _chk(pred, torch.float32, "pred"); _chk(target, torch.float32, "target")

@@ -81,16 +81,17 @@ class _Packed:
                      for l in range(1, meta.post_layers)]
 
 
-def _chain_fwd(inp: Tensor, layers, relu_last: bool = False):
+def _chain_fwd(inp: Tensor, layers, relu_last: bool = False, want_masks: bool = True):
     """Linear + ReLU layers (no ReLU after the last unless ``relu_last``); returns the input and every layer output,
-    and for every output the packed ReLU mask its backward needs (``None`` where no ReLU was applied)."""
+    and for every output the packed ReLU mask its backward needs (``None`` where no ReLU was applied, or when no
+    backward will run)."""
     outs, bits = [inp], [None]
     for i, (w, b) in enumerate(layers):
         relu = relu_last or i < len(layers) - 1
-        if relu:
+        if relu and want_masks:
             o, m = ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=True, want_relu_bits=True)
         else:
-            o, m = ops.gemm(outs[-1], w, trans_b=True, bias=b), None
+            o, m = ops.gemm(outs[-1], w, trans_b=True, bias=b, relu=relu), None
         outs.append(o); bits.append(m)
     return outs, bits
 
@@ -132,11 +133,12 @@ class PNAConvFn(Function):
         r = ops.gemm(e1, pk.wr, trans_b=True, bias=pk.br)
         pq = ops.gemm(x, pk.wpq, trans_b=True)
         ridx = meta.codes if meta.codes is not None else g.csr_eid
-        if meta.pre_layers > 1:
+        train = any(ctx.needs_input_grad)             # False under no_grad: no ReLU masks to keep
+        if meta.pre_layers > 1 and train:
             h, hbits = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=True, want_relu_bits=True)
         else:
-            h, hbits = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=False), None
-        hs, hmasks = _chain_fwd(h, pk.pre)
+            h, hbits = ops.pna_gather_fwd(pq, r, ridx, g.rowptr, g.csr_src, relu=meta.pre_layers > 1), None
+        hs, hmasks = _chain_fwd(h, pk.pre, want_masks=train)
         hmasks[0] = hbits
         m = hs[-1]
         agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
@@ -148,7 +150,7 @@ class PNAConvFn(Function):
         o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
         if pk.post:                                   # fold the activation-free last post Linear into `lin`
             w_last, b_last = pk.post[-1]
-            os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True)
+            os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True, want_masks=train)
             wf = _wprod(wl, w_last)
             bf = _wprod(wl, b_last.unsqueeze(1)).squeeze(1) + bl
         else:

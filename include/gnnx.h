@@ -278,6 +278,15 @@ GNNX_API int gnnx_tconv_bwd(const float* dout, const float* qkv, const float* e,
                    int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float dropout_p,
                    float* dqkv, float* ds, float* de, void* stream);
 
+/* ------------------------------------------------------------------ bulk-screening output stage */
+/* The 9-vector the reference hands to feos (demo/utils.py:664-691, _get_model_params):
+ *   out9[g] = [m, sigma, epsilon/k, kappa_AB, epsilon_AB/k, mu, n_a, n_b, MW]
+ * msigmae [G,3] = pred_with_bounds of the (m, sigma, epsilon/k) model; the association pair is either
+ * 10 ** (log10assoc * [-1, +1]) from the association model's clipped prediction [G,2], or the known
+ * values `assoc` [G,2], or zeros when both are null; munanb [G,3] and mw [G] are per-graph attributes. */
+GNNX_API int gnnx_assemble_params(const float* msigmae, const float* log10assoc, const float* assoc,
+                         const float* munanb, const float* mw, int64_t num_graphs, float* out9, void* stream);
+
 /* ------------------------------------------------------------------ loss + optimizer tail */
 /* Relative-error Huber(delta) + MAPE of GNNePCSAFTL.training_step (models.py:89-92), fused
  * forward + gradient: out[0] = loss, out[1] = mape, dpred = d loss / d pred. */

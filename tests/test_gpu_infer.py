@@ -44,3 +44,44 @@ def test_sharded_screening_matches_oracle_and_unsharded():
     assert sum(p.shape[0] for p in parts) == 300
     assert_close(torch.cat(parts), ref, 1e-4, 1e-5, "3 shards vs oracle")
     assert not mp.training
+
+
+def test_output_stage_assembles_the_feos_parameter_vector(tmp_path):
+    """both models' clipped predictions -> [m, sigma, eps/k, kappa_AB, eps_AB/k, mu, na, nb, MW],
+    checked against the reference's formula (demo/utils.py:664-691) evaluated on the oracle's predictions."""
+    from gnnepcsaft_b200.infer import screen_parameters
+    from tests.util import GAT_CFG_SMALL
+    ops.set_matmul_precision("fp32")
+    torch.set_float32_matmul_precision("highest")
+    graphs = synth.make_inference_graphs(120, seed=12)
+    deg = deg_hist(graphs)
+    torch.manual_seed(5)
+    mo_p = O.GNNePCSAFT(dict(PNA_CFG1, deg=deg)).eval()
+    mo_a = O.GNNePCSAFT(dict(GAT_CFG_SMALL, deg=deg)).eval()
+    mp_p = G.GNNePCSAFT(dict(PNA_CFG1, deg=deg)).cuda().eval()
+    mp_a = G.GNNePCSAFT(dict(GAT_CFG_SMALL, deg=deg)).cuda().eval()
+    mp_p.load_state_dict(mo_p.state_dict(), strict=True)
+    mp_a.load_state_dict(mo_a.state_dict(), strict=True)
+    t = torch.from_numpy
+    rng = np.random.default_rng(0)
+    munanb = t(np.stack([rng.uniform(0, 3, 120), rng.integers(0, 3, 120), rng.integers(0, 3, 120)], 1).astype(np.float32))
+    mw = t(rng.uniform(16, 400, 120).astype(np.float32))
+    with torch.no_grad():
+        b = O.collate([O.Graph(t(g.x), t(g.edge_index), t(g.edge_attr)) for g in graphs])
+        msigmae, la = mo_p.pred_with_bounds(b), mo_a.pred_with_bounds(b)
+    want = torch.cat([msigmae, 10 ** (la * torch.tensor([-1.0, 1.0])), munanb, mw[:, None]], 1)
+    store = graph.DeviceGraphStore(synth.pack(graphs), torch.device("cuda", 0))
+    got = screen_parameters(mp_p, store, munanb, mw, model_assoc=mp_a, max_nodes=1500, max_graphs=40,
+                            out_path=str(tmp_path / "params"))
+    assert got.shape == (120, 9)
+    assert_close(got, want, 1e-4, 1e-5, "9-vector", floor=0.0)
+    assert np.array_equal(np.load(str(tmp_path / "params") + ".rank0.npy"), got.cpu().numpy())
+    # non-associating path: known association values (or zeros) pass straight through; shards concatenate
+    known = t(rng.uniform(0, 1, (120, 2)).astype(np.float32))
+    parts = [screen_parameters(mp_p, store, munanb, mw, assoc=known, rank=r, world=2) for r in range(2)]
+    want2 = torch.cat([msigmae, known, munanb, mw[:, None]], 1)
+    assert_close(torch.cat(parts), want2, 1e-4, 1e-5, "9-vector, known assoc", floor=0.0)
+    zeros = screen_parameters(mp_p, store, munanb, mw)
+    assert bool((zeros[:, 3:5] == 0).all())
+    with pytest.raises(ValueError):
+        screen_parameters(mp_p, store, munanb, mw, model_assoc=mp_a, assoc=known)
