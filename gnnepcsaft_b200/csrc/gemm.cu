@@ -3,6 +3,8 @@
 //   GNNX_PREC_TF32 / GNNX_PREC_BF16 -> tcgen05 + TMEM kernels (gemm_tc.cu); shapes the tensor-core
 //   kernel does not cover (tiny or unaligned: the 60-row bond tables, the num_para-wide head output)
 //   run on the fp32 kernel, which is at least as accurate.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gnnx {
@@ -15,7 +17,7 @@ bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, 
 size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision);
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
             int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
-            int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st);
 }  // namespace gnnx
 
 using namespace gnnx;
@@ -24,6 +26,12 @@ extern "C" {
 
 size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, int32_t tb, int32_t precision) {
     size_t s = simt_workspace_bytes(M, N, K);
+    if (!ta) {                                             // room for colsum_a_out: per-CTA partials or the two-pass kernel's
+        size_t c = gnnx_colsum_workspace_bytes(M, K);
+        size_t f = (size_t)kNumSMs * K * sizeof(float);
+        if (f > c) c = f;
+        if (c > s) s = c;
+    }
     if (precision != GNNX_PREC_FP32) {
         size_t t = tc_workspace_bytes(M, N, K, ta, tb, precision);
         if (t > s) s = t;
@@ -33,7 +41,7 @@ size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, in
 
 int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
               int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, const void* relu_mask_v, int64_t ld_mask,
-              uint32_t* relu_bits_out, int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+              uint32_t* relu_bits_out, float* colsum_a_out, int32_t precision, void* ws, size_t ws_bytes, void* stream) {
     const float* relu_mask = static_cast<const float*>(relu_mask_v);      // uint32 words under GNNX_GEMM_MASK_BITS
     GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
     GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
@@ -45,8 +53,18 @@ int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t l
     GNNX_REQUIRE(!bits || ld_mask >= (N + 31) / 32, "gemm: packed mask rows need at least ceil(N/32) words");
     GNNX_REQUIRE(!(relu_bits_out && (flags & GNNX_GEMM_ACCUMULATE)), "gemm: relu_bits_out is not available with ACCUMULATE");
     const bool mask_ok = !relu_mask || bits || (((uintptr_t)relu_mask & 15) == 0 && (ld_mask & 3) == 0);
-    if (precision != GNNX_PREC_FP32 && mask_ok && tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision))
-        return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, precision, ws, ws_bytes, st);
+    GNNX_REQUIRE(!(colsum_a_out && ta), "gemm: colsum_a_out needs trans_a = 0");
+    static int use_v1 = -1;
+    if (use_v1 < 0) { const char* e = getenv("GNNX_GEMM_V1"); use_v1 = (e && e[0] == '1') ? 1 : 0; }
+    const bool tc = precision != GNNX_PREC_FP32 && mask_ok && tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
+    const bool fuse_colsum = colsum_a_out && tc && !use_v1 && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
+    if (colsum_a_out && !fuse_colsum) {                    // separate two-pass kernel (same result, one more read of A)
+        int rc = gnnx_colsum(A, lda, M, K, colsum_a_out, ws, ws_bytes, stream);
+        if (rc) return rc;
+    }
+    if (tc)
+        return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out,
+                       fuse_colsum ? colsum_a_out : nullptr, precision, ws, ws_bytes, st);
     return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, ws, ws_bytes, st);
 }
 

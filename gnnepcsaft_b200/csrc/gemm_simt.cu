@@ -272,6 +272,10 @@ __global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, i
     for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
     if (lane == 0) out[c] = s;
 }
+int colsum_final_launch(const float* partial, int nchunks, int cols, float* out, cudaStream_t st) {
+    k_colsum_final<<<ceil_div(cols, 8), 256, 0, st>>>(partial, nchunks, cols, out);
+    return check_launch("colsum_final");
+}
 int colsum_chunks(int64_t rows, int64_t cols) {
     int slabs = ceil_div(cols, 256);
     int target = max(1, (kNumSMs * 4) / slabs);

@@ -25,6 +25,7 @@ namespace gnnx {
 int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* C, long long ldc, const float* bias,
                          int flags, const float* mask, long long ldm, cudaStream_t st);
 int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t* bits, cudaStream_t st);
+int colsum_final_launch(const float* partial, int nchunks, int cols, float* out, cudaStream_t st);
 
 namespace tc {
 
@@ -359,6 +360,8 @@ constexpr int kA2 = 128 * 128;                  // 16 KB
 constexpr int kB2 = 256 * 128;                  // 32 KB
 constexpr int kStage2 = kA2 + kB2;              // 48 KB
 constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes + 256;
+constexpr int kThreads2 = 224;                  // + warp 6: column sums of the A tiles (the bias gradient riding a dX product)
+constexpr int kColsumMaxK = 256;                // columns the fused sum covers (8 k-blocks of accumulators in registers)
 
 struct Smem2 {
     uint8_t* base;
@@ -374,11 +377,11 @@ struct Smem2 {
 };
 
 template <bool kBMN, int kCluster>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads2, 1)
 k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
                   const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
-                  uint32_t* __restrict__ bits_out, long long ldbits) {
+                  uint32_t* __restrict__ bits_out, long long ldbits, float* __restrict__ colsum_partial) {
     extern __shared__ uint8_t smem_raw[];
     Smem2 sm;
     sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -387,7 +390,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages2; ++s) {
             mbar_init(sm.full(s), 1);
-            mbar_init(sm.empty(s), kCluster);
+            mbar_init(sm.empty(s), kCluster + (colsum_partial ? 1 : 0));     // + this CTA's column-sum warp
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(sm.tmem_full(b), 1);
@@ -455,6 +458,54 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     if (kb == KB - 1) mma_commit(sm.tmem_full(buf));
                     if (++stage == kStages2) { stage = 0; phase ^= 1; }
                 }
+            }
+        }
+    } else if (warp == 6) {
+        // Column sums of A over this CTA's row tiles: out[k] = sum_m A[m, k] (rows past M arrive as TMA zero fill).
+        // Lane l reads the 16-byte chunk (l & 7) -- columns 4(l&7)..+3 of the k-block -- of rows (l >> 3), +4, +8, ...;
+        // a stage is released to the producer only after this warp has read it.
+        if (colsum_partial) {
+            float4 acc[kColsumMaxK / kBK];
+#pragma unroll
+            for (int j = 0; j < kColsumMaxK / kBK; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int cj = lane & 7, rr = lane >> 3;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int w = cid; w < work; w += ncl) {
+                const bool first_n = (w % n_tiles) == 0;              // every A tile is loaded once per N tile: count it once
+#pragma unroll
+                for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
+                    if (kb < KB) {
+                        mbar_wait(sm.full(stage), phase);
+                        if (first_n) {
+                            const uint8_t* a = sm.base + stage * kStage2;
+                            float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+#pragma unroll 8
+                            for (int r = rr; r < 128; r += 8) {       // K-major SW128: 16-byte chunk index ^ (row & 7)
+                                const float4 v0 = *reinterpret_cast<const float4*>(a + r * 128 + ((cj ^ (r & 7)) << 4));
+                                const float4 v1 = *reinterpret_cast<const float4*>(a + (r + 4) * 128 + ((cj ^ ((r + 4) & 7)) << 4));
+                                s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+                                s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
+                            }
+                            acc[kb].x += s0.x + s1.x; acc[kb].y += s0.y + s1.y; acc[kb].z += s0.z + s1.z; acc[kb].w += s0.w + s1.w;
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(sm.empty(stage));
+                        if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+#pragma unroll
+            for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
+                float4 v = acc[kb];                                   // fold the four row lanes (fixed order)
+#pragma unroll
+                for (int o = 8; o <= 16; o <<= 1) {
+                    v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                    v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+                }
+                const int col = kb * kBK + cj * 4;
+                if (kb < KB && rr == 0 && col < K)                    // K % 4 == 0 (tc_supported: lda % 4, TMA box)
+                    *reinterpret_cast<float4*>(colsum_partial + (long long)blockIdx.x * K + col) = v;
             }
         }
     } else {
@@ -684,7 +735,7 @@ size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int p
 
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
             int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
-            int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
+            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
     (void)precision;
     static bool attr_done = false;
     if (!attr_done) {
@@ -723,7 +774,7 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         }
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(ncl * cluster);
-        cfg.blockDim = dim3(kThreads);
+        cfg.blockDim = dim3(kThreads2);
         cfg.dynamicSmemBytes = kSmem2;
         cfg.stream = st;
         cudaLaunchAttribute at[1];
@@ -733,15 +784,23 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         const int Mi = (int)M, Ni = (int)N, Ki = (int)K;
         const long long ldc_ = ldc, ldm_ = ldm;
         const long long ldbits = (N + 31) / 32;          // packed masks are row-major: [M, ceil(N/32)] words
+        float* csp = nullptr;                            // per-CTA partial column sums of A (fused bias gradient)
+        if (colsum_a_out) {
+            GNNX_REQUIRE(K <= kColsumMaxK, "gemm_tc: fused column sums cover K <= %d", kColsumMaxK);
+            GNNX_REQUIRE(ws && ws_bytes >= (size_t)ncl * cluster * K * sizeof(float), "gemm_tc: workspace too small for the column-sum partials");
+            csp = (float*)ws;
+        }
         cudaError_t e;
         if (cluster == 2)
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp);
         else
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp);
         if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
-        return check_launch("gemm_tf32_rows2");
+        int rc = check_launch("gemm_tf32_rows2");
+        if (rc == GNNX_OK && csp) rc = colsum_final_launch(csp, ncl * cluster, (int)K, colsum_a_out, st);
+        return rc;
     }
     if (!ta) {
         int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));

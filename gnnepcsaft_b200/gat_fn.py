@@ -59,14 +59,16 @@ class GATv2ConvFn(Function):
         dxlr, datt, ds = ops.gatv2_bwd(dout, out, bias, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
                                        meta.self_loops, meta.dropout_p)
         dl, dr = dxlr[:, :H], dxlr[:, H:]
-        dx = None
-        if ctx.needs_input_grad[0]:
-            dx = ops.gemm(dl, wl)
-            ops.gemm(dr, wr, out=dx, accumulate=True)
+        dx = dbl = dbr = None
+        if ctx.needs_input_grad[0]:                                  # the bias gradients ride the dX products
+            dx, dbl = ops.gemm(dl, wl, want_colsum_a=True)
+            _, dbr = ops.gemm(dr, wr, out=dx, accumulate=True, want_colsum_a=True)
+        else:
+            dbl, dbr = ops.colsum(dl), ops.colsum(dr)
+        dbl = dbl if ctx.has[0] else None
+        dbr = dbr if ctx.has[1] else None
         dwl = ops.gemm(dl, x, trans_a=True)
         dwr = ops.gemm(dr, x, trans_a=True)
-        dbl = ops.colsum(dl) if ctx.has[0] else None
-        dbr = ops.colsum(dr) if ctx.has[1] else None
         dbias = ops.colsum(dout) if ctx.has[2] else None
         table = meta.codes is not None
         de = ops.gatv2_edge_grad(ds, g, H, meta.self_loops, original_order=not table)

@@ -184,11 +184,14 @@ def _ld(t: Tensor) -> int:
 
 def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, bias: Optional[Tensor] = None,
          relu: bool = False, out: Optional[Tensor] = None, accumulate: bool = False,
-         precision: Optional[int] = None, relu_mask: Optional[Tensor] = None, want_relu_bits: bool = False):
+         precision: Optional[int] = None, relu_mask: Optional[Tensor] = None, want_relu_bits: bool = False,
+         want_colsum_a: bool = False):
     """``out = act(op(a) @ op(b) + bias)``; ``a``/``b``/``out`` may be column slices (row stride = ld).
     ``relu_mask`` [M,N]: the result is zeroed where ``relu_mask <= 0`` (fused ReLU backward of the layer below); an
     int32 tensor is taken as the PACKED form (bit c%32 of word [r, c//32] set where the activation was
-    positive) -- int32 [M, ceil(N/32)].  ``want_relu_bits``: also return that packed mask of the result -> ``(out, bits)``."""
+    positive) -- int32 [M, ceil(N/32)].  ``want_relu_bits``: also return that packed mask of the result -> ``(out, bits)``.
+    ``want_colsum_a`` (``trans_a=False``): also return ``a.sum(0)`` -- the bias gradient that goes with a dX product,
+    summed from the operand tiles the kernel already holds -> ``(out, colsum)``."""
     for t, n in ((a, "a"), (b, "b")):
         if not t.is_cuda or t.dtype != torch.float32:
             raise RuntimeError(f"gnnx.gemm: `{n}` must be a CUDA float32 tensor (no CPU fallback exists)")
@@ -220,11 +223,16 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
         else:
             ld_mask = _ld(relu_mask)
     bits = torch.empty((M, words), dtype=torch.int32, device=a.device) if want_relu_bits else None
+    if want_colsum_a and (trans_a or want_relu_bits):
+        raise ValueError("gnnx.gemm: want_colsum_a needs trans_a=False and cannot be combined with want_relu_bits")
+    csum = torch.empty(K, dtype=torch.float32, device=a.device) if want_colsum_a else None
     prec = _default_precision if precision is None else precision
     L = lib()
     ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
     L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),
-           M, N, K, _p(bias), flags, _p(relu_mask), ld_mask, _p(bits), prec, _p(ws), nb, _stream())
+           M, N, K, _p(bias), flags, _p(relu_mask), ld_mask, _p(bits), _p(csum), prec, _p(ws), nb, _stream())
+    if want_colsum_a:
+        return out, csum
     return (out, bits) if want_relu_bits else out
 
 

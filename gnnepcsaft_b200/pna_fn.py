@@ -109,8 +109,7 @@ def _chain_bwd(d: Tensor, acts: List[Tensor], masks, layers):
     for i in range(len(layers) - 1, -1, -1):
         w, _ = layers[i]
         dws[i] = ops.gemm(d, acts[i], trans_a=True)
-        dbs[i] = ops.colsum(d)
-        d = ops.gemm(d, w, relu_mask=masks[i])
+        d, dbs[i] = ops.gemm(d, w, relu_mask=masks[i], want_colsum_a=True)      # db = colsum(d) rides the dX product
     return d, dws, dbs
 
 
@@ -187,10 +186,11 @@ class PNAConvFn(Function):
 
         # lin (fused with the last post Linear when there is one)
         dwf = ops.gemm(dout, os_[-1], trans_a=True)
-        dbf = ops.colsum(dout)
         if pk.post:
             w_last, b_last = pk.post[-1]
             wf = _wprod(wl, w_last)
+            # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
+            d, dbf = ops.gemm(dout, wf, relu_mask=omasks[-1], want_colsum_a=True)
             grads[id(wl)] = _wprod(dwf, w_last, trans_b=True) + torch.outer(dbf, b_last)
             grads[id(bl)] = dbf
             dw_last = _wprod(wl, dwf, trans_a=True)
@@ -199,11 +199,9 @@ class PNAConvFn(Function):
             for t, blk in enumerate(_diag_blocks(dw_last, T)):
                 grads[id(post[t][l_last][0])] = blk
                 grads[id(post[t][l_last][1])] = db_last[t * Fo:(t + 1) * Fo]
-            # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
-            d = ops.gemm(dout, wf, relu_mask=omasks[-1])
         else:
+            d, dbf = ops.gemm(dout, wl, want_colsum_a=True)
             grads[id(wl)], grads[id(bl)] = dwf, dbf
-            d = ops.gemm(dout, wl)
         # post layers 1..post-2 -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
         d, dws, dbs = _chain_bwd(d, os_, omasks, pk.post[:-1])
         for l, (dw, db) in enumerate(zip(dws, dbs), start=1):

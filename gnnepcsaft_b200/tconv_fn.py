@@ -61,14 +61,13 @@ class TransformerConvFn(Function):
         eidx = meta.codes if table else g.csr_eid
         dqkv, de = ops.tconv_bwd(dout, qkv, e, eidx, alpha, agg, g, heads, c, original_order=not table,
                                  dropout_p=meta.dropout_p)
-        dx = None
-        if ctx.needs_input_grad[0]:
-            dx = ops.gemm(dqkv, wqkv)
-            ops.gemm(dout, wskip, out=dx, accumulate=True)
+        if ctx.needs_input_grad[0]:                                  # the bias gradients ride the dX products
+            dx, dbqkv = ops.gemm(dqkv, wqkv, want_colsum_a=True)
+            _, dbskip = ops.gemm(dout, wskip, out=dx, accumulate=True, want_colsum_a=True)
+        else:
+            dx, dbqkv, dbskip = None, ops.colsum(dqkv), ops.colsum(dout)
         dwqkv = ops.gemm(dqkv, x, trans_a=True)                      # [3H, H]
-        dbqkv = ops.colsum(dqkv)
         dwskip = ops.gemm(dout, x, trans_a=True)
-        dbskip = ops.colsum(dout)
         if table:
             de = ops.code_segment_sum(de, meta.codes, efeat.shape[0])
         dwedge = ops.gemm(de, efeat, trans_a=True)

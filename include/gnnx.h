@@ -123,7 +123,12 @@ GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_fe
  *   (1 bit instead of 4 bytes of mask traffic per element; a row's words share one 32-byte sector,
  *   so the one-row-per-thread epilogue misses once per row and then hits L1).  relu_bits_out:
  *   optional [M, ceil(N/32)] uint32 -- the same packing of (C > 0) for the result just computed,
- *   written by a ReLU'd forward product for its own backward.  precision: GNNX_PREC_* below.
+ *   written by a ReLU'd forward product for its own backward.  colsum_a_out: optional [K]
+ *   (trans_a = 0 only): out[k] = sum_m A[m,k] -- the BIAS gradient of the Linear whose input
+ *   gradient this product computes (dX = dY W, db = colsum(dY)); on the tensor-core path with
+ *   K <= 256 it is summed from the A tiles already staged in shared memory (no second read of dY,
+ *   operands as the tensor pipe sees them), otherwise by the two-pass column-sum kernel.
+ *   precision: GNNX_PREC_* below.
  * Split-K (deterministic two-pass) is chosen internally when M*N is small and K large;
  * workspace may be null when gnnx_gemm_workspace_bytes() returns 0. */
 #define GNNX_GEMM_RELU 1
@@ -136,8 +141,8 @@ GNNX_API size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32
                                  int32_t precision);
 GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float* B, int64_t ldb, int32_t trans_b,
               float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags,
-              const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out, int32_t precision, void* workspace,
-              size_t workspace_bytes, void* stream);
+              const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out, float* colsum_a_out,
+              int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);

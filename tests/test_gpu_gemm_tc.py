@@ -159,3 +159,31 @@ def test_packed_relu_bits_produced_and_consumed(prec, M, K, N):
     ops.gemm(dy.to(DEV), w2.to(DEV), out=o1, accumulate=True, relu_mask=y)
     ops.gemm(dy.to(DEV), w2.to(DEV), out=o2, accumulate=True, relu_mask=bits)
     assert torch.equal(o1, o2), "packed-mask accumulate variant differs"
+
+
+@pytest.mark.parametrize("prec", ["tf32", "fp32"])
+@pytest.mark.parametrize("M,K,N,tb", [(101028, 256, 256, False), (3000, 256, 512, False), (1000, 64, 96, True),
+                                      (333, 128, 256, False), (130, 256, 256, False), (5000, 768, 256, False),
+                                      (60, 256, 64, False), (4096, 32, 64, True)])
+def test_fused_column_sums_of_a(prec, M, K, N, tb):
+    """``want_colsum_a``: the bias gradient colsum(dY) delivered by the dX product itself (summed from the staged A
+    tiles on the tensor-core path for K <= 256, by the two-pass kernel otherwise); the product is unchanged."""
+    ops.set_matmul_precision(prec)
+    torch.manual_seed(M + K)
+    a = torch.randn(M, K) + 0.25
+    b = torch.randn(N, K) if tb else torch.randn(K, N)
+    plain = ops.gemm(a.to(DEV), b.to(DEV), trans_b=tb)
+    out, cs = ops.gemm(a.to(DEV), b.to(DEV), trans_b=tb, want_colsum_a=True)
+    assert torch.equal(out, plain)
+    ref = a.double().sum(0)
+    scale = a.double().abs().sum(0)
+    u = U_TF32 if prec == "tf32" else 2.0 ** -24                 # tf32 tier: operands as the tensor pipe sees them
+    assert float(((cs.double().cpu() - ref).abs() / (scale * u * 2 + 1e-6)).max()) <= 1.0
+    y = torch.randn(M, N)
+    prev = torch.randn(M, N)
+    o2 = prev.to(DEV).clone()
+    _, cs2 = ops.gemm(a.to(DEV), b.to(DEV), trans_b=tb, out=o2, accumulate=True, relu_mask=y.to(DEV), want_colsum_a=True)
+    assert torch.equal(cs2, cs), "column sums must not depend on the epilogue variant"
+    o3 = prev.to(DEV).clone()
+    ops.gemm(a.to(DEV), b.to(DEV), trans_b=tb, out=o3, accumulate=True, relu_mask=y.to(DEV))
+    assert torch.equal(o2, o3)
