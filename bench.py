@@ -227,7 +227,19 @@ def _algorithmic_bytes(name, a, N, E, H):
     return None
 
 
-def summarise_roofline(records, N, E, H, peak, peak_src):
+def _measured_traffic(workload):
+    """DRAM bytes per step per entry point from the committed ncu launch list of this workload
+    (profiles/traffic_r1.json, written by scripts/traffic_from_launches.py); {} when there is none."""
+    path = os.path.join(ROOT, "profiles", "traffic_r1.json")
+    if not os.path.exists(path):
+        return {}, None
+    with open(path) as f:
+        doc = json.load(f)
+    w = doc.get(workload)
+    return (w["dram_bytes_per_step"], w["source"]) if w else ({}, None)
+
+
+def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_timed=2):
     agg = {}
     for name, a, ms in records:
         r = _algorithmic_bytes(name, a, N, E, H)
@@ -236,6 +248,7 @@ def summarise_roofline(records, N, E, H, peak, peak_src):
         d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
         d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]
     total_ms = sum(ms for _, _, ms in records)
+    traffic, traffic_src = _measured_traffic(workload)
     kernels = {}
     for name, d in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
         gbs = d["bytes"] / (d["ms"] / 1e3) / 1e9
@@ -243,12 +256,17 @@ def summarise_roofline(records, N, E, H, peak, peak_src):
              "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / peak}
         if d["flops"]:
             k["achieved_TFLOPs"] = d["flops"] / (d["ms"] / 1e3) / 1e12
+        if name in traffic:                               # ncu dram__bytes_{read,write}.sum of the same step, per call
+            k["dram_bytes_per_call"] = traffic[name] * steps_timed / d["calls"]
+            k["algorithmic_bytes_per_call"] = d["bytes"] / d["calls"]
         kernels[name] = k
     top = max(agg.items(), key=lambda kv: kv[1]["ms"])
     name, d = top
     achieved = d["bytes"] / (d["ms"] / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": name + (" (tcgen05 tf32 k_gemm_tf32_rows / k_gemm_tf32_red)" if name == "gnnx_gemm" else ""),
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": (traffic[name] * steps_timed / d["calls"]) if name in traffic else None,
+                "traffic_source": traffic_src,
                 "bytes_per_launch": d["bytes"] / d["calls"], "ms_per_launch": d["ms"] / d["calls"], "launches_timed": d["calls"],
                 "peak_source": peak_src, "nodes": N, "edges": E,
                 "note": "algorithmic bytes of every call of the entry point / CUDA-event time of those calls inside 2 full "
@@ -361,7 +379,7 @@ def run_gpu_arm(args, cfg, target):
     for i in range(2):
         resident_step(i)
     records = lib().stop_timing()
-    roofline, kernels = summarise_roofline(records, N, E, H, peak, peak_src)
+    roofline, kernels = summarise_roofline(records, N, E, H, peak, peak_src, workload=args.workload, steps_timed=2)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
