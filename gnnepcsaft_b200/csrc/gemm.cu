@@ -56,7 +56,11 @@ int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t l
     GNNX_REQUIRE(!(colsum_a_out && ta), "gemm: colsum_a_out needs trans_a = 0");
     static int use_v1 = -1;
     if (use_v1 < 0) { const char* e = getenv("GNNX_GEMM_V1"); use_v1 = (e && e[0] == '1') ? 1 : 0; }
-    const bool tc = precision != GNNX_PREC_FP32 && mask_ok && tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
+    // tiny products (60-row bond tables, weight-space 256^3) are launch-latency-bound: one CTA of the tensor-core
+    // kernel would walk them alone, the 32x32-tile fp32 kernel spreads them over the SMs (and is exact)
+    const bool tiny = (double)M * (double)N * (double)K < 33554432.0;
+    const bool tc = precision != GNNX_PREC_FP32 && !tiny && mask_ok &&
+                    tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
     const bool fuse_colsum = colsum_a_out && tc && !use_v1 && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
     if (colsum_a_out && !fuse_colsum) {                    // separate two-pass kernel (same result, one more read of A)
         int rc = gnnx_colsum(A, lda, M, K, colsum_a_out, ws, ws_bytes, stream);

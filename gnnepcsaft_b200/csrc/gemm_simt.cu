@@ -115,6 +115,82 @@ k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__
     }
 }
 
+// Small products (weight-space W_lin W_last, the 60-row bond tables, the MLP head): 32x32 tiles, K walked in one pass
+// by every block -- ONE launch instead of split-K partials + reduce, which is what these latency-bound shapes need.
+constexpr int SB = 32, SK = 64;
+template <bool TA, bool TB>
+__global__ void __launch_bounds__(256)
+k_gemm_f32_small(const float* __restrict__ A, long long lda, const float* __restrict__ B, long long ldb,
+                 float* __restrict__ C, long long ldc, int M, int N, int K, const float* __restrict__ bias, int flags,
+                 const float* __restrict__ mask, long long ldm) {
+    __shared__ float As[SK][SB + 1];
+    __shared__ float Bs[SK][SB + 1];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * SB, n0 = blockIdx.x * SB;
+    const int tx = tid & 15, ty = tid >> 4;          // 16 x 16 threads, 2 x 2 outputs each (strided by 16)
+    constexpr int kPer = SB * SK / 256;              // elements of each operand tile per thread
+    float ra[kPer], rb[kPer];
+    auto load = [&](int k0) {                        // global -> registers: all loads of a tile in flight together
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int el = tid + i * 256;
+            int m, k;
+            if (TA) { k = el / SB; m = el % SB; } else { m = el / SK; k = el % SK; }
+            const int gm = m0 + m, gk = k0 + k;
+            ra[i] = (gm < M && gk < K) ? (TA ? __ldg(A + (long long)gk * lda + gm) : __ldg(A + (long long)gm * lda + gk)) : 0.f;
+            int n, kb;
+            if (TB) { n = el / SK; kb = el % SK; } else { kb = el / SB; n = el % SB; }
+            const int gn = n0 + n, gkb = k0 + kb;
+            rb[i] = (gn < N && gkb < K) ? (TB ? __ldg(B + (long long)gn * ldb + gkb) : __ldg(B + (long long)gkb * ldb + gn)) : 0.f;
+        }
+    };
+    auto stash = [&]() {                             // registers -> shared
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int el = tid + i * 256;
+            int m, k;
+            if (TA) { k = el / SB; m = el % SB; } else { m = el / SK; k = el % SK; }
+            As[k][m] = ra[i];
+            int n, kb;
+            if (TB) { n = el / SK; kb = el % SK; } else { kb = el / SB; n = el % SB; }
+            Bs[kb][n] = rb[i];
+        }
+    };
+    float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+    load(0);
+    for (int k0 = 0; k0 < K; k0 += SK) {
+        stash();
+        __syncthreads();
+        if (k0 + SK < K) load(k0 + SK);              // next tile's loads overlap this tile's FMAs
+#pragma unroll
+        for (int kk = 0; kk < SK; ++kk) {
+            const float a0 = As[kk][ty], a1 = As[kk][ty + 16], b0 = Bs[kk][tx], b1 = Bs[kk][tx + 16];
+            acc[0][0] = fmaf(a0, b0, acc[0][0]); acc[0][1] = fmaf(a0, b1, acc[0][1]);
+            acc[1][0] = fmaf(a1, b0, acc[1][0]); acc[1][1] = fmaf(a1, b1, acc[1][1]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int gm = m0 + ty + 16 * i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int gn = n0 + tx + 16 * j;
+            if (gn >= N) continue;
+            float v = acc[i][j];
+            if (bias) v += bias[gn];
+            if (flags & GNNX_GEMM_ACCUMULATE) v += C[(long long)gm * ldc + gn];
+            if (mask && !mask_keeps(mask, ldm, flags, gm, gn)) v = 0.f;
+            if (flags & GNNX_GEMM_RELU) v = fmaxf(v, 0.f);
+            C[(long long)gm * ldc + gn] = v;
+        }
+    }
+}
+static bool simt_small(int64_t M, int64_t N, int64_t K) {
+    return K <= 1024 && (long long)ceil_div(M, BM) * ceil_div(N, BN) < kNumSMs && ceil_div(M, SB) <= 65535;
+}
+
 __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ C,
                                 long long ldc, const float* __restrict__ bias, int flags, const float* __restrict__ mask,
                                 long long ldm) {
@@ -150,6 +226,7 @@ int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* 
 }
 
 int simt_splits(int64_t M, int64_t N, int64_t K) {
+    if (simt_small(M, N, K)) return 1;
     long long tiles = (long long)ceil_div(M, BM) * ceil_div(N, BN);
     if (tiles >= kNumSMs || K < 128) return 1;
     long long want = (2ll * kNumSMs + tiles - 1) / tiles;
@@ -188,6 +265,18 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
               int64_t M, int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm,
               uint32_t* bits_out, void* ws, size_t ws_bytes, cudaStream_t st) {
     if (M == 0 || N == 0) return GNNX_OK;
+    if (simt_small(M, N, K)) {
+        dim3 grid(ceil_div(N, SB), ceil_div(M, SB));
+#define LAUNCH_S(TA, TB) k_gemm_f32_small<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, bias, flags, mask, ldm)
+        if (ta && tb) LAUNCH_S(true, true);
+        else if (ta) LAUNCH_S(true, false);
+        else if (tb) LAUNCH_S(false, true);
+        else LAUNCH_S(false, false);
+#undef LAUNCH_S
+        int rc = check_launch("gemm_simt_small");
+        if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
+        return rc;
+    }
     int splits = simt_splits(M, N, K);
     float* partial = nullptr;
     if (splits > 1) {

@@ -156,6 +156,7 @@ class PNAConvFn(Function):
             os_, omasks, wf, bf = [o], [None], wl, bl
         out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
         ctx.meta = meta
+        ctx.pk, ctx.wf = pk, (wf if pk.post else None)     # packed / fused weights of this call, reused by the backward
         ctx.n_hs, ctx.n_os = len(hs), len(os_)
         omasks[0] = None                               # the combine output's own ReLU is undone by combine_bwd
         ctx.mask_slots = [m is not None for m in hmasks + omasks]
@@ -180,7 +181,7 @@ class PNAConvFn(Function):
         hmasks, omasks = masks[:ctx.n_hs], masks[ctx.n_hs:]
         params = saved[pos:]
         we, be, pre, post, wl, bl = _split_params(meta, params)
-        pk = _Packed(meta, pre, post)
+        pk, wf = ctx.pk, ctx.wf
         grads: dict = {}
         dout = _c(dout)
 
@@ -188,7 +189,6 @@ class PNAConvFn(Function):
         dwf = ops.gemm(dout, os_[-1], trans_a=True)
         if pk.post:
             w_last, b_last = pk.post[-1]
-            wf = _wprod(wl, w_last)
             # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
             d, dbf = ops.gemm(dout, wf, relu_mask=omasks[-1], want_colsum_a=True)
             grads[id(wl)] = _wprod(dwf, w_last, trans_b=True) + torch.outer(dbf, b_last)
