@@ -101,10 +101,17 @@ __global__ void k_bn_stats_final(const float* __restrict__ partial, int nchunks,
     const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= C) return;                              // warp-uniform
     Welford t = {0.f, 0.f, 0.f};
-    for (int ch = lane; ch < nchunks; ch += 32) {
-        const float* p = partial + (long long)ch * 3 * C;
-        Welford o = {p[c], p[C + c], p[2 * C + c]};
-        welford_merge(t, o);
+    for (int base = 0; base < nchunks; base += 32 * 8) {           // 24 independent loads in flight, merged in chunk order
+        Welford o[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int ch = base + u * 32 + lane;
+            const float* p = partial + (long long)ch * 3 * C;
+            if (ch < nchunks) { o[u].n = p[c]; o[u].mean = p[C + c]; o[u].m2 = p[2 * C + c]; }
+            else { o[u].n = 0.f; o[u].mean = 0.f; o[u].m2 = 0.f; }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) welford_merge(t, o[u]);
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {

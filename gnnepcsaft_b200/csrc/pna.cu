@@ -125,9 +125,21 @@ __global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* 
     for (int i = threadIdx.x; i < ncodes * 32; i += 32) mine[i] = 0.f;
     __syncwarp();
     int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
-    if (c < H)
-        for (int r = r0 + threadIdx.y; r < r1; r += kCodeRows)
-            mine[(int)codes[r] * 32 + threadIdx.x] += __ldg(dh + (long long)r * H + c);
+    if (c < H) {
+        int r = r0 + threadIdx.y;
+        for (; r + 3 * kCodeRows < r1; r += 4 * kCodeRows) {           // 4 rows in flight; adds stay in row order
+            int cd[4];
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                cd[u] = codes[r + u * kCodeRows];
+                v[u] = __ldcs(dh + (long long)(r + u * kCodeRows) * H + c);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) mine[cd[u] * 32 + threadIdx.x] += v[u];
+        }
+        for (; r < r1; r += kCodeRows) mine[(int)codes[r] * 32 + threadIdx.x] += __ldg(dh + (long long)r * H + c);
+    }
     __syncthreads();
     if (c < H)
         for (int code = threadIdx.y; code < ncodes; code += kCodeRows) {
