@@ -20,7 +20,7 @@ _SCALARS = {
     "int64_t": ctypes.c_int64, "int32_t": ctypes.c_int32, "int": ctypes.c_int,
     "size_t": ctypes.c_size_t, "float": ctypes.c_float,
 }
-_PROTO = re.compile(r"GNNX_API\s+(const\s+char\s*\*|int64_t|int|size_t)\s+(gnnx_\w+)\s*\(([^;]*?)\)\s*;", re.S)
+_PROTO = re.compile(r"GNNX_API\s+(const\s+char\s*\*|int64_t|int32_t|int|size_t)\s+(gnnx_\w+)\s*\(([^;]*?)\)\s*;", re.S)
 
 
 def parse_header(path: Path = HEADER) -> Dict[str, Tuple[object, List[object]]]:

@@ -11,13 +11,21 @@ namespace gnnx {
 size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K);
 int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
               int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
-              void* ws, size_t ws_bytes, cudaStream_t st);
+              void* ws, size_t ws_bytes, cudaStream_t st, const int* bucket_ptr = nullptr, int n_groups = 1);
+int gemm_simt_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
+                          const int* split_table, int S, float* partial, cudaStream_t st);
 bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
                   const void* B, const void* C, int precision);
 size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int precision);
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
             int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
-            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st,
+            const int* bucket_ptr = nullptr, int n_groups = 1);
+int tc_red_grouped_splits(int64_t Mo, int64_t No, int64_t R);
+int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
+                        const int* split_table, int S, float* partial, cudaStream_t st);
+int group_reduce_launch(const float* partial, const int* split_table, int S, const float* coef, int J, long long total,
+                        float* out, cudaStream_t st);
 }  // namespace gnnx
 
 using namespace gnnx;
@@ -39,9 +47,10 @@ size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, in
     return s;
 }
 
-int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
+static int gemm_dispatch(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
               int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, const void* relu_mask_v, int64_t ld_mask,
-              uint32_t* relu_bits_out, float* colsum_a_out, int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+              uint32_t* relu_bits_out, float* colsum_a_out, int32_t precision, void* ws, size_t ws_bytes, void* stream,
+              const int32_t* bucket_ptr, int32_t n_groups) {
     const float* relu_mask = static_cast<const float*>(relu_mask_v);      // uint32 words under GNNX_GEMM_MASK_BITS
     GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
     GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
@@ -59,7 +68,10 @@ int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t l
     // tiny products (60-row bond tables, weight-space 256^3) are launch-latency-bound: one CTA of the tensor-core
     // kernel would walk them alone, the 32x32-tile fp32 kernel spreads them over the SMs (and is exact)
     const bool tiny = (double)M * (double)N * (double)K < 33554432.0;
-    const bool tc = precision != GNNX_PREC_FP32 && !tiny && mask_ok &&
+    // grouped tensor-core products: the row blocks of a 2-CTA cluster share one weight block (256-row buckets), and an
+    // MN-major weight stack [G*K, N] must not let a k-block straddle two groups
+    const bool group_ok = !bucket_ptr || (!use_v1 && (tb || K % 32 == 0));
+    const bool tc = precision != GNNX_PREC_FP32 && !tiny && mask_ok && group_ok &&
                     tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
     const bool fuse_colsum = colsum_a_out && tc && !use_v1 && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
     if (colsum_a_out && !fuse_colsum) {                    // separate two-pass kernel (same result, one more read of A)
@@ -68,8 +80,57 @@ int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t l
     }
     if (tc)
         return gemm_tc(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out,
-                       fuse_colsum ? colsum_a_out : nullptr, precision, ws, ws_bytes, st);
-    return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, ws, ws_bytes, st);
+                       fuse_colsum ? colsum_a_out : nullptr, precision, ws, ws_bytes, st, bucket_ptr, n_groups);
+    return gemm_simt(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, ws, ws_bytes, st,
+                     bucket_ptr, n_groups);
+}
+
+int gnnx_gemm(const float* A, int64_t lda, int32_t ta, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
+              int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags, const void* relu_mask, int64_t ld_mask,
+              uint32_t* relu_bits_out, float* colsum_a_out, int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+    return gemm_dispatch(A, lda, ta, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, colsum_a_out,
+                         precision, ws, ws_bytes, stream, nullptr, 1);
+}
+
+int gnnx_gemm_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int32_t tb, float* C, int64_t ldc,
+                      int64_t M, int64_t N, int64_t K, const int32_t* bucket_ptr, int32_t n_groups, const float* bias,
+                      int32_t flags, const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out, float* colsum_a_out,
+                      int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(bucket_ptr && n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS, "gemm_grouped: 1..%d groups and a bucket_ptr", GNNX_MAX_GROUPS);
+    return gemm_dispatch(A, lda, 0, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, colsum_a_out,
+                         precision, ws, ws_bytes, stream, bucket_ptr, n_groups);
+}
+
+static bool grouped_dw_tc(int64_t Mo, int64_t No, int64_t R, int64_t lda, int64_t ldb, const void* A, const void* B, int precision) {
+    return precision != GNNX_PREC_FP32 && tc_supported(Mo, No, R, 1, 0, lda, ldb, No, A, B, A, precision);
+}
+
+int32_t gnnx_gemm_grouped_dw_splits(int64_t Mo, int64_t No, int64_t R, int32_t n_groups, int32_t precision) {
+    int s = precision != GNNX_PREC_FP32 ? tc_red_grouped_splits(Mo, No, R) : 2 * kNumSMs / (ceil_div(Mo, 128) * ceil_div(No, 128));
+    if (s < n_groups) s = n_groups;                       // every non-empty group needs a split of its own
+    if (s < 1) s = 1;
+    return s;
+}
+
+size_t gnnx_gemm_grouped_dw_workspace_bytes(int64_t Mo, int64_t No, int32_t splits) {
+    return (size_t)splits * Mo * No * sizeof(float);
+}
+
+int gnnx_gemm_grouped_dw(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t R, int64_t Mo, int64_t No,
+                         const int32_t* split_table, int32_t splits, const float* coef, int32_t J, float* out,
+                         int32_t precision, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(A && B && out && split_table && coef, "gemm_grouped_dw: null operand");
+    GNNX_REQUIRE(J >= 1 && J <= 4 && splits >= 1, "gemm_grouped_dw: 1..4 coefficient columns, at least one split");
+    GNNX_REQUIRE((Mo * No) % 4 == 0, "gemm_grouped_dw: Mo * No must be a multiple of 4");
+    GNNX_REQUIRE(ws && ws_bytes >= gnnx_gemm_grouped_dw_workspace_bytes(Mo, No, splits), "gemm_grouped_dw: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    int rc;
+    if (grouped_dw_tc(Mo, No, R, lda, ldb, A, B, precision))
+        rc = gemm_tc_red_grouped(A, lda, B, ldb, Mo, No, R, split_table, splits, (float*)ws, st);
+    else
+        rc = gemm_simt_red_grouped(A, lda, B, ldb, Mo, No, R, split_table, splits, (float*)ws, st);
+    if (rc) return rc;
+    return group_reduce_launch((const float*)ws, split_table, splits, coef, J, (long long)Mo * No, out, st);
 }
 
 }  // extern "C"

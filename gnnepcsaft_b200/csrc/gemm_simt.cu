@@ -15,19 +15,32 @@ __device__ __forceinline__ bool mask_keeps(const float* __restrict__ mask, long 
     return mask[m * ldm + n] > 0.f;
 }
 
+// grouped product: rows are bucketed (bucket_ptr[n_groups+1], boundaries multiples of 128) and row block m0 uses
+// the weight block of its bucket; rows past the last boundary use the last group
+__device__ __forceinline__ int group_offset(const int* __restrict__ bucket_ptr, int n_groups, int m0) {
+    int g = 0;
+    if (bucket_ptr)
+        for (int d = 1; d < n_groups; ++d) g += (m0 >= bucket_ptr[d]) ? 1 : 0;
+    return g;
+}
+
 // element (m,k) of op(A): trans ? A[k*lda + m] : A[m*lda + k]
 template <bool TA, bool TB>
 __global__ void __launch_bounds__(256, 2)
 k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__ B, long long ldb,
            float* __restrict__ C, long long ldc, int M, int N, int K, int k_per_split,
            const float* __restrict__ bias, int flags, float* __restrict__ partial,
-           const float* __restrict__ mask, long long ldm) {
+           const float* __restrict__ mask, long long ldm, const int* __restrict__ bucket_ptr, int n_groups,
+           long long group_stride, const int* __restrict__ split_table) {
     __shared__ float As[2][BK][BM + 4];
     __shared__ float Bs[2][BK][BN + 4];
     const int tid = threadIdx.x;
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    const int kbeg = blockIdx.z * k_per_split;
-    const int kend = min(K, kbeg + k_per_split);
+    // grouped dW: the split's reduction range comes from the per-batch table {begin, end, group}
+    const int kbeg = split_table ? split_table[3 * blockIdx.z] : blockIdx.z * k_per_split;
+    const int kend = split_table ? split_table[3 * blockIdx.z + 1] : min(K, kbeg + k_per_split);
+    if (split_table && kbeg >= kend) return;            // unused split: its partial is never read
+    B += group_offset(bucket_ptr, n_groups, m0) * group_stride;
     const int tx = tid % 16, ty = tid / 16;     // 16x16 threads, each 8x8 outputs (strided by 16 -> conflict-free)
 
     float acc[TM][TN];
@@ -122,11 +135,13 @@ template <bool TA, bool TB>
 __global__ void __launch_bounds__(256)
 k_gemm_f32_small(const float* __restrict__ A, long long lda, const float* __restrict__ B, long long ldb,
                  float* __restrict__ C, long long ldc, int M, int N, int K, const float* __restrict__ bias, int flags,
-                 const float* __restrict__ mask, long long ldm) {
+                 const float* __restrict__ mask, long long ldm, const int* __restrict__ bucket_ptr, int n_groups,
+                 long long group_stride) {
     __shared__ float As[SK][SB + 1];
     __shared__ float Bs[SK][SB + 1];
     const int tid = threadIdx.x;
     const int m0 = blockIdx.y * SB, n0 = blockIdx.x * SB;
+    B += group_offset(bucket_ptr, n_groups, m0) * group_stride;
     const int tx = tid & 15, ty = tid >> 4;          // 16 x 16 threads, 2 x 2 outputs each (strided by 16)
     constexpr int kPer = SB * SK / 256;              // elements of each operand tile per thread
     float ra[kPer], rb[kPer];
@@ -263,11 +278,13 @@ int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t*
 
 int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc,
               int64_t M, int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm,
-              uint32_t* bits_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+              uint32_t* bits_out, void* ws, size_t ws_bytes, cudaStream_t st, const int* bucket_ptr, int n_groups) {
     if (M == 0 || N == 0) return GNNX_OK;
+    // grouped: B stacks one weight block per group -- [G*N, K] rows (tb) or [G*K, N] rows
+    const long long gstride = bucket_ptr ? (tb ? (long long)N * ldb : (long long)K * ldb) : 0;
     if (simt_small(M, N, K)) {
         dim3 grid(ceil_div(N, SB), ceil_div(M, SB));
-#define LAUNCH_S(TA, TB) k_gemm_f32_small<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, bias, flags, mask, ldm)
+#define LAUNCH_S(TA, TB) k_gemm_f32_small<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, bias, flags, mask, ldm, bucket_ptr, n_groups, gstride)
         if (ta && tb) LAUNCH_S(true, true);
         else if (ta) LAUNCH_S(true, false);
         else if (tb) LAUNCH_S(false, true);
@@ -290,7 +307,7 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
     GNNX_REQUIRE(grid.y <= 65535 * 1 || true, "gemm: M too large");
     if (grid.y > 65535) return set_error(GNNX_ERR_UNSUPPORTED, "gemm_simt: M=%lld exceeds grid.y limit", (long long)M);
-#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial, mask, ldm)
+#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial, mask, ldm, bucket_ptr, n_groups, gstride, nullptr)
     if (ta && tb) LAUNCH(true, true);
     else if (ta) LAUNCH(true, false);
     else if (tb) LAUNCH(false, true);
@@ -301,6 +318,15 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     int rc = check_launch("gemm_simt", partial ? 2 : 1);
     if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
     return rc;
+}
+
+// Grouped dW on the fp32 tier: partial[z][Mo,No] = A[rows_z, Mo]^T B[rows_z, No] over the table's row ranges.
+int gemm_simt_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
+                          const int* split_table, int S, float* partial, cudaStream_t st) {
+    dim3 grid(ceil_div(No, BN), ceil_div(Mo, BM), S);
+    k_gemm_f32<true, false><<<grid, 256, 0, st>>>(A, lda, B, ldb, nullptr, 0, (int)Mo, (int)No, (int)R, 0, nullptr, 0, partial,
+                                                  nullptr, 0, nullptr, 1, 0, split_table);
+    return check_launch("gemm_simt_red(grouped)");
 }
 
 // ------------------------------------------------------------------ column sums

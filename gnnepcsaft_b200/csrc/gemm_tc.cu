@@ -381,7 +381,8 @@ __global__ void __launch_bounds__(kThreads2, 1)
 k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
                   const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
-                  uint32_t* __restrict__ bits_out, long long ldbits, float* __restrict__ colsum_partial) {
+                  uint32_t* __restrict__ bits_out, long long ldbits, float* __restrict__ colsum_partial,
+                  const int* __restrict__ bucket_ptr, int n_groups, int group_rows) {
     extern __shared__ uint8_t smem_raw[];
     Smem2 sm;
     sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -420,16 +421,23 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int half = BN / 2;
             for (int w = cid; w < work; w += ncl) {
                 const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
+                // grouped product: the row block's group (bucket boundaries are multiples of 128 * kCluster rows, so both
+                // CTAs of a cluster agree) selects a block of B rows: weights [G * N, K] (K-major) or [G * K, N] (MN-major)
+                int goff = 0;
+                if (bucket_ptr) {
+                    const int mbase = (w / n_tiles) * kCluster * 128;
+                    for (int d = 1; d < n_groups; ++d) goff += (mbase >= __ldg(bucket_ptr + d)) ? group_rows : 0;
+                }
                 for (int kb = 0; kb < KB; ++kb) {
                     mbar_wait(sm.empty(stage), phase ^ 1);
                     mbar_expect_tx(sm.full(stage), tx);
                     tma_load_2d(sm.a(stage), &tmA, sm.full(stage), kb * kBK, m0);
                     if (kCluster == 1) {
-                        if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK, n0 / 32);
-                        else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0);
+                        if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK + goff, n0 / 32);
+                        else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0 + goff);
                     } else {
-                        if (kBMN) tma_load_3d_mc(sm.b(stage) + rank * (half / 32) * 4096, &tmB, sm.full(stage), 0, kb * kBK, n0 / 32 + rank * (half / 32), 3);
-                        else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kb * kBK, n0 + rank * half, 3);
+                        if (kBMN) tma_load_3d_mc(sm.b(stage) + rank * (half / 32) * 4096, &tmB, sm.full(stage), 0, kb * kBK + goff, n0 / 32 + rank * (half / 32), 3);
+                        else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kb * kBK, n0 + rank * half + goff, 3);
                     }
                     if (++stage == kStages2) { stage = 0; phase ^= 1; }
                 }
@@ -544,7 +552,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmP, float* __restrict__ partial, int Mo, int No, int R,
-                int rows_per_split, int BM, int BN) {
+                int rows_per_split, int BM, int BN, const int* __restrict__ split_table) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -552,8 +560,9 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
     const int n_tiles = (No + BN - 1) / BN;
     const int m0 = (blockIdx.x / n_tiles) * BM, n0 = (blockIdx.x % n_tiles) * BN;
-    const int r_begin = blockIdx.y * rows_per_split;
-    const int r_end = min(R, r_begin + rows_per_split);
+    // row range of this split: uniform, or (grouped dW) read from the per-batch split table {begin, end, group}
+    const int r_begin = split_table ? split_table[3 * blockIdx.y] : blockIdx.y * rows_per_split;
+    const int r_end = split_table ? split_table[3 * blockIdx.y + 1] : min(R, r_begin + rows_per_split);
     const int RB = (r_end - r_begin + kBK - 1) / kBK;
     const int halves = BM / 128;
 
@@ -607,7 +616,7 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int h = 0; h < halves; ++h)
                 epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmP, prow + m0 + h * 128, prow + Mo, n0, ncols, nullptr, No, 0, it);
             if (lane == 0) tma_store_wait_all();
-        } else {                                   // empty row range: this split contributes zeros
+        } else if (!split_table) {                 // empty row range: this split contributes zeros (the grouped reduce skips it)
             for (int h = 0; h < halves; ++h)
                 for (int r = q * 32 + lane; r < 128; r += 128) {
                     const int grow = m0 + h * 128 + r;
@@ -735,8 +744,10 @@ size_t tc_workspace_bytes(int64_t M, int64_t N, int64_t K, int ta, int tb, int p
 
 int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, int tb, float* C, int64_t ldc, int64_t M,
             int64_t N, int64_t K, const float* bias, int flags, const float* mask, int64_t ldm, uint32_t* bits_out,
-            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st) {
+            float* colsum_a_out, int precision, void* ws, size_t ws_bytes, cudaStream_t st, const int* bucket_ptr,
+            int n_groups) {
     (void)precision;
+    if (!bucket_ptr) n_groups = 1;
     static bool attr_done = false;
     if (!attr_done) {
         GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
@@ -755,11 +766,12 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         const int m_tiles = ceil_div(M, 128);
         const int cluster = (m_tiles >= 2 && (tb ? (BN % 16 == 0) : (BN % 64 == 0))) ? 2 : 1;
         if (make_map_kmajor(&mA, A, M, K, lda, 128)) return GNNX_ERR_INVALID;
-        if (tb) {
-            if (make_map_kmajor(&mB, B, N, K, ldb, BN / cluster)) return GNNX_ERR_INVALID;
+        if (tb) {                                        // grouped: B stacks one [N, K] / [K, N] weight block per group
+            if (make_map_kmajor(&mB, B, N * n_groups, K, ldb, BN / cluster)) return GNNX_ERR_INVALID;
         } else {
-            if (make_map_mnmajor(&mB, B, K, N, ldb, BN / 32 / cluster)) return GNNX_ERR_INVALID;
+            if (make_map_mnmajor(&mB, B, K * n_groups, N, ldb, BN / 32 / cluster)) return GNNX_ERR_INVALID;
         }
+        const int group_rows = (int)(tb ? N : K);
         if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
         const int work = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
         const int max_cl = kNumSMs / cluster;
@@ -792,17 +804,18 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         }
         cudaError_t e;
         if (cluster == 2)
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows);
         else
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows);
         if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
         int rc = check_launch("gemm_tf32_rows2");
         if (rc == GNNX_OK && csp) rc = colsum_final_launch(csp, ncl * cluster, (int)K, colsum_a_out, st);
         return rc;
     }
     if (!ta) {
+        GNNX_REQUIRE(!bucket_ptr, "gemm_tc: grouped products need the v2 kernel (unset GNNX_GEMM_V1)");
         int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
         if (make_map_kmajor(&mA, A, M, K, lda, 256)) return GNNX_ERR_INVALID;
         if (tb) {
@@ -820,18 +833,41 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
+    GNNX_REQUIRE(!bucket_ptr, "gemm_tc: grouped dW goes through gemm_tc_red_grouped");
     RedPlan p = red_plan(M, N, K);
     GNNX_REQUIRE(ws && ws_bytes >= (size_t)p.splits * M * N * sizeof(float), "gemm_tc: workspace too small for the row-split partials");
     if (make_map_mnmajor(&mA, A, K, M, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, K, N, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, (const float*)ws, (int64_t)p.splits * M, N, N)) return GNNX_ERR_INVALID;
     k_gemm_tf32_red<<<dim3(p.tiles, p.splits), kThreads, kSmemBytes, st>>>(mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
-                                                                          p.rows_per_split, p.BM, p.BN);
+                                                                          p.rows_per_split, p.BM, p.BN, nullptr);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
     rc = splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
     if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
     return rc;
+}
+
+
+// Grouped dW: partial[z][Mo,No] = A[rows_z, Mo]^T B[rows_z, No] for the S row ranges of `split_table` ({begin, end,
+// group} per split; every range lies inside one group and is a multiple of 32 rows; begin == end marks an unused
+// split, whose partial is left unwritten).  The caller folds the partials with per-group coefficients.
+int tc_red_grouped_splits(int64_t Mo, int64_t No, int64_t R) { return red_plan(Mo, No, R).splits; }
+
+int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
+                        const int* split_table, int S, float* partial, cudaStream_t st) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_done = true;
+    }
+    RedPlan p = red_plan(Mo, No, R);
+    CUtensorMap mA, mB, mC;
+    if (make_map_mnmajor(&mA, A, R, Mo, lda, p.BM / 32)) return GNNX_ERR_INVALID;
+    if (make_map_mnmajor(&mB, B, R, No, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
+    if (make_map_store(&mC, partial, (int64_t)S * Mo, No, No)) return GNNX_ERR_INVALID;
+    k_gemm_tf32_red<<<dim3(p.tiles, S), kThreads, kSmemBytes, st>>>(mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
+    return check_launch("gemm_tf32_red(grouped)");
 }
 
 }  // namespace gnnx

@@ -177,16 +177,30 @@ __device__ __forceinline__ void agg_acc(const F4& v, F4& s, F4& s2, F4& mn, F4& 
 
 __global__ void __launch_bounds__(256)
 k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr, int N, int T, int F,
-                    float* __restrict__ agg) {
+                    float* __restrict__ agg, long long ld_agg, const int* __restrict__ row_node, int rows,
+                    const float* __restrict__ x) {
+    // row_node == null: output row i = node i.  Otherwise the kernel walks the `rows` OUTPUT rows (degree-bucket order):
+    // row r holds node row_node[r], or is a padding row (-1) and is zero-filled; with x the node's input row is copied
+    // behind the aggregates ([agg | x], the operand of the degree-grouped post Linear).
     const int H = T * F;
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
-    const long long nwork = (long long)N * chunks;
+    const long long nwork = (long long)(row_node ? rows : N) * chunks;
     const int wpb = blockDim.x >> 5;
     for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
-        int i = (int)(w / chunks);
+        const int r = (int)(w / chunks);
         int c = (int)(w % chunks) * 128 + lane * 4;
         if (c >= H) continue;
+        const int i = row_node ? row_node[r] : r;
+        if (i < 0) {
+            const int t = c / F, f = c % F;
+            float* o = agg + (long long)r * ld_agg + (long long)t * 4 * F + f;
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            stg4_stream(o, z4); stg4_stream(o + F, z4); stg4_stream(o + 2 * F, z4); stg4_stream(o + 3 * F, z4);
+            if (x) stg4_stream(agg + (long long)r * ld_agg + 4 * H + c, z4);
+            continue;
+        }
+        if (x) stg4_stream(agg + (long long)r * ld_agg + 4 * H + c, ldg4(x + (long long)i * H + c));
         int b = rowptr[i], e = rowptr[i + 1];
         F4 s = f4_zero(), s2 = f4_zero(), mn = f4_fill(INFINITY), mx = f4_fill(-INFINITY);
         int k = b;
@@ -221,7 +235,7 @@ k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr,
         }
         if (b == e) { mn = f4_zero(); mx = f4_zero(); }
         int t = c / F, f = c % F;
-        float* o = agg + (((long long)i * T + t) * 4) * F + f;
+        float* o = agg + (long long)r * ld_agg + (long long)t * 4 * F + f;
         stg4_stream(o, mean.q);
         stg4_stream(o + F, mn.q);
         stg4_stream(o + 2 * F, mx.q);
@@ -231,7 +245,10 @@ k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr,
 
 __global__ void __launch_bounds__(256)
 k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m, const float* __restrict__ agg,
-                    const int* __restrict__ rowptr, int N, int T, int F, float* __restrict__ dm) {
+                    const int* __restrict__ rowptr, int N, int T, int F, float* __restrict__ dm, long long ld_agg,
+                    const int* __restrict__ node_pos, float* __restrict__ dx) {
+    // node_pos != null: agg / dagg rows live at node_pos[i] (degree-bucket order, row stride ld_agg); with dx the
+    // gradient of the copied input row ([agg | x] operand) is moved back to node order: dx[i] = dagg[pos, 4H:5H]
     const int H = T * F;
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
@@ -242,9 +259,11 @@ k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m,
         int c = (int)(w % chunks) * 128 + lane * 4;
         if (c >= H) continue;
         int b = rowptr[i], e = rowptr[i + 1];
+        const long long row = node_pos ? node_pos[i] : i;
+        if (dx) stg4(dx + (long long)i * H + c, ldg4_stream(dagg + row * ld_agg + 4 * H + c));
         if (b == e) continue;
         int t = c / F, f = c % F;
-        long long base = (((long long)i * T + t) * 4) * F + f;
+        long long base = row * ld_agg + (long long)t * 4 * F + f;
         F4 mean = f4_lds(agg + base), mn = f4_lds(agg + base + F), mx = f4_lds(agg + base + 2 * F), sd = f4_lds(agg + base + 3 * F);
         F4 gmean = f4_lds(dagg + base), gmn = f4_lds(dagg + base + F), gmx = f4_lds(dagg + base + 2 * F), gsd = f4_lds(dagg + base + 3 * F);
         // pass 1: tie counts for min / max (PyG CPU semantics: gradient split evenly among ties)
@@ -424,8 +443,18 @@ int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t N, int
     GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_fwd: F must be a positive multiple of 4");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((T * F + 127) / 128);
-    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, agg);
+    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, agg, 4ll * T * F, nullptr, 0, nullptr);
     return check_launch("pna_aggregate_fwd");
+}
+
+int gnnx_pna_aggregate_rows_fwd(const float* m, const int32_t* rowptr, int64_t N, int32_t T, int32_t F, const int32_t* row_node,
+                                int64_t rows, const float* x, float* out, int64_t ld_out, void* stream) {
+    GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_rows_fwd: F must be a positive multiple of 4");
+    GNNX_REQUIRE(row_node && ld_out % 4 == 0 && ld_out >= (x ? 5 : 4) * (int64_t)T * F, "pna_aggregate_rows_fwd: row map / stride");
+    if (rows == 0) return GNNX_OK;
+    long long nwork = (long long)rows * ((T * F + 127) / 128);
+    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, out, ld_out, row_node, (int)rows, x);
+    return check_launch("pna_aggregate_rows_fwd");
 }
 
 int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, const int32_t* rowptr, int64_t N,
@@ -433,8 +462,18 @@ int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, 
     GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_bwd: F must be a positive multiple of 4");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((T * F + 127) / 128);
-    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm);
+    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm, 4ll * T * F, nullptr, nullptr);
     return check_launch("pna_aggregate_bwd");
+}
+
+int gnnx_pna_aggregate_rows_bwd(const float* dagg, const float* m, const float* agg, int64_t ld, const int32_t* node_pos,
+                                const int32_t* rowptr, int64_t N, int32_t T, int32_t F, float* dm, float* dx, void* stream) {
+    GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_rows_bwd: F must be a positive multiple of 4");
+    GNNX_REQUIRE(node_pos && ld % 4 == 0 && ld >= (dx ? 5 : 4) * (int64_t)T * F, "pna_aggregate_rows_bwd: row map / stride");
+    if (N == 0) return GNNX_OK;
+    long long nwork = (long long)N * ((T * F + 127) / 128);
+    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm, ld, node_pos, dx);
+    return check_launch("pna_aggregate_rows_bwd");
 }
 
 int gnnx_pna_post_combine_fwd(const float* z, const float* bias, const int32_t* rowptr, float avg_deg_log, int64_t N,

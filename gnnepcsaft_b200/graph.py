@@ -18,17 +18,49 @@ from torch import Tensor
 from . import ops
 
 
+class DegreeBuckets:
+    """Nodes of one batch bucketed by in-degree (``ops.degree_buckets``): the row order of the degree-grouped
+    first post_nn Linear of PNAConv.  Built once per batch, shared by all layers and by the backward."""
+
+    __slots__ = ("n_groups", "node_pos", "row_node", "bucket_ptr", "err_flag", "capacity", "_tables")
+
+    def __init__(self, rowptr: Tensor, n_groups: int):
+        self.n_groups = n_groups
+        self.node_pos, self.row_node, self.bucket_ptr, self.err_flag, self.capacity = ops.degree_buckets(rowptr, n_groups)
+        self._tables = {}
+
+    def split_table(self, splits: int) -> Tensor:
+        t = self._tables.get(splits)
+        if t is None:
+            t = self._tables[splits] = ops.group_split_table(self.bucket_ptr, self.n_groups, splits)
+        return t
+
+
 class GraphIndex:
     """dst-sorted CSR + src-sorted view of one (batched, block-diagonal) ``edge_index``."""
 
     __slots__ = ("num_nodes", "num_edges", "rowptr", "csr_src", "csr_eid", "pos_of_eid", "colptr", "csc_pos",
-                 "csc_dst", "err_flag", "_codes")
+                 "csc_dst", "err_flag", "_codes", "max_degree", "_buckets")
 
     def __init__(self, num_nodes: int, num_edges: int, parts):
         self.num_nodes, self.num_edges = num_nodes, num_edges
         (self.rowptr, self.csr_src, self.csr_eid, self.pos_of_eid, self.colptr, self.csc_pos, self.csc_dst,
          self.err_flag) = parts
         self._codes = None
+        self.max_degree = None        # host-side bound on the in-degree, when the collator knows one
+        self._buckets = None
+
+    def degree_buckets(self) -> Optional[DegreeBuckets]:
+        """In-degree buckets of this batch, or ``None`` when it has more than ``ops.MAX_GROUPS`` degree classes
+        (the caller then takes the general scaler path).  Without a host-side bound from the collator the maximum
+        in-degree is read back once per batch (one device->host sync)."""
+        if self._buckets is None:
+            if self.max_degree is None:
+                mx = torch.zeros(1, dtype=torch.int32, device=self.rowptr.device)
+                ops.degree_hist(self.rowptr, torch.zeros(1, dtype=torch.int64, device=self.rowptr.device), mx)
+                self.max_degree = int(mx.item())
+            self._buckets = DegreeBuckets(self.rowptr, self.max_degree + 1) if self.max_degree < ops.MAX_GROUPS else False
+        return self._buckets or None
 
     @staticmethod
     def build(edge_index: Tensor, num_nodes: int, check: bool = False) -> "GraphIndex":
@@ -107,6 +139,10 @@ class DeviceGraphStore:
         self.node_ptr_host, self.edge_ptr_host = packed.node_ptr, packed.edge_ptr   # numpy, for sizing on the host
         self.num_graphs = packed.num_graphs
         self.device = device
+        # largest in-degree of the dataset, known on the host: every batch buckets its nodes into the same degree classes
+        deg = np.bincount(np.repeat(packed.node_ptr[:-1], np.diff(packed.edge_ptr)) + packed.dst.astype(np.int64),
+                          minlength=int(packed.node_ptr[-1])) if packed.dst.size else np.zeros(1, np.int64)
+        self.max_degree = int(deg.max()) if deg.size else 0
 
     def collate(self, graph_ids: np.ndarray) -> Batch:
         """Block-diagonal batch of the selected molecules, built entirely on the device."""
@@ -122,6 +158,7 @@ class DeviceGraphStore:
         gids = dev_offs[0, :-1].contiguous()
         x, src, dst, ea, batch = ops.collate_packed(self, gids, dev_offs[1], dev_offs[2], N, E)
         index = GraphIndex.build_i32(src, dst, N)
+        index.max_degree = self.max_degree
         graph_ptr = dev_offs[1].to(torch.int32)
         b = Batch(x=x, edge_index=None, edge_attr=ea, batch=batch, num_graphs=int(ids.size), index=index,
                   graph_ptr=graph_ptr, para=self.para[gids], assoc=self.assoc[gids])

@@ -317,6 +317,121 @@ def pna_post_combine_bwd(dout: Tensor, out: Tensor, rowptr: Tensor, avg_deg_log:
     return dz
 
 
+# ------------------------------------------------------------------ degree-grouped first post Linear (PNAConv)
+MAX_GROUPS = 16
+GROUP_ALIGN = 256       # bucket padding: one 2-CTA row block of the tensor-core kernel
+
+
+def degree_buckets(rowptr: Tensor, n_groups: int):
+    """Stable bucketing of the nodes by in-degree -> ``(node_pos[N], row_node[cap], bucket_ptr[n_groups+1], err, cap)``."""
+    _chk(rowptr, torch.int32, "rowptr")
+    if not 1 <= n_groups <= MAX_GROUPS:
+        raise ValueError(f"gnnx.degree_buckets: 1..{MAX_GROUPS} groups")
+    N, dev = rowptr.numel() - 1, rowptr.device
+    cap = _query("gnnx_degree_buckets_capacity", N, n_groups, GROUP_ALIGN)
+    i32 = dict(dtype=torch.int32, device=dev)
+    node_pos, row_node = torch.empty(N, **i32), torch.empty(cap, **i32)
+    bucket_ptr, err = torch.empty(n_groups + 1, **i32), torch.empty(1, **i32)
+    ws, nb = _ws(_query("gnnx_degree_buckets_workspace_bytes", N, n_groups), dev)
+    lib().call("gnnx_degree_buckets", rowptr.data_ptr(), N, n_groups, GROUP_ALIGN, node_pos.data_ptr(), row_node.data_ptr(),
+               cap, bucket_ptr.data_ptr(), err.data_ptr(), _p(ws), nb, _stream())
+    return node_pos, row_node, bucket_ptr, err, cap
+
+
+def group_split_table(bucket_ptr: Tensor, n_groups: int, splits: int) -> Tensor:
+    table = torch.empty((splits, 3), dtype=torch.int32, device=bucket_ptr.device)
+    lib().call("gnnx_group_split_table", bucket_ptr.data_ptr(), n_groups, 32, splits, table.data_ptr(), _stream())
+    return table
+
+
+def pna_aggregate_rows_fwd(m: Tensor, x: Tensor, g, buckets, towers: int) -> Tensor:
+    """``[agg | x]`` in degree-bucket order: [cap, 5H], padding rows zero."""
+    _chk(m, torch.float32, "m"); _chk(x, torch.float32, "x")
+    H = m.shape[1]
+    out = torch.empty((buckets.capacity, 5 * H), dtype=torch.float32, device=m.device)
+    lib().call("gnnx_pna_aggregate_rows_fwd", m.data_ptr(), g.rowptr.data_ptr(), g.num_nodes, towers, H // towers,
+               buckets.row_node.data_ptr(), buckets.capacity, x.data_ptr(), out.data_ptr(), 5 * H, _stream())
+    return out
+
+
+def pna_aggregate_rows_bwd(dax: Tensor, m: Tensor, ax: Tensor, g, buckets, towers: int):
+    """-> ``(dm [E,H], dx [N,H])`` from the gradient of the bucket-ordered ``[agg | x]`` operand."""
+    _chk(dax, torch.float32, "dax"); _chk(m, torch.float32, "m"); _chk(ax, torch.float32, "ax")
+    H = m.shape[1]
+    dm = torch.empty_like(m)
+    dx = torch.empty((g.num_nodes, H), dtype=torch.float32, device=m.device)
+    lib().call("gnnx_pna_aggregate_rows_bwd", dax.data_ptr(), m.data_ptr(), ax.data_ptr(), 5 * H, buckets.node_pos.data_ptr(),
+               g.rowptr.data_ptr(), g.num_nodes, towers, H // towers, dm.data_ptr(), dx.data_ptr(), _stream())
+    return dm, dx
+
+
+def pna_degree_weights(wz: Tensor, wx: Tensor, avg_deg_log: float, n_groups: int):
+    """-> ``(weff [D*Ho, 4H+H], coef [D,3])`` (see include/gnnx.h)."""
+    _chk(wz, torch.float32, "wz"); _chk(wx, torch.float32, "wx")
+    Ho, H = wx.shape
+    K4 = wz.shape[1]
+    weff = torch.empty((n_groups * Ho, K4 + H), dtype=torch.float32, device=wz.device)
+    coef = torch.empty((n_groups, 3), dtype=torch.float32, device=wz.device)
+    lib().call("gnnx_pna_degree_weights", wz.data_ptr(), wx.data_ptr(), Ho, K4, H, float(avg_deg_log), n_groups,
+               weff.data_ptr(), coef.data_ptr(), _stream())
+    return weff, coef
+
+
+def gather_rows(src: Tensor, idx: Tensor, cols: Optional[int] = None, want_relu_bits: bool = False):
+    """``out[r] = src[idx[r], :cols]`` (zero rows where ``idx[r] < 0``); ``src`` may be a column slice."""
+    _chk(idx, torch.int32, "idx")
+    if not src.is_cuda or src.dtype != torch.float32:
+        raise RuntimeError("gnnx.gather_rows: needs a CUDA float32 tensor")
+    cols = src.shape[1] if cols is None else cols
+    rows = idx.numel()
+    out = torch.empty((rows, cols), dtype=torch.float32, device=src.device)
+    bits = torch.empty((rows, (cols + 31) // 32), dtype=torch.int32, device=src.device) if want_relu_bits else None
+    lib().call("gnnx_gather_rows", src.data_ptr(), _ld(src), idx.data_ptr(), rows, cols, out.data_ptr(), cols, _p(bits), _stream())
+    return (out, bits) if want_relu_bits else out
+
+
+def gemm_grouped(a: Tensor, b: Tensor, buckets, *, trans_b: bool, bias: Optional[Tensor] = None, relu: bool = False,
+                 precision: Optional[int] = None, want_colsum_a: bool = False):
+    """``out[rows of bucket g] = act(a @ op(b_g) + bias)``; ``b`` stacks one weight block per group along its rows."""
+    for t, n in ((a, "a"), (b, "b")):
+        if not t.is_cuda or t.dtype != torch.float32:
+            raise RuntimeError(f"gnnx.gemm_grouped: `{n}` must be a CUDA float32 tensor (no CPU fallback exists)")
+    G = buckets.n_groups
+    M, K = a.shape
+    if trans_b:
+        N = b.shape[0] // G
+        ok = b.shape == (G * N, K)
+    else:
+        N = b.shape[1]
+        ok = b.shape == (G * K, N)
+    if not ok or M != buckets.capacity:
+        raise ValueError("gnnx.gemm_grouped: operand shapes do not match the bucket layout")
+    out = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    csum = torch.empty(K, dtype=torch.float32, device=a.device) if want_colsum_a else None
+    prec = _default_precision if precision is None else precision
+    ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, 0, int(trans_b), prec), a.device)
+    lib().call("gnnx_gemm_grouped", a.data_ptr(), _ld(a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), N, M, N, K,
+               buckets.bucket_ptr.data_ptr(), G, _p(bias), GEMM_RELU if relu else 0, None, 0, None, _p(csum), prec,
+               _p(ws), nb, _stream())
+    return (out, csum) if want_colsum_a else out
+
+
+def gemm_grouped_dw(a: Tensor, b: Tensor, buckets, coef: Tensor, precision: Optional[int] = None) -> Tensor:
+    """``out[j] = sum_g coef[g, j] * a[rows_g]^T @ b[rows_g]`` -> [J, Mo, No]."""
+    _chk(a, torch.float32, "a"); _chk(b, torch.float32, "b"); _chk(coef, torch.float32, "coef")
+    R, Mo = a.shape
+    No = b.shape[1]
+    J = coef.shape[1]
+    prec = _default_precision if precision is None else precision
+    S = _query("gnnx_gemm_grouped_dw_splits", Mo, No, R, buckets.n_groups, prec)
+    table = buckets.split_table(S)
+    out = torch.empty((J, Mo, No), dtype=torch.float32, device=a.device)
+    ws, nb = _ws(_query("gnnx_gemm_grouped_dw_workspace_bytes", Mo, No, S), a.device)
+    lib().call("gnnx_gemm_grouped_dw", a.data_ptr(), Mo, b.data_ptr(), No, R, Mo, No, table.data_ptr(), S, coef.data_ptr(), J,
+               out.data_ptr(), prec, _p(ws), nb, _stream())
+    return out
+
+
 def relu_bwd(dy: Tensor, y: Tensor) -> Tensor:
     _chk(dy, torch.float32, "dy"); _chk(y, torch.float32, "y")
     dx = torch.empty_like(dy)

@@ -29,6 +29,10 @@ from . import ops
 from .functional import _c
 
 
+# Degree-grouped first post Linear (include/gnnx.h, csrc/degree_groups.cu): used whenever the batch has at most
+# ops.MAX_GROUPS in-degree classes; False forces the general scaler-folded path (tests compare the two).
+GROUPED_POST = True
+
 # Debug taps: when set to a list, every PNAConv forward appends dict(agg [N, T*4*F], m [E, T*F] dst-sorted, g)
 # (tests read which Std entries were zero-masked and which messages were the min / max of their row).
 CAPTURE_AGG = None
@@ -140,13 +144,28 @@ class PNAConvFn(Function):
         hs, hmasks = _chain_fwd(h, pk.pre, want_masks=train)
         hmasks[0] = hbits
         m = hs[-1]
-        agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
-        if CAPTURE_AGG is not None:
-            CAPTURE_AGG.append(dict(agg=agg, m=m, g=g))
-        z = torch.empty((x.shape[0], 3 * Ho), dtype=torch.float32, device=x.device)
-        ops.gemm(agg, pk.wz, trans_b=True, out=z)
-        ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
-        o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
+        relu0 = meta.post_layers > 1
+        bk = g.degree_buckets() if GROUPED_POST and Ho % 32 == 0 and (T * F) % 32 == 0 else None
+        obits = weff = coef = None
+        if bk is not None:
+            # rows bucketed by in-degree: [agg | x] W_eff(d)^T, one grouped product with a third of the flops
+            agg = ops.pna_aggregate_rows_fwd(m, x, g, bk, T)                       # [cap, 5H], bucket order
+            if CAPTURE_AGG is not None:
+                CAPTURE_AGG.append(dict(agg=ops.gather_rows(agg, bk.node_pos, cols=4 * T * F), m=m, g=g))
+            weff, coef = ops.pna_degree_weights(pk.wz, pk.wx, meta.avg_deg_log, bk.n_groups)
+            o_b = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=relu0)
+            if relu0 and train:
+                o, obits = ops.gather_rows(o_b, bk.node_pos, want_relu_bits=True)   # back to node order
+            else:
+                o = ops.gather_rows(o_b, bk.node_pos)
+        else:
+            agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
+            if CAPTURE_AGG is not None:
+                CAPTURE_AGG.append(dict(agg=agg, m=m, g=g))
+            z = torch.empty((x.shape[0], 3 * Ho), dtype=torch.float32, device=x.device)
+            ops.gemm(agg, pk.wz, trans_b=True, out=z)
+            ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
+            o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=relu0)
         if pk.post:                                   # fold the activation-free last post Linear into `lin`
             w_last, b_last = pk.post[-1]
             os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True, want_masks=train)
@@ -158,7 +177,8 @@ class PNAConvFn(Function):
         ctx.meta = meta
         ctx.pk, ctx.wf = pk, (wf if pk.post else None)     # packed / fused weights of this call, reused by the backward
         ctx.n_hs, ctx.n_os = len(hs), len(os_)
-        omasks[0] = None                               # the combine output's own ReLU is undone by combine_bwd
+        ctx.bk, ctx.weff, ctx.coef = bk, weff, coef
+        omasks[0] = obits                              # general path: the combine output's own ReLU is undone by combine_bwd
         ctx.mask_slots = [m is not None for m in hmasks + omasks]
         ctx.save_for_backward(x, efeat, e1, agg, *hs, *os_, *[m for m in hmasks + omasks if m is not None], *params)
         return out
@@ -208,20 +228,34 @@ class PNAConvFn(Function):
             for t, blk in enumerate(_diag_blocks(dw, T)):
                 grads[id(post[t][l][0])] = blk
                 grads[id(post[t][l][1])] = db[t * Fo:(t + 1) * Fo]
-        # first post Linear with folded scalers
-        dz = ops.pna_post_combine_bwd(d, os_[0], g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
-        dy0 = dz[:, :Ho]
-        dwz = ops.gemm(dz, agg, trans_a=True)                   # [3Ho, 4H]
-        dwx = ops.gemm(dy0, x, trans_a=True)                    # [Ho, H]
-        db0 = ops.colsum(dy0)
-        dagg = ops.gemm(dz, pk.wz)                              # [N, 4H]
+        bk = ctx.bk
+        dxp = None
+        if bk is not None:
+            # degree-grouped first post Linear: d is already masked by the ReLU (packed bits rode the dX product above)
+            dyb = ops.gather_rows(d, bk.row_node)                                   # [cap, Ho] bucket order, padding rows 0
+            dagg, db0 = ops.gemm_grouped(dyb, ctx.weff, bk, trans_b=False, want_colsum_a=True)   # d[agg | x]  [cap, 5H]
+            gw = ops.gemm_grouped_dw(dyb, agg, bk, ctx.coef)                        # [3, Ho, 5H]
+            dwz = gw[:, :, :4 * H].reshape(3 * Ho, 4 * H)
+            dwx = gw[0, :, 4 * H:]
+            dz = dy0 = None
+        else:
+            # first post Linear with folded scalers
+            dz = ops.pna_post_combine_bwd(d, os_[0], g.rowptr, meta.avg_deg_log, relu=meta.post_layers > 1)
+            dy0 = dz[:, :Ho]
+            dwz = ops.gemm(dz, agg, trans_a=True)                   # [3Ho, 4H]
+            dwx = ops.gemm(dy0, x, trans_a=True)                    # [Ho, H]
+            db0 = ops.colsum(dy0)
+            dagg = ops.gemm(dz, pk.wz)                              # [N, 4H]
         for t in range(T):
             cols = [dwx[t * Fo:(t + 1) * Fo, t * F:(t + 1) * F]]
             cols += [dwz[s * Ho + t * Fo:s * Ho + (t + 1) * Fo, t * 4 * F:(t + 1) * 4 * F] for s in range(3)]
             grads[id(post[t][0][0])] = torch.cat(cols, 1)
             grads[id(post[t][0][1])] = db0[t * Fo:(t + 1) * Fo]
         # aggregators
-        dm = ops.pna_aggregate_bwd(dagg, hs[-1], agg, g.rowptr, T)
+        if bk is not None:
+            dm, dxp = ops.pna_aggregate_rows_bwd(dagg, hs[-1], agg, g, bk, T)
+        else:
+            dm = ops.pna_aggregate_bwd(dagg, hs[-1], agg, g.rowptr, T)
         if CAPTURE_BWD is not None:
             CAPTURE_BWD.append(dict(dagg=dagg, dm=dm, m=hs[-1], agg=agg, dz=dz, d_post=d))
         # pre layers 1.. -> gradient at the gather output (ReLU of the first layer fused into the last dX product)
@@ -236,8 +270,11 @@ class PNAConvFn(Function):
             dr = ops.code_segment_sum(dh, meta.codes, efeat.shape[0])
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = ops.gemm(dpq, pk.wpq)
-            ops.gemm(dy0, pk.wx, out=dx, accumulate=True)
+            if dxp is not None:                                 # the x block of d[agg | x], already in node order
+                dx = ops.gemm(dpq, pk.wpq, out=dxp, accumulate=True)
+            else:
+                dx = ops.gemm(dpq, pk.wpq)
+                ops.gemm(dy0, pk.wx, out=dx, accumulate=True)
         dwpq = ops.gemm(dpq, x, trans_a=True)                   # [2H, H]
         dwr = ops.gemm(dr, e1, trans_a=True)                    # [H, F]
         dbr = ops.colsum(dr)

@@ -199,6 +199,68 @@ GNNX_API int gnnx_pna_post_combine_bwd(const float* dout, const float* out, cons
                               float avg_deg_log, int64_t num_nodes, int32_t h_out, int32_t relu, float* dz,
                               void* stream);
 
+/* ------------------------------------------------------------------ degree-grouped first post_nn Linear (PNAConv) */
+/* Replaces the same reference code as gnnx_pna_post_combine_* -- DegreeScalerAggregation's scalers
+ * (models.py:443-449; PyG R5) followed by post_nn[0] (R6) -- for batches with at most
+ * GNNX_MAX_GROUPS distinct in-degree classes (molecules: 0..4).  The scalers depend on the
+ * in-degree d only, so for every row of in-degree d
+ *     [x | agg | s_amp(d) agg | s_att(d) agg] W^T = [agg | x] W_eff(d)^T,
+ *     W_eff(d) = [W_id + s_amp(d) W_amp + s_att(d) W_att | W_x]          ([h_out, 4H + H])
+ * and with the node rows bucketed by in-degree the product is ONE grouped GEMM with a third of
+ * the flops of the K = 13F formulation and no [N, 3H] intermediate.
+ *
+ * gnnx_degree_buckets: stable bucketing of the nodes by in-degree (degrees >= n_groups are
+ * clamped into the last bucket and raise *err_flag -- the caller must then use the general path).
+ * Bucket d occupies rows bucket_ptr[d]..bucket_ptr[d+1] of the bucket order, each bucket padded to
+ * a multiple of `align` rows (256: one 2-CTA row block of the tensor-core kernel);
+ *   node_pos[N]      bucket-order row of node i
+ *   row_node[cap]    node held by bucket-order row r, -1 for padding rows
+ *   bucket_ptr[n_groups+1]
+ * capacity >= gnnx_degree_buckets_capacity(N, n_groups, align) rows (host-side bound). */
+#define GNNX_MAX_GROUPS 16
+GNNX_API int64_t gnnx_degree_buckets_capacity(int64_t num_nodes, int32_t n_groups, int32_t align);
+GNNX_API size_t gnnx_degree_buckets_workspace_bytes(int64_t num_nodes, int32_t n_groups);
+GNNX_API int gnnx_degree_buckets(const int32_t* rowptr, int64_t num_nodes, int32_t n_groups, int32_t align,
+                        int32_t* node_pos, int32_t* row_node, int64_t capacity, int32_t* bucket_ptr,
+                        int32_t* err_flag, void* workspace, size_t workspace_bytes, void* stream);
+/* Fused multi-aggregator written in bucket order: out row r = [mean|min|max|std per tower (4H) | x[node] (H, only
+ * if x != null)] of node row_node[r]; padding rows are zero-filled.  `rows` = the bucket capacity. */
+GNNX_API int gnnx_pna_aggregate_rows_fwd(const float* m, const int32_t* rowptr, int64_t num_nodes, int32_t towers, int32_t f,
+                                const int32_t* row_node, int64_t rows, const float* x, float* out, int64_t ld_out,
+                                void* stream);
+/* Backward of the above: agg / dagg are read at row node_pos[i] (row stride ld); dm as gnnx_pna_aggregate_bwd;
+ * dx (optional, [N,H]) receives dagg[node_pos[i], 4H:5H] -- the gradient of the copied input row in node order. */
+GNNX_API int gnnx_pna_aggregate_rows_bwd(const float* dagg, const float* m, const float* agg, int64_t ld,
+                                const int32_t* node_pos, const int32_t* rowptr, int64_t num_nodes, int32_t towers,
+                                int32_t f, float* dm, float* dx, void* stream);
+/* weff[d] = [wz[0:Ho] + s_amp(d) wz[Ho:2Ho] + s_att(d) wz[2Ho:3Ho] | wx] for d = 0..n_groups-1 (wz [3Ho, k_agg],
+ * wx [Ho, h_in]; s_amp = log(d+1)/avg_deg_log, s_att = avg_deg_log/log(max(d,1)+1));  coef[d] = (1, s_amp, s_att). */
+GNNX_API int gnnx_pna_degree_weights(const float* wz, const float* wx, int32_t h_out, int32_t k_agg, int32_t h_in,
+                            float avg_deg_log, int32_t n_groups, float* weff, float* coef, void* stream);
+/* out[r,:] = idx[r] >= 0 ? src[idx[r],:] : 0 -- moves rows between node order and bucket order (idx = node_pos
+ * or row_node); relu_bits_out: optional packed (out > 0) mask [rows, ceil(cols/32)] (GNNX_GEMM_MASK_BITS layout). */
+GNNX_API int gnnx_gather_rows(const float* src, int64_t ld_src, const int32_t* idx, int64_t rows, int32_t cols, float* out,
+                     int64_t ld_out, uint32_t* relu_bits_out, void* stream);
+/* Grouped product C[M,N] = epilogue(A[M,K] op(B_g)): row block [bucket_ptr[g], bucket_ptr[g+1]) uses weight block g
+ * of B = [n_groups * N, K] (trans_b = 1) or [n_groups * K, N] (trans_b = 0); rows past bucket_ptr[n_groups] use the
+ * last block.  Bucket boundaries must be multiples of 256 rows.  Everything else as gnnx_gemm (trans_a = 0);
+ * workspace as gnnx_gemm_workspace_bytes(M, N, K, 0, trans_b, precision). */
+GNNX_API int gnnx_gemm_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int32_t trans_b, float* C, int64_t ldc,
+                      int64_t M, int64_t N, int64_t K, const int32_t* bucket_ptr, int32_t n_groups, const float* bias,
+                      int32_t flags, const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out,
+                      float* colsum_a_out, int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
+/* Grouped dW: out[j] = sum_g coef[g, j] * A[rows_g, Mo]^T B[rows_g, No]  (j < J <= 4; out [J, Mo, No]).
+ * The R rows are cut into `splits` ranges by gnnx_group_split_table (each inside one bucket, a multiple of `unit`
+ * = 32 rows; table int32 [splits, 3] = {begin, end, group}); partials are folded in split order (deterministic).
+ * splits = gnnx_gemm_grouped_dw_splits(...); workspace = gnnx_gemm_grouped_dw_workspace_bytes(Mo, No, splits). */
+GNNX_API int32_t gnnx_gemm_grouped_dw_splits(int64_t Mo, int64_t No, int64_t R, int32_t n_groups, int32_t precision);
+GNNX_API size_t gnnx_gemm_grouped_dw_workspace_bytes(int64_t Mo, int64_t No, int32_t splits);
+GNNX_API int gnnx_group_split_table(const int32_t* bucket_ptr, int32_t n_groups, int32_t unit, int32_t splits,
+                           int32_t* table, void* stream);
+GNNX_API int gnnx_gemm_grouped_dw(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t R, int64_t Mo, int64_t No,
+                         const int32_t* split_table, int32_t splits, const float* coef, int32_t J, float* out,
+                         int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
+
 /* dx = dy * (y > 0) elementwise (ReLU backward between Linear layers). */
 GNNX_API int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream);
 

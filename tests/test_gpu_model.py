@@ -16,6 +16,7 @@ import torch
 
 import gnnepcsaft_b200 as G
 from gnnepcsaft_b200 import gat_fn, graph, nn as gnn, ops, pna_fn, tconv_fn
+from gnnepcsaft_b200._lib import lib
 from oracle import pyg_restated as O
 from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_as_accurate, assert_close, deg_hist, make_batch, branches_from
 
@@ -83,13 +84,19 @@ def _conv_pair(make_o, make_p, b, H, seed=0):
     _grads_close(cp, co, co64, 1e-4)
 
 
-@pytest.mark.parametrize("H,T,pre,post", [(64, 1, 2, 4), (64, 4, 1, 1), (128, 8, 3, 2), (256, 1, 2, 4), (48, 2, 4, 3)])
-def test_pnaconv_dense_edge_attr(H, T, pre, post):
+@pytest.mark.parametrize("grouped", [True, False])
+@pytest.mark.parametrize("H,T,pre,post", [(64, 1, 2, 4), (64, 4, 1, 1), (128, 8, 3, 2), (256, 1, 2, 4), (48, 2, 4, 3), (64, 2, 2, 2)])
+def test_pnaconv_dense_edge_attr(H, T, pre, post, grouped, monkeypatch):
+    """grouped: the degree-bucketed first post Linear ([agg | x] W_eff(d)^T, csrc/degree_groups.cu); otherwise the
+    general scaler-folded path (also what H = 48 takes: its width is not a multiple of 32)."""
+    monkeypatch.setattr(pna_fn, "GROUPED_POST", grouped)
     graphs, b = make_batch(24, seed=31)
     deg = torch.tensor(deg_hist(graphs))
     kw = dict(in_channels=H, out_channels=H, aggregators=AGG, scalers=SCA, deg=deg, edge_dim=H, towers=T,
               pre_layers=pre, post_layers=post, divide_input=True)
+    n0 = lib().launch_count()
     _conv_pair(lambda: O.PNAConv(**kw), lambda: gnn.PNAConv(**kw), b, H)
+    assert lib().launch_count() > n0
 
 
 @pytest.mark.parametrize("H,heads,loops", [(64, 2, True), (64, 8, True), (256, 2, True), (256, 1, True), (128, 4, False), (512, 2, True)])
