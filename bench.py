@@ -191,6 +191,18 @@ def _algorithmic_bytes(name, a, N, E, H):
         if mask:
             byts += (M * Nn / 8.0) if (flags & 4) else 4.0 * M * Nn      # packed (1 bit / element) or fp32 mask
         return byts, 2.0 * M * Nn * K
+    if name == "gnnx_gemm_grouped":               # degree-grouped product: one weight block per in-degree class
+        M, Nn, K, G, flags = a[7], a[8], a[9], a[11], a[13]
+        return 4.0 * (M * K + G * Nn * K + M * Nn), 2.0 * M * Nn * K
+    if name == "gnnx_gemm_grouped_dw":            # both operands read once, J weighted sums written
+        R, Mo, No, J = a[4], a[5], a[6], a[10]
+        return 4.0 * (R * (Mo + No) + J * Mo * No), 2.0 * R * Mo * No
+    if name == "gnnx_pna_aggregate_rows_fwd":     # as aggregate_fwd + the x row copied behind the aggregates ([agg | x])
+        return 4.0 * E * H + 24.0 * N * H + 8.0 * N, 0.0
+    if name == "gnnx_pna_aggregate_rows_bwd":     # as aggregate_bwd + the x block of d[agg | x] moved to node order
+        return 8.0 * E * H + 40.0 * N * H + 4.0 * N, 0.0
+    if name == "gnnx_gather_rows":                # rows moved between node order and degree-bucket order
+        return 8.0 * a[3] * a[4] + 4.0 * a[3], 0.0
     if name == "gnnx_pna_aggregate_fwd":          # read messages once, write the four aggregates (4EH + 16NH + 4N)
         return 4.0 * E * H + 16.0 * N * H + 4.0 * N, 0.0
     if name == "gnnx_pna_aggregate_bwd":          # 8EH + 32NH
@@ -245,6 +257,8 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
         r = _algorithmic_bytes(name, a, N, E, H)
         if r is None:
             continue
+        if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw"):   # same kernels as gnnx_gemm (k_gemm_tf32_rows2 / _red)
+            name = "gnnx_gemm"
         d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
         d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]
     total_ms = sum(ms for _, _, ms in records)
@@ -256,8 +270,9 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
              "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / peak}
         if d["flops"]:
             k["achieved_TFLOPs"] = d["flops"] / (d["ms"] / 1e3) / 1e12
-        if name in traffic:                               # ncu dram__bytes_{read,write}.sum of the same step, per call
-            k["dram_bytes_per_call"] = traffic[name] * steps_timed / d["calls"]
+        tname = name.replace("_rows", "")                 # the bucket-order aggregate entry points share the kernels
+        if tname in traffic:                              # ncu dram__bytes_{read,write}.sum of the same step, per call
+            k["dram_bytes_per_call"] = traffic[tname] * steps_timed / d["calls"]
             k["algorithmic_bytes_per_call"] = d["bytes"] / d["calls"]
         kernels[name] = k
     top = max(agg.items(), key=lambda kv: kv[1]["ms"])

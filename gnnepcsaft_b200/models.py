@@ -18,7 +18,7 @@ from torch.nn import BatchNorm1d, Dropout, Linear, Module, ModuleList, ReLU, Seq
 
 from . import functional as Fn
 from . import nn as gnn
-from . import ops
+from . import ops, streams
 from .graph import Batch, batch_from_reference_tensors
 
 
@@ -82,6 +82,7 @@ class GNNePCSAFT(Module):
             Linear(h // 4, config["num_para"]),
         )
         self._bounds_dev = None
+        self._prep_cache = None
 
     # -- reference signature -------------------------------------------------------------
     def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Union[Tensor, None],
@@ -98,11 +99,13 @@ class GNNePCSAFT(Module):
         g = b.index
         x_idx = b.x if b.x.dtype == torch.uint8 else ops.narrow_u8(b.x)
         ea_u8 = b.edge_attr if b.edge_attr.dtype == torch.uint8 else ops.narrow_u8(b.edge_attr)
-        x = self.node_embed(x_idx)
         edges = self.edge_embed.forward_table(ops.edge_codes(ea_u8.contiguous(), g.csr_eid))
-        for conv, batch_norm in zip(self.convs, self.batch_norms):
+        preps = self._prepare_convs(edges, g)
+        x = self.node_embed(x_idx)
+        for conv, batch_norm, prep in zip(self.convs, self.batch_norms, preps):
             x = self.dropout(x)
-            x = batch_norm(conv(x, b.edge_index, edges, index=g), relu=True)
+            out = conv(x, b.edge_index, edges, index=g) if prep is None else conv(x, b.edge_index, edges, index=g, prep=prep)
+            x = batch_norm(out, relu=True)
         if b.batch is not None or b.graph_ptr is not None:
             x = self.global_pool(x, ptr=b.graph_ptr)
         else:
@@ -110,6 +113,38 @@ class GNNePCSAFT(Module):
             ptr = torch.tensor([0, n], dtype=torch.int32, device=x.device)
             x = Fn.segment_pool(x, ptr, self.global_pool_type)
         return self._head(x)
+
+    def _prepare_convs(self, edges, g):
+        """Queue the parameter-only work of every PNAConv layer (fused / packed weights, the 60-row edge-term tables,
+        the per-degree weights) on the side stream, ahead of the layer loop: ~5 tiny kernels per layer that would
+        otherwise each cost a launch latency between the HBM-bound kernels.  Each layer waits on its own event.
+        Without gradients and outside training the result is kept until a parameter changes (bulk screening runs
+        thousands of batches on fixed weights)."""
+        L = len(self.convs)
+        sd = streams.side(edges.table.device)
+        if sd is None or not all(isinstance(c, gnn.PNAConv) for c in self.convs):
+            return [None] * L
+        reuse = not torch.is_grad_enabled() and not self.training
+        if not reuse and not streams.PREP_AHEAD:
+            return [None] * L
+        key = None
+        if reuse:
+            bk = g.degree_buckets()
+            key = (ops.param_epoch(), bk.n_groups if bk is not None else 0) + tuple(
+                (p.data_ptr(), p._version) for m in (self.convs, self.edge_embed) for p in m.parameters())
+            if self._prep_cache is not None and self._prep_cache[0] == key:
+                return self._prep_cache[1]
+        sd.begin()
+        try:
+            preps = []
+            for conv in self.convs:
+                p = conv.prepare(edges.table.detach(), g)
+                p.event = sd.mark()
+                preps.append(p)
+        finally:
+            sd.end()
+        self._prep_cache = (key, preps) if reuse else None
+        return preps
 
     def _head(self, x: Tensor) -> Tensor:
         m = self.mlp

@@ -20,7 +20,7 @@ from . import ops
 from .functional import EdgeTable
 from .gat_fn import GATMeta, GATv2ConvFn
 from .graph import GraphIndex, graph_index_for
-from .pna_fn import PNAConvFn, PNAMeta
+from .pna_fn import PNAConvFn, PNAMeta, grouped_ok, prepare as pna_prepare
 from .tconv_fn import TConvMeta, TransformerConvFn
 
 ATOM_FEATURE_DIMS = (119, 5, 12, 12, 10, 6, 6, 2, 2)   # gnnepcsaft/data/ogb_utils.py:9-23
@@ -232,16 +232,26 @@ class PNAConv(Module):
                     ps += [m.weight, m.bias]
         return ps + [self.lin.weight, self.lin.bias]
 
+    def _meta(self, g, codes, prep=None) -> PNAMeta:
+        return PNAMeta(g, codes, self.towers, self.F_in, self.F_out, self.pre_layers, self.post_layers,
+                       self.aggr_module.avg_deg_log_value(), prep)
+
+    def prepare(self, table: Optional[Tensor], g: GraphIndex):
+        """The parameter-only part of a call (``pna_fn.PNAPrep``), computed ahead of it -- GNNePCSAFT queues this for
+        all its layers on the side stream.  ``table``: the factored bond-feature table, ``g``: the batch's index."""
+        meta = self._meta(g, None)
+        bk = g.degree_buckets() if grouped_ok(meta) else None
+        with torch.no_grad():
+            return pna_prepare(meta, self._flat_params(), table, bk.n_groups if bk is not None else 0)
+
     def forward(self, x: Tensor, edge_index: Optional[Tensor], edge_attr: Union[Tensor, EdgeTable, None] = None,
-                index: Optional[GraphIndex] = None) -> Tensor:
+                index: Optional[GraphIndex] = None, prep=None) -> Tensor:
         _require_cuda(x, "PNAConv")
         if x.dim() != 2 or x.shape[1] != self.in_channels:
             raise ValueError(f"PNAConv: x must be [N, {self.in_channels}], got {tuple(x.shape)}")
         g = index if index is not None else graph_index_for(edge_index, x.shape[0])
         efeat, codes = _resolve_edges(edge_attr, self.edge_dim, g, "PNAConv")
-        meta = PNAMeta(g, codes, self.towers, self.F_in, self.F_out, self.pre_layers, self.post_layers,
-                       self.aggr_module.avg_deg_log_value())
-        return PNAConvFn.apply(x, efeat, meta, *self._flat_params())
+        return PNAConvFn.apply(x, efeat, self._meta(g, codes, prep), *self._flat_params())
 
 
 # ------------------------------------------------------------------ GATv2

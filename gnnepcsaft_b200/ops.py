@@ -604,6 +604,15 @@ def relhuber_fwd_bwd(pred: Tensor, target: Tensor, delta: float = 0.01, want_gra
     return out2, dpred
 
 
+_param_epoch = 0
+
+
+def param_epoch() -> int:
+    """Bumped whenever a gnnx kernel rewrites parameters in place (the optimizer step works on raw pointers, so
+    ``Tensor._version`` does not move); caches of parameter-derived tensors key on it."""
+    return _param_epoch
+
+
 def adamw_amsgrad_(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Tensor, max_exp_avg_sq: Tensor, *, lr: float,
                    beta1: float, beta2: float, eps: float, weight_decay: float, step: int, grad_scale: float = 1.0) -> None:
     for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq"), (max_exp_avg_sq, "max_exp_avg_sq")):
@@ -611,3 +620,5 @@ def adamw_amsgrad_(param: Tensor, grad: Tensor, exp_avg: Tensor, exp_avg_sq: Ten
     lib().call("gnnx_adamw_amsgrad", param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
                max_exp_avg_sq.data_ptr(), param.numel(), float(lr), float(beta1), float(beta2), float(eps),
                float(weight_decay), int(step), float(grad_scale), _stream())
+    global _param_epoch
+    _param_epoch += 1

@@ -42,11 +42,12 @@ CAPTURE_BWD = None
 class PNAMeta:
     """Non-tensor arguments of one PNAConv call."""
 
-    __slots__ = ("g", "codes", "towers", "f_in", "f_out", "pre_layers", "post_layers", "avg_deg_log")
+    __slots__ = ("g", "codes", "towers", "f_in", "f_out", "pre_layers", "post_layers", "avg_deg_log", "prep")
 
-    def __init__(self, g, codes, towers, f_in, f_out, pre_layers, post_layers, avg_deg_log):
+    def __init__(self, g, codes, towers, f_in, f_out, pre_layers, post_layers, avg_deg_log, prep=None):
         self.g, self.codes, self.towers, self.f_in, self.f_out = g, codes, towers, f_in, f_out
         self.pre_layers, self.post_layers, self.avg_deg_log = pre_layers, post_layers, avg_deg_log
+        self.prep = prep              # parameter-only tensors computed ahead of the call (PNAPrep), or None
 
 
 def _split_params(meta: PNAMeta, params):
@@ -122,18 +123,61 @@ def _diag_blocks(m: Tensor, T: int) -> List[Tensor]:
     return [m[t * r:(t + 1) * r, t * c:(t + 1) * c] for t in range(T)]
 
 
+def grouped_ok(meta: PNAMeta) -> bool:
+    """Widths the degree-grouped tensor-core products take (32-column operand chunks)."""
+    return GROUPED_POST and (meta.towers * meta.f_out) % 32 == 0 and (meta.towers * meta.f_in) % 32 == 0
+
+
+class PNAPrep:
+    """Everything a PNAConv call derives from its PARAMETERS alone (and the 60-row bond table): packed weights, the
+    edge-encoder tables, the fused ``W_lin W_last`` weight and the per-degree weights.  Computed inline by the call, or
+    ahead of it on the side stream (``event`` then marks its completion) -- GNNePCSAFT prepares all layers at once."""
+
+    __slots__ = ("pk", "e1", "r", "wf", "bf", "weff", "coef", "n_groups", "event")
+
+
+def prepare(meta: PNAMeta, params, table: Tensor = None, n_groups: int = 0) -> PNAPrep:
+    """``table``: the bond-feature table [codes, edge_dim] when the edge features are factored (else the edge terms
+    are per-edge products and stay with the call); ``n_groups`` > 0: also the per-degree weights of the grouped path."""
+    we, be, pre, post, wl, bl = _split_params(meta, params)
+    p = PNAPrep()
+    p.pk = pk = _Packed(meta, pre, post)
+    p.e1 = p.r = p.weff = p.coef = p.event = None
+    p.n_groups = n_groups
+    if table is not None:
+        # edge term: edge_encoder, then the e' block of the first pre_nn Linear (+ its bias); 60 rows in table form
+        p.e1 = ops.gemm(table, we, trans_b=True, bias=be)
+        p.r = ops.gemm(p.e1, pk.wr, trans_b=True, bias=pk.br)
+    if pk.post:                                       # fold the activation-free last post Linear into `lin`
+        w_last, b_last = pk.post[-1]
+        p.wf = _wprod(wl, w_last)
+        p.bf = _wprod(wl, b_last.unsqueeze(1)).squeeze(1) + bl
+    else:
+        p.wf, p.bf = wl, bl
+    if n_groups:
+        p.weff, p.coef = ops.pna_degree_weights(pk.wz, pk.wx, meta.avg_deg_log, n_groups)
+    return p
+
+
 class PNAConvFn(Function):
     @staticmethod
     def forward(ctx, x, efeat, meta: PNAMeta, *params):
         g, T, F, Fo = meta.g, meta.towers, meta.f_in, meta.f_out
         Ho = T * Fo
         we, be, pre, post, wl, bl = _split_params(meta, params)
-        pk = _Packed(meta, pre, post)
         x = _c(x)
         efeat = _c(efeat)
-        # edge term: edge_encoder, then the e' block of the first pre_nn Linear (+ its bias); 60 rows in table form
-        e1 = ops.gemm(efeat, we, trans_b=True, bias=be)
-        r = ops.gemm(e1, pk.wr, trans_b=True, bias=pk.br)
+        bk = g.degree_buckets() if grouped_ok(meta) else None
+        prep = meta.prep
+        if prep is None or prep.n_groups != (bk.n_groups if bk is not None else 0):
+            prep = prepare(meta, params, efeat if meta.codes is not None else None, bk.n_groups if bk is not None else 0)
+        elif prep.event is not None:
+            torch.cuda.current_stream().wait_event(prep.event)
+        pk = prep.pk
+        e1, r = prep.e1, prep.r
+        if e1 is None:                                # dense edge features: per-edge products
+            e1 = ops.gemm(efeat, we, trans_b=True, bias=be)
+            r = ops.gemm(e1, pk.wr, trans_b=True, bias=pk.br)
         pq = ops.gemm(x, pk.wpq, trans_b=True)
         ridx = meta.codes if meta.codes is not None else g.csr_eid
         train = any(ctx.needs_input_grad)             # False under no_grad: no ReLU masks to keep
@@ -145,14 +189,12 @@ class PNAConvFn(Function):
         hmasks[0] = hbits
         m = hs[-1]
         relu0 = meta.post_layers > 1
-        bk = g.degree_buckets() if GROUPED_POST and Ho % 32 == 0 and (T * F) % 32 == 0 else None
-        obits = weff = coef = None
+        obits, weff, coef = None, prep.weff, prep.coef
         if bk is not None:
             # rows bucketed by in-degree: [agg | x] W_eff(d)^T, one grouped product with a third of the flops
             agg = ops.pna_aggregate_rows_fwd(m, x, g, bk, T)                       # [cap, 5H], bucket order
             if CAPTURE_AGG is not None:
                 CAPTURE_AGG.append(dict(agg=ops.gather_rows(agg, bk.node_pos, cols=4 * T * F), m=m, g=g))
-            weff, coef = ops.pna_degree_weights(pk.wz, pk.wx, meta.avg_deg_log, bk.n_groups)
             o_b = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=relu0)
             if relu0 and train:
                 o, obits = ops.gather_rows(o_b, bk.node_pos, want_relu_bits=True)   # back to node order
@@ -166,13 +208,11 @@ class PNAConvFn(Function):
             ops.gemm(agg, pk.wz, trans_b=True, out=z)
             ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
             o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=relu0)
-        if pk.post:                                   # fold the activation-free last post Linear into `lin`
-            w_last, b_last = pk.post[-1]
+        wf, bf = prep.wf, prep.bf
+        if pk.post:
             os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True, want_masks=train)
-            wf = _wprod(wl, w_last)
-            bf = _wprod(wl, b_last.unsqueeze(1)).squeeze(1) + bl
         else:
-            os_, omasks, wf, bf = [o], [None], wl, bl
+            os_, omasks = [o], [None]
         out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
         ctx.meta = meta
         ctx.pk, ctx.wf = pk, (wf if pk.post else None)     # packed / fused weights of this call, reused by the backward
@@ -211,14 +251,7 @@ class PNAConvFn(Function):
             w_last, b_last = pk.post[-1]
             # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
             d, dbf = ops.gemm(dout, wf, relu_mask=omasks[-1], want_colsum_a=True)
-            grads[id(wl)] = _wprod(dwf, w_last, trans_b=True) + torch.outer(dbf, b_last)
-            grads[id(bl)] = dbf
-            dw_last = _wprod(wl, dwf, trans_a=True)
-            db_last = _wprod(wl, dbf.unsqueeze(1), trans_a=True).squeeze(1)
-            l_last = meta.post_layers - 1
-            for t, blk in enumerate(_diag_blocks(dw_last, T)):
-                grads[id(post[t][l_last][0])] = blk
-                grads[id(post[t][l_last][1])] = db_last[t * Fo:(t + 1) * Fo]
+            # chain rule back to W_lin / W_last / their biases: weight-space products, queued with the side work below
         else:
             d, dbf = ops.gemm(dout, wl, want_colsum_a=True)
             grads[id(wl)], grads[id(bl)] = dwf, dbf
@@ -276,14 +309,25 @@ class PNAConvFn(Function):
                 dx = ops.gemm(dpq, pk.wpq)
                 ops.gemm(dy0, pk.wx, out=dx, accumulate=True)
         dwpq = ops.gemm(dpq, x, trans_a=True)                   # [2H, H]
+        # ---- weight-space tail (parameters and 60-row tables only)
+        if pk.post:                                             # chain rule of the fused lin back to W_lin / W_last / biases
+            w_last, b_last = pk.post[-1]
+            grads[id(wl)] = _wprod(dwf, w_last, trans_b=True) + torch.outer(dbf, b_last)
+            grads[id(bl)] = dbf
+            dw_last = _wprod(wl, dwf, trans_a=True)
+            db_last = _wprod(wl, dbf.unsqueeze(1), trans_a=True).squeeze(1)
+            l_last = meta.post_layers - 1
+            for t, blk in enumerate(_diag_blocks(dw_last, T)):
+                grads[id(post[t][l_last][0])] = blk
+                grads[id(post[t][l_last][1])] = db_last[t * Fo:(t + 1) * Fo]
         dwr = ops.gemm(dr, e1, trans_a=True)                    # [H, F]
         dbr = ops.colsum(dr)
-        for t in range(T):
-            sl = slice(t * F, (t + 1) * F)
-            grads[id(pre[t][0][0])] = torch.cat([dwpq[sl, sl], dwpq[H + t * F:H + (t + 1) * F, sl], dwr[sl]], 1)
-            grads[id(pre[t][0][1])] = dbr[sl]
         de1 = ops.gemm(dr, pk.wr)
         grads[id(we)] = ops.gemm(de1, efeat, trans_a=True)
         grads[id(be)] = ops.colsum(de1)
         defeat = ops.gemm(de1, we) if ctx.needs_input_grad[1] else None
+        for t in range(T):
+            sl = slice(t * F, (t + 1) * F)
+            grads[id(pre[t][0][0])] = torch.cat([dwpq[sl, sl], dwpq[H + t * F:H + (t + 1) * F, sl], dwr[sl]], 1)
+            grads[id(pre[t][0][1])] = dbr[sl]
         return (dx, defeat, None, *[grads.get(id(p)) for p in params])

@@ -8,8 +8,9 @@
 import collections, csv, json, os, re, sys
 
 KERNEL_TO_ENTRY = [
-    (r"tc::k_gemm_tf32|k_splitk_reduce|k_gemm_f32|k_pack_relu_bits", "gnnx_gemm"),
+    (r"tc::k_gemm_tf32|k_splitk_reduce|k_gemm_f32|k_pack_relu_bits|k_group_reduce", "gnnx_gemm"),
     (r"k_pna_aggregate_bwd", "gnnx_pna_aggregate_bwd"), (r"k_pna_aggregate_fwd", "gnnx_pna_aggregate_fwd"),
+    (r"k_gather_rows", "gnnx_gather_rows"),
     (r"k_pna_gather_bwd|k_permute_rows", "gnnx_pna_gather_bwd"), (r"k_pna_gather_fwd", "gnnx_pna_gather_fwd"),
     (r"k_pna_post_combine_bwd", "gnnx_pna_post_combine_bwd"), (r"k_pna_post_combine_fwd", "gnnx_pna_post_combine_fwd"),
     (r"k_bn_bwd", "gnnx_bn_relu_bwd"), (r"k_bn_stats|k_bn_apply", "gnnx_bn_relu_fwd"),

@@ -279,3 +279,55 @@ def test_packed_store_path_equals_reference_tensor_path_and_is_deterministic():
         y.square().sum().backward()
         grads.append(torch.cat([p.grad.flatten() for p in mp.parameters()]).clone())
     assert torch.equal(grads[0], grads[1]), "atomic-free kernels must give bit-identical reruns"
+
+
+def test_side_stream_and_cached_prep_are_bit_identical(monkeypatch):
+    """The parameter-only work of the PNAConv layers can run ahead on a side stream (gnnepcsaft_b200/streams.py), ordered by
+    events only: outputs and every gradient must be bit-identical with the single-stream schedule, repeatedly (a race
+    would show as a mismatch in some repetition); the eval-mode cache of that work must follow parameter updates."""
+    from gnnepcsaft_b200 import streams, synth
+    from gnnepcsaft_b200.train import Trainer
+    import numpy as np
+    ops.set_matmul_precision("tf32")
+    try:
+        graphs, _ = make_batch(512, seed=9)
+        cfg = dict(PNA_CFG1, hidden_dim=128)
+        _, mp = _model_pair(cfg, graphs)
+        mp.train()
+        store = graph.DeviceGraphStore(synth.pack(graphs), DEV)
+        bt = store.collate(np.arange(512))
+
+        def run():
+            mp.zero_grad()
+            y = mp.forward_batch(bt)
+            y.square().sum().backward()
+            torch.cuda.synchronize()
+            return y.detach().clone(), torch.cat([p.grad.flatten() for p in mp.parameters()]).clone()
+
+        monkeypatch.setattr(streams, "ENABLED", False)
+        y0, g0 = run()
+        monkeypatch.setattr(streams, "ENABLED", True)
+        monkeypatch.setattr(streams, "PREP_AHEAD", True)        # training forward: all layers' prep queued on the side stream
+        for rep in range(6):
+            y1, g1 = run()
+            assert torch.equal(y0, y1) and torch.equal(g0, g1), f"side-stream schedule differs (repetition {rep})"
+        # eval cache: same weights -> reused; after an optimizer step -> recomputed
+        mp.eval()
+        with torch.no_grad():
+            e0 = mp.forward_batch(bt).clone()
+            cache = mp._prep_cache
+            assert cache is not None
+            e1 = mp.forward_batch(bt)
+            assert mp._prep_cache is cache and torch.equal(e0, e1)
+        mp.train()
+        tr = Trainer(mp)
+        tr.step(bt)
+        mp.eval()
+        with torch.no_grad():
+            e2 = mp.forward_batch(bt)
+            assert mp._prep_cache is not cache
+            monkeypatch.setattr(streams, "ENABLED", False)
+            e3 = mp.forward_batch(bt)
+        assert torch.equal(e2, e3) and not torch.equal(e0, e2)
+    finally:
+        ops.set_matmul_precision("fp32")
