@@ -43,7 +43,9 @@ static int bn_chunks(int64_t rows, int32_t C) {
 // first row), which keeps the single-pass variance as accurate as Welford's update without a division per element;
 // lanes and chunks are then merged with Chan's formula in a fixed order.
 __global__ void __launch_bounds__(256)
-k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial) {
+k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial,
+                   const int* __restrict__ row_node) {
+    // row_node != null: x is in degree-bucket order and rows with row_node[r] < 0 are padding (not part of the batch)
     __shared__ float sh[4][3][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
     const int c = (blockIdx.x * 64 + tx) * 4;
@@ -56,20 +58,26 @@ k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_ch
         int r = r0 + ty;
         for (; r + 12 < r1; r += 16) {
             F4 v[4];
+            bool ok[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u].q = ldg4_stream(x + (long long)(r + 4 * u) * C + c);
+            for (int u = 0; u < 4; ++u) {
+                v[u].q = ldg4_stream(x + (long long)(r + 4 * u) * C + c);
+                ok[u] = !row_node || row_node[r + 4 * u] >= 0;
+            }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 4; ++u) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) { float d = v[u].a[j] - p.a[j]; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
-            n += 4.f;
+                for (int j = 0; j < 4; ++j) { float d = ok[u] ? v[u].a[j] - p.a[j] : 0.f; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+                n += ok[u] ? 1.f : 0.f;
+            }
         }
         for (; r < r1; r += 4) {
             F4 v;
             v.q = ldg4_stream(x + (long long)r * C + c);
+            const bool ok = !row_node || row_node[r] >= 0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { float d = v.a[j] - p.a[j]; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
-            n += 1.f;
+            for (int j = 0; j < 4; ++j) { float d = ok ? v.a[j] - p.a[j] : 0.f; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+            n += ok ? 1.f : 0.f;
         }
     }
 #pragma unroll
@@ -138,11 +146,13 @@ __global__ void k_bn_eval_stats(const float* __restrict__ rm, const float* __res
 
 __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, const float* __restrict__ weight,
                            const float* __restrict__ bias, const float* __restrict__ mean, const float* __restrict__ rstd,
-                           int relu, float* __restrict__ y) {
+                           int relu, float* __restrict__ y, const int* __restrict__ row_node) {
     const int c4 = C / 4;
     long long total = rows * c4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int c = (int)(i % c4) * 4;
+        long long orow = i / c4;                      // bucket-ordered input: the result goes to the node's own row
+        if (row_node) { orow = row_node[orow]; if (orow < 0) continue; }
         F4 v, mu, rs, w, b, o;
         v.q = ldg4_stream(x + i * 4);
         mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
@@ -153,7 +163,7 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
             float t = (v.a[j] - mu.a[j]) * rs.a[j] * w.a[j] + b.a[j];
             o.a[j] = relu ? fmaxf(t, 0.f) : t;
         }
-        stg4(y + i * 4, o.q);
+        stg4(y + orow * C + c, o.q);
     }
 }
 
@@ -161,7 +171,8 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
 __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
                  int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
-                 int rows_per_chunk, float* __restrict__ partial) {
+                 int rows_per_chunk, float* __restrict__ partial, const int* __restrict__ row_node) {
+    // row_node != null: x is in degree-bucket order (rows = bucket capacity), dy / y in node order
     __shared__ float sh[4][2][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
     const int c = (blockIdx.x * 64 + tx) * 4;
@@ -177,8 +188,13 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 long long o = (long long)(r + 4 * u) * C + c;
-                g[u].q = ldg4_stream(dy + o);
                 xv[u].q = ldg4(x + o);
+                if (row_node) {
+                    const int node = row_node[r + 4 * u];
+                    if (node < 0) { g[u].q = make_float4(0.f, 0.f, 0.f, 0.f); yv[u].q = g[u].q; continue; }
+                    o = (long long)node * C + c;
+                }
+                g[u].q = ldg4_stream(dy + o);
                 if (relu) yv[u].q = ldg4(y + o);
             }
 #pragma unroll
@@ -193,7 +209,13 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
         for (; r < r1; r += 4) {
             long long o = (long long)r * C + c;
             F4 g, xv, yv;
-            g.q = ldg4_stream(dy + o); xv.q = ldg4(x + o);
+            xv.q = ldg4(x + o);
+            if (row_node) {
+                const int node = row_node[r];
+                if (node < 0) continue;
+                o = (long long)node * C + c;
+            }
+            g.q = ldg4_stream(dy + o);
             if (relu) yv.q = ldg4(y + o);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -237,16 +259,23 @@ __global__ void k_bn_bwd_final(const float* __restrict__ partial, int nchunks, i
 __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
                                long long rows, int C, const float* __restrict__ weight, const float* __restrict__ mean,
                                const float* __restrict__ rstd, const float* __restrict__ dweight,
-                               const float* __restrict__ dbias, int relu, float* __restrict__ dx) {
+                               const float* __restrict__ dbias, int relu, float* __restrict__ dx,
+                               const int* __restrict__ row_node, long long n_valid) {
     const int c4 = C / 4;
     long long total = rows * c4;
-    const float inv_n = 1.f / (float)rows;
+    const float inv_n = 1.f / (float)n_valid;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int c = (int)(i % c4) * 4;
+        long long ni = i;                             // bucket-ordered x / dx: dy and y are read at the node's own row
+        if (row_node) {
+            const int node = row_node[i / c4];
+            if (node < 0) { stg4(dx + i * 4, make_float4(0.f, 0.f, 0.f, 0.f)); continue; }   // padding rows carry no gradient
+            ni = (long long)node * c4 + (i % c4);
+        }
         F4 g, xv, yv, mu, rs, w, dw, db, o;
-        g.q = ldg4_stream(dy + i * 4);
+        g.q = ldg4_stream(dy + ni * 4);
         xv.q = ldg4_stream(x + i * 4);
-        if (relu) yv.q = ldg4_stream(y + i * 4);
+        if (relu) yv.q = ldg4_stream(y + ni * 4);
         mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
         w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
         dw.q = ldg4(dweight + c); db.q = ldg4(dbias + c);
@@ -389,41 +418,71 @@ size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t C) {
     return ((size_t)bn_chunks(rows, C) * 3 * C + 2 * (size_t)C) * sizeof(float);
 }
 
-int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weight, const float* bias, float* running_mean,
-                     float* running_var, int32_t training, float momentum, float eps, int32_t relu, float* y,
-                     float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
+static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int32_t* row_node, int32_t C, const float* weight,
+                       const float* bias, float* running_mean, float* running_var, int32_t training, float momentum, float eps,
+                       int32_t relu, float* y, float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(C % 4 == 0, "bn_relu_fwd: channels must be a multiple of 4");
     GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_fwd: workspace too small");
     GNNX_REQUIRE(save_mean && save_rstd, "bn_relu_fwd: save_mean / save_rstd are required");
-    if (rows == 0) return GNNX_OK;
+    if (rows == 0 || n_valid == 0) return GNNX_OK;
     cudaStream_t st = as_stream(stream);
     if (training) {
-        GNNX_REQUIRE(rows > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
+        GNNX_REQUIRE(n_valid > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
         int nch = bn_chunks(rows, C);
         int rpc = ceil_div(rows, nch);
-        k_bn_stats_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(x, (int)rows, C, rpc, (float*)ws);
+        k_bn_stats_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(x, (int)rows, C, rpc, (float*)ws, row_node);
         k_bn_stats_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
     } else {
         GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
         k_bn_eval_stats<<<ceil_div(C, 128), 128, 0, st>>>(running_mean, running_var, C, eps, save_mean, save_rstd);
     }
-    k_bn_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(x, rows, C, weight, bias, save_mean, save_rstd, relu, y);
+    k_bn_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(x, rows, C, weight, bias, save_mean, save_rstd, relu, y, row_node);
     return check_launch("bn_relu_fwd", training ? 3 : 2);
 }
 
-int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
-                     const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
-                     void* ws, size_t ws_bytes, void* stream) {
+int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weight, const float* bias, float* running_mean,
+                     float* running_var, int32_t training, float momentum, float eps, int32_t relu, float* y,
+                     float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
+    return bn_fwd_impl(x, rows, rows, nullptr, C, weight, bias, running_mean, running_var, training, momentum, eps, relu, y,
+                       save_mean, save_rstd, ws, ws_bytes, stream);
+}
+
+int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* row_node, int64_t num_nodes, int32_t C,
+                          const float* weight, const float* bias, float* running_mean, float* running_var, int32_t training,
+                          float momentum, float eps, int32_t relu, float* y, float* save_mean, float* save_rstd, void* ws,
+                          size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(row_node, "bn_relu_rows_fwd: row_node is required");
+    return bn_fwd_impl(x, rows, num_nodes, row_node, C, weight, bias, running_mean, running_var, training, momentum, eps, relu,
+                       y, save_mean, save_rstd, ws, ws_bytes, stream);
+}
+
+static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t rows, int64_t n_valid, const int32_t* row_node,
+                       int32_t C, const float* weight, const float* save_mean, const float* save_rstd, int32_t relu, float* dx,
+                       float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(C % 4 == 0, "bn_relu_bwd: channels must be a multiple of 4");
     GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_bwd: workspace too small");
     if (rows == 0) return GNNX_OK;
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
-    k_bn_bwd_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws);
+    k_bn_bwd_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node);
     k_bn_bwd_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
-    k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx);
+    k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid);
     return check_launch("bn_relu_bwd", 3);
+}
+
+int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
+                     const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
+                     void* ws, size_t ws_bytes, void* stream) {
+    return bn_bwd_impl(dy, x, y, rows, rows, nullptr, C, weight, save_mean, save_rstd, relu, dx, dweight, dbias, ws, ws_bytes, stream);
+}
+
+int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
+                          int64_t num_nodes, int32_t C, const float* weight, const float* save_mean, const float* save_rstd,
+                          int32_t relu, float* dx, float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(row_node, "bn_relu_rows_bwd: row_node is required");
+    return bn_bwd_impl(dy, x, y, rows, num_nodes, row_node, C, weight, save_mean, save_rstd, relu, dx, dweight, dbias, ws,
+                       ws_bytes, stream);
 }
 
 int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, int32_t C, int32_t mode, float* out, void* stream) {

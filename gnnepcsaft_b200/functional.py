@@ -52,9 +52,9 @@ def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor], relu: bool = False
 # ------------------------------------------------------------------ BatchNorm (+ReLU)
 class _BatchNormFn(Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu):
-        y, mean, rstd = ops.bn_relu_fwd(x, weight, bias, running_mean, running_var, training, momentum, eps, relu)
-        ctx.relu, ctx.training = relu, training
+    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets=None):
+        y, mean, rstd = ops.bn_relu_fwd(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets)
+        ctx.relu, ctx.training, ctx.buckets = relu, training, buckets
         ctx.save_for_backward(x, y, weight, mean, rstd)
         return y
 
@@ -64,18 +64,19 @@ class _BatchNormFn(Function):
         x, y, weight, mean, rstd = ctx.saved_tensors
         if not ctx.training:
             raise NotImplementedError("gnnx: batch-norm backward is implemented for training mode only")
-        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, y, weight, mean, rstd, ctx.relu)
-        return dx, dw, db, None, None, None, None, None, None
+        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, y, weight, mean, rstd, ctx.relu, ctx.buckets)
+        return dx, dw, db, None, None, None, None, None, None, None
 
 
-def batch_norm(x: Tensor, bn: torch.nn.BatchNorm1d, relu: bool = False) -> Tensor:
-    """BatchNorm1d (+ fused ReLU) with the module's parameters / running statistics."""
+def batch_norm(x: Tensor, bn: torch.nn.BatchNorm1d, relu: bool = False, buckets=None) -> Tensor:
+    """BatchNorm1d (+ fused ReLU) with the module's parameters / running statistics.  ``buckets``: ``x`` is a PNAConv
+    output in degree-bucket order (``PNAConv(..., bucket_out=True)``); the result is in node order."""
     training = bn.training or not bn.track_running_stats
     momentum = 0.1 if bn.momentum is None else bn.momentum
     if training and bn.track_running_stats and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
     return _BatchNormFn.apply(_c(x), bn.weight, bn.bias, bn.running_mean, bn.running_var, training, momentum,
-                              bn.eps, relu)
+                              bn.eps, relu, buckets)
 
 
 # ------------------------------------------------------------------ graph pooling

@@ -104,8 +104,13 @@ class GNNePCSAFT(Module):
         x = self.node_embed(x_idx)
         for conv, batch_norm, prep in zip(self.convs, self.batch_norms, preps):
             x = self.dropout(x)
-            out = conv(x, b.edge_index, edges, index=g) if prep is None else conv(x, b.edge_index, edges, index=g, prep=prep)
-            x = batch_norm(out, relu=True)
+            if isinstance(conv, gnn.PNAConv):
+                # degree-grouped layers hand their rows to the batch norm in bucket order (no extra pass back to node order)
+                bk = conv.bucket_rows(g)
+                out = conv(x, b.edge_index, edges, index=g, prep=prep, bucket_out=bk is not None)
+                x = batch_norm(out, relu=True, buckets=bk)
+            else:
+                x = batch_norm(conv(x, b.edge_index, edges, index=g), relu=True)
         if b.batch is not None or b.graph_ptr is not None:
             x = self.global_pool(x, ptr=b.graph_ptr)
         else:

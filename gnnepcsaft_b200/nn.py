@@ -103,8 +103,10 @@ class BatchNorm(Module):
     def reset_parameters(self):
         self.module.reset_parameters()
 
-    def forward(self, x: Tensor, relu: bool = False) -> Tensor:
+    def forward(self, x: Tensor, relu: bool = False, buckets=None) -> Tensor:
         _require_cuda(x, "BatchNorm")
+        if buckets is not None:
+            return Fn.batch_norm(x, self.module, relu, buckets)
         if self.allow_single_element and x.size(0) <= 1:
             was = self.module.training
             self.module.eval()
@@ -244,14 +246,22 @@ class PNAConv(Module):
         with torch.no_grad():
             return pna_prepare(meta, self._flat_params(), table, bk.n_groups if bk is not None else 0)
 
+    def bucket_rows(self, g: GraphIndex):
+        """The batch's degree buckets when this layer takes the degree-grouped path on ``g`` (else ``None``)."""
+        return g.degree_buckets() if grouped_ok(self._meta(g, None)) else None
+
     def forward(self, x: Tensor, edge_index: Optional[Tensor], edge_attr: Union[Tensor, EdgeTable, None] = None,
-                index: Optional[GraphIndex] = None, prep=None) -> Tensor:
+                index: Optional[GraphIndex] = None, prep=None, bucket_out: bool = False) -> Tensor:
+        """``bucket_out`` (only with ``bucket_rows(g)`` not ``None``): leave the result in degree-bucket order
+        [capacity, out_channels] for a consumer that reads rows through the bucket map (``BatchNorm(..., buckets=)``)."""
         _require_cuda(x, "PNAConv")
         if x.dim() != 2 or x.shape[1] != self.in_channels:
             raise ValueError(f"PNAConv: x must be [N, {self.in_channels}], got {tuple(x.shape)}")
         g = index if index is not None else graph_index_for(edge_index, x.shape[0])
         efeat, codes = _resolve_edges(edge_attr, self.edge_dim, g, "PNAConv")
-        return PNAConvFn.apply(x, efeat, self._meta(g, codes, prep), *self._flat_params())
+        meta = self._meta(g, codes, prep)
+        meta.bucket_out = bucket_out
+        return PNAConvFn.apply(x, efeat, meta, *self._flat_params())
 
 
 # ------------------------------------------------------------------ GATv2

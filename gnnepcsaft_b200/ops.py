@@ -391,7 +391,7 @@ def gather_rows(src: Tensor, idx: Tensor, cols: Optional[int] = None, want_relu_
 
 
 def gemm_grouped(a: Tensor, b: Tensor, buckets, *, trans_b: bool, bias: Optional[Tensor] = None, relu: bool = False,
-                 precision: Optional[int] = None, want_colsum_a: bool = False):
+                 precision: Optional[int] = None, want_colsum_a: bool = False, want_relu_bits: bool = False):
     """``out[rows of bucket g] = act(a @ op(b_g) + bias)``; ``b`` stacks one weight block per group along its rows."""
     for t, n in ((a, "a"), (b, "b")):
         if not t.is_cuda or t.dtype != torch.float32:
@@ -408,11 +408,14 @@ def gemm_grouped(a: Tensor, b: Tensor, buckets, *, trans_b: bool, bias: Optional
         raise ValueError("gnnx.gemm_grouped: operand shapes do not match the bucket layout")
     out = torch.empty((M, N), dtype=torch.float32, device=a.device)
     csum = torch.empty(K, dtype=torch.float32, device=a.device) if want_colsum_a else None
+    bits = torch.empty((M, (N + 31) // 32), dtype=torch.int32, device=a.device) if want_relu_bits else None
     prec = _default_precision if precision is None else precision
     ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, 0, int(trans_b), prec), a.device)
     lib().call("gnnx_gemm_grouped", a.data_ptr(), _ld(a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), N, M, N, K,
-               buckets.bucket_ptr.data_ptr(), G, _p(bias), GEMM_RELU if relu else 0, None, 0, None, _p(csum), prec,
+               buckets.bucket_ptr.data_ptr(), G, _p(bias), GEMM_RELU if relu else 0, None, 0, _p(bits), _p(csum), prec,
                _p(ws), nb, _stream())
+    if want_relu_bits:
+        return out, bits
     return (out, csum) if want_colsum_a else out
 
 
@@ -441,28 +444,44 @@ def relu_bwd(dy: Tensor, y: Tensor) -> Tensor:
 
 # ------------------------------------------------------------------ batch norm / pooling
 def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bool, momentum: float, eps: float,
-                relu: bool):
+                relu: bool, buckets=None):
+    """``buckets`` (graph.DegreeBuckets): ``x`` is a PNAConv output left in degree-bucket order [capacity, C]; the
+    result is in node order [N, C] and padding rows take no part in the statistics."""
     _chk(x, torch.float32, "x")
     rows, C = x.shape
-    y = torch.empty_like(x)
     mean = torch.empty(C, dtype=torch.float32, device=x.device)
     rstd = torch.empty(C, dtype=torch.float32, device=x.device)
     ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
-    lib().call("gnnx_bn_relu_fwd", x.data_ptr(), rows, C, _p(weight), _p(bias), _p(running_mean), _p(running_var),
-               int(training), float(momentum), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-               _p(ws), nb, _stream())
+    if buckets is None:
+        y = torch.empty_like(x)
+        lib().call("gnnx_bn_relu_fwd", x.data_ptr(), rows, C, _p(weight), _p(bias), _p(running_mean), _p(running_var),
+                   int(training), float(momentum), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                   _p(ws), nb, _stream())
+    else:
+        n = buckets.node_pos.numel()
+        if rows != buckets.capacity:
+            raise ValueError("gnnx.bn_relu_fwd: a bucket-ordered input must have `capacity` rows")
+        y = torch.empty((n, C), dtype=torch.float32, device=x.device)
+        lib().call("gnnx_bn_relu_rows_fwd", x.data_ptr(), rows, buckets.row_node.data_ptr(), n, C, _p(weight), _p(bias),
+                   _p(running_mean), _p(running_var), int(training), float(momentum), float(eps), int(relu), y.data_ptr(),
+                   mean.data_ptr(), rstd.data_ptr(), _p(ws), nb, _stream())
     return y, mean, rstd
 
 
-def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Tensor, relu: bool):
+def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Tensor, relu: bool, buckets=None):
     _chk(dy, torch.float32, "dy")
     rows, C = x.shape
     dx = torch.empty_like(x)
     dw = torch.empty(C, dtype=torch.float32, device=x.device)
     db = torch.empty(C, dtype=torch.float32, device=x.device)
     ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
-    lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, _p(weight), mean.data_ptr(),
-               rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
+    if buckets is None:
+        lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, _p(weight), mean.data_ptr(),
+                   rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
+    else:
+        lib().call("gnnx_bn_relu_rows_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, buckets.row_node.data_ptr(),
+                   buckets.node_pos.numel(), C, _p(weight), mean.data_ptr(), rstd.data_ptr(), int(relu), dx.data_ptr(),
+                   dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
     return dx, dw, db
 
 

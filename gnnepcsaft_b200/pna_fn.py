@@ -42,12 +42,13 @@ CAPTURE_BWD = None
 class PNAMeta:
     """Non-tensor arguments of one PNAConv call."""
 
-    __slots__ = ("g", "codes", "towers", "f_in", "f_out", "pre_layers", "post_layers", "avg_deg_log", "prep")
+    __slots__ = ("g", "codes", "towers", "f_in", "f_out", "pre_layers", "post_layers", "avg_deg_log", "prep", "bucket_out")
 
     def __init__(self, g, codes, towers, f_in, f_out, pre_layers, post_layers, avg_deg_log, prep=None):
         self.g, self.codes, self.towers, self.f_in, self.f_out = g, codes, towers, f_in, f_out
         self.pre_layers, self.post_layers, self.avg_deg_log = pre_layers, post_layers, avg_deg_log
         self.prep = prep              # parameter-only tensors computed ahead of the call (PNAPrep), or None
+        self.bucket_out = False       # leave the output (and take dout) in degree-bucket order
 
 
 def _split_params(meta: PNAMeta, params):
@@ -195,11 +196,19 @@ class PNAConvFn(Function):
             agg = ops.pna_aggregate_rows_fwd(m, x, g, bk, T)                       # [cap, 5H], bucket order
             if CAPTURE_AGG is not None:
                 CAPTURE_AGG.append(dict(agg=ops.gather_rows(agg, bk.node_pos, cols=4 * T * F), m=m, g=g))
-            o_b = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=relu0)
-            if relu0 and train:
-                o, obits = ops.gather_rows(o_b, bk.node_pos, want_relu_bits=True)   # back to node order
+            if meta.bucket_out:                        # the rest of the layer is row-wise: stay in bucket order
+                if relu0 and train:
+                    o, obits = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=True, want_relu_bits=True)
+                else:
+                    o = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=relu0)
             else:
-                o = ops.gather_rows(o_b, bk.node_pos)
+                o_b = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=relu0)
+                if relu0 and train:
+                    o, obits = ops.gather_rows(o_b, bk.node_pos, want_relu_bits=True)   # back to node order
+                else:
+                    o = ops.gather_rows(o_b, bk.node_pos)
+        elif meta.bucket_out:
+            raise ValueError("PNAConv: bucket_out needs the degree-grouped path (bucket_rows(g) is None for this layer)")
         else:
             agg = ops.pna_aggregate_fwd(m, g.rowptr, T)
             if CAPTURE_AGG is not None:
@@ -265,7 +274,8 @@ class PNAConvFn(Function):
         dxp = None
         if bk is not None:
             # degree-grouped first post Linear: d is already masked by the ReLU (packed bits rode the dX product above)
-            dyb = ops.gather_rows(d, bk.row_node)                                   # [cap, Ho] bucket order, padding rows 0
+            # [cap, Ho] in bucket order, padding rows 0 (bucket_out: dout arrived that way and the chain above is row-wise)
+            dyb = d if meta.bucket_out else ops.gather_rows(d, bk.row_node)
             dagg, db0 = ops.gemm_grouped(dyb, ctx.weff, bk, trans_b=False, want_colsum_a=True)   # d[agg | x]  [cap, 5H]
             gw = ops.gemm_grouped_dw(dyb, agg, bk, ctx.coef)                        # [3, Ho, 5H]
             dwz = gw[:, :, :4 * H].reshape(3 * Ho, 4 * H)

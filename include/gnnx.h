@@ -279,6 +279,17 @@ GNNX_API int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, i
                      const float* weight, const float* save_mean, const float* save_rstd,
                      int32_t relu, float* dx, float* dweight, float* dbias, void* workspace,
                      size_t workspace_bytes, void* stream);
+/* The same batch norm fed by a PNAConv output left in DEGREE-BUCKET order (gnnx_degree_buckets): x / dx are
+ * [rows = bucket capacity, C] with padding rows where row_node[r] < 0 (excluded from the statistics, zero gradient),
+ * y / dy are [num_nodes, C] in node order -- the move back to node order costs no extra pass. */
+GNNX_API int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* row_node, int64_t num_nodes, int32_t channels,
+                          const float* weight, const float* bias, float* running_mean, float* running_var,
+                          int32_t training, float momentum, float eps, int32_t relu, float* y, float* save_mean,
+                          float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
+GNNX_API int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
+                          int64_t num_nodes, int32_t channels, const float* weight, const float* save_mean,
+                          const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
+                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ graph pooling (K9) */
 /* Replaces aggr.{Sum,Mean,Max}Aggregation()(x, batch) (models.py:218-219, 587-595) over the

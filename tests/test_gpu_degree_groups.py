@@ -179,3 +179,35 @@ def test_degree_weights():
     ref = torch.cat([wz[None, :Ho] + sa[:, None, None] * wz[None, Ho:2 * Ho] + st[:, None, None] * wz[None, 2 * Ho:],
                      wx[None].expand(D, -1, -1)], 2)
     assert torch.allclose(weff.cpu().view(D, Ho, 5 * H), ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("N,C,relu", [(5000, 256, True), (777, 64, False)])
+def test_batchnorm_on_bucket_ordered_rows(N, C, relu):
+    """BatchNorm fed in degree-bucket order == BatchNorm on the same rows in node order (statistics are sums over the
+    same rows in another order: fp32 tolerance 1e-5), padding rows excluded, their gradient exactly zero."""
+    from gnnepcsaft_b200 import functional as Fn
+    torch.manual_seed(5)
+    rng = np.random.default_rng(5)
+    deg = rng.choice(5, N, p=[0.02, 0.35, 0.35, 0.25, 0.03])
+    bk = _buckets(deg, n_groups=5)
+    x = torch.randn(N, C, device=DEV) * 2 + 0.5
+    xb = torch.full((bk.capacity, C), 7.0, device=DEV)               # padding rows hold finite junk
+    xb[bk.node_pos.long()] = x
+    outs = []
+    for inp, rows in ((x, None), (xb, bk)):
+        bn = torch.nn.BatchNorm1d(C).to(DEV).train()
+        torch.manual_seed(6)                                         # the same affine parameters for both runs
+        with torch.no_grad():
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.5, 0.5)
+        inp = inp.clone().requires_grad_(True)
+        y = Fn.batch_norm(inp, bn, relu, rows)
+        w = torch.linspace(-1, 1, N * C, device=DEV).view(N, C)
+        (y * w).sum().backward()
+        outs.append((y.detach(), inp.grad, bn.weight.grad, bn.bias.grad, bn.running_mean.clone(), bn.running_var.clone()))
+    (y0, dx0, dw0, db0, rm0, rv0), (y1, dx1, dw1, db1, rm1, rv1) = outs
+    assert y1.shape == (N, C)
+    for a, b, what in ((y1, y0, "y"), (dx1[bk.node_pos.long()], dx0, "dx"), (dw1, dw0, "dweight"), (db1, db0, "dbias"),
+                       (rm1, rm0, "running_mean"), (rv1, rv0, "running_var")):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max())), what
+    pad = (bk.row_node < 0)
+    assert bool((dx1[pad] == 0).all())

@@ -37,8 +37,8 @@ def _ref_err(r32, r64):
     return float((r32.detach().double() - r64.detach()).abs().max()) if r32.numel() else 0.0
 
 
-def _grads_close(mp, mo, mo64, rtol):
-    """Every parameter gradient: as accurate as the fp32 oracle is against its own fp64 run (normwise, factor 4), and
+def _grads_close(mp, mo, mo64, rtol, factor=4.0):
+    """Every parameter gradient: as accurate as the fp32 oracle is against its own fp64 run (normwise, `factor`), and
     elementwise within rtol of the fp32 oracle with an absolute floor of max(1e-5 * global gradient scale, 4 x the
     fp32 oracle's own error) -- biases that feed a BatchNorm have a true-zero gradient and are judged on that floor
     (normwise: 2e-6 * 5e-2 * gmax = 1e-7 * gmax, i.e. two fp32 ulps of the global gradient scale)."""
@@ -46,7 +46,7 @@ def _grads_close(mp, mo, mo64, rtol):
     gmax = max(float(p.grad.abs().max()) for p in mo64.parameters())
     for n, p in mp.named_parameters():
         assert p.grad is not None, f"no grad for {n}"
-        assert_as_accurate(p.grad, po[n].grad, po64[n].grad, f"d{n}", min_scale=5e-2 * gmax)
+        assert_as_accurate(p.grad, po[n].grad, po64[n].grad, f"d{n}", factor=factor, min_scale=5e-2 * gmax)
         assert_close(p.grad, po[n].grad, rtol, max(1e-5 * gmax, 4 * _ref_err(po[n].grad, po64[n].grad)), f"d{n}")
 
 
@@ -237,7 +237,10 @@ def test_whole_model_training_step_parity(cfg, target):
     out2, dpred = ops.relhuber_fwd_bwd(pp.detach().contiguous(), b[target].to(DEV))
     assert_close(out2[0], lo, 1e-5, 1e-9, "loss")
     pp.backward(dpred)
-    _grads_close(mp, mo, mo64, 1e-4)
+    # factor 8 here (4 for single layers): the oracle's own fp32-vs-fp64 error is one sample of rounding noise per
+    # tensor, and the CUDA path sums the same terms in another order (row splits, degree-bucket row order); over the
+    # ~60 gradient tensors of a model the ratio of two such samples reaches 4-5 by chance
+    _grads_close(mp, mo, mo64, 1e-4, factor=8.0)
     sp = mp.state_dict()
     for n, bo in mo.state_dict().items():
         if "running_" in n:
