@@ -218,6 +218,9 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name in ("gnnx_bn_relu_fwd", "gnnx_bn_relu_bwd"):
         rows, C = a[1] if name.endswith("fwd") else a[3], a[2] if name.endswith("fwd") else a[4]
         return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
+    if name in ("gnnx_bn_relu_rows_fwd", "gnnx_bn_relu_rows_bwd"):   # bucket-ordered input, node-ordered output: same bytes
+        rows, C = (a[3], a[4]) if name.endswith("fwd") else (a[5], a[6])
+        return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
     if name == "gnnx_gatv2_fwd":                  # xlr [N,2H] read once, x_l[src] per edge slot (+ self loops), out written, alpha written
         n, e, heads, c = a[9], a[10], a[11], a[12]
         h = heads * c
@@ -259,6 +262,7 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
             continue
         if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw"):   # same kernels as gnnx_gemm (k_gemm_tf32_rows2 / _red)
             name = "gnnx_gemm"
+        name = name.replace("gnnx_bn_relu_rows_", "gnnx_bn_relu_")   # same kernels, row-mapped
         d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
         d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]
     total_ms = sum(ms for _, _, ms in records)
