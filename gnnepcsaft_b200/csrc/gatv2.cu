@@ -425,7 +425,7 @@ int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t
                    float* alpha, void* stream) {
     GNNX_REQUIRE(attn_shape_ok(heads, C), "gatv2_fwd: need C a power of two in [4, 1024] and heads*C <= 4096");
     GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "gatv2_fwd: dropout_p must be in [0, 1)");
-    GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_fwd: exactly one of eidx_i32 / eidx_u8");
+    GNNX_REQUIRE(E == 0 || (eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_fwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ld_e % 4 == 0, "gatv2_fwd: ld_e must be a multiple of 4");
     if (N == 0) return GNNX_OK;
     const AttnShape s = attn_shape(heads, C);
@@ -457,7 +457,7 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     const int H = heads * C;
     GNNX_REQUIRE(attn_shape_ok(heads, C), "gatv2_bwd: need C a power of two in [4, 1024] and heads*C <= 4096");
     GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "gatv2_bwd: dropout_p must be in [0, 1)");
-    GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_bwd: exactly one of eidx_i32 / eidx_u8");
+    GNNX_REQUIRE(E == 0 || (eidx_i32 != nullptr) != (eidx_u8 != nullptr), "gatv2_bwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ws_bytes >= gnnx_gatv2_bwd_workspace_bytes(N, E, heads, C), "gatv2_bwd: workspace too small");
     cudaStream_t st = as_stream(stream);
     if (N == 0) { GNNX_CUDA(cudaMemsetAsync(datt, 0, H * sizeof(float), st)); return GNNX_OK; }

@@ -54,9 +54,14 @@ static int gemm_dispatch(const float* A, int64_t lda, int32_t ta, const float* B
     const float* relu_mask = static_cast<const float*>(relu_mask_v);      // uint32 words under GNNX_GEMM_MASK_BITS
     GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
     GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
-    if (M == 0 || N == 0) return GNNX_OK;
-    GNNX_REQUIRE(A && B && C, "gemm: null operand");
     cudaStream_t st = as_stream(stream);
+    if (M == 0 || N == 0) {                                // empty result; the column sum of a zero-row A is zero
+        if (colsum_a_out && K > 0) GNNX_CUDA(cudaMemsetAsync(colsum_a_out, 0, (size_t)K * sizeof(float), st));
+        return GNNX_OK;
+    }
+    // K == 0 (a weight gradient over zero rows: a batch without edges) is an empty sum: the fp32 kernel writes the
+    // epilogue of a zero accumulator and never reads A / B, which may then be null (empty device tensors)
+    GNNX_REQUIRE(C && (K == 0 || (A && B)), "gemm: null operand");
     const bool bits = (flags & GNNX_GEMM_MASK_BITS) != 0;
     GNNX_REQUIRE(!bits || relu_mask, "gemm: GNNX_GEMM_MASK_BITS without a mask");
     GNNX_REQUIRE(!bits || ld_mask >= (N + 31) / 32, "gemm: packed mask rows need at least ceil(N/32) words");

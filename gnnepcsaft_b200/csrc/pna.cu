@@ -391,7 +391,7 @@ int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t 
                         const uint8_t* ridx_u8, const int32_t* rowptr, const int32_t* csr_src, int64_t N, int64_t E,
                         int32_t H, int32_t relu, float* h, uint32_t* relu_bits_out, void* stream) {
     GNNX_REQUIRE(H % 4 == 0 && ld_pq % 4 == 0 && ld_r % 4 == 0, "pna_gather_fwd: hidden / strides must be multiples of 4");
-    GNNX_REQUIRE((ridx_i32 != nullptr) != (ridx_u8 != nullptr), "pna_gather_fwd: exactly one of ridx_i32 / ridx_u8");
+    GNNX_REQUIRE(E == 0 || (ridx_i32 != nullptr) != (ridx_u8 != nullptr), "pna_gather_fwd: exactly one of ridx_i32 / ridx_u8");
     if (N == 0 || E == 0) return GNNX_OK;
     const int chunks = (H + 127) / 128;
     int grid = warp_grid((long long)N * chunks);

@@ -301,7 +301,7 @@ int gnnx_tconv_fwd(const float* qkv, const float* e, int64_t ld_e, const int32_t
     (void)E;
     GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "tconv_fwd: dropout_p must be in [0, 1)");
     GNNX_REQUIRE(attn_shape_ok(heads, C), "tconv_fwd: need C a power of two in [4, 1024] and heads*C <= 4096");
-    GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "tconv_fwd: exactly one of eidx_i32 / eidx_u8");
+    GNNX_REQUIRE(E == 0 || (eidx_i32 != nullptr) != (eidx_u8 != nullptr), "tconv_fwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ld_e % 4 == 0, "tconv_fwd: ld_e must be a multiple of 4");
     if (N == 0) return GNNX_OK;
     const AttnShape s = attn_shape(heads, C);
@@ -327,7 +327,7 @@ int gnnx_tconv_bwd(const float* dout, const float* qkv, const float* e, int64_t 
     (void)E;
     GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "tconv_bwd: dropout_p must be in [0, 1)");
     GNNX_REQUIRE(attn_shape_ok(heads, C), "tconv_bwd: need C a power of two in [4, 1024] and heads*C <= 4096");
-    GNNX_REQUIRE((eidx_i32 != nullptr) != (eidx_u8 != nullptr), "tconv_bwd: exactly one of eidx_i32 / eidx_u8");
+    GNNX_REQUIRE(E == 0 || (eidx_i32 != nullptr) != (eidx_u8 != nullptr), "tconv_bwd: exactly one of eidx_i32 / eidx_u8");
     GNNX_REQUIRE(ld_e % 4 == 0, "tconv_bwd: ld_e must be a multiple of 4");
     if (N == 0) return GNNX_OK;
     const AttnShape s = attn_shape(heads, C);

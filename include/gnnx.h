@@ -154,7 +154,7 @@ GNNX_API int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols
  * models.py:211-216).  With pq = x [W_dst ; W_src]^T computed node-side, for every
  * dst-sorted slot p:  h[p,:] = act( pq[dst_p, 0:H] + pq[src_p, H:2H] + r[ridx_p, :] )
  * where r is either the per-edge term in ORIGINAL edge order (ridx = csr_eid) or a 60-row
- * bond-type table (ridx = codes, uint8).  Exactly one of ridx_i32 / ridx_u8 is non-null.
+ * bond-type table (ridx = codes, uint8).  Exactly one of ridx_i32 / ridx_u8 is non-null (both may be null when E == 0; the attention entry points follow the same rule for eidx_*).
  * relu != 0 applies the ReLU that follows the first Linear when pre_layers > 1.
  * relu_bits_out: optional [E, ceil(H/32)] uint32, the packed (h > 0) mask in the layout
  * gnnx_gemm's GNNX_GEMM_MASK_BITS consumes (the backward of that ReLU rides a dX product). */
