@@ -33,6 +33,33 @@ inline int check_launch(const char* what, int kernels = 1) {
         if (!(cond)) return gnnx::set_error(GNNX_ERR_INVALID, __VA_ARGS__);               \
     } while (0)
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------
+// Every gnnx kernel is launched through launch() with cudaLaunchAttributeProgrammaticStreamSerialization and starts
+// with pdl_enter(): `griddepcontrol.wait` blocks until the preceding kernel of the stream has completed and its
+// writes are visible (so NO global memory may be touched before it), `griddepcontrol.launch_dependents` then lets the
+// next kernel's CTAs become resident as this kernel's CTAs retire: its launch latency, prologue and ramp-up overlap
+// this kernel's tail instead of following it (measured: 2 us per kernel boundary, ~400 boundaries per cfg2 step).
+// GNNX_PDL=0 in the environment launches everything fully serialised (the wait / trigger are then no-ops).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
+
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    if (pdl_enabled()) { cfg.attrs = attr; cfg.numAttrs = 1; }
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

@@ -5,6 +5,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gnnx {
@@ -12,6 +14,11 @@ namespace gnnx {
 static thread_local char g_err[512] = "";
 static unsigned long long g_launches = 0;
 void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("GNNX_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+}
 int set_error(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -24,6 +31,7 @@ int set_error(int code, const char* fmt, ...) {
 template <typename IdxT>
 __global__ void k_hist(const IdxT* __restrict__ src, const IdxT* __restrict__ dst, int E, int N,
                        int* __restrict__ cnt_dst, int* __restrict__ cnt_src, int* __restrict__ err) {
+    pdl_enter();
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
         long long s = (long long)src[e], d = (long long)dst[e];
         if (s < 0 || s >= N || d < 0 || d >= N) { *err = 1; continue; }
@@ -63,6 +71,7 @@ __device__ __forceinline__ int block_scan_inclusive(int v, int* smem_warp) {
 }
 
 __global__ void k_scan_tiles(int* __restrict__ a0, int* __restrict__ a1, int n, int* __restrict__ sums, int ntiles) {
+    pdl_enter();
     __shared__ int sw[32];
     int* a = blockIdx.y ? a1 : a0;
     int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
@@ -83,6 +92,7 @@ __global__ void k_scan_tiles(int* __restrict__ a0, int* __restrict__ a1, int n, 
 }
 
 __global__ void k_scan_sums(int* __restrict__ sums, int ntiles) {
+    pdl_enter();
     // one block per array; sequential over chunks of kScanThreads with a running carry
     __shared__ int sw[32];
     __shared__ int carry_s;
@@ -102,6 +112,7 @@ __global__ void k_scan_sums(int* __restrict__ sums, int ntiles) {
 }
 
 __global__ void k_scan_add(int* __restrict__ a0, int* __restrict__ a1, int n, const int* __restrict__ sums, int ntiles) {
+    pdl_enter();
     int* a = blockIdx.y ? a1 : a0;
     int add = sums[blockIdx.y * ntiles + blockIdx.x];
     int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
@@ -116,6 +127,7 @@ __global__ void k_place(const IdxT* __restrict__ src, const IdxT* __restrict__ d
                         const int* __restrict__ rowptr, const int* __restrict__ colptr,
                         int* __restrict__ fill_dst, int* __restrict__ fill_src,
                         int* __restrict__ tmp_dst, int* __restrict__ tmp_src) {
+    pdl_enter();
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
         long long s = (long long)src[e], d = (long long)dst[e];
         if (s < 0 || s >= N || d < 0 || d >= N) continue;
@@ -163,6 +175,7 @@ template <typename IdxT>
 __global__ void k_sort_rows_dst(const IdxT* __restrict__ src, int N, const int* __restrict__ rowptr,
                                 int* __restrict__ tmp_dst, int* __restrict__ csr_src,
                                 int* __restrict__ csr_eid, int* __restrict__ pos_of_eid) {
+    pdl_enter();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         int b = rowptr[i], n = rowptr[i + 1] - b;
         sort_ids(tmp_dst + b, n);
@@ -179,6 +192,7 @@ template <typename IdxT>
 __global__ void k_sort_rows_src(const IdxT* __restrict__ dst, int N, const int* __restrict__ colptr,
                                 int* __restrict__ tmp_src, const int* __restrict__ pos_of_eid,
                                 int* __restrict__ csc_pos, int* __restrict__ csc_dst) {
+    pdl_enter();
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < N; j += gridDim.x * blockDim.x) {
         int b = colptr[j], n = colptr[j + 1] - b;
         sort_ids(tmp_src + b, n);
@@ -217,15 +231,15 @@ static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t
     GNNX_CUDA(cudaMemsetAsync(fill_src, 0, sizeof(int) * (size_t)n1, st));
     GNNX_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
     int eb = E > 0 ? min(ceil_div(E, 256), kNumSMs * 16) : 0;
-    if (E > 0) k_hist<IdxT><<<eb, 256, 0, st>>>(src, dst, E, N, rowptr, colptr, err_flag);
-    k_scan_tiles<<<dim3(ntiles, 2), kScanThreads, 0, st>>>(rowptr, colptr, n1, sums, ntiles);
-    k_scan_sums<<<2, kScanThreads, 0, st>>>(sums, ntiles);
-    k_scan_add<<<dim3(ntiles, 2), kScanThreads, 0, st>>>(rowptr, colptr, n1, sums, ntiles);
+    if (E > 0) launch(k_hist<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, err_flag);
+    launch(k_scan_tiles, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
+    launch(k_scan_sums, 2, kScanThreads, 0, st, sums, ntiles);
+    launch(k_scan_add, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
     if (E > 0) {
-        k_place<IdxT><<<eb, 256, 0, st>>>(src, dst, E, N, rowptr, colptr, fill_dst, fill_src, tmp_dst, tmp_src);
+        launch(k_place<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, fill_dst, fill_src, tmp_dst, tmp_src);
         int nb = min(ceil_div(N, 128), kNumSMs * 16);
-        k_sort_rows_dst<IdxT><<<nb, 128, 0, st>>>(src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
-        k_sort_rows_src<IdxT><<<nb, 128, 0, st>>>(dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
+        launch(k_sort_rows_dst<IdxT>, nb, 128, 0, st, src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
+        launch(k_sort_rows_src<IdxT>, nb, 128, 0, st, dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
     }
     return check_launch("csr_build", E > 0 ? 7 : 3);
 }
@@ -233,6 +247,7 @@ static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t
 // ------------------------------------------------------------------ degree histogram / graph_ptr / misc
 __global__ void k_degree_hist(const int* __restrict__ rowptr, int N, unsigned long long* __restrict__ hist,
                               int nbins, int* __restrict__ maxdeg) {
+    pdl_enter();
     extern __shared__ int sh[];   // nbins counters + 1 max
     for (int i = threadIdx.x; i <= nbins; i += blockDim.x) sh[i] = 0;
     __syncthreads();
@@ -248,6 +263,7 @@ __global__ void k_degree_hist(const int* __restrict__ rowptr, int N, unsigned lo
 }
 
 __global__ void k_graph_ptr(const int64_t* __restrict__ batch, int N, int G, int* __restrict__ gp) {
+    pdl_enter();
     for (int n = blockIdx.x * blockDim.x + threadIdx.x; n <= N; n += gridDim.x * blockDim.x) {
         long long prev = n == 0 ? -1 : batch[n - 1];
         long long cur = n == N ? (long long)G : batch[n];
@@ -257,11 +273,13 @@ __global__ void k_graph_ptr(const int64_t* __restrict__ batch, int N, int G, int
 }
 
 __global__ void k_narrow(const int64_t* __restrict__ in, long long count, uint8_t* __restrict__ out) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
         out[i] = (uint8_t)in[i];
 }
 
 __global__ void k_edge_codes(const uint8_t* __restrict__ ea, const int* __restrict__ eid, int E, uint8_t* __restrict__ codes) {
+    pdl_enter();
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < E; p += gridDim.x * blockDim.x) {
         const uint8_t* a = ea + 3ll * eid[p];
         codes[p] = (uint8_t)((a[0] * 6 + a[1]) * 2 + a[2]);
@@ -276,6 +294,7 @@ __global__ void k_collate_packed(const uint8_t* __restrict__ sx, const int16_t* 
                                  const int64_t* __restrict__ eoff, uint8_t* __restrict__ ox,
                                  int* __restrict__ osrc, int* __restrict__ odst, uint8_t* __restrict__ oea,
                                  int* __restrict__ obatch) {
+    pdl_enter();
     int lane = threadIdx.x & 31;
     int warps_per_block = blockDim.x >> 5;
     for (int g = blockIdx.x * warps_per_block + (threadIdx.x >> 5); g < G; g += gridDim.x * warps_per_block) {
@@ -329,7 +348,7 @@ int gnnx_degree_hist(const int32_t* rowptr, int64_t N, int64_t* hist, int32_t nb
     GNNX_REQUIRE(nbins >= 1 && nbins <= 4096, "degree_hist: nbins must be in [1,4096]");
     if (N == 0) return GNNX_OK;
     int nb = min(ceil_div(N, 256), kNumSMs * 4);
-    k_degree_hist<<<nb, 256, sizeof(int) * (nbins + 1), as_stream(stream)>>>(
+    launch(k_degree_hist, nb, 256, sizeof(int) * (nbins + 1), as_stream(stream), 
         rowptr, (int)N, (unsigned long long*)hist, nbins, max_degree);
     return check_launch("degree_hist");
 }
@@ -337,21 +356,21 @@ int gnnx_degree_hist(const int32_t* rowptr, int64_t N, int64_t* hist, int32_t nb
 int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream) {
     GNNX_REQUIRE(N >= 0 && G >= 0, "graph_ptr: negative size");
     int nb = min(ceil_div(N + 1, 256), kNumSMs * 8);
-    k_graph_ptr<<<nb, 256, 0, as_stream(stream)>>>(batch, (int)N, (int)G, graph_ptr);
+    launch(k_graph_ptr, nb, 256, 0, as_stream(stream), batch, (int)N, (int)G, graph_ptr);
     return check_launch("graph_ptr_from_batch");
 }
 
 int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream) {
     if (count == 0) return GNNX_OK;
     int nb = min(ceil_div(count, 256), kNumSMs * 16);
-    k_narrow<<<nb, 256, 0, as_stream(stream)>>>(in, count, out);
+    launch(k_narrow, nb, 256, 0, as_stream(stream), in, count, out);
     return check_launch("narrow_i64_u8");
 }
 
 int gnnx_edge_codes(const uint8_t* ea, const int32_t* csr_eid, int64_t E, uint8_t* codes, void* stream) {
     if (E == 0) return GNNX_OK;
     int nb = min(ceil_div(E, 256), kNumSMs * 16);
-    k_edge_codes<<<nb, 256, 0, as_stream(stream)>>>(ea, csr_eid, (int)E, codes);
+    launch(k_edge_codes, nb, 256, 0, as_stream(stream), ea, csr_eid, (int)E, codes);
     return check_launch("edge_codes");
 }
 
@@ -361,7 +380,7 @@ int gnnx_collate_packed(const uint8_t* sx, const int16_t* ssrc, const int16_t* s
                         uint8_t* oea, int32_t* obatch, void* stream) {
     if (G == 0) return GNNX_OK;
     int nb = min(ceil_div(G, 8), kNumSMs * 8);
-    k_collate_packed<<<nb, 256, 0, as_stream(stream)>>>(sx, ssrc, sdst, sea, snp, sep, gids, (int)G, noff, eoff,
+    launch(k_collate_packed, nb, 256, 0, as_stream(stream), sx, ssrc, sdst, sea, snp, sep, gids, (int)G, noff, eoff,
                                                         ox, osrc, odst, oea, obatch);
     return check_launch("collate_packed");
 }

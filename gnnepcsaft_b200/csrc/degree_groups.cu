@@ -21,6 +21,7 @@ constexpr int kDgBlock = 256;
 // pass 1: cnt[d * nb + blk] = nodes of in-degree d in block blk
 __global__ void __launch_bounds__(kDgBlock)
 k_dg_count(const int* __restrict__ rowptr, int N, int D, int* __restrict__ cnt, int nb, int* __restrict__ err) {
+    pdl_enter();
     __shared__ int sh[GNNX_MAX_GROUPS];
     if (threadIdx.x < GNNX_MAX_GROUPS) sh[threadIdx.x] = 0;
     __syncthreads();
@@ -38,6 +39,7 @@ k_dg_count(const int* __restrict__ rowptr, int N, int D, int* __restrict__ cnt, 
 // to a multiple of `align` rows.  cnt becomes the first bucket row of (degree, block).
 __global__ void __launch_bounds__(1024)
 k_dg_scan(int* __restrict__ cnt, int nb, int D, int align, int* __restrict__ bucket_ptr) {
+    pdl_enter();
     __shared__ int sw[32];
     __shared__ int s_carry;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -84,6 +86,7 @@ k_dg_scan(int* __restrict__ cnt, int nb, int D, int align, int* __restrict__ buc
 __global__ void __launch_bounds__(kDgBlock)
 k_dg_place(const int* __restrict__ rowptr, int N, int D, const int* __restrict__ off, int nb, int* __restrict__ node_pos,
            int* __restrict__ row_node) {
+    pdl_enter();
     __shared__ int wc[kDgBlock / 32][GNNX_MAX_GROUPS];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * kDgBlock + threadIdx.x;
@@ -108,6 +111,7 @@ k_dg_place(const int* __restrict__ rowptr, int N, int D, const int* __restrict__
 // one split, the rest are handed out in proportion to the bucket sizes (largest rows-per-split first); ranges are
 // multiples of `unit` rows.  Unused splits are {0, 0, -1}.
 __global__ void k_group_split_table(const int* __restrict__ bucket_ptr, int D, int unit, int S, int* __restrict__ table) {
+    pdl_enter();
     if (threadIdx.x || blockIdx.x) return;
     int u[GNNX_MAX_GROUPS], s[GNNX_MAX_GROUPS];
     long long U = 0;
@@ -148,6 +152,7 @@ __global__ void k_group_split_table(const int* __restrict__ bucket_ptr, int D, i
 // weff[d] = [wz_id + s_amp(d) wz_amp + s_att(d) wz_att | wx]   ([Ho, K4 + H] per degree);  coef[d] = (1, s_amp, s_att)
 __global__ void k_pna_degree_weights(const float* __restrict__ wz, const float* __restrict__ wx, int Ho, int K4, int H,
                                      float avg_deg_log, int D, float* __restrict__ weff, float* __restrict__ coef) {
+    pdl_enter();
     const int Kt = K4 + H, k4 = Kt / 4;
     const long long total = (long long)D * Ho * k4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -175,6 +180,7 @@ __global__ void k_pna_degree_weights(const float* __restrict__ wz, const float* 
 __global__ void __launch_bounds__(256)
 k_gather_rows(const float* __restrict__ src, long long ld_src, const int* __restrict__ idx, int rows, int cols,
               float* __restrict__ out, long long ld_out, uint32_t* __restrict__ bits) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (cols + 127) / 128, words = (cols + 31) / 32;
     const long long nwork = (long long)rows * chunks;
@@ -202,6 +208,7 @@ k_gather_rows(const float* __restrict__ src, long long ld_src, const int* __rest
 __global__ void __launch_bounds__(256)
 k_group_reduce(const float* __restrict__ partial, const int* __restrict__ table, int S, const float* __restrict__ coef,
                int J, long long total4, float* __restrict__ out) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4; i += (long long)gridDim.x * blockDim.x) {
         float4 acc[4];
 #pragma unroll
@@ -229,7 +236,7 @@ int group_reduce_launch(const float* partial, const int* split_table, int S, con
     const long long total4 = total / 4;
     long long blocks = (total4 + 255) / 256;
     if (blocks > (long long)kNumSMs * 8) blocks = (long long)kNumSMs * 8;
-    k_group_reduce<<<(int)blocks, 256, 0, st>>>(partial, split_table, S, coef, J, total4, out);
+    launch(k_group_reduce, (int)blocks, 256, 0, st, partial, split_table, S, coef, J, total4, out);
     return check_launch("group_reduce");
 }
 
@@ -259,9 +266,9 @@ int gnnx_degree_buckets(const int32_t* rowptr, int64_t N, int32_t n_groups, int3
     if (N == 0) { GNNX_CUDA(cudaMemsetAsync(bucket_ptr, 0, (size_t)(n_groups + 1) * sizeof(int32_t), st)); return GNNX_OK; }
     const int nb = ceil_div(N, kDgBlock);
     int* cnt = static_cast<int*>(ws);
-    k_dg_count<<<nb, kDgBlock, 0, st>>>(rowptr, (int)N, n_groups, cnt, nb, err_flag);
-    k_dg_scan<<<1, 1024, 0, st>>>(cnt, nb, n_groups, align, bucket_ptr);
-    k_dg_place<<<nb, kDgBlock, 0, st>>>(rowptr, (int)N, n_groups, cnt, nb, node_pos, row_node);
+    launch(k_dg_count, nb, kDgBlock, 0, st, rowptr, (int)N, n_groups, cnt, nb, err_flag);
+    launch(k_dg_scan, 1, 1024, 0, st, cnt, nb, n_groups, align, bucket_ptr);
+    launch(k_dg_place, nb, kDgBlock, 0, st, rowptr, (int)N, n_groups, cnt, nb, node_pos, row_node);
     return check_launch("degree_buckets", 3);
 }
 
@@ -269,7 +276,7 @@ int gnnx_group_split_table(const int32_t* bucket_ptr, int32_t n_groups, int32_t 
                            void* stream) {
     GNNX_REQUIRE(n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS && unit >= 1 && splits >= n_groups,
                  "group_split_table: need 1..%d groups and at least one split per group", GNNX_MAX_GROUPS);
-    k_group_split_table<<<1, 32, 0, as_stream(stream)>>>(bucket_ptr, n_groups, unit, splits, table);
+    launch(k_group_split_table, 1, 32, 0, as_stream(stream), bucket_ptr, n_groups, unit, splits, table);
     return check_launch("group_split_table");
 }
 
@@ -280,7 +287,7 @@ int gnnx_pna_degree_weights(const float* wz, const float* wx, int32_t h_out, int
     const long long total = (long long)n_groups * h_out * ((k_agg + h_in) / 4);
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)kNumSMs * 8) blocks = (long long)kNumSMs * 8;
-    k_pna_degree_weights<<<(int)(blocks > 0 ? blocks : 1), 256, 0, as_stream(stream)>>>(wz, wx, h_out, k_agg, h_in, avg_deg_log, n_groups, weff, coef);
+    launch(k_pna_degree_weights, (int)(blocks > 0 ? blocks : 1), 256, 0, as_stream(stream), wz, wx, h_out, k_agg, h_in, avg_deg_log, n_groups, weff, coef);
     return check_launch("pna_degree_weights");
 }
 
@@ -292,7 +299,7 @@ int gnnx_gather_rows(const float* src, int64_t ld_src, const int32_t* idx, int64
     const long long nwork = rows * ((cols + 127) / 128);
     long long blocks = (nwork + 7) / 8;
     if (blocks > (long long)kNumSMs * 32) blocks = (long long)kNumSMs * 32;
-    k_gather_rows<<<(int)blocks, 256, 0, as_stream(stream)>>>(src, ld_src, idx, (int)rows, cols, out, ld_out, relu_bits_out);
+    launch(k_gather_rows, (int)blocks, 256, 0, as_stream(stream), src, ld_src, idx, (int)rows, cols, out, ld_out, relu_bits_out);
     return check_launch("gather_rows");
 }
 

@@ -9,6 +9,7 @@ namespace gnnx {
 
 __global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, const int* __restrict__ offsets,
                             const float* __restrict__ table, int H, float* __restrict__ out) {
+    pdl_enter();
     int lane = threadIdx.x & 31;
     int wpb = blockDim.x >> 5;
     for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += gridDim.x * wpb) {
@@ -36,6 +37,7 @@ __global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, i
                                     const int* __restrict__ offsets, int table_rows,
                                     const float* __restrict__ dout, int H, int rows_per_chunk,
                                     float* __restrict__ partial) {
+    pdl_enter();
     extern __shared__ float tab[];
     int c = blockIdx.x * kEmbSlab + threadIdx.x;
     int k = threadIdx.y;
@@ -77,6 +79,7 @@ __global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, i
 
 __global__ void k_reduce_partials(const float* __restrict__ partial, int nchunks, long long count,
                                   float* __restrict__ out) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         float s = 0.f;
         for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * count + i];
@@ -103,7 +106,7 @@ int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
     GNNX_REQUIRE(H % 4 == 0, "embed_sum_fwd: hidden must be a multiple of 4");
     if (rows == 0) return GNNX_OK;
     int nb = min(ceil_div(rows, 8), kNumSMs * 8);
-    k_embed_fwd<<<nb, 256, 0, as_stream(stream)>>>(idx, (int)rows, K, offsets, table, H, out);
+    launch(k_embed_fwd, nb, 256, 0, as_stream(stream), idx, (int)rows, K, offsets, table, H, out);
     return check_launch("embed_sum_fwd");
 }
 
@@ -124,9 +127,9 @@ int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
     GNNX_REQUIRE(smem <= 200 * 1024, "embed_sum_bwd: table too large for the shared-memory slab");
     if (smem > 48 * 1024)
         GNNX_CUDA(cudaFuncSetAttribute(k_embed_bwd_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_embed_bwd_partial<<<dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st>>>(
+    launch(k_embed_bwd_partial, dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st, 
         idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws);
-    k_reduce_partials<<<min(ceil_div(count, 256), kNumSMs * 8), 256, 0, st>>>((const float*)ws, nchunks, count, dtable);
+    launch(k_reduce_partials, min(ceil_div(count, 256), kNumSMs * 8), 256, 0, st, (const float*)ws, nchunks, count, dtable);
     return check_launch("embed_sum_bwd", 2);
 }
 

@@ -14,6 +14,7 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
             const float* __restrict__ att, const float* __restrict__ bias, const int* __restrict__ rowptr,
             const int* __restrict__ csr_src, int N, int E, int heads, int C, int log2c, int groups, float slope,
             int self_loops, unsigned int drop_thr, float keep_scale, unsigned long long seed, float* __restrict__ out, float* alpha) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -181,6 +182,7 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
                 const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,
                 const int* __restrict__ csr_src, int N, int E, int heads, int C, int log2c, int groups, float slope,
                 int self_loops, float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -308,6 +310,7 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
 // datt[c] = sum over the warps that owned column c's head group, in warp order; one warp per column
 __global__ void k_gatv2_datt_final(const float* __restrict__ partial, int total_warps, int groups, int width, int H,
                                    float* __restrict__ datt) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= H) return;
@@ -325,6 +328,7 @@ __global__ void __launch_bounds__(256)
 k_gatv2_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, const float* __restrict__ alpha,
                 const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csc_dst, int N,
                 int E, int heads, int C, int log2c, int self_loops, float keep_scale, float* __restrict__ dxlr) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -371,6 +375,7 @@ k_gatv2_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, co
 __global__ void __launch_bounds__(256)
 k_gatv2_edge_grad(const float* __restrict__ ds, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
                   const int* __restrict__ csr_eid, int N, int E, int H, int self_loops, float* __restrict__ de) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
     const long long nwork = (long long)N * chunks;
@@ -435,8 +440,8 @@ int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_fwd<NQ, int><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
-    else k_gatv2_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha)
+    if (eidx_i32) launch(k_gatv2_fwd<NQ, int>, grid, 256, 0, st, xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
+    else launch(k_gatv2_fwd<NQ, uint8_t>, grid, 256, 0, st, xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha)
     GAT_DISPATCH(s, CALL);
 #undef CALL
     return check_launch("gatv2_fwd");
@@ -465,12 +470,12 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     const int grid = gat_bwd_grid(N, s.groups);
     const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) k_gatv2_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
-    else k_gatv2_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
+    if (eidx_i32) launch(k_gatv2_bwd_dst<NQ, int>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
+    else launch(k_gatv2_bwd_dst<NQ, uint8_t>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
     GAT_DISPATCH(s, CALL);
 #undef CALL
-    k_gatv2_bwd_src<<<attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);
-    k_gatv2_datt_final<<<ceil_div(H, 8), 256, 0, st>>>((const float*)ws, grid * 8, s.groups, 128 * s.nq, H, datt);
+    launch(k_gatv2_bwd_src, attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st, dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);
+    launch(k_gatv2_datt_final, ceil_div(H, 8), 256, 0, st, (const float*)ws, grid * 8, s.groups, 128 * s.nq, H, datt);
     return check_launch("gatv2_bwd", 3);
 }
 
@@ -480,7 +485,7 @@ int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* 
     if (N == 0 || E == 0) return GNNX_OK;
     long long nwork = (long long)N * ((H + 127) / 128);
     long long blocks = (nwork + 7) / 8, cap = (long long)kNumSMs * 32;
-    k_gatv2_edge_grad<<<(int)(blocks < cap ? blocks : cap), 256, 0, as_stream(stream)>>>(ds, rowptr, csr_src, csr_eid, (int)N, (int)E, H, self_loops, de);
+    launch(k_gatv2_edge_grad, (int)(blocks < cap ? blocks : cap), 256, 0, as_stream(stream), ds, rowptr, csr_src, csr_eid, (int)N, (int)E, H, self_loops, de);
     return check_launch("gatv2_edge_grad");
 }
 

@@ -32,6 +32,7 @@ k_gemm_f32(const float* __restrict__ A, long long lda, const float* __restrict__
            const float* __restrict__ bias, int flags, float* __restrict__ partial,
            const float* __restrict__ mask, long long ldm, const int* __restrict__ bucket_ptr, int n_groups,
            long long group_stride, const int* __restrict__ split_table) {
+    pdl_enter();
     __shared__ float As[2][BK][BM + 4];
     __shared__ float Bs[2][BK][BN + 4];
     const int tid = threadIdx.x;
@@ -137,6 +138,7 @@ k_gemm_f32_small(const float* __restrict__ A, long long lda, const float* __rest
                  float* __restrict__ C, long long ldc, int M, int N, int K, const float* __restrict__ bias, int flags,
                  const float* __restrict__ mask, long long ldm, const int* __restrict__ bucket_ptr, int n_groups,
                  long long group_stride) {
+    pdl_enter();
     __shared__ float As[SK][SB + 1];
     __shared__ float Bs[SK][SB + 1];
     const int tid = threadIdx.x;
@@ -209,6 +211,7 @@ static bool simt_small(int64_t M, int64_t N, int64_t K) {
 __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ C,
                                 long long ldc, const float* __restrict__ bias, int flags, const float* __restrict__ mask,
                                 long long ldm) {
+    pdl_enter();
     long long total = (long long)M * N;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int m = (int)(i / N), n = (int)(i % N);
@@ -236,7 +239,7 @@ int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* 
     long long total = (long long)M * N;
     int blocks = (int)((total + 255) / 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    k_splitk_reduce<<<blocks, 256, 0, st>>>(partial, splits, M, N, C, ldc, bias, flags, mask, ldm);
+    launch(k_splitk_reduce, blocks, 256, 0, st, partial, splits, M, N, C, ldc, bias, flags, mask, ldm);
     return check_launch("splitk_reduce");
 }
 
@@ -258,6 +261,7 @@ size_t simt_workspace_bytes(int64_t M, int64_t N, int64_t K) {
 
 // bits[r, w] = OR_j (C[r, 32 w + j] > 0) << j : the packed ReLU mask a forward product leaves for its backward
 __global__ void k_pack_relu_bits(const float* __restrict__ C, long long ldc, int M, int N, uint32_t* __restrict__ bits) {
+    pdl_enter();
     const int words = (N + 31) / 32;
     const long long total = (long long)M * words;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -272,7 +276,7 @@ int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t*
     long long total = (long long)M * ((N + 31) / 32);
     int blocks = (int)((total + 255) / 256);
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    k_pack_relu_bits<<<blocks, 256, 0, st>>>(C, ldc, M, N, bits);
+    launch(k_pack_relu_bits, blocks, 256, 0, st, C, ldc, M, N, bits);
     return check_launch("pack_relu_bits");
 }
 
@@ -284,7 +288,7 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     const long long gstride = bucket_ptr ? (tb ? (long long)N * ldb : (long long)K * ldb) : 0;
     if (simt_small(M, N, K)) {
         dim3 grid(ceil_div(N, SB), ceil_div(M, SB));
-#define LAUNCH_S(TA, TB) k_gemm_f32_small<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, bias, flags, mask, ldm, bucket_ptr, n_groups, gstride)
+#define LAUNCH_S(TA, TB) launch(k_gemm_f32_small<TA, TB>, grid, 256, 0, st, A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, bias, flags, mask, ldm, bucket_ptr, n_groups, gstride)
         if (ta && tb) LAUNCH_S(true, true);
         else if (ta) LAUNCH_S(true, false);
         else if (tb) LAUNCH_S(false, true);
@@ -307,14 +311,14 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
     GNNX_REQUIRE(grid.y <= 65535 * 1 || true, "gemm: M too large");
     if (grid.y > 65535) return set_error(GNNX_ERR_UNSUPPORTED, "gemm_simt: M=%lld exceeds grid.y limit", (long long)M);
-#define LAUNCH(TA, TB) k_gemm_f32<TA, TB><<<grid, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial, mask, ldm, bucket_ptr, n_groups, gstride, nullptr)
+#define LAUNCH(TA, TB) launch(k_gemm_f32<TA, TB>, grid, 256, 0, st, A, lda, B, ldb, C, ldc, (int)M, (int)N, (int)K, kps, bias, flags, partial, mask, ldm, bucket_ptr, n_groups, gstride, nullptr)
     if (ta && tb) LAUNCH(true, true);
     else if (ta) LAUNCH(true, false);
     else if (tb) LAUNCH(false, true);
     else LAUNCH(false, false);
 #undef LAUNCH
     if (partial)
-        k_splitk_reduce<<<min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st>>>(partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
+        launch(k_splitk_reduce, min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st, partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
     int rc = check_launch("gemm_simt", partial ? 2 : 1);
     if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
     return rc;
@@ -324,7 +328,7 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
 int gemm_simt_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
                           const int* split_table, int S, float* partial, cudaStream_t st) {
     dim3 grid(ceil_div(No, BN), ceil_div(Mo, BM), S);
-    k_gemm_f32<true, false><<<grid, 256, 0, st>>>(A, lda, B, ldb, nullptr, 0, (int)Mo, (int)No, (int)R, 0, nullptr, 0, partial,
+    launch(k_gemm_f32<true, false>, grid, 256, 0, st, A, lda, B, ldb, nullptr, 0, (int)Mo, (int)No, (int)R, 0, nullptr, 0, partial,
                                                   nullptr, 0, nullptr, 1, 0, split_table);
     return check_launch("gemm_simt_red(grouped)");
 }
@@ -333,6 +337,7 @@ int gemm_simt_red_grouped(const float* A, int64_t lda, const float* B, int64_t l
 constexpr int kCsRows = 8;
 __global__ void k_colsum_partial(const float* __restrict__ in, long long ld, int rows, int cols, int rows_per_chunk,
                                  float* __restrict__ partial) {
+    pdl_enter();
     __shared__ float sh[kCsRows][33];
     int c = blockIdx.x * 32 + threadIdx.x;
     int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
@@ -351,6 +356,7 @@ __global__ void k_colsum_partial(const float* __restrict__ in, long long ld, int
 // float4 variant (cols % 4 == 0, 16-byte aligned rows): 64 column groups x 4 row lanes, 4 rows in flight per thread
 __global__ void __launch_bounds__(256)
 k_colsum_partial4(const float* __restrict__ in, long long ld, int rows, int cols, int rows_per_chunk, float* __restrict__ partial) {
+    pdl_enter();
     __shared__ float sh[4][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
     const int c = (blockIdx.x * 64 + tx) * 4;
@@ -378,6 +384,7 @@ k_colsum_partial4(const float* __restrict__ in, long long ld, int rows, int cols
 
 // one warp per column: lanes stride over the chunks, then a fixed shuffle tree (deterministic)
 __global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, int cols, float* __restrict__ out) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= cols) return;
@@ -388,7 +395,7 @@ __global__ void k_colsum_final(const float* __restrict__ partial, int nchunks, i
     if (lane == 0) out[c] = s;
 }
 int colsum_final_launch(const float* partial, int nchunks, int cols, float* out, cudaStream_t st) {
-    k_colsum_final<<<ceil_div(cols, 8), 256, 0, st>>>(partial, nchunks, cols, out);
+    launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, partial, nchunks, cols, out);
     return check_launch("colsum_final");
 }
 int colsum_chunks(int64_t rows, int64_t cols) {
@@ -417,10 +424,10 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
     int nch = colsum_chunks(rows, cols);
     int rpc = ceil_div(rows, nch);
     if ((cols & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)in & 15) == 0)
-        k_colsum_partial4<<<dim3(ceil_div(cols, 256), nch), 256, 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+        launch(k_colsum_partial4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);
     else
-        k_colsum_partial<<<dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st>>>(in, ld, (int)rows, (int)cols, rpc, (float*)ws);
-    k_colsum_final<<<ceil_div(cols, 8), 256, 0, st>>>((const float*)ws, nch, (int)cols, out);
+        launch(k_colsum_partial, dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+    launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, (const float*)ws, nch, (int)cols, out);
     return check_launch("colsum", 2);
 }
 

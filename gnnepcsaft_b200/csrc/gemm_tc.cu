@@ -262,6 +262,7 @@ k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t tmem_base = prologue(sm, warp);
+    pdl_enter();           // barriers, TMEM and descriptors are set up while the previous kernel drains; global memory only from here
 
     const int n_tiles = (N + BN - 1) / BN;
     const int m_tiles = (M + 255) / 256;
@@ -404,6 +405,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (kCluster > 1) cluster_sync_all(); else __syncthreads();      // peers must see initialised barriers before any multicast
     tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_ptr();
+    pdl_enter();           // barriers, TMEM and the cluster handshake overlap the previous kernel's tail; global memory only from here
 
     const int n_tiles = (N + BN - 1) / BN;
     const int m_groups = ((M + 127) / 128 + kCluster - 1) / kCluster;
@@ -557,6 +559,7 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t tmem_base = prologue(sm, warp);
+    pdl_enter();           // barriers, TMEM and descriptors are set up while the previous kernel drains; global memory only from here
 
     const int n_tiles = (No + BN - 1) / BN;
     const int m0 = (blockIdx.x / n_tiles) * BM, n0 = (blockIdx.x % n_tiles) * BN;
@@ -789,10 +792,12 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         cfg.blockDim = dim3(kThreads2);
         cfg.dynamicSmemBytes = kSmem2;
         cfg.stream = st;
-        cudaLaunchAttribute at[1];
+        cudaLaunchAttribute at[2];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.attrs = at; cfg.numAttrs = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // see common.cuh: pdl_enter()
+        at[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
         const int Mi = (int)M, Ni = (int)N, Ki = (int)K;
         const long long ldc_ = ldc, ldm_ = ldm;
         const long long ldbits = (N + 31) / 32;          // packed masks are row-major: [M, ceil(N/32)] words
@@ -827,9 +832,9 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         int tiles = ceil_div(M, 256) * ceil_div(N, BN);
         int grid = tiles < kNumSMs ? tiles : kNumSMs;
         if (tb)
-            k_gemm_tf32_rows<false><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
+            launch(k_gemm_tf32_rows<false>, grid, kThreads, kSmemBytes, st, mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
         else
-            k_gemm_tf32_rows<true><<<grid, kThreads, kSmemBytes, st>>>(mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
+            launch(k_gemm_tf32_rows<true>, grid, kThreads, kSmemBytes, st, mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
         return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
@@ -839,7 +844,7 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     if (make_map_mnmajor(&mA, A, K, M, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, K, N, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, (const float*)ws, (int64_t)p.splits * M, N, N)) return GNNX_ERR_INVALID;
-    k_gemm_tf32_red<<<dim3(p.tiles, p.splits), kThreads, kSmemBytes, st>>>(mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
+    launch(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
                                                                           p.rows_per_split, p.BM, p.BN, nullptr);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
@@ -866,7 +871,7 @@ int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb
     if (make_map_mnmajor(&mA, A, R, Mo, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, R, No, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, partial, (int64_t)S * Mo, No, No)) return GNNX_ERR_INVALID;
-    k_gemm_tf32_red<<<dim3(p.tiles, S), kThreads, kSmemBytes, st>>>(mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
+    launch(k_gemm_tf32_red, dim3(p.tiles, S), kThreads, kSmemBytes, st, mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
     return check_launch("gemm_tf32_red(grouped)");
 }
 

@@ -45,6 +45,7 @@ static int bn_chunks(int64_t rows, int32_t C) {
 __global__ void __launch_bounds__(256)
 k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial,
                    const int* __restrict__ row_node) {
+    pdl_enter();
     // row_node != null: x is in degree-bucket order and rows with row_node[r] < 0 are padding (not part of the batch)
     __shared__ float sh[4][3][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
@@ -105,6 +106,7 @@ k_bn_stats_partial(const float* __restrict__ x, int rows, int C, int rows_per_ch
 __global__ void k_bn_stats_final(const float* __restrict__ partial, int nchunks, int C, float eps, float momentum,
                                  float* __restrict__ running_mean, float* __restrict__ running_var,
                                  float* __restrict__ save_mean, float* __restrict__ save_rstd) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= C) return;                              // warp-uniform
@@ -140,6 +142,7 @@ __global__ void k_bn_stats_final(const float* __restrict__ partial, int nchunks,
 
 __global__ void k_bn_eval_stats(const float* __restrict__ rm, const float* __restrict__ rv, int C, float eps,
                                 float* __restrict__ mean, float* __restrict__ rstd) {
+    pdl_enter();
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c < C) { mean[c] = rm[c]; rstd[c] = rsqrtf(rv[c] + eps); }
 }
@@ -147,6 +150,7 @@ __global__ void k_bn_eval_stats(const float* __restrict__ rm, const float* __res
 __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, const float* __restrict__ weight,
                            const float* __restrict__ bias, const float* __restrict__ mean, const float* __restrict__ rstd,
                            int relu, float* __restrict__ y, const int* __restrict__ row_node) {
+    pdl_enter();
     const int c4 = C / 4;
     long long total = rows * c4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -172,6 +176,7 @@ __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
                  int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
                  int rows_per_chunk, float* __restrict__ partial, const int* __restrict__ row_node) {
+    pdl_enter();
     // row_node != null: x is in degree-bucket order (rows = bucket capacity), dy / y in node order
     __shared__ float sh[4][2][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
@@ -240,6 +245,7 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
 
 // one warp per channel: lanes stride over the chunks (each lane sums its chunks in order), then a fixed shuffle tree
 __global__ void k_bn_bwd_final(const float* __restrict__ partial, int nchunks, int C, float* __restrict__ dweight, float* __restrict__ dbias) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (c >= C) return;                              // warp-uniform
@@ -261,6 +267,7 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
                                const float* __restrict__ rstd, const float* __restrict__ dweight,
                                const float* __restrict__ dbias, int relu, float* __restrict__ dx,
                                const int* __restrict__ row_node, long long n_valid) {
+    pdl_enter();
     const int c4 = C / 4;
     long long total = rows * c4;
     const float inv_n = 1.f / (float)n_valid;
@@ -292,6 +299,7 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
 // ------------------------------------------------------------------ graph pooling over contiguous node ranges
 // one warp per (graph, 128-col chunk); mode 0 add, 1 mean, 2 max (empty graph -> 0)
 __global__ void k_pool_fwd(const float* __restrict__ x, const int* __restrict__ gp, int G, int C, int mode, float* __restrict__ out) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (C + 127) / 128;
     const long long nwork = (long long)G * chunks;
@@ -321,6 +329,7 @@ __global__ void k_pool_fwd(const float* __restrict__ x, const int* __restrict__ 
 
 __global__ void k_pool_bwd(const float* __restrict__ dout, const float* __restrict__ x, const float* __restrict__ out,
                            const int* __restrict__ gp, int G, int C, int mode, float* __restrict__ dx) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (C + 127) / 128;
     const long long nwork = (long long)G * chunks;
@@ -360,6 +369,7 @@ __global__ void k_pool_bwd(const float* __restrict__ dout, const float* __restri
 // ------------------------------------------------------------------ loss: Huber(delta) on the relative error + MAPE
 __global__ void k_relhuber(const float* __restrict__ pred, const float* __restrict__ target, int count, float delta,
                            float* __restrict__ out2, float* __restrict__ dpred) {
+    pdl_enter();
     __shared__ float sh[2][32];
     float l = 0.f, mp = 0.f;
     const float inv = 1.f / (float)count;
@@ -390,6 +400,7 @@ __global__ void k_relhuber(const float* __restrict__ pred, const float* __restri
 __global__ void k_adamw_amsgrad(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                                 float* __restrict__ vmax, long long count, float lr, float b1, float b2, float eps, float wd,
                                 float bc1, float bc2_sqrt, float gscale) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         float grad = g[i] * gscale;
         float param = p[i] * (1.f - lr * wd);
@@ -430,13 +441,13 @@ static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int3
         GNNX_REQUIRE(n_valid > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
         int nch = bn_chunks(rows, C);
         int rpc = ceil_div(rows, nch);
-        k_bn_stats_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(x, (int)rows, C, rpc, (float*)ws, row_node);
-        k_bn_stats_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
+        launch(k_bn_stats_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, x, (int)rows, C, rpc, (float*)ws, row_node);
+        launch(k_bn_stats_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
     } else {
         GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
-        k_bn_eval_stats<<<ceil_div(C, 128), 128, 0, st>>>(running_mean, running_var, C, eps, save_mean, save_rstd);
+        launch(k_bn_eval_stats, ceil_div(C, 128), 128, 0, st, running_mean, running_var, C, eps, save_mean, save_rstd);
     }
-    k_bn_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(x, rows, C, weight, bias, save_mean, save_rstd, relu, y, row_node);
+    launch(k_bn_apply, flat_grid(rows * (C / 4)), 256, 0, st, x, rows, C, weight, bias, save_mean, save_rstd, relu, y, row_node);
     return check_launch("bn_relu_fwd", training ? 3 : 2);
 }
 
@@ -465,9 +476,9 @@ static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t 
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
-    k_bn_bwd_partial<<<dim3(ceil_div(C, 256), nch), 256, 0, st>>>(dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node);
-    k_bn_bwd_final<<<ceil_div(C, 8), 256, 0, st>>>((const float*)ws, nch, C, dweight, dbias);
-    k_bn_bwd_apply<<<flat_grid(rows * (C / 4)), 256, 0, st>>>(dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid);
+    launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node);
+    launch(k_bn_bwd_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, dweight, dbias);
+    launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid);
     return check_launch("bn_relu_bwd", 3);
 }
 
@@ -490,7 +501,7 @@ int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, i
     if (G == 0) return GNNX_OK;
     long long nwork = G * ((C + 127) / 128);
     int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
-    k_pool_fwd<<<nb, 256, 0, as_stream(stream)>>>(x, graph_ptr, (int)G, C, mode, out);
+    launch(k_pool_fwd, nb, 256, 0, as_stream(stream), x, graph_ptr, (int)G, C, mode, out);
     return check_launch("segment_pool_fwd");
 }
 
@@ -500,13 +511,13 @@ int gnnx_segment_pool_bwd(const float* dout, const float* x, const float* out, c
     if (G == 0) return GNNX_OK;
     long long nwork = G * ((C + 127) / 128);
     int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
-    k_pool_bwd<<<nb, 256, 0, as_stream(stream)>>>(dout, x, out, graph_ptr, (int)G, C, mode, dx);
+    launch(k_pool_bwd, nb, 256, 0, as_stream(stream), dout, x, out, graph_ptr, (int)G, C, mode, dx);
     return check_launch("segment_pool_bwd");
 }
 
 int gnnx_relhuber_fwd_bwd(const float* pred, const float* target, int64_t count, float delta, float* out2, float* dpred, void* stream) {
     GNNX_REQUIRE(count > 0 && count < (1ll << 31), "relhuber: count out of range");
-    k_relhuber<<<1, 1024, 0, as_stream(stream)>>>(pred, target, (int)count, delta, out2, dpred);
+    launch(k_relhuber, 1, 1024, 0, as_stream(stream), pred, target, (int)count, delta, out2, dpred);
     return check_launch("relhuber_fwd_bwd");
 }
 
@@ -516,7 +527,7 @@ int gnnx_adamw_amsgrad(float* param, const float* grad, float* exp_avg, float* e
     if (count == 0) return GNNX_OK;
     double bc1 = 1.0 - pow((double)beta1, (double)step);
     double bc2 = 1.0 - pow((double)beta2, (double)step);
-    k_adamw_amsgrad<<<flat_grid(count), 256, 0, as_stream(stream)>>>(param, grad, exp_avg, exp_avg_sq, max_exp_avg_sq, count, lr, beta1,
+    launch(k_adamw_amsgrad, flat_grid(count), 256, 0, as_stream(stream), param, grad, exp_avg, exp_avg_sq, max_exp_avg_sq, count, lr, beta1,
                                                                       beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
     return check_launch("adamw_amsgrad");
 }
@@ -528,6 +539,7 @@ namespace gnnx {
 __global__ void k_assemble_params(const float* __restrict__ msigmae, const float* __restrict__ log10assoc,
                                   const float* __restrict__ assoc, const float* __restrict__ munanb,
                                   const float* __restrict__ mw, long long G, float* __restrict__ out) {
+    pdl_enter();
     for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < G; g += (long long)gridDim.x * blockDim.x) {
         float* o = out + g * 9;
         o[0] = msigmae[g * 3]; o[1] = msigmae[g * 3 + 1]; o[2] = msigmae[g * 3 + 2];
@@ -551,6 +563,6 @@ extern "C" int gnnx_assemble_params(const float* msigmae, const float* log10asso
     if (G == 0) return GNNX_OK;
     long long blocks = (G + 255) / 256;
     if (blocks > gnnx::kNumSMs * 8) blocks = gnnx::kNumSMs * 8;
-    gnnx::k_assemble_params<<<(int)blocks, 256, 0, gnnx::as_stream(stream)>>>(msigmae, log10assoc, assoc, munanb, mw, G, out9);
+    launch(gnnx::k_assemble_params, (int)blocks, 256, 0, gnnx::as_stream(stream), msigmae, log10assoc, assoc, munanb, mw, G, out9);
     return gnnx::check_launch("assemble_params");
 }

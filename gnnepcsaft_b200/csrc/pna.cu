@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(256)
 k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __restrict__ r, long long ld_r,
                  const RIdx* __restrict__ ridx, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
                  int N, int H, int relu, float* __restrict__ h, uint32_t* __restrict__ bits) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
     const int words = (H + 31) / 32;
@@ -79,6 +80,7 @@ k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __r
 __global__ void __launch_bounds__(256)
 k_pna_gather_bwd(const float* __restrict__ dh, const int* __restrict__ rowptr, const int* __restrict__ colptr,
                  const int* __restrict__ csc_pos, int N, int H, float* __restrict__ dpq, long long ld) {
+    pdl_enter();
     const int lane = threadIdx.x & 31;
     const int chunks = (H + 127) / 128;
     const long long nwork = (long long)N * chunks;
@@ -106,6 +108,7 @@ k_pna_gather_bwd(const float* __restrict__ dh, const int* __restrict__ rowptr, c
 
 __global__ void k_permute_rows(const float* __restrict__ in, const int* __restrict__ dst_row, long long E, int H,
                                float* __restrict__ out, long long ld_out) {
+    pdl_enter();
     const int h4 = H / 4;
     long long total = E * h4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -119,6 +122,7 @@ __global__ void k_permute_rows(const float* __restrict__ in, const int* __restri
 constexpr int kCodeRows = 8;
 __global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* __restrict__ codes, int rows,
                                    int ncodes, int H, int rows_per_chunk, float* __restrict__ partial) {
+    pdl_enter();
     extern __shared__ float tab[];   // [kCodeRows][ncodes][32]
     int c = blockIdx.x * 32 + threadIdx.x;
     float* mine = tab + (long long)threadIdx.y * ncodes * 32;
@@ -150,6 +154,7 @@ __global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* 
         }
 }
 __global__ void k_sum_partials(const float* __restrict__ partial, int nchunks, long long count, float* __restrict__ out) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
         float s = 0.f;
         for (int ch = 0; ch < nchunks; ++ch) s += partial[(long long)ch * count + i];
@@ -179,6 +184,7 @@ __global__ void __launch_bounds__(256)
 k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr, int N, int T, int F,
                     float* __restrict__ agg, long long ld_agg, const int* __restrict__ row_node, int rows,
                     const float* __restrict__ x) {
+    pdl_enter();
     // row_node == null: output row i = node i.  Otherwise the kernel walks the `rows` OUTPUT rows (degree-bucket order):
     // row r holds node row_node[r], or is a padding row (-1) and is zero-filled; with x the node's input row is copied
     // behind the aggregates ([agg | x], the operand of the degree-grouped post Linear).
@@ -247,6 +253,7 @@ __global__ void __launch_bounds__(256)
 k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m, const float* __restrict__ agg,
                     const int* __restrict__ rowptr, int N, int T, int F, float* __restrict__ dm, long long ld_agg,
                     const int* __restrict__ node_pos, float* __restrict__ dx) {
+    pdl_enter();
     // node_pos != null: agg / dagg rows live at node_pos[i] (degree-bucket order, row stride ld_agg); with dx the
     // gradient of the copied input row ([agg | x] operand) is moved back to node order: dx[i] = dagg[pos, 4H:5H]
     const int H = T * F;
@@ -310,6 +317,7 @@ __device__ __forceinline__ void pna_scalers(const int* __restrict__ rowptr, int 
 __global__ void k_pna_post_combine_fwd(const float* __restrict__ z, const float* __restrict__ bias,
                                        const int* __restrict__ rowptr, float avg_deg_log, long long N, int H, int relu,
                                        float* __restrict__ out) {
+    pdl_enter();
     const int h4 = H / 4;
     long long total = N * h4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -333,6 +341,7 @@ __global__ void k_pna_post_combine_fwd(const float* __restrict__ z, const float*
 __global__ void k_pna_post_combine_bwd(const float* __restrict__ dout, const float* __restrict__ out,
                                        const int* __restrict__ rowptr, float avg_deg_log, long long N, int H, int relu,
                                        float* __restrict__ dz) {
+    pdl_enter();
     const int h4 = H / 4;
     long long total = N * h4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -357,6 +366,7 @@ __global__ void k_pna_post_combine_bwd(const float* __restrict__ dout, const flo
 }
 
 __global__ void k_relu_bwd(const float* __restrict__ dy, const float* __restrict__ y, long long count, float* __restrict__ dx) {
+    pdl_enter();
     long long n4 = count / 4;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
         F4 g = f4_lds(dy + i * 4), o = f4_lds(y + i * 4);
@@ -397,9 +407,9 @@ int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t 
     int grid = warp_grid((long long)N * chunks);
     grid = (grid + chunks - 1) / chunks * chunks;               // every warp keeps one column chunk
     if (ridx_i32)
-        k_pna_gather_fwd<int><<<grid, 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
+        launch(k_pna_gather_fwd<int>, grid, 256, 0, as_stream(stream), pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
     else
-        k_pna_gather_fwd<uint8_t><<<grid, 256, 0, as_stream(stream)>>>(pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
+        launch(k_pna_gather_fwd<uint8_t>, grid, 256, 0, as_stream(stream), pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
     return check_launch("pna_gather_fwd");
 }
 
@@ -409,10 +419,10 @@ int gnnx_pna_gather_bwd(const float* dh, const int32_t* rowptr, const int32_t* c
     GNNX_REQUIRE(H % 4 == 0 && ld_dpq % 4 == 0, "pna_gather_bwd: hidden / strides must be multiples of 4");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((H + 127) / 128);
-    k_pna_gather_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
+    launch(k_pna_gather_bwd, warp_grid(nwork), 256, 0, as_stream(stream), dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
     if (dr_edge && E > 0) {
         GNNX_REQUIRE(ld_dr % 4 == 0 && csr_eid, "pna_gather_bwd: dr_edge needs csr_eid and an aligned stride");
-        k_permute_rows<<<flat_grid(E * (H / 4)), 256, 0, as_stream(stream)>>>(dh, csr_eid, E, H, dr_edge, ld_dr);
+        launch(k_permute_rows, flat_grid(E * (H / 4)), 256, 0, as_stream(stream), dh, csr_eid, E, H, dr_edge, ld_dr);
     }
     return check_launch("pna_gather_bwd", (dr_edge && E > 0) ? 2 : 1);
 }
@@ -434,8 +444,8 @@ int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, i
     GNNX_REQUIRE(smem <= 200 * 1024, "code_segment_sum: too many codes for the shared-memory tables");
     if (smem > 48 * 1024)
         GNNX_CUDA(cudaFuncSetAttribute(k_code_sum_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_code_sum_partial<<<dim3(ceil_div(H, 32), nch), dim3(32, kCodeRows), smem, st>>>(dh, codes, (int)rows, ncodes, H, rpc, (float*)ws);
-    k_sum_partials<<<flat_grid(count), 256, 0, st>>>((const float*)ws, nch, count, dtable);
+    launch(k_code_sum_partial, dim3(ceil_div(H, 32), nch), dim3(32, kCodeRows), smem, st, dh, codes, (int)rows, ncodes, H, rpc, (float*)ws);
+    launch(k_sum_partials, flat_grid(count), 256, 0, st, (const float*)ws, nch, count, dtable);
     return check_launch("code_segment_sum", 2);
 }
 
@@ -443,7 +453,7 @@ int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t N, int
     GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_fwd: F must be a positive multiple of 4");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((T * F + 127) / 128);
-    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, agg, 4ll * T * F, nullptr, 0, nullptr);
+    launch(k_pna_aggregate_fwd, warp_grid(nwork), 256, 0, as_stream(stream), m, rowptr, (int)N, T, F, agg, 4ll * T * F, nullptr, 0, nullptr);
     return check_launch("pna_aggregate_fwd");
 }
 
@@ -453,7 +463,7 @@ int gnnx_pna_aggregate_rows_fwd(const float* m, const int32_t* rowptr, int64_t N
     GNNX_REQUIRE(row_node && ld_out % 4 == 0 && ld_out >= (x ? 5 : 4) * (int64_t)T * F, "pna_aggregate_rows_fwd: row map / stride");
     if (rows == 0) return GNNX_OK;
     long long nwork = (long long)rows * ((T * F + 127) / 128);
-    k_pna_aggregate_fwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(m, rowptr, (int)N, T, F, out, ld_out, row_node, (int)rows, x);
+    launch(k_pna_aggregate_fwd, warp_grid(nwork), 256, 0, as_stream(stream), m, rowptr, (int)N, T, F, out, ld_out, row_node, (int)rows, x);
     return check_launch("pna_aggregate_rows_fwd");
 }
 
@@ -462,7 +472,7 @@ int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, 
     GNNX_REQUIRE(T >= 1 && F >= 4 && F % 4 == 0, "pna_aggregate_bwd: F must be a positive multiple of 4");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((T * F + 127) / 128);
-    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm, 4ll * T * F, nullptr, nullptr);
+    launch(k_pna_aggregate_bwd, warp_grid(nwork), 256, 0, as_stream(stream), dagg, m, agg, rowptr, (int)N, T, F, dm, 4ll * T * F, nullptr, nullptr);
     return check_launch("pna_aggregate_bwd");
 }
 
@@ -472,7 +482,7 @@ int gnnx_pna_aggregate_rows_bwd(const float* dagg, const float* m, const float* 
     GNNX_REQUIRE(node_pos && ld % 4 == 0 && ld >= (dx ? 5 : 4) * (int64_t)T * F, "pna_aggregate_rows_bwd: row map / stride");
     if (N == 0) return GNNX_OK;
     long long nwork = (long long)N * ((T * F + 127) / 128);
-    k_pna_aggregate_bwd<<<warp_grid(nwork), 256, 0, as_stream(stream)>>>(dagg, m, agg, rowptr, (int)N, T, F, dm, ld, node_pos, dx);
+    launch(k_pna_aggregate_bwd, warp_grid(nwork), 256, 0, as_stream(stream), dagg, m, agg, rowptr, (int)N, T, F, dm, ld, node_pos, dx);
     return check_launch("pna_aggregate_rows_bwd");
 }
 
@@ -480,7 +490,7 @@ int gnnx_pna_post_combine_fwd(const float* z, const float* bias, const int32_t* 
                               int32_t H, int32_t relu, float* out, void* stream) {
     GNNX_REQUIRE(H % 4 == 0, "pna_post_combine_fwd: h_out must be a multiple of 4");
     if (N == 0) return GNNX_OK;
-    k_pna_post_combine_fwd<<<flat_grid(N * (H / 4)), 256, 0, as_stream(stream)>>>(z, bias, rowptr, avg_deg_log, N, H, relu, out);
+    launch(k_pna_post_combine_fwd, flat_grid(N * (H / 4)), 256, 0, as_stream(stream), z, bias, rowptr, avg_deg_log, N, H, relu, out);
     return check_launch("pna_post_combine_fwd");
 }
 
@@ -488,14 +498,14 @@ int gnnx_pna_post_combine_bwd(const float* dout, const float* out, const int32_t
                               int32_t H, int32_t relu, float* dz, void* stream) {
     GNNX_REQUIRE(H % 4 == 0, "pna_post_combine_bwd: h_out must be a multiple of 4");
     if (N == 0) return GNNX_OK;
-    k_pna_post_combine_bwd<<<flat_grid(N * (H / 4)), 256, 0, as_stream(stream)>>>(dout, out, rowptr, avg_deg_log, N, H, relu, dz);
+    launch(k_pna_post_combine_bwd, flat_grid(N * (H / 4)), 256, 0, as_stream(stream), dout, out, rowptr, avg_deg_log, N, H, relu, dz);
     return check_launch("pna_post_combine_bwd");
 }
 
 int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream) {
     if (count == 0) return GNNX_OK;
     GNNX_REQUIRE(((uintptr_t)dy % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)dx % 16 == 0), "relu_bwd: pointers must be 16-byte aligned");
-    k_relu_bwd<<<flat_grid(count / 4 + 1), 256, 0, as_stream(stream)>>>(dy, y, count, dx);
+    launch(k_relu_bwd, flat_grid(count / 4 + 1), 256, 0, as_stream(stream), dy, y, count, dx);
     return check_launch("relu_bwd");
 }
 

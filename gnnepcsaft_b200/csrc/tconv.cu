@@ -14,6 +14,7 @@ k_tconv_fwd(const float* __restrict__ qkv, const float* __restrict__ ee, long lo
             const int* __restrict__ rowptr, const int* __restrict__ csr_src, int N, int heads, int C, int log2c, int groups,
             float scale, unsigned int drop_thr, float keep_scale, unsigned long long seed, const float* skip,
             float* __restrict__ agg, float* out, float* alpha) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -147,6 +148,7 @@ k_tconv_bwd_dst(const float* __restrict__ dout, const float* __restrict__ qkv, c
                 const int* __restrict__ rowptr, const int* __restrict__ csr_src, const int* __restrict__ csr_eid, int N,
                 int heads, int C, int log2c, int groups, float scale, float keep_scale, float* __restrict__ dqkv,
                 float* __restrict__ ds, float* __restrict__ de) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -241,6 +243,7 @@ __global__ void __launch_bounds__(256)
 k_tconv_bwd_src(const float* __restrict__ dout, const float* __restrict__ ds, const float* __restrict__ alpha,
                 const int* __restrict__ colptr, const int* __restrict__ csc_pos, const int* __restrict__ csc_dst, int N,
                 int heads, int C, int log2c, float keep_scale, float* __restrict__ dqkv) {
+    pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
@@ -312,8 +315,8 @@ int gnnx_tconv_fwd(const float* qkv, const float* e, int64_t ld_e, const int32_t
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
 #define CALL(NQ)                                                                                                          \
-    if (eidx_i32) k_tconv_fwd<NQ, int><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_i32, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha); \
-    else k_tconv_fwd<NQ, uint8_t><<<grid, 256, 0, st>>>(qkv, e, ld_e, eidx_u8, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha)
+    if (eidx_i32) launch(k_tconv_fwd<NQ, int>, grid, 256, 0, st, qkv, e, ld_e, eidx_i32, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha); \
+    else launch(k_tconv_fwd<NQ, uint8_t>, grid, 256, 0, st, qkv, e, ld_e, eidx_u8, rowptr, csr_src, (int)N, heads, C, ilog2(C), s.groups, scale, thr, ks, sd, skip, agg, out, alpha)
     TCONV_DISPATCH(s, CALL);
 #undef CALL
     return check_launch("tconv_fwd");
@@ -336,11 +339,11 @@ int gnnx_tconv_bwd(const float* dout, const float* qkv, const float* e, int64_t 
     const int grid = attn_row_grid(N, s.groups, 16);
     const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                          \
-    if (eidx_i32) k_tconv_bwd_dst<NQ, int><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_i32, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de); \
-    else k_tconv_bwd_dst<NQ, uint8_t><<<grid, 256, 0, st>>>(dout, qkv, e, ld_e, eidx_u8, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de)
+    if (eidx_i32) launch(k_tconv_bwd_dst<NQ, int>, grid, 256, 0, st, dout, qkv, e, ld_e, eidx_i32, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de); \
+    else launch(k_tconv_bwd_dst<NQ, uint8_t>, grid, 256, 0, st, dout, qkv, e, ld_e, eidx_u8, alpha, agg, rowptr, csr_src, csr_eid, (int)N, heads, C, ilog2(C), s.groups, scale, ks, dqkv, ds, de)
     TCONV_DISPATCH(s, CALL);
 #undef CALL
-    k_tconv_bwd_src<<<attn_row_grid(N, (s.H + 127) / 128, 16), 256, 0, st>>>(dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, heads, C, ilog2(C), ks, dqkv);
+    launch(k_tconv_bwd_src, attn_row_grid(N, (s.H + 127) / 128, 16), 256, 0, st, dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, heads, C, ilog2(C), ks, dqkv);
     return check_launch("tconv_bwd", 2);
 }
 
