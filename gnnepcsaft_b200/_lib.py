@@ -98,6 +98,21 @@ class _Lib:
             raise GnnxError(f"{name} failed with code {rc}: {self.last_error()}")
         self._timing.append((name, args, e0, e1))
 
+    def trace_begin(self) -> None:
+        """Open a per-kernel device timeline (two CUDA events around every kernel launch of the library)."""
+        self._dll.gnnx_trace_begin()
+
+    def trace_end(self):
+        """Close it: ``[(kernel name, kernel us, us since the previous gnnx kernel ended)]`` in launch order."""
+        n = int(self._dll.gnnx_trace_end(None, 0))
+        buf = ctypes.create_string_buffer(n + 16)
+        self._dll.gnnx_trace_end(buf, n + 16)
+        rows = []
+        for line in buf.value.decode().splitlines():
+            name, us, gap = line.rsplit("\t", 2)
+            rows.append((name, float(us), float(gap)))
+        return rows
+
     def launch_count(self) -> int:
         """Kernels launched by libgnnx so far in this process."""
         return int(self._dll.gnnx_launch_count())

@@ -45,6 +45,12 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 __device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
 
 bool pdl_enabled();
+// Per-kernel device timeline (gnnx_trace_begin / gnnx_trace_end): while a trace is open every launch() is bracketed by
+// two CUDA events on its stream, so the report gives each kernel's in-situ duration (warm caches, real predecessors)
+// and the time the stream spent between gnnx kernels (other libraries' kernels, launch gaps).
+bool trace_on();
+void trace_before(const void* func, cudaStream_t st);
+void trace_after(cudaStream_t st);
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
@@ -57,7 +63,11 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     if (pdl_enabled()) { cfg.attrs = attr; cfg.numAttrs = 1; }
-    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    if (!trace_on()) return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    trace_before(reinterpret_cast<const void*>(kernel), st);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    trace_after(st);
+    return e;
 }
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }

@@ -6,6 +6,10 @@
 #include <string.h>
 
 #include <stdlib.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
 
 #include "common.cuh"
 
@@ -14,6 +18,19 @@ namespace gnnx {
 static thread_local char g_err[512] = "";
 static unsigned long long g_launches = 0;
 void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+// ---- per-kernel device timeline (diagnostic; single-threaded use)
+struct TraceRec { const void* func; cudaEvent_t e0, e1; };
+static bool g_trace = false;
+static std::vector<TraceRec> g_trace_recs;
+bool trace_on() { return g_trace; }
+void trace_before(const void* func, cudaStream_t st) {
+    TraceRec r; r.func = func;
+    cudaEventCreate(&r.e0); cudaEventCreate(&r.e1);
+    cudaEventRecord(r.e0, st);
+    g_trace_recs.push_back(r);
+}
+void trace_after(cudaStream_t st) { cudaEventRecord(g_trace_recs.back().e1, st); }
+
 bool pdl_enabled() {
     static int on = -1;
     if (on < 0) { const char* e = getenv("GNNX_PDL"); on = (e && e[0] == '0') ? 0 : 1; }
@@ -383,6 +400,37 @@ int gnnx_collate_packed(const uint8_t* sx, const int16_t* ssrc, const int16_t* s
     launch(k_collate_packed, nb, 256, 0, as_stream(stream), sx, ssrc, sdst, sea, snp, sep, gids, (int)G, noff, eoff,
                                                         ox, osrc, odst, oea, obatch);
     return check_launch("collate_packed");
+}
+
+
+int gnnx_trace_begin(void) {
+    for (auto& r : g_trace_recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+    g_trace_recs.clear();
+    g_trace = true;
+    return GNNX_OK;
+}
+
+// Writes "name\tkernel_us\tgap_before_us" lines (launch order; gap = end of the previous gnnx kernel -> start of this
+// one on the device timeline) into buf, returns the number of bytes needed (call with cap = 0 to size the buffer).
+int64_t gnnx_trace_end(char* buf, int64_t cap) {
+    g_trace = false;
+    cudaDeviceSynchronize();
+    int64_t need = 0;
+    for (size_t i = 0; i < g_trace_recs.size(); ++i) {
+        const TraceRec& r = g_trace_recs[i];
+        float us = 0.f, gap = 0.f;
+        cudaEventElapsedTime(&us, r.e0, r.e1);
+        if (i > 0) cudaEventElapsedTime(&gap, g_trace_recs[i - 1].e1, r.e0);
+        const char* name = nullptr;
+        if (cudaFuncGetName(&name, r.func) != cudaSuccess || !name) name = "?";
+        char line[1024];
+        int n = snprintf(line, sizeof line, "%s\t%.3f\t%.3f\n", name, us * 1000.f, gap * 1000.f);
+        if (buf && need + n < cap) memcpy(buf + need, line, n);
+        need += n;
+    }
+    if (buf && cap > 0) buf[need < cap ? need : cap - 1] = 0;
+    cudaGetLastError();
+    return need + 1;
 }
 
 }  // extern "C"

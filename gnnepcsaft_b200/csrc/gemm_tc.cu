@@ -17,6 +17,10 @@
 // HBM/L2-bound, not tensor-bound: see DESIGN.md for the roofline of each.
 #include <cudaTypedefs.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -383,7 +387,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
                   const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
                   uint32_t* __restrict__ bits_out, long long ldbits, float* __restrict__ colsum_partial,
-                  const int* __restrict__ bucket_ptr, int n_groups, int group_rows) {
+                  const int* __restrict__ bucket_ptr, int n_groups, int group_rows, float* __restrict__ colsum_out,
+                  int* __restrict__ ticket) {
     extern __shared__ uint8_t smem_raw[];
     Smem2 sm;
     sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -516,6 +521,45 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int col = kb * kBK + cj * 4;
                 if (kb < KB && rr == 0 && col < K)                    // K % 4 == 0 (tc_supported: lda % 4, TMA box)
                     *reinterpret_cast<float4*>(colsum_partial + (long long)blockIdx.x * K + col) = v;
+            }
+            // The CTA whose partial row lands last folds all of them, in CTA order (which CTA that is varies from run to
+            // run, the order of the sum does not): no second launch for the bias gradient.  The ticket is left at 0.
+            __threadfence();
+            __syncwarp();
+            int last = 0;
+            if (lane == 0) last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
+            last = __shfl_sync(0xffffffffu, last, 0);
+            if (last) {
+                __threadfence();
+                const int nb = (int)gridDim.x;
+                // lane l folds columns 4l..4l+3 and 128+4l..; 8 partial rows x 2 column groups = 16 loads in flight
+                const int c0 = lane * 4, c1 = c0 + 128;
+                const bool h0 = c0 < K, h1 = c1 < K;
+                float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+                const float4 z = s0;
+                int b = 0;
+                for (; b + 8 <= nb; b += 8) {
+                    float4 t0[8], t1[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float* p = colsum_partial + (long long)(b + j) * K;
+                        t0[j] = h0 ? __ldcg(reinterpret_cast<const float4*>(p + c0)) : z;
+                        t1[j] = h1 ? __ldcg(reinterpret_cast<const float4*>(p + c1)) : z;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        s0.x += t0[j].x; s0.y += t0[j].y; s0.z += t0[j].z; s0.w += t0[j].w;
+                        s1.x += t1[j].x; s1.y += t1[j].y; s1.z += t1[j].z; s1.w += t1[j].w;
+                    }
+                }
+                for (; b < nb; ++b) {
+                    const float* p = colsum_partial + (long long)b * K;
+                    if (h0) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p + c0)); s0.x += t.x; s0.y += t.y; s0.z += t.z; s0.w += t.w; }
+                    if (h1) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p + c1)); s1.x += t.x; s1.y += t.y; s1.z += t.z; s1.w += t.w; }
+                }
+                if (h0) *reinterpret_cast<float4*>(colsum_out + c0) = s0;
+                if (h1) *reinterpret_cast<float4*>(colsum_out + c1) = s1;
+                if (lane == 0) *ticket = 0;
             }
         }
     } else {
@@ -720,6 +764,23 @@ static RedPlan red_plan(int64_t Mo, int64_t No, int64_t R) {
 
 using namespace tc;
 
+// One zero-initialised arrival counter per (device, stream): kernels of a stream run in order and each leaves it at 0.
+static int* stream_ticket(cudaStream_t stream) {
+    static std::mutex mu;
+    static std::map<std::pair<int, cudaStream_t>, int*> tickets;
+    std::lock_guard<std::mutex> lock(mu);
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    const std::pair<int, cudaStream_t> st(dev, stream);
+    auto it = tickets.find(st);
+    if (it != tickets.end()) return it->second;
+    int* p = nullptr;
+    if (cudaMalloc(&p, 256) != cudaSuccess) return nullptr;
+    if (cudaMemset(p, 0, 256) != cudaSuccess) return nullptr;
+    tickets[st] = p;
+    return p;
+}
+
 bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
                   const void* B, const void* C, int precision) {
     (void)precision;
@@ -802,22 +863,28 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         const long long ldc_ = ldc, ldm_ = ldm;
         const long long ldbits = (N + 31) / 32;          // packed masks are row-major: [M, ceil(N/32)] words
         float* csp = nullptr;                            // per-CTA partial column sums of A (fused bias gradient)
+        int* tk = nullptr;                               // arrival counter: the last CTA folds the partials in-kernel
         if (colsum_a_out) {
             GNNX_REQUIRE(K <= kColsumMaxK, "gemm_tc: fused column sums cover K <= %d", kColsumMaxK);
             GNNX_REQUIRE(ws && ws_bytes >= (size_t)ncl * cluster * K * sizeof(float), "gemm_tc: workspace too small for the column-sum partials");
             csp = (float*)ws;
+            GNNX_REQUIRE(((uintptr_t)colsum_a_out & 15) == 0, "gemm_tc: colsum_a_out must be 16-byte aligned");
+            tk = stream_ticket(st);
+            if (!tk) return set_error(GNNX_ERR_INVALID, "gemm_tc: could not allocate the column-sum ticket");
         }
         cudaError_t e;
+        if (trace_on())
+            trace_before(cluster == 2 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 2> : (const void*)k_gemm_tf32_rows2<true, 2>)
+                                      : (tb ? (const void*)k_gemm_tf32_rows2<false, 1> : (const void*)k_gemm_tf32_rows2<true, 1>), st);
         if (cluster == 2)
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
         else
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
+        if (trace_on()) trace_after(st);
         if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
-        int rc = check_launch("gemm_tf32_rows2");
-        if (rc == GNNX_OK && csp) rc = colsum_final_launch(csp, ncl * cluster, (int)K, colsum_a_out, st);
-        return rc;
+        return check_launch("gemm_tf32_rows2");
     }
     if (!ta) {
         GNNX_REQUIRE(!bucket_ptr, "gemm_tc: grouped products need the v2 kernel (unset GNNX_GEMM_V1)");

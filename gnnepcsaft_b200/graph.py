@@ -191,3 +191,48 @@ def batch_from_reference_tensors(x: Tensor, edge_index: Tensor, edge_attr: Tenso
         G = num_graphs
         gp = ops.graph_ptr_from_batch(batch, G)
     return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, batch=batch, num_graphs=G, index=index, graph_ptr=gp)
+
+
+class HostBatchPrefetcher:
+    """Host -> device input pipeline for the reference-facing path (the reference's ``DataLoader(pin_memory=True)`` hands
+    ``training_step`` one host batch at a time, train/train.py:59-75): iterates over tuples of PINNED host tensors and
+    yields them as device tensors, with the copy of batch i+1 issued on a copy stream before batch i is returned, so
+    the H2D transfer (16 MB of int64 at cfg2, ~0.6 ms) runs under the previous step's kernels.  Stream-ordered only:
+    the consumer's stream waits on the copy's event, and the tensors are recorded on it for the caching allocator."""
+
+    def __init__(self, host_batches, device):
+        self.it = iter(host_batches)
+        self.device = device
+        self.copy_stream = torch.cuda.Stream(device)
+        self._next = None
+        self._stage()
+
+    def _stage(self):
+        try:
+            host = next(self.it)
+        except StopIteration:
+            self._next = None
+            return
+        for t in host:
+            if isinstance(t, Tensor) and not t.is_pinned():
+                raise ValueError("HostBatchPrefetcher: host tensors must be pinned (the copy would not be asynchronous)")
+        with torch.cuda.stream(self.copy_stream):
+            dev = tuple(t.to(self.device, non_blocking=True) if isinstance(t, Tensor) else t for t in host)
+            ev = torch.cuda.Event()
+            ev.record(self.copy_stream)
+        self._next = (dev, ev)
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self._next is None:
+            raise StopIteration
+        dev, ev = self._next
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        for t in dev:
+            if isinstance(t, Tensor):
+                t.record_stream(cur)
+        self._stage()
+        return dev

@@ -44,6 +44,12 @@ GNNX_API int gnnx_abi_version(void);
 GNNX_API const char* gnnx_last_error(void);
 /* Total number of CUDA kernels launched by this library in this process (monotonic). */
 GNNX_API int64_t gnnx_launch_count(void);
+/* Diagnostic per-kernel device timeline: between trace_begin and trace_end every kernel launch of this library is
+ * bracketed by two CUDA events on its stream.  trace_end synchronises the device and writes one line per launch,
+ * "kernel name \t kernel us \t us since the previous gnnx kernel ended" (launch order), into buf; it returns the
+ * buffer size needed (call with buf = NULL to size it first; the records stay until the next trace_begin). */
+GNNX_API int gnnx_trace_begin(void);
+GNNX_API int64_t gnnx_trace_end(char* buf, int64_t cap);
 
 /* ------------------------------------------------------------------ collator (integer) */
 /* Replaces: PyG Batch.from_data_list + the unordered COO scatter indexing

