@@ -120,6 +120,7 @@ __global__ void k_permute_rows(const float* __restrict__ in, const int* __restri
 
 // grid: (ceil(H/32), nchunks), block (32, 8): each threadIdx.y owns a private [ncodes][32] table in smem
 constexpr int kCodeRows = 8;
+constexpr int kCodeFlight = 12;   // 12 KB in flight per SM at 4 rows was the limiter (2.5 TB/s): Little's law wants ~3x that
 __global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* __restrict__ codes, int rows,
                                    int ncodes, int H, int rows_per_chunk, float* __restrict__ partial) {
     pdl_enter();
@@ -131,16 +132,16 @@ __global__ void k_code_sum_partial(const float* __restrict__ dh, const uint8_t* 
     int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
     if (c < H) {
         int r = r0 + threadIdx.y;
-        for (; r + 3 * kCodeRows < r1; r += 4 * kCodeRows) {           // 4 rows in flight; adds stay in row order
-            int cd[4];
-            float v[4];
+        for (; r + (kCodeFlight - 1) * kCodeRows < r1; r += kCodeFlight * kCodeRows) {   // rows in flight; adds stay in row order
+            int cd[kCodeFlight];
+            float v[kCodeFlight];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kCodeFlight; ++u) {
                 cd[u] = codes[r + u * kCodeRows];
                 v[u] = __ldcs(dh + (long long)(r + u * kCodeRows) * H + c);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) mine[cd[u] * 32 + threadIdx.x] += v[u];
+            for (int u = 0; u < kCodeFlight; ++u) mine[cd[u] * 32 + threadIdx.x] += v[u];
         }
         for (; r < r1; r += kCodeRows) mine[(int)codes[r] * 32 + threadIdx.x] += __ldg(dh + (long long)r * H + c);
     }

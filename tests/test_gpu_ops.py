@@ -11,7 +11,7 @@ import torch
 from gnnepcsaft_b200 import functional as Fn
 from gnnepcsaft_b200 import graph, nn as gnn, ops
 from oracle import pyg_restated as O
-from tests.util import assert_as_accurate, assert_close, make_batch
+from tests.util import reproducible, assert_as_accurate, assert_close, make_batch
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -101,7 +101,7 @@ def test_pna_aggregate_fwd_bwd(T, F):
         mo = m.detach().clone().to(dtype).requires_grad_(True)
         out = torch.cat([O._AGGRS[a](mo.view(E, T, F), ei[1], N) for a in ("mean", "min", "max", "std")], -1)   # [N,T,4F]
         return mo, out
-    m_o, ref = oracle(torch.float32)
+    m_o, ref = reproducible(lambda: oracle(torch.float32))
     m_64, ref64 = oracle(torch.float64)
     m_sorted = m[perm].contiguous().to(DEV)
     agg = ops.pna_aggregate_fwd(m_sorted, g.rowptr, T)

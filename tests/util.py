@@ -113,3 +113,22 @@ class branches_from:
             assert not bad, f"ReLU sign disagreements outside the rounding band: {bad}"
             assert sum(v[0] for v in O.RELU_BAND_VIOLATIONS) <= 8, f"too many ReLU sign disagreements: {O.RELU_BAND_VIOLATIONS}"
         return False
+
+
+def reproducible(fn, tries: int = 4):
+    """Evaluate an fp32 CPU-oracle closure until two consecutive evaluations agree bit for bit, and return the last.
+
+    On the 16-thread host of the GPU box the FIRST fp32 evaluation of the oracle's std aggregate in a process was seen
+    to come out 5e-4 off (about 1 process in 12; the CUDA result and a re-evaluation of the oracle both matched the fp64
+    oracle, and the effect does not reproduce in isolation: scripts/exp/oracle_scatter_stress.py).  That is a host-side
+    torch artefact, not a property of the path under test, so the checker insists on an oracle value that reproduces
+    itself.  ``fn`` returns a tensor or a tuple whose LAST element is the tensor compared."""
+    prev = fn()
+    for _ in range(tries):
+        cur = fn()
+        a = prev[-1] if isinstance(prev, tuple) else prev
+        b = cur[-1] if isinstance(cur, tuple) else cur
+        if torch.equal(a.detach(), b.detach()):
+            return cur
+        prev = cur
+    raise AssertionError("the CPU oracle does not reproduce its own result")
