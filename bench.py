@@ -380,7 +380,13 @@ def run_gpu_arm(args, cfg, target):
         out2, dpred = ops.relhuber_fwd_bwd(pred.detach().contiguous(), tgt)
         pred.backward(dpred)
         trainer.optimizer_step()
+        feed.prepare_next(index_ahead)                     # next batch's CSR / degree buckets queue up behind this step
         return float(out2[0].item())                       # D2H read of the step's loss
+
+    def index_ahead(t):
+        g = graph.graph_index_for(t[1], int(t[0].shape[0]))      # memoised on the edge_index tensor: forward() finds it
+        if cfg["conv"] == "PNA":
+            g.degree_buckets()
 
     for i in range(n_warm):
         e2e_step()

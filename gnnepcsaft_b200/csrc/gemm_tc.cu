@@ -839,7 +839,12 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
         const int work = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
         const int max_cl = kNumSMs / cluster;
-        const int ncl = work < max_cl ? work : max_cl;
+        // Balanced rounds: 400 work items on 74 clusters are 5 full rounds plus one that keeps 30 clusters busy at their
+        // per-SM rate; ceil(400 / 6) = 67 clusters all run 6 rounds at the chip's HBM rate instead (GNNX_GEMM_BALANCE=0: off)
+        static int balance = -1;
+        if (balance < 0) { const char* e = getenv("GNNX_GEMM_BALANCE"); balance = (e && e[0] == '0') ? 0 : 1; }
+        int ncl = work < max_cl ? work : max_cl;
+        if (balance && work > max_cl) ncl = ceil_div(work, ceil_div(work, max_cl));
         static bool attr2 = false;
         if (!attr2) {
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));

@@ -225,14 +225,29 @@ class HostBatchPrefetcher:
     def __iter__(self):
         return self
 
+    def _claim(self):
+        """Make the staged batch usable on the current stream (idempotent)."""
+        dev, ev = self._next
+        if ev is not None:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(ev)
+            for t in dev:
+                if isinstance(t, Tensor):
+                    t.record_stream(cur)
+            self._next = (dev, None)
+        return dev
+
+    def prepare_next(self, fn) -> None:
+        """Queue ``fn(device_tensors)`` for the batch the next ``__next__`` will return -- typically the parameter-free
+        index work of that batch (``graph_index_for(edge_index, N).degree_buckets()``: CSR build, degree buckets and the
+        one max-degree readback).  Called after a step's kernels are queued and BEFORE its result is read back, it keeps
+        the device busy across the host's wait and leaves one host synchronisation per step instead of two."""
+        if self._next is not None:
+            fn(self._claim())
+
     def __next__(self):
         if self._next is None:
             raise StopIteration
-        dev, ev = self._next
-        cur = torch.cuda.current_stream(self.device)
-        cur.wait_event(ev)
-        for t in dev:
-            if isinstance(t, Tensor):
-                t.record_stream(cur)
+        dev = self._claim()
         self._stage()
         return dev
