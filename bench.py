@@ -200,13 +200,13 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name == "gnnx_pna_aggregate_rows_fwd":     # as aggregate_fwd + the x row copied behind the aggregates ([agg | x])
         return 4.0 * E * H + 24.0 * N * H + 8.0 * N, 0.0
     if name == "gnnx_pna_aggregate_rows_bwd":     # as aggregate_bwd + the x block of d[agg | x] moved to node order
-        return 8.0 * E * H + 40.0 * N * H + 4.0 * N, 0.0
+        return 8.0 * E * H + 24.0 * N * H + 4.0 * N, 0.0          # d[agg | x] read (20NH), dx written (4NH); agg is recomputed
     if name == "gnnx_gather_rows":                # rows moved between node order and degree-bucket order
         return 8.0 * a[3] * a[4] + 4.0 * a[3], 0.0
     if name == "gnnx_pna_aggregate_fwd":          # read messages once, write the four aggregates (4EH + 16NH + 4N)
         return 4.0 * E * H + 16.0 * N * H + 4.0 * N, 0.0
-    if name == "gnnx_pna_aggregate_bwd":          # 8EH + 32NH
-        return 8.0 * E * H + 32.0 * N * H, 0.0
+    if name == "gnnx_pna_aggregate_bwd":          # SURVEY 8d counts 8EH + 32NH; the kernel recomputes agg from m: 8EH + 16NH
+        return 8.0 * E * H + 16.0 * N * H, 0.0
     if name == "gnnx_pna_gather_fwd":             # unique node rows [N,2H] read, messages [E,H] written
         return 8.0 * N * H + 4.0 * E * H + 5.0 * E, 0.0
     if name == "gnnx_pna_gather_bwd":             # dh [E,H] read, dpq [N,2H] written

@@ -250,7 +250,8 @@ k_pna_aggregate_fwd(const float* __restrict__ m, const int* __restrict__ rowptr,
     }
 }
 
-__global__ void __launch_bounds__(256)
+constexpr int kAggRegRows = 4;   // messages of one destination row kept in registers by the backward
+__global__ void __launch_bounds__(256, 3)      // 80 registers; 4 blocks per SM spill and are slower (248 vs 230 us)
 k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m, const float* __restrict__ agg,
                     const int* __restrict__ rowptr, int N, int T, int F, float* __restrict__ dm, long long ld_agg,
                     const int* __restrict__ node_pos, float* __restrict__ dx) {
@@ -272,19 +273,61 @@ k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m,
         if (b == e) continue;
         int t = c / F, f = c % F;
         long long base = row * ld_agg + (long long)t * 4 * F + f;
-        F4 mean = f4_lds(agg + base), mn = f4_lds(agg + base + F), mx = f4_lds(agg + base + 2 * F), sd = f4_lds(agg + base + 3 * F);
         F4 gmean = f4_lds(dagg + base), gmn = f4_lds(dagg + base + F), gmx = f4_lds(dagg + base + 2 * F), gsd = f4_lds(dagg + base + 3 * F);
-        // pass 1: tie counts for min / max (PyG CPU semantics: gradient split evenly among ties)
-        F4 nmn = f4_zero(), nmx = f4_zero();
-        for (int k = b; k < e; ++k) {
-            F4 v = f4_ld(m + (long long)k * H + c);
+        // The four aggregates are RECOMPUTED from the messages with the forward kernel's operation sequence (agg_acc in
+        // slot order, the same rounding calls), so they are bit-identical to what the forward stored and [N, 4H] is never
+        // read back.  Rows of up to kAggRegRows messages (every molecular graph) are held in registers: one set of loads,
+        // all in flight together, serves the statistics, the tie counts and the gradient.
+        const int deg = e - b;
+        F4 vr[kAggRegRows];
+        const bool in_regs = deg <= kAggRegRows;
+        if (in_regs) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                nmn.a[j] += (v.a[j] == mn.a[j]) ? 1.f : 0.f;
-                nmx.a[j] += (v.a[j] == mx.a[j]) ? 1.f : 0.f;
+            for (int u = 0; u < kAggRegRows; ++u)
+                if (u < deg) vr[u] = f4_ld(m + (long long)(b + u) * H + c);
+        }
+        F4 s = f4_zero(), s2 = f4_zero(), mn = f4_fill(INFINITY), mx = f4_fill(-INFINITY);
+        if (in_regs) {
+#pragma unroll
+            for (int u = 0; u < kAggRegRows; ++u)
+                if (u < deg) agg_acc(vr[u], s, s2, mn, mx);
+        } else {
+            for (int k = b; k < e; ++k) agg_acc(f4_ld(m + (long long)k * H + c), s, s2, mn, mx);
+        }
+        const float cnt = (float)deg;
+        F4 mean, sd;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float mu = __fdiv_rn(s.a[j], cnt);
+            const float m2 = __fdiv_rn(s2.a[j], cnt);
+            const float var = __fsub_rn(m2, __fmul_rn(mu, mu));
+            const float o = __fsqrt_rn(fmaxf(var, 1e-5f));
+            mean.a[j] = mu;
+            sd.a[j] = (o <= GNNX_STD_MASK) ? 0.f : o;
+        }
+        // tie counts for min / max (PyG CPU semantics: gradient split evenly among ties)
+        F4 nmn = f4_zero(), nmx = f4_zero();
+        if (in_regs) {
+#pragma unroll
+            for (int u = 0; u < kAggRegRows; ++u)
+                if (u < deg) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        nmn.a[j] += (vr[u].a[j] == mn.a[j]) ? 1.f : 0.f;
+                        nmx.a[j] += (vr[u].a[j] == mx.a[j]) ? 1.f : 0.f;
+                    }
+                }
+        } else {
+            for (int k = b; k < e; ++k) {
+                F4 v = f4_ld(m + (long long)k * H + c);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    nmn.a[j] += (v.a[j] == mn.a[j]) ? 1.f : 0.f;
+                    nmx.a[j] += (v.a[j] == mx.a[j]) ? 1.f : 0.f;
+                }
             }
         }
-        float inv_cnt = 1.f / (float)(e - b);
+        float inv_cnt = 1.f / cnt;
         F4 cmean, cmn, cmx, csd;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -293,9 +336,7 @@ k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m,
             cmx.a[j] = gmx.a[j] / nmx.a[j];
             csd.a[j] = sd.a[j] > 0.f ? gsd.a[j] * inv_cnt / sd.a[j] : 0.f;   // d std / d m_e = (m_e - mean) / (cnt * std)
         }
-        // pass 2 (rows are L1/L2-resident from pass 1)
-        for (int k = b; k < e; ++k) {
-            F4 v = f4_ld(m + (long long)k * H + c);
+        auto grad_row = [&](const F4& v, int k) {
             F4 g;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -304,6 +345,13 @@ k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m,
                          csd.a[j] * (x - mean.a[j]);
             }
             stg4(dm + (long long)k * H + c, g.q);
+        };
+        if (in_regs) {
+#pragma unroll
+            for (int u = 0; u < kAggRegRows; ++u)
+                if (u < deg) grad_row(vr[u], b + u);
+        } else {
+            for (int k = b; k < e; ++k) grad_row(f4_ld(m + (long long)k * H + c), k);   // L1 / L2-resident from the passes above
         }
     }
 }

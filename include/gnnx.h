@@ -190,7 +190,9 @@ GNNX_API int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_
 GNNX_API int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t num_nodes, int32_t towers,
                            int32_t f, float* agg, void* stream);
 /* dm[p] from dagg [N,T,4,F]; min/max gradients are split evenly among tied extrema and
- * std has zero gradient where it was clamped to 0 (PyG CPU semantics). */
+ * std has zero gradient where it was clamped to 0 (PyG CPU semantics).
+ * `agg` is accepted for interface stability and NOT read (may be null): the kernel recomputes the four aggregates
+ * from m with the forward's operation sequence (bit-identical), which saves reading [N,4H] back. */
 GNNX_API int gnnx_pna_aggregate_bwd(const float* dagg, const float* m, const float* agg, const int32_t* rowptr,
                            int64_t num_nodes, int32_t towers, int32_t f, float* dm, void* stream);
 
