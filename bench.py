@@ -217,10 +217,10 @@ def _algorithmic_bytes(name, a, N, E, H):
         return 20.0 * N * H, 0.0
     if name in ("gnnx_bn_relu_fwd", "gnnx_bn_relu_bwd"):
         rows, C = a[1] if name.endswith("fwd") else a[3], a[2] if name.endswith("fwd") else a[4]
-        return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
+        return (8.0 if name.endswith("fwd") else 12.0) * rows * C, 0.0      # bwd: dy, x read, dx written (mask re-derived from x)
     if name in ("gnnx_bn_relu_rows_fwd", "gnnx_bn_relu_rows_bwd"):   # bucket-ordered input, node-ordered output: same bytes
         rows, C = (a[3], a[4]) if name.endswith("fwd") else (a[5], a[6])
-        return (8.0 if name.endswith("fwd") else 16.0) * rows * C, 0.0
+        return (8.0 if name.endswith("fwd") else 12.0) * rows * C, 0.0
     if name == "gnnx_gatv2_fwd":                  # xlr [N,2H] read once, x_l[src] per edge slot (+ self loops), out written, alpha written
         n, e, heads, c = a[9], a[10], a[11], a[12]
         h = heads * c

@@ -147,6 +147,12 @@ __global__ void k_bn_eval_stats(const float* __restrict__ rm, const float* __res
     if (c < C) { mean[c] = rm[c]; rstd[c] = rsqrtf(rv[c] + eps); }
 }
 
+// y = (x - mean) * rstd * w + b with a fixed operation sequence: the backward re-evaluates it to recover the ReLU mask
+// (sign of y) bit for bit instead of reading y back.
+__device__ __forceinline__ float bn_affine(float v, float mu, float rs, float w, float b) {
+    return __fmaf_rn(__fmul_rn(__fsub_rn(v, mu), rs), w, b);
+}
+
 __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, const float* __restrict__ weight,
                            const float* __restrict__ bias, const float* __restrict__ mean, const float* __restrict__ rstd,
                            int relu, float* __restrict__ y, const int* __restrict__ row_node) {
@@ -164,7 +170,7 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
         b.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float t = (v.a[j] - mu.a[j]) * rs.a[j] * w.a[j] + b.a[j];
+            float t = bn_affine(v.a[j], mu.a[j], rs.a[j], w.a[j], b.a[j]);
             o.a[j] = relu ? fmaxf(t, 0.f) : t;
         }
         stg4(y + orow * C + c, o.q);
@@ -175,8 +181,10 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
 __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
                  int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
-                 int rows_per_chunk, float* __restrict__ partial, const int* __restrict__ row_node) {
+                 int rows_per_chunk, float* __restrict__ partial, const int* __restrict__ row_node,
+                 const float* __restrict__ weight, const float* __restrict__ bias) {
     pdl_enter();
+    (void)y;                                       // the ReLU mask is re-derived from x (bn_affine): y is not read
     // row_node != null: x is in degree-bucket order (rows = bucket capacity), dy / y in node order
     __shared__ float sh[4][2][256 + 4];
     const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
@@ -185,35 +193,38 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
     F4 s1, s2;
     s1.q = s2.q = make_float4(0.f, 0.f, 0.f, 0.f);
     if (c < C) {
-        F4 mu, rs;
+        F4 mu, rs, wv, bv;
         mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+        wv.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        bv.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
         int r = r0 + ty;
         for (; r + 4 < r1; r += 8) {
-            F4 g[2], xv[2], yv[2];
+            F4 g[2], xv[2];
+            bool pad[2] = {false, false};
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 long long o = (long long)(r + 4 * u) * C + c;
                 xv[u].q = ldg4(x + o);
                 if (row_node) {
                     const int node = row_node[r + 4 * u];
-                    if (node < 0) { g[u].q = make_float4(0.f, 0.f, 0.f, 0.f); yv[u].q = g[u].q; continue; }
+                    if (node < 0) { g[u].q = make_float4(0.f, 0.f, 0.f, 0.f); pad[u] = true; continue; }
                     o = (long long)node * C + c;
                 }
                 g[u].q = ldg4_stream(dy + o);
-                if (relu) yv[u].q = ldg4(y + o);
             }
 #pragma unroll
             for (int u = 0; u < 2; ++u)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    float gg = (relu && !(yv[u].a[j] > 0.f)) ? 0.f : g[u].a[j];
+                    const bool off = pad[u] || (relu && !(bn_affine(xv[u].a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f));
+                    float gg = off ? 0.f : g[u].a[j];
                     s1.a[j] += gg;
                     s2.a[j] = fmaf(gg, (xv[u].a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
                 }
         }
         for (; r < r1; r += 4) {
             long long o = (long long)r * C + c;
-            F4 g, xv, yv;
+            F4 g, xv;
             xv.q = ldg4(x + o);
             if (row_node) {
                 const int node = row_node[r];
@@ -221,10 +232,9 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
                 o = (long long)node * C + c;
             }
             g.q = ldg4_stream(dy + o);
-            if (relu) yv.q = ldg4(y + o);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                float gg = (relu && !(yv.a[j] > 0.f)) ? 0.f : g.a[j];
+                float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f)) ? 0.f : g.a[j];
                 s1.a[j] += gg;
                 s2.a[j] = fmaf(gg, (xv.a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
             }
@@ -266,8 +276,9 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
                                long long rows, int C, const float* __restrict__ weight, const float* __restrict__ mean,
                                const float* __restrict__ rstd, const float* __restrict__ dweight,
                                const float* __restrict__ dbias, int relu, float* __restrict__ dx,
-                               const int* __restrict__ row_node, long long n_valid) {
+                               const int* __restrict__ row_node, long long n_valid, const float* __restrict__ bias) {
     pdl_enter();
+    (void)y;
     const int c4 = C / 4;
     long long total = rows * c4;
     const float inv_n = 1.f / (float)n_valid;
@@ -279,16 +290,16 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
             if (node < 0) { stg4(dx + i * 4, make_float4(0.f, 0.f, 0.f, 0.f)); continue; }   // padding rows carry no gradient
             ni = (long long)node * c4 + (i % c4);
         }
-        F4 g, xv, yv, mu, rs, w, dw, db, o;
+        F4 g, xv, mu, rs, w, bb, dw, db, o;
         g.q = ldg4_stream(dy + ni * 4);
         xv.q = ldg4_stream(x + i * 4);
-        if (relu) yv.q = ldg4_stream(y + ni * 4);
         mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
         w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        bb.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
         dw.q = ldg4(dweight + c); db.q = ldg4(dbias + c);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float gg = (relu && !(yv.a[j] > 0.f)) ? 0.f : g.a[j];
+            float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], w.a[j], bb.a[j]) > 0.f)) ? 0.f : g.a[j];
             float xh = (xv.a[j] - mu.a[j]) * rs.a[j];
             o.a[j] = w.a[j] * rs.a[j] * (gg - db.a[j] * inv_n - xh * dw.a[j] * inv_n);
         }
@@ -468,7 +479,7 @@ int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* row_node,
 }
 
 static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t rows, int64_t n_valid, const int32_t* row_node,
-                       int32_t C, const float* weight, const float* save_mean, const float* save_rstd, int32_t relu, float* dx,
+                       int32_t C, const float* weight, const float* bias, const float* save_mean, const float* save_rstd, int32_t relu, float* dx,
                        float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(C % 4 == 0, "bn_relu_bwd: channels must be a multiple of 4");
     GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_bwd: workspace too small");
@@ -476,23 +487,23 @@ static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t 
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
-    launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node);
+    launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node, weight, bias);
     launch(k_bn_bwd_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, dweight, dbias);
-    launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid);
+    launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid, bias);
     return check_launch("bn_relu_bwd", 3);
 }
 
 int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
-                     const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
+                     const float* bias, const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
                      void* ws, size_t ws_bytes, void* stream) {
-    return bn_bwd_impl(dy, x, y, rows, rows, nullptr, C, weight, save_mean, save_rstd, relu, dx, dweight, dbias, ws, ws_bytes, stream);
+    return bn_bwd_impl(dy, x, y, rows, rows, nullptr, C, weight, bias, save_mean, save_rstd, relu, dx, dweight, dbias, ws, ws_bytes, stream);
 }
 
 int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
-                          int64_t num_nodes, int32_t C, const float* weight, const float* save_mean, const float* save_rstd,
-                          int32_t relu, float* dx, float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
+                          int64_t num_nodes, int32_t C, const float* weight, const float* bias, const float* save_mean,
+                          const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(row_node, "bn_relu_rows_bwd: row_node is required");
-    return bn_bwd_impl(dy, x, y, rows, num_nodes, row_node, C, weight, save_mean, save_rstd, relu, dx, dweight, dbias, ws,
+    return bn_bwd_impl(dy, x, y, rows, num_nodes, row_node, C, weight, bias, save_mean, save_rstd, relu, dx, dweight, dbias, ws,
                        ws_bytes, stream);
 }
 

@@ -55,16 +55,16 @@ class _BatchNormFn(Function):
     def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets=None):
         y, mean, rstd = ops.bn_relu_fwd(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets)
         ctx.relu, ctx.training, ctx.buckets = relu, training, buckets
-        ctx.save_for_backward(x, y, weight, mean, rstd)
+        ctx.save_for_backward(x, weight, bias, mean, rstd)     # the backward re-derives the ReLU mask from x: y is not kept
         return y
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dy):
-        x, y, weight, mean, rstd = ctx.saved_tensors
+        x, weight, bias, mean, rstd = ctx.saved_tensors
         if not ctx.training:
             raise NotImplementedError("gnnx: batch-norm backward is implemented for training mode only")
-        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, y, weight, mean, rstd, ctx.relu, ctx.buckets)
+        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, None, weight, mean, rstd, ctx.relu, ctx.buckets, bias=bias)
         return dx, dw, db, None, None, None, None, None, None, None
 
 

@@ -468,7 +468,9 @@ def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bo
     return y, mean, rstd
 
 
-def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Tensor, relu: bool, buckets=None):
+def bn_relu_bwd(dy: Tensor, x: Tensor, y: Optional[Tensor], weight, mean: Tensor, rstd: Tensor, relu: bool, buckets=None,
+                bias=None):
+    """``bias``: the forward's bias -- the ReLU mask is re-derived from ``x`` (``y`` is not read and may be ``None``)."""
     _chk(dy, torch.float32, "dy")
     rows, C = x.shape
     dx = torch.empty_like(x)
@@ -476,11 +478,11 @@ def bn_relu_bwd(dy: Tensor, x: Tensor, y: Tensor, weight, mean: Tensor, rstd: Te
     db = torch.empty(C, dtype=torch.float32, device=x.device)
     ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
     if buckets is None:
-        lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, C, _p(weight), mean.data_ptr(),
+        lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), _p(y), rows, C, _p(weight), _p(bias), mean.data_ptr(),
                    rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
     else:
-        lib().call("gnnx_bn_relu_rows_bwd", dy.data_ptr(), x.data_ptr(), y.data_ptr(), rows, buckets.row_node.data_ptr(),
-                   buckets.node_pos.numel(), C, _p(weight), mean.data_ptr(), rstd.data_ptr(), int(relu), dx.data_ptr(),
+        lib().call("gnnx_bn_relu_rows_bwd", dy.data_ptr(), x.data_ptr(), _p(y), rows, buckets.row_node.data_ptr(),
+                   buckets.node_pos.numel(), C, _p(weight), _p(bias), mean.data_ptr(), rstd.data_ptr(), int(relu), dx.data_ptr(),
                    dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
     return dx, dw, db
 

@@ -282,9 +282,10 @@ GNNX_API int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t channels, co
                      const float* bias, float* running_mean, float* running_var, int32_t training,
                      float momentum, float eps, int32_t relu, float* y, float* save_mean,
                      float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
-/* dx, dweight, dbias from dy; y is the forward output (used for the ReLU mask), x the input. */
+/* dx, dweight, dbias from dy and the input x.  The ReLU mask is re-derived from x, weight and bias with the forward's
+ * operation sequence (sign of y, bit for bit); y is accepted for interface stability and NOT read (may be null). */
 GNNX_API int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t channels,
-                     const float* weight, const float* save_mean, const float* save_rstd,
+                     const float* weight, const float* bias, const float* save_mean, const float* save_rstd,
                      int32_t relu, float* dx, float* dweight, float* dbias, void* workspace,
                      size_t workspace_bytes, void* stream);
 /* The same batch norm fed by a PNAConv output left in DEGREE-BUCKET order (gnnx_degree_buckets): x / dx are
@@ -295,8 +296,8 @@ GNNX_API int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* 
                           int32_t training, float momentum, float eps, int32_t relu, float* y, float* save_mean,
                           float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
 GNNX_API int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
-                          int64_t num_nodes, int32_t channels, const float* weight, const float* save_mean,
-                          const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
+                          int64_t num_nodes, int32_t channels, const float* weight, const float* bias,
+                          const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
                           void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ graph pooling (K9) */

@@ -57,8 +57,10 @@ def install_op_checks():
         _note("colsum", f"{tuple(x.shape)} ld{x.stride(0)}", float((res.double() - ref).abs().max()), float(x.double().abs().sum(0).max()))
         return res
 
-    def bn_relu_bwd(dy, x, y, weight, mean, rstd, relu):
-        dx, dw, db = b0(dy, x, y, weight, mean, rstd, relu)
+    def bn_relu_bwd(dy, x, y, weight, mean, rstd, relu, buckets=None, bias=None):
+        dx, dw, db = b0(dy, x, y, weight, mean, rstd, relu, buckets, bias=bias)
+        if y is None:
+            y = (x - mean) * rstd * weight + (bias if bias is not None else 0.0)
         g = dy.double() * (y > 0) if relu else dy.double()
         xh = (x.double() - mean.double()) * rstd.double()
         rdb, rdw = g.sum(0), (g * xh).sum(0)
