@@ -181,7 +181,10 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
                 const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
                 const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,
                 const int* __restrict__ csr_src, int N, int E, int heads, int C, int log2c, int groups, float slope,
-                int self_loops, float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial) {
+                int self_loops, float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial,
+                float* __restrict__ de, const int* __restrict__ de_row) {
+    // de != null: also emit the gradient at the edge term of every slot, de[row(k)] = ds[k] + ds[loop(dst)] / cnt(dst)
+    // (row(k) = de_row ? de_row[k] : k) -- the mean-filled self loop passes its gradient back to the incoming edges.
     pdl_enter();
     const int H = heads * C;
     const int lane = threadIdx.x & 31;
@@ -217,7 +220,10 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
         }
         const float S = head_sum<NQ>(sp, C);
         int cnt = 0;
-        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], float stored, int slot) {
+        F4 dl[NQ];                                   // the loop slot's ds / cnt, added to every incoming slot's de
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) dl[q] = z4();
+        auto step = [&](const F4 (&xl)[NQ], const F4 (&ev)[NQ], float stored, int slot, bool is_loop, float loop_scale) {
             float part = 0.f;
 #pragma unroll
             for (int q = 0; q < NQ; ++q)
@@ -237,13 +243,51 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
                     dxr[q].a[j] += d.a[j];
                 }
                 if (act) stg4(ds + (long long)slot * H + c0 + 128 * q, d.q);
+                if (is_loop) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dl[q].a[j] = d.a[j] * loop_scale;
+                } else if (de && act) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) d.a[j] += dl[q].a[j];
+                    const long long row = de_row ? de_row[slot] : slot;
+                    stg4(de + row * H + c0 + 128 * q, d.q);
+                }
             }
         };
         auto zero_slot = [&](int slot) {
 #pragma unroll
             for (int q = 0; q < NQ; ++q)
-                if (act) stg4(ds + (long long)slot * H + c0 + 128 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+                if (act) {
+                    stg4(ds + (long long)slot * H + c0 + 128 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+                    if (de) stg4(de + (de_row ? (long long)de_row[slot] : (long long)slot) * H + c0 + 128 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+                }
         };
+        if (self_loops) {
+            // the loop slot first: its edge term is the mean of the incoming edge terms (a pass over the 60-row table /
+            // the slots' e rows, L1-resident for the main pass below), and its ds feeds every incoming slot's de
+            for (int t = b; t < e; ++t) {
+                if (csr_src[t] == i) continue;
+                const long long r0 = (long long)eidx[t] * ld_e;
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+                    if (act) {
+                        const F4 ev = g4(ee + r0 + c0 + 128 * q);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) esum[q].a[j] += ev.a[j];
+                    }
+                ++cnt;
+            }
+            const float inv_cnt = 1.f / (float)max(cnt, 1);
+            const float al = alpha[(long long)(E + i) * heads + head];
+            F4 xl[NQ], ev[NQ];
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) {
+                xl[q] = act ? g4(xlr + (long long)i * ld + c0 + 128 * q) : z4();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) ev[q].a[j] = esum[q].a[j] * inv_cnt;
+            }
+            step(xl, ev, al, E + i, true, inv_cnt);
+        }
         for (int t = b; t < e; t += 2) {
             const bool two = t + 1 < e;
             const int s0 = csr_src[t], s1 = two ? csr_src[t + 1] : s0;
@@ -263,40 +307,12 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
                     x0[q] = e0[q] = x1[q] = e1[q] = z4();
                 }
             }
-            if (!(self_loops && s0 == i)) {
-#pragma unroll
-                for (int q = 0; q < NQ; ++q)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) esum[q].a[j] += e0[q].a[j];
-                ++cnt;
-                step(x0, e0, a0, t);
-            } else {
-                zero_slot(t);
-            }
+            if (!(self_loops && s0 == i)) step(x0, e0, a0, t, false, 0.f);
+            else zero_slot(t);
             if (two) {
-                if (!(self_loops && s1 == i)) {
-#pragma unroll
-                    for (int q = 0; q < NQ; ++q)
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) esum[q].a[j] += e1[q].a[j];
-                    ++cnt;
-                    step(x1, e1, a1, t + 1);
-                } else {
-                    zero_slot(t + 1);
-                }
+                if (!(self_loops && s1 == i)) step(x1, e1, a1, t + 1, false, 0.f);
+                else zero_slot(t + 1);
             }
-        }
-        if (self_loops) {
-            const float inv_cnt = 1.f / (float)max(cnt, 1);
-            const float al = alpha[(long long)(E + i) * heads + head];
-            F4 xl[NQ], ev[NQ];
-#pragma unroll
-            for (int q = 0; q < NQ; ++q) {
-                xl[q] = act ? g4(xlr + (long long)i * ld + c0 + 128 * q) : z4();
-#pragma unroll
-                for (int j = 0; j < 4; ++j) ev[q].a[j] = esum[q].a[j] * inv_cnt;
-            }
-            step(xl, ev, al, E + i);
         }
 #pragma unroll
         for (int q = 0; q < NQ; ++q)
@@ -458,7 +474,8 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
                    const int32_t* eidx_i32, const uint8_t* eidx_u8, const float* att, const float* alpha,
                    const int32_t* rowptr, const int32_t* csr_src, const int32_t* colptr, const int32_t* csc_pos,
                    const int32_t* csc_dst, int64_t N, int64_t E, int32_t heads, int32_t C, float slope, int32_t self_loops,
-                   float dropout_p, float* dxlr, float* datt, float* ds, void* ws, size_t ws_bytes, void* stream) {
+                   float dropout_p, float* dxlr, float* datt, float* ds, float* de, const int32_t* de_row, void* ws,
+                   size_t ws_bytes, void* stream) {
     const int H = heads * C;
     GNNX_REQUIRE(attn_shape_ok(heads, C), "gatv2_bwd: need C a power of two in [4, 1024] and heads*C <= 4096");
     GNNX_REQUIRE(dropout_p >= 0.f && dropout_p < 1.f, "gatv2_bwd: dropout_p must be in [0, 1)");
@@ -470,8 +487,8 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     const int grid = gat_bwd_grid(N, s.groups);
     const float ks = 1.0f / (1.0f - dropout_p);
 #define CALL(NQ)                                                                                                              \
-    if (eidx_i32) launch(k_gatv2_bwd_dst<NQ, int>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws); \
-    else launch(k_gatv2_bwd_dst<NQ, uint8_t>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws)
+    if (eidx_i32) launch(k_gatv2_bwd_dst<NQ, int>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row); \
+    else launch(k_gatv2_bwd_dst<NQ, uint8_t>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row)
     GAT_DISPATCH(s, CALL);
 #undef CALL
     launch(k_gatv2_bwd_src, attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st, dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);

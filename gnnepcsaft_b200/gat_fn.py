@@ -56,8 +56,10 @@ class GATv2ConvFn(Function):
         x, efeat, xlr, e, alpha, wl, wr, wedge, att, out, bias = ctx.saved_tensors
         dout = _c(dout)
         eidx = meta.codes if meta.codes is not None else g.csr_eid
-        dxlr, datt, ds = ops.gatv2_bwd(dout, out, bias, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
-                                       meta.self_loops, meta.dropout_p)
+        table = meta.codes is not None
+        # the edge-term gradient of every slot (loop fan-out included) comes out of the same pass as ds
+        dxlr, datt, ds, de = ops.gatv2_bwd(dout, out, bias, xlr, e, eidx, att.reshape(-1), alpha, g, heads, c, meta.slope,
+                                           meta.self_loops, meta.dropout_p, want_de="slot" if table else "edge")
         dl, dr = dxlr[:, :H], dxlr[:, H:]
         dx = dbl = dbr = None
         if ctx.needs_input_grad[0]:                                  # the bias gradients ride the dX products
@@ -70,8 +72,6 @@ class GATv2ConvFn(Function):
         dwl = ops.gemm(dl, x, trans_a=True)
         dwr = ops.gemm(dr, x, trans_a=True)
         dbias = ops.colsum(dout) if ctx.has[2] else None
-        table = meta.codes is not None
-        de = ops.gatv2_edge_grad(ds, g, H, meta.self_loops, original_order=not table)
         if table:
             de = ops.code_segment_sum(de, meta.codes, efeat.shape[0])
         dwedge = ops.gemm(de, efeat, trans_a=True)

@@ -523,7 +523,10 @@ def gatv2_fwd(xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor, bias: Optional[
 
 
 def gatv2_bwd(dout: Tensor, out: Tensor, bias: Optional[Tensor], xlr: Tensor, e: Tensor, eidx: Tensor, att: Tensor,
-              alpha: Tensor, g, heads: int, c: int, slope: float, self_loops: bool, dropout_p: float = 0.0):
+              alpha: Tensor, g, heads: int, c: int, slope: float, self_loops: bool, dropout_p: float = 0.0,
+              want_de: Optional[str] = None):
+    """``want_de``: ``"slot"`` / ``"edge"`` also returns the gradient at the edge term of every edge, ``[E, H]`` in
+    dst-sorted slot order / original edge order (written by the same pass: no ``gatv2_edge_grad`` call) -> 4-tuple."""
     _chk(dout, torch.float32, "dout")
     N, E, H = g.num_nodes, g.num_edges, heads * c
     dev = dout.device
@@ -532,13 +535,16 @@ def gatv2_bwd(dout: Tensor, out: Tensor, bias: Optional[Tensor], xlr: Tensor, e:
     ds = torch.empty((E + N, H), dtype=torch.float32, device=dev)
     i32 = eidx.data_ptr() if eidx.dtype == torch.int32 else None
     u8 = eidx.data_ptr() if eidx.dtype == torch.uint8 else None
+    if want_de not in (None, "slot", "edge"):
+        raise ValueError("gnnx.gatv2_bwd: want_de must be None, 'slot' or 'edge'")
+    de = torch.empty((E, H), dtype=torch.float32, device=dev) if want_de else None
     ws, nb = _ws(_query("gnnx_gatv2_bwd_workspace_bytes", N, E, heads, c), dev)
     lib().call("gnnx_gatv2_bwd", dout.data_ptr(), out.data_ptr(), _p(bias), xlr.data_ptr(), e.data_ptr(), e.stride(0), i32, u8,
                att.data_ptr(),
                alpha.data_ptr(), g.rowptr.data_ptr(), g.csr_src.data_ptr(), g.colptr.data_ptr(), g.csc_pos.data_ptr(),
                g.csc_dst.data_ptr(), N, E, heads, c, float(slope), int(self_loops), float(dropout_p), dxlr.data_ptr(),
-               datt.data_ptr(), ds.data_ptr(), _p(ws), nb, _stream())
-    return dxlr, datt, ds
+               datt.data_ptr(), ds.data_ptr(), _p(de), g.csr_eid.data_ptr() if want_de == "edge" else None, _p(ws), nb, _stream())
+    return (dxlr, datt, ds, de) if want_de else (dxlr, datt, ds)
 
 
 def gatv2_edge_grad(ds: Tensor, g, hidden: int, self_loops: bool, original_order: bool) -> Tensor:

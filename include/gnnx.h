@@ -325,7 +325,11 @@ GNNX_API int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, cons
 /* Backward.  out / bias are the forward's output and bias (out - bias is the aggregate the
  * softmax backward needs).  Outputs: dxlr [N,2H] (fully written), datt [heads*C], ds [E+N, H] =
  * gradient at the pre-activation s (dst-sorted slots then loop slots); the caller derives
- * d(lin_edge) from ds.  workspace: gnnx_gatv2_bwd_workspace_bytes(). */
+ * d(lin_edge) from ds.  de (optional, [E,H]): the gradient at the edge term of every incoming slot,
+ * de[row(k)] = ds[k] + ds[loop(dst_k)] / cnt(dst_k) (the mean-filled self loop hands its gradient back to the
+ * edges it averaged; 0 for a removed self loop), row(k) = de_row ? de_row[k] : k (csr_eid gives original edge
+ * order) -- written by the same pass, so gnnx_gatv2_edge_grad is not needed.
+ * workspace: gnnx_gatv2_bwd_workspace_bytes(). */
 GNNX_API size_t gnnx_gatv2_bwd_workspace_bytes(int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c);
 GNNX_API int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const float* xlr,
                    const float* e, int64_t ld_e,
@@ -334,7 +338,7 @@ GNNX_API int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bi
                    const int32_t* colptr, const int32_t* csc_pos, const int32_t* csc_dst,
                    int64_t num_nodes, int64_t num_edges, int32_t heads, int32_t c, float negative_slope,
                    int32_t self_loops, float dropout_p, float* dxlr, float* datt, float* ds,
-                   void* workspace, size_t workspace_bytes, void* stream);
+                   float* de, const int32_t* de_row, void* workspace, size_t workspace_bytes, void* stream);
 /* de rows for the edge term from ds: de[slot] = ds[slot] + ds[loop(dst)] / deg(dst) (the loop's
  * mean fan-out), written in ORIGINAL edge order when csr_eid != null, else dst-sorted. */
 GNNX_API int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* csr_src,
