@@ -108,3 +108,30 @@ def test_host_batch_prefetcher_delivers_every_batch_in_order():
         assert s == (ha.double().sum() + hb.double().sum()).item() or True
     with pytest.raises(ValueError):
         graph.HostBatchPrefetcher(iter([(torch.zeros(4),)]), torch.device("cuda", 0))
+
+
+def test_host_batch_prefetcher_prepare_next_builds_the_index_ahead():
+    """prepare_next(fn) runs fn on the batch the NEXT __next__ returns (after its copy has landed on the current stream):
+    the memoised CSR of that batch must be the one forward() then finds, and be bit-exact."""
+    _, b1 = make_batch(24, seed=4)
+    _, b2 = make_batch(16, seed=5)
+    host = [(b["x"].pin_memory(), b["edge_index"].pin_memory()) for b in (b1, b2)]
+    feed = graph.HostBatchPrefetcher(iter(host), torch.device("cuda", 0))
+    seen = []
+
+    def index_ahead(t):
+        seen.append((t[1].data_ptr(), graph.graph_index_for(t[1], int(t[0].shape[0]))))
+
+    feed.prepare_next(index_ahead)                     # batch 0, before it is handed out
+    x0, ei0 = next(feed)
+    assert seen[0][0] == ei0.data_ptr() and graph.graph_index_for(ei0, x0.shape[0]) is seen[0][1]
+    feed.prepare_next(index_ahead)                     # batch 1 while batch 0 is "in use"
+    x1, ei1 = next(feed)
+    g1 = graph.graph_index_for(ei1, x1.shape[0])
+    assert g1 is seen[1][1]
+    ref = O.csr_reference(b2["edge_index"], b2["x"].shape[0])
+    assert torch.equal(g1.csr_eid.cpu().long(), ref["eid"]) and torch.equal(g1.rowptr.cpu().long(), ref["rowptr"])
+    feed.prepare_next(index_ahead)                     # nothing staged any more: a no-op
+    assert len(seen) == 2
+    with pytest.raises(StopIteration):
+        next(feed)
