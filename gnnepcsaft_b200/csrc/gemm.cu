@@ -24,6 +24,11 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
 int tc_red_grouped_splits(int64_t Mo, int64_t No, int64_t R);
 int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
                         const int* split_table, int S, float* partial, cudaStream_t st);
+bool tc_red_batched_ok(int n, int64_t Mo, int64_t No, int64_t R);
+size_t tc_red_batched_workspace_bytes(int n, int64_t Mo, int64_t No, int64_t R);
+int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const float* const* B, const int64_t* ldb,
+                        float* const* C, const int64_t* ldc, int64_t Mo, int64_t No, int64_t R, void* ws, size_t ws_bytes,
+                        cudaStream_t st);
 int group_reduce_launch(const float* partial, const int* split_table, int S, const float* coef, int J, long long total,
                         float* out, cudaStream_t st);
 }  // namespace gnnx
@@ -104,6 +109,37 @@ int gnnx_gemm_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, 
     GNNX_REQUIRE(bucket_ptr && n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS, "gemm_grouped: 1..%d groups and a bucket_ptr", GNNX_MAX_GROUPS);
     return gemm_dispatch(A, lda, 0, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, colsum_a_out,
                          precision, ws, ws_bytes, stream, bucket_ptr, n_groups);
+}
+
+static bool dw_batched_tc(int32_t n, const float* const* dY, const int64_t* ld_dy, const float* const* X, const int64_t* ld_x,
+                          float* const* dW, const int64_t* ld_dw, int64_t Mo, int64_t No, int64_t R, int32_t precision) {
+    if (precision == GNNX_PREC_FP32 || !tc_red_batched_ok(n, Mo, No, R)) return false;
+    for (int z = 0; z < n; ++z)
+        if (!tc_supported(Mo, No, R, 1, 0, ld_dy[z], ld_x[z], ld_dw[z], dY[z], X[z], dW[z], precision)) return false;
+    return true;
+}
+
+size_t gnnx_gemm_dw_batched_workspace_bytes(int32_t n, int64_t Mo, int64_t No, int64_t R, int32_t precision) {
+    size_t s = gnnx_gemm_workspace_bytes(Mo, No, R, 1, 0, precision);          // the one-by-one path
+    if (precision != GNNX_PREC_FP32 && tc_red_batched_ok(n, Mo, No, R)) {
+        size_t t = tc_red_batched_workspace_bytes(n, Mo, No, R);
+        if (t > s) s = t;
+    }
+    return s;
+}
+
+int gnnx_gemm_dw_batched(int32_t n, const float* const* dY, const int64_t* ld_dy, const float* const* X, const int64_t* ld_x,
+                         float* const* dW, const int64_t* ld_dw, int64_t Mo, int64_t No, int64_t R, int32_t precision,
+                         void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(n >= 1 && dY && X && dW && ld_dy && ld_x && ld_dw, "gemm_dw_batched: null argument");
+    if (dw_batched_tc(n, dY, ld_dy, X, ld_x, dW, ld_dw, Mo, No, R, precision))
+        return gemm_tc_red_batched(n, dY, ld_dy, X, ld_x, dW, ld_dw, Mo, No, R, ws, ws_bytes, as_stream(stream));
+    for (int z = 0; z < n; ++z) {                          // shapes the batched kernel does not take: one product at a time
+        int rc = gnnx_gemm(dY[z], ld_dy[z], 1, X[z], ld_x[z], 0, dW[z], ld_dw[z], Mo, No, R, nullptr, 0, nullptr, 0, nullptr,
+                           nullptr, precision, ws, ws_bytes, stream);
+        if (rc) return rc;
+    }
+    return GNNX_OK;
 }
 
 static bool grouped_dw_tc(int64_t Mo, int64_t No, int64_t R, int64_t lda, int64_t ldb, const void* A, const void* B, int precision) {

@@ -595,10 +595,9 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 }
 
 // ------------------------------------------------------------------ partial[z][Mo,No] = A[rows_z, Mo]^T * B[rows_z, No]
-__global__ void __launch_bounds__(kThreads, 1)
-k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                const __grid_constant__ CUtensorMap tmP, float* __restrict__ partial, int Mo, int No, int R,
-                int rows_per_split, int BM, int BN, const int* __restrict__ split_table) {
+__device__ __forceinline__ void red_body(const CUtensorMap* tmA, const CUtensorMap* tmB, const CUtensorMap* tmP,
+                                         float* __restrict__ partial, int Mo, int No, int R, int rows_per_split, int BM,
+                                         int BN, const int* __restrict__ split_table, const int split) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -608,23 +607,23 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int n_tiles = (No + BN - 1) / BN;
     const int m0 = (blockIdx.x / n_tiles) * BM, n0 = (blockIdx.x % n_tiles) * BN;
     // row range of this split: uniform, or (grouped dW) read from the per-batch split table {begin, end, group}
-    const int r_begin = split_table ? split_table[3 * blockIdx.y] : blockIdx.y * rows_per_split;
-    const int r_end = split_table ? split_table[3 * blockIdx.y + 1] : min(R, r_begin + rows_per_split);
+    const int r_begin = split_table ? split_table[3 * split] : split * rows_per_split;
+    const int r_end = split_table ? split_table[3 * split + 1] : min(R, r_begin + rows_per_split);
     const int RB = (r_end - r_begin + kBK - 1) / kBK;
     const int halves = BM / 128;
 
     if (warp == 0) {
         if (lane == 0) {
-            tma_prefetch_desc(&tmA);
-            tma_prefetch_desc(&tmB);
+            tma_prefetch_desc(tmA);
+            tma_prefetch_desc(tmB);
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t tx = (uint32_t)(BM + BN) * 128u;
             for (int rb = 0; rb < RB; ++rb) {
                 mbar_wait(sm.empty(stage), phase ^ 1);
                 mbar_expect_tx(sm.full(stage), tx);
-                tma_load_3d(sm.a(stage), &tmA, sm.full(stage), 0, r_begin + rb * kBK, m0 / 32);
-                tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, r_begin + rb * kBK, n0 / 32);
+                tma_load_3d(sm.a(stage), tmA, sm.full(stage), 0, r_begin + rb * kBK, m0 / 32);
+                tma_load_3d(sm.b(stage), tmB, sm.full(stage), 0, r_begin + rb * kBK, n0 / 32);
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
@@ -651,7 +650,7 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
     } else {
         const int q = warp & 3;
-        float* out = partial + (long long)blockIdx.y * Mo * No;
+        float* out = partial + (long long)split * Mo * No;
         if (RB > 0) {
             mbar_wait(sm.tmem_full(), 0);
             tc_fence_after();
@@ -659,9 +658,9 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             uint32_t it = 0;
             // tmP views the partials as [splits * Mo, No]; Mo and No are multiples of 32, so a 32x32 staging tile is
             // either wholly inside this split's [Mo, No] block or skipped (row_end / col_end guards).
-            const int prow = blockIdx.y * Mo;
+            const int prow = split * Mo;
             for (int h = 0; h < halves; ++h)
-                epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmP, prow + m0 + h * 128, prow + Mo, n0, ncols, nullptr, No, 0, it);
+                epilogue_tma(sm, tmem_base + h * 256, q, lane, tmP, prow + m0 + h * 128, prow + Mo, n0, ncols, nullptr, No, 0, it);
             if (lane == 0) tma_store_wait_all();
         } else if (!split_table) {                 // empty row range: this split contributes zeros (the grouped reduce skips it)
             for (int h = 0; h < halves; ++h)
@@ -678,6 +677,27 @@ k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
     }
+}
+
+
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmP, float* __restrict__ partial, int Mo, int No, int R,
+                int rows_per_split, int BM, int BN, const int* __restrict__ split_table) {
+    red_body(&tmA, &tmB, &tmP, partial, Mo, No, R, rows_per_split, BM, BN, split_table, (int)blockIdx.y);
+}
+
+// Up to kRedBatch weight gradients of one shape in ONE launch (blockIdx.z = problem): the three post_nn products of a
+// PNAConv layer share the row count, so each gets a third of the CTAs, three times the rows per CTA (the prologue, the
+// un-overlapped 256 KB epilogue and the launch are paid once instead of three times) and a third of the partials.
+constexpr int kRedBatch = 4;
+struct RedBatch { CUtensorMap a[kRedBatch], b[kRedBatch], p[kRedBatch]; };
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_tf32_red_batched(const __grid_constant__ RedBatch bt, float* __restrict__ partial, long long partial_stride, int Mo,
+                        int No, int R, int rows_per_split, int BM, int BN) {
+    const int z = blockIdx.z;
+    red_body(&bt.a[z], &bt.b[z], &bt.p[z], partial + z * partial_stride, Mo, No, R, rows_per_split, BM, BN, nullptr,
+             (int)blockIdx.y);
 }
 
 // ------------------------------------------------------------------ host side
@@ -945,6 +965,51 @@ int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb
     if (make_map_store(&mC, partial, (int64_t)S * Mo, No, No)) return GNNX_ERR_INVALID;
     launch(k_gemm_tf32_red, dim3(p.tiles, S), kThreads, kSmemBytes, st, mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
     return check_launch("gemm_tf32_red(grouped)");
+}
+
+// n weight gradients C_z[Mo,No] = A_z[R,Mo]^T B_z[R,No] of one shape in one launch + one ordered reduce per problem.
+bool tc_red_batched_ok(int n, int64_t Mo, int64_t No, int64_t R) {
+    return n >= 2 && n <= kRedBatch && ceil_div(Mo, Mo > 128 ? 256 : 128) * ceil_div(No, 256) * n <= kNumSMs && R >= 256;
+}
+static RedPlan red_plan_batched(int n, int64_t Mo, int64_t No, int64_t R) {
+    RedPlan p = red_plan(Mo, No, R);
+    int want = kNumSMs / (p.tiles * n);
+    if (want < 1) want = 1;
+    int64_t max_splits = (R + 255) / 256;
+    int splits = (int)(want < max_splits ? want : max_splits);
+    int rps = ceil_div(ceil_div(R, splits), kBK) * kBK;
+    if (rps < kBK) rps = kBK;
+    p.rows_per_split = rps;
+    p.splits = ceil_div(R, rps);
+    return p;
+}
+size_t tc_red_batched_workspace_bytes(int n, int64_t Mo, int64_t No, int64_t R) {
+    return (size_t)n * red_plan_batched(n, Mo, No, R).splits * Mo * No * sizeof(float);
+}
+int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const float* const* B, const int64_t* ldb,
+                        float* const* C, const int64_t* ldc, int64_t Mo, int64_t No, int64_t R, void* ws, size_t ws_bytes,
+                        cudaStream_t st) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_done = true;
+    }
+    const RedPlan p = red_plan_batched(n, Mo, No, R);
+    const long long stride = (long long)p.splits * Mo * No;
+    GNNX_REQUIRE(ws && ws_bytes >= (size_t)n * stride * sizeof(float), "gemm_dw_batched: workspace too small");
+    RedBatch bt;
+    for (int z = 0; z < n; ++z) {
+        if (make_map_mnmajor(&bt.a[z], A[z], R, Mo, lda[z], p.BM / 32)) return GNNX_ERR_INVALID;
+        if (make_map_mnmajor(&bt.b[z], B[z], R, No, ldb[z], p.BN / 32)) return GNNX_ERR_INVALID;
+        if (make_map_store(&bt.p[z], (const float*)ws + z * stride, (int64_t)p.splits * Mo, No, No)) return GNNX_ERR_INVALID;
+    }
+    for (int z = n; z < kRedBatch; ++z) { bt.a[z] = bt.a[0]; bt.b[z] = bt.b[0]; bt.p[z] = bt.p[0]; }
+    launch(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
+           (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
+    int rc = check_launch("gemm_tf32_red(batched)");
+    for (int z = 0; z < n && rc == GNNX_OK; ++z)
+        rc = splitk_reduce_launch((const float*)ws + z * stride, p.splits, (int)Mo, (int)No, C[z], ldc[z], nullptr, 0, nullptr, 0, st);
+    return rc;
 }
 
 }  // namespace gnnx

@@ -236,6 +236,25 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
     return (out, bits) if want_relu_bits else out
 
 
+def gemm_dw_batched(dys, xs, precision: Optional[int] = None):
+    """``[dy.T @ x for dy, x in zip(dys, xs)]`` for products of ONE shape (dy [R, Mo], x [R, No], unit inner stride) in a
+    single launch -- the weight gradients of consecutive Linear layers that see the same number of rows."""
+    import ctypes
+    n = len(dys)
+    R, Mo, No = dys[0].shape[0], dys[0].shape[1], xs[0].shape[1]
+    for dy, x in zip(dys, xs):
+        if dy.shape != (R, Mo) or x.shape != (R, No) or dy.dtype != torch.float32 or x.dtype != torch.float32 or not dy.is_cuda:
+            raise ValueError("gnnx.gemm_dw_batched: all products must share one shape (float32, CUDA)")
+    outs = [torch.empty((Mo, No), dtype=torch.float32, device=dys[0].device) for _ in range(n)]
+    prec = _default_precision if precision is None else precision
+    ws, nb = _ws(_query("gnnx_gemm_dw_batched_workspace_bytes", n, Mo, No, R, prec), dys[0].device)
+    vp, i64 = ctypes.c_void_p * n, ctypes.c_int64 * n
+    lib().call("gnnx_gemm_dw_batched", n, vp(*[t.data_ptr() for t in dys]), i64(*[_ld(t) for t in dys]),
+               vp(*[t.data_ptr() for t in xs]), i64(*[_ld(t) for t in xs]), vp(*[t.data_ptr() for t in outs]),
+               i64(*[No] * n), Mo, No, R, prec, _p(ws), nb, _stream())
+    return outs
+
+
 def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
     if not x.is_cuda or x.dtype != torch.float32:
         raise RuntimeError("gnnx.colsum: needs a CUDA float32 tensor")

@@ -107,15 +107,26 @@ def _wprod(a: Tensor, b: Tensor, **kw) -> Tensor:
     return ops.gemm(a, b, precision=ops.PREC_FP32, **kw)
 
 
-def _chain_bwd(d: Tensor, acts: List[Tensor], masks, layers):
+def _chain_bwd(d: Tensor, acts: List[Tensor], masks, layers, extra=None):
     """Backward of ``_chain_fwd``.  ``acts[i]`` is the input of layer i and ``masks[i]`` the packed mask of the ReLU
     it went through (``None``: no ReLU to undo here); that ReLU's backward is fused into the dX product.
-    Returns (d at acts[0], dW, db)."""
-    dws, dbs = [None] * len(layers), [None] * len(layers)
-    for i in range(len(layers) - 1, -1, -1):
+    Returns (d at acts[0], dW, db).  The weight gradients of the chain -- and of ``extra`` = (dY, X) of a layer above
+    it with the same shapes -- are ONE batched product (``ops.gemm_dw_batched``) once every dY is known; with
+    ``extra`` the result is (d, dW, db, dW_extra)."""
+    n = len(layers)
+    dys, dbs = [None] * n, [None] * n
+    for i in range(n - 1, -1, -1):
         w, _ = layers[i]
-        dws[i] = ops.gemm(d, acts[i], trans_a=True)
+        dys[i] = d
         d, dbs[i] = ops.gemm(d, w, relu_mask=masks[i], want_colsum_a=True)      # db = colsum(d) rides the dX product
+    pairs = [(dys[i], acts[i]) for i in range(n)] + ([extra] if extra is not None else [])
+    same = len({(a.shape, b.shape) for a, b in pairs}) == 1
+    if len(pairs) >= 2 and len(pairs) <= 4 and same:
+        dws = ops.gemm_dw_batched([a for a, _ in pairs], [b for _, b in pairs])
+    else:
+        dws = [ops.gemm(a, b, trans_a=True) for a, b in pairs]
+    if extra is not None:
+        return d, dws[:n], dbs, dws[n]
     return d, dws, dbs
 
 
@@ -254,8 +265,8 @@ class PNAConvFn(Function):
         grads: dict = {}
         dout = _c(dout)
 
-        # lin (fused with the last post Linear when there is one)
-        dwf = ops.gemm(dout, os_[-1], trans_a=True)
+        # lin (fused with the last post Linear when there is one); its weight gradient joins the chain's batched product
+        dwf = None if pk.post else ops.gemm(dout, os_[-1], trans_a=True)
         if pk.post:
             w_last, b_last = pk.post[-1]
             # os_[-1] went through a ReLU; for os_[0] (the combine output) combine_bwd undoes it
@@ -265,7 +276,10 @@ class PNAConvFn(Function):
             d, dbf = ops.gemm(dout, wl, want_colsum_a=True)
             grads[id(wl)], grads[id(bl)] = dwf, dbf
         # post layers 1..post-2 -> gradient at o (the combine output; its own ReLU is undone by combine_bwd)
-        d, dws, dbs = _chain_bwd(d, os_, omasks, pk.post[:-1])
+        if pk.post:
+            d, dws, dbs, dwf = _chain_bwd(d, os_, omasks, pk.post[:-1], extra=(dout, os_[-1]))
+        else:
+            d, dws, dbs = _chain_bwd(d, os_, omasks, pk.post[:-1])
         for l, (dw, db) in enumerate(zip(dws, dbs), start=1):
             for t, blk in enumerate(_diag_blocks(dw, T)):
                 grads[id(post[t][l][0])] = blk

@@ -149,6 +149,16 @@ GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float
               float* C, int64_t ldc, int64_t M, int64_t N, int64_t K, const float* bias, int32_t flags,
               const void* relu_mask, int64_t ld_mask, uint32_t* relu_bits_out, float* colsum_a_out,
               int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
+/* n weight gradients of ONE shape, dW_z[Mo,No] = dY_z[R,Mo]^T X_z[R,No] (the dW = dY^T X of n Linear layers fed by the
+ * same number of rows, e.g. the post_nn chain of a PNAConv layer), in one launch: each product gets 1/n of the SMs
+ * and n times the rows per CTA, so the fixed cost of a launch (prologue, un-overlapped partial-tile epilogue) and the
+ * row-split partials shrink n-fold.  The pointer / stride arrays live in HOST memory (n entries each); results are
+ * deterministic (ordered reduce per product).  Shapes or precisions the batched kernel does not take are served one
+ * product at a time with the same result as gnnx_gemm(trans_a = 1). */
+GNNX_API size_t gnnx_gemm_dw_batched_workspace_bytes(int32_t n, int64_t Mo, int64_t No, int64_t R, int32_t precision);
+GNNX_API int gnnx_gemm_dw_batched(int32_t n, const float* const* dY, const int64_t* ld_dy, const float* const* X,
+                         const int64_t* ld_x, float* const* dW, const int64_t* ld_dw, int64_t Mo, int64_t No,
+                         int64_t R, int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);

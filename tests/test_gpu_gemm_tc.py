@@ -187,3 +187,40 @@ def test_fused_column_sums_of_a(prec, M, K, N, tb):
     o3 = prev.to(DEV).clone()
     ops.gemm(a.to(DEV), b.to(DEV), trans_b=tb, out=o3, accumulate=True, relu_mask=y.to(DEV))
     assert torch.equal(o2, o3)
+
+
+@pytest.mark.parametrize("n,R,Mo,No", [(3, 5000, 256, 256), (2, 70001, 128, 256), (4, 3000, 256, 128), (3, 1000, 96, 200),
+                                       (1, 4096, 256, 256)])
+def test_batched_weight_gradients(n, R, Mo, No):
+    """gnnx_gemm_dw_batched: n products dY_z^T X_z of one shape in one launch (blockIdx.z = product) must each meet the
+    tf32 bound, be bit-identical across reruns and independent of their batch mates; shapes the batched kernel does not
+    take (96 x 200: not multiples of 32; n = 1) are served one by one with exactly gemm(trans_a=True)'s result."""
+    dys = [torch.randn(R, Mo, device=DEV) for _ in range(n)]
+    xs = [torch.randn(R, No, device=DEV) for _ in range(n)]
+    outs = ops.gemm_dw_batched(dys, xs)
+    again = ops.gemm_dw_batched(dys, xs)
+    for z in range(n):
+        _check(outs[z], dys[z].double().cpu().t(), xs[z].double().cpu(), what=f"batched dW {z}")
+        assert torch.equal(outs[z], again[z])
+    if n >= 2:
+        other = ops.gemm_dw_batched(dys[::-1], xs[::-1])[::-1]         # same products at other batch positions
+        for z in range(n):
+            assert torch.equal(outs[z], other[z])
+    if Mo % 32 or No % 32 or n == 1:
+        for z in range(n):
+            assert torch.equal(outs[z], ops.gemm(dys[z], xs[z], trans_a=True))
+    fp32 = ops.gemm_dw_batched(dys, xs, precision=ops.PREC_FP32)
+    for z in range(n):
+        ref = dys[z].double().t() @ xs[z].double()
+        assert float((fp32[z].double() - ref).abs().max()) <= 1e-5 * float(ref.abs().max()) + 1e-4
+
+
+def test_batched_weight_gradients_strided_operands():
+    """Operands that are column slices of wider matrices (row stride != width), as the packed layouts hand them over."""
+    R = 9000
+    big_dy, big_x = torch.randn(R, 640, device=DEV), torch.randn(R, 512, device=DEV)
+    dys = [big_dy[:, 0:256], big_dy[:, 256:512]]
+    xs = [big_x[:, 256:512], big_x[:, 0:256]]
+    outs = ops.gemm_dw_batched(dys, xs)
+    for z in range(2):
+        _check(outs[z], dys[z].double().cpu().t(), xs[z].double().cpu(), what=f"strided batched dW {z}")
