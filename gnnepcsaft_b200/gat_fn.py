@@ -69,8 +69,7 @@ class GATv2ConvFn(Function):
             dbl, dbr = ops.colsum(dl), ops.colsum(dr)
         dbl = dbl if ctx.has[0] else None
         dbr = dbr if ctx.has[1] else None
-        dwl = ops.gemm(dl, x, trans_a=True)
-        dwr = ops.gemm(dr, x, trans_a=True)
+        dwl, dwr = ops.gemm_dw_batched([dl, dr], [x, x])             # two same-shape weight gradients, one launch
         dbias = ops.colsum(dout) if ctx.has[2] else None
         if table:
             de = ops.code_segment_sum(de, meta.codes, efeat.shape[0])
