@@ -66,11 +66,11 @@ class TransformerConvFn(Function):
             _, dbskip = ops.gemm(dout, wskip, out=dx, accumulate=True, want_colsum_a=True)
         else:
             dx, dbqkv, dbskip = None, ops.colsum(dqkv), ops.colsum(dout)
-        dwqkv = ops.gemm(dqkv, x, trans_a=True)                      # [3H, H]
-        dwskip = ops.gemm(dout, x, trans_a=True)
+        # four same-shape weight gradients (q, k, v, skip), one batched launch
+        dwq, dwk, dwv, dwskip = ops.gemm_dw_batched([dqkv[:, :H], dqkv[:, H:2 * H], dqkv[:, 2 * H:], dout], [x, x, x, x])
         if table:
             de = ops.code_segment_sum(de, meta.codes, efeat.shape[0])
         dwedge = ops.gemm(de, efeat, trans_a=True)
         defeat = ops.gemm(de, wedge) if ctx.needs_input_grad[1] else None
-        return (dx, defeat, None, dwqkv[:H], dbqkv[:H], dwqkv[H:2 * H], dbqkv[H:2 * H], dwqkv[2 * H:], dbqkv[2 * H:],
+        return (dx, defeat, None, dwq, dbqkv[:H], dwk, dbqkv[H:2 * H], dwv, dbqkv[2 * H:],
                 dwedge, dwskip, dbskip)
