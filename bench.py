@@ -194,6 +194,9 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name == "gnnx_gemm_grouped":               # degree-grouped product: one weight block per in-degree class
         M, Nn, K, G, flags = a[7], a[8], a[9], a[11], a[13]
         return 4.0 * (M * K + G * Nn * K + M * Nn), 2.0 * M * Nn * K
+    if name == "gnnx_gemm_dw_batched":            # n same-shape weight gradients in one launch: n x (both operands + result)
+        n, Mo, No, R = a[0], a[7], a[8], a[9]
+        return n * 4.0 * (R * (Mo + No) + Mo * No), n * 2.0 * R * Mo * No
     if name == "gnnx_gemm_grouped_dw":            # both operands read once, J weighted sums written
         R, Mo, No, J = a[4], a[5], a[6], a[10]
         return 4.0 * (R * (Mo + No) + J * Mo * No), 2.0 * R * Mo * No
@@ -260,7 +263,7 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
         r = _algorithmic_bytes(name, a, N, E, H)
         if r is None:
             continue
-        if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw"):   # same kernels as gnnx_gemm (k_gemm_tf32_rows2 / _red)
+        if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched"):   # same kernels as gnnx_gemm (k_gemm_tf32_rows2 / _red)
             name = "gnnx_gemm"
         name = name.replace("gnnx_bn_relu_rows_", "gnnx_bn_relu_")   # same kernels, row-mapped
         d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
