@@ -11,7 +11,6 @@ union F4 {
     float a[4];
 };
 
-constexpr int kBnRows = 8;   // block = (32 channels, 8 row lanes)
 
 struct Welford {
     float n, mean, m2;
