@@ -429,7 +429,7 @@ def run_gpu_arm(args, cfg, target):
     line = {
         "metric": "train molecular graphs/sec", "value": value, "unit": "graphs/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "tf32"}[args.precision],
+        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32"}[args.precision],
         "data": "synthetic",
         "config": {"workload": WORKLOAD_NAMES[args.workload], "graphs_per_gpu": G, "global_batch": world * G,
                    "nodes_per_batch": N, "edges_per_batch": E, "parallelism": f"dp{world}",
@@ -565,7 +565,7 @@ def run_infer_arm(args, cfg):
         line = {
             "metric": "infer molecular graphs/sec", "value": value, "unit": "graphs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "tf32"}[args.precision], "data": "synthetic",
+            "dtype": {"fp32": "f32", "tf32": "tf32"}[args.precision], "data": "synthetic",
             "config": {"workload": WORKLOAD_NAMES["cfg5"], "graphs_per_step_per_gpu": per_step, "nodes_per_batch": N,
                        "edges_per_batch": E, "parallelism": f"shard{world}", "l2": "inputs per step (GBs of activations) far exceed the 126 MB L2"},
             "clocks": clocks.summary(),
@@ -586,7 +586,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "bf16"])
+    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

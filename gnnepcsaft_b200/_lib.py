@@ -48,6 +48,28 @@ class GnnxError(RuntimeError):
     pass
 
 
+ABI_VERSION = 2
+
+
+def _header_abi_version(path: Path = HEADER) -> int:
+    m = re.search(r"#define\s+GNNX_ABI_VERSION\s+(\d+)", path.read_text())
+    return int(m.group(1)) if m else -1
+
+
+def _stale(dll) -> str:
+    """'' when the loaded binary was built from the sources on disk, else why not.  All pointers cross the boundary as
+    c_void_p, so a stale .so with the same symbol names but another argument layout would corrupt device memory
+    instead of failing: the build digest (header + every csrc file + flags) is stamped into the library and compared."""
+    from . import build as _b
+    try:
+        fn = dll.gnnx_build_digest
+    except AttributeError:
+        return "it predates gnnx_build_digest()"
+    fn.restype, fn.argtypes = ctypes.c_char_p, []
+    have, want = (fn() or b"").decode(), _b.source_digest()
+    return "" if have == want else f"its build digest {have[:12]} differs from the sources' {want[:12]}"
+
+
 class _Lib:
     def __init__(self):
         if not LIB_PATH.exists():
@@ -55,13 +77,31 @@ class _Lib:
                 f"{LIB_PATH} is missing: build it with `python -m gnnepcsaft_b200.build` "
                 "(there is no CPU or PyTorch fallback for the gnnx kernels)")
         self._dll = ctypes.CDLL(str(LIB_PATH))
+        why = _stale(self._dll)
+        if why:
+            # rebuild in place once (nvcc is part of the image); a library that still does not match is refused
+            from . import build as _b
+            try:
+                _b.build(force=True)
+            except Exception as e:  # noqa: BLE001
+                raise RuntimeError(f"{LIB_PATH.name} is stale ({why}) and could not be rebuilt: {e}") from e
+            # dlopen caches by path: load the fresh file through a unique name so the old mapping is not reused
+            import shutil
+            import tempfile
+            tmp = Path(tempfile.mkdtemp(prefix="gnnx_")) / LIB_PATH.name
+            shutil.copy2(LIB_PATH, tmp)
+            self._dll = ctypes.CDLL(str(tmp))
+            why = _stale(self._dll)
+            if why:
+                raise RuntimeError(f"{LIB_PATH.name} is stale after a rebuild ({why}); refusing to call it")
         self.protos = parse_header()
         for name, (restype, argtypes) in self.protos.items():
             fn = getattr(self._dll, name)          # AttributeError if the .so lacks a declared symbol
             fn.restype, fn.argtypes = restype, argtypes
         abi = self._dll.gnnx_abi_version()
-        if abi != 1:
-            raise RuntimeError(f"libgnnx_sm100.so ABI {abi} does not match the Python layer (1)")
+        if abi != ABI_VERSION or _header_abi_version() != ABI_VERSION:
+            raise RuntimeError(f"libgnnx_sm100.so ABI {abi} / header ABI {_header_abi_version()} do not match the "
+                               f"Python layer ({ABI_VERSION})")
 
     def last_error(self) -> str:
         msg = self._dll.gnnx_last_error()
@@ -116,6 +156,10 @@ class _Lib:
     def launch_count(self) -> int:
         """Kernels launched by libgnnx so far in this process."""
         return int(self._dll.gnnx_launch_count())
+
+    def tc_launch_count(self) -> int:
+        """Of those, tcgen05 tensor-core kernels (k_gemm_tf32_rows2 / k_gemm_tf32_red*)."""
+        return int(self._dll.gnnx_tc_launch_count())
 
     def query(self, name: str, *args) -> int:
         """Call a ``size_t``-returning ``*_workspace_bytes`` entry point."""

@@ -49,11 +49,16 @@ def sources():
     return sorted(CSRC.glob("*.cu"))
 
 
+def source_digest() -> str:
+    """Digest of everything the library is compiled from (header, sources, flags); stamped into the .so
+    (``gnnx_build_digest()``) and compared by the loader (``_lib.py``)."""
+    return _digest(sources() + sorted(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "gnnx.h"])
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     srcs = sources()
-    deps = srcs + sorted(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "gnnx.h"]
     stamp = BUILD / "stamp"
-    digest = _digest(deps)
+    digest = source_digest()
     if not force and LIB.exists() and stamp.exists() and stamp.read_text() == digest:
         return LIB
     BUILD.mkdir(exist_ok=True)
@@ -61,7 +66,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     def compile_one(src: Path):
         obj = BUILD / (src.stem + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, f'-DGNNX_BUILD_DIGEST="{digest}"', "-c", str(src), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         (BUILD / (src.stem + ".ptxas.log")).write_text(r.stderr)
         if r.returncode != 0:

@@ -61,7 +61,7 @@ __device__ __forceinline__ bool attn_dropped(float stored_alpha) { return (__flo
 // (no index division in the row loop), so the number of warps must be a multiple of `groups`.
 static inline int attn_row_grid(long long N, int groups, int blocks_per_sm) {
     long long blocks = (N * groups + 7) / 8;
-    long long cap = (long long)kNumSMs * blocks_per_sm;
+    long long cap = (long long)num_sms() * blocks_per_sm;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return (int)((blocks + groups - 1) / groups * groups);
@@ -71,7 +71,7 @@ static inline int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; 
 // grid for a warp-per-work-item grid-stride kernel with 8 warps per block
 static inline int attn_grid(long long work) {
     long long blocks = (work + 7) / 8;
-    long long cap = (long long)kNumSMs * 16;
+    long long cap = (long long)num_sms() * 16;
     return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 

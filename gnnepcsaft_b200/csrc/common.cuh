@@ -11,8 +11,10 @@ namespace gnnx {
 // Thread-local last-error message, read through gnnx_last_error().
 int set_error(int code, const char* fmt, ...);
 
-// Number of kernels this library has launched (read through gnnx_launch_count()).
+// Number of kernels this library has launched (read through gnnx_launch_count()), and how many of them were
+// tcgen05 tensor-core kernels (gnnx_tc_launch_count(): lets a test tell the tensor path from the fp32 fallback).
 void count_launches(int n);
+void count_tc_launches(int n);
 
 inline int check_launch(const char* what, int kernels = 1) {
     count_launches(kernels);
@@ -73,8 +75,9 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-// 148 SMs on B200; grids of grid-stride kernels are sized in multiples of this.
-constexpr int kNumSMs = 148;
+// SM count of the current device (148 on B200), queried once per device; grids of grid-stride kernels are sized in
+// multiples of it.
+int num_sms();
 
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void stg4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }

@@ -17,7 +17,19 @@ namespace gnnx {
 
 static thread_local char g_err[512] = "";
 static unsigned long long g_launches = 0;
+static unsigned long long g_tc_launches = 0;
 void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+void count_tc_launches(int n) { __atomic_fetch_add(&g_tc_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+int num_sms() {
+    static int cached[64];                                // 0 = not queried yet; benign race (every thread stores the same value)
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return 148; }
+    int v = __atomic_load_n(&cached[dev & 63], __ATOMIC_RELAXED);
+    if (v > 0) return v;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) { cudaGetLastError(); return 148; }
+    __atomic_store_n(&cached[dev & 63], v, __ATOMIC_RELAXED);
+    return v;
+}
 // ---- per-kernel device timeline (diagnostic; single-threaded use)
 struct TraceRec { const void* func; cudaEvent_t e0, e1; };
 static bool g_trace = false;
@@ -247,14 +259,14 @@ static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t
     GNNX_CUDA(cudaMemsetAsync(fill_dst, 0, sizeof(int) * (size_t)n1, st));
     GNNX_CUDA(cudaMemsetAsync(fill_src, 0, sizeof(int) * (size_t)n1, st));
     GNNX_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
-    int eb = E > 0 ? min(ceil_div(E, 256), kNumSMs * 16) : 0;
+    int eb = E > 0 ? min(ceil_div(E, 256), num_sms() * 16) : 0;
     if (E > 0) launch(k_hist<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, err_flag);
     launch(k_scan_tiles, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
     launch(k_scan_sums, 2, kScanThreads, 0, st, sums, ntiles);
     launch(k_scan_add, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
     if (E > 0) {
         launch(k_place<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, fill_dst, fill_src, tmp_dst, tmp_src);
-        int nb = min(ceil_div(N, 128), kNumSMs * 16);
+        int nb = min(ceil_div(N, 128), num_sms() * 16);
         launch(k_sort_rows_dst<IdxT>, nb, 128, 0, st, src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
         launch(k_sort_rows_src<IdxT>, nb, 128, 0, st, dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
     }
@@ -338,6 +350,11 @@ extern "C" {
 int gnnx_abi_version(void) { return GNNX_ABI_VERSION; }
 const char* gnnx_last_error(void) { return gnnx::g_err; }
 int64_t gnnx_launch_count(void) { return (int64_t)__atomic_load_n(&gnnx::g_launches, __ATOMIC_RELAXED); }
+int64_t gnnx_tc_launch_count(void) { return (int64_t)__atomic_load_n(&gnnx::g_tc_launches, __ATOMIC_RELAXED); }
+#ifndef GNNX_BUILD_DIGEST
+#define GNNX_BUILD_DIGEST "unstamped"
+#endif
+const char* gnnx_build_digest(void) { return GNNX_BUILD_DIGEST; }
 
 size_t gnnx_csr_workspace_bytes(int64_t N, int64_t E) {
     size_t n1 = (size_t)N + 1, e = (size_t)(E > 0 ? E : 1);
@@ -364,7 +381,7 @@ int gnnx_degree_hist(const int32_t* rowptr, int64_t N, int64_t* hist, int32_t nb
                      void* stream) {
     GNNX_REQUIRE(nbins >= 1 && nbins <= 4096, "degree_hist: nbins must be in [1,4096]");
     if (N == 0) return GNNX_OK;
-    int nb = min(ceil_div(N, 256), kNumSMs * 4);
+    int nb = min(ceil_div(N, 256), num_sms() * 4);
     launch(k_degree_hist, nb, 256, sizeof(int) * (nbins + 1), as_stream(stream), 
         rowptr, (int)N, (unsigned long long*)hist, nbins, max_degree);
     return check_launch("degree_hist");
@@ -372,21 +389,21 @@ int gnnx_degree_hist(const int32_t* rowptr, int64_t N, int64_t* hist, int32_t nb
 
 int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream) {
     GNNX_REQUIRE(N >= 0 && G >= 0, "graph_ptr: negative size");
-    int nb = min(ceil_div(N + 1, 256), kNumSMs * 8);
+    int nb = min(ceil_div(N + 1, 256), num_sms() * 8);
     launch(k_graph_ptr, nb, 256, 0, as_stream(stream), batch, (int)N, (int)G, graph_ptr);
     return check_launch("graph_ptr_from_batch");
 }
 
 int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream) {
     if (count == 0) return GNNX_OK;
-    int nb = min(ceil_div(count, 256), kNumSMs * 16);
+    int nb = min(ceil_div(count, 256), num_sms() * 16);
     launch(k_narrow, nb, 256, 0, as_stream(stream), in, count, out);
     return check_launch("narrow_i64_u8");
 }
 
 int gnnx_edge_codes(const uint8_t* ea, const int32_t* csr_eid, int64_t E, uint8_t* codes, void* stream) {
     if (E == 0) return GNNX_OK;
-    int nb = min(ceil_div(E, 256), kNumSMs * 16);
+    int nb = min(ceil_div(E, 256), num_sms() * 16);
     launch(k_edge_codes, nb, 256, 0, as_stream(stream), ea, csr_eid, (int)E, codes);
     return check_launch("edge_codes");
 }
@@ -396,7 +413,7 @@ int gnnx_collate_packed(const uint8_t* sx, const int16_t* ssrc, const int16_t* s
                         const int64_t* noff, const int64_t* eoff, uint8_t* ox, int32_t* osrc, int32_t* odst,
                         uint8_t* oea, int32_t* obatch, void* stream) {
     if (G == 0) return GNNX_OK;
-    int nb = min(ceil_div(G, 8), kNumSMs * 8);
+    int nb = min(ceil_div(G, 8), num_sms() * 8);
     launch(k_collate_packed, nb, 256, 0, as_stream(stream), sx, ssrc, sdst, sea, snp, sep, gids, (int)G, noff, eoff,
                                                         ox, osrc, odst, oea, obatch);
     return check_launch("collate_packed");

@@ -235,7 +235,7 @@ int group_reduce_launch(const float* partial, const int* split_table, int S, con
                         float* out, cudaStream_t st) {
     const long long total4 = total / 4;
     long long blocks = (total4 + 255) / 256;
-    if (blocks > (long long)kNumSMs * 8) blocks = (long long)kNumSMs * 8;
+    if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
     launch(k_group_reduce, (int)blocks, 256, 0, st, partial, split_table, S, coef, J, total4, out);
     return check_launch("group_reduce");
 }
@@ -286,7 +286,7 @@ int gnnx_pna_degree_weights(const float* wz, const float* wx, int32_t h_out, int
     GNNX_REQUIRE(n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS, "pna_degree_weights: 1..%d groups", GNNX_MAX_GROUPS);
     const long long total = (long long)n_groups * h_out * ((k_agg + h_in) / 4);
     long long blocks = (total + 255) / 256;
-    if (blocks > (long long)kNumSMs * 8) blocks = (long long)kNumSMs * 8;
+    if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
     launch(k_pna_degree_weights, (int)(blocks > 0 ? blocks : 1), 256, 0, as_stream(stream), wz, wx, h_out, k_agg, h_in, avg_deg_log, n_groups, weff, coef);
     return check_launch("pna_degree_weights");
 }
@@ -298,7 +298,7 @@ int gnnx_gather_rows(const float* src, int64_t ld_src, const int32_t* idx, int64
     if (rows == 0 || cols == 0) return GNNX_OK;
     const long long nwork = rows * ((cols + 127) / 128);
     long long blocks = (nwork + 7) / 8;
-    if (blocks > (long long)kNumSMs * 32) blocks = (long long)kNumSMs * 32;
+    if (blocks > (long long)num_sms() * 32) blocks = (long long)num_sms() * 32;
     launch(k_gather_rows, (int)blocks, 256, 0, as_stream(stream), src, ld_src, idx, (int)rows, cols, out, ld_out, relu_bits_out);
     return check_launch("gather_rows");
 }

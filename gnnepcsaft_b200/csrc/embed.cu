@@ -87,7 +87,7 @@ __global__ void k_reduce_partials(const float* __restrict__ partial, int nchunks
 
 static int embed_chunks(int64_t rows, int32_t H) {
     int slabs = ceil_div(H, kEmbSlab);
-    int target = max(1, (kNumSMs * 6) / slabs);
+    int target = max(1, (num_sms() * 6) / slabs);
     int by_rows = max(1, (int)((rows + 255) / 256));    // at least ~256 rows per chunk
     return min(target, by_rows);
 }
@@ -103,7 +103,7 @@ int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
     GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_fwd: num_features must be in [1,32]");
     GNNX_REQUIRE(H % 4 == 0, "embed_sum_fwd: hidden must be a multiple of 4");
     if (rows == 0) return GNNX_OK;
-    int nb = min(ceil_div(rows, 8), kNumSMs * 8);
+    int nb = min(ceil_div(rows, 8), num_sms() * 8);
     launch(k_embed_fwd, nb, 256, 0, as_stream(stream), idx, (int)rows, K, offsets, table, H, out);
     return check_launch("embed_sum_fwd");
 }
@@ -127,7 +127,7 @@ int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
         GNNX_CUDA(cudaFuncSetAttribute(k_embed_bwd_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     launch(k_embed_bwd_partial, dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st, 
         idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws);
-    launch(k_reduce_partials, min(ceil_div(count, 256), kNumSMs * 8), 256, 0, st, (const float*)ws, nchunks, count, dtable);
+    launch(k_reduce_partials, min(ceil_div(count, 256), num_sms() * 8), 256, 0, st, (const float*)ws, nchunks, count, dtable);
     return check_launch("embed_sum_bwd", 2);
 }
 

@@ -501,7 +501,7 @@ int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* 
     GNNX_REQUIRE(H % 4 == 0, "gatv2_edge_grad: hidden must be a multiple of 4");
     if (N == 0 || E == 0) return GNNX_OK;
     long long nwork = (long long)N * ((H + 127) / 128);
-    long long blocks = (nwork + 7) / 8, cap = (long long)kNumSMs * 32;
+    long long blocks = (nwork + 7) / 8, cap = (long long)num_sms() * 32;
     launch(k_gatv2_edge_grad, (int)(blocks < cap ? blocks : cap), 256, 0, as_stream(stream), ds, rowptr, csr_src, csr_eid, (int)N, (int)E, H, self_loops, de);
     return check_launch("gatv2_edge_grad");
 }

@@ -1,6 +1,6 @@
 // gnnx_gemm: precision dispatch for the dense transforms (Linear layers of PNAConv / GATv2Conv / head).
 //   GNNX_PREC_FP32 -> CUDA-core fp32 kernel (gemm_simt.cu), the rel-1e-5 parity tier.
-//   GNNX_PREC_TF32 / GNNX_PREC_BF16 -> tcgen05 + TMEM kernels (gemm_tc.cu); shapes the tensor-core
+//   GNNX_PREC_TF32 -> tcgen05 + TMEM kernels (gemm_tc.cu); shapes the tensor-core
 //   kernel does not cover (tiny or unaligned: the 60-row bond tables, the num_para-wide head output)
 //   run on the fp32 kernel, which is at least as accurate.
 #include <stdlib.h>
@@ -41,7 +41,7 @@ size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, in
     size_t s = simt_workspace_bytes(M, N, K);
     if (!ta) {                                             // room for colsum_a_out: per-CTA partials or the two-pass kernel's
         size_t c = gnnx_colsum_workspace_bytes(M, K);
-        size_t f = (size_t)kNumSMs * K * sizeof(float);
+        size_t f = (size_t)num_sms() * K * sizeof(float);
         if (f > c) c = f;
         if (c > s) s = c;
     }
@@ -58,7 +58,8 @@ static int gemm_dispatch(const float* A, int64_t lda, int32_t ta, const float* B
               const int32_t* bucket_ptr, int32_t n_groups) {
     const float* relu_mask = static_cast<const float*>(relu_mask_v);      // uint32 words under GNNX_GEMM_MASK_BITS
     GNNX_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative dimension");
-    GNNX_REQUIRE(precision >= GNNX_PREC_FP32 && precision <= GNNX_PREC_BF16, "gemm: unknown precision %d", precision);
+    if (precision == GNNX_PREC_BF16) return set_error(GNNX_ERR_UNSUPPORTED, "gemm: no bf16 kernels are built (use GNNX_PREC_TF32)");
+    GNNX_REQUIRE(precision == GNNX_PREC_FP32 || precision == GNNX_PREC_TF32, "gemm: unknown precision %d", precision);
     cudaStream_t st = as_stream(stream);
     if (M == 0 || N == 0) {                                // empty result; the column sum of a zero-row A is zero
         if (colsum_a_out && K > 0) GNNX_CUDA(cudaMemsetAsync(colsum_a_out, 0, (size_t)K * sizeof(float), st));
@@ -73,17 +74,15 @@ static int gemm_dispatch(const float* A, int64_t lda, int32_t ta, const float* B
     GNNX_REQUIRE(!(relu_bits_out && (flags & GNNX_GEMM_ACCUMULATE)), "gemm: relu_bits_out is not available with ACCUMULATE");
     const bool mask_ok = !relu_mask || bits || (((uintptr_t)relu_mask & 15) == 0 && (ld_mask & 3) == 0);
     GNNX_REQUIRE(!(colsum_a_out && ta), "gemm: colsum_a_out needs trans_a = 0");
-    static int use_v1 = -1;
-    if (use_v1 < 0) { const char* e = getenv("GNNX_GEMM_V1"); use_v1 = (e && e[0] == '1') ? 1 : 0; }
     // tiny products (60-row bond tables, weight-space 256^3) are launch-latency-bound: one CTA of the tensor-core
     // kernel would walk them alone, the 32x32-tile fp32 kernel spreads them over the SMs (and is exact)
     const bool tiny = (double)M * (double)N * (double)K < 33554432.0;
     // grouped tensor-core products: the row blocks of a 2-CTA cluster share one weight block (256-row buckets), and an
     // MN-major weight stack [G*K, N] must not let a k-block straddle two groups
-    const bool group_ok = !bucket_ptr || (!use_v1 && (tb || K % 32 == 0));
+    const bool group_ok = !bucket_ptr || (tb || K % 32 == 0);
     const bool tc = precision != GNNX_PREC_FP32 && !tiny && mask_ok && group_ok &&
                     tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
-    const bool fuse_colsum = colsum_a_out && tc && !use_v1 && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
+    const bool fuse_colsum = colsum_a_out && tc && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
     if (colsum_a_out && !fuse_colsum) {                    // separate two-pass kernel (same result, one more read of A)
         int rc = gnnx_colsum(A, lda, M, K, colsum_a_out, ws, ws_bytes, stream);
         if (rc) return rc;
@@ -147,7 +146,7 @@ static bool grouped_dw_tc(int64_t Mo, int64_t No, int64_t R, int64_t lda, int64_
 }
 
 int32_t gnnx_gemm_grouped_dw_splits(int64_t Mo, int64_t No, int64_t R, int32_t n_groups, int32_t precision) {
-    int s = precision != GNNX_PREC_FP32 ? tc_red_grouped_splits(Mo, No, R) : 2 * kNumSMs / (ceil_div(Mo, 128) * ceil_div(No, 128));
+    int s = precision != GNNX_PREC_FP32 ? tc_red_grouped_splits(Mo, No, R) : 2 * num_sms() / (ceil_div(Mo, 128) * ceil_div(No, 128));
     if (s < n_groups) s = n_groups;                       // every non-empty group needs a split of its own
     if (s < 1) s = 1;
     return s;

@@ -205,7 +205,7 @@ k_gemm_f32_small(const float* __restrict__ A, long long lda, const float* __rest
     }
 }
 static bool simt_small(int64_t M, int64_t N, int64_t K) {
-    return K <= 1024 && (long long)ceil_div(M, BM) * ceil_div(N, BN) < kNumSMs && ceil_div(M, SB) <= 65535;
+    return K <= 1024 && (long long)ceil_div(M, BM) * ceil_div(N, BN) < num_sms() && ceil_div(M, SB) <= 65535;
 }
 
 __global__ void k_splitk_reduce(const float* __restrict__ partial, int splits, int M, int N, float* __restrict__ C,
@@ -238,7 +238,7 @@ int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* 
                          int flags, const float* mask, long long ldm, cudaStream_t st) {
     long long total = (long long)M * N;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     launch(k_splitk_reduce, blocks, 256, 0, st, partial, splits, M, N, C, ldc, bias, flags, mask, ldm);
     return check_launch("splitk_reduce");
 }
@@ -246,8 +246,8 @@ int splitk_reduce_launch(const float* partial, int splits, int M, int N, float* 
 int simt_splits(int64_t M, int64_t N, int64_t K) {
     if (simt_small(M, N, K)) return 1;
     long long tiles = (long long)ceil_div(M, BM) * ceil_div(N, BN);
-    if (tiles >= kNumSMs || K < 128) return 1;
-    long long want = (2ll * kNumSMs + tiles - 1) / tiles;
+    if (tiles >= num_sms() || K < 128) return 1;
+    long long want = (2ll * num_sms() + tiles - 1) / tiles;
     long long maxs = K >= 1024 ? K / 256 : K / 32;       // small weight-space products are latency-bound: split deeper
     long long s = want < maxs ? want : maxs;
     if (s > 128) s = 128;
@@ -275,7 +275,7 @@ __global__ void k_pack_relu_bits(const float* __restrict__ C, long long ldc, int
 int pack_relu_bits_launch(const float* C, long long ldc, int M, int N, uint32_t* bits, cudaStream_t st) {
     long long total = (long long)M * ((N + 31) / 32);
     int blocks = (int)((total + 255) / 256);
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     launch(k_pack_relu_bits, blocks, 256, 0, st, C, ldc, M, N, bits);
     return check_launch("pack_relu_bits");
 }
@@ -318,7 +318,7 @@ int gemm_simt(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, 
     else LAUNCH(false, false);
 #undef LAUNCH
     if (partial)
-        launch(k_splitk_reduce, min(ceil_div(M * N, 256), kNumSMs * 8), 256, 0, st, partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
+        launch(k_splitk_reduce, min(ceil_div(M * N, 256), num_sms() * 8), 256, 0, st, partial, splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm);
     int rc = check_launch("gemm_simt", partial ? 2 : 1);
     if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
     return rc;
@@ -400,7 +400,7 @@ int colsum_final_launch(const float* partial, int nchunks, int cols, float* out,
 }
 int colsum_chunks(int64_t rows, int64_t cols) {
     int slabs = ceil_div(cols, 256);
-    int target = max(1, (kNumSMs * 4) / slabs);
+    int target = max(1, (num_sms() * 4) / slabs);
     int by_rows = max(1, (int)((rows + 63) / 64));
     return min(target, by_rows);
 }

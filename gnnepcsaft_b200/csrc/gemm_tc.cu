@@ -1,14 +1,13 @@
 // tcgen05 + TMEM + TMA GEMMs (kind::tf32, fp32 in HBM, fp32 accumulate) for the dense transforms of the
 // hot path: the Linear layers inside PNAConv / GATv2Conv / the MLP head and their dX / dW products.
 //
-// Two kernels, both warp-specialised (warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
+// Two kernel families, both warp-specialised (warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
 // epilogue, one per TMEM lane quadrant), fed by 128-byte-swizzled TMA boxes straight from the fp32
-// tensors (no conversion pass: the tensor map's TFLOAT32 type rounds on load) through a 3-stage mbarrier ring:
+// tensors (no conversion pass: the tensor map's TFLOAT32 type rounds on load) through an mbarrier ring:
 //
-//   k_gemm_tf32_rows   C[M,N] = A[M,K] * op(B)      A K-major.  op(B) = B^T with B [N,K] (Linear forward,
-//                      K-major) or B [K,N] (dX = dY W, MN-major B descriptor).  One CTA owns 256 rows
-//                      (two 128x256 accumulators = all 512 TMEM columns) so every B stage is used twice and
-//                      A is read exactly once; persistent over row blocks, N tiles innermost (A stays in L2).
+//   k_gemm_tf32_rows2  C[M,N] = A[M,K] * op(B)      A K-major.  op(B) = B^T with B [N,K] (Linear forward,
+//                      K-major) or B [K,N] (dX = dY W, MN-major B descriptor).  One CTA owns a 128-row tile and ONE
+//                      128 x BN accumulator, two accumulators ping-pong in TMEM; 2-CTA clusters multicast the weights.
 //   k_gemm_tf32_red    C[Mo,No] = A[R,Mo]^T * B[R,No]  (dW = dY^T X): both operands MN-major, the reduction
 //                      runs over the R rows; grid = output tiles x row splits, partials reduced by a
 //                      deterministic second pass (no atomics).
@@ -17,8 +16,12 @@
 // HBM/L2-bound, not tensor-bound: see DESIGN.md for the roofline of each.
 #include <cudaTypedefs.h>
 
+#include <string.h>
+
+#include <atomic>
 #include <map>
 #include <mutex>
+#include <unordered_map>
 #include <utility>
 
 #include "common.cuh"
@@ -91,23 +94,6 @@ __device__ __forceinline__ void epilogue_acc(const SM& sm, uint32_t tmem_acc, in
     float* st = sm.epi(q);
     const int cc = (lane & 7) * 4;
     const bool acc = (flags & GNNX_GEMM_ACCUMULATE) != 0;
-    const int dbg = (flags >> 8) & 3;            // GNNX_EPI_DEBUG experiments (wrong results for dbg >= 2)
-    if (dbg == 3) return;
-    if (dbg == 1 || dbg == 2) {
-        for (int c = 0; c < ncols; c += 32) {
-            float v[32];
-            tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-            tmem_ld_wait();
-            const long long grow = row0 + q * 32 + lane;
-            if (dbg == 1 && grow < row_end) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (col0 + c + 4 * j < col_end)
-                        *reinterpret_cast<float4*>(C + grow * ldc + col0 + c + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-            } else if (v[0] == 123.456f) C[0] = v[1];
-        }
-        return;
-    }
     for (int c = 0; c < ncols; c += 32) {
         const int gcol = col0 + c + cc;
         const bool col_ok = gcol < col_end;
@@ -256,105 +242,6 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
 }
 
 // ------------------------------------------------------------------ C[M,N] = A[M,K] * op(B)
-template <bool kBMN>
-__global__ void __launch_bounds__(kThreads, 1)
-k_gemm_tf32_rows(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
-                 const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
-                 uint32_t* __restrict__ bits_out, long long ldbits) {
-    extern __shared__ uint8_t smem_raw[];
-    const Smem sm = carve_smem(smem_raw);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t tmem_base = prologue(sm, warp);
-    pdl_enter();           // barriers, TMEM and descriptors are set up while the previous kernel drains; global memory only from here
-
-    const int n_tiles = (N + BN - 1) / BN;
-    const int m_tiles = (M + 255) / 256;
-    const int tiles = n_tiles * m_tiles;
-    const int KB = (K + kBK - 1) / kBK;
-
-    if (warp == 0) {
-        if (lane == 0) {
-            tma_prefetch_desc(&tmA);
-            tma_prefetch_desc(&tmB);
-            int stage = 0;
-            uint32_t phase = 0;
-            const uint32_t tx = kAStage + (uint32_t)BN * 128u;
-            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-                const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
-                for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(sm.empty(stage), phase ^ 1);
-                    mbar_expect_tx(sm.full(stage), tx);
-                    tma_load_2d(sm.a(stage), &tmA, sm.full(stage), kb * kBK, m0);
-                    if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK, n0 / 32);
-                    else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0);
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_tf32(128, BN, 0, kBMN ? 1 : 0);
-            int stage = 0;
-            uint32_t phase = 0, tphase = 0;
-            for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-                const int m0 = (t / n_tiles) * 256;
-                const int halves = (m0 + 128 < M) ? 2 : 1;
-                mbar_wait(sm.tmem_empty(), tphase ^ 1);
-                tc_fence_after();
-                for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(sm.full(stage), phase);
-                    tc_fence_after();
-#pragma unroll
-                    for (int k = 0; k < kBK / 8; ++k) {
-                        const uint64_t bdesc = kBMN ? make_smem_desc(sm.b(stage) + k * 1024, 32 * 128, 512, kLayoutSw128B32)
-                                                    : make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
-                        for (int h = 0; h < halves; ++h) {
-                            const uint64_t adesc = make_smem_desc(sm.a(stage) + h * (128 * 128) + k * 32, 16, 1024, kLayoutSw128);
-                            mma_tf32(tmem_base + h * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
-                        }
-                    }
-                    mma_commit(sm.empty(stage));
-                    if (kb == KB - 1) mma_commit(sm.tmem_full());
-                    if (++stage == kStages) { stage = 0; phase ^= 1; }
-                }
-                tphase ^= 1;
-            }
-        }
-    } else {
-        const int q = warp & 3;
-        uint32_t tphase = 0, it = 0;
-        // register-store path only for act(C + AB): the epilogue must read C before it can apply the activation / mask
-        const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask)) && ((flags >> 8) & 3) == 0;
-        if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
-        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-            const int m0 = (t / n_tiles) * 256, n0 = (t % n_tiles) * BN;
-            const int halves = (m0 + 128 < M) ? 2 : 1;
-            mbar_wait(sm.tmem_full(), tphase);
-            tc_fence_after();
-            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
-            for (int h = 0; h < halves; ++h) {
-                if (use_tma)
-                    epilogue_tma(sm, tmem_base + h * 256, q, lane, &tmC, m0 + h * 128, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
-                else
-                    epilogue_acc(sm, tmem_base + h * 256, q, lane, C, ldc, (long long)m0 + h * 128, M, n0, N, ncols, bias, flags, mask, ldm);
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(sm.tmem_empty());
-            tphase ^= 1;
-        }
-        if (use_tma && lane == 0) tma_store_wait_all();
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
-    }
-}
-
-// ------------------------------------------------------------------ C[M,N] = A[M,K] * op(B), version 2
 // 128 rows per CTA and tile (ONE 128 x BN accumulator = 256 TMEM columns), so the 512 columns hold two accumulators
 // and the epilogue of tile i overlaps the loads + MMAs of tile i+1; 4 stages x 48 KB.  With kCluster == 2 two CTAs
 // (a thread-block cluster, adjacent row tiles, same N tile) each load HALF of every weight stage and multicast it to
@@ -577,7 +464,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 if (use_tma)
                     epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
                 else
-                    epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags & 0xff, mask, ldm);
+                    epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags, mask, ldm);
             }
             tc_fence_before();
             __syncwarp();
@@ -702,60 +589,115 @@ k_gemm_tf32_red_batched(const __grid_constant__ RedBatch bt, float* __restrict__
 
 // ------------------------------------------------------------------ host side
 static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+    static std::once_flag once;
     static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
+    std::call_once(once, [] {
         void* p = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
             q == cudaDriverEntryPointSuccess)
             fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
-    }
+    });
     return fn;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device property of a kernel: set it once per (kernel set, device).
+template <class SetFn>
+static int ensure_attrs(std::atomic<uint64_t>& done, SetFn set) {
+    int dev = 0;
+    GNNX_CUDA(cudaGetDevice(&dev));
+    const uint64_t bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_acquire) & bit) return GNNX_OK;
+    int rc = set();                                       // idempotent: two threads racing here both set the same value
+    if (rc == GNNX_OK) done.fetch_or(bit, std::memory_order_release);
+    return rc;
+}
+
 static CUtensorMapDataType tma_dtype() {
-    static int f32 = -1;
-    if (f32 < 0) {
+    static std::once_flag once;
+    static int f32 = 0;
+    std::call_once(once, [] {
         const char* e = getenv("GNNX_TMA_F32");      // diagnostic: raw fp32 bits (MMA truncates) instead of round-to-tf32
         f32 = (e && e[0] == '1') ? 1 : 0;
-    }
+    });
     return f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32;
 }
 
-// K-major view of a row-major [rows, cols] fp32 matrix: box = 32 floats x box_rows rows.
-static int make_map_kmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
-    cuuint32_t es[2] = {1, 1};
-    CUresult r = encode_fn()(m, tma_dtype(), 2, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (K-major) failed: %d", (int)r);
-}
-// MN-major view of a row-major [rows, cols] fp32 matrix (cols % 32 == 0): dims (32, rows, cols/32) so that one
-// box lands as [chunk][k row][32 floats] = the canonical MN-major operand layout of tf32 (128B swizzle, 32B atoms).
-static int make_map_mnmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_chunks) {
-    cuuint64_t dims[3] = {32, (cuuint64_t)rows, (cuuint64_t)(cols / 32)};
-    cuuint64_t strides[2] = {(cuuint64_t)ld * 4, 128};
-    cuuint32_t box[3] = {32, 32, (cuuint32_t)box_chunks};
-    cuuint32_t es[3] = {1, 1, 1};
-    CUresult r = encode_fn()(m, tma_dtype(), 3, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (MN-major) failed: %d", (int)r);
+// ---- tensor-map cache.  A CUtensorMap is a pure function of (address, dims, row stride, box, kind): the allocator
+// hands the same blocks back step after step, so the ~520 cuTensorMapEncodeTiled calls of a cfg2 step become lookups.
+struct MapKey {
+    const void* p; int64_t rows, cols, ld; int32_t box, kind, dtype, pad;
+    bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+        uint64_t h = 1469598103934665603ull;
+        for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) { h ^= w[i]; h *= 1099511628211ull; }
+        return (size_t)h;
+    }
+};
+enum { kMapKMajor = 0, kMapMNMajor = 1, kMapStore = 2 };
+
+static int encode_map(CUtensorMap* m, const MapKey& k) {
+    const float* p = static_cast<const float*>(k.p);
+    CUresult r;
+    if (k.kind == kMapKMajor) {
+        // K-major view of a row-major [rows, cols] fp32 matrix: box = 32 floats x box rows.
+        cuuint64_t dims[2] = {(cuuint64_t)k.cols, (cuuint64_t)k.rows};
+        cuuint64_t strides[1] = {(cuuint64_t)k.ld * 4};
+        cuuint32_t box[2] = {32, (cuuint32_t)k.box};
+        cuuint32_t es[2] = {1, 1};
+        r = encode_fn()(m, (CUtensorMapDataType)k.dtype, 2, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else if (k.kind == kMapMNMajor) {
+        // MN-major view of a row-major [rows, cols] fp32 matrix (cols % 32 == 0): dims (32, rows, cols/32) so that one
+        // box lands as [chunk][k row][32 floats] = the canonical MN-major operand layout of tf32 (128B swizzle, 32B atoms).
+        cuuint64_t dims[3] = {32, (cuuint64_t)k.rows, (cuuint64_t)(k.cols / 32)};
+        cuuint64_t strides[2] = {(cuuint64_t)k.ld * 4, 128};
+        cuuint32_t box[3] = {32, 32, (cuuint32_t)k.box};
+        cuuint32_t es[3] = {1, 1, 1};
+        r = encode_fn()(m, (CUtensorMapDataType)k.dtype, 3, const_cast<float*>(p), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        // Store view of a row-major [rows, cols] fp32 matrix: 32x32 tiles, 128B swizzle (matches epilogue_tma's staging).
+        cuuint64_t dims[2] = {(cuuint64_t)k.cols, (cuuint64_t)k.rows};
+        cuuint64_t strides[1] = {(cuuint64_t)k.ld * 4};
+        cuuint32_t box[2] = {32, 32};
+        cuuint32_t es[2] = {1, 1};
+        r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(p), dims, strides, box, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (kind %d) failed: %d", k.kind, (int)r);
 }
 
-// Store view of a row-major [rows, cols] fp32 matrix: 32x32 tiles, 128B swizzle (matches epilogue_tma's staging).
+static int cached_map(CUtensorMap* m, const void* p, int64_t rows, int64_t cols, int64_t ld, int box, int kind) {
+    static std::mutex mu;
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    MapKey k;
+    memset(&k, 0, sizeof k);
+    k.p = p; k.rows = rows; k.cols = cols; k.ld = ld; k.box = box; k.kind = kind;
+    k.dtype = kind == kMapStore ? (int)CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (int)tma_dtype();
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = cache.find(k);
+        if (it != cache.end()) { *m = it->second; return 0; }
+    }
+    if (encode_map(m, k)) return GNNX_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(mu);
+    if (cache.size() >= 8192) cache.clear();               // bounded: a long run with ever-new shapes starts over
+    cache.emplace(k, *m);
+    return 0;
+}
+static int make_map_kmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    return cached_map(m, p, rows, cols, ld, box_rows, kMapKMajor);
+}
+static int make_map_mnmajor(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld, int box_chunks) {
+    return cached_map(m, p, rows, cols, ld, box_chunks, kMapMNMajor);
+}
 static int make_map_store(CUtensorMap* m, const float* p, int64_t rows, int64_t cols, int64_t ld) {
-    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {32, 32};
-    cuuint32_t es[2] = {1, 1};
-    CUresult r = encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(p), dims, strides, box, es,
-                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : set_error(GNNX_ERR_INVALID, "cuTensorMapEncodeTiled (store) failed: %d", (int)r);
+    return cached_map(m, p, rows, cols, ld, 32, kMapStore);
 }
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -768,7 +710,7 @@ static RedPlan red_plan(int64_t Mo, int64_t No, int64_t R) {
     p.BM = Mo > 128 ? 256 : 128;
     p.BN = (int)(No < 256 ? No : 256);
     p.tiles = ceil_div(Mo, p.BM) * ceil_div(No, p.BN);
-    int want = kNumSMs / p.tiles;
+    int want = num_sms() / p.tiles;
     if (want < 1) want = 1;
     int64_t max_splits = (R + 255) / 256;                 // at least 256 rows per split
     if (max_splits < 1) max_splits = 1;
@@ -832,20 +774,20 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
             int n_groups) {
     (void)precision;
     if (!bucket_ptr) n_groups = 1;
-    static bool attr_done = false;
-    if (!attr_done) {
-        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_done = true;
+    static std::atomic<uint64_t> attrs_done{0};
+    {
+        int rc = ensure_attrs(attrs_done, []() -> int {
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            return GNNX_OK;
+        });
+        if (rc) return rc;
     }
-    static int epi_dbg = -1;
-    if (epi_dbg < 0) { const char* e = getenv("GNNX_EPI_DEBUG"); epi_dbg = e ? atoi(e) & 3 : 0; }
-    flags |= epi_dbg << 8;
     CUtensorMap mA, mB, mC;
-    static int use_v1 = -1;
-    if (use_v1 < 0) { const char* e = getenv("GNNX_GEMM_V1"); use_v1 = (e && e[0] == '1') ? 1 : 0; }
-    if (!ta && !use_v1) {
+    if (!ta) {
         const int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
         const int m_tiles = ceil_div(M, 128);
         const int cluster = (m_tiles >= 2 && (tb ? (BN % 16 == 0) : (BN % 64 == 0))) ? 2 : 1;
@@ -858,21 +800,14 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         const int group_rows = (int)(tb ? N : K);
         if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
         const int work = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
-        const int max_cl = kNumSMs / cluster;
+        const int max_cl = num_sms() / cluster;
         // Balanced rounds: 400 work items on 74 clusters are 5 full rounds plus one that keeps 30 clusters busy at their
         // per-SM rate; ceil(400 / 6) = 67 clusters all run 6 rounds at the chip's HBM rate instead (GNNX_GEMM_BALANCE=0: off)
-        static int balance = -1;
-        if (balance < 0) { const char* e = getenv("GNNX_GEMM_BALANCE"); balance = (e && e[0] == '0') ? 0 : 1; }
+        static std::once_flag bal_once;
+        static int balance = 1;
+        std::call_once(bal_once, [] { const char* e = getenv("GNNX_GEMM_BALANCE"); balance = (e && e[0] == '0') ? 0 : 1; });
         int ncl = work < max_cl ? work : max_cl;
         if (balance && work > max_cl) ncl = ceil_div(work, ceil_div(work, max_cl));
-        static bool attr2 = false;
-        if (!attr2) {
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            attr2 = true;
-        }
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(ncl * cluster);
         cfg.blockDim = dim3(kThreads2);
@@ -909,25 +844,8 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
                    : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 1>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
         if (trace_on()) trace_after(st);
         if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_rows2 launch: %s", cudaGetErrorString(e));
+        count_tc_launches(1);
         return check_launch("gemm_tf32_rows2");
-    }
-    if (!ta) {
-        GNNX_REQUIRE(!bucket_ptr, "gemm_tc: grouped products need the v2 kernel (unset GNNX_GEMM_V1)");
-        int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
-        if (make_map_kmajor(&mA, A, M, K, lda, 256)) return GNNX_ERR_INVALID;
-        if (tb) {
-            if (make_map_kmajor(&mB, B, N, K, ldb, BN)) return GNNX_ERR_INVALID;
-        } else {
-            if (make_map_mnmajor(&mB, B, K, N, ldb, BN / 32)) return GNNX_ERR_INVALID;
-        }
-        if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
-        int tiles = ceil_div(M, 256) * ceil_div(N, BN);
-        int grid = tiles < kNumSMs ? tiles : kNumSMs;
-        if (tb)
-            launch(k_gemm_tf32_rows<false>, grid, kThreads, kSmemBytes, st, mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
-        else
-            launch(k_gemm_tf32_rows<true>, grid, kThreads, kSmemBytes, st, mA, mB, mC, C, ldc, (int)M, (int)N, (int)K, BN, bias, flags, mask, ldm, bits_out, (long long)((N + 31) / 32));
-        return check_launch("gemm_tf32_rows");
     }
     // C[M,N] = A[K,M]^T B[K,N]: reduction over the K rows
     GNNX_REQUIRE(!bucket_ptr, "gemm_tc: grouped dW goes through gemm_tc_red_grouped");
@@ -938,6 +856,7 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     if (make_map_store(&mC, (const float*)ws, (int64_t)p.splits * M, N, N)) return GNNX_ERR_INVALID;
     launch(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
                                                                           p.rows_per_split, p.BM, p.BN, nullptr);
+    count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
     rc = splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
@@ -953,10 +872,13 @@ int tc_red_grouped_splits(int64_t Mo, int64_t No, int64_t R) { return red_plan(M
 
 int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, int64_t Mo, int64_t No, int64_t R,
                         const int* split_table, int S, float* partial, cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_done = true;
+    static std::atomic<uint64_t> attrs_done{0};
+    {
+        int rc = ensure_attrs(attrs_done, []() -> int {
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            return GNNX_OK;
+        });
+        if (rc) return rc;
     }
     RedPlan p = red_plan(Mo, No, R);
     CUtensorMap mA, mB, mC;
@@ -964,16 +886,17 @@ int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb
     if (make_map_mnmajor(&mB, B, R, No, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, partial, (int64_t)S * Mo, No, No)) return GNNX_ERR_INVALID;
     launch(k_gemm_tf32_red, dim3(p.tiles, S), kThreads, kSmemBytes, st, mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
+    count_tc_launches(1);
     return check_launch("gemm_tf32_red(grouped)");
 }
 
 // n weight gradients C_z[Mo,No] = A_z[R,Mo]^T B_z[R,No] of one shape in one launch + one ordered reduce per problem.
 bool tc_red_batched_ok(int n, int64_t Mo, int64_t No, int64_t R) {
-    return n >= 2 && n <= kRedBatch && ceil_div(Mo, Mo > 128 ? 256 : 128) * ceil_div(No, 256) * n <= kNumSMs && R >= 256;
+    return n >= 2 && n <= kRedBatch && ceil_div(Mo, Mo > 128 ? 256 : 128) * ceil_div(No, 256) * n <= num_sms() && R >= 256;
 }
 static RedPlan red_plan_batched(int n, int64_t Mo, int64_t No, int64_t R) {
     RedPlan p = red_plan(Mo, No, R);
-    int want = kNumSMs / (p.tiles * n);
+    int want = num_sms() / (p.tiles * n);
     if (want < 1) want = 1;
     int64_t max_splits = (R + 255) / 256;
     int splits = (int)(want < max_splits ? want : max_splits);
@@ -989,10 +912,13 @@ size_t tc_red_batched_workspace_bytes(int n, int64_t Mo, int64_t No, int64_t R) 
 int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const float* const* B, const int64_t* ldb,
                         float* const* C, const int64_t* ldc, int64_t Mo, int64_t No, int64_t R, void* ws, size_t ws_bytes,
                         cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_done = true;
+    static std::atomic<uint64_t> attrs_done{0};
+    {
+        int rc = ensure_attrs(attrs_done, []() -> int {
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_red_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+            return GNNX_OK;
+        });
+        if (rc) return rc;
     }
     const RedPlan p = red_plan_batched(n, Mo, No, R);
     const long long stride = (long long)p.splits * Mo * No;
@@ -1006,6 +932,7 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
     for (int z = n; z < kRedBatch; ++z) { bt.a[z] = bt.a[0]; bt.b[z] = bt.b[0]; bt.p[z] = bt.p[0]; }
     launch(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
            (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
+    count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red(batched)");
     for (int z = 0; z < n && rc == GNNX_OK; ++z)
         rc = splitk_reduce_launch((const float*)ws + z * stride, p.splits, (int)Mo, (int)No, C[z], ldc[z], nullptr, 0, nullptr, 0, st);

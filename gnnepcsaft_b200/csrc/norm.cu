@@ -32,7 +32,7 @@ __device__ __forceinline__ void welford_merge(Welford& a, const Welford& b) {
 
 static int bn_chunks(int64_t rows, int32_t C) {
     int slabs = ceil_div(C, 256);
-    int target = max(1, (kNumSMs * 4) / slabs);
+    int target = max(1, (num_sms() * 4) / slabs);
     int by_rows = max(1, (int)((rows + 63) / 64));
     return min(target, by_rows);
 }
@@ -425,7 +425,7 @@ __global__ void k_adamw_amsgrad(float* __restrict__ p, const float* __restrict__
 
 static inline int flat_grid(long long nthreads) {
     long long blocks = (nthreads + 255) / 256;
-    long long cap = (long long)kNumSMs * 32;
+    long long cap = (long long)num_sms() * 32;
     return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 
@@ -510,7 +510,7 @@ int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, i
     GNNX_REQUIRE(C % 4 == 0 && mode >= 0 && mode <= 2, "segment_pool_fwd: channels %% 4 == 0 and mode in {0,1,2}");
     if (G == 0) return GNNX_OK;
     long long nwork = G * ((C + 127) / 128);
-    int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
+    int nb = (int)min((nwork + 7) / 8, (long long)num_sms() * 32);
     launch(k_pool_fwd, nb, 256, 0, as_stream(stream), x, graph_ptr, (int)G, C, mode, out);
     return check_launch("segment_pool_fwd");
 }
@@ -520,7 +520,7 @@ int gnnx_segment_pool_bwd(const float* dout, const float* x, const float* out, c
     GNNX_REQUIRE(C % 4 == 0 && mode >= 0 && mode <= 2, "segment_pool_bwd: channels %% 4 == 0 and mode in {0,1,2}");
     if (G == 0) return GNNX_OK;
     long long nwork = G * ((C + 127) / 128);
-    int nb = (int)min((nwork + 7) / 8, (long long)kNumSMs * 32);
+    int nb = (int)min((nwork + 7) / 8, (long long)num_sms() * 32);
     launch(k_pool_bwd, nb, 256, 0, as_stream(stream), dout, x, out, graph_ptr, (int)G, C, mode, dx);
     return check_launch("segment_pool_bwd");
 }
@@ -572,7 +572,7 @@ extern "C" int gnnx_assemble_params(const float* msigmae, const float* log10asso
     GNNX_REQUIRE(!(log10assoc && assoc), "assemble_params: give the predicted log10 association pair OR known values, not both");
     if (G == 0) return GNNX_OK;
     long long blocks = (G + 255) / 256;
-    if (blocks > gnnx::kNumSMs * 8) blocks = gnnx::kNumSMs * 8;
+    if (blocks > gnnx::num_sms() * 8) blocks = gnnx::num_sms() * 8;
     launch(gnnx::k_assemble_params, (int)blocks, 256, 0, gnnx::as_stream(stream), msigmae, log10assoc, assoc, munanb, mw, G, out9);
     return gnnx::check_launch("assemble_params");
 }

@@ -164,7 +164,7 @@ __global__ void k_sum_partials(const float* __restrict__ partial, int nchunks, l
 }
 static int code_chunks(int64_t rows, int32_t H) {
     int slabs = ceil_div(H, 32);
-    int target = max(1, (kNumSMs * 3) / slabs);
+    int target = max(1, (num_sms() * 3) / slabs);
     int by_rows = max(1, (int)((rows + 511) / 512));
     return min(target, by_rows);
 }
@@ -431,12 +431,12 @@ __global__ void k_relu_bwd(const float* __restrict__ dy, const float* __restrict
 
 static inline int warp_grid(long long nwork) {   // 8 warps per block, grid a multiple of the SM count
     long long blocks = (nwork + 7) / 8;
-    long long cap = (long long)kNumSMs * 32;
+    long long cap = (long long)num_sms() * 32;
     return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 static inline int flat_grid(long long nthreads) {
     long long blocks = (nthreads + 255) / 256;
-    long long cap = (long long)kNumSMs * 32;
+    long long cap = (long long)num_sms() * 32;
     return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 

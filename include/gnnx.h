@@ -38,12 +38,20 @@ extern "C" {
 #define GNNX_ERR_UNSUPPORTED (-2) /* configuration outside the compiled envelope */
 #define GNNX_ERR_WORKSPACE (-3)   /* workspace too small */
 
-#define GNNX_ABI_VERSION 1
+/* Bumped on every prototype change; the Python layer refuses a library whose version differs. */
+#define GNNX_ABI_VERSION 2
 
 GNNX_API int gnnx_abi_version(void);
+/* SHA-256 (hex) of this header, every csrc/ source and the compiler flags the library was built from (stamped by
+ * gnnepcsaft_b200/build.py).  The loader compares it with the digest of the sources on disk, so a stale binary with
+ * the same symbol names but shifted argument layouts is rebuilt or refused instead of being called. */
+GNNX_API const char* gnnx_build_digest(void);
 GNNX_API const char* gnnx_last_error(void);
 /* Total number of CUDA kernels launched by this library in this process (monotonic). */
 GNNX_API int64_t gnnx_launch_count(void);
+/* Of those, the tcgen05 tensor-core kernels (k_gemm_tf32_rows2 / k_gemm_tf32_red*): lets a caller verify that a
+ * product really took the tensor path and not the fp32 CUDA-core fallback. */
+GNNX_API int64_t gnnx_tc_launch_count(void);
 /* Diagnostic per-kernel device timeline: between trace_begin and trace_end every kernel launch of this library is
  * bracketed by two CUDA events on its stream.  trace_end synchronises the device and writes one line per launch,
  * "kernel name \t kernel us \t us since the previous gnnx kernel ended" (launch order), into buf; it returns the
@@ -142,7 +150,7 @@ GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_fe
 #define GNNX_GEMM_MASK_BITS 4
 #define GNNX_PREC_FP32 0 /* CUDA-core fp32 FMA (parity tier, rel 1e-5)              */
 #define GNNX_PREC_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM             */
-#define GNNX_PREC_BF16 2 /* the reference's "medium": served by the tf32 kernels (more precise) */
+#define GNNX_PREC_BF16 2 /* reserved: rejected with GNNX_ERR_UNSUPPORTED (no bf16 kernels are built; tf32 is the tensor tier) */
 GNNX_API size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t trans_a, int32_t trans_b,
                                  int32_t precision);
 GNNX_API int gnnx_gemm(const float* A, int64_t lda, int32_t trans_a, const float* B, int64_t ldb, int32_t trans_b,

@@ -17,7 +17,26 @@ def test_library_exports_every_declared_symbol():
     dll = ctypes.CDLL(str(_lib.LIB_PATH))
     for name in _lib.parse_header():
         assert hasattr(dll, name), name
-    assert dll.gnnx_abi_version() == 1
+    assert dll.gnnx_abi_version() == _lib.ABI_VERSION == _lib._header_abi_version()
+
+
+def test_loaded_library_matches_the_sources_on_disk():
+    """a stale .so with the same symbols but another argument layout must not be callable.  The build digest
+    stamped into the binary equals the digest of include/gnnx.h + csrc/ + flags on disk (the loader rebuilds or raises)."""
+    from gnnepcsaft_b200 import build
+    L = _lib.lib()
+    assert L._dll.gnnx_build_digest().decode() == build.source_digest()
+    assert _lib._stale(L._dll) == ""
+
+
+def test_unknown_precisions_are_rejected():
+    import pytest
+    from gnnepcsaft_b200 import ops
+    with pytest.raises(ValueError):
+        ops.set_matmul_precision("bf16")           # no bf16 kernels are built; "medium" is served by the tf32 tier
+    ops.set_matmul_precision("medium")
+    assert ops.get_matmul_precision() == ops.PREC_TF32
+    ops.set_matmul_precision("fp32")
 
 
 def test_no_torch_types_in_signatures():
