@@ -76,12 +76,18 @@ static int gemm_dispatch(const float* A, int64_t lda, int32_t ta, const float* B
     GNNX_REQUIRE(!(colsum_a_out && ta), "gemm: colsum_a_out needs trans_a = 0");
     // tiny products (60-row bond tables, weight-space 256^3) are launch-latency-bound: one CTA of the tensor-core
     // kernel would walk them alone, the 32x32-tile fp32 kernel spreads them over the SMs (and is exact)
-    const bool tiny = (double)M * (double)N * (double)K < 33554432.0;
+    const bool force_tc = (flags & GNNX_GEMM_FORCE_TC) != 0;
+    flags &= ~GNNX_GEMM_FORCE_TC;
+    const bool tiny = !force_tc && (double)M * (double)N * (double)K < 33554432.0;
     // grouped tensor-core products: the row blocks of a 2-CTA cluster share one weight block (256-row buckets), and an
     // MN-major weight stack [G*K, N] must not let a k-block straddle two groups
     const bool group_ok = !bucket_ptr || (tb || K % 32 == 0);
     const bool tc = precision != GNNX_PREC_FP32 && !tiny && mask_ok && group_ok &&
                     tc_supported(M, N, K, ta, tb, lda, ldb, ldc, A, B, C, precision);
+    if (force_tc && !tc)
+        return set_error(GNNX_ERR_UNSUPPORTED, "gemm: GNNX_GEMM_FORCE_TC, but the tensor-core kernels do not take this product "
+                         "(precision %d, M %lld N %lld K %lld, trans %d/%d, alignment / mask / group constraints)", precision,
+                         (long long)M, (long long)N, (long long)K, ta, tb);
     const bool fuse_colsum = colsum_a_out && tc && K <= 256 && (K & 3) == 0;   // rides the tensor-core kernel's A tiles
     if (colsum_a_out && !fuse_colsum) {                    // separate two-pass kernel (same result, one more read of A)
         int rc = gnnx_colsum(A, lda, M, K, colsum_a_out, ws, ws_bytes, stream);

@@ -22,6 +22,11 @@ from . import ops, streams
 from .graph import Batch, batch_from_reference_tensors
 
 
+# Debug tap: when set to a list, the MLP head appends its two BatchNorm+ReLU outputs (tests teacher-force their sign
+# pattern onto the oracle's head ReLUs).
+CAPTURE_HEAD = None
+
+
 def get_conv(config: dict) -> Module:
     """Conv factory, reference models.py:441-584 (the convs any file in ``configs/`` selects)."""
     aggregators = ["mean", "min", "max", "std"]
@@ -154,7 +159,11 @@ class GNNePCSAFT(Module):
     def _head(self, x: Tensor) -> Tensor:
         m = self.mlp
         x = Fn.batch_norm(Fn.linear(x, m[0].weight, m[0].bias), m[1], relu=True)
+        if CAPTURE_HEAD is not None:
+            CAPTURE_HEAD.append(x.detach())
         x = Fn.batch_norm(Fn.linear(x, m[3].weight, m[3].bias), m[4], relu=True)
+        if CAPTURE_HEAD is not None:
+            CAPTURE_HEAD.append(x.detach())
         return Fn.linear(x, m[6].weight, m[6].bias)
 
     def pred_with_bounds(self, data: Any) -> Tensor:

@@ -15,7 +15,9 @@ from torch import Tensor
 from ._lib import lib
 
 PREC_FP32, PREC_TF32 = 0, 1
-GEMM_RELU, GEMM_ACCUMULATE, GEMM_MASK_BITS = 1, 2, 4
+GEMM_RELU, GEMM_ACCUMULATE, GEMM_MASK_BITS, GEMM_FORCE_TC = 1, 2, 4, 8
+# tests set this to pin every tf32-tier product onto the tcgen05 kernels (products they cannot take then raise)
+FORCE_TC = False
 # torch's names map onto the two tiers that exist: "highest" = CUDA-core fp32, "high" = tcgen05 tf32.  The reference's
 # "medium" (bf16-class products, train/train.py:54) has no kernels of its own here: it is served by the tf32 tier, which
 # is MORE precise than requested, and results are reported as tf32 (bench.py dtype), never as bf16.
@@ -231,6 +233,8 @@ def gemm(a: Tensor, b: Tensor, *, trans_a: bool = False, trans_b: bool = False, 
         raise ValueError("gnnx.gemm: want_colsum_a needs trans_a=False and cannot be combined with want_relu_bits")
     csum = torch.empty(K, dtype=torch.float32, device=a.device) if want_colsum_a else None
     prec = _default_precision if precision is None else precision
+    if FORCE_TC and prec != PREC_FP32:
+        flags |= GEMM_FORCE_TC
     L = lib()
     ws, nb = _ws(_query("gnnx_gemm_workspace_bytes", M, N, K, int(trans_a), int(trans_b), prec), a.device)
     L.call("gnnx_gemm", a.data_ptr(), _ld(a), int(trans_a), b.data_ptr(), _ld(b), int(trans_b), out.data_ptr(), _ld(out),

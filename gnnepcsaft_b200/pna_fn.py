@@ -33,8 +33,9 @@ from .functional import _c
 # ops.MAX_GROUPS in-degree classes; False forces the general scaler-folded path (tests compare the two).
 GROUPED_POST = True
 
-# Debug taps: when set to a list, every PNAConv forward appends dict(agg [N, T*4*F], m [E, T*F] dst-sorted, g)
-# (tests read which Std entries were zero-masked and which messages were the min / max of their row).
+# Debug taps: when set to a list, every PNAConv forward appends dict(agg [N, T*4*F], m [E, T*F] dst-sorted, g,
+# pre_relu [..], post_relu [..]) (tests read which Std entries were zero-masked, which messages were the min / max of
+# their row, and the sign pattern of every ReLU inside the layer).
 CAPTURE_AGG = None
 CAPTURE_BWD = None
 
@@ -234,6 +235,15 @@ class PNAConvFn(Function):
         else:
             os_, omasks = [o], [None]
         out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
+        if CAPTURE_AGG is not None:
+            # ReLU'd activations inside the pre / post chains (tests teacher-force their sign pattern onto the oracle):
+            # pre in dst-sorted slot order, post in node order
+            cap = CAPTURE_AGG[-1]
+            cap["pre_relu"] = list(hs[:-1]) if meta.pre_layers > 1 else []
+            post_relu = list(os_) if meta.post_layers > 1 else []
+            if meta.bucket_out:
+                post_relu = [ops.gather_rows(t, bk.node_pos) for t in post_relu]
+            cap["post_relu"] = post_relu
         ctx.meta = meta
         ctx.pk, ctx.wf = pk, (wf if pk.post else None)     # packed / fused weights of this call, reused by the backward
         ctx.n_hs, ctx.n_os = len(hs), len(os_)

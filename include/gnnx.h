@@ -148,6 +148,8 @@ GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_fe
 #define GNNX_GEMM_RELU 1
 #define GNNX_GEMM_ACCUMULATE 2
 #define GNNX_GEMM_MASK_BITS 4
+#define GNNX_GEMM_FORCE_TC 8 /* skip the size heuristic that sends small products to the fp32 kernel; GNNX_ERR_UNSUPPORTED
+                              * if the tensor-core kernels cannot take the product (tests pin the tcgen05 path with it) */
 #define GNNX_PREC_FP32 0 /* CUDA-core fp32 FMA (parity tier, rel 1e-5)              */
 #define GNNX_PREC_TF32 1 /* tcgen05 kind::tf32, fp32 accumulate in TMEM             */
 #define GNNX_PREC_BF16 2 /* reserved: rejected with GNNX_ERR_UNSUPPORTED (no bf16 kernels are built; tf32 is the tensor tier) */

@@ -223,6 +223,8 @@ def var_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
 # within the relative band STD_BAND of the threshold -- those would be genuine disagreements, not rounding.
 STD_MASKS = None
 STD_BAND = 2e-3
+STD_BAND_ABS = 0.0        # extra allowance proportional to E[x^2] (reduced-precision tiers: var = E[x^2] - E[x]^2 inherits
+                          # the ABSOLUTE error of its two terms, which a tf32 product puts at ~1e-3 E[x^2], far above 1e-5)
 STD_BAND_VIOLATIONS = []
 
 
@@ -236,7 +238,11 @@ def std_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
     forced = STD_MASKS.pop(0).to(own_mask.device).view_as(own_mask)
     differ = forced != own_mask
     if bool(differ.any()):
-        rel = (var.detach()[differ].double() - 1e-5).abs() / 1e-5
+        rel = (var.detach()[differ].double() - 1e-5).abs()
+        if STD_BAND_ABS > 0.0:
+            ex2 = scatter((x * x).detach(), index, dim_size, "mean")[differ].double()
+            rel = (rel - STD_BAND_ABS * ex2).clamp(min=0.0)
+        rel = rel / 1e-5
         STD_BAND_VIOLATIONS.append((int(differ.sum()), int((rel > STD_BAND).sum()), float(rel.max())))
     return var.clamp(min=1e-12).sqrt().masked_fill(forced, 0.0)
 
@@ -291,6 +297,33 @@ class DegreeScalerAggregation(Module):
         return torch.cat(outs, dim=-1) if len(outs) > 1 else outs[0]
 
 
+# Test hook for the ReLUs INSIDE PNAConv's pre_nn / post_nn chains and the MLP head.  A tensor-core (tf32) run of the
+# path carries ~1e-3 of relative error per product, so a visible fraction of pre-activations sits closer to zero than
+# that and two correct implementations disagree on their sign -- which switches those entries' gradients on or off
+# and hides the smooth (depth x 2^-11) error the tf32 parity test wants to bound.  When INNER_RELU_MASKS is a
+# non-empty list, successive ReLUs take their "kept" mask from it (teacher forcing the implementation under test),
+# and INNER_RELU_BAND_VIOLATIONS records every forced entry whose own |value| exceeds INNER_RELU_BAND x max|activation|.
+INNER_RELU_MASKS = None
+INNER_RELU_BAND = 2e-5
+INNER_RELU_BAND_VIOLATIONS = []
+
+
+class ForcedReLU(Module):
+    """``torch.nn.ReLU`` (parameter-free, same position in the Sequential: state-dict keys are unchanged)."""
+
+    def forward(self, y: Tensor) -> Tensor:
+        if not INNER_RELU_MASKS:
+            return F.relu(y)
+        forced = INNER_RELU_MASKS.pop(0).to(y.device).view_as(y)
+        differ = forced != (y > 0)
+        if bool(differ.any()):
+            gap = y.detach()[differ].abs().double()
+            scale = float(y.detach().abs().max())
+            INNER_RELU_BAND_VIOLATIONS.append((int(differ.sum()), int((gap > INNER_RELU_BAND * scale).sum()),
+                                               float(gap.max()) / max(scale, 1e-30)))
+        return torch.where(forced, y, torch.zeros_like(y))
+
+
 # --------------------------------------------------------------------------- R6
 class PNAConv(Module):
     """R6 -- ``gnn.PNAConv`` as instantiated at gnnepcsaft/train/models.py:445-457."""
@@ -314,12 +347,12 @@ class PNAConv(Module):
         for _ in range(towers):
             mods: List[Module] = [Linear((3 if edge_dim else 2) * self.F_in, self.F_in)]
             for _ in range(pre_layers - 1):
-                mods += [ReLU(), Linear(self.F_in, self.F_in)]
+                mods += [ForcedReLU(), Linear(self.F_in, self.F_in)]
             self.pre_nns.append(Sequential(*mods))
             k_in = (len(aggregators) * len(scalers) + 1) * self.F_in
             mods = [Linear(k_in, self.F_out)]
             for _ in range(post_layers - 1):
-                mods += [ReLU(), Linear(self.F_out, self.F_out)]
+                mods += [ForcedReLU(), Linear(self.F_out, self.F_out)]
             self.post_nns.append(Sequential(*mods))
         self.lin = Linear(out_channels, out_channels)
 
@@ -575,8 +608,8 @@ class GNNePCSAFT(Module):
             self.batch_norms.append(BatchNorm(config["hidden_dim"]))
         h = config["hidden_dim"]
         self.mlp = Sequential(
-            Linear(h, h // 2), BatchNorm1d(h // 2), ReLU(),
-            Linear(h // 2, h // 4), BatchNorm1d(h // 4), ReLU(),
+            Linear(h, h // 2), BatchNorm1d(h // 2), ForcedReLU(),
+            Linear(h // 2, h // 4), BatchNorm1d(h // 4), ForcedReLU(),
             Linear(h // 4, config["num_para"]),
         )
 

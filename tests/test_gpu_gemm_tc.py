@@ -41,10 +41,15 @@ def _prec():
 
 
 def _tc_taken(fn):
-    """Run fn and assert it launched kernels (the tensor-core path counts 1 launch for rows, 2 for the reduction)."""
-    n0 = lib().launch_count()
-    out = fn()
-    assert lib().launch_count() > n0
+    """Run fn with the size heuristic off (ops.FORCE_TC: a product the tcgen05 kernels cannot take raises instead of
+    falling back) and assert that a tensor-core kernel really was launched (gnnx_tc_launch_count)."""
+    n0 = lib().tc_launch_count()
+    ops.FORCE_TC = True
+    try:
+        out = fn()
+    finally:
+        ops.FORCE_TC = False
+    assert lib().tc_launch_count() > n0, "no tcgen05 kernel was launched"
     return out
 
 
@@ -54,7 +59,7 @@ def test_linear_forward_layout(M, N, K):
     a, w, bias = torch.randn(M, K), torch.randn(N, K), torch.randn(N)
     out = _tc_taken(lambda: ops.gemm(a.to(DEV), w.to(DEV), trans_b=True, bias=bias.to(DEV)))
     _check(out, a.double(), w.double().t(), bias.double(), what=f"NT {M}x{N}x{K}")
-    out = ops.gemm(a.to(DEV), w.to(DEV), trans_b=True, bias=bias.to(DEV), relu=True)
+    out = _tc_taken(lambda: ops.gemm(a.to(DEV), w.to(DEV), trans_b=True, bias=bias.to(DEV), relu=True))
     _check(out, a.double(), w.double().t(), bias.double(), relu=True, what=f"NT+relu {M}x{N}x{K}")
 
 
@@ -100,9 +105,17 @@ def test_dw_strided_accumulate():
 
 def test_small_or_unaligned_shapes_fall_back_to_fp32_kernel():
     a, w = torch.randn(60, 13), torch.randn(64, 13)        # the 60-row bond table product: SIMT path, fp32-exact class
+    t0 = lib().tc_launch_count()
     out = ops.gemm(a.to(DEV), w.to(DEV), trans_b=True)
+    assert lib().tc_launch_count() == t0
     ref = a.double() @ w.double().t()
     assert float((out.double().cpu() - ref).abs().max()) < 1e-4
+    ops.FORCE_TC = True                                    # and pinning it onto the tensor path must fail loudly
+    try:
+        with pytest.raises(RuntimeError):
+            ops.gemm(a.to(DEV), w.to(DEV), trans_b=True)
+    finally:
+        ops.FORCE_TC = False
 
 
 @pytest.mark.parametrize("prec", ["tf32", "fp32"])

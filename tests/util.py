@@ -70,11 +70,33 @@ class branches_from:
     rounding band of its discontinuity (oracle/pyg_restated.py: STD_MASKS, EXTREMUM_SELECT).  No entry is dropped
     from the comparison.  Use one instance per oracle forward pass."""
 
-    def __init__(self, captured, towers, relu_outputs=()):
+    def __init__(self, captured, towers, relu_outputs=(), inner_relus=False, head_outputs=(), relu_band=None):
         """``relu_outputs``: the CUDA model's per-layer BatchNorm+ReLU outputs (their > 0 pattern is forced onto the
-        oracle's ReLU behind each BatchNorm, oracle/pyg_restated.py: RELU_MASKS)."""
+        oracle's ReLU behind each BatchNorm, oracle/pyg_restated.py: RELU_MASKS).  ``inner_relus``: also force the ReLUs
+        inside every PNAConv's pre_nn / post_nn chains (captured ``pre_relu`` / ``post_relu``) and, with ``head_outputs``
+        (models.CAPTURE_HEAD), the two ReLUs of the MLP head -- the tf32 tier's test, where ~1e-3 of product error moves
+        many pre-activations across zero.  ``relu_band``: the rounding band those disagreements must lie in, relative
+        to max|activation| (default: the oracle's fp32 bands)."""
         self.std_masks, self.selects = [], []
         self.relu_masks = [(y.detach() > 0).cpu() for y in relu_outputs]
+        self.inner_masks = []
+        self.relu_band = relu_band
+        self.max_relu_flips = 8
+        if inner_relus:
+            for c in captured:
+                g = c["g"]
+                eid = g.csr_eid.long()
+                for t in range(towers):                     # oracle order: tower by tower, pre chains first
+                    for h in c["pre_relu"]:
+                        f = h.shape[1] // towers
+                        m = torch.empty((h.shape[0], f), dtype=torch.bool, device=h.device)
+                        m[eid] = h[:, t * f:(t + 1) * f] > 0       # dst-sorted slot -> original edge order
+                        self.inner_masks.append(m.cpu())
+                for t in range(towers):
+                    for o in c["post_relu"]:
+                        f = o.shape[1] // towers
+                        self.inner_masks.append((o[:, t * f:(t + 1) * f] > 0).cpu())
+            self.inner_masks += [(y.detach() > 0).cpu() for y in head_outputs]
         for c in captured:
             agg, m, g = c["agg"], c["m"], c["g"]
             n, e = agg.shape[0], m.shape[0]
@@ -93,16 +115,32 @@ class branches_from:
         O.STD_MASKS = [m.clone() for m in self.std_masks]
         O.EXTREMUM_SELECT = [m.clone() for m in self.selects]
         O.RELU_MASKS = [m.clone() for m in self.relu_masks] if self.relu_masks else None
+        O.INNER_RELU_MASKS = [m.clone() for m in self.inner_masks] if self.inner_masks else None
         O.STD_BAND_VIOLATIONS.clear()
         O.EXTREMUM_BAND_VIOLATIONS.clear()
         O.RELU_BAND_VIOLATIONS.clear()
+        O.INNER_RELU_BAND_VIOLATIONS.clear()
+        self._bands = (O.RELU_BAND, O.INNER_RELU_BAND, O.STD_BAND_ABS, O.EXTREMUM_BAND)
+        if self.relu_band is not None:                   # tf32 tier: every band widens to the tier's rounding
+            O.RELU_BAND = O.INNER_RELU_BAND = self.relu_band
+            O.STD_BAND_ABS = self.relu_band              # |var - 1e-5| <= STD_BAND * 1e-5 + band * E[x^2]
+            O.EXTREMUM_BAND = max(O.EXTREMUM_BAND, self.relu_band)
         return self
 
     def __exit__(self, *exc):
-        left = len(O.STD_MASKS) + len(O.EXTREMUM_SELECT) + len(O.RELU_MASKS or ())
+        left = len(O.STD_MASKS) + len(O.EXTREMUM_SELECT) + len(O.RELU_MASKS or ()) + len(O.INNER_RELU_MASKS or ())
         O.STD_MASKS = None
         O.EXTREMUM_SELECT = None
         O.RELU_MASKS = None
+        O.INNER_RELU_MASKS = None
+        O.RELU_BAND, O.INNER_RELU_BAND, O.STD_BAND_ABS, O.EXTREMUM_BAND = self._bands
+        if exc[0] is None and self.relu_band is not None:
+            assert left == 0, "oracle made fewer aggregator / ReLU calls than the CUDA path"
+            for name, v in (("Std mask", O.STD_BAND_VIOLATIONS), ("min/max routing", O.EXTREMUM_BAND_VIOLATIONS),
+                            ("BatchNorm ReLU sign", O.RELU_BAND_VIOLATIONS), ("inner ReLU sign", O.INNER_RELU_BAND_VIOLATIONS)):
+                bad = [x for x in v if x[1] > 0]
+                assert not bad, f"{name} disagreements outside the tf32 rounding band: {bad}"
+            return False
         if exc[0] is None:
             assert left == 0, "oracle made fewer aggregator calls than the CUDA path"
             bad = [v for v in O.STD_BAND_VIOLATIONS if v[1] > 0]
