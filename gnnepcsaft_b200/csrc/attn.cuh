@@ -45,16 +45,9 @@ __device__ __forceinline__ float head_sum(float part, int C) {
 // (seed, slot * heads + head) so that forward and backward agree without storing a mask -- the forward still records
 // the outcome in the SIGN of the saved alpha (alpha >= 0; dropped entries are stored negated, -0.0 included).
 __device__ __forceinline__ bool attn_keep(unsigned long long seed, long long index, unsigned int threshold) {
-    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(index + 1);
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;          // splitmix64 finaliser
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    return (unsigned int)(z >> 32) >= threshold;           // P(drop) = threshold / 2^32
+    return dropout_keep(seed, index, threshold);          // common.cuh (shared with the node-feature dropout)
 }
-static inline unsigned int attn_drop_threshold(float p) {
-    double t = (double)p * 4294967296.0;
-    return t <= 0.0 ? 0u : (t >= 4294967295.0 ? 4294967295u : (unsigned int)t);
-}
+static inline unsigned int attn_drop_threshold(float p) { return dropout_threshold(p); }
 __device__ __forceinline__ bool attn_dropped(float stored_alpha) { return (__float_as_uint(stored_alpha) >> 31) != 0u; }
 
 // Grid for the destination-side kernels: every warp keeps ONE head group for its whole life and strides over rows

@@ -85,6 +85,37 @@ __device__ __forceinline__ void stg4(float* p, float4 v) { *reinterpret_cast<flo
 __device__ __forceinline__ float4 ldg4_stream(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ void stg4_stream(float* p, float4 v) { __stcs(reinterpret_cast<float4*>(p), v); }
 
+// Counter-based dropout draw: keep(index) is a pure function of (seed, index), so a forward kernel and its backward agree
+// without a stored mask.  Used per (slot, head) by the attention kernels and per element by the node-feature dropout
+// fused into the BatchNorm apply / embedding kernels.  P(drop) = threshold / 2^32.
+__device__ __forceinline__ bool dropout_keep(unsigned long long seed, long long index, unsigned int threshold) {
+    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(index + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;          // splitmix64 finaliser
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (unsigned int)(z >> 32) >= threshold;
+}
+static inline unsigned int dropout_threshold(float p) {
+    double t = (double)p * 4294967296.0;
+    return t <= 0.0 ? 0u : (t >= 4294967295.0 ? 4294967295u : (unsigned int)t);
+}
+// Node-feature dropout applied in an epilogue: thr == 0 means "off"; kept values are scaled by 1 / (1 - p).
+struct NodeDropout {
+    unsigned long long seed;
+    unsigned int thr;
+    float scale;
+};
+static inline NodeDropout node_dropout(float p, long long seed) {
+    NodeDropout d;
+    d.seed = (unsigned long long)seed;
+    d.thr = dropout_threshold(p);
+    d.scale = p > 0.f && p < 1.f ? 1.f / (1.f - p) : (p >= 1.f ? 0.f : 1.f);
+    return d;
+}
+__device__ __forceinline__ float drop_apply(const NodeDropout& d, long long index, float v) {
+    return d.thr == 0u ? v : (dropout_keep(d.seed, index, d.thr) ? v * d.scale : 0.f);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

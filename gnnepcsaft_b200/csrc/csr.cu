@@ -59,11 +59,12 @@ int set_error(int code, const char* fmt, ...) {
 // ------------------------------------------------------------------ histogram
 template <typename IdxT>
 __global__ void k_hist(const IdxT* __restrict__ src, const IdxT* __restrict__ dst, int E, int N,
-                       int* __restrict__ cnt_dst, int* __restrict__ cnt_src, int* __restrict__ err) {
+                       int* __restrict__ cnt_dst, int* __restrict__ cnt_src, int* __restrict__ err,
+                       int* __restrict__ pos_of_eid) {
     pdl_enter();
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
         long long s = (long long)src[e], d = (long long)dst[e];
-        if (s < 0 || s >= N || d < 0 || d >= N) { *err = 1; continue; }
+        if (s < 0 || s >= N || d < 0 || d >= N) { *err = 1; if (pos_of_eid) pos_of_eid[e] = 0; continue; }
         atomicAdd(&cnt_dst[d + 1], 1);
         atomicAdd(&cnt_src[s + 1], 1);
     }
@@ -159,7 +160,7 @@ __global__ void k_place(const IdxT* __restrict__ src, const IdxT* __restrict__ d
     pdl_enter();
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += gridDim.x * blockDim.x) {
         long long s = (long long)src[e], d = (long long)dst[e];
-        if (s < 0 || s >= N || d < 0 || d >= N) continue;
+        if (s < 0 || s >= N || d < 0 || d >= N) continue;      // (k_hist raised err_flag; the slot tails are zero-filled below)
         tmp_dst[rowptr[d] + atomicAdd(&fill_dst[d], 1)] = e;
         tmp_src[colptr[s] + atomicAdd(&fill_src[s], 1)] = e;
     }
@@ -203,8 +204,14 @@ __device__ void sort_ids(int* a, int n) {
 template <typename IdxT>
 __global__ void k_sort_rows_dst(const IdxT* __restrict__ src, int N, const int* __restrict__ rowptr,
                                 int* __restrict__ tmp_dst, int* __restrict__ csr_src,
-                                int* __restrict__ csr_eid, int* __restrict__ pos_of_eid) {
+                                int* __restrict__ csr_eid, int* __restrict__ pos_of_eid, int E) {
     pdl_enter();
+    // edges with an out-of-range endpoint were skipped (err_flag): the slots past rowptr[N] hold no edge.  They are
+    // zero-filled so that no consumer ever indexes with uninitialised memory (a valid batch has rowptr[N] == E).
+    for (int p = rowptr[N] + blockIdx.x * blockDim.x + threadIdx.x; p < E; p += gridDim.x * blockDim.x) {
+        csr_eid[p] = 0;
+        csr_src[p] = 0;
+    }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         int b = rowptr[i], n = rowptr[i + 1] - b;
         sort_ids(tmp_dst + b, n);
@@ -220,8 +227,12 @@ __global__ void k_sort_rows_dst(const IdxT* __restrict__ src, int N, const int* 
 template <typename IdxT>
 __global__ void k_sort_rows_src(const IdxT* __restrict__ dst, int N, const int* __restrict__ colptr,
                                 int* __restrict__ tmp_src, const int* __restrict__ pos_of_eid,
-                                int* __restrict__ csc_pos, int* __restrict__ csc_dst) {
+                                int* __restrict__ csc_pos, int* __restrict__ csc_dst, int E) {
     pdl_enter();
+    for (int p = colptr[N] + blockIdx.x * blockDim.x + threadIdx.x; p < E; p += gridDim.x * blockDim.x) {
+        csc_pos[p] = 0;
+        csc_dst[p] = 0;
+    }
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < N; j += gridDim.x * blockDim.x) {
         int b = colptr[j], n = colptr[j + 1] - b;
         sort_ids(tmp_src + b, n);
@@ -260,15 +271,15 @@ static int csr_build_impl(const IdxT* src, const IdxT* dst, int64_t N64, int64_t
     GNNX_CUDA(cudaMemsetAsync(fill_src, 0, sizeof(int) * (size_t)n1, st));
     GNNX_CUDA(cudaMemsetAsync(err_flag, 0, sizeof(int), st));
     int eb = E > 0 ? min(ceil_div(E, 256), num_sms() * 16) : 0;
-    if (E > 0) launch(k_hist<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, err_flag);
+    if (E > 0) launch(k_hist<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, err_flag, pos_of_eid);
     launch(k_scan_tiles, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
     launch(k_scan_sums, 2, kScanThreads, 0, st, sums, ntiles);
     launch(k_scan_add, dim3(ntiles, 2), kScanThreads, 0, st, rowptr, colptr, n1, sums, ntiles);
     if (E > 0) {
         launch(k_place<IdxT>, eb, 256, 0, st, src, dst, E, N, rowptr, colptr, fill_dst, fill_src, tmp_dst, tmp_src);
         int nb = min(ceil_div(N, 128), num_sms() * 16);
-        launch(k_sort_rows_dst<IdxT>, nb, 128, 0, st, src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid);
-        launch(k_sort_rows_src<IdxT>, nb, 128, 0, st, dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst);
+        launch(k_sort_rows_dst<IdxT>, nb, 128, 0, st, src, N, rowptr, tmp_dst, csr_src, csr_eid, pos_of_eid, E);
+        launch(k_sort_rows_src<IdxT>, nb, 128, 0, st, dst, N, colptr, tmp_src, pos_of_eid, csc_pos, csc_dst, E);
     }
     return check_launch("csr_build", E > 0 ? 7 : 3);
 }
@@ -301,18 +312,36 @@ __global__ void k_graph_ptr(const int64_t* __restrict__ batch, int N, int G, int
     }
 }
 
-__global__ void k_narrow(const int64_t* __restrict__ in, long long count, uint8_t* __restrict__ out) {
+// Column limits of a categorical feature matrix (vocabulary sizes); n == 0: no range check (limit 256).
+struct NarrowLimits { int n; int lim[16]; };
+
+__global__ void k_narrow(const int64_t* __restrict__ in, long long count, NarrowLimits lim, uint8_t* __restrict__ out,
+                         int* __restrict__ err) {
     pdl_enter();
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
-        out[i] = (uint8_t)in[i];
+    bool bad = false;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x) {
+        const long long v = in[i];
+        const int hi = lim.n ? lim.lim[i % lim.n] : 256;
+        const bool ok = v >= 0 && v < hi;
+        bad |= !ok;
+        out[i] = ok ? (uint8_t)v : (uint8_t)0;            // an out-of-vocabulary id never reaches a table lookup
+    }
+    if (bad && err) *err = 1;
 }
 
-__global__ void k_edge_codes(const uint8_t* __restrict__ ea, const int* __restrict__ eid, int E, uint8_t* __restrict__ codes) {
+__global__ void k_edge_codes(const uint8_t* __restrict__ ea, const int* __restrict__ eid, int E,
+                             uint8_t* __restrict__ codes, int* __restrict__ err) {
     pdl_enter();
+    bool bad = false;
     for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < E; p += gridDim.x * blockDim.x) {
-        const uint8_t* a = ea + 3ll * eid[p];
-        codes[p] = (uint8_t)((a[0] * 6 + a[1]) * 2 + a[2]);
+        const int e = eid[p];
+        const bool eok = e >= 0 && e < E;
+        const uint8_t* a = ea + 3ll * (eok ? e : 0);
+        const bool ok = eok && a[0] < 5 && a[1] < 6 && a[2] < 2;      // OGB bond vocabularies (data/ogb_utils.py:24-33)
+        bad |= !ok;
+        codes[p] = ok ? (uint8_t)((a[0] * 6 + a[1]) * 2 + a[2]) : (uint8_t)0;
     }
+    if (bad && err) *err = 1;
 }
 
 // one warp per selected molecule: copy its node / edge records to the batch, adding offsets
@@ -394,17 +423,27 @@ int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t N, int64_t G, int32_
     return check_launch("graph_ptr_from_batch");
 }
 
-int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream) {
+int gnnx_narrow_i64_u8(const int64_t* in, int64_t rows, int32_t cols, const int32_t* limits_host, uint8_t* out,
+                       int32_t* err_flag, void* stream) {
+    GNNX_REQUIRE(rows >= 0 && cols >= 1, "narrow_i64_u8: bad shape");
+    GNNX_REQUIRE(!limits_host || cols <= 16, "narrow_i64_u8: at most 16 checked columns");
+    const long long count = (long long)rows * cols;
     if (count == 0) return GNNX_OK;
+    NarrowLimits lim;
+    lim.n = limits_host ? cols : 0;
+    for (int k = 0; k < 16; ++k) {
+        int v = (limits_host && k < cols) ? limits_host[k] : 256;
+        lim.lim[k] = v < 256 ? v : 256;
+    }
     int nb = min(ceil_div(count, 256), num_sms() * 16);
-    launch(k_narrow, nb, 256, 0, as_stream(stream), in, count, out);
+    launch(k_narrow, nb, 256, 0, as_stream(stream), in, count, lim, out, err_flag);
     return check_launch("narrow_i64_u8");
 }
 
-int gnnx_edge_codes(const uint8_t* ea, const int32_t* csr_eid, int64_t E, uint8_t* codes, void* stream) {
+int gnnx_edge_codes(const uint8_t* ea, const int32_t* csr_eid, int64_t E, uint8_t* codes, int32_t* err_flag, void* stream) {
     if (E == 0) return GNNX_OK;
     int nb = min(ceil_div(E, 256), num_sms() * 16);
-    launch(k_edge_codes, nb, 256, 0, as_stream(stream), ea, csr_eid, (int)E, codes);
+    launch(k_edge_codes, nb, 256, 0, as_stream(stream), ea, csr_eid, (int)E, codes, err_flag);
     return check_launch("edge_codes");
 }
 

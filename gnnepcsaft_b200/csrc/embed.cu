@@ -8,7 +8,7 @@
 namespace gnnx {
 
 __global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, const int* __restrict__ offsets,
-                            const float* __restrict__ table, int H, float* __restrict__ out) {
+                            const float* __restrict__ table, int H, float* __restrict__ out, NodeDropout drop) {
     pdl_enter();
     int lane = threadIdx.x & 31;
     int wpb = blockDim.x >> 5;
@@ -25,7 +25,12 @@ __global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, co
                     acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
                 }
             }
-            if (active) stg4(out + (long long)r * H + c, acc);
+            if (active) {
+                const long long o = (long long)r * H + c;            // Dropout(p) on the first layer's input (models.py:209)
+                acc.x = drop_apply(drop, o, acc.x); acc.y = drop_apply(drop, o + 1, acc.y);
+                acc.z = drop_apply(drop, o + 2, acc.z); acc.w = drop_apply(drop, o + 3, acc.w);
+                stg4(out + o, acc);
+            }
         }
     }
 }
@@ -37,7 +42,7 @@ constexpr int kEmbFlight = 16; // rows in flight per thread: the row walk is a l
 __global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, int K,
                                     const int* __restrict__ offsets, int table_rows,
                                     const float* __restrict__ dout, int H, int rows_per_chunk,
-                                    float* __restrict__ partial) {
+                                    float* __restrict__ partial, NodeDropout drop) {
     pdl_enter();
     extern __shared__ float tab[];
     int c = blockIdx.x * kEmbSlab + threadIdx.x;
@@ -55,14 +60,14 @@ __global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, i
             int ix[kEmbFlight];
 #pragma unroll
             for (int u = 0; u < kEmbFlight; ++u) {
-                v[u] = __ldg(dout + (long long)(r + u) * H + c);
+                v[u] = drop_apply(drop, (long long)(r + u) * H + c, __ldg(dout + (long long)(r + u) * H + c));
                 ix[u] = off + idx[(long long)(r + u) * K + k];
             }
 #pragma unroll
             for (int u = 0; u < kEmbFlight; ++u) tab[ix[u] * kEmbSlab + threadIdx.x] += v[u];
         }
         for (; r < r1; ++r) {
-            float v = __ldg(dout + (long long)r * H + c);
+            float v = drop_apply(drop, (long long)r * H + c, __ldg(dout + (long long)r * H + c));
             tab[(off + idx[(long long)r * K + k]) * kEmbSlab + threadIdx.x] += v;
         }
     }
@@ -99,12 +104,13 @@ using namespace gnnx;
 extern "C" {
 
 int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_t* offsets, const float* table,
-                       int32_t H, float* out, void* stream) {
+                       int32_t H, float dropout_p, int64_t seed, float* out, void* stream) {
+    GNNX_REQUIRE(dropout_p >= 0.f && dropout_p <= 1.f, "embed_sum_fwd: dropout_p must be in [0, 1]");
     GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_fwd: num_features must be in [1,32]");
     GNNX_REQUIRE(H % 4 == 0, "embed_sum_fwd: hidden must be a multiple of 4");
     if (rows == 0) return GNNX_OK;
     int nb = min(ceil_div(rows, 8), num_sms() * 8);
-    launch(k_embed_fwd, nb, 256, 0, as_stream(stream), idx, (int)rows, K, offsets, table, H, out);
+    launch(k_embed_fwd, nb, 256, 0, as_stream(stream), idx, (int)rows, K, offsets, table, H, out, node_dropout(dropout_p, seed));
     return check_launch("embed_sum_fwd");
 }
 
@@ -113,7 +119,8 @@ size_t gnnx_embed_sum_bwd_workspace_bytes(int64_t rows, int32_t table_rows, int3
 }
 
 int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_t* offsets, int32_t table_rows,
-                       const float* dout, int32_t H, float* dtable, void* ws, size_t ws_bytes, void* stream) {
+                       const float* dout, int32_t H, float dropout_p, int64_t seed, float* dtable, void* ws, size_t ws_bytes,
+                       void* stream) {
     GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_bwd: num_features must be in [1,32]");
     GNNX_REQUIRE(ws_bytes >= gnnx_embed_sum_bwd_workspace_bytes(rows, table_rows, H), "embed_sum_bwd: workspace too small");
     cudaStream_t st = as_stream(stream);
@@ -126,7 +133,7 @@ int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
     if (smem > 48 * 1024)
         GNNX_CUDA(cudaFuncSetAttribute(k_embed_bwd_partial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     launch(k_embed_bwd_partial, dim3(ceil_div(H, kEmbSlab), nchunks), dim3(32, K), smem, st, 
-        idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws);
+        idx, (int)rows, K, offsets, table_rows, dout, H, rpc, (float*)ws, node_dropout(dropout_p, seed));
     launch(k_reduce_partials, min(ceil_div(count, 256), num_sms() * 8), 256, 0, st, (const float*)ws, nchunks, count, dtable);
     return check_launch("embed_sum_bwd", 2);
 }

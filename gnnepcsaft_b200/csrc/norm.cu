@@ -154,7 +154,7 @@ __device__ __forceinline__ float bn_affine(float v, float mu, float rs, float w,
 
 __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, const float* __restrict__ weight,
                            const float* __restrict__ bias, const float* __restrict__ mean, const float* __restrict__ rstd,
-                           int relu, float* __restrict__ y, const int* __restrict__ row_node) {
+                           int relu, float* __restrict__ y, const int* __restrict__ row_node, NodeDropout drop) {
     pdl_enter();
     const int c4 = C / 4;
     long long total = rows * c4;
@@ -170,7 +170,8 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             float t = bn_affine(v.a[j], mu.a[j], rs.a[j], w.a[j], b.a[j]);
-            o.a[j] = relu ? fmaxf(t, 0.f) : t;
+            t = relu ? fmaxf(t, 0.f) : t;
+            o.a[j] = drop_apply(drop, orow * C + c + j, t);     // Dropout(p) of the NEXT layer's input (models.py:209), node-order index
         }
         stg4(y + orow * C + c, o.q);
     }
@@ -181,7 +182,7 @@ __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
                  int rows, int C, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
                  int rows_per_chunk, float* __restrict__ partial, const int* __restrict__ row_node,
-                 const float* __restrict__ weight, const float* __restrict__ bias) {
+                 const float* __restrict__ weight, const float* __restrict__ bias, NodeDropout drop) {
     pdl_enter();
     (void)y;                                       // the ReLU mask is re-derived from x (bn_affine): y is not read
     // row_node != null: x is in degree-bucket order (rows = bucket capacity), dy / y in node order
@@ -200,6 +201,7 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
         for (; r + 4 < r1; r += 8) {
             F4 g[2], xv[2];
             bool pad[2] = {false, false};
+            long long oi[2] = {0, 0};
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 long long o = (long long)(r + 4 * u) * C + c;
@@ -209,6 +211,7 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
                     if (node < 0) { g[u].q = make_float4(0.f, 0.f, 0.f, 0.f); pad[u] = true; continue; }
                     o = (long long)node * C + c;
                 }
+                oi[u] = o;
                 g[u].q = ldg4_stream(dy + o);
             }
 #pragma unroll
@@ -216,7 +219,7 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const bool off = pad[u] || (relu && !(bn_affine(xv[u].a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f));
-                    float gg = off ? 0.f : g[u].a[j];
+                    float gg = off ? 0.f : drop_apply(drop, oi[u] + j, g[u].a[j]);
                     s1.a[j] += gg;
                     s2.a[j] = fmaf(gg, (xv[u].a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
                 }
@@ -233,7 +236,7 @@ k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, cons
             g.q = ldg4_stream(dy + o);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f)) ? 0.f : g.a[j];
+                float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f)) ? 0.f : drop_apply(drop, o + j, g.a[j]);
                 s1.a[j] += gg;
                 s2.a[j] = fmaf(gg, (xv.a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
             }
@@ -275,12 +278,14 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
                                long long rows, int C, const float* __restrict__ weight, const float* __restrict__ mean,
                                const float* __restrict__ rstd, const float* __restrict__ dweight,
                                const float* __restrict__ dbias, int relu, float* __restrict__ dx,
-                               const int* __restrict__ row_node, long long n_valid, const float* __restrict__ bias) {
+                               const int* __restrict__ row_node, long long n_valid, const float* __restrict__ bias,
+                               NodeDropout drop, int training) {
     pdl_enter();
     (void)y;
     const int c4 = C / 4;
     long long total = rows * c4;
-    const float inv_n = 1.f / (float)n_valid;
+    // eval mode: mean / rstd are constants (running statistics), so dx = w rstd dy' with no batch-coupling terms
+    const float inv_n = training ? 1.f / (float)n_valid : 0.f;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         int c = (int)(i % c4) * 4;
         long long ni = i;                             // bucket-ordered x / dx: dy and y are read at the node's own row
@@ -298,7 +303,7 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
         dw.q = ldg4(dweight + c); db.q = ldg4(dbias + c);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], w.a[j], bb.a[j]) > 0.f)) ? 0.f : g.a[j];
+            float gg = (relu && !(bn_affine(xv.a[j], mu.a[j], rs.a[j], w.a[j], bb.a[j]) > 0.f)) ? 0.f : drop_apply(drop, ni * 4 + j, g.a[j]);
             float xh = (xv.a[j] - mu.a[j]) * rs.a[j];
             o.a[j] = w.a[j] * rs.a[j] * (gg - db.a[j] * inv_n - xh * dw.a[j] * inv_n);
         }
@@ -441,7 +446,9 @@ size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t C) {
 
 static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int32_t* row_node, int32_t C, const float* weight,
                        const float* bias, float* running_mean, float* running_var, int32_t training, float momentum, float eps,
-                       int32_t relu, float* y, float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
+                       int32_t relu, float dropout_p, int64_t seed, float* y, float* save_mean, float* save_rstd, void* ws,
+                       size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(dropout_p >= 0.f && dropout_p <= 1.f, "bn_relu_fwd: dropout_p must be in [0, 1]");
     GNNX_REQUIRE(C % 4 == 0, "bn_relu_fwd: channels must be a multiple of 4");
     GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_fwd: workspace too small");
     GNNX_REQUIRE(save_mean && save_rstd, "bn_relu_fwd: save_mean / save_rstd are required");
@@ -457,53 +464,59 @@ static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int3
         GNNX_REQUIRE(running_mean && running_var, "bn_relu_fwd: eval mode needs running statistics");
         launch(k_bn_eval_stats, ceil_div(C, 128), 128, 0, st, running_mean, running_var, C, eps, save_mean, save_rstd);
     }
-    launch(k_bn_apply, flat_grid(rows * (C / 4)), 256, 0, st, x, rows, C, weight, bias, save_mean, save_rstd, relu, y, row_node);
+    launch(k_bn_apply, flat_grid(rows * (C / 4)), 256, 0, st, x, rows, C, weight, bias, save_mean, save_rstd, relu, y, row_node,
+           node_dropout(dropout_p, seed));
     return check_launch("bn_relu_fwd", training ? 3 : 2);
 }
 
 int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t C, const float* weight, const float* bias, float* running_mean,
-                     float* running_var, int32_t training, float momentum, float eps, int32_t relu, float* y,
-                     float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
-    return bn_fwd_impl(x, rows, rows, nullptr, C, weight, bias, running_mean, running_var, training, momentum, eps, relu, y,
-                       save_mean, save_rstd, ws, ws_bytes, stream);
+                     float* running_var, int32_t training, float momentum, float eps, int32_t relu, float dropout_p,
+                     int64_t seed, float* y, float* save_mean, float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
+    return bn_fwd_impl(x, rows, rows, nullptr, C, weight, bias, running_mean, running_var, training, momentum, eps, relu,
+                       dropout_p, seed, y, save_mean, save_rstd, ws, ws_bytes, stream);
 }
 
 int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* row_node, int64_t num_nodes, int32_t C,
                           const float* weight, const float* bias, float* running_mean, float* running_var, int32_t training,
-                          float momentum, float eps, int32_t relu, float* y, float* save_mean, float* save_rstd, void* ws,
-                          size_t ws_bytes, void* stream) {
+                          float momentum, float eps, int32_t relu, float dropout_p, int64_t seed, float* y, float* save_mean,
+                          float* save_rstd, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(row_node, "bn_relu_rows_fwd: row_node is required");
     return bn_fwd_impl(x, rows, num_nodes, row_node, C, weight, bias, running_mean, running_var, training, momentum, eps, relu,
-                       y, save_mean, save_rstd, ws, ws_bytes, stream);
+                       dropout_p, seed, y, save_mean, save_rstd, ws, ws_bytes, stream);
 }
 
 static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t rows, int64_t n_valid, const int32_t* row_node,
-                       int32_t C, const float* weight, const float* bias, const float* save_mean, const float* save_rstd, int32_t relu, float* dx,
+                       int32_t C, const float* weight, const float* bias, const float* save_mean, const float* save_rstd, int32_t relu,
+                       int32_t training, float dropout_p, int64_t seed, float* dx,
                        float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
+    const NodeDropout drop = node_dropout(dropout_p, seed);
     GNNX_REQUIRE(C % 4 == 0, "bn_relu_bwd: channels must be a multiple of 4");
     GNNX_REQUIRE(ws_bytes >= gnnx_bn_workspace_bytes(rows, C), "bn_relu_bwd: workspace too small");
     if (rows == 0) return GNNX_OK;
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
-    launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node, weight, bias);
+    launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node, weight, bias, drop);
     launch(k_bn_bwd_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, dweight, dbias);
-    launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid, bias);
+    launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid, bias, drop, training);
     return check_launch("bn_relu_bwd", 3);
 }
 
 int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t C, const float* weight,
-                     const float* bias, const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
-                     void* ws, size_t ws_bytes, void* stream) {
-    return bn_bwd_impl(dy, x, y, rows, rows, nullptr, C, weight, bias, save_mean, save_rstd, relu, dx, dweight, dbias, ws, ws_bytes, stream);
+                     const float* bias, const float* save_mean, const float* save_rstd, int32_t relu, int32_t training,
+                     float dropout_p, int64_t seed, float* dx, float* dweight, float* dbias, void* ws, size_t ws_bytes,
+                     void* stream) {
+    return bn_bwd_impl(dy, x, y, rows, rows, nullptr, C, weight, bias, save_mean, save_rstd, relu, training, dropout_p, seed, dx,
+                       dweight, dbias, ws, ws_bytes, stream);
 }
 
 int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
                           int64_t num_nodes, int32_t C, const float* weight, const float* bias, const float* save_mean,
-                          const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
+                          const float* save_rstd, int32_t relu, int32_t training, float dropout_p, int64_t seed, float* dx,
+                          float* dweight, float* dbias, void* ws, size_t ws_bytes, void* stream) {
     GNNX_REQUIRE(row_node, "bn_relu_rows_bwd: row_node is required");
-    return bn_bwd_impl(dy, x, y, rows, num_nodes, row_node, C, weight, bias, save_mean, save_rstd, relu, dx, dweight, dbias, ws,
-                       ws_bytes, stream);
+    return bn_bwd_impl(dy, x, y, rows, num_nodes, row_node, C, weight, bias, save_mean, save_rstd, relu, training, dropout_p, seed,
+                       dx, dweight, dbias, ws, ws_bytes, stream);
 }
 
 int gnnx_segment_pool_fwd(const float* x, const int32_t* graph_ptr, int64_t G, int32_t C, int32_t mode, float* out, void* stream) {
@@ -565,6 +578,21 @@ __global__ void k_assemble_params(const float* __restrict__ msigmae, const float
     }
 }
 }  // namespace gnnx
+
+namespace gnnx {
+__global__ void k_dropout_keep_mask(NodeDropout d, long long count, uint8_t* __restrict__ keep) {
+    pdl_enter();
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
+        keep[i] = (d.thr == 0u || dropout_keep(d.seed, i, d.thr)) ? 1 : 0;
+}
+}  // namespace gnnx
+
+extern "C" int gnnx_dropout_keep_mask(float dropout_p, int64_t seed, int64_t count, uint8_t* keep, void* stream) {
+    GNNX_REQUIRE(dropout_p >= 0.f && dropout_p <= 1.f && count >= 0, "dropout_keep_mask: bad argument");
+    if (count == 0) return GNNX_OK;
+    launch(gnnx::k_dropout_keep_mask, gnnx::flat_grid(count), 256, 0, gnnx::as_stream(stream), gnnx::node_dropout(dropout_p, seed), count, keep);
+    return gnnx::check_launch("dropout_keep_mask");
+}
 
 extern "C" int gnnx_assemble_params(const float* msigmae, const float* log10assoc, const float* assoc, const float* munanb,
                                     const float* mw, int64_t G, float* out9, void* stream) {

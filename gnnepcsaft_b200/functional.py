@@ -52,9 +52,11 @@ def linear(x: Tensor, weight: Tensor, bias: Optional[Tensor], relu: bool = False
 # ------------------------------------------------------------------ BatchNorm (+ReLU)
 class _BatchNormFn(Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets=None):
-        y, mean, rstd = ops.bn_relu_fwd(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets)
-        ctx.relu, ctx.training, ctx.buckets = relu, training, buckets
+    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets=None,
+                dropout_p=0.0, seed=0):
+        y, mean, rstd = ops.bn_relu_fwd(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, buckets,
+                                        dropout_p, seed)
+        ctx.relu, ctx.training, ctx.buckets, ctx.drop = relu, training, buckets, (dropout_p, seed)
         ctx.save_for_backward(x, weight, bias, mean, rstd)     # the backward re-derives the ReLU mask from x: y is not kept
         return y
 
@@ -62,21 +64,26 @@ class _BatchNormFn(Function):
     @once_differentiable
     def backward(ctx, dy):
         x, weight, bias, mean, rstd = ctx.saved_tensors
-        if not ctx.training:
-            raise NotImplementedError("gnnx: batch-norm backward is implemented for training mode only")
-        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, None, weight, mean, rstd, ctx.relu, ctx.buckets, bias=bias)
-        return dx, dw, db, None, None, None, None, None, None, None
+        dx, dw, db = ops.bn_relu_bwd(_c(dy), x, None, weight, mean, rstd, ctx.relu, ctx.buckets, bias=bias,
+                                     training=ctx.training, dropout_p=ctx.drop[0], seed=ctx.drop[1])
+        return dx, dw, db, None, None, None, None, None, None, None, None, None
 
 
-def batch_norm(x: Tensor, bn: torch.nn.BatchNorm1d, relu: bool = False, buckets=None) -> Tensor:
-    """BatchNorm1d (+ fused ReLU) with the module's parameters / running statistics.  ``buckets``: ``x`` is a PNAConv
-    output in degree-bucket order (``PNAConv(..., bucket_out=True)``); the result is in node order."""
+def batch_norm(x: Tensor, bn: torch.nn.BatchNorm1d, relu: bool = False, buckets=None, dropout_p: float = 0.0,
+               seed: int = 0) -> Tensor:
+    """BatchNorm1d (+ fused ReLU, + the next layer's node-feature Dropout) with the module's parameters / running
+    statistics.  ``buckets``: ``x`` is a PNAConv output in degree-bucket order (``PNAConv(..., bucket_out=True)``); the
+    result is in node order.  Gradients flow in eval mode too (frozen statistics: fine-tuning, saliency)."""
     training = bn.training or not bn.track_running_stats
-    momentum = 0.1 if bn.momentum is None else bn.momentum
     if training and bn.track_running_stats and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
+    if bn.momentum is None:
+        # torch: cumulative moving average, factor 1 / num_batches_tracked (one host read; no reference config uses it)
+        momentum = 1.0 / max(1, int(bn.num_batches_tracked.item())) if (training and bn.track_running_stats) else 0.0
+    else:
+        momentum = bn.momentum
     return _BatchNormFn.apply(_c(x), bn.weight, bn.bias, bn.running_mean, bn.running_var, training, momentum,
-                              bn.eps, relu, buckets)
+                              bn.eps, relu, buckets, dropout_p, seed)
 
 
 # ------------------------------------------------------------------ graph pooling
@@ -102,20 +109,20 @@ def segment_pool(x: Tensor, graph_ptr: Tensor, mode: str) -> Tensor:
 # ------------------------------------------------------------------ OGB embedding sums
 class _EmbedFn(Function):
     @staticmethod
-    def forward(ctx, table, idx_u8, offsets):
+    def forward(ctx, table, idx_u8, offsets, dropout_p=0.0, seed=0):
         ctx.save_for_backward(idx_u8, offsets)
-        ctx.rows = table.shape[0]
-        return ops.embed_sum_fwd(idx_u8, offsets, table)
+        ctx.rows, ctx.drop = table.shape[0], (dropout_p, seed)
+        return ops.embed_sum_fwd(idx_u8, offsets, table, dropout_p, seed)
 
     @staticmethod
     @once_differentiable
     def backward(ctx, dout):
         idx_u8, offsets = ctx.saved_tensors
-        return ops.embed_sum_bwd(idx_u8, offsets, ctx.rows, _c(dout)), None, None
+        return ops.embed_sum_bwd(idx_u8, offsets, ctx.rows, _c(dout), ctx.drop[0], ctx.drop[1]), None, None, None, None
 
 
-def embed_sum(table: Tensor, idx_u8: Tensor, offsets: Tensor) -> Tensor:
-    return _EmbedFn.apply(table, idx_u8, offsets)
+def embed_sum(table: Tensor, idx_u8: Tensor, offsets: Tensor, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+    return _EmbedFn.apply(table, idx_u8, offsets, dropout_p, seed)
 
 
 class _MatFn(Function):

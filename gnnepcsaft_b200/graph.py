@@ -17,6 +17,9 @@ from torch import Tensor
 
 from . import ops
 
+ATOM_FEATURE_DIMS = (119, 5, 12, 12, 10, 6, 6, 2, 2)   # gnnepcsaft/data/ogb_utils.py:9-23
+BOND_FEATURE_DIMS = (5, 6, 2)                           # gnnepcsaft/data/ogb_utils.py:24-33
+
 
 class DegreeBuckets:
     """Nodes of one batch bucketed by in-degree (``ops.degree_buckets``): the row order of the degree-grouped
@@ -53,14 +56,26 @@ class GraphIndex:
     def degree_buckets(self) -> Optional[DegreeBuckets]:
         """In-degree buckets of this batch, or ``None`` when it has more than ``ops.MAX_GROUPS`` degree classes
         (the caller then takes the general scaler path).  Without a host-side bound from the collator the maximum
-        in-degree is read back once per batch (one device->host sync)."""
+        in-degree is read back once per batch (one device->host sync) -- together with the batch's error flags, so
+        an out-of-range ``edge_index`` / feature id raises here like PyG / torch.nn.Embedding do, at no extra sync."""
         if self._buckets is None:
             if self.max_degree is None:
-                mx = torch.zeros(1, dtype=torch.int32, device=self.rowptr.device)
-                ops.degree_hist(self.rowptr, torch.zeros(1, dtype=torch.int64, device=self.rowptr.device), mx)
-                self.max_degree = int(mx.item())
+                ops.degree_hist(self.rowptr, torch.zeros(1, dtype=torch.int64, device=self.rowptr.device),
+                                self.err_flag[ops.ST_MAX_DEGREE:ops.ST_MAX_DEGREE + 1])
+                self.max_degree = self.read_status()[ops.ST_MAX_DEGREE]
             self._buckets = DegreeBuckets(self.rowptr, self.max_degree + 1) if self.max_degree < ops.MAX_GROUPS else False
         return self._buckets or None
+
+    def read_status(self) -> List[int]:
+        """The batch's status words (``ops.ST_*``) on the host -- ONE device->host sync; raises on any error flag."""
+        vals = self.err_flag.tolist()
+        if vals[ops.ST_EDGE]:
+            raise IndexError("edge_index contains node ids outside [0, num_nodes)")
+        if vals[ops.ST_ATOM]:
+            raise IndexError("x contains an atom feature id outside its OGB vocabulary (gnnepcsaft/data/ogb_utils.py:9-23)")
+        if vals[ops.ST_BOND]:
+            raise IndexError("edge_attr contains a bond feature id outside its OGB vocabulary (gnnepcsaft/data/ogb_utils.py:24-33)")
+        return vals
 
     @staticmethod
     def build(edge_index: Tensor, num_nodes: int, check: bool = False) -> "GraphIndex":
@@ -77,9 +92,8 @@ class GraphIndex:
         return g
 
     def check(self) -> None:
-        """Raise like PyG does on an out-of-range endpoint (costs one device->host sync)."""
-        if int(self.err_flag.item()) != 0:
-            raise IndexError("edge_index contains node ids outside [0, num_nodes)")
+        """Raise like PyG / torch do on an out-of-range endpoint or feature id (costs one device->host sync)."""
+        self.read_status()
 
     @property
     def in_degree(self) -> Tensor:
@@ -127,11 +141,27 @@ class Batch:
     def num_nodes(self) -> int:
         return int(self.x.shape[0])
 
+    def validate(self) -> None:
+        """Raise ``IndexError`` if any endpoint / feature id of this batch was out of range (one device->host sync).
+        The kernels are memory-safe either way (such ids are skipped / read as 0); paths that already synchronise
+        (``forward(..., batch)`` without ``num_graphs``, the max-degree readback) check the same flags for free."""
+        if self.index is not None:
+            self.index.read_status()
+
 
 class DeviceGraphStore:
     """A whole dataset kept packed in HBM (uint8 features, int16 local endpoints) -- SURVEY §8(f) rank 2."""
 
     def __init__(self, packed, device):
+        # the packed store is validated ONCE on the host, so batches collated from it need no device-side check
+        n_of_edge = np.repeat(np.diff(packed.node_ptr).astype(np.int32), np.diff(packed.edge_ptr))
+        if packed.src.size and (packed.src.min() < 0 or packed.dst.min() < 0 or (packed.src >= n_of_edge).any()
+                                or (packed.dst >= n_of_edge).any()):
+            raise IndexError("packed store: an edge endpoint lies outside its molecule's node range")
+        if packed.x.size and (packed.x >= np.asarray(ATOM_FEATURE_DIMS, packed.x.dtype)).any():
+            raise IndexError("packed store: an atom feature id is outside its OGB vocabulary")
+        if packed.edge_attr.size and (packed.edge_attr >= np.asarray(BOND_FEATURE_DIMS, packed.edge_attr.dtype)).any():
+            raise IndexError("packed store: a bond feature id is outside its OGB vocabulary")
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
         self.x, self.src, self.dst, self.edge_attr = t(packed.x), t(packed.src), t(packed.dst), t(packed.edge_attr)
         self.node_ptr, self.edge_ptr = t(packed.node_ptr), t(packed.edge_ptr)
@@ -183,11 +213,22 @@ def batch_from_reference_tensors(x: Tensor, edge_index: Tensor, edge_attr: Tenso
     """Wrap the reference's int64 batch tensors (already on the device) and build the index once."""
     N = int(x.shape[0])
     index = graph_index_for(edge_index, N)
+    st = index.err_flag
+    # narrow the categorical features here, range-checked against the OGB vocabularies: the flags land in the batch's
+    # status words, which the ONE host read below (or the max-degree readback, or Batch.validate()) checks
+    if x.dtype != torch.uint8:
+        x = ops.narrow_u8(x, ATOM_FEATURE_DIMS, st[ops.ST_ATOM:ops.ST_ATOM + 1])
+    if edge_attr.dtype != torch.uint8:
+        edge_attr = ops.narrow_u8(edge_attr, BOND_FEATURE_DIMS, st[ops.ST_BOND:ops.ST_BOND + 1])
     gp = None
     G = 1
     if batch is not None:
         if num_graphs is None:
-            num_graphs = int(batch[-1].item()) + 1 if N > 0 else 0     # PyG syncs here too (int(batch.max())+1)
+            if N > 0:                                              # PyG syncs here too (int(batch.max())+1)
+                st[ops.ST_LAST_GRAPH:ops.ST_LAST_GRAPH + 1].copy_(batch[-1:])
+                num_graphs = index.read_status()[ops.ST_LAST_GRAPH] + 1
+            else:
+                num_graphs = 0
         G = num_graphs
         gp = ops.graph_ptr_from_batch(batch, G)
     return Batch(x=x, edge_index=edge_index, edge_attr=edge_attr, batch=batch, num_graphs=G, index=index, graph_ptr=gp)

@@ -25,6 +25,9 @@ from .graph import Batch, batch_from_reference_tensors
 # Debug tap: when set to a list, the MLP head appends its two BatchNorm+ReLU outputs (tests teacher-force their sign
 # pattern onto the oracle's head ReLUs).
 CAPTURE_HEAD = None
+# Debug tap: when set to a list, every training-mode forward appends (p, [one seed per conv layer]) of its node-feature
+# dropout draws (tests rebuild the keep-masks with ops.dropout_keep_mask and replay them on the oracle).
+NODE_DROPOUT_SEEDS = None
 
 
 def get_conv(config: dict) -> Module:
@@ -102,20 +105,30 @@ class GNNePCSAFT(Module):
     # -- fast path: everything prebuilt on the device --------------------------------------
     def forward_batch(self, b: Batch) -> Tensor:
         g = b.index
-        x_idx = b.x if b.x.dtype == torch.uint8 else ops.narrow_u8(b.x)
-        ea_u8 = b.edge_attr if b.edge_attr.dtype == torch.uint8 else ops.narrow_u8(b.edge_attr)
-        edges = self.edge_embed.forward_table(ops.edge_codes(ea_u8.contiguous(), g.csr_eid))
+        st = g.err_flag
+        x_idx = b.x if b.x.dtype == torch.uint8 else ops.narrow_u8(b.x, gnn.ATOM_FEATURE_DIMS, st[ops.ST_ATOM:ops.ST_ATOM + 1])
+        ea_u8 = b.edge_attr if b.edge_attr.dtype == torch.uint8 else ops.narrow_u8(
+            b.edge_attr, gnn.BOND_FEATURE_DIMS, st[ops.ST_BOND:ops.ST_BOND + 1])
+        edges = self.edge_embed.forward_table(ops.edge_codes(ea_u8.contiguous(), g.csr_eid, st[ops.ST_BOND:ops.ST_BOND + 1]))
         preps = self._prepare_convs(edges, g)
-        x = self.node_embed(x_idx)
-        for conv, batch_norm, prep in zip(self.convs, self.batch_norms, preps):
-            x = self.dropout(x)
+        # Dropout(p) in front of every conv (reference models.py:209) is fused into the kernel that PRODUCES that conv's
+        # input: the embedding sum for layer 0, the BatchNorm+ReLU apply of layer l-1 for layer l.  No mask tensor: the
+        # draw is a function of (seed, element index) that the backward replays.  NODE_DROPOUT_SEEDS taps the seeds.
+        p = self.dropout.p if self.training else 0.0
+        L = len(self.convs)
+        seeds = [ops.dropout_seed() if p > 0.0 else 0 for _ in range(L)]
+        if NODE_DROPOUT_SEEDS is not None:
+            NODE_DROPOUT_SEEDS.append((p, list(seeds)))
+        x = self.node_embed(x_idx, dropout_p=p, seed=seeds[0]) if L else self.node_embed(x_idx)
+        for l, (conv, batch_norm, prep) in enumerate(zip(self.convs, self.batch_norms, preps)):
+            pn, sn = (p, seeds[l + 1]) if l + 1 < L else (0.0, 0)     # the next conv's dropout; none after the last layer
             if isinstance(conv, gnn.PNAConv):
                 # degree-grouped layers hand their rows to the batch norm in bucket order (no extra pass back to node order)
                 bk = conv.bucket_rows(g)
                 out = conv(x, b.edge_index, edges, index=g, prep=prep, bucket_out=bk is not None)
-                x = batch_norm(out, relu=True, buckets=bk)
+                x = batch_norm(out, relu=True, buckets=bk, dropout_p=pn, seed=sn)
             else:
-                x = batch_norm(conv(x, b.edge_index, edges, index=g), relu=True)
+                x = batch_norm(conv(x, b.edge_index, edges, index=g), relu=True, dropout_p=pn, seed=sn)
         if b.batch is not None or b.graph_ptr is not None:
             x = self.global_pool(x, ptr=b.graph_ptr)
         else:

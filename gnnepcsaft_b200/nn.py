@@ -19,12 +19,10 @@ from . import functional as Fn
 from . import ops
 from .functional import EdgeTable
 from .gat_fn import GATMeta, GATv2ConvFn
-from .graph import GraphIndex, graph_index_for
+from .graph import ATOM_FEATURE_DIMS, BOND_FEATURE_DIMS, GraphIndex, graph_index_for
 from .pna_fn import PNAConvFn, PNAMeta, grouped_ok, prepare as pna_prepare
 from .tconv_fn import TConvMeta, TransformerConvFn
 
-ATOM_FEATURE_DIMS = (119, 5, 12, 12, 10, 6, 6, 2, 2)   # gnnepcsaft/data/ogb_utils.py:9-23
-BOND_FEATURE_DIMS = (5, 6, 2)                           # gnnepcsaft/data/ogb_utils.py:24-33
 NUM_BOND_CODES = 60
 
 _PNA_AGGREGATORS = ["mean", "min", "max", "std"]
@@ -57,10 +55,13 @@ class _FeatureEncoder(Module):
     def table(self) -> Tensor:
         return torch.cat([e.weight for e in getattr(self, self.list_name)], 0)
 
-    def forward(self, x: Tensor) -> Tensor:
+    def forward(self, x: Tensor, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+        """``dropout_p`` > 0 (gnnx extension): also apply the node-feature Dropout that follows in the model, fused."""
         _require_cuda(x, type(self).__name__)
-        idx = x if x.dtype == torch.uint8 else ops.narrow_u8(x.contiguous())
-        return Fn.embed_sum(self.table(), idx.contiguous(), self._offsets)
+        # stand-alone use with int64 ids: out-of-vocabulary values are read as id 0 (memory-safe); the model path narrows
+        # with an error flag instead (graph.batch_from_reference_tensors) and raises IndexError like torch's Embedding
+        idx = x if x.dtype == torch.uint8 else ops.narrow_u8(x.contiguous(), self.dims)
+        return Fn.embed_sum(self.table(), idx.contiguous(), self._offsets, dropout_p, seed)
 
 
 class AtomEncoder(_FeatureEncoder):
@@ -103,18 +104,20 @@ class BatchNorm(Module):
     def reset_parameters(self):
         self.module.reset_parameters()
 
-    def forward(self, x: Tensor, relu: bool = False, buckets=None) -> Tensor:
+    def forward(self, x: Tensor, relu: bool = False, buckets=None, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+        """``relu`` / ``dropout_p`` (gnnx extensions): fuse the ReLU that follows in the model (models.py:212) and the
+        next layer's Dropout (models.py:209) into the same pass."""
         _require_cuda(x, "BatchNorm")
         if buckets is not None:
-            return Fn.batch_norm(x, self.module, relu, buckets)
+            return Fn.batch_norm(x, self.module, relu, buckets, dropout_p, seed)
         if self.allow_single_element and x.size(0) <= 1:
             was = self.module.training
             self.module.eval()
             try:
-                return Fn.batch_norm(x, self.module, relu)
+                return Fn.batch_norm(x, self.module, relu, None, dropout_p, seed)
             finally:
                 self.module.train(was)
-        return Fn.batch_norm(x, self.module, relu)
+        return Fn.batch_norm(x, self.module, relu, None, dropout_p, seed)
 
 
 class _SegmentAggregation(Module):

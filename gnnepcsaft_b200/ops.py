@@ -87,6 +87,10 @@ def _query(name: str, *args) -> int:
 
 
 # ------------------------------------------------------------------ collator
+STATUS_WORDS = 8
+ST_EDGE, ST_ATOM, ST_BOND, ST_LAST_GRAPH, ST_MAX_DEGREE = 0, 1, 2, 3, 4
+
+
 def csr_build(edge_index: Optional[Tensor], num_nodes: int, src32: Optional[Tensor] = None,
               dst32: Optional[Tensor] = None):
     """dst-sorted CSR + src-sorted view.  Pass either int64 ``edge_index`` [2,E] or int32 src/dst."""
@@ -103,7 +107,9 @@ def csr_build(edge_index: Optional[Tensor], num_nodes: int, src32: Optional[Tens
     rowptr, colptr = torch.empty(num_nodes + 1, **i32), torch.empty(num_nodes + 1, **i32)
     csr_src, csr_eid, pos = torch.empty(E, **i32), torch.empty(E, **i32), torch.empty(E, **i32)
     csc_pos, csc_dst = torch.empty(E, **i32), torch.empty(E, **i32)
-    err = torch.empty(1, **i32)
+    # status words of the batch: [0] edge endpoint out of range (written here), [1] atom feature / [2] bond feature out
+    # of vocabulary (narrow_u8 / edge_codes), [3] last graph id, [4] max in-degree -- read back together (graph.py)
+    err = torch.zeros(STATUS_WORDS, **i32)
     ws, nb = _ws(_query("gnnx_csr_workspace_bytes", num_nodes, E), dev)
     if edge_index is not None:
         L.call("gnnx_csr_build_i64", edge_index.data_ptr(), num_nodes, E, rowptr.data_ptr(), csr_src.data_ptr(),
@@ -129,18 +135,29 @@ def graph_ptr_from_batch(batch: Tensor, num_graphs: int) -> Tensor:
     return gp
 
 
-def narrow_u8(t: Tensor) -> Tensor:
+def narrow_u8(t: Tensor, limits=None, err: Optional[Tensor] = None) -> Tensor:
+    """int64 categorical features [rows, K] -> uint8.  ``limits`` (K vocabulary sizes): values outside [0, limit) are
+    written as 0 and raise ``err`` (a 1-element int32 device tensor / view) -- nothing downstream can index past a table."""
+    import ctypes
     _chk(t, torch.int64, "features")
+    if t.dim() != 2:
+        raise ValueError("gnnx.narrow_u8: features must be [rows, K]")
+    rows, K = t.shape
+    if limits is not None and len(limits) != K:
+        raise ValueError(f"gnnx.narrow_u8: {K} feature columns but {len(limits)} vocabulary sizes")
     out = torch.empty(t.shape, dtype=torch.uint8, device=t.device)
-    lib().call("gnnx_narrow_i64_u8", t.data_ptr(), t.numel(), out.data_ptr(), _stream())
+    lim = (ctypes.c_int32 * K)(*limits) if limits is not None else None
+    lib().call("gnnx_narrow_i64_u8", t.data_ptr(), rows, K, lim, out.data_ptr(), _p(err), _stream())
     return out
 
 
-def edge_codes(edge_attr_u8: Tensor, csr_eid: Tensor) -> Tensor:
+def edge_codes(edge_attr_u8: Tensor, csr_eid: Tensor, err: Optional[Tensor] = None) -> Tensor:
     _chk(edge_attr_u8, torch.uint8, "edge_attr_u8"); _chk(csr_eid, torch.int32, "csr_eid")
     E = csr_eid.numel()
+    if edge_attr_u8.numel() != 3 * E:
+        raise ValueError(f"gnnx.edge_codes: edge_attr must be [{E}, 3], got {tuple(edge_attr_u8.shape)}")
     codes = torch.empty(E, dtype=torch.uint8, device=csr_eid.device)
-    lib().call("gnnx_edge_codes", edge_attr_u8.data_ptr(), csr_eid.data_ptr(), E, codes.data_ptr(), _stream())
+    lib().call("gnnx_edge_codes", edge_attr_u8.data_ptr(), csr_eid.data_ptr(), E, codes.data_ptr(), _p(err), _stream())
     return codes
 
 
@@ -161,24 +178,33 @@ def collate_packed(store, graph_ids: Tensor, node_off: Tensor, edge_off: Tensor,
 
 
 # ------------------------------------------------------------------ embeddings
-def embed_sum_fwd(idx_u8: Tensor, offsets: Tensor, table: Tensor) -> Tensor:
+def embed_sum_fwd(idx_u8: Tensor, offsets: Tensor, table: Tensor, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
+    """``dropout_p`` > 0: the reference's node-feature Dropout in front of the first conv, fused (see include/gnnx.h)."""
     _chk(idx_u8, torch.uint8, "idx"); _chk(offsets, torch.int32, "offsets"); _chk(table, torch.float32, "table")
     rows, K = idx_u8.shape
     H = table.shape[1]
     out = torch.empty((rows, H), dtype=torch.float32, device=table.device)
-    lib().call("gnnx_embed_sum_fwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table.data_ptr(), H, out.data_ptr(), _stream())
+    lib().call("gnnx_embed_sum_fwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table.data_ptr(), H, float(dropout_p),
+               int(seed), out.data_ptr(), _stream())
     return out
 
 
-def embed_sum_bwd(idx_u8: Tensor, offsets: Tensor, table_rows: int, dout: Tensor) -> Tensor:
+def embed_sum_bwd(idx_u8: Tensor, offsets: Tensor, table_rows: int, dout: Tensor, dropout_p: float = 0.0, seed: int = 0) -> Tensor:
     _chk(idx_u8, torch.uint8, "idx"); _chk(dout, torch.float32, "dout")
     rows, K = idx_u8.shape
     H = dout.shape[1]
     dtable = torch.empty((table_rows, H), dtype=torch.float32, device=dout.device)
     ws, nb = _ws(_query("gnnx_embed_sum_bwd_workspace_bytes", rows, table_rows, H), dout.device)
     lib().call("gnnx_embed_sum_bwd", idx_u8.data_ptr(), rows, K, offsets.data_ptr(), table_rows, dout.data_ptr(), H,
-               dtable.data_ptr(), _p(ws), nb, _stream())
+               float(dropout_p), int(seed), dtable.data_ptr(), _p(ws), nb, _stream())
     return dtable
+
+
+def dropout_keep_mask(dropout_p: float, seed: int, shape, device) -> Tensor:
+    """The node-feature dropout draw for (seed, flat element index) as a bool tensor of ``shape`` (tests replay it)."""
+    keep = torch.empty(shape, dtype=torch.uint8, device=device)
+    lib().call("gnnx_dropout_keep_mask", float(dropout_p), int(seed), keep.numel(), keep.data_ptr(), _stream())
+    return keep.bool()
 
 
 # ------------------------------------------------------------------ dense transforms
@@ -471,9 +497,10 @@ def relu_bwd(dy: Tensor, y: Tensor) -> Tensor:
 
 # ------------------------------------------------------------------ batch norm / pooling
 def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bool, momentum: float, eps: float,
-                relu: bool, buckets=None):
+                relu: bool, buckets=None, dropout_p: float = 0.0, seed: int = 0):
     """``buckets`` (graph.DegreeBuckets): ``x`` is a PNAConv output left in degree-bucket order [capacity, C]; the
-    result is in node order [N, C] and padding rows take no part in the statistics."""
+    result is in node order [N, C] and padding rows take no part in the statistics.  ``dropout_p`` > 0: the next
+    layer's node-feature Dropout applied in the same pass (draw = f(seed, node-order element index))."""
     _chk(x, torch.float32, "x")
     rows, C = x.shape
     mean = torch.empty(C, dtype=torch.float32, device=x.device)
@@ -482,22 +509,23 @@ def bn_relu_fwd(x: Tensor, weight, bias, running_mean, running_var, training: bo
     if buckets is None:
         y = torch.empty_like(x)
         lib().call("gnnx_bn_relu_fwd", x.data_ptr(), rows, C, _p(weight), _p(bias), _p(running_mean), _p(running_var),
-                   int(training), float(momentum), float(eps), int(relu), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-                   _p(ws), nb, _stream())
+                   int(training), float(momentum), float(eps), int(relu), float(dropout_p), int(seed), y.data_ptr(),
+                   mean.data_ptr(), rstd.data_ptr(), _p(ws), nb, _stream())
     else:
         n = buckets.node_pos.numel()
         if rows != buckets.capacity:
             raise ValueError("gnnx.bn_relu_fwd: a bucket-ordered input must have `capacity` rows")
         y = torch.empty((n, C), dtype=torch.float32, device=x.device)
         lib().call("gnnx_bn_relu_rows_fwd", x.data_ptr(), rows, buckets.row_node.data_ptr(), n, C, _p(weight), _p(bias),
-                   _p(running_mean), _p(running_var), int(training), float(momentum), float(eps), int(relu), y.data_ptr(),
-                   mean.data_ptr(), rstd.data_ptr(), _p(ws), nb, _stream())
+                   _p(running_mean), _p(running_var), int(training), float(momentum), float(eps), int(relu), float(dropout_p),
+                   int(seed), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), _p(ws), nb, _stream())
     return y, mean, rstd
 
 
 def bn_relu_bwd(dy: Tensor, x: Tensor, y: Optional[Tensor], weight, mean: Tensor, rstd: Tensor, relu: bool, buckets=None,
-                bias=None):
-    """``bias``: the forward's bias -- the ReLU mask is re-derived from ``x`` (``y`` is not read and may be ``None``)."""
+                bias=None, training: bool = True, dropout_p: float = 0.0, seed: int = 0):
+    """``bias``: the forward's bias -- the ReLU mask is re-derived from ``x`` (``y`` is not read and may be ``None``).
+    ``training=False``: eval-mode backward (the statistics are constants).  ``dropout_p`` / ``seed``: as in the forward."""
     _chk(dy, torch.float32, "dy")
     rows, C = x.shape
     dx = torch.empty_like(x)
@@ -506,11 +534,12 @@ def bn_relu_bwd(dy: Tensor, x: Tensor, y: Optional[Tensor], weight, mean: Tensor
     ws, nb = _ws(_query("gnnx_bn_workspace_bytes", rows, C), x.device)
     if buckets is None:
         lib().call("gnnx_bn_relu_bwd", dy.data_ptr(), x.data_ptr(), _p(y), rows, C, _p(weight), _p(bias), mean.data_ptr(),
-                   rstd.data_ptr(), int(relu), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
+                   rstd.data_ptr(), int(relu), int(training), float(dropout_p), int(seed), dx.data_ptr(), dw.data_ptr(),
+                   db.data_ptr(), _p(ws), nb, _stream())
     else:
         lib().call("gnnx_bn_relu_rows_bwd", dy.data_ptr(), x.data_ptr(), _p(y), rows, buckets.row_node.data_ptr(),
-                   buckets.node_pos.numel(), C, _p(weight), _p(bias), mean.data_ptr(), rstd.data_ptr(), int(relu), dx.data_ptr(),
-                   dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
+                   buckets.node_pos.numel(), C, _p(weight), _p(bias), mean.data_ptr(), rstd.data_ptr(), int(relu),
+                   int(training), float(dropout_p), int(seed), dx.data_ptr(), dw.data_ptr(), db.data_ptr(), _p(ws), nb, _stream())
     return dx, dw, db
 
 

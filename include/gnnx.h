@@ -73,7 +73,9 @@ GNNX_API size_t gnnx_csr_workspace_bytes(int64_t num_nodes, int64_t num_edges);
  *   pos_of_eid[E]                        slot of original edge e in the dst-sorted order
  *   colptr[N+1], csc_pos[E], csc_dst[E]  src-sorted view: dst-sorted slot / destination of
  *                                        each edge, grouped by source (backward scatter)
- *   err_flag[1]                          set to 1 if any endpoint is outside [0,N)        */
+ *   err_flag[1]                          set to 1 if any endpoint is outside [0,N); such edges are
+ *                                        skipped and the unused slot tails [rowptr[N], E) of the
+ *                                        per-slot arrays are zero-filled (nothing is left uninitialised) */
 GNNX_API int gnnx_csr_build_i64(const int64_t* edge_index, int64_t num_nodes, int64_t num_edges,
                        int32_t* rowptr, int32_t* csr_src, int32_t* csr_eid, int32_t* pos_of_eid,
                        int32_t* colptr, int32_t* csc_pos, int32_t* csc_dst, int32_t* err_flag,
@@ -93,13 +95,18 @@ GNNX_API int gnnx_degree_hist(const int32_t* rowptr, int64_t num_nodes, int64_t*
 GNNX_API int gnnx_graph_ptr_from_batch(const int64_t* batch, int64_t num_nodes, int64_t num_graphs,
                               int32_t* graph_ptr, void* stream);
 
-/* Narrow int64 categorical features [rows, K] to uint8 (vocabularies are <= 119). */
-GNNX_API int gnnx_narrow_i64_u8(const int64_t* in, int64_t count, uint8_t* out, void* stream);
+/* Narrow int64 categorical features [rows, cols] to uint8 (vocabularies are <= 119).  limits_host (HOST pointer,
+ * cols <= 16 entries, optional): the vocabulary size of every column -- a value outside [0, limit) (torch's
+ * Embedding raises on those) is written as 0 and raises *err_flag (optional, device int32, only ever set to 1), so
+ * an out-of-vocabulary id can never index past an embedding table. */
+GNNX_API int gnnx_narrow_i64_u8(const int64_t* in, int64_t rows, int32_t cols, const int32_t* limits_host, uint8_t* out,
+                       int32_t* err_flag, void* stream);
 
 /* Bond-type code per dst-sorted slot: code = (a0*6 + a1)*2 + a2 in [0,60) from uint8 [E,3]
- * edge attributes in original edge order and csr_eid. */
+ * edge attributes in original edge order and csr_eid.  Attributes outside the OGB bond vocabularies (5, 6, 2) give
+ * code 0 and raise *err_flag (optional, device int32). */
 GNNX_API int gnnx_edge_codes(const uint8_t* edge_attr_u8, const int32_t* csr_eid, int64_t num_edges,
-                    uint8_t* codes, void* stream);
+                    uint8_t* codes, int32_t* err_flag, void* stream);
 
 /* Device-side block-diagonal collation of G molecules picked from a packed, device-resident
  * store (uint8 features, int16 graph-local endpoints).  graph_ids[G] selects molecules;
@@ -116,13 +123,16 @@ GNNX_API int gnnx_collate_packed(const uint8_t* store_x, const int16_t* store_sr
 /* Replaces ogb AtomEncoder / BondEncoder.forward (models.py:175-176, 205-206):
  * out[r,:] = sum_k table[offset[k] + idx[r,k], :], accumulated in k order.
  * idx is uint8 [rows,K]; table is the row-concatenation of the K embedding weights. */
+/* dropout_p > 0 (training mode): the reference's Dropout(p) in front of the FIRST conv layer (models.py:209) applied
+ * to the freshly summed row -- element (r, c) is kept (and scaled by 1/(1-p)) iff gnnx_dropout_keep_mask's draw for
+ * index r * hidden + c says so; the backward replays the same draw on dout. */
 GNNX_API int gnnx_embed_sum_fwd(const uint8_t* idx, int64_t rows, int32_t num_features, const int32_t* offsets,
-                       const float* table, int32_t hidden, float* out, void* stream);
+                       const float* table, int32_t hidden, float dropout_p, int64_t seed, float* out, void* stream);
 GNNX_API size_t gnnx_embed_sum_bwd_workspace_bytes(int64_t rows, int32_t table_rows, int32_t hidden);
 /* dtable[table_rows, hidden] = sum over rows (deterministic, atomic-free). */
 GNNX_API int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t num_features, const int32_t* offsets,
-                       int32_t table_rows, const float* dout, int32_t hidden, float* dtable,
-                       void* workspace, size_t workspace_bytes, void* stream);
+                       int32_t table_rows, const float* dout, int32_t hidden, float dropout_p, int64_t seed,
+                       float* dtable, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ dense transforms (d) */
 /* C[M,N] = epilogue( op(A) * op(B) ) for the Linear layers inside PNAConv / GATv2Conv / the
@@ -293,32 +303,42 @@ GNNX_API int gnnx_gemm_grouped_dw(const float* A, int64_t lda, const float* B, i
 GNNX_API int gnnx_relu_bwd(const float* dy, const float* y, int64_t count, float* dx, void* stream);
 
 /* ------------------------------------------------------------------ batch norm + ReLU (K8) */
-/* Replaces torch_geometric.nn.BatchNorm / BatchNorm1d + F.relu (models.py:184, 212-213).
+/* Replaces torch_geometric.nn.BatchNorm / BatchNorm1d + F.relu (models.py:184, 212-213) and the Dropout(p) the
+ * NEXT layer applies to this output (models.py:177, 209).
  * Training: batch statistics over all rows (biased variance to normalise), running stats
  * updated with the unbiased variance and `momentum`; eval: running stats.
- * save_mean / save_rstd [C] are written in training mode for the backward. */
+ * save_mean / save_rstd [C] are written in both modes (eval: the running statistics) for the backward.
+ * dropout_p > 0: y = dropout(relu(bn(x))) in the same pass -- element (r, c) of the node-order output is kept (and
+ * scaled by 1/(1-p)) iff the counter-based draw for (seed, r * channels + c) says so (gnnx_dropout_keep_mask writes
+ * the same draw out); no mask tensor exists, the backward replays the draw. */
 GNNX_API size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t channels);
 GNNX_API int gnnx_bn_relu_fwd(const float* x, int64_t rows, int32_t channels, const float* weight,
                      const float* bias, float* running_mean, float* running_var, int32_t training,
-                     float momentum, float eps, int32_t relu, float* y, float* save_mean,
-                     float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
+                     float momentum, float eps, int32_t relu, float dropout_p, int64_t seed, float* y,
+                     float* save_mean, float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
 /* dx, dweight, dbias from dy and the input x.  The ReLU mask is re-derived from x, weight and bias with the forward's
- * operation sequence (sign of y, bit for bit); y is accepted for interface stability and NOT read (may be null). */
+ * operation sequence (sign of y, bit for bit); y is accepted for interface stability and NOT read (may be null).
+ * training = 0: the eval-mode backward (save_mean / save_rstd are constants: dx = w rstd dy', no batch coupling).
+ * dropout_p / seed: as passed to the forward. */
 GNNX_API int gnnx_bn_relu_bwd(const float* dy, const float* x, const float* y, int64_t rows, int32_t channels,
                      const float* weight, const float* bias, const float* save_mean, const float* save_rstd,
-                     int32_t relu, float* dx, float* dweight, float* dbias, void* workspace,
-                     size_t workspace_bytes, void* stream);
+                     int32_t relu, int32_t training, float dropout_p, int64_t seed, float* dx, float* dweight,
+                     float* dbias, void* workspace, size_t workspace_bytes, void* stream);
+/* keep[i] = 1 iff the node-feature dropout draw for (seed, i) keeps element i (tests replay it on the oracle). */
+GNNX_API int gnnx_dropout_keep_mask(float dropout_p, int64_t seed, int64_t count, uint8_t* keep, void* stream);
 /* The same batch norm fed by a PNAConv output left in DEGREE-BUCKET order (gnnx_degree_buckets): x / dx are
  * [rows = bucket capacity, C] with padding rows where row_node[r] < 0 (excluded from the statistics, zero gradient),
  * y / dy are [num_nodes, C] in node order -- the move back to node order costs no extra pass. */
 GNNX_API int gnnx_bn_relu_rows_fwd(const float* x, int64_t rows, const int32_t* row_node, int64_t num_nodes, int32_t channels,
                           const float* weight, const float* bias, float* running_mean, float* running_var,
-                          int32_t training, float momentum, float eps, int32_t relu, float* y, float* save_mean,
-                          float* save_rstd, void* workspace, size_t workspace_bytes, void* stream);
+                          int32_t training, float momentum, float eps, int32_t relu, float dropout_p, int64_t seed,
+                          float* y, float* save_mean, float* save_rstd, void* workspace, size_t workspace_bytes,
+                          void* stream);
 GNNX_API int gnnx_bn_relu_rows_bwd(const float* dy, const float* x, const float* y, int64_t rows, const int32_t* row_node,
                           int64_t num_nodes, int32_t channels, const float* weight, const float* bias,
-                          const float* save_mean, const float* save_rstd, int32_t relu, float* dx, float* dweight, float* dbias,
-                          void* workspace, size_t workspace_bytes, void* stream);
+                          const float* save_mean, const float* save_rstd, int32_t relu, int32_t training, float dropout_p,
+                          int64_t seed, float* dx, float* dweight, float* dbias, void* workspace, size_t workspace_bytes,
+                          void* stream);
 
 /* ------------------------------------------------------------------ graph pooling (K9) */
 /* Replaces aggr.{Sum,Mean,Max}Aggregation()(x, batch) (models.py:218-219, 587-595) over the

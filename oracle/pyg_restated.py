@@ -223,8 +223,9 @@ def var_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
 # within the relative band STD_BAND of the threshold -- those would be genuine disagreements, not rounding.
 STD_MASKS = None
 STD_BAND = 2e-3
-STD_BAND_ABS = 0.0        # extra allowance proportional to E[x^2] (reduced-precision tiers: var = E[x^2] - E[x]^2 inherits
-                          # the ABSOLUTE error of its two terms, which a tf32 product puts at ~1e-3 E[x^2], far above 1e-5)
+STD_BAND_ABS = 0.0        # reduced-precision tiers: a tf32 product leaves every message entry with an ABSOLUTE error
+                          # delta = STD_BAND_ABS * rms(messages) (relative to the row scale, not to the entry), and
+                          # var = E[x^2] - E[x]^2 then moves by up to 2 sqrt(E[x^2]) delta + delta^2 -- far above 1e-5
 STD_BAND_VIOLATIONS = []
 
 
@@ -241,7 +242,8 @@ def std_aggregation(x: Tensor, index: Tensor, dim_size: int) -> Tensor:
         rel = (var.detach()[differ].double() - 1e-5).abs()
         if STD_BAND_ABS > 0.0:
             ex2 = scatter((x * x).detach(), index, dim_size, "mean")[differ].double()
-            rel = (rel - STD_BAND_ABS * ex2).clamp(min=0.0)
+            delta = STD_BAND_ABS * float(x.detach().double().pow(2).mean().sqrt())
+            rel = (rel - (2.0 * ex2.sqrt() * delta + delta * delta)).clamp(min=0.0)
         rel = rel / 1e-5
         STD_BAND_VIOLATIONS.append((int(differ.sum()), int((rel > STD_BAND).sum()), float(rel.max())))
     return var.clamp(min=1e-12).sqrt().masked_fill(forced, 0.0)
@@ -580,13 +582,30 @@ RELU_BAND_VIOLATIONS = []
 def _relu_after_bn(y: Tensor) -> Tensor:
     if not RELU_MASKS:
         return F.relu(y)
-    forced = RELU_MASKS.pop(0).to(y.device).view_as(y)
+    forced = RELU_MASKS.pop(0)
+    if isinstance(forced, tuple):                       # (mask, valid): entries with valid == False keep the oracle's own sign
+        forced, valid = forced
+        forced = torch.where(valid.to(y.device).view_as(y), forced.to(y.device).view_as(y), y > 0)
+    forced = forced.to(y.device).view_as(y)
     differ = forced != (y > 0)
     if bool(differ.any()):
         gap = y.detach()[differ].abs().double()
         scale = float(y.detach().abs().max())
         RELU_BAND_VIOLATIONS.append((int(differ.sum()), int((gap > RELU_BAND * scale).sum()), float(gap.max())))
     return torch.where(forced, y, torch.zeros_like(y))
+
+
+# Test hook for the node-feature Dropout in front of every conv (models.py:177, 209): RNG streams of two
+# implementations cannot match, so when NODE_DROPOUT_KEEP is a list, successive layers take their keep-mask ([N, H]
+# bool) from it -- the draw of the implementation under test -- instead of drawing their own.
+NODE_DROPOUT_KEEP = None
+
+
+def _node_dropout(mod: Dropout, x: Tensor) -> Tensor:
+    if NODE_DROPOUT_KEEP is None or not mod.training or mod.p == 0.0:
+        return mod(x)
+    keep = NODE_DROPOUT_KEEP.pop(0).to(x.device).view_as(x)
+    return torch.where(keep, x / (1.0 - mod.p), torch.zeros_like(x))
 
 
 class GNNePCSAFT(Module):
@@ -617,7 +636,7 @@ class GNNePCSAFT(Module):
         x = self.node_embed(x)
         edge_attr = self.edge_embed(edge_attr)
         for conv, batch_norm in zip(self.convs, self.batch_norms):
-            x = self.dropout(x)
+            x = _node_dropout(self.dropout, x)
             x = _relu_after_bn(batch_norm(conv(x=x, edge_index=edge_index, edge_attr=edge_attr)))
         if batch is not None:
             x = self.global_pool(x, batch)

@@ -136,3 +136,72 @@ def test_host_batch_prefetcher_prepare_next_builds_the_index_ahead():
     assert len(seen) == 2
     with pytest.raises(StopIteration):
         next(feed)
+
+
+# ------------------------------------------------------------------ invalid inputs (graph.py:66)
+def _small_model():
+    import copy
+    import gnnepcsaft_b200 as G
+    from tests.util import PNA_CFG1, deg_hist
+    graphs, b = make_batch(8, seed=11)
+    cfg = dict(PNA_CFG1, deg=deg_hist(graphs))
+    torch.manual_seed(0)
+    return G.GNNePCSAFT(copy.deepcopy(cfg)).to(DEV).eval(), b
+
+
+@pytest.mark.parametrize("what", ["edge", "atom", "bond"])
+def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what):
+    """PyG raises on an edge_index entry >= num_nodes and torch.nn.Embedding on an id outside its vocabulary.  Here the
+    reference-signature forward() raises IndexError on the host read it pays anyway (int(batch[-1]) + 1); with
+    num_graphs= given (no sync) the kernels skip / zero the offending entries -- finite output, nothing uninitialised
+    is ever used as an index -- and Batch.validate() / GraphIndex.check() report it."""
+    from gnnepcsaft_b200 import graph as gr
+    model, b = _small_model()
+    x, ei, ea, bt = (b[k].clone() for k in ("x", "edge_index", "edge_attr", "batch"))
+    G = int(bt[-1]) + 1
+    if what == "edge":
+        ei[1, 7] = x.shape[0] + 5
+        ei[0, 3] = -2
+    elif what == "atom":
+        x[4, 0] = 119                                     # atomic-number vocabulary is 0..118
+        x[9, 8] = 7
+    else:
+        ea[5, 1] = 6                                      # bond stereo vocabulary is 0..5
+    args = [t.to(DEV) for t in (x, ei, ea, bt)]
+    with torch.no_grad():
+        with pytest.raises(IndexError):
+            model(*args)                                  # reference signature: the one host read checks the flags
+        gr._INDEX_CACHE.clear()
+        out = model(*args, num_graphs=G)                  # sync-free path: memory-safe, flags left on the device
+        assert out.shape == (G, 3) and bool(torch.isfinite(out).all())
+        bb = gr.batch_from_reference_tensors(*args, num_graphs=G)
+        with pytest.raises(IndexError):
+            bb.validate()
+        if what == "edge":
+            g = bb.index
+            E = ei.shape[1]
+            nvalid = int(g.rowptr[-1])
+            assert nvalid == E - 2                        # two edges skipped; the slot tails are zero-filled
+            for t in (g.csr_src, g.csr_eid, g.csc_pos, g.csc_dst):
+                assert bool((t[nvalid:] == 0).all()) and int(t.min()) >= 0 and int(t.max()) < max(E, x.shape[0])
+    # valid input: no flag, no exception
+    good = [b[k].to(DEV) for k in ("x", "edge_index", "edge_attr", "batch")]
+    gr._INDEX_CACHE.clear()
+    with torch.no_grad():
+        model(*good)
+        gr.batch_from_reference_tensors(*good, num_graphs=G).validate()
+
+
+def test_packed_store_is_validated_on_the_host():
+    from gnnepcsaft_b200 import graph as gr, synth
+    graphs, _ = make_batch(6, seed=12)
+    p = synth.pack(graphs)
+    gr.DeviceGraphStore(p, DEV)
+    bad = synth.pack(graphs)
+    bad.x[3, 0] = 200
+    with pytest.raises(IndexError):
+        gr.DeviceGraphStore(bad, DEV)
+    bad = synth.pack(graphs)
+    bad.dst[2] = 120
+    with pytest.raises(IndexError):
+        gr.DeviceGraphStore(bad, DEV)

@@ -88,7 +88,7 @@ def test_dw_layout(Mo, No, R):
     dy, x = torch.randn(R, Mo), torch.randn(R, No)
     out = _tc_taken(lambda: ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True))
     _check(out, dy.double().t(), x.double(), what=f"TN {Mo}x{No}x{R}")
-    again = ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True)
+    again = _tc_taken(lambda: ops.gemm(dy.to(DEV), x.to(DEV), trans_a=True))
     assert torch.equal(out, again), "dW must be deterministic (ordered split reduction, no atomics)"
 
 

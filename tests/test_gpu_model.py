@@ -334,3 +334,133 @@ def test_side_stream_and_cached_prep_are_bit_identical(monkeypatch):
         assert torch.equal(e2, e3) and not torch.equal(e0, e2)
     finally:
         ops.set_matmul_precision("fp32")
+
+
+# ------------------------------------------------------------------ node-feature dropout (a7) and eval-mode BatchNorm gradients
+@pytest.mark.parametrize("cfg,target,p", [(dict(PNA_CFG1, dropout=0.25), "para", 0.25),
+                                          (dict(PNA_CFG1, dropout=0.1, towers=4, pre_layers=1, post_layers=2), "para", 0.1)])
+def test_node_feature_dropout_is_fused_and_replayable(cfg, target, p):
+    """``Dropout(p=config["dropout"])`` in front of every conv (reference models.py:177, 209; p = 0.1 / 0.25 in
+    configs/gatv2_msigmae_3.py:41, pna_msigmae_7.py:40) runs inside the kernel that produces the conv's input (embedding sum,
+    BatchNorm+ReLU apply) with a counter-based draw and no mask tensor.  The draw is replayed on the oracle
+    (ops.dropout_keep_mask -> O.NODE_DROPOUT_KEEP), then forward, loss and every gradient must meet the fp32 tier's
+    bounds; the draw is repeatable under torch.manual_seed, differs between calls, drops ~p, and eval mode drops nothing."""
+    from gnnepcsaft_b200 import models
+    graphs, b = make_batch(32, seed=1234)
+    mo, mp = _model_pair(cfg, graphs)
+    mo64 = copy.deepcopy(mo).double()
+    mo.train(); mp.train(); mo64.train()
+    args = [b[k].to(DEV) for k in ("x", "edge_index", "edge_attr", "batch")]
+    N, H, L = b["x"].shape[0], cfg["hidden_dim"], cfg["propagation_depth"]
+    pna_fn.CAPTURE_AGG, models.NODE_DROPOUT_SEEDS = [], []
+    relu_out = []
+    hooks = [bn.register_forward_hook(lambda _m, _i, out: relu_out.append(out.detach())) for bn in mp.batch_norms]
+    try:
+        torch.manual_seed(5)
+        pp = mp(*args)
+        aggs = list(pna_fn.CAPTURE_AGG)
+        (p_used, seeds), = models.NODE_DROPOUT_SEEDS
+        torch.manual_seed(5)
+        with torch.no_grad():
+            again = mp(*args)
+            other = mp(*args)
+    finally:
+        pna_fn.CAPTURE_AGG = models.NODE_DROPOUT_SEEDS = None
+        for h in hooks:
+            h.remove()
+    assert p_used == p and len(seeds) == L and len(set(seeds)) == L
+    assert torch.equal(pp.detach(), again), "same torch seed must give the same draw"
+    assert not torch.equal(pp.detach(), other), "successive calls must draw different masks"
+    keeps = [ops.dropout_keep_mask(p, s, (N, H), DEV) for s in seeds]
+    for k in keeps:
+        assert abs(1.0 - float(k.float().mean()) - p) < 0.02, "dropped fraction far from p"
+    for l in range(L - 1):                                        # a dropped entry of a layer output is exactly zero
+        assert bool((relu_out[l][~keeps[l + 1]] == 0).all())
+    valid = [keeps[l + 1] if l + 1 < L else None for l in range(L)]
+    try:
+        O.NODE_DROPOUT_KEEP = [k.cpu() for k in keeps]
+        with branches_from(aggs, cfg["towers"], relu_out[:L], relu_valid=valid):
+            po = mo(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
+        O.NODE_DROPOUT_KEEP = [k.cpu() for k in keeps]
+        with branches_from(aggs, cfg["towers"], relu_out[:L], relu_valid=valid):
+            p64 = mo64(b["x"], b["edge_index"], b["edge_attr"], b["batch"])
+    finally:
+        O.NODE_DROPOUT_KEEP = None
+    assert_as_accurate(pp, po, p64, "model fwd (dropout)")
+    assert_close(pp, po, 1e-4, 1e-6, "model fwd (dropout)")
+    lo, _ = O.training_loss(po, b[target])
+    l64, _ = O.training_loss(p64, b[target].double())
+    lo.backward(); l64.backward()
+    out2, dpred = ops.relhuber_fwd_bwd(pp.detach().contiguous(), b[target].to(DEV))
+    assert_close(out2[0], lo, 1e-5, 1e-9, "loss (dropout)")
+    pp.backward(dpred)
+    _grads_close(mp, mo, mo64, 1e-4, factor=8.0)
+    mp.eval()
+    with torch.no_grad():
+        assert torch.equal(mp(*args), mp(*args)), "eval mode must not drop anything"
+
+
+def test_batch_norm_backward_in_eval_mode_and_cumulative_momentum():
+    """gradients must flow through model.eval() (frozen statistics: fine-tuning, saliency) -- dx = dy w rstd
+    under the ReLU mask, dw / db as column sums -- and momentum=None is torch's cumulative average, not 0.1."""
+    torch.manual_seed(3)
+    C, N = 64, 500
+    ref = torch.nn.BatchNorm1d(C)
+    ref.running_mean.uniform_(-1, 1); ref.running_var.uniform_(0.5, 2.0)
+    ref.weight.data.uniform_(0.5, 1.5); ref.bias.data.uniform_(-0.5, 0.5)
+    mod = gnn.BatchNorm(C).to(DEV)
+    mod.module.load_state_dict(ref.state_dict())
+    ref.eval(); mod.eval()
+    x = torch.randn(N, C)
+    xo = x.clone().requires_grad_(True)
+    xp = x.clone().to(DEV).requires_grad_(True)
+    w = torch.randn(N, C)
+    (torch.relu(ref(xo)) * w).sum().backward()
+    (mod(xp, relu=True) * w.to(DEV)).sum().backward()
+    assert_close(xp.grad, xo.grad, 1e-5, 1e-6, "eval-mode dx")
+    assert_close(mod.module.weight.grad, ref.weight.grad, 1e-5, 1e-5, "eval-mode dweight")
+    assert_close(mod.module.bias.grad, ref.bias.grad, 1e-5, 1e-5, "eval-mode dbias")
+    # momentum=None: running stats = plain average over the batches seen
+    r2 = torch.nn.BatchNorm1d(C, momentum=None).train()
+    m2 = gnn.BatchNorm(C, momentum=None).to(DEV).train()
+    for i in range(3):
+        xb = torch.randn(200, C) * (i + 1) + i
+        r2(xb); m2(xb.to(DEV))
+    assert_close(m2.module.running_mean, r2.running_mean, 1e-5, 1e-6, "cumulative running_mean")
+    assert_close(m2.module.running_var, r2.running_var, 1e-5, 1e-6, "cumulative running_var")
+    assert int(m2.module.num_batches_tracked) == 3
+
+
+@pytest.mark.parametrize("bucketed", [False, True])
+def test_bn_relu_dropout_kernel_matches_a_replayed_mask(bucketed):
+    """The fused BatchNorm+ReLU+Dropout apply and its backward against torch ops fed with the kernel's own draw; the
+    bucket-ordered variant (PNAConv(bucket_out=True) output) must use the NODE-order element index for its draw."""
+    torch.manual_seed(11)
+    graphs, b = make_batch(24, seed=8)
+    N, C, p, seed = b["x"].shape[0], 64, 0.3, 123456789
+    g = graph.GraphIndex.build(b["edge_index"].to(DEV), N)
+    bn = torch.nn.BatchNorm1d(C).to(DEV).train()
+    bn.weight.data.uniform_(0.5, 1.5); bn.bias.data.uniform_(-0.5, 0.5)
+    x = torch.randn(N, C, device=DEV)
+    keep = ops.dropout_keep_mask(p, seed, (N, C), DEV)
+    xr = x.clone().requires_grad_(True)
+    ref_bn = copy.deepcopy(bn)
+    yr = torch.where(keep, torch.relu(ref_bn(xr)) / (1 - p), torch.zeros_like(x))
+    w = torch.randn(N, C, device=DEV)
+    (yr * w).sum().backward()
+    from gnnepcsaft_b200 import functional as Fn
+    if bucketed:
+        bk = g.degree_buckets()
+        xb = torch.zeros((bk.capacity, C), device=DEV)
+        xb[bk.node_pos.long()] = x
+        xin = xb.requires_grad_(True)
+        y = Fn.batch_norm(xin, bn, relu=True, buckets=bk, dropout_p=p, seed=seed)
+    else:
+        xin = x.clone().requires_grad_(True)
+        y = Fn.batch_norm(xin, bn, relu=True, dropout_p=p, seed=seed)
+    assert_close(y, yr, 1e-5, 1e-6, "bn+relu+dropout fwd")
+    (y * w).sum().backward()
+    dx = xin.grad[bk.node_pos.long()] if bucketed else xin.grad
+    assert_close(dx, xr.grad, 1e-4, 1e-6, "bn+relu+dropout dx")
+    assert_close(bn.weight.grad, ref_bn.weight.grad, 1e-4, 1e-5, "dweight")
+    assert_close(bn.bias.grad, ref_bn.bias.grad, 1e-4, 1e-5, "dbias")

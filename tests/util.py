@@ -70,7 +70,7 @@ class branches_from:
     rounding band of its discontinuity (oracle/pyg_restated.py: STD_MASKS, EXTREMUM_SELECT).  No entry is dropped
     from the comparison.  Use one instance per oracle forward pass."""
 
-    def __init__(self, captured, towers, relu_outputs=(), inner_relus=False, head_outputs=(), relu_band=None):
+    def __init__(self, captured, towers, relu_outputs=(), inner_relus=False, head_outputs=(), relu_band=None, relu_valid=None):
         """``relu_outputs``: the CUDA model's per-layer BatchNorm+ReLU outputs (their > 0 pattern is forced onto the
         oracle's ReLU behind each BatchNorm, oracle/pyg_restated.py: RELU_MASKS).  ``inner_relus``: also force the ReLUs
         inside every PNAConv's pre_nn / post_nn chains (captured ``pre_relu`` / ``post_relu``) and, with ``head_outputs``
@@ -79,6 +79,8 @@ class branches_from:
         to max|activation| (default: the oracle's fp32 bands)."""
         self.std_masks, self.selects = [], []
         self.relu_masks = [(y.detach() > 0).cpu() for y in relu_outputs]
+        if relu_valid is not None:      # node dropout fused behind the ReLU: a dropped entry's sign is unknown -> oracle's own
+            self.relu_masks = [m if v is None else (m, v.cpu()) for m, v in zip(self.relu_masks, relu_valid)]
         self.inner_masks = []
         self.relu_band = relu_band
         self.max_relu_flips = 8
@@ -114,7 +116,7 @@ class branches_from:
     def __enter__(self):
         O.STD_MASKS = [m.clone() for m in self.std_masks]
         O.EXTREMUM_SELECT = [m.clone() for m in self.selects]
-        O.RELU_MASKS = [m.clone() for m in self.relu_masks] if self.relu_masks else None
+        O.RELU_MASKS = list(self.relu_masks) if self.relu_masks else None
         O.INNER_RELU_MASKS = [m.clone() for m in self.inner_masks] if self.inner_masks else None
         O.STD_BAND_VIOLATIONS.clear()
         O.EXTREMUM_BAND_VIOLATIONS.clear()
@@ -123,7 +125,7 @@ class branches_from:
         self._bands = (O.RELU_BAND, O.INNER_RELU_BAND, O.STD_BAND_ABS, O.EXTREMUM_BAND)
         if self.relu_band is not None:                   # tf32 tier: every band widens to the tier's rounding
             O.RELU_BAND = O.INNER_RELU_BAND = self.relu_band
-            O.STD_BAND_ABS = self.relu_band              # |var - 1e-5| <= STD_BAND * 1e-5 + band * E[x^2]
+            O.STD_BAND_ABS = self.relu_band              # per-entry message error delta = band * rms(messages)
             O.EXTREMUM_BAND = max(O.EXTREMUM_BAND, self.relu_band)
         return self
 
