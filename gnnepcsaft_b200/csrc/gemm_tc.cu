@@ -727,20 +727,28 @@ static RedPlan red_plan(int64_t Mo, int64_t No, int64_t R) {
 using namespace tc;
 
 // One zero-initialised arrival counter per (device, stream): kernels of a stream run in order and each leaves it at 0.
+// The counters of a device live in ONE block allocated (and zeroed) on first use, so that handing a counter to a new
+// stream -- e.g. the capture stream of a CUDA graph -- involves no CUDA call at all (cudaMalloc / cudaMemset are not
+// allowed while a stream is being captured; the first tensor-core product of a process must therefore run eagerly,
+// which the usual warm-up step before a capture does anyway).
 static int* stream_ticket(cudaStream_t stream) {
+    constexpr int kSlots = 1024, kStride = 64;             // ints: 256 B apart
+    struct Pool { int* base = nullptr; int next = 0; std::map<cudaStream_t, int> slot; };
     static std::mutex mu;
-    static std::map<std::pair<int, cudaStream_t>, int*> tickets;
+    static std::map<int, Pool> pools;
     std::lock_guard<std::mutex> lock(mu);
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-    const std::pair<int, cudaStream_t> st(dev, stream);
-    auto it = tickets.find(st);
-    if (it != tickets.end()) return it->second;
-    int* p = nullptr;
-    if (cudaMalloc(&p, 256) != cudaSuccess) return nullptr;
-    if (cudaMemset(p, 0, 256) != cudaSuccess) return nullptr;
-    tickets[st] = p;
-    return p;
+    Pool& p = pools[dev];
+    if (!p.base) {
+        int* q = nullptr;
+        if (cudaMalloc(&q, (size_t)kSlots * kStride * sizeof(int)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        if (cudaMemset(q, 0, (size_t)kSlots * kStride * sizeof(int)) != cudaSuccess) { cudaGetLastError(); cudaFree(q); return nullptr; }
+        p.base = q;
+    }
+    auto it = p.slot.find(stream);
+    if (it == p.slot.end()) it = p.slot.emplace(stream, p.next++ % kSlots).first;     // > 1024 live streams would share
+    return p.base + (size_t)it->second * kStride;
 }
 
 bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,

@@ -30,6 +30,21 @@ CAPTURE_HEAD = None
 NODE_DROPOUT_SEEDS = None
 
 
+_FORCE_CUSTOM_OPS = False
+
+
+def use_custom_ops(flag: bool) -> None:
+    """Route ``GNNePCSAFT.forward`` through the ``torch.ops.gnnx.*`` custom-op face (``torch_ops.py``) in eager mode too.
+    Tracing (``torch.export``, FakeTensor inputs) always takes it."""
+    global _FORCE_CUSTOM_OPS
+    _FORCE_CUSTOM_OPS = bool(flag)
+
+
+def _traced(x: Tensor) -> bool:
+    from torch._subclasses.fake_tensor import is_fake
+    return _FORCE_CUSTOM_OPS or is_fake(x) or torch.compiler.is_compiling() or torch.compiler.is_exporting()
+
+
 def get_conv(config: dict) -> Module:
     """Conv factory, reference models.py:441-584 (the convs any file in ``configs/`` selects)."""
     aggregators = ["mean", "min", "max", "std"]
@@ -98,9 +113,75 @@ class GNNePCSAFT(Module):
         """Forward pass of the model (same inputs / output as the reference's ``forward``)."""
         if not x.is_cuda:
             raise RuntimeError("GNNePCSAFT (gnnx): inputs must be CUDA tensors; there is no CPU fallback")
+        if _traced(x):
+            return self.forward_custom_ops(x, edge_index, edge_attr, batch, num_graphs)
         b = batch_from_reference_tensors(x.contiguous(), edge_index.contiguous(), edge_attr.contiguous(), batch,
                                          num_graphs)
         return self.forward_batch(b)
+
+    # -- the torch.library face: every step is a torch.ops.gnnx.* custom op or a plain ATen op ----------------
+    def forward_custom_ops(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Union[Tensor, None],
+                           num_graphs: Optional[int] = None) -> Tensor:
+        """Same result as ``forward`` through ``torch.ops.gnnx.*`` only (``torch_ops.py``): no host read, no Python
+        object crosses an op boundary, shapes may be symbolic -- what ``torch.export.export(model, (x, edge_index,
+        edge_attr, None), dynamic_shapes=...)`` (reference demo/utils.py:890-915) traces.  Differentiable."""
+        from . import torch_ops  # noqa: F401  (registers the ops)
+        T = torch.ops.gnnx
+        N = x.shape[0]
+        index = T.csr_build(edge_index, N)
+        status = index[7]
+        x8 = T.narrow_u8(x, list(gnn.ATOM_FEATURE_DIMS), status, ops.ST_ATOM)
+        ea8 = T.narrow_u8(edge_attr, list(gnn.BOND_FEATURE_DIMS), status, ops.ST_BOND)
+        codes = T.edge_codes(ea8, index[2], status)
+        table = self.edge_embed.table60()
+        p = self.dropout.p if self.training else 0.0
+        L = len(self.convs)
+        seeds = [ops.dropout_seed() if p > 0.0 else 0 for _ in range(L)]
+        h = T.embed_sum(self.node_embed.table(), x8, self.node_embed._offsets, p, seeds[0] if L else 0)
+        for l, (conv, bn) in enumerate(zip(self.convs, self.batch_norms)):
+            pn, sn = (p, seeds[l + 1]) if l + 1 < L else (0.0, 0)
+            if isinstance(conv, gnn.PNAConv):
+                h = T.pna_conv(h, table, codes, index, conv._flat_params(), conv.towers, conv.pre_layers, conv.post_layers,
+                               conv.aggr_module.avg_deg_log_value(), -1)
+            elif isinstance(conv, gnn.GATv2Conv):
+                pa = conv.dropout if self.training else 0.0
+                h = T.gatv2_conv(h, table, codes, index, [conv.lin_l.weight, conv.lin_l.bias, conv.lin_r.weight, conv.lin_r.bias,
+                                                          conv.lin_edge.weight, conv.att, conv.bias], conv.heads,
+                                 conv.out_channels, conv.negative_slope, conv.add_self_loops, pa,
+                                 ops.dropout_seed() if pa > 0.0 else 0)
+            else:
+                pa = conv.dropout if self.training else 0.0
+                h = T.transformer_conv(h, table, codes, index, [conv.lin_query.weight, conv.lin_query.bias, conv.lin_key.weight,
+                                                                conv.lin_key.bias, conv.lin_value.weight, conv.lin_value.bias,
+                                                                conv.lin_edge.weight, conv.lin_skip.weight, conv.lin_skip.bias],
+                                       conv.heads, conv.out_channels, pa, ops.dropout_seed() if pa > 0.0 else 0)
+            h = self._bn_op(h, bn.module, pn, sn)
+        if batch is not None:
+            if num_graphs is None:
+                raise ValueError("GNNePCSAFT (custom-op face): pass num_graphs= together with a batch vector (reading "
+                                 "int(batch[-1]) + 1 back is a host sync a traced graph cannot contain)")
+            ptr = T.graph_ptr(batch, num_graphs)
+        else:
+            ptr = (torch.arange(2, device=x.device) * N).to(torch.int32)          # [0, N]: one graph
+        h = T.segment_pool(h, ptr, ops.POOL_MODES[self.global_pool_type])
+        m = self.mlp
+        h = self._bn_op(T.linear(h, m[0].weight, m[0].bias, False), m[1], 0.0, 0)
+        h = self._bn_op(T.linear(h, m[3].weight, m[3].bias, False), m[4], 0.0, 0)
+        return T.linear(h, m[6].weight, m[6].bias, False)
+
+    @staticmethod
+    def _bn_op(h: Tensor, bn: BatchNorm1d, dropout_p: float, seed: int) -> Tensor:
+        training = bn.training or not bn.track_running_stats
+        if training and bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+        momentum = 0.1 if bn.momentum is None else bn.momentum
+        out = torch.ops.gnnx.bn_relu(h, bn.weight, bn.bias, bn.running_mean, bn.running_var, training, momentum, bn.eps,
+                                     True, dropout_p, seed)
+        if training and bn.track_running_stats:
+            with torch.no_grad():
+                bn.running_mean.copy_(out[3])
+                bn.running_var.copy_(out[4])
+        return out[0]
 
     # -- fast path: everything prebuilt on the device --------------------------------------
     def forward_batch(self, b: Batch) -> Tensor:

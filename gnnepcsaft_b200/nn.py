@@ -82,6 +82,15 @@ class BondEncoder(_FeatureEncoder):
             sel[code, 5 + a1] = 1.0
             sel[code, 11 + a2] = 1.0
         self.register_buffer("_selector", sel, persistent=False)
+        codes = torch.arange(NUM_BOND_CODES)
+        self.register_buffer("_code_features", torch.stack([codes // 12, (codes // 2) % 6, codes % 2], 1), persistent=False)
+
+    def table60(self) -> Tensor:
+        """The 60-row table of every bond-feature combination with plain ATen ops (traceable: the custom-op face);
+        the same sums in the same order as ``forward_table``'s selector product."""
+        e = self.bond_embedding_list
+        f = self._code_features
+        return (e[0].weight[f[:, 0]] + e[1].weight[f[:, 1]]) + e[2].weight[f[:, 2]]
 
     def forward_table(self, codes: Tensor) -> EdgeTable:
         """Factored output: the 60-row table of every bond-feature combination + per-slot codes."""
@@ -173,10 +182,21 @@ class DegreeScalerAggregation(Module):
         self._cache = None
 
     def avg_deg_log_value(self) -> float:
+        from torch._subclasses.fake_tensor import is_fake
+        if is_fake(self.avg_deg_log) or torch.compiler.is_compiling():
+            # traced / exported: the buffer is a FakeTensor, its value cannot be read -- use the last value seen eagerly
+            # (refreshed by __init__ and by every load_state_dict), which export bakes in as a constant
+            return self._cache[1] if self._cache is not None else self.init_avg_deg_log
         key = (self.avg_deg_log.data_ptr(), self.avg_deg_log._version)
         if self._cache is None or self._cache[0] != key:
             self._cache = (key, float(self.avg_deg_log.item()))      # one sync per (re)load, not per step
         return self._cache[1]
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        super()._load_from_state_dict(*args, **kwargs)
+        self._cache = None
+        if not self.avg_deg_log.is_meta:
+            self.avg_deg_log_value()                                  # refresh the host copy while the value is readable
 
 
 def _resolve_edges(edge_attr, edge_dim: int, g: GraphIndex, who: str):

@@ -1,0 +1,142 @@
+"""GPU side of the custom-op face: the exported program computes what the eager model computes (on molecules of other
+sizes than the one it was traced with), the two faces agree forward and backward, and a whole training step captures
+into a CUDA graph and replays bit-identically."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+from torch.export import Dim
+
+import gnnepcsaft_b200 as G
+from gnnepcsaft_b200 import graph, models, ops, synth
+from gnnepcsaft_b200.train import Trainer
+from tests.util import GAT_CFG_SMALL, PNA_CFG1, assert_close, deg_hist, make_batch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+DYN = {"x": (Dim.AUTO, 9), "edge_index": (2, Dim.AUTO), "edge_attr": (Dim.AUTO, 3), "batch": None}
+CFGS = [PNA_CFG1, GAT_CFG_SMALL, dict(GAT_CFG_SMALL, conv="Transformer", num_para=3)]
+
+
+@pytest.fixture(autouse=True)
+def _precision():
+    torch.set_float32_matmul_precision("highest")
+    ops.set_matmul_precision("fp32")
+    torch.manual_seed(0)
+    yield
+    models.use_custom_ops(False)
+
+
+def _mol(g):
+    t = torch.from_numpy
+    return t(g.x).to(DEV), t(g.edge_index).to(DEV), t(g.edge_attr).to(DEV)
+
+
+@pytest.mark.parametrize("cfg", CFGS, ids=[c["conv"] for c in CFGS])
+def test_exported_program_matches_eager_on_other_molecules(cfg):
+    """``torch.export.export(model, (x, edge_index, edge_attr, None), dynamic_shapes=...)`` exactly as the reference
+    calls it (demo/utils.py:890-915), then the exported module on molecules of OTHER sizes against the eager model
+    (the reference's own check, test_onnx at demo/utils.py:918-972, is np.allclose: rtol 1e-5, atol 1e-8)."""
+    graphs, _ = make_batch(12, seed=21, single_atom_frac=0.0)
+    cfg = dict(cfg, deg=deg_hist(graphs))
+    m = G.GNNePCSAFT(copy.deepcopy(cfg)).to(DEV).eval()
+    x, ei, ea = _mol(graphs[0])
+    ep = torch.export.export(m, (x, ei, ea, None), dynamic_shapes=DYN)
+    mod = ep.module()
+    sizes = set()
+    with torch.no_grad():
+        for g in graphs[1:8]:
+            x, ei, ea = _mol(g)
+            sizes.add((x.shape[0], ei.shape[1]))
+            got = mod(x, ei, ea, None)
+            want = m(x, ei, ea, None)
+            assert got.shape == (1, cfg["num_para"])
+            assert_close(got, want, 1e-5, 1e-6, "exported vs eager")
+    assert len(sizes) >= 3, "the molecules must differ in size for this test to mean anything"
+
+
+@pytest.mark.parametrize("cfg,target", [(PNA_CFG1, "para"), (GAT_CFG_SMALL, "assoc"),
+                                        (dict(GAT_CFG_SMALL, conv="Transformer", num_para=3), "para")],
+                         ids=["PNA", "GATv2", "Transformer"])
+def test_custom_op_face_equals_fused_face_forward_and_backward(cfg, target):
+    """Training step through torch.ops.gnnx.* (register_autograd formulas; conv layers by recomputation) against the
+    fused autograd nodes: same predictions, same gradients for every parameter, same BatchNorm running statistics."""
+    graphs, b = make_batch(32, seed=1234)
+    cfg = dict(cfg, deg=deg_hist(graphs))
+    m1 = G.GNNePCSAFT(copy.deepcopy(cfg)).to(DEV).train()
+    m2 = copy.deepcopy(m1)
+    args = [b[k].to(DEV) for k in ("x", "edge_index", "edge_attr", "batch")]
+    Gn = int(b["batch"][-1]) + 1
+    p1 = m1(*args, num_graphs=Gn)
+    models.use_custom_ops(True)
+    try:
+        p2 = m2(*args, num_graphs=Gn)
+    finally:
+        models.use_custom_ops(False)
+    assert_close(p2, p1, 1e-5, 1e-6, "custom-op face fwd")
+    w = torch.randn_like(p1)
+    (p1 * w).sum().backward()
+    (p2 * w).sum().backward()
+    gmax = max(float(p.grad.abs().max()) for p in m1.parameters())
+    for (n, a), (_, c) in zip(m2.named_parameters(), m1.named_parameters()):
+        assert a.grad is not None, n
+        assert_close(a.grad, c.grad, 1e-4, 1e-5 * gmax, f"custom-op face d{n}")
+    for (n, a), (_, c) in zip(m2.named_buffers(), m1.named_buffers()):
+        if "running" in n or "num_batches" in n:
+            assert_close(a.float(), c.float(), 1e-5, 1e-6, f"buffer {n}")
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_training_step_captures_into_a_cuda_graph_and_replays_bit_identically(prec):
+    """One full Trainer.step (forward, loss, backward, gradient packing, AdamW-amsgrad) on a pre-collated batch: the
+    eager step and the replay of its captured graph, both started from the same state, must leave the parameters and
+    the optimizer state bit-identical -- no host sync, no allocation outside the graph pool, no un-capturable call
+    anywhere on the path."""
+    ops.set_matmul_precision(prec)
+    graphs, _ = make_batch(256, seed=77)
+    cfg = dict(PNA_CFG1, hidden_dim=128, deg=deg_hist(graphs))
+    store = graph.DeviceGraphStore(synth.pack(graphs), torch.device(DEV))
+    torch.manual_seed(3)
+    model = G.GNNePCSAFT(copy.deepcopy(cfg)).to(DEV).train()
+    tr = Trainer(model)
+    bt = store.collate(np.arange(256))
+    bt.index.degree_buckets()                                    # per-batch index work happens at collation, not in the step
+    for _ in range(3):                                           # warm-up: lazy one-off allocations, kernel attributes
+        tr.step(bt)
+    torch.cuda.synchronize()
+
+    def state():
+        bufs = [b_.clone() for b_ in model.buffers()]
+        return [tr.flat.data.clone(), tr.exp_avg.clone(), tr.exp_avg_sq.clone(), tr.max_exp_avg_sq.clone()], bufs, tr.step_count
+
+    def restore(s):
+        for dst, src in zip((tr.flat.data, tr.exp_avg, tr.exp_avg_sq, tr.max_exp_avg_sq), s[0]):
+            dst.copy_(src)
+        for b_, src in zip(model.buffers(), s[1]):
+            b_.copy_(src)
+        tr.step_count = s[2]
+
+    s0 = state()
+    out_eager = tr.step(bt).clone()
+    torch.cuda.synchronize()
+    after_eager = state()
+    restore(s0)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            out_graph = tr.step(bt)
+    torch.cuda.current_stream().wait_stream(side)
+    for rep in range(2):
+        restore(s0)
+        g.replay()
+        torch.cuda.synchronize()
+        got = state()
+        assert torch.equal(out_graph, out_eager), f"loss differs on replay {rep}"
+        for a, c in zip(got[0], after_eager[0]):
+            assert torch.equal(a, c), f"parameter / optimizer state differs on replay {rep}"
+        for a, c in zip(got[1], after_eager[1]):
+            assert torch.equal(a, c), f"BatchNorm buffer differs on replay {rep}"
+    ops.set_matmul_precision("fp32")
