@@ -189,6 +189,8 @@ class DegreeScalerAggregation(Module):
             return self._cache[1] if self._cache is not None else self.init_avg_deg_log
         key = (self.avg_deg_log.data_ptr(), self.avg_deg_log._version)
         if self._cache is None or self._cache[0] != key:
+            if self._cache is not None and self.avg_deg_log.is_cuda and torch.cuda.is_current_stream_capturing():
+                return self._cache[1]                                 # a host read would invalidate the capture
             self._cache = (key, float(self.avg_deg_log.item()))      # one sync per (re)load, not per step
         return self._cache[1]
 

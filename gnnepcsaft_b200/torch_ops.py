@@ -363,7 +363,7 @@ def _conv_autograd(op, runner, n_static):
             out = runner(xg, eg, codes, list(index), pg, *ctx.static)
             grads = torch.autograd.grad(out, [xg, eg, *pg], dout.contiguous(), allow_unused=True)
         pgr = [g if g is not None else torch.zeros_like(p) for g, p in zip(grads[2:], params)]
-        return (grads[0], grads[1], None, None, pgr) + (None,) * n_static
+        return (grads[0], grads[1], None, [None] * ctx.n_index, pgr) + (None,) * n_static
 
     op.register_autograd(backward, setup_context=setup)
 

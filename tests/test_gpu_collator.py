@@ -139,12 +139,12 @@ def test_host_batch_prefetcher_prepare_next_builds_the_index_ahead():
 
 
 # ------------------------------------------------------------------ invalid inputs (graph.py:66)
-def _small_model():
+def _small_model(cfg_base=None):
     import copy
     import gnnepcsaft_b200 as G
     from tests.util import PNA_CFG1, deg_hist
     graphs, b = make_batch(8, seed=11)
-    cfg = dict(PNA_CFG1, deg=deg_hist(graphs))
+    cfg = dict(cfg_base or PNA_CFG1, deg=deg_hist(graphs))
     torch.manual_seed(0)
     return G.GNNePCSAFT(copy.deepcopy(cfg)).to(DEV).eval(), b
 
@@ -152,11 +152,14 @@ def _small_model():
 @pytest.mark.parametrize("what", ["edge", "atom", "bond"])
 def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what):
     """PyG raises on an edge_index entry >= num_nodes and torch.nn.Embedding on an id outside its vocabulary.  Here the
-    reference-signature forward() raises IndexError on the host read it pays anyway (int(batch[-1]) + 1); with
-    num_graphs= given (no sync) the kernels skip / zero the offending entries -- finite output, nothing uninitialised
-    is ever used as an index -- and Batch.validate() / GraphIndex.check() report it."""
+    flags ride the host reads the path pays anyway: ``int(batch[-1]) + 1`` of the reference-signature forward(), and the
+    max-degree readback of the PNA path (so a PNA model raises IndexError even with num_graphs= given).  A path without
+    any host read (GATv2 with num_graphs=) skips / zeroes the offending entries -- finite output, nothing uninitialised
+    is ever used as an index -- and Batch.validate() / GraphIndex.check() report them."""
     from gnnepcsaft_b200 import graph as gr
+    from tests.util import GAT_CFG_SMALL
     model, b = _small_model()
+    gat, _ = _small_model(GAT_CFG_SMALL)
     x, ei, ea, bt = (b[k].clone() for k in ("x", "edge_index", "edge_attr", "batch"))
     G = int(bt[-1]) + 1
     if what == "edge":
@@ -169,11 +172,17 @@ def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what)
         ea[5, 1] = 6                                      # bond stereo vocabulary is 0..5
     args = [t.to(DEV) for t in (x, ei, ea, bt)]
     with torch.no_grad():
-        with pytest.raises(IndexError):
-            model(*args)                                  # reference signature: the one host read checks the flags
+        for m in (model, gat):
+            gr._INDEX_CACHE.clear()
+            with pytest.raises(IndexError):
+                m(*args)                                  # reference signature: the one host read checks the flags
         gr._INDEX_CACHE.clear()
-        out = model(*args, num_graphs=G)                  # sync-free path: memory-safe, flags left on the device
-        assert out.shape == (G, 3) and bool(torch.isfinite(out).all())
+        with pytest.raises(IndexError):
+            model(*args, num_graphs=G)                    # PNA: the max-degree readback checks them too
+        gr._INDEX_CACHE.clear()
+        out = gat(*args, num_graphs=G)                    # sync-free path: memory-safe, flags left on the device
+        assert out.shape == (G, 2) and bool(torch.isfinite(out).all())
+        gr._INDEX_CACHE.clear()
         bb = gr.batch_from_reference_tensors(*args, num_graphs=G)
         with pytest.raises(IndexError):
             bb.validate()
@@ -189,6 +198,7 @@ def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what)
     gr._INDEX_CACHE.clear()
     with torch.no_grad():
         model(*good)
+        gat(*good, num_graphs=G)
         gr.batch_from_reference_tensors(*good, num_graphs=G).validate()
 
 
