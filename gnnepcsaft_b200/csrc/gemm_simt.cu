@@ -2,6 +2,8 @@
 // fp32 oracle) and the fallback for shapes the tcgen05 path does not take (tiny / unaligned).
 // 128x128x8 tiles, 256 threads, 8x8 register micro-tile, register-staged double buffering,
 // deterministic split-K (partials + ordered reduce) for the weight-gradient shapes (small M*N, huge K).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace gnnx {
@@ -429,6 +431,66 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
         launch(k_colsum_partial, dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);
     launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, (const float*)ws, nch, (int)cols, out);
     return check_launch("colsum", 2);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ column sums without any allocation
+// gnnx_colsum_noalloc: the chunk partials of gnnx_colsum live in a file-scope device array instead of a caller
+// workspace, for callers that cannot call cudaMalloc.  Every device that loads the library holds the array until
+// exit.  In host code `g_colsum_scratch` is only a stand-in for the symbol: the device address is fetched once per
+// device (that device current) with cudaGetSymbolAddress and handed to the kernels.
+static __device__ __align__(256) float g_colsum_scratch[GNNX_COLSUM_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+float* g_scratch_ptr[kMaxDevices] = {};
+
+// 0 and *ptr set, or an error code (message in gnnx_last_error())
+int colsum_scratch(float** ptr) {
+    int dev = -1;
+    GNNX_CUDA(cudaGetDevice(&dev));
+    GNNX_REQUIRE(dev >= 0 && dev < kMaxDevices, "colsum_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> g(g_scratch_mu);
+    if (!g_scratch_ptr[dev]) {
+        void* p = nullptr;
+        GNNX_CUDA(cudaGetSymbolAddress(&p, g_colsum_scratch));
+        g_scratch_ptr[dev] = static_cast<float*>(p);
+    }
+    *ptr = g_scratch_ptr[dev];
+    return GNNX_OK;
+}
+}  // namespace
+
+extern "C" {
+
+size_t gnnx_colsum_noalloc_max_bytes(void) { return GNNX_COLSUM_NOALLOC_SCRATCH_BYTES; }
+
+int gnnx_colsum_noalloc(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out, void* stream) {
+    if (cols == 0) return GNNX_OK;
+    GNNX_REQUIRE(rows >= 0 && cols > 0 && ld >= cols && out != nullptr && (in != nullptr || rows == 0), "colsum_noalloc: bad arguments");
+    GNNX_REQUIRE(rows <= INT32_MAX && cols <= INT32_MAX, "colsum_noalloc: rows / cols beyond int32");
+    const size_t need = gnnx_colsum_workspace_bytes(rows, cols);
+    if (need > (size_t)GNNX_COLSUM_NOALLOC_SCRATCH_BYTES)
+        return set_error(GNNX_ERR_WORKSPACE, "colsum_noalloc: [%lld x %lld] needs %zu bytes of partials, the built-in scratch holds %zu "
+                         "(use gnnx_colsum with a caller workspace)", (long long)rows, (long long)cols, need,
+                         (size_t)GNNX_COLSUM_NOALLOC_SCRATCH_BYTES);
+    cudaStream_t st = as_stream(stream);
+    if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(out, 0, cols * sizeof(float), st)); return GNNX_OK; }
+    float* scratch = nullptr;
+    int rc = colsum_scratch(&scratch);
+    if (rc != GNNX_OK) return rc;
+    // every partial [nch, cols] the final pass reads is written by the partial pass of THIS call: nothing in the shared
+    // array has to start at zero, and what the previous call left behind is never read
+    int nch = colsum_chunks(rows, cols);
+    int rpc = ceil_div(rows, nch);
+    if ((cols & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)in & 15) == 0)
+        launch(k_colsum_partial4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, scratch);
+    else
+        launch(k_colsum_partial, dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st, in, ld, (int)rows, (int)cols, rpc, scratch);
+    launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, (const float*)scratch, nch, (int)cols, out);
+    return check_launch("colsum_noalloc", 2);
 }
 
 }  // extern "C"

@@ -184,6 +184,20 @@ GNNX_API int gnnx_gemm_dw_batched(int32_t n, const float* const* dY, const int64
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);
 GNNX_API int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* gnnx_colsum without a caller workspace and without any allocation (no cudaMalloc / cudaFree, no allocating library
+ * routine): the chunk partials live in a file-scope device array of GNNX_COLSUM_NOALLOC_SCRATCH_BYTES that every GPU
+ * which loads the library holds until exit.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same result, bit for bit, as gnnx_colsum on the same input.  Shapes whose partials
+ * (gnnx_colsum_workspace_bytes(rows, cols): at most 4 * SMs * 256 floats = 592 KiB on a B200 while cols <= 151 552,
+ * 4 * cols bytes beyond that, so cols > 262 144 never fits) exceed the array are rejected with GNNX_ERR_WORKSPACE
+ * and nothing is launched.  All calls on
+ * a device share the one array: it keeps the previous call's partials (each call overwrites every partial it reads,
+ * nothing has to start at zero), and two calls that overlap on the GPU (different streams, no ordering between them)
+ * race on it -- order them, or use gnnx_colsum with separate workspaces. */
+#define GNNX_COLSUM_NOALLOC_SCRATCH_BYTES (1u << 20)
+GNNX_API size_t gnnx_colsum_noalloc_max_bytes(void);
+GNNX_API int gnnx_colsum_noalloc(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out, void* stream);
 
 /* ------------------------------------------------------------------ PNA message passing */
 /* Replaces the gather + first pre_nn Linear of PNAConv.message (PyG; called from
