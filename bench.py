@@ -41,6 +41,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GRAPHS_PER_GPU = 4096
+REFERENCE_SAMPLE = 2048          # graphs per step of the CPU reference arm (--impl reference)
 WORKLOADS = {
     "cfg2": dict(conv="PNA", hidden_dim=256, propagation_depth=6, dropout=0.0, global_pool="add", num_para=3,
                  towers=1, pre_layers=2, post_layers=4, heads=2, add_self_loops=True, model="gnn"),
@@ -146,6 +147,43 @@ def cpu_oracle_steps(cfg, graphs, deg, sample: int, steps: int, warmup: int, thr
     return times
 
 
+CFG1 = dict(conv="PNA", hidden_dim=64, propagation_depth=3, dropout=0.0, global_pool="add", num_para=3, towers=1,
+            pre_layers=2, post_layers=4, heads=2, add_self_loops=True, model="gnn")
+
+
+def cpu_cfg1_baseline(iters: int = 30, warmup: int = 5):
+    """BASELINE.md section 3 / SURVEY 8(d) "CPU baseline timing": BASELINE configs[0] -- PNA hidden 64, 3 layers, fwd + bwd
+    on a batch of 32 synthetic ~25-atom graphs, collate included -- on the CPU oracle with 1 thread and with all host
+    threads: warm-up 5, median of >= 30 iterations, time.perf_counter."""
+    from oracle import pyg_restated as O
+    from gnnepcsaft_b200 import synth
+    graphs = synth.make_graphs(32, seed=1234)
+    t = torch.from_numpy
+    og = [O.Graph(t(g.x), t(g.edge_index), t(g.edge_attr), para=t(g.para), assoc=t(g.assoc)) for g in graphs]
+    deg = O.calc_deg(og)
+    torch.manual_seed(0)
+    model = O.GNNePCSAFT(dict(CFG1, deg=deg)).train()
+    out = {"config": "BASELINE configs[0]: PNA hidden 64, 3 layers, collate + fwd + loss + bwd, batch of 32 graphs",
+           "iters": iters, "warmup": warmup, "torch": torch.__version__}
+    before = torch.get_num_threads()
+    for threads in (1, os.cpu_count() or 1):
+        torch.set_num_threads(threads)
+        times = []
+        for i in range(warmup + iters):
+            t0 = time.perf_counter()
+            b = O.collate(og)
+            pred = model(b.x, b.edge_index, b.edge_attr, b.batch)
+            loss, _ = O.training_loss(pred, b.para)
+            model.zero_grad(set_to_none=True)
+            loss.backward()
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+        med = float(np.median(times))
+        out[f"threads_{threads}"] = {"ms_per_iter_median": 1e3 * med, "graphs_per_s": 32 / med}
+    torch.set_num_threads(before)
+    return out
+
+
 def run_reference_arm(args, cfg, target):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -155,11 +193,9 @@ def run_reference_arm(args, cfg, target):
     graphs = make_dataset(0, 2048)
     t = torch.from_numpy
     deg = O.calc_deg([O.Graph(t(g.x), t(g.edge_index), t(g.edge_attr)) for g in graphs])
-    probe = cpu_oracle_steps(cfg, graphs, deg, 64, 1, 1, threads, target)[0]
-    budget = 150.0                                        # seconds for the whole --steps/--warmup run
-    per_graph = probe / 64
-    sample = int(budget / max(1, args.steps + args.warmup) / per_graph)
-    sample = max(32, min(GRAPHS_PER_GPU, sample, len(graphs)))
+    # a CONSTANT bounded sample (half a cfg2 batch per step), so that two runs of this arm measure the same thing: at the
+    # 300-600 graphs/s of a 16-core host a 20 + 5 step run takes 1.5-3 minutes
+    sample = REFERENCE_SAMPLE
     times = cpu_oracle_steps(cfg, graphs, deg, sample, args.steps, args.warmup, threads, target)
     ms = 1e3 * float(np.mean(times))
     value = sample / (ms / 1e3)
@@ -172,7 +208,8 @@ def run_reference_arm(args, cfg, target):
                            "not installable here or on the GPU box) on a bounded sample of the workload"},
         "cpu_baseline": {"value": value, "unit": "graphs/s", "cores": threads, "kind": "port",
                          "sample": f"{sample} graphs/step x {args.steps} steps, collate+fwd+loss+bwd+AdamW, "
-                                   f"torch {torch.__version__}, {threads} threads"},
+                                   f"torch {torch.__version__}, {threads} threads",
+                         "cfg1": cpu_cfg1_baseline()},
         "e2e": {"value": value, "unit": "graphs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -200,6 +237,10 @@ def _algorithmic_bytes(name, a, N, E, H):
     if name == "gnnx_gemm_grouped_dw":            # both operands read once, J weighted sums written
         R, Mo, No, J = a[4], a[5], a[6], a[10]
         return 4.0 * (R * (Mo + No) + J * Mo * No), 2.0 * R * Mo * No
+    if name == "gnnx_pna_post_fused_fwd":         # aggregate + grouped first post Linear in one kernel: messages and x read once,
+        rows, Hh, G, Ho, keep = a[3], a[5] * a[6], a[10], a[15], a[17]      # out written (+ the [agg | x] copy kept for the backward)
+        return (4.0 * E * H + 4.0 * N * H + 4.0 * rows * Ho + 4.0 * G * Ho * 5 * Hh + (20.0 * rows * Hh if keep else 0.0),
+                2.0 * rows * Ho * 5 * Hh)
     if name == "gnnx_pna_aggregate_rows_fwd":     # as aggregate_fwd + the x row copied behind the aggregates ([agg | x])
         return 4.0 * E * H + 24.0 * N * H + 8.0 * N, 0.0
     if name == "gnnx_pna_aggregate_rows_bwd":     # as aggregate_bwd + the x block of d[agg | x] moved to node order
@@ -314,7 +355,9 @@ def run_gpu_arm(args, cfg, target):
         dist.init_process_group("nccl", device_id=dev)
     ops.set_matmul_precision(args.precision)
 
-    G = GRAPHS_PER_GPU
+    # weak scaling (default): 4096 graphs per GPU whatever N is.  strong (BASELINE configs[3]): a fixed global batch
+    # (32 768 graphs) cut into N equal shards -- 16 384 / 8 192 / 4 096 graphs per GPU at N = 2 / 4 / 8.
+    G = GRAPHS_PER_GPU if args.scaling == "weak" else args.global_batch // world
     graphs = make_dataset(rank, 2 * G)
     store = graph.DeviceGraphStore(synth.pack(graphs), dev)
     hist = torch.zeros(64, dtype=torch.int64, device=dev)
@@ -402,6 +445,30 @@ def run_gpu_arm(args, cfg, target):
     e2e_ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
     e2e_value = world * G / (e2e_ms / 1e3)
 
+    # the same loop through the EXACT reference signature forward(x, edge_index, edge_attr, batch): without num_graphs=
+    # the model reads int(batch[-1]) + 1 back (PyG's own sync at models.py:219), one more host round trip per step
+    n_exact = max(3, min(10, args.steps))
+    feed = graph.HostBatchPrefetcher((host[i % n_batches] for i in range(2 + n_exact)), dev)
+
+    def exact_step():
+        x, ei, ea, bt, tgt = next(feed)
+        trainer.flat.zero_grad()
+        pred = model(x, ei, ea, bt)
+        out2, dpred = ops.relhuber_fwd_bwd(pred.detach().contiguous(), tgt)
+        pred.backward(dpred)
+        trainer.optimizer_step()
+        return float(out2[0].item())
+
+    for i in range(2):
+        exact_step()
+    sync()
+    e0.record()
+    for i in range(n_exact):
+        exact_step()
+    e1.record()
+    sync()
+    exact_ms = max_over_ranks(e0.elapsed_time(e1) / n_exact)
+
     # ---- roofline pass: 2 more steps of the SAME workload with CUDA events around every gnnx entry point (on the
     # launching stream); algorithmic bytes per call from its shapes (DESIGN.md "Kernels and rooflines").
     b = store.collate(batch_ids[0])
@@ -425,19 +492,22 @@ def run_gpu_arm(args, cfg, target):
         times = cpu_oracle_steps(cfg, graphs[:1024], deg, sample, 3, 1, threads, target)
         cpu_baseline = {"value": sample / float(np.mean(times)), "unit": "graphs/s", "cores": threads, "kind": "port",
                         "sample": f"{sample} graphs/step x 3 steps (1 warm-up) of the same model/config: collate+fwd+"
-                                  f"loss+bwd+AdamW on the CPU oracle, torch {torch.__version__}, {threads} threads"}
+                                  f"loss+bwd+AdamW on the CPU oracle, torch {torch.__version__}, {threads} threads",
+                        "cfg1": cpu_cfg1_baseline()}
     line = {
         "metric": "train molecular graphs/sec", "value": value, "unit": "graphs/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32"}[args.precision],
+        "scaling": args.scaling, "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32"}[args.precision],
         "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[args.workload], "graphs_per_gpu": G, "global_batch": world * G,
+        "config": {"workload": WORKLOAD_NAMES[args.workload].replace("4096 synthetic", f"{G} synthetic"), "graphs_per_gpu": G,
+                   "global_batch": world * G,
                    "nodes_per_batch": N, "edges_per_batch": E, "parallelism": f"dp{world}",
                    "l2": "per-step working set (activations ~10 GB) is far larger than the 126 MB L2; no flush needed",
                    "final_loss": final_loss},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_value, "unit": "graphs/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 4, "api": "GNNePCSAFT.forward(x, edge_index, edge_attr, batch) on int64 tensors "
+                "d2h_bytes_per_step": 4, "exact_signature_ms_per_step": exact_ms,
+                "exact_signature_value": world * G / (exact_ms / 1e3), "api": "GNNePCSAFT.forward(x, edge_index, edge_attr, batch) on int64 tensors "
                                                  "from pinned host memory (graph.HostBatchPrefetcher: H2D of batch i+1 under step i) + loss.item()"},
         "gpu_launches": launches,
         "roofline": roofline,
@@ -588,6 +658,9 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 4096 graphs per GPU; strong: --global-batch graphs cut into N shards (BASELINE configs[3])")
+    ap.add_argument("--global-batch", type=int, default=32768)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     cfg = WORKLOADS[args.workload]

@@ -8,6 +8,6 @@ python scripts/profile_step.py --steps 2 > gpurun_out/profile_step_$TAG.log 2>&1
 ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
     --csv --log-file gpurun_out/launches_${TAG}_cfg2_tf32.csv python scripts/profile_step.py --steps 2 > gpurun_out/ncu_list_$TAG.log 2>&1
 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:k_gemm_tf32 --launch-skip 60 --launch-count 12 \
-    -o gpurun_out/ncu_${TAG}_gemm_set_full -f python scripts/profile_step.py --steps 1 > gpurun_out/ncu_full_$TAG.log 2>&1
-ncu -i gpurun_out/ncu_${TAG}_gemm_set_full.ncu-rep --page raw --csv > gpurun_out/ncu_${TAG}_gemm_set_full_raw.csv 2>/dev/null
+    -o /tmp/ncu_${TAG}_gemm_set_full -f python scripts/profile_step.py --steps 1 > gpurun_out/ncu_full_$TAG.log 2>&1
+ncu -i /tmp/ncu_${TAG}_gemm_set_full.ncu-rep --page raw --csv > gpurun_out/ncu_${TAG}_gemm_set_full_raw.csv 2>/dev/null
 ls -la gpurun_out | tail -8

@@ -68,7 +68,17 @@ def test_custom_op_face_equals_fused_face_forward_and_backward(cfg, target):
     m2 = copy.deepcopy(m1)
     args = [b[k].to(DEV) for k in ("x", "edge_index", "edge_attr", "batch")]
     Gn = int(b["batch"][-1]) + 1
-    p1 = m1(*args, num_graphs=Gn)
+    # The custom-op face has no host-side degree bound (a traced graph cannot read one back), so its PNAConv takes the
+    # general scaler-folded path; the fused face is held to the same path here.  (Its default, the degree-grouped path,
+    # is algebraically equal but rounds differently, and training-mode BatchNorm amplifies a 1e-8 difference in a
+    # near-constant column by up to 1 / sqrt(eps) = 316 per layer: measured 2.7e-4 on these predictions, both paths
+    # inside the oracle tolerances of test_gpu_model.py.  scripts/diag_custom_ops2.py prints the layer-by-layer trail.)
+    from gnnepcsaft_b200 import pna_fn
+    pna_fn.GROUPED_POST = False
+    try:
+        p1 = m1(*args, num_graphs=Gn)
+    finally:
+        pna_fn.GROUPED_POST = True
     models.use_custom_ops(True)
     try:
         p2 = m2(*args, num_graphs=Gn)
