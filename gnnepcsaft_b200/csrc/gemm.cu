@@ -31,6 +31,11 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
                         cudaStream_t st);
 int group_reduce_launch(const float* partial, const int* split_table, int S, const float* coef, int J, long long total,
                         float* out, cudaStream_t st);
+bool pna_post_fused_ok(int64_t rows, int64_t Ho, int64_t H, int64_t F, int64_t ldw, int64_t ld_out, int64_t ld_agg,
+                       const void* weff, const void* out, const void* agg_out, const void* msg, const void* x);
+int pna_post_fused(const float* msg, const int* rowptr, const int* row_node, int64_t rows, const float* x, int64_t H, int64_t F,
+                   const float* weff, int64_t ldw, const int* bucket_ptr, int n_groups, const float* bias, int flags,
+                   float* out, int64_t ld_out, int64_t Ho, uint32_t* bits_out, float* agg_out, int64_t ld_agg, cudaStream_t st);
 }  // namespace gnnx
 
 using namespace gnnx;
@@ -114,6 +119,32 @@ int gnnx_gemm_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, 
     GNNX_REQUIRE(bucket_ptr && n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS, "gemm_grouped: 1..%d groups and a bucket_ptr", GNNX_MAX_GROUPS);
     return gemm_dispatch(A, lda, 0, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, colsum_a_out,
                          precision, ws, ws_bytes, stream, bucket_ptr, n_groups);
+}
+
+int32_t gnnx_pna_post_fused_supported(int64_t rows, int32_t towers, int32_t f, int32_t h_out, int32_t precision) {
+    const int64_t H = (int64_t)towers * f;
+    if (precision == GNNX_PREC_FP32 || towers < 1 ||
+        !pna_post_fused_ok(rows, h_out, H, f, 5 * H, h_out, 5 * H, nullptr, nullptr, nullptr, nullptr, nullptr))
+        return 0;
+    // 1: the kernel takes the shape; 2: and the product is large enough that gnnx_gemm would send it to the tensor cores
+    return (double)rows * (double)h_out * (double)(5 * H) < 33554432.0 ? 1 : 2;
+}
+
+int gnnx_pna_post_fused_fwd(const float* m, const int32_t* rowptr, const int32_t* row_node, int64_t rows, const float* x,
+                            int32_t towers, int32_t f, const float* weff, int64_t ld_w, const int32_t* bucket_ptr,
+                            int32_t n_groups, const float* bias, int32_t relu, float* out, int64_t ld_out, int32_t h_out,
+                            uint32_t* relu_bits_out, float* agg_out, int64_t ld_agg, int32_t precision, void* stream) {
+    GNNX_REQUIRE(precision != GNNX_PREC_FP32, "pna_post_fused_fwd: tensor-core tier only (the fp32 tier runs aggregate + grouped product)");
+    GNNX_REQUIRE(rowptr && row_node && x && weff && bucket_ptr && out, "pna_post_fused_fwd: null operand");
+    GNNX_REQUIRE(n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS && towers >= 1, "pna_post_fused_fwd: 1..%d groups", GNNX_MAX_GROUPS);
+    const int64_t H = (int64_t)towers * f;
+    if (!agg_out) ld_agg = 5 * H;
+    if (!pna_post_fused_ok(rows, h_out, H, f, ld_w, ld_out, ld_agg, weff, out, agg_out, m, x))
+        return set_error(GNNX_ERR_UNSUPPORTED, "pna_post_fused_fwd: shape / alignment outside the fused kernel's envelope "
+                         "(rows %% 256, F %% 32, h_out %% 16; see gnnx_pna_post_fused_supported)");
+    GNNX_REQUIRE(ld_w >= 5 * H && ld_out >= h_out && ld_agg >= 5 * H, "pna_post_fused_fwd: row strides too small");
+    return pna_post_fused(m, rowptr, row_node, rows, x, H, f, weff, ld_w, bucket_ptr, n_groups, bias,
+                          relu ? GNNX_GEMM_RELU : 0, out, ld_out, h_out, relu_bits_out, agg_out, ld_agg, as_stream(stream));
 }
 
 static bool dw_batched_tc(int32_t n, const float* const* dY, const int64_t* ld_dy, const float* const* X, const int64_t* ld_x,

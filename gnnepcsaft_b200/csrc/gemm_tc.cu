@@ -23,6 +23,7 @@
 #include <mutex>
 #include <unordered_map>
 #include <utility>
+#include <type_traits>
 
 #include "common.cuh"
 #include "tc_ptx.cuh"
@@ -475,6 +476,325 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tc_fence_before();
     __syncwarp();                                                    // re-converge the single-lane role warps
     if (kCluster > 1) cluster_sync_all(); else __syncthreads();      // no CTA may exit while its peer can still multicast into it
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------ PNAConv: aggregate -> first post Linear, ONE kernel
+// out[r, :] = act([mean | min | max | std | x](row r) W_eff(d_r)^T + b) for the degree-bucketed rows (degree_groups.cu).
+// Same pipeline as k_gemm_tf32_rows2 (weights by multicast TMA, tcgen05 accumulators ping-ponging in TMEM, TMA-store
+// epilogue), but the A operand never exists in HBM on the way in: eight PRODUCER warps build every 128-row x 32-column
+// A stage in shared memory -- the swizzled K-major layout TMA would have written -- straight from the dst-sorted
+// messages m[E, H] (mean / min / max / std of each row's incoming run, k_pna_aggregate_fwd's operation sequence) and from
+// x[row_node[r]].  The K order is permuted so that the four aggregates of one 32-column chunk are consecutive k-blocks
+// (the weight box is fetched at the matching K coordinate, the sum over K does not care): the chunk's messages are read
+// from HBM once and served to the other three from L1 / L2.  The product is tensor-bound (K = 5H), so the producers'
+// loads hide under the MMAs; the separate aggregate pass (write + re-read of [rows, 5H]) is gone.  For the backward's
+// weight gradient the producers can also store what they computed (`agg_out`, fp32, unrounded).
+// Warp roles: warps 0-3 = TMA, MMA + two idle warps, warps 4-7 = epilogue (TMEM lane quadrant = warp % 4), warps 8-15 =
+// producers.  512 threads x 128 registers; setmaxnreg re-balancing was tried and made ptxas spill more, not less.
+constexpr int kProdWarps = 8;                       // two groups of four: alternate units of k-blocks
+constexpr int kFirstEpiWarp = 4;
+constexpr int kFirstProdWarp = 8;
+constexpr int kThreadsF = (kFirstProdWarp + kProdWarps) * 32;
+constexpr float kStdMaskF = 0.003162277629598975f;  // sqrt(1e-5f) rounded as in pna.cu (GNNX_STD_MASK)
+
+__device__ __forceinline__ float to_tf32(float v, int mode) {
+    uint32_t r;
+    if (mode == 0) asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    else if (mode == 1) asm("cvt.rn.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    else return v;
+    return __uint_as_float(r);
+}
+
+// One output float4 of aggregate `typ` (0 mean, 1 min, 2 max, 3 std) of a row with `deg` messages, the first U of them in
+// registers (entries past deg are ignored), the tail beyond 4 read from memory (hypervalent rows only).  The operation
+// sequence is agg_acc / k_pna_aggregate_fwd's of pna.cu, so the results are bit-identical with that kernel's.
+template <int U>
+__device__ __forceinline__ float4 agg_reduce4(const float4 (&v)[U], int deg, int typ, const float* __restrict__ tail, int H) {
+    float s[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    float mn[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const bool on = u < deg;
+        const float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            s[j] = on ? __fadd_rn(s[j], e[j]) : s[j];
+            s2[j] = on ? __fadd_rn(s2[j], __fmul_rn(e[j], e[j])) : s2[j];
+            mn[j] = on ? fminf(mn[j], e[j]) : mn[j];
+            mx[j] = on ? fmaxf(mx[j], e[j]) : mx[j];
+        }
+    }
+    if (U >= 4)
+        for (int u = 4; u < deg; ++u) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(tail + (long long)u * H));
+            const float e[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                s[j] = __fadd_rn(s[j], e[j]);
+                s2[j] = __fadd_rn(s2[j], __fmul_rn(e[j], e[j]));
+                mn[j] = fminf(mn[j], e[j]);
+                mx[j] = fmaxf(mx[j], e[j]);
+            }
+        }
+    const float cnt = fmaxf((float)deg, 1.f);
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float mu = __fdiv_rn(s[j], cnt);
+        if (typ == 0) o[j] = mu;
+        else if (typ == 1) o[j] = deg ? mn[j] : 0.f;
+        else if (typ == 2) o[j] = deg ? mx[j] : 0.f;
+        else {
+            const float m2 = __fdiv_rn(s2[j], cnt);
+            const float var = __fsub_rn(m2, __fmul_rn(mu, mu));
+            const float sd = __fsqrt_rn(fmaxf(var, 1e-5f));
+            o[j] = (sd <= kStdMaskF) ? 0.f : sd;
+        }
+    }
+    return make_float4(o[0], o[1], o[2], o[3]);
+}
+
+template <int kCluster>
+__global__ void __launch_bounds__(kThreadsF, 1)
+k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmC,
+                 const float* __restrict__ msg, const int* __restrict__ rowptr, const int* __restrict__ row_node,
+                 const float* __restrict__ x, int M, int N, int H, int F, int BN, const float* __restrict__ bias, int flags,
+                 uint32_t* __restrict__ bits_out, long long ldbits, const int* __restrict__ bucket_ptr, int n_groups,
+                 float* __restrict__ agg_out, long long ld_agg, int round_mode) {
+    extern __shared__ uint8_t smem_raw[];
+    Smem2 sm;
+    sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = kCluster > 1 ? (int)cluster_ctarank() : 0;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages2; ++s) {
+            mbar_init(sm.full(s), (round_mode & 512) ? 1 : (round_mode & 4096) ? 2 : 1 + kProdWarps);   // the weight TMA's expect_tx + the eight producer warps
+            mbar_init(sm.empty(s), kCluster);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(sm.tmem_full(b), 1);
+            mbar_init(sm.tmem_empty(b), 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(sm.tmem_ptr()), kTmemCols);
+    tc_fence_before();
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr();
+    pdl_enter();
+
+    const int n_tiles = (N + BN - 1) / BN;
+    const int m_groups = ((M + 127) / 128 + kCluster - 1) / kCluster;
+    const int work = n_tiles * m_groups;
+    const int cid = blockIdx.x / kCluster, ncl = gridDim.x / kCluster;
+    const int HB = H / kBK;                          // 32-column chunks of the hidden width
+    const int KB = 5 * HB;                           // k-blocks: (chunk, aggregate) pairs, then the x chunks
+    // K coordinate (column of W_eff / of [agg | x]) of k-block kb: agg layout is [tower][mean|min|max|std][F]
+    auto kcoord = [&](int kb) -> int {
+        if (kb >= 4 * HB) return 4 * H + (kb - 4 * HB) * kBK;
+        const int c = (kb >> 2) * kBK, typ = kb & 3;
+        return (c / F) * 4 * F + typ * F + (c % F);
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmB);
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = (uint32_t)BN * 128u;
+            const int half = BN / 2;
+            for (int w = cid; w < work; w += ncl) {
+                const int n0 = (w % n_tiles) * BN;
+                int goff = 0;
+                const int mbase = (w / n_tiles) * kCluster * 128;
+                for (int d = 1; d < n_groups; ++d) goff += (mbase >= __ldg(bucket_ptr + d)) ? N : 0;
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait_poll(sm.empty(stage), phase ^ 1);
+                    mbar_expect_tx(sm.full(stage), tx);
+                    if (kCluster == 1) tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kcoord(kb), n0 + goff);
+                    else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kcoord(kb), n0 + rank * half + goff, 3);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, BN, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0, i = 0;
+            for (int w = cid; w < work; w += ncl, ++i) {
+                const uint32_t buf = i & 1;
+                mbar_wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait_poll(sm.full(stage), phase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < kBK / 8; ++k) {
+                        const uint64_t bdesc = make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        const uint64_t adesc = make_smem_desc(sm.a(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        mma_tf32(tmem_base + buf * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    if (kCluster > 1) mma_commit_mc(sm.empty(stage), 3); else mma_commit(sm.empty(stage));
+                    if (kb == KB - 1) mma_commit(sm.tmem_full(buf));
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= kFirstProdWarp && !(round_mode & 512) && (!(round_mode & 4096) || warp == kFirstProdWarp)) {
+        // ---- producers: all eight warps build every k-block.  Warp pw owns rows pw * 16 .. +15 of the tile; lane l covers
+        // the 16-byte chunk (l & 7) of rows (l >> 3) + 4 i, i < 4: 8 lanes read one 128-byte row segment of a message,
+        // 4 rows per load instruction.  The k-blocks come in UNITS -- the four aggregates of one 32-column chunk from ONE
+        // set of message loads held in registers, then the x chunks two at a time -- and with in-degree <= 2 the loads of
+        // unit u + 1 are issued before unit u is computed.  Loads are unconditional (clamped row indices, selects in the
+        // arithmetic) so that all loads of a unit are in flight together.
+        const int pw = warp - kFirstProdWarp;
+        const int cj = lane & 7, rr = lane >> 3;
+        const float* dummy = x + cj * 4;                      // any mapped address: deg-0 / padding rows load it and discard it
+        const int NU = HB + (HB + 1) / 2;                     // units per tile
+        uint32_t it = 0;                                      // k-blocks of this CTA so far (all work items)
+        for (int w = cid; w < work; w += ncl) {
+            const int m0 = ((w / n_tiles) * kCluster + rank) * 128;
+            const bool store_agg = agg_out != nullptr && (w % n_tiles) == 0;
+            // per row group: node id, and first edge slot + in-degree in one register (e0 << 4 | min(deg, 15): the bucket
+            // layout caps the number of degree classes at GNNX_MAX_GROUPS = 16)
+            uint32_t ed[4];
+            int nd[4];
+            int dmax = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = m0 + pw * 16 + i * 4 + rr;
+                const int node = (r < M && !(round_mode & 2048)) ? __ldg(row_node + r) : -1;
+                const int b = node >= 0 ? __ldg(rowptr + node) : 0;
+                const int d = node >= 0 ? __ldg(rowptr + node + 1) - b : 0;
+                nd[i] = node;
+                ed[i] = ((uint32_t)b << 4) | (uint32_t)min(d, 15);
+                dmax = max(dmax, d);
+            }
+            dmax = __reduce_max_sync(0xffffffffu, dmax);
+
+            // value -> A stage (tf32-rounded, swizzled K-major row) and, for the backward, the fp32 operand copy
+            auto emit = [&](uint32_t k, int i, int kc, const float4& o) {
+                if (round_mode & 128) return;
+                const int r = pw * 16 + i * 4 + rr;
+                if (store_agg && !(round_mode & 64) && m0 + r < M) __stcs(reinterpret_cast<float4*>(agg_out + (long long)(m0 + r) * ld_agg + kc), o);
+                uint8_t* a = sm.base + (int)(k % kStages2) * kStage2;
+                *reinterpret_cast<float4*>(a + r * 128 + ((cj ^ (r & 7)) << 4)) =
+                    make_float4(to_tf32(o.x, round_mode & 3), to_tf32(o.y, round_mode & 3), to_tf32(o.z, round_mode & 3), to_tf32(o.w, round_mode & 3));
+            };
+            // one poller per warp: 256 threads spinning on try_wait keep the barrier's shared-memory word busy and delay
+            // the very arrivals (tcgen05.commit, TMA complete_tx) they are waiting for
+            auto wait_empty = [&](uint32_t k) {
+                if (lane == 0 && !(round_mode & 1024)) mbar_wait_poll(sm.empty((int)(k % kStages2)), ((k / kStages2) & 1u) ^ 1u);
+                __syncwarp();
+            };
+            auto publish = [&](uint32_t k) {
+                if (!(round_mode & 128)) fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core's async proxy
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sm.full((int)(k % kStages2)));
+            };
+            // loads of unit u into v[row group][slot]: U message rows of chunk u, or two x chunks
+            auto load_agg = [&](auto& v, int u) {
+                constexpr int U = sizeof(v[0]) / sizeof(float4);
+                const int col = u * kBK + cj * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int d = (int)(ed[i] & 15u), b = (int)(ed[i] >> 4);
+#pragma unroll
+                    for (int k = 0; k < U; ++k)
+                        v[i][k] = (round_mode & 16) ? make_float4(1.f, 2.f, 3.f, 4.f)
+                                                    : __ldg(reinterpret_cast<const float4*>(d > 0 ? msg + (long long)(b + min(k, d - 1)) * H + col : dummy));
+                }
+            };
+            auto load_x = [&](auto& v, int u) {
+                const int xc = 2 * (u - HB), n = min(2, HB - xc);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+                        v[i][k] = __ldg(reinterpret_cast<const float4*>((nd[i] >= 0 && k < n) ? x + (long long)nd[i] * H + (xc + k) * kBK + cj * 4 : dummy));
+            };
+            auto produce_agg = [&](auto& v, int u) {
+                constexpr int U = sizeof(v[0]) / sizeof(float4);
+                const int col = u * kBK + cj * 4;
+#pragma unroll
+                for (int typ = 0; typ < 4; ++typ) {
+                    wait_empty(it + typ);
+                    const int kc = kcoord(4 * u + typ) + cj * 4;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        emit(it + typ, i, kc, (round_mode & 32) ? v[i][0] : agg_reduce4<U>(v[i], (int)(ed[i] & 15u), typ, msg + (long long)(ed[i] >> 4) * H + col, H));
+                    publish(it + typ);
+                }
+                it += 4;
+            };
+            auto produce_x = [&](auto& v, int u) {
+                const int xc = 2 * (u - HB), n = min(2, HB - xc);
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    if (k < n) {
+                        wait_empty(it + k);
+                        const int kc = 4 * H + (xc + k) * kBK + cj * 4;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) emit(it + k, i, kc, nd[i] >= 0 ? v[i][k] : make_float4(0.f, 0.f, 0.f, 0.f));
+                        publish(it + k);
+                    }
+                it += n;
+            };
+
+            if (dmax <= 2) {
+                float4 va[4][2], vb[4][2];                    // unit u in va while unit u + 1 lands in vb, and vice versa
+                load_agg(va, 0);
+#pragma unroll 1
+                for (int u = 0; u < NU; u += 2) {
+                    if (u + 1 < NU) { if (u + 1 < HB) load_agg(vb, u + 1); else load_x(vb, u + 1); }
+                    if (u < HB) produce_agg(va, u); else produce_x(va, u);
+                    if (u + 1 < NU) {
+                        if (u + 2 < NU) { if (u + 2 < HB) load_agg(va, u + 2); else load_x(va, u + 2); }
+                        if (u + 1 < HB) produce_agg(vb, u + 1); else produce_x(vb, u + 1);
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int u = 0; u < HB; ++u) {
+                    float4 v[4][4];
+                    load_agg(v, u);
+                    produce_agg(v, u);
+                }
+#pragma unroll 1
+                for (int u = HB; u < NU; ++u) {
+                    float4 v[4][2];
+                    load_x(v, u);
+                    produce_x(v, u);
+                }
+            }
+        }
+    } else if (warp >= kFirstEpiWarp && warp < kFirstProdWarp) {
+        const int q = warp & 3;
+        uint32_t it = 0, i = 0;
+        if (lane == 0) tma_prefetch_desc(&tmC);
+        for (int w = cid; w < work; w += ncl, ++i) {
+            const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
+            const uint32_t buf = i & 1;
+            mbar_wait(sm.tmem_full(buf), (i >> 1) & 1);
+            tc_fence_after();
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
+            if (m0 < M && !(round_mode & 256))
+                epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, nullptr, 0, bits_out, ldbits);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sm.tmem_empty(buf));
+        }
+        if (lane == 0) tma_store_wait_all();
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -945,6 +1265,70 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
     for (int z = 0; z < n && rc == GNNX_OK; ++z)
         rc = splitk_reduce_launch((const float*)ws + z * stride, p.splits, (int)Mo, (int)No, C[z], ldc[z], nullptr, 0, nullptr, 0, st);
     return rc;
+}
+
+// ------------------------------------------------------------------ fused aggregate -> grouped post Linear (forward)
+bool pna_post_fused_ok(int64_t rows, int64_t Ho, int64_t H, int64_t F, int64_t ldw, int64_t ld_out, int64_t ld_agg,
+                       const void* weff, const void* out, const void* agg_out, const void* msg, const void* x) {
+    if (!encode_fn()) return false;
+    if (rows < 256 || rows % 256 || rows > 0x7fffffff) return false;        // buckets are padded to 2-CTA row blocks
+    if (H < 32 || H % 32 || F < 32 || F % 32 || H % F) return false;        // 32-column chunks never straddle a tower block
+    if (Ho < 16 || Ho % 16 || (Ho > 256 && Ho % 256)) return false;
+    if ((ldw & 3) || (ld_out & 3) || (ld_agg & 3)) return false;
+    return aligned16(weff) && aligned16(out) && aligned16(agg_out) && aligned16(msg) && aligned16(x);
+}
+
+int pna_post_fused(const float* msg, const int* rowptr, const int* row_node, int64_t rows, const float* x, int64_t H, int64_t F,
+                   const float* weff, int64_t ldw, const int* bucket_ptr, int n_groups, const float* bias, int flags,
+                   float* out, int64_t ld_out, int64_t Ho, uint32_t* bits_out, float* agg_out, int64_t ld_agg, cudaStream_t st) {
+    static std::atomic<uint64_t> attrs_done{0};
+    {
+        int rc = ensure_attrs(attrs_done, []() -> int {
+            GNNX_CUDA(cudaFuncSetAttribute(k_pna_post_fused<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            return GNNX_OK;
+        });
+        if (rc) return rc;
+    }
+    static std::once_flag rm_once;
+    // how the producers round fp32 -> tf32: 1 = cvt.rn (what the TMA's TFLOAT32 tensor maps do: measured, the fused
+    // product then equals the two-kernel product up to the K order of the accumulation), 0 = cvt.rna, 2 = leave the low
+    // mantissa bits for the tensor core to drop (GNNX_FUSED_ROUND: diagnostic)
+    static int round_mode = 1;
+    std::call_once(rm_once, [] {
+        const char* e = getenv("GNNX_FUSED_ROUND");
+        if (e && e[0] >= '0' && e[0] <= '2') round_mode = e[0] - '0';
+        const char* d = getenv("GNNX_FUSED_DBG");           // diagnostic (wrong results): 16 no message loads, 32 no reduction, 64 no operand copy
+        if (d) round_mode |= atoi(d) & 8176;
+    });
+    const int BN = (int)(Ho >= 256 ? 256 : Ho);
+    constexpr int cluster = 2;
+    CUtensorMap mB, mC;
+    if (make_map_kmajor(&mB, weff, Ho * n_groups, 5 * H, ldw, BN / cluster)) return GNNX_ERR_INVALID;
+    if (make_map_store(&mC, out, rows, Ho, ld_out)) return GNNX_ERR_INVALID;
+    const int m_tiles = ceil_div(rows, 128);
+    const int work = ceil_div(m_tiles, cluster) * ceil_div(Ho, BN);
+    const int max_cl = num_sms() / cluster;
+    int ncl = work < max_cl ? work : max_cl;
+    if (work > max_cl) ncl = ceil_div(work, ceil_div(work, max_cl));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ncl * cluster);
+    cfg.blockDim = dim3(kThreadsF);
+    cfg.dynamicSmemBytes = kSmem2;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    const long long ldbits = (Ho + 31) / 32, ld_agg_ = ld_agg;
+    if (trace_on()) trace_before((const void*)k_pna_post_fused<2>, st);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_pna_post_fused<2>, mB, mC, msg, rowptr, row_node, x, (int)rows, (int)Ho, (int)H, (int)F,
+                                       BN, bias, flags, bits_out, ldbits, bucket_ptr, n_groups, agg_out, ld_agg_, round_mode);
+    if (trace_on()) trace_after(st);
+    if (e != cudaSuccess) return set_error((int)e, "pna_post_fused launch: %s", cudaGetErrorString(e));
+    count_tc_launches(1);
+    return check_launch("pna_post_fused");
 }
 
 }  // namespace gnnx

@@ -7,6 +7,8 @@ CPU path: a CPU tensor raises.
 
 from __future__ import annotations
 
+import os
+
 from typing import Optional, Tuple
 
 import torch
@@ -18,6 +20,11 @@ PREC_FP32, PREC_TF32 = 0, 1
 GEMM_RELU, GEMM_ACCUMULATE, GEMM_MASK_BITS, GEMM_FORCE_TC = 1, 2, 4, 8
 # tests set this to pin every tf32-tier product onto the tcgen05 kernels (products they cannot take then raise)
 FORCE_TC = False
+# PNAConv forward: aggregate -> first post Linear as ONE tcgen05 kernel whose A operand is produced in shared memory
+# (csrc/gemm_tc.cu: k_pna_post_fused).  Correct (tests/test_gpu_pna_fused.py) but OFF by default: on a B200 it takes 674 us
+# per cfg2 layer against 156 + 139 us for the aggregate kernel plus the grouped product it replaces (DESIGN.md section 8
+# has the ablation: a software agent in the stage hand-shake alone costs 150 us).  GNNX_FUSED_POST=1 switches it on.
+FUSED_POST = os.environ.get("GNNX_FUSED_POST", "0") == "1"
 # torch's names map onto the two tiers that exist: "highest" = CUDA-core fp32, "high" = tcgen05 tf32.  The reference's
 # "medium" (bf16-class products, train/train.py:54) has no kernels of its own here: it is served by the tf32 tier, which
 # is MORE precise than requested, and results are reported as tf32 (bench.py dtype), never as bf16.
@@ -405,6 +412,37 @@ def pna_aggregate_rows_fwd(m: Tensor, x: Tensor, g, buckets, towers: int) -> Ten
     lib().call("gnnx_pna_aggregate_rows_fwd", m.data_ptr(), g.rowptr.data_ptr(), g.num_nodes, towers, H // towers,
                buckets.row_node.data_ptr(), buckets.capacity, x.data_ptr(), out.data_ptr(), 5 * H, _stream())
     return out
+
+
+def pna_post_fused_ok(buckets, towers: int, f: int, h_out: int, precision: Optional[int] = None) -> bool:
+    """Whether ``pna_post_fused_fwd`` replaces ``pna_aggregate_rows_fwd`` + ``gemm_grouped`` for this layer shape."""
+    prec = _default_precision if precision is None else precision
+    if prec == PREC_FP32 or not FUSED_POST:
+        return False
+    level = _query("gnnx_pna_post_fused_supported", buckets.capacity, towers, f, h_out, prec)
+    return level >= (1 if FORCE_TC else 2)
+
+
+def pna_post_fused_fwd(m: Tensor, x: Tensor, g, buckets, towers: int, weff: Tensor, bias: Optional[Tensor], relu: bool,
+                       want_relu_bits: bool = False, want_agg: bool = False, precision: Optional[int] = None):
+    """``act([agg | x] W_eff(d)^T + b)`` in bucket order without materialising ``[agg | x]`` on the way in (one tcgen05
+    kernel whose A operand is produced in shared memory from the messages) -> ``(out [cap, Ho], bits | None, agg | None)``;
+    ``want_agg``: also keep the operand ([cap, 5H], what ``pna_aggregate_rows_fwd`` returns) for the backward."""
+    _chk(m, torch.float32, "m"); _chk(x, torch.float32, "x"); _chk(weff, torch.float32, "weff")
+    H = x.shape[1]
+    G = buckets.n_groups
+    Ho = weff.shape[0] // G
+    cap = buckets.capacity
+    if weff.shape != (G * Ho, 5 * H) or m.shape[1] != H:
+        raise ValueError("gnnx.pna_post_fused_fwd: operand shapes do not match the bucket layout")
+    out = torch.empty((cap, Ho), dtype=torch.float32, device=x.device)
+    bits = torch.empty((cap, (Ho + 31) // 32), dtype=torch.int32, device=x.device) if want_relu_bits else None
+    agg = torch.empty((cap, 5 * H), dtype=torch.float32, device=x.device) if want_agg else None
+    prec = _default_precision if precision is None else precision
+    lib().call("gnnx_pna_post_fused_fwd", _p(m), g.rowptr.data_ptr(), buckets.row_node.data_ptr(), cap, x.data_ptr(), towers,
+               H // towers, weff.data_ptr(), _ld(weff), buckets.bucket_ptr.data_ptr(), G, _p(bias), int(relu), out.data_ptr(), Ho,
+               Ho, _p(bits), _p(agg), 5 * H, prec, _stream())
+    return out, bits, agg
 
 
 def pna_aggregate_rows_bwd(dax: Tensor, m: Tensor, ax: Tensor, g, buckets, towers: int):

@@ -205,10 +205,24 @@ class PNAConvFn(Function):
         obits, weff, coef = None, prep.weff, prep.coef
         if bk is not None:
             # rows bucketed by in-degree: [agg | x] W_eff(d)^T, one grouped product with a third of the flops
-            agg = ops.pna_aggregate_rows_fwd(m, x, g, bk, T)                       # [cap, 5H], bucket order
+            fused = ops.pna_post_fused_ok(bk, T, F, Ho)
+            if fused:
+                # aggregate -> product in ONE tcgen05 kernel: [agg | x] is produced in shared memory, and written out
+                # only when a backward (its weight gradient) or a test tap will read it
+                want_bits = relu0 and train and meta.bucket_out
+                o, obits, agg = ops.pna_post_fused_fwd(m, x, g, bk, T, weff, pk.b0, relu0, want_relu_bits=want_bits,
+                                                       want_agg=train or CAPTURE_AGG is not None)
+            else:
+                agg = ops.pna_aggregate_rows_fwd(m, x, g, bk, T)                   # [cap, 5H], bucket order
             if CAPTURE_AGG is not None:
                 CAPTURE_AGG.append(dict(agg=ops.gather_rows(agg, bk.node_pos, cols=4 * T * F), m=m, g=g))
-            if meta.bucket_out:                        # the rest of the layer is row-wise: stay in bucket order
+            if fused:
+                if not meta.bucket_out:
+                    if relu0 and train:
+                        o, obits = ops.gather_rows(o, bk.node_pos, want_relu_bits=True)    # back to node order
+                    else:
+                        o = ops.gather_rows(o, bk.node_pos)
+            elif meta.bucket_out:                      # the rest of the layer is row-wise: stay in bucket order
                 if relu0 and train:
                     o, obits = ops.gemm_grouped(agg, weff, bk, trans_b=True, bias=pk.b0, relu=True, want_relu_bits=True)
                 else:

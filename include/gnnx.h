@@ -280,6 +280,20 @@ GNNX_API int gnnx_degree_buckets(const int32_t* rowptr, int64_t num_nodes, int32
 GNNX_API int gnnx_pna_aggregate_rows_fwd(const float* m, const int32_t* rowptr, int64_t num_nodes, int32_t towers, int32_t f,
                                 const int32_t* row_node, int64_t rows, const float* x, float* out, int64_t ld_out,
                                 void* stream);
+/* gnnx_pna_aggregate_rows_fwd and the degree-grouped first post Linear (gnnx_gemm_grouped on [agg | x], trans_b = 1) as
+ * ONE tcgen05 kernel: the [rows, 5H] operand is built in shared memory by producer warps straight from the messages
+ * and never crosses HBM on the way in (PNAConv.aggregate + post_nns[t][0] of PyG; called from models.py:211-216).
+ *   out[r, :] = act([agg | x](row r) weff[group(r)]^T + bias),  weff = [n_groups * h_out, 5H] (row stride ld_w)
+ * relu_bits_out: optional packed (out > 0) mask [rows, ceil(h_out/32)]; agg_out: optional [rows, 5H] copy of the operand
+ * (fp32, exactly what gnnx_pna_aggregate_rows_fwd writes) for the backward's weight gradient -- null in inference.
+ * Tensor-core tier only; gnnx_pna_post_fused_supported() returns 0 when the shape is not taken (rows % 256 == 0: the
+ * bucket capacity at align 256; f % 32 == 0; h_out % 16 == 0 and <= 256 or a multiple of 256), 1 when it is, 2 when
+ * the product is also large enough that gnnx_gemm_grouped would run it on the tensor cores (its small-product rule). */
+GNNX_API int32_t gnnx_pna_post_fused_supported(int64_t rows, int32_t towers, int32_t f, int32_t h_out, int32_t precision);
+GNNX_API int gnnx_pna_post_fused_fwd(const float* m, const int32_t* rowptr, const int32_t* row_node, int64_t rows, const float* x,
+                            int32_t towers, int32_t f, const float* weff, int64_t ld_w, const int32_t* bucket_ptr,
+                            int32_t n_groups, const float* bias, int32_t relu, float* out, int64_t ld_out, int32_t h_out,
+                            uint32_t* relu_bits_out, float* agg_out, int64_t ld_agg, int32_t precision, void* stream);
 /* Backward of the above: agg / dagg are read at row node_pos[i] (row stride ld); dm as gnnx_pna_aggregate_bwd;
  * dx (optional, [N,H]) receives dagg[node_pos[i], 4H:5H] -- the gradient of the copied input row in node order. */
 GNNX_API int gnnx_pna_aggregate_rows_bwd(const float* dagg, const float* m, const float* agg, int64_t ld,
