@@ -58,6 +58,48 @@ class BulkScreener:
         return out
 
 
+class HostResultStream:
+    """Predictions of successive batches streamed into ONE pinned host array without a synchronisation per batch: each
+    batch's rows are copied device -> host on a side stream behind an event, and the device tensor is kept alive until
+    its copy has drained (``record_stream``).  ``finish()`` waits once.  Replaces ``out.cpu().numpy()`` per shard."""
+
+    def __init__(self, rows: int, cols: int, device):
+        self.host = torch.empty((rows, cols), dtype=torch.float32).pin_memory()
+        self.stream = torch.cuda.Stream(device)
+        self.device = device
+        self.bytes = 0
+
+    def push(self, row0: int, pred: Tensor) -> None:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            self.host[row0:row0 + pred.shape[0]].copy_(pred, non_blocking=True)
+        pred.record_stream(self.stream)
+        self.bytes += pred.numel() * 4
+
+    def finish(self) -> Tensor:
+        self.stream.synchronize()
+        return self.host
+
+
+@torch.no_grad()
+def screen_to_host(model: torch.nn.Module, store: DeviceGraphStore, rank: int = 0, world: int = 1,
+                   max_nodes: int = 1 << 21, max_graphs: int = 16384) -> Tuple[Tensor, int]:
+    """A rank's whole shard through ``pred_with_bounds`` with the results landing in pinned host memory while the next
+    batches run -> ``(pinned [G_shard, num_para], bytes copied device -> host)``."""
+    scr = BulkScreener(model, store, rank, world, max_nodes, max_graphs)
+    was_training = model.training
+    model.eval()
+    try:
+        sink = HostResultStream(scr.num_graphs, model.num_para, store.device)
+        for k, (lo, hi) in enumerate(scr.batches):
+            sink.push(lo - scr.lo, scr.run_batch(k))
+        return sink.finish(), sink.bytes
+    finally:
+        model.train(was_training)
+
+
 def screen_parameters(model_msigmae: torch.nn.Module, store: DeviceGraphStore, munanb: Tensor, mw: Tensor,
                       model_assoc: Optional[torch.nn.Module] = None, assoc: Optional[Tensor] = None, rank: int = 0,
                       world: int = 1, max_nodes: int = 1 << 20, max_graphs: int = 16384,

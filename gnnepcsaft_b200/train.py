@@ -20,13 +20,34 @@ from . import ops
 from .graph import Batch
 
 
-class FlatParameters:
-    """Re-homes every parameter (and its gradient) of ``model`` into one contiguous fp32 buffer each."""
+def upper_half_bucket(name: str, depth: int) -> bool:
+    """True for the parameters whose gradients are complete FIRST in a backward pass of ``GNNePCSAFT``: the MLP head and
+    the upper half of the conv / batch-norm stack.  Their slice of the flat gradient can be all-reduced while the lower
+    layers are still running backward."""
+    parts = name.split(".")
+    if parts[0] == "mlp":
+        return True
+    if parts[0] in ("convs", "batch_norms") and len(parts) > 1 and parts[1].isdigit():
+        return int(parts[1]) >= (depth + 1) // 2
+    return False
 
-    def __init__(self, model: torch.nn.Module):
-        self.params = [p for p in model.parameters() if p.requires_grad]
-        if not self.params:
+
+class FlatParameters:
+    """Re-homes every parameter (and its gradient) of ``model`` into one contiguous fp32 buffer each.
+
+    ``early``: optional predicate on the parameter name.  Parameters it selects are laid out behind the others, so that
+    their gradients form ONE contiguous slice ``grad[early_lo:]`` (bucket 1) and the rest ``grad[:early_lo]`` (bucket 0);
+    ``arm_early_hook(fn)`` then calls ``fn()`` from inside the backward pass as soon as every bucket-1 gradient exists
+    and has been packed into the flat buffer."""
+
+    def __init__(self, model: torch.nn.Module, early=None):
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        if not named:
             raise ValueError("model has no trainable parameters")
+        first = [p for n, p in named if not (early and early(n))]
+        last = [p for n, p in named if early and early(n)]
+        self.params = first + last
+        self.n_first = len(first)
         dev = self.params[0].device
         sizes = [p.numel() for p in self.params]
         # keep every view 16-byte aligned so vectorised kernels can run on parameter slices
@@ -42,6 +63,39 @@ class FlatParameters:
             self.data[o:o + n].copy_(p.data.reshape(-1))
             p.data = self.data[o:o + n].view(p.shape)
         self.grad_views = [self.grad[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, self.offsets)]
+        self.early_lo = self.offsets[self.n_first] if self.n_first < len(self.params) else self.numel
+        self._early_fn = None
+        self._early_seen = 0
+        self._early_done = False
+        self._hooks = []
+
+    # -- bucket 1 ("early") gradients: packed and handed to a callback while the backward is still running
+    def arm_early_hook(self, fn) -> None:
+        """Install (once) the per-parameter hooks of bucket 1 and set the callback for the NEXT backward pass."""
+        if not self._hooks and self.n_first < len(self.params):
+            for p in self.params[self.n_first:]:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._on_early_grad))
+        self._early_fn, self._early_seen, self._early_done = fn, 0, False
+
+    def _on_early_grad(self, _p) -> None:
+        self._early_seen += 1
+        if self._early_fn is not None and not self._early_done and self._early_seen == len(self.params) - self.n_first:
+            self._early_done = True
+            self._pack(self.n_first, len(self.params))
+            self._early_fn()
+
+    def _pack(self, lo: int, hi: int) -> None:
+        src, dst = [], []
+        for p, v in zip(self.params[lo:hi], self.grad_views[lo:hi]):
+            if p.grad is None:
+                v.zero_()
+            elif p.grad.data_ptr() != v.data_ptr():
+                src.append(p.grad.reshape(v.shape))
+                dst.append(v)
+        if src:
+            torch._foreach_copy_(dst, src)
+        for p, v in zip(self.params[lo:hi], self.grad_views[lo:hi]):
+            p.grad = v
 
     def zero_grad(self) -> None:
         """Drop the per-parameter gradients: with ``.grad`` unset autograd hands each parameter the tensor the backward
@@ -52,17 +106,11 @@ class FlatParameters:
     def gather_grads(self) -> None:
         """Pack every ``p.grad`` into the flat gradient buffer with one multi-tensor copy; afterwards ``p.grad`` IS the
         matching view of the flat buffer.  Parameters the backward did not reach get a zero gradient."""
-        src, dst = [], []
-        for p, v in zip(self.params, self.grad_views):
-            if p.grad is None:
-                v.zero_()
-            elif p.grad.data_ptr() != v.data_ptr():
-                src.append(p.grad.reshape(v.shape))
-                dst.append(v)
-        if src:
-            torch._foreach_copy_(dst, src)
-        for p, v in zip(self.params, self.grad_views):
-            p.grad = v
+        if self._early_done:                       # bucket 1 was packed (and possibly all-reduced) during the backward
+            self._pack(0, self.n_first)
+        else:
+            self._pack(0, len(self.params))
+        self._early_fn = None
 
 
 def shard_range(num_items: int, rank: int, world: int):
@@ -104,9 +152,17 @@ class Trainer:
 
     def __init__(self, model: torch.nn.Module, lr: float = 1e-3, weight_decay: float = 1e-2, betas=(0.9, 0.999),
                  eps: float = 1e-5, target: str = "para", huber_delta: float = 0.01,
-                 process_group: Optional[dist.ProcessGroup] = None, distributed: Optional[bool] = None):
+                 process_group: Optional[dist.ProcessGroup] = None, distributed: Optional[bool] = None,
+                 overlap: bool = True):
         self.model = model
-        self.flat = FlatParameters(model)
+        depth = len(getattr(model, "convs", []))
+        self.distributed = dist.is_initialized() if distributed is None else distributed
+        self.world = dist.get_world_size(process_group) if self.distributed else 1
+        # data parallel: the gradients of the head and the upper half of the stack are complete halfway through the
+        # backward; their slice of the flat buffer is all-reduced (asynchronously, on NCCL's stream) under the rest of it
+        self.overlap = overlap and self.world > 1 and depth >= 2
+        self.flat = FlatParameters(model, (lambda n: upper_half_bucket(n, depth)) if self.overlap else None)
+        self._early_work = None
         self.lr, self.weight_decay, self.betas, self.eps = lr, weight_decay, betas, eps
         self.target, self.huber_delta = target, huber_delta
         self.exp_avg = torch.zeros_like(self.flat.data)
@@ -114,23 +170,43 @@ class Trainer:
         self.max_exp_avg_sq = torch.zeros_like(self.flat.data)
         self.step_count = 0
         self.pg = process_group
-        self.distributed = dist.is_initialized() if distributed is None else distributed
-        self.world = dist.get_world_size(self.pg) if self.distributed else 1
         if self.distributed:                                  # identical replicas to start from
             dist.broadcast(self.flat.data, src=0, group=self.pg)
+
+    def backward(self, pred: Tensor, dpred: Tensor) -> None:
+        """``pred.backward(dpred)`` with the gradients landing in the flat buffer (and, data parallel, the all-reduce of
+        the upper layers' slice started from inside the backward).  Call ``flat.zero_grad()`` before the forward."""
+        if self.overlap:
+            self.flat.arm_early_hook(self._reduce_early)
+        pred.backward(dpred)
+        self.flat.gather_grads()
 
     def forward_backward(self, batch: Batch) -> Tensor:
         self.flat.zero_grad()
         pred = self.model.forward_batch(batch)
         target = getattr(batch, self.target)
         out2, dpred = ops.relhuber_fwd_bwd(pred.detach().contiguous(), target.contiguous(), self.huber_delta)
-        pred.backward(dpred)
-        self.flat.gather_grads()
+        self.backward(pred, dpred)
         return out2
 
-    def optimizer_step(self) -> None:
-        if self.distributed and self.world > 1:
+    def _reduce_early(self) -> None:
+        """Called from inside the backward once bucket 1 is packed: its all-reduce runs under the lower layers' backward."""
+        self._early_work = dist.all_reduce(self.flat.grad[self.flat.early_lo:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+
+    def reduce_gradients(self) -> None:
+        """Sum the flat gradient over the ranks: ONE all-reduce, or -- with ``overlap`` -- the same bytes in two slices,
+        the first of which was started during the backward (``_reduce_early``)."""
+        if not (self.distributed and self.world > 1):
+            return
+        if self._early_work is not None:
+            dist.all_reduce(self.flat.grad[:self.flat.early_lo], op=dist.ReduceOp.SUM, group=self.pg)
+            self._early_work.wait()
+            self._early_work = None
+        else:
             dist.all_reduce(self.flat.grad, op=dist.ReduceOp.SUM, group=self.pg)   # the single collective of the step
+
+    def optimizer_step(self) -> None:
+        self.reduce_gradients()
         self.step_count += 1
         ops.adamw_amsgrad_(self.flat.data, self.flat.grad, self.exp_avg, self.exp_avg_sq, self.max_exp_avg_sq,
                            lr=self.lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,

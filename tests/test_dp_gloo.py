@@ -94,3 +94,76 @@ def test_node_balanced_batches():
         assert hi - lo <= 128 and (n[lo:hi].sum() <= 4096 or hi - lo == 1)
     assert node_balanced_batches([], 10, 10) == []
     assert node_balanced_batches([500], 10, 10) == [(0, 1)]
+
+
+class _Toy(torch.nn.Module):
+    """Names like GNNePCSAFT's: convs.{l}.*, batch_norms.{l}.*, mlp.*"""
+
+    def __init__(self):
+        super().__init__()
+        self.node_embed = torch.nn.Linear(9, 16)
+        self.convs = torch.nn.ModuleList([torch.nn.Linear(16, 16) for _ in range(4)])
+        self.batch_norms = torch.nn.ModuleList([torch.nn.LayerNorm(16) for _ in range(4)])
+        self.mlp = torch.nn.Linear(16, 3)
+
+    def forward(self, x):
+        h = self.node_embed(x)
+        for c, b in zip(self.convs, self.batch_norms):
+            h = torch.relu(b(c(h)))
+        return self.mlp(h)
+
+
+def _overlap_worker(rank, world, port, out):
+    from gnnepcsaft_b200.train import upper_half_bucket
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        res = {}
+        x, y = torch.randn(40, 9), torch.randn(40, 3)
+        lo, hi = shard_range(40, rank, world)
+        for mode in ("single", "two_buckets"):
+            torch.manual_seed(1)
+            model = _Toy()
+            flat = FlatParameters(model, (lambda n: upper_half_bucket(n, 4)) if mode == "two_buckets" else None)
+            dist.broadcast(flat.data, src=0)
+            fired = {}
+
+            def early():
+                # called from INSIDE the backward: the lower layers have no gradient yet, the upper slice is packed
+                fired["lower_pending"] = model.convs[0].weight.grad is None
+                fired["work"] = dist.all_reduce(flat.grad[flat.early_lo:], async_op=True)
+
+            for step in range(2):                              # twice: the hooks persist, the callback is re-armed
+                flat.zero_grad()
+                fired.clear()
+                if mode == "two_buckets":
+                    flat.arm_early_hook(early)
+                ((model(x[lo:hi]) - y[lo:hi]) ** 2).sum().backward()
+                flat.gather_grads()
+                if mode == "two_buckets":
+                    assert fired.get("lower_pending") is True, "the early slice must be reduced while the backward is still running"
+                    dist.all_reduce(flat.grad[:flat.early_lo])
+                    fired["work"].wait()
+                else:
+                    dist.all_reduce(flat.grad)
+            names = {id(p): n for n, p in model.named_parameters()}
+            res[mode] = {names[id(p)]: p.grad.clone() for p in flat.params}
+            if mode == "two_buckets":
+                early_names = [names[id(p)] for p in flat.params[flat.n_first:]]
+                assert all(upper_half_bucket(n, 4) for n in early_names) and len(early_names) == 2 * 2 + 2 * 2 + 2
+                assert flat.early_lo == flat.offsets[flat.n_first]
+        if rank == 0:
+            torch.save(res, out)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_bucket_overlapped_allreduce_equals_the_single_one(tmp_path):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_overlap_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    res = torch.load(out)
+    assert set(res["single"]) == set(res["two_buckets"])
+    for n, g in res["single"].items():
+        assert torch.equal(g, res["two_buckets"][n]), n

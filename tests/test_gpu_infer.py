@@ -44,6 +44,13 @@ def test_sharded_screening_matches_oracle_and_unsharded():
     assert sum(p.shape[0] for p in parts) == 300
     assert_close(torch.cat(parts), ref, 1e-4, 1e-5, "3 shards vs oracle")
     assert not mp.training
+    # the streamed variant (pinned host array filled on a side stream, one wait at the end) gives the same numbers
+    from gnnepcsaft_b200.infer import screen_to_host
+    host, nbytes = screen_to_host(mp, store, max_nodes=2000, max_graphs=64)
+    assert host.is_pinned() and nbytes == 300 * 3 * 4
+    assert torch.equal(host, out.cpu())
+    h1, _ = screen_to_host(mp, store, 1, 3, max_nodes=1500, max_graphs=50)
+    assert torch.equal(h1, parts[1].cpu())
 
 
 def test_output_stage_assembles_the_feos_parameter_vector(tmp_path):
