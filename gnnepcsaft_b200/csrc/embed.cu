@@ -35,44 +35,54 @@ __global__ void k_embed_fwd(const uint8_t* __restrict__ idx, int rows, int K, co
     }
 }
 
-constexpr int kEmbSlab = 32;   // columns per CTA in the backward
-constexpr int kEmbFlight = 16; // rows in flight per thread: the row walk is a latency chain (4 in flight ran at 0.5 TB/s)
+constexpr int kEmbSlab = 128;  // columns per CTA in the backward: 4 per lane (ncu r2a: the 1-column version was issue-bound,
+                               // 18 instructions per update at 0.5 TB/s; index / address work is now shared by 4 columns)
+constexpr int kEmbFlight = 8;  // rows in flight per thread (float4 each): the row walk is a latency chain
 
-// grid: (ceil(H/32), nchunks); block: (32, K).  smem: table_rows * 32 floats.
+// grid: (ceil(H/128), nchunks); block: (32, K).  smem: table_rows * 128 floats.
 __global__ void k_embed_bwd_partial(const uint8_t* __restrict__ idx, int rows, int K,
                                     const int* __restrict__ offsets, int table_rows,
                                     const float* __restrict__ dout, int H, int rows_per_chunk,
                                     float* __restrict__ partial, NodeDropout drop) {
     pdl_enter();
     extern __shared__ float tab[];
-    int c = blockIdx.x * kEmbSlab + threadIdx.x;
-    int k = threadIdx.y;
-    int tid = threadIdx.y * 32 + threadIdx.x, nthreads = blockDim.x * blockDim.y;
+    const int c = blockIdx.x * kEmbSlab + threadIdx.x * 4;
+    const int k = threadIdx.y;
+    const int tid = threadIdx.y * 32 + threadIdx.x, nthreads = blockDim.x * blockDim.y;
     for (int i = tid; i < table_rows * kEmbSlab; i += nthreads) tab[i] = 0.f;
     __syncthreads();
-    int r0 = blockIdx.y * rows_per_chunk;
-    int r1 = min(rows, r0 + rows_per_chunk);
-    int off = offsets[k];
-    if (c < H) {
+    const int r0 = blockIdx.y * rows_per_chunk;
+    const int r1 = min(rows, r0 + rows_per_chunk);
+    const int off = offsets[k];
+    auto fetch = [&](int r) -> float4 {
+        const long long o = (long long)r * H + c;
+        float4 v = ldg4(dout + o);
+        v.x = drop_apply(drop, o, v.x); v.y = drop_apply(drop, o + 1, v.y);
+        v.z = drop_apply(drop, o + 2, v.z); v.w = drop_apply(drop, o + 3, v.w);
+        return v;
+    };
+    auto update = [&](int row, const float4& v) {          // feature k owns its table rows: no other warp touches them
+        float4* t = reinterpret_cast<float4*>(tab + row * kEmbSlab + threadIdx.x * 4);
+        float4 a = *t;
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+        *t = a;
+    };
+    if (c < H) {                                            // H % 4 == 0: a lane's four columns are in or out together
         int r = r0;
-        for (; r + kEmbFlight <= r1; r += kEmbFlight) {       // independent loads in flight, then updates in row order
-            float v[kEmbFlight];
+        for (; r + kEmbFlight <= r1; r += kEmbFlight) {     // independent loads in flight, then updates in row order
+            float4 v[kEmbFlight];
             int ix[kEmbFlight];
 #pragma unroll
             for (int u = 0; u < kEmbFlight; ++u) {
-                v[u] = drop_apply(drop, (long long)(r + u) * H + c, __ldg(dout + (long long)(r + u) * H + c));
+                v[u] = fetch(r + u);
                 ix[u] = off + idx[(long long)(r + u) * K + k];
             }
 #pragma unroll
-            for (int u = 0; u < kEmbFlight; ++u) tab[ix[u] * kEmbSlab + threadIdx.x] += v[u];
+            for (int u = 0; u < kEmbFlight; ++u) update(ix[u], v[u]);
         }
-        for (; r < r1; ++r) {
-            float v = drop_apply(drop, (long long)r * H + c, __ldg(dout + (long long)r * H + c));
-            tab[(off + idx[(long long)r * K + k]) * kEmbSlab + threadIdx.x] += v;
-        }
+        for (; r < r1; ++r) update(off + idx[(long long)r * K + k], fetch(r));
     }
     __syncthreads();
-    // feature k owns table rows [offsets[k], offsets[k+1]) exclusively, so the slab is race-free
     float* dst = partial + (long long)blockIdx.y * table_rows * H;
     for (int i = tid; i < table_rows * kEmbSlab; i += nthreads) {
         int tr = i / kEmbSlab, cc = blockIdx.x * kEmbSlab + (i % kEmbSlab);
@@ -92,7 +102,7 @@ __global__ void k_reduce_partials(const float* __restrict__ partial, int nchunks
 
 static int embed_chunks(int64_t rows, int32_t H) {
     int slabs = ceil_div(H, kEmbSlab);
-    int target = max(1, (num_sms() * 6) / slabs);
+    int target = max(1, (num_sms() * 2) / slabs);       // two 89 KB slabs per SM are resident; every chunk costs a [table, H] partial
     int by_rows = max(1, (int)((rows + 255) / 256));    // at least ~256 rows per chunk
     return min(target, by_rows);
 }
@@ -122,6 +132,7 @@ int gnnx_embed_sum_bwd(const uint8_t* idx, int64_t rows, int32_t K, const int32_
                        const float* dout, int32_t H, float dropout_p, int64_t seed, float* dtable, void* ws, size_t ws_bytes,
                        void* stream) {
     GNNX_REQUIRE(K >= 1 && K <= 32, "embed_sum_bwd: num_features must be in [1,32]");
+    GNNX_REQUIRE(H % 4 == 0 && ((uintptr_t)dout & 15) == 0, "embed_sum_bwd: hidden must be a multiple of 4 and dout 16-byte aligned");
     GNNX_REQUIRE(ws_bytes >= gnnx_embed_sum_bwd_workspace_bytes(rows, table_rows, H), "embed_sum_bwd: workspace too small");
     cudaStream_t st = as_stream(stream);
     long long count = (long long)table_rows * H;

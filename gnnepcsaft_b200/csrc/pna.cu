@@ -327,14 +327,17 @@ k_pna_aggregate_bwd(const float* __restrict__ dagg, const float* __restrict__ m,
                 }
             }
         }
-        float inv_cnt = 1.f / cnt;
+        // the kernel is issue-bound (ncu: 58 % issue-active, 3.9 long-scoreboard stalls per issue): the coefficient
+        // divisions use the 2-ulp fast divide -- the tie counts are small integers and the gradients are held to
+        // rel 1e-4 --, while everything that DECIDES a branch (min / max equality, the Std mask) stays exact above
+        float inv_cnt = __fdividef(1.f, cnt);
         F4 cmean, cmn, cmx, csd;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             cmean.a[j] = gmean.a[j] * inv_cnt;
-            cmn.a[j] = gmn.a[j] / nmn.a[j];
-            cmx.a[j] = gmx.a[j] / nmx.a[j];
-            csd.a[j] = sd.a[j] > 0.f ? gsd.a[j] * inv_cnt / sd.a[j] : 0.f;   // d std / d m_e = (m_e - mean) / (cnt * std)
+            cmn.a[j] = __fdividef(gmn.a[j], nmn.a[j]);
+            cmx.a[j] = __fdividef(gmx.a[j], nmx.a[j]);
+            csd.a[j] = sd.a[j] > 0.f ? __fdividef(gsd.a[j] * inv_cnt, sd.a[j]) : 0.f;   // d std / d m_e = (m_e - mean) / (cnt * std)
         }
         auto grad_row = [&](const F4& v, int k) {
             F4 g;
