@@ -313,7 +313,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t tx = kA2 + (uint32_t)BN * 128u;
-            const int half = BN / 2;
+            const int half = BN / kCluster;                      // rows (K-major) / columns (MN-major) of B this CTA fetches for the cluster
+            constexpr uint16_t kAll = (uint16_t)((1u << kCluster) - 1u);
             for (int w = cid; w < work; w += ncl) {
                 const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
                 // grouped product: the row block's group (bucket boundaries are multiples of 128 * kCluster rows, so both
@@ -331,8 +332,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         if (kBMN) tma_load_3d(sm.b(stage), &tmB, sm.full(stage), 0, kb * kBK + goff, n0 / 32);
                         else tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kb * kBK, n0 + goff);
                     } else {
-                        if (kBMN) tma_load_3d_mc(sm.b(stage) + rank * (half / 32) * 4096, &tmB, sm.full(stage), 0, kb * kBK + goff, n0 / 32 + rank * (half / 32), 3);
-                        else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kb * kBK, n0 + rank * half + goff, 3);
+                        if (kBMN) tma_load_3d_mc(sm.b(stage) + rank * (half / 32) * 4096, &tmB, sm.full(stage), 0, kb * kBK + goff, n0 / 32 + rank * (half / 32), kAll);
+                        else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kb * kBK, n0 + rank * half + goff, kAll);
                     }
                     if (++stage == kStages2) { stage = 0; phase ^= 1; }
                 }
@@ -357,7 +358,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         const uint64_t adesc = make_smem_desc(sm.a(stage) + k * 32, 16, 1024, kLayoutSw128);
                         mma_tf32(tmem_base + buf * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
                     }
-                    if (kCluster > 1) mma_commit_mc(sm.empty(stage), 3); else mma_commit(sm.empty(stage));
+                    if (kCluster > 1) mma_commit_mc(sm.empty(stage), (uint16_t)((1u << kCluster) - 1u)); else mma_commit(sm.empty(stage));
                     if (kb == KB - 1) mma_commit(sm.tmem_full(buf));
                     if (++stage == kStages2) { stage = 0; phase ^= 1; }
                 }
@@ -1110,6 +1111,8 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             return GNNX_OK;
         });
         if (rc) return rc;
@@ -1118,7 +1121,15 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     if (!ta) {
         const int BN = (int)(N >= 256 ? 256 : (tb ? (N + 15) / 16 * 16 : N));
         const int m_tiles = ceil_div(M, 128);
-        const int cluster = (m_tiles >= 2 && (tb ? (BN % 16 == 0) : (BN % 64 == 0))) ? 2 : 1;
+        // 2-CTA clusters halve the weight traffic from L2 per output tile.  4-CTA clusters (GNNX_GEMM_CLUSTER=4) halve it
+        // again but were measured SLOWER on a B200 (cfg2 step: forward products 62.8 us against 58.9, dX 68.9 against 65.1):
+        // these products are not bound by L2 -> SM bandwidth, and fewer 4-CTA clusters fit the GPCs.  Default: pairs.
+        static std::once_flag cl_once;
+        static int max_cluster = 2;
+        std::call_once(cl_once, [] { const char* e = getenv("GNNX_GEMM_CLUSTER"); if (e && (e[0] == '1' || e[0] == '2' || e[0] == '4')) max_cluster = e[0] - '0'; });
+        int cluster = (m_tiles >= 2 && (tb ? (BN % 16 == 0) : (BN % 64 == 0))) ? 2 : 1;
+        if (cluster == 2 && max_cluster >= 4 && !bucket_ptr && m_tiles >= 16 && (tb ? (BN % 32 == 0) : (BN % 128 == 0))) cluster = 4;
+        if (cluster > max_cluster) cluster = max_cluster;
         if (make_map_kmajor(&mA, A, M, K, lda, 128)) return GNNX_ERR_INVALID;
         if (tb) {                                        // grouped: B stacks one [N, K] / [K, N] weight block per group
             if (make_map_kmajor(&mB, B, N * n_groups, K, ldb, BN / cluster)) return GNNX_ERR_INVALID;
@@ -1128,14 +1139,40 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         const int group_rows = (int)(tb ? N : K);
         if (make_map_store(&mC, C, M, N, ldc)) return GNNX_ERR_INVALID;
         const int work = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
-        const int max_cl = num_sms() / cluster;
+        int max_cl = num_sms() / cluster;
+        if (cluster == 4) {
+            // clusters are placed inside one GPC: how many 4-CTA clusters fit at once is a property of the die, not SMs / 4
+            static std::atomic<int> fit4{0};
+            int f = fit4.load();
+            if (f == 0) {
+                cudaLaunchConfig_t q = {};
+                q.gridDim = dim3(num_sms() / 4 * 4); q.blockDim = dim3(kThreads2); q.dynamicSmemBytes = kSmem2;
+                cudaLaunchAttribute qa[1];
+                qa[0].id = cudaLaunchAttributeClusterDimension;
+                qa[0].val.clusterDim.x = 4; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+                q.attrs = qa; q.numAttrs = 1;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, k_gemm_tf32_rows2<false, 4>, &q) != cudaSuccess || n < 1) { cudaGetLastError(); n = -1; }
+                fit4.store(n); f = n;
+            }
+            if (f < 0) {                                         // the query failed: stay with pairs
+                cluster = 2;
+                if (tb) { if (make_map_kmajor(&mB, B, N * n_groups, K, ldb, BN / cluster)) return GNNX_ERR_INVALID; }
+                else if (make_map_mnmajor(&mB, B, K * n_groups, N, ldb, BN / 32 / cluster)) return GNNX_ERR_INVALID;
+                max_cl = num_sms() / cluster;
+            } else if (f < max_cl) {
+                max_cl = f;
+            }
+        }
+        const int work_c = ceil_div(m_tiles, cluster) * ceil_div(N, BN);
         // Balanced rounds: 400 work items on 74 clusters are 5 full rounds plus one that keeps 30 clusters busy at their
         // per-SM rate; ceil(400 / 6) = 67 clusters all run 6 rounds at the chip's HBM rate instead (GNNX_GEMM_BALANCE=0: off)
         static std::once_flag bal_once;
         static int balance = 1;
         std::call_once(bal_once, [] { const char* e = getenv("GNNX_GEMM_BALANCE"); balance = (e && e[0] == '0') ? 0 : 1; });
-        int ncl = work < max_cl ? work : max_cl;
-        if (balance && work > max_cl) ncl = ceil_div(work, ceil_div(work, max_cl));
+        int ncl = work_c < max_cl ? work_c : max_cl;
+        if (balance && work_c > max_cl) ncl = ceil_div(work_c, ceil_div(work_c, max_cl));
+        (void)work;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(ncl * cluster);
         cfg.blockDim = dim3(kThreads2);
@@ -1162,9 +1199,13 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         }
         cudaError_t e;
         if (trace_on())
-            trace_before(cluster == 2 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 2> : (const void*)k_gemm_tf32_rows2<true, 2>)
+            trace_before(cluster == 4 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 4> : (const void*)k_gemm_tf32_rows2<true, 4>)
+                         : cluster == 2 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 2> : (const void*)k_gemm_tf32_rows2<true, 2>)
                                       : (tb ? (const void*)k_gemm_tf32_rows2<false, 1> : (const void*)k_gemm_tf32_rows2<true, 1>), st);
-        if (cluster == 2)
+        if (cluster == 4)
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
+        else if (cluster == 2)
             e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
                    : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
         else
