@@ -615,7 +615,7 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
                 const int mbase = (w / n_tiles) * kCluster * 128;
                 for (int d = 1; d < n_groups; ++d) goff += (mbase >= __ldg(bucket_ptr + d)) ? N : 0;
                 for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait_poll(sm.empty(stage), phase ^ 1);
+                    mbar_wait_sleep(sm.empty(stage), phase ^ 1, 64);
                     mbar_expect_tx(sm.full(stage), tx);
                     if (kCluster == 1) tma_load_2d(sm.b(stage), &tmB, sm.full(stage), kcoord(kb), n0 + goff);
                     else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &tmB, sm.full(stage), kcoord(kb), n0 + rank * half + goff, 3);
@@ -630,10 +630,10 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
             uint32_t phase = 0, i = 0;
             for (int w = cid; w < work; w += ncl, ++i) {
                 const uint32_t buf = i & 1;
-                mbar_wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                mbar_wait_sleep(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1, 64);
                 tc_fence_after();
                 for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait_poll(sm.full(stage), phase);
+                    mbar_wait_sleep(sm.full(stage), phase, 32);
                     tc_fence_after();
 #pragma unroll
                     for (int k = 0; k < kBK / 8; ++k) {
@@ -691,7 +691,7 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
             // one poller per warp: 256 threads spinning on try_wait keep the barrier's shared-memory word busy and delay
             // the very arrivals (tcgen05.commit, TMA complete_tx) they are waiting for
             auto wait_empty = [&](uint32_t k) {
-                if (lane == 0 && !(round_mode & 1024)) mbar_wait_poll(sm.empty((int)(k % kStages2)), ((k / kStages2) & 1u) ^ 1u);
+                if (lane == 0 && !(round_mode & 1024)) mbar_wait_sleep(sm.empty((int)(k % kStages2)), ((k / kStages2) & 1u) ^ 1u, 20);
                 __syncwarp();
             };
             auto publish = [&](uint32_t k) {
@@ -749,16 +749,13 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
             };
 
             if (dmax <= 2) {
-                float4 va[4][2], vb[4][2];                    // unit u in va while unit u + 1 lands in vb, and vice versa
-                load_agg(va, 0);
+                // (a double-buffered variant that issued unit u + 1's loads before reducing unit u spilled ~45 registers
+                // to local memory, whose lines the streaming loads keep evicting from the 28 KB L1: 90 % local-load misses)
 #pragma unroll 1
-                for (int u = 0; u < NU; u += 2) {
-                    if (u + 1 < NU) { if (u + 1 < HB) load_agg(vb, u + 1); else load_x(vb, u + 1); }
-                    if (u < HB) produce_agg(va, u); else produce_x(va, u);
-                    if (u + 1 < NU) {
-                        if (u + 2 < NU) { if (u + 2 < HB) load_agg(va, u + 2); else load_x(va, u + 2); }
-                        if (u + 1 < HB) produce_agg(vb, u + 1); else produce_x(vb, u + 1);
-                    }
+                for (int u = 0; u < NU; ++u) {
+                    float4 v[4][2];
+                    if (u < HB) { load_agg(v, u); produce_agg(v, u); }
+                    else { load_x(v, u); produce_x(v, u); }
                 }
             } else {
 #pragma unroll 1
@@ -782,7 +779,7 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
         for (int w = cid; w < work; w += ncl, ++i) {
             const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
             const uint32_t buf = i & 1;
-            mbar_wait(sm.tmem_full(buf), (i >> 1) & 1);
+            mbar_wait_sleep(sm.tmem_full(buf), (i >> 1) & 1, 256);
             tc_fence_after();
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M && !(round_mode & 256))

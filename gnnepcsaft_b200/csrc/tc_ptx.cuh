@@ -66,6 +66,30 @@ __device__ __forceinline__ void mbar_wait_poll(uint32_t bar, uint32_t parity) {
     }
 }
 
+// Waiting with back-off: a role that spins on try_wait is always ready to issue and competes for its scheduler's issue
+// slots with the warps that share the SM sub-partition.  In k_pna_post_fused those are the producer warps, whose
+// instruction stream IS the critical path; waiters there sleep between polls so the slots go to the producers.
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t it = 0;; ++it) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        __nanosleep(ns);
+        if ((it & 4095u) == 4095u) {
+            long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ll) __trap();
+        }
+    }
+}
+
 // ------------------------------------------------------------------ TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");

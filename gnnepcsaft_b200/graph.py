@@ -27,9 +27,9 @@ class DegreeBuckets:
 
     __slots__ = ("n_groups", "node_pos", "row_node", "bucket_ptr", "err_flag", "capacity", "_tables")
 
-    def __init__(self, rowptr: Tensor, n_groups: int):
+    def __init__(self, rowptr: Tensor, n_groups: int, err: Optional[Tensor] = None):
         self.n_groups = n_groups
-        self.node_pos, self.row_node, self.bucket_ptr, self.err_flag, self.capacity = ops.degree_buckets(rowptr, n_groups)
+        self.node_pos, self.row_node, self.bucket_ptr, self.err_flag, self.capacity = ops.degree_buckets(rowptr, n_groups, err)
         self._tables = {}
 
     def split_table(self, splits: int) -> Tensor:
@@ -43,7 +43,7 @@ class GraphIndex:
     """dst-sorted CSR + src-sorted view of one (batched, block-diagonal) ``edge_index``."""
 
     __slots__ = ("num_nodes", "num_edges", "rowptr", "csr_src", "csr_eid", "pos_of_eid", "colptr", "csc_pos",
-                 "csc_dst", "err_flag", "_codes", "max_degree", "_buckets")
+                 "csc_dst", "err_flag", "_codes", "max_degree", "_buckets", "degree_hint", "_status_host")
 
     def __init__(self, num_nodes: int, num_edges: int, parts):
         self.num_nodes, self.num_edges = num_nodes, num_edges
@@ -51,7 +51,9 @@ class GraphIndex:
          self.err_flag) = parts
         self._codes = None
         self.max_degree = None        # host-side bound on the in-degree, when the collator knows one
+        self.degree_hint = None       # a bound the CALLER vouches for (the dataset histogram behind PNAConv's `deg`): checked on the device
         self._buckets = None
+        self._status_host = None      # (pinned copy of the status words, event) queued by the hinted bucketing
 
     def degree_buckets(self) -> Optional[DegreeBuckets]:
         """In-degree buckets of this batch, or ``None`` when it has more than ``ops.MAX_GROUPS`` degree classes
@@ -59,6 +61,26 @@ class GraphIndex:
         in-degree is read back once per batch (one device->host sync) -- together with the batch's error flags, so
         an out-of-range ``edge_index`` / feature id raises here like PyG / torch.nn.Embedding do, at no extra sync."""
         if self._buckets is None:
+            if self.max_degree is None and self.degree_hint is not None and self.degree_hint < ops.MAX_GROUPS:
+                # no read-back: bucket with the hinted number of degree classes; a node beyond it raises the batch's
+                # ST_DEGREE_OVERFLOW status word (read_status() raises; GNNePCSAFT.forward reads it one call later)
+                st = self.err_flag[ops.ST_DEGREE_OVERFLOW:ops.ST_DEGREE_OVERFLOW + 1]
+                self._buckets = DegreeBuckets(self.rowptr, self.degree_hint + 1, st)
+                # the status words travel to pinned memory on a copy stream, behind an event: reading them later
+                # (read_status_async) waits for THIS point of the stream only, not for whatever was queued after it
+                dev = self.rowptr.device
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(dev))
+                cs = _status_stream(dev)
+                cs.wait_event(ev)
+                host = torch.empty(ops.STATUS_WORDS, dtype=torch.int32).pin_memory()
+                with torch.cuda.stream(cs):
+                    host.copy_(self.err_flag, non_blocking=True)
+                    done = torch.cuda.Event()
+                    done.record(cs)
+                self.err_flag.record_stream(cs)
+                self._status_host = (host, done)
+                return self._buckets
             if self.max_degree is None:
                 ops.degree_hist(self.rowptr, torch.zeros(1, dtype=torch.int64, device=self.rowptr.device),
                                 self.err_flag[ops.ST_MAX_DEGREE:ops.ST_MAX_DEGREE + 1])
@@ -66,15 +88,31 @@ class GraphIndex:
             self._buckets = DegreeBuckets(self.rowptr, self.max_degree + 1) if self.max_degree < ops.MAX_GROUPS else False
         return self._buckets or None
 
+    def read_status_async(self) -> Optional[List[int]]:
+        """The status words as they were right after a hinted ``degree_buckets()`` (copied to pinned memory on a side
+        stream at that point): waits for that copy only.  ``None`` when no such copy was queued.  Raises like ``read_status``."""
+        if self._status_host is None:
+            return None
+        host, done = self._status_host
+        done.synchronize()
+        return self._raise_on_flags(host.tolist())
+
     def read_status(self) -> List[int]:
         """The batch's status words (``ops.ST_*``) on the host -- ONE device->host sync; raises on any error flag."""
-        vals = self.err_flag.tolist()
+        return self._raise_on_flags(self.err_flag.tolist())
+
+    @staticmethod
+    def _raise_on_flags(vals: List[int]) -> List[int]:
         if vals[ops.ST_EDGE]:
             raise IndexError("edge_index contains node ids outside [0, num_nodes)")
         if vals[ops.ST_ATOM]:
             raise IndexError("x contains an atom feature id outside its OGB vocabulary (gnnepcsaft/data/ogb_utils.py:9-23)")
         if vals[ops.ST_BOND]:
             raise IndexError("edge_attr contains a bond feature id outside its OGB vocabulary (gnnepcsaft/data/ogb_utils.py:24-33)")
+        if vals[ops.ST_DEGREE_OVERFLOW]:
+            raise IndexError("a node's in-degree exceeds the degree histogram the PNA model was built with (`deg`): the degree-grouped "
+                             "path was bucketed with too few classes and this batch's result is wrong; set model.degree_hint = None "
+                             "(one read-back per batch) or rebuild the histogram with calc_deg over this data")
         return vals
 
     @staticmethod
@@ -101,6 +139,15 @@ class GraphIndex:
 
 
 _INDEX_CACHE: dict = {}
+_STATUS_STREAMS: dict = {}
+
+
+def _status_stream(device) -> "torch.cuda.Stream":
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    s = _STATUS_STREAMS.get(key)
+    if s is None:
+        s = _STATUS_STREAMS[key] = torch.cuda.Stream(torch.device("cuda", key))
+    return s
 
 
 def graph_index_for(edge_index: Tensor, num_nodes: int) -> GraphIndex:

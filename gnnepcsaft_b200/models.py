@@ -106,6 +106,13 @@ class GNNePCSAFT(Module):
         )
         self._bounds_dev = None
         self._prep_cache = None
+        # PNA: the dataset's largest in-degree (the length of the `deg` histogram the layers were built from) bounds every
+        # batch of that dataset, so the reference-signature forward can bucket nodes by degree without reading the batch's
+        # maximum back (one host sync per batch less).  A batch that breaks the bound is flagged on the device and raises
+        # at the next forward / validate(); None switches the hint off.
+        deg = config.get("deg") if config.get("conv") == "PNA" else None
+        self.degree_hint = (len(deg) - 1) if deg is not None and len(deg) >= 1 else None
+        self._hinted = None
 
     # -- reference signature -------------------------------------------------------------
     def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Union[Tensor, None],
@@ -117,7 +124,19 @@ class GNNePCSAFT(Module):
             return self.forward_custom_ops(x, edge_index, edge_attr, batch, num_graphs)
         b = batch_from_reference_tensors(x.contiguous(), edge_index.contiguous(), edge_attr.contiguous(), batch,
                                          num_graphs)
+        self.check_pending()
+        if self.degree_hint is not None and b.index.max_degree is None:
+            if b.index._buckets is None:                 # (a caller may have bucketed ahead, with the same hint)
+                b.index.degree_hint = self.degree_hint
+            self._hinted = b.index
         return self.forward_batch(b)
+
+    def check_pending(self) -> None:
+        """Raise if the PREVIOUS reference-signature batch broke the degree hint (its status words are read now: that
+        batch's index kernels finished long ago, so this does not stall the launch queue)."""
+        g, self._hinted = self._hinted, None
+        if g is not None:
+            g.read_status_async()
 
     # -- the torch.library face: every step is a torch.ops.gnnx.* custom op or a plain ATen op ----------------
     def forward_custom_ops(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor, batch: Union[Tensor, None],

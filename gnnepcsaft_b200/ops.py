@@ -95,7 +95,7 @@ def _query(name: str, *args) -> int:
 
 # ------------------------------------------------------------------ collator
 STATUS_WORDS = 8
-ST_EDGE, ST_ATOM, ST_BOND, ST_LAST_GRAPH, ST_MAX_DEGREE = 0, 1, 2, 3, 4
+ST_EDGE, ST_ATOM, ST_BOND, ST_LAST_GRAPH, ST_MAX_DEGREE, ST_DEGREE_OVERFLOW = 0, 1, 2, 3, 4, 5
 
 
 def csr_build(edge_index: Optional[Tensor], num_nodes: int, src32: Optional[Tensor] = None,
@@ -382,8 +382,9 @@ MAX_GROUPS = 16
 GROUP_ALIGN = 256       # bucket padding: one 2-CTA row block of the tensor-core kernel
 
 
-def degree_buckets(rowptr: Tensor, n_groups: int):
-    """Stable bucketing of the nodes by in-degree -> ``(node_pos[N], row_node[cap], bucket_ptr[n_groups+1], err, cap)``."""
+def degree_buckets(rowptr: Tensor, n_groups: int, err: Optional[Tensor] = None):
+    """Stable bucketing of the nodes by in-degree -> ``(node_pos[N], row_node[cap], bucket_ptr[n_groups+1], err, cap)``.
+    ``err`` (int32 [1], optional): where the "a node has in-degree >= n_groups" flag goes (e.g. a batch status word)."""
     _chk(rowptr, torch.int32, "rowptr")
     if not 1 <= n_groups <= MAX_GROUPS:
         raise ValueError(f"gnnx.degree_buckets: 1..{MAX_GROUPS} groups")
@@ -391,7 +392,9 @@ def degree_buckets(rowptr: Tensor, n_groups: int):
     cap = _query("gnnx_degree_buckets_capacity", N, n_groups, GROUP_ALIGN)
     i32 = dict(dtype=torch.int32, device=dev)
     node_pos, row_node = torch.empty(N, **i32), torch.empty(cap, **i32)
-    bucket_ptr, err = torch.empty(n_groups + 1, **i32), torch.empty(1, **i32)
+    bucket_ptr = torch.empty(n_groups + 1, **i32)
+    if err is None:
+        err = torch.empty(1, **i32)
     ws, nb = _ws(_query("gnnx_degree_buckets_workspace_bytes", N, n_groups), dev)
     lib().call("gnnx_degree_buckets", rowptr.data_ptr(), N, n_groups, GROUP_ALIGN, node_pos.data_ptr(), row_node.data_ptr(),
                cap, bucket_ptr.data_ptr(), err.data_ptr(), _p(ws), nb, _stream())

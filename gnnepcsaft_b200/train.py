@@ -146,6 +146,35 @@ def cosine_warm_restarts_lr(base_lr: float, epoch: int, t_0: int, t_mult: int = 
     return eta_min + (base_lr - eta_min) * (1 + math.cos(math.pi * t_cur / t_i)) / 2
 
 
+class LossReadback:
+    """Per-step device -> host read of ``[loss, mape]`` without stalling the launch queue: step i's values are copied into
+    pinned memory asynchronously and handed out when step i + 1 calls ``push`` (the host then waits on an event that
+    completed long ago).  A ``loss.item()`` per step drains the queue every step, and the GPU then idles while the host
+    issues the ~60 small launches at the head of the next step (measured: 1.3 ms of a 16.2 ms cfg2 step).  The
+    reference logs through Lightning's ``self.log`` (models.py:93-106), which does not synchronise per step either."""
+
+    def __init__(self, device, width: int = 2):
+        self.slots = [torch.zeros(width, dtype=torch.float32).pin_memory() for _ in range(2)]
+        self.events = [torch.cuda.Event(), torch.cuda.Event()]
+        self.n = 0
+        self.device = device
+
+    def push(self, values: Tensor):
+        """Queue the D2H copy of this step's values; returns the PREVIOUS step's values as a list (None at step 0)."""
+        k = self.n & 1
+        prev = self.last() if self.n > 0 else None
+        self.slots[k].copy_(values.detach().reshape(-1)[: self.slots[k].numel()], non_blocking=True)
+        self.events[k].record(torch.cuda.current_stream(self.device))
+        self.n += 1
+        return prev
+
+    def last(self):
+        """Values of the most recently pushed step (waits for its copy)."""
+        k = (self.n - 1) & 1
+        self.events[k].synchronize()
+        return self.slots[k].tolist()
+
+
 class Trainer:
     """One object per rank.  ``step(batch)`` runs a full training step and returns a device tensor
     ``[loss, mape]`` (no host sync inside)."""

@@ -152,8 +152,9 @@ def _small_model(cfg_base=None):
 @pytest.mark.parametrize("what", ["edge", "atom", "bond"])
 def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what):
     """PyG raises on an edge_index entry >= num_nodes and torch.nn.Embedding on an id outside its vocabulary.  Here the
-    flags ride the host reads the path pays anyway: ``int(batch[-1]) + 1`` of the reference-signature forward(), and the
-    max-degree readback of the PNA path (so a PNA model raises IndexError even with num_graphs= given).  A path without
+    flags ride the host reads the path pays anyway: ``int(batch[-1]) + 1`` of the reference-signature forward(), the
+    max-degree readback of the PNA path when the model has no degree hint, and otherwise the lagged status copy that the
+    next forward checks.  A path without
     any host read (GATv2 with num_graphs=) skips / zeroes the offending entries -- finite output, nothing uninitialised
     is ever used as an index -- and Batch.validate() / GraphIndex.check() report them."""
     from gnnepcsaft_b200 import graph as gr
@@ -176,9 +177,21 @@ def test_out_of_range_inputs_raise_like_pyg_and_never_touch_foreign_memory(what)
             gr._INDEX_CACHE.clear()
             with pytest.raises(IndexError):
                 m(*args)                                  # reference signature: the one host read checks the flags
+        # PNA with num_graphs=: the dataset histogram bounds the in-degree (model.degree_hint), so nothing is read back
+        # during the call -- memory-safe, finite -- and the batch's status words, copied to pinned memory on a side
+        # stream, make the NEXT forward raise; without the hint the max-degree read-back raises at once
+        gr._INDEX_CACHE.clear()
+        out = model(*args, num_graphs=G)
+        assert bool(torch.isfinite(out).all())
         gr._INDEX_CACHE.clear()
         with pytest.raises(IndexError):
-            model(*args, num_graphs=G)                    # PNA: the max-degree readback checks them too
+            model(*args, num_graphs=G)
+        hint, model.degree_hint = model.degree_hint, None
+        model._hinted = None
+        gr._INDEX_CACHE.clear()
+        with pytest.raises(IndexError):
+            model(*args, num_graphs=G)
+        model.degree_hint = hint
         gr._INDEX_CACHE.clear()
         out = gat(*args, num_graphs=G)                    # sync-free path: memory-safe, flags left on the device
         assert out.shape == (G, 2) and bool(torch.isfinite(out).all())

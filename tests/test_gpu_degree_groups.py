@@ -211,3 +211,36 @@ def test_batchnorm_on_bucket_ordered_rows(N, C, relu):
         assert torch.allclose(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max())), what
     pad = (bk.row_node < 0)
     assert bool((dx1[pad] == 0).all())
+
+
+def test_degree_hint_skips_the_readback_and_flags_a_batch_that_breaks_it():
+    """Reference-signature forward of a PNA model: the dataset histogram's length bounds the in-degree, so no per-batch
+    maximum is read back; a batch with a node beyond the histogram still runs (wrongly bucketed), is flagged on the
+    device, and the NEXT forward raises.  With the hint switched off the same batch is served by one read-back."""
+    import copy
+    import gnnepcsaft_b200 as G
+    from tests.util import PNA_CFG1, deg_hist, make_batch
+    ops.set_matmul_precision("fp32")
+    graphs, b = make_batch(16, seed=5)
+    hist = deg_hist(graphs)
+    args = [b[k].to(DEV) for k in ("x", "edge_index", "edge_attr", "batch")]
+    m = G.GNNePCSAFT(copy.deepcopy(dict(PNA_CFG1, deg=hist))).to(DEV).eval()
+    assert m.degree_hint == len(hist) - 1
+    with torch.no_grad():
+        y_hint = m(*args, num_graphs=16)
+        idx = graph.graph_index_for(args[1], args[0].shape[0])
+        assert idx.max_degree is None and idx.degree_hint == m.degree_hint and idx._status_host is not None
+        m.check_pending()                                            # nothing flagged
+        m.degree_hint = None
+        graph._INDEX_CACHE.clear()
+        y_read = m(*args, num_graphs=16)
+        assert torch.equal(y_hint, y_read)
+        # a model whose histogram stops one short of this batch's largest in-degree
+        short = G.GNNePCSAFT(copy.deepcopy(dict(PNA_CFG1, deg=hist[:-1]))).to(DEV).eval()
+        graph._INDEX_CACHE.clear()
+        short(*args, num_graphs=16)                                  # runs, flagged on the device
+        with pytest.raises(IndexError, match="degree histogram"):
+            short(*args, num_graphs=16)
+        short.degree_hint = None
+        graph._INDEX_CACHE.clear()
+        assert bool(torch.isfinite(short(*args, num_graphs=16)).all())
