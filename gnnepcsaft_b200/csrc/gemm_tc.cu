@@ -254,6 +254,7 @@ constexpr int kB2 = 256 * 128;                  // 32 KB
 constexpr int kStage2 = kA2 + kB2;              // 48 KB
 constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes + 256;
 constexpr int kThreads2 = 224;                  // + warp 6: column sums of the A tiles (the bias gradient riding a dX product)
+constexpr int kBackoffFlag = 1 << 16;             // internal launch flag: waiting roles sleep between polls
 constexpr int kColsumMaxK = 256;                // columns the fused sum covers (8 k-blocks of accumulators in registers)
 
 struct Smem2 {
@@ -299,6 +300,11 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_ptr();
     pdl_enter();           // barriers, TMEM and the cluster handshake overlap the previous kernel's tail; global memory only from here
+    // Optional (GNNX_GEMM_BACKOFF=1): waiting roles sleep between polls.  In k_pna_post_fused spinning waiters cost the
+    // producer warps a third of the kernel; here the epilogue warps do not mind, and it is 1-2 % slower.
+    const bool nap = (flags & kBackoffFlag) != 0;
+    flags &= ~kBackoffFlag;
+    auto wait = [&](uint32_t bar, uint32_t parity, unsigned ns) { if (nap) mbar_wait_sleep(bar, parity, ns); else mbar_wait(bar, parity); };
 
     const int n_tiles = (N + BN - 1) / BN;
     const int m_groups = ((M + 127) / 128 + kCluster - 1) / kCluster;
@@ -325,7 +331,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     for (int d = 1; d < n_groups; ++d) goff += (mbase >= __ldg(bucket_ptr + d)) ? group_rows : 0;
                 }
                 for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(sm.empty(stage), phase ^ 1);
+                    wait(sm.empty(stage), phase ^ 1, 64);
                     mbar_expect_tx(sm.full(stage), tx);
                     tma_load_2d(sm.a(stage), &tmA, sm.full(stage), kb * kBK, m0);
                     if (kCluster == 1) {
@@ -346,10 +352,10 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             uint32_t phase = 0, i = 0;
             for (int w = cid; w < work; w += ncl, ++i) {
                 const uint32_t buf = i & 1;
-                mbar_wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1, 64);
                 tc_fence_after();
                 for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(sm.full(stage), phase);
+                    wait(sm.full(stage), phase, 20);
                     tc_fence_after();
 #pragma unroll
                     for (int k = 0; k < kBK / 8; ++k) {
@@ -380,7 +386,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
                 for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
                     if (kb < KB) {
-                        mbar_wait(sm.full(stage), phase);
+                        wait(sm.full(stage), phase, 64);
                         if (first_n) {
                             const uint8_t* a = sm.base + stage * kStage2;
                             float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
@@ -459,7 +465,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int w = cid; w < work; w += ncl, ++i) {
             const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
             const uint32_t buf = i & 1;
-            mbar_wait(sm.tmem_full(buf), (i >> 1) & 1);
+            wait(sm.tmem_full(buf), (i >> 1) & 1, 128);
             tc_fence_after();
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
@@ -1181,6 +1187,10 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // see common.cuh: pdl_enter()
         at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+        static std::once_flag nap_once;
+        static int nap = 0;          // measured on a B200 (cfg2): 83.8 / 73.5 us per dX / forward product with back-off, 82.5 / 72.0 without
+        std::call_once(nap_once, [] { const char* e = getenv("GNNX_GEMM_BACKOFF"); nap = (e && e[0] == '1') ? 1 : 0; });
+        if (nap) flags |= kBackoffFlag;
         const int Mi = (int)M, Ni = (int)N, Ki = (int)K;
         const long long ldc_ = ldc, ldm_ = ldm;
         const long long ldbits = (N + 31) / 32;          // packed masks are row-major: [M, ceil(N/32)] words

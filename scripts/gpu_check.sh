@@ -1,8 +1,3 @@
 #!/bin/bash
-python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -4 gpurun_out/pytest_gpu.log; grep -E "^(FAILED|ERROR)|Error" gpurun_out/pytest_gpu.log | head
-python bench.py --steps 30 --no-cpu-baseline > gpurun_out/bench_r2g_cfg2.json 2> gpurun_out/bench_r2g.err; echo "exit $?"; tail -3 gpurun_out/bench_r2g.err
-python - <<PY
-import json
-d=json.loads([l for l in open("gpurun_out/bench_r2g_cfg2.json") if l.startswith("{")][0])
-print("value ms", d["ms_per_step"], "e2e", {k: v for k, v in d["e2e"].items() if k != "api"})
-PY
+python -m pytest tests/test_gpu_gemm_tc.py tests/test_gpu_degree_groups.py -m gpu -q 2>&1 | tail -2
+for b in 0 1 0 1; do echo "GNNX_GEMM_BACKOFF=$b"; GNNX_GEMM_BACKOFF=$b python scripts/kernel_trace.py --workload cfg2 --steps 2 2>/dev/null | grep -E "^cfg2|k_gemm_tf32_rows2" | cut -c1-150; done
