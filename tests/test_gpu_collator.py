@@ -228,3 +228,29 @@ def test_packed_store_is_validated_on_the_host():
     bad.dst[2] = 120
     with pytest.raises(IndexError):
         gr.DeviceGraphStore(bad, DEV)
+
+
+def test_reference_file_to_device_batches(tmp_path):
+    """SURVEY 8(f) rank 2 end to end: a processed dataset file in the reference's (data, slices) layout -> packed device
+    store -> shuffled epoch of device-collated batches, each bit-exactly the PyG collation of the graphs the DataLoader
+    would have put into it."""
+    from gnnepcsaft_b200 import dataset
+    graphs = synth.make_graphs(70, 33, 1, 30, 0.1)
+    p = tmp_path / "es_graph_data.pt"
+    torch.save(dataset.collate_graphs(graphs), p)
+    store = graph.DeviceGraphStore(dataset.pack_collated(*dataset.load_collated(p)), DEV)
+    assert store.num_graphs == 70 and store.calc_deg() == O.calc_deg(oracle_graphs(graphs))
+    torch.manual_seed(9)
+    want_order = [b.tolist() for b in torch.utils.data.DataLoader(torch.arange(70), batch_size=16, shuffle=True)]
+    torch.manual_seed(9)
+    loader = dataset.EpochLoader(store, 16, shuffle=True)
+    og = oracle_graphs(graphs)
+    seen = []
+    for b, ids in zip(loader, want_order):
+        ref = O.collate([og[i] for i in ids])
+        assert b.num_graphs == len(ids)
+        assert torch.equal(b.x.cpu().long(), ref.x) and torch.equal(b.edge_attr.cpu().long(), ref.edge_attr)
+        assert torch.equal(torch.stack([b._src32, b._dst32]).cpu().long(), ref.edge_index)
+        assert torch.equal(b.batch.cpu().long(), ref.batch) and torch.equal(b.para.cpu(), ref.para)
+        seen += ids
+    assert sorted(seen) == list(range(70)) and len(loader) == 5
