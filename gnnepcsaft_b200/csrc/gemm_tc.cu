@@ -162,12 +162,15 @@ template <class SM>
 __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, int q, int lane, const CUtensorMap* tmC,
                                             int row0, int row_end, int col0, int ncols, const float* __restrict__ bias,
                                             int col_end, int flags, uint32_t& it, const float* __restrict__ mask = nullptr,
-                                            long long ldm = 0, uint32_t* __restrict__ bits_out = nullptr, long long ldbits = 0) {
-    uint8_t* stage = reinterpret_cast<uint8_t*>(sm.epi(q));
+                                            long long ldm = 0, uint32_t* __restrict__ bits_out = nullptr, long long ldbits = 0,
+                                            int c_first = 0, int c_stride = 32, uint8_t* stage1 = nullptr) {
+    // stage1 != null: this warp shares its TMEM lane quadrant with a second epilogue warp (each takes every other
+    // 32-column chunk: c_first / c_stride) and has ONE 4 KB staging tile of its own instead of two
+    uint8_t* stage = stage1 ? stage1 : reinterpret_cast<uint8_t*>(sm.epi(q));
     const int mr = lane >> 3, mj = lane & 7;            // coalesced mask mapping: 8 lanes cover one 128-byte row segment
     const bool mbits = mask && (flags & GNNX_GEMM_MASK_BITS);
     const long long myrow = (long long)row0 + q * 32 + lane;   // this thread's accumulator row
-    for (int c = 0; c < ncols; c += 32, ++it) {
+    for (int c = c_first; c < ncols; c += c_stride, ++it) {
         // ReLU mask of the layer below, requested before the TMEM load.  Packed: ONE word per thread covers its row's
         // 32 columns of this chunk.  fp32: 4 full 128-byte rows per load instruction, applied on the staged tile.
         float4 mk[8];
@@ -193,8 +196,8 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
         }
         float v[32];
         tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-        uint8_t* buf = stage + (it & 1) * 4096;
-        if (lane == 0) tma_store_wait_read<1>();          // the store that last read this buffer has drained it
+        uint8_t* buf = stage1 ? stage : stage + (it & 1) * 4096;
+        if (lane == 0) { if (stage1) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }   // the store that last read this buffer has drained it
         __syncwarp();
         tmem_ld_wait();
         if (bias) {
@@ -270,8 +273,12 @@ struct Smem2 {
     __device__ uint32_t* tmem_ptr() const { return reinterpret_cast<uint32_t*>(bars() + 2 * kStages2 + 4); }
 };
 
-template <bool kBMN, int kCluster>
-__global__ void __launch_bounds__(kThreads2, 1)
+// kEpi8: eight epilogue warps (warps 2-5 and 7-10, two per TMEM lane quadrant, alternate 32-column chunks) instead of
+// four: an epilogue warp walks its chunks one after the other (TMEM load -> registers -> staging tile -> bulk store), and
+// the epilogue of a CTA's LAST tile overlaps nothing, so its length is a fixed cost of every launch.
+constexpr int kThreads2E8 = 352;
+template <bool kBMN, int kCluster, bool kEpi8 = false>
+__global__ void __launch_bounds__(kEpi8 ? kThreads2E8 : kThreads2, 1)
 k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
                   const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
@@ -290,7 +297,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(sm.tmem_full(b), 1);
-            mbar_init(sm.tmem_empty(b), 4);
+            mbar_init(sm.tmem_empty(b), kEpi8 ? 8 : 4);
         }
         mbar_fence_init();
     }
@@ -459,6 +466,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
     } else {
         const int q = warp & 3;
+        const int second = kEpi8 && warp > 6 ? 1 : 0;                 // second epilogue warp of this quadrant
+        uint8_t* stage1 = kEpi8 ? reinterpret_cast<uint8_t*>(sm.epi(0)) + ((warp > 6 ? warp - 3 : warp - 2) * 4096) : nullptr;
         uint32_t it = 0, i = 0;
         const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask));
         if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
@@ -470,8 +479,9 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
                 if (use_tma)
-                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
-                else
+                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits,
+                                 kEpi8 ? 32 * second : 0, kEpi8 ? 64 : 32, stage1);
+                else if (!second)
                     epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags, mask, ldm);
             }
             tc_fence_before();
@@ -1116,6 +1126,8 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             return GNNX_OK;
         });
         if (rc) return rc;
@@ -1209,7 +1221,16 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
             trace_before(cluster == 4 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 4> : (const void*)k_gemm_tf32_rows2<true, 4>)
                          : cluster == 2 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 2> : (const void*)k_gemm_tf32_rows2<true, 2>)
                                       : (tb ? (const void*)k_gemm_tf32_rows2<false, 1> : (const void*)k_gemm_tf32_rows2<true, 1>), st);
-        if (cluster == 4)
+        // GNNX_GEMM_EPI8=1: eight epilogue warps.  Measured on a B200 (cfg2): dX products 84.0 us against 81.9, forward 72.2
+        // against 71.7 -- the un-overlapped last epilogue is not what the fixed ~12 us per launch is made of.  Off.
+        static std::once_flag e8_once;
+        static int epi8 = 0;
+        std::call_once(e8_once, [] { const char* e = getenv("GNNX_GEMM_EPI8"); epi8 = (e && e[0] == '1') ? 1 : 0; });
+        if (epi8 && cluster == 2) {
+            cfg.blockDim = dim3(kThreads2E8);
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2, true>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2, true>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
+        } else if (cluster == 4)
             e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
                    : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
         else if (cluster == 2)
