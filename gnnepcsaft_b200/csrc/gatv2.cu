@@ -323,21 +323,6 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
         stg4(datt_partial + (long long)gw * (128 * NQ) + q * 128 + lane * 4, datt[q].q);
 }
 
-// datt[c] = sum over the warps that owned column c's head group, in warp order; one warp per column
-__global__ void k_gatv2_datt_final(const float* __restrict__ partial, int total_warps, int groups, int width, int H,
-                                   float* __restrict__ datt) {
-    pdl_enter();
-    const int lane = threadIdx.x & 31;
-    const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (c >= H) return;
-    const int grp = c / width, off = c % width;
-    float s = 0.f;
-    for (int gw = grp + lane * groups; gw < total_warps; gw += 32 * groups) s += partial[(long long)gw * width + off];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-    if (lane == 0) datt[c] = s;
-}
-
 // Backward, source side: dxlr[j, 0:H] = sum_{edges j->i} (ds[pos] + alpha'[pos] * dout[i]) + loop term.
 // Warp per (source row, 128-column chunk), two out-edges per iteration.
 __global__ void __launch_bounds__(256)
@@ -467,7 +452,11 @@ size_t gnnx_gatv2_bwd_workspace_bytes(int64_t N, int64_t E, int32_t heads, int32
     (void)E;
     if (!attn_shape_ok(heads, C)) return 0;
     const AttnShape s = attn_shape(heads, C);
-    return (size_t)gat_bwd_grid(N, s.groups) * 8 * 128 * s.nq * sizeof(float);
+    // per-warp partials of d att, viewed as a row-major [warps / groups, groups * width] matrix, + the workspace of the
+    // column sum that folds them
+    const size_t part = (size_t)gat_bwd_grid(N, s.groups) * 8 * 128 * s.nq * sizeof(float);
+    const int64_t rows = (int64_t)gat_bwd_grid(N, s.groups) * 8 / s.groups;
+    return part + gnnx_colsum_workspace_bytes(rows, (int64_t)heads * C);
 }
 
 int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const float* xlr, const float* e, int64_t ld_e,
@@ -492,8 +481,14 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     GAT_DISPATCH(s, CALL);
 #undef CALL
     launch(k_gatv2_bwd_src, attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st, dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);
-    launch(k_gatv2_datt_final, ceil_div(H, 8), 256, 0, st, (const float*)ws, grid * 8, s.groups, 128 * s.nq, H, datt);
-    return check_launch("gatv2_bwd", 3);
+    int rc = check_launch("gatv2_bwd", 2);
+    if (rc) return rc;
+    // d att = column sums of the per-warp partials: warp gw owns head group gw % groups, so `groups` consecutive partial
+    // rows are one row of all H columns.  (A one-warp-per-column fold walked 300 strided rows per lane: 35 us for 5 MB;
+    // the two-pass column sum reads them coalesced.)
+    const size_t part = (size_t)grid * 8 * 128 * s.nq * sizeof(float);
+    return gnnx_colsum((const float*)ws, (int64_t)s.groups * 128 * s.nq, (int64_t)grid * 8 / s.groups, H, datt,
+                       (char*)ws + part, ws_bytes - part, stream);
 }
 
 int gnnx_gatv2_edge_grad(const float* ds, const int32_t* rowptr, const int32_t* csr_src, const int32_t* csr_eid, int64_t N,
