@@ -325,9 +325,34 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
         sb = _strict_bytes(name, a, N, E, H)
         d = agg.setdefault(name, dict(calls=0, ms=0.0, bytes=0.0, flops=0.0, strict=0.0))
         d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]; d["strict"] += sb if sb is not None else r[0]
+    # the dense products by class: K, N <= 512 (HBM-bound with fp32 operands) against the wide ones (K or N >= 768: the
+    # degree-grouped [agg | x] products, close to the tf32 tensor peak) -- the entry-point average above mixes the two
+    cls = {}
+    for name, a, ms in records:
+        if name not in ("gnnx_gemm", "gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched"):
+            continue
+        r = _algorithmic_bytes(name, a, N, E, H)
+        if r is None or r[1] < 2.0 * 33554432:            # the tiny weight-space products are launch-latency, not roofline
+            continue
+        wide = r[1] / r[0] > 90.0                          # FLOP per algorithmic byte: 64 at K = N = 256, 106 at K = 1280, N = 256
+        d = cls.setdefault("gnnx_gemm[wide, K or N >= 768]" if wide else "gnnx_gemm[K, N <= 512]", dict(calls=0, ms=0.0, bytes=0.0, flops=0.0))
+        d["calls"] += 1; d["ms"] += ms; d["bytes"] += r[0]; d["flops"] += r[1]
     total_ms = sum(ms for _, _, ms in records)
     traffic, traffic_src = _measured_traffic(workload)
     kernels = {}
+    tf32_peak = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            tf32_peak = float(json.load(f)["bf16_tflops"]) / 2.0       # kind::tf32 runs at half the bf16 rate
+    except Exception:
+        pass
+    for name, d in cls.items():
+        k = {"calls": d["calls"], "ms_per_call": d["ms"] / d["calls"], "share_of_gnnx_time": d["ms"] / total_ms,
+             "achieved_GBps": d["bytes"] / (d["ms"] / 1e3) / 1e9, "frac_of_hbm_peak": d["bytes"] / (d["ms"] / 1e3) / 1e9 / peak,
+             "achieved_TFLOPs": d["flops"] / (d["ms"] / 1e3) / 1e12}
+        if tf32_peak:
+            k["frac_of_tf32_tensor_peak"] = k["achieved_TFLOPs"] / tf32_peak
+        kernels[name] = k
     for name, d in sorted(agg.items(), key=lambda kv: -kv[1]["ms"]):
         gbs = d["bytes"] / (d["ms"] / 1e3) / 1e9
         k = {"calls": d["calls"], "ms_per_call": d["ms"] / d["calls"], "share_of_gnnx_time": d["ms"] / total_ms,
