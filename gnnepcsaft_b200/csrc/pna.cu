@@ -3,6 +3,8 @@
 // scatters, and the scaler-folded combine of the first post_nn Linear.  All kernels are
 // deterministic and atomic-free: one warp owns one (destination row, 128-column chunk), walks the
 // row's edges in edge order with float4 loads (several rows in flight), and writes each output once.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gnnx {
@@ -30,46 +32,66 @@ __device__ __forceinline__ uint32_t pack_relu_word(const F4& o, bool act, int la
     return v;
 }
 
-template <typename RIdx>
-__global__ void __launch_bounds__(256)
+// V = float4 groups per lane: a warp covers 128 * V columns (V = 2: the whole row at hidden 256 -- half the index loads
+// per byte and twice the bytes in flight per warp; these kernels are latency-bound).  Lane l holds columns c + 128 v ..
+// +3, so every load instruction still covers 512 contiguous bytes.
+template <typename RIdx, int V>
+__global__ void __launch_bounds__(256, V == 2 ? 4 : 6)
 k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __restrict__ r, long long ld_r,
                  const RIdx* __restrict__ ridx, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
                  int N, int H, int relu, float* __restrict__ h, uint32_t* __restrict__ bits) {
     pdl_enter();
     const int lane = threadIdx.x & 31;
-    const int chunks = (H + 127) / 128;
+    const int chunks = (H + 128 * V - 1) / (128 * V);
     const int words = (H + 31) / 32;
     const int wpb = blockDim.x >> 5;
     const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);        // fixed column chunk per warp, rows strided
     const int row_stride = (gridDim.x * wpb) / chunks;           // host guarantees divisibility
-    const int c = (gw % chunks) * 128 + lane * 4;
-    const bool act = c < H;
+    const int c = (gw % chunks) * 128 * V + lane * 4;
+    bool act[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) act[v] = c + 128 * v < H;
     for (int i = gw / chunks; i < N; i += row_stride) {
         const int b = rowptr[i], e = rowptr[i + 1];
         if (b == e) continue;
-        const F4 p = act ? f4_ld(pq + (long long)i * ld_pq + c) : f4_zero();
+        F4 p[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) p[v] = act[v] ? f4_ld(pq + (long long)i * ld_pq + c + 128 * v) : f4_zero();
         for (int k = b; k < e; k += 2) {
             const bool two = k + 1 < e;
             const int s0 = csr_src[k], s1 = two ? csr_src[k + 1] : s0;
             const long long r0 = (long long)ridx[k], r1 = two ? (long long)ridx[k + 1] : r0;
-            F4 o0 = f4_zero(), o1 = f4_zero();
-            if (act) {
-                const F4 q0 = f4_ld(pq + (long long)s0 * ld_pq + H + c), q1 = f4_ld(pq + (long long)s1 * ld_pq + H + c);
-                const F4 t0 = f4_ld(r + r0 * ld_r + c), t1 = f4_ld(r + r1 * ld_r + c);
+            F4 q0[V], q1[V], t0[V], t1[V];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    o0.a[j] = p.a[j] + q0.a[j] + t0.a[j];
-                    o1.a[j] = p.a[j] + q1.a[j] + t1.a[j];
-                    if (relu) { o0.a[j] = fmaxf(o0.a[j], 0.f); o1.a[j] = fmaxf(o1.a[j], 0.f); }
+            for (int v = 0; v < V; ++v) {
+                if (act[v]) {
+                    q0[v] = f4_ld(pq + (long long)s0 * ld_pq + H + c + 128 * v);
+                    q1[v] = f4_ld(pq + (long long)s1 * ld_pq + H + c + 128 * v);
+                    t0[v] = f4_ld(r + r0 * ld_r + c + 128 * v);
+                    t1[v] = f4_ld(r + r1 * ld_r + c + 128 * v);
+                } else {
+                    q0[v] = q1[v] = t0[v] = t1[v] = f4_zero();
                 }
-                stg4(h + (long long)k * H + c, o0.q);
-                if (two) stg4(h + (long long)(k + 1) * H + c, o1.q);
             }
-            if (bits) {                                          // packed ReLU mask of the rows just written
-                const uint32_t w0 = pack_relu_word(o0, act, lane), w1 = pack_relu_word(o1, act, lane);
-                if (act && (lane & 7) == 0) {
-                    bits[(long long)k * words + (c >> 5)] = w0;
-                    if (two) bits[(long long)(k + 1) * words + (c >> 5)] = w1;
+#pragma unroll
+            for (int v = 0; v < V; ++v) {
+                F4 o0 = f4_zero(), o1 = f4_zero();
+                if (act[v]) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        o0.a[j] = p[v].a[j] + q0[v].a[j] + t0[v].a[j];
+                        o1.a[j] = p[v].a[j] + q1[v].a[j] + t1[v].a[j];
+                        if (relu) { o0.a[j] = fmaxf(o0.a[j], 0.f); o1.a[j] = fmaxf(o1.a[j], 0.f); }
+                    }
+                    stg4(h + (long long)k * H + c + 128 * v, o0.q);
+                    if (two) stg4(h + (long long)(k + 1) * H + c + 128 * v, o1.q);
+                }
+                if (bits) {                                      // packed ReLU mask of the rows just written
+                    const uint32_t w0 = pack_relu_word(o0, act[v], lane), w1 = pack_relu_word(o1, act[v], lane);
+                    if (act[v] && (lane & 7) == 0) {
+                        bits[(long long)k * words + ((c + 128 * v) >> 5)] = w0;
+                        if (two) bits[(long long)(k + 1) * words + ((c + 128 * v) >> 5)] = w1;
+                    }
                 }
             }
         }
@@ -103,6 +125,44 @@ k_pna_gather_bwd(const float* __restrict__ dh, const int* __restrict__ rowptr, c
             for (int j = 0; j < 4; ++j) s.a[j] += v.a[j];
         }
         stg4(dpq + (long long)i * ld + H + c, s.q);
+    }
+}
+
+// Same with 8 columns per lane (a warp covers 256 columns: the whole row at hidden 256): half the index loads per byte
+// and twice the bytes in flight per warp -- the 4-column version is latency-bound (ncu r2a: 18.8 long-scoreboard stalls
+// per issue, 51 % of the DRAM peak).  Lane l holds columns c .. c+3 and c+128 .. c+131 so every load instruction still
+// covers 512 contiguous bytes.
+__global__ void __launch_bounds__(256)
+k_pna_gather_bwd8(const float* __restrict__ dh, const int* __restrict__ rowptr, const int* __restrict__ colptr,
+                  const int* __restrict__ csc_pos, int N, int H, float* __restrict__ dpq, long long ld) {
+    pdl_enter();
+    const int lane = threadIdx.x & 31;
+    const int chunks = (H + 255) / 256;
+    const long long nwork = (long long)N * chunks;
+    const int wpb = blockDim.x >> 5;
+    for (long long w = blockIdx.x * (long long)wpb + (threadIdx.x >> 5); w < nwork; w += (long long)gridDim.x * wpb) {
+        const int i = (int)(w / chunks);
+        const int c = (int)(w % chunks) * 256 + lane * 4;
+        const bool a0 = c < H, a1 = c + 128 < H;
+        if (!a0) continue;
+        const int kb = rowptr[i], ke = rowptr[i + 1], sb = colptr[i], se = colptr[i + 1];
+        F4 p0 = f4_zero(), p1 = f4_zero(), q0 = f4_zero(), q1 = f4_zero();
+        for (int k = kb; k < ke; ++k) {
+            const float* row = dh + (long long)k * H + c;
+            const F4 v0 = f4_ld(row), v1 = a1 ? f4_ld(row + 128) : f4_zero();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { p0.a[j] += v0.a[j]; p1.a[j] += v1.a[j]; }
+        }
+        for (int k = sb; k < se; ++k) {
+            const float* row = dh + (long long)csc_pos[k] * H + c;
+            const F4 v0 = f4_ld(row), v1 = a1 ? f4_ld(row + 128) : f4_zero();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { q0.a[j] += v0.a[j]; q1.a[j] += v1.a[j]; }
+        }
+        float* o = dpq + (long long)i * ld + c;
+        stg4(o, p0.q);
+        stg4(o + H, q0.q);
+        if (a1) { stg4(o + 128, p1.q); stg4(o + H + 128, q1.q); }
     }
 }
 
@@ -455,13 +515,18 @@ int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t 
     GNNX_REQUIRE(H % 4 == 0 && ld_pq % 4 == 0 && ld_r % 4 == 0, "pna_gather_fwd: hidden / strides must be multiples of 4");
     GNNX_REQUIRE(E == 0 || (ridx_i32 != nullptr) != (ridx_u8 != nullptr), "pna_gather_fwd: exactly one of ridx_i32 / ridx_u8");
     if (N == 0 || E == 0) return GNNX_OK;
-    const int chunks = (H + 127) / 128;
+    static int wide = -1;
+    if (wide < 0) { const char* e = getenv("GNNX_GATHER8"); wide = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }
+    // 8 columns per lane pay in the backward (96.5 -> 79.5 us) but not here: three operand rows per edge at V = 2 need 64
+    // registers, the lost occupancy eats the gain (94.5 us against 92.7).  GNNX_GATHER8=2 selects it all the same.
+    const int V = (wide == 2 && H > 128) ? 2 : 1;
+    const int chunks = (H + 128 * V - 1) / (128 * V);
     int grid = warp_grid((long long)N * chunks);
     grid = (grid + chunks - 1) / chunks * chunks;               // every warp keeps one column chunk
-    if (ridx_i32)
-        launch(k_pna_gather_fwd<int>, grid, 256, 0, as_stream(stream), pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
-    else
-        launch(k_pna_gather_fwd<uint8_t>, grid, 256, 0, as_stream(stream), pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out);
+#define GATHER_FWD(T, VV, IDX) launch(k_pna_gather_fwd<T, VV>, grid, 256, 0, as_stream(stream), pq, ld_pq, r, ld_r, IDX, rowptr, csr_src, (int)N, H, relu, h, relu_bits_out)
+    if (ridx_i32) { if (V == 2) GATHER_FWD(int, 2, ridx_i32); else GATHER_FWD(int, 1, ridx_i32); }
+    else { if (V == 2) GATHER_FWD(uint8_t, 2, ridx_u8); else GATHER_FWD(uint8_t, 1, ridx_u8); }
+#undef GATHER_FWD
     return check_launch("pna_gather_fwd");
 }
 
@@ -470,8 +535,15 @@ int gnnx_pna_gather_bwd(const float* dh, const int32_t* rowptr, const int32_t* c
                         float* dr_edge, int64_t ld_dr, void* stream) {
     GNNX_REQUIRE(H % 4 == 0 && ld_dpq % 4 == 0, "pna_gather_bwd: hidden / strides must be multiples of 4");
     if (N == 0) return GNNX_OK;
-    long long nwork = (long long)N * ((H + 127) / 128);
-    launch(k_pna_gather_bwd, warp_grid(nwork), 256, 0, as_stream(stream), dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
+    static int wide = -1;
+    if (wide < 0) { const char* e = getenv("GNNX_GATHER8"); wide = (e && e[0] == '0') ? 0 : 1; }
+    if (wide && H > 128) {
+        long long nwork = (long long)N * ((H + 255) / 256);
+        launch(k_pna_gather_bwd8, warp_grid(nwork), 256, 0, as_stream(stream), dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
+    } else {
+        long long nwork = (long long)N * ((H + 127) / 128);
+        launch(k_pna_gather_bwd, warp_grid(nwork), 256, 0, as_stream(stream), dh, rowptr, colptr, csc_pos, (int)N, H, dpq, ld_dpq);
+    }
     if (dr_edge && E > 0) {
         GNNX_REQUIRE(ld_dr % 4 == 0 && csr_eid, "pna_gather_bwd: dr_edge needs csr_eid and an aligned stride");
         launch(k_permute_rows, flat_grid(E * (H / 4)), 256, 0, as_stream(stream), dh, csr_eid, E, H, dr_edge, ld_dr);
