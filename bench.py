@@ -228,6 +228,9 @@ def _algorithmic_bytes(name, a, N, E, H):
         if mask:
             byts += (M * Nn / 8.0) if (flags & 4) else 4.0 * M * Nn      # packed (1 bit / element) or fp32 mask
         return byts, 2.0 * M * Nn * K
+    if name == "gnnx_gemm_chain":                 # n square Linear layers in one launch: input read once, every output written once
+        n, M, W = a[0], a[10], a[11]
+        return 4.0 * M * W * (n + 1) + 4.0 * n * W * W, 2.0 * n * M * W * W
     if name == "gnnx_gemm_grouped":               # degree-grouped product: one weight block per in-degree class
         M, Nn, K, G, flags = a[7], a[8], a[9], a[11], a[13]
         return 4.0 * (M * K + G * Nn * K + M * Nn), 2.0 * M * Nn * K
@@ -319,7 +322,7 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
         r = _algorithmic_bytes(name, a, N, E, H)
         if r is None:
             continue
-        if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched"):   # same kernels as gnnx_gemm (k_gemm_tf32_rows2 / _red)
+        if name in ("gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched", "gnnx_gemm_chain"):   # same kernel family as gnnx_gemm (k_gemm_tf32_rows2 / _red)
             name = "gnnx_gemm"
         name = name.replace("gnnx_bn_relu_rows_", "gnnx_bn_relu_")   # same kernels, row-mapped
         sb = _strict_bytes(name, a, N, E, H)
@@ -329,7 +332,7 @@ def summarise_roofline(records, N, E, H, peak, peak_src, workload=None, steps_ti
     # degree-grouped [agg | x] products, close to the tf32 tensor peak) -- the entry-point average above mixes the two
     cls = {}
     for name, a, ms in records:
-        if name not in ("gnnx_gemm", "gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched"):
+        if name not in ("gnnx_gemm", "gnnx_gemm_grouped", "gnnx_gemm_grouped_dw", "gnnx_gemm_dw_batched", "gnnx_gemm_chain"):
             continue
         r = _algorithmic_bytes(name, a, N, E, H)
         if r is None or r[1] < 2.0 * 33554432:            # the tiny weight-space products are launch-latency, not roofline

@@ -31,6 +31,11 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
                         cudaStream_t st);
 int group_reduce_launch(const float* partial, const int* split_table, int S, const float* coef, int J, long long total,
                         float* out, cudaStream_t st);
+bool tc_chain_ok(int n, int64_t M, int64_t W, const float* A, int64_t lda, const float* const* Wt, const int64_t* ldw,
+                 float* const* C, const int64_t* ldc);
+int gemm_tc_chain(int n, const float* A, int64_t lda, const float* const* Wt, const int64_t* ldw, const float* const* bias,
+                  const int* flags, float* const* C, const int64_t* ldc, uint32_t* const* bits, int64_t M, int64_t W,
+                  cudaStream_t st);
 bool pna_post_fused_ok(int64_t rows, int64_t Ho, int64_t H, int64_t F, int64_t ldw, int64_t ld_out, int64_t ld_agg,
                        const void* weff, const void* out, const void* agg_out, const void* msg, const void* x);
 int pna_post_fused(const float* msg, const int* rowptr, const int* row_node, int64_t rows, const float* x, int64_t H, int64_t F,
@@ -119,6 +124,25 @@ int gnnx_gemm_grouped(const float* A, int64_t lda, const float* B, int64_t ldb, 
     GNNX_REQUIRE(bucket_ptr && n_groups >= 1 && n_groups <= GNNX_MAX_GROUPS, "gemm_grouped: 1..%d groups and a bucket_ptr", GNNX_MAX_GROUPS);
     return gemm_dispatch(A, lda, 0, B, ldb, tb, C, ldc, M, N, K, bias, flags, relu_mask, ld_mask, relu_bits_out, colsum_a_out,
                          precision, ws, ws_bytes, stream, bucket_ptr, n_groups);
+}
+
+int gnnx_gemm_chain(int32_t n, const float* A, int64_t lda, const float* const* W, const int64_t* ld_w,
+                    const float* const* bias, const int32_t* flags, float* const* C, const int64_t* ld_c,
+                    uint32_t* const* relu_bits_out, int64_t M, int64_t width, int32_t precision, void* stream) {
+    GNNX_REQUIRE(n >= 1 && A && W && ld_w && C && ld_c, "gemm_chain: null argument");
+    GNNX_REQUIRE(M >= 0 && width >= 1, "gemm_chain: bad shape");
+    if (M == 0) return GNNX_OK;
+    static int chain = -1;
+    if (chain < 0) { const char* e = getenv("GNNX_GEMM_CHAIN"); chain = (e && e[0] == '0') ? 0 : 1; }
+    if (chain && precision != GNNX_PREC_FP32 && tc_chain_ok(n, M, width, A, lda, W, ld_w, C, ld_c))
+        return gemm_tc_chain(n, A, lda, W, ld_w, bias, flags, C, ld_c, relu_bits_out, M, width, as_stream(stream));
+    for (int p = 0; p < n; ++p) {                          // shapes / tiers the chain kernel does not take: one product at a time
+        int rc = gnnx_gemm(p == 0 ? A : C[p - 1], p == 0 ? lda : ld_c[p - 1], 0, W[p], ld_w[p], 1, C[p], ld_c[p], M, width, width,
+                           bias ? bias[p] : nullptr, flags ? flags[p] : 0, nullptr, 0, relu_bits_out ? relu_bits_out[p] : nullptr,
+                           nullptr, precision, nullptr, 0, stream);
+        if (rc) return rc;
+    }
+    return GNNX_OK;
 }
 
 int32_t gnnx_pna_post_fused_supported(int64_t rows, int32_t towers, int32_t f, int32_t h_out, int32_t precision) {

@@ -499,6 +499,176 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
 }
 
+// ------------------------------------------------------------------ Linear -> ReLU -> Linear (-> ...) chains, ONE launch
+// Up to kChainMax same-width products C_p = act(A_p W_p^T + b_p) with A_{p+1} = C_p, row-local: tile t of product p + 1
+// needs only tile t of product p.  Separate launches pay the kernel boundary per product (drain + refill, ~12 us of a
+// ~45 us product at 100 k rows) and read every intermediate back from HBM.  Here a cluster walks its row tiles in groups
+// of kChainGroup: all tiles of the group through product 0, then through product 1, ... -- so the store of (tile, p) has
+// a group's worth of other work items to complete before (tile, p + 1) loads it back, from L2.  The epilogue warps
+// signal "the stores of item i are complete" on a small ring of mbarriers (cp.async.bulk.wait_group 0, then arrive),
+// and the TMA thread waits for the item it depends on before issuing that item's A loads.  Everything else is
+// k_gemm_tf32_rows2: multicast weights, two accumulators ping-ponging in TMEM, TMA-store epilogue, packed ReLU masks.
+constexpr int kChainMax = 4;
+constexpr int kChainGroupMax = 8;                   // tiles per group (run-time G <= this)
+constexpr int kChainSlots = 16;                     // ring of "stores complete" barriers: > G + 2
+struct ChainArgs {
+    CUtensorMap a[kChainMax], b[kChainMax], c[kChainMax];
+    const float* bias[kChainMax];
+    uint32_t* bits[kChainMax];
+    int flags[kChainMax];
+    int n;
+};
+
+struct ChainSmem : Smem2 {
+    __device__ uint32_t cdone(int s) const { return smem_u32(bars() + 2 * kStages2 + 6 + s); }
+};
+constexpr int kSmemChain = kSmem2 + 64;
+
+// item i of a cluster's schedule -> (row-tile index within the cluster's list, product); g = tiles in the item's group
+struct ChainItem { int tile, p, g; };
+__device__ __forceinline__ ChainItem chain_item(int i, int ntiles, int n, int G) {
+    const int per_full = G * n;
+    const int full = ntiles / G;                           // full groups
+    int grp = i / per_full, r = i - grp * per_full, g = G;
+    if (grp >= full) {                                     // the last, partial group
+        grp = full;
+        r = i - full * per_full;
+        g = ntiles - full * G;
+    }
+    ChainItem it;
+    it.g = g;
+    it.p = r / g;
+    it.tile = grp * G + (r - it.p * g);
+    return it;
+}
+
+template <int kCluster>
+__global__ void __launch_bounds__(kThreads2, 1)
+k_gemm_tf32_chain(const __grid_constant__ ChainArgs args, int M, int W, int G) {
+    extern __shared__ uint8_t smem_raw[];
+    ChainSmem sm;
+    sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = kCluster > 1 ? (int)cluster_ctarank() : 0;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages2; ++s) {
+            mbar_init(sm.full(s), 1);
+            mbar_init(sm.empty(s), kCluster);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(sm.tmem_full(b), 1);
+            mbar_init(sm.tmem_empty(b), 4);
+        }
+        for (int s = 0; s < kChainSlots; ++s) mbar_init(sm.cdone(s), 4);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(smem_u32(sm.tmem_ptr()), kTmemCols);
+    tc_fence_before();
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr();
+    pdl_enter();
+
+    const int n = args.n;
+    const int m_groups = ((M + 127) / 128 + kCluster - 1) / kCluster;      // row blocks of kCluster tiles
+    const int cid = blockIdx.x / kCluster, ncl = gridDim.x / kCluster;
+    const int ntiles = cid < m_groups ? (m_groups - cid + ncl - 1) / ncl : 0;   // this cluster's row blocks: cid, cid + ncl, ...
+    const int items = ntiles * n;
+    const int KB = (W + kBK - 1) / kBK;
+    const int BN = W;                                                      // one N tile: W <= 256
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int p = 0; p < n; ++p) { tma_prefetch_desc(&args.a[p]); tma_prefetch_desc(&args.b[p]); }
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = kA2 + (uint32_t)BN * 128u;
+            const int half = BN / kCluster;
+            constexpr uint16_t kAll = (uint16_t)((1u << kCluster) - 1u);
+            for (int i = 0; i < items; ++i) {
+                const ChainItem it = chain_item(i, ntiles, n, G);
+                const int m0 = ((cid + it.tile * ncl) * kCluster + rank) * 128;
+                if (it.p > 0) {                                            // A of this item = C of item i - g: wait for its stores
+                    const int d = i - it.g;
+                    mbar_wait(sm.cdone(d % kChainSlots), (uint32_t)((d / kChainSlots) & 1));
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                }
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.empty(stage), phase ^ 1);
+                    mbar_expect_tx(sm.full(stage), tx);
+                    tma_load_2d(sm.a(stage), &args.a[it.p], sm.full(stage), kb * kBK, m0);
+                    if (kCluster == 1) tma_load_2d(sm.b(stage), &args.b[it.p], sm.full(stage), kb * kBK, 0);
+                    else tma_load_2d_mc(sm.b(stage) + rank * half * 128, &args.b[it.p], sm.full(stage), kb * kBK, rank * half, kAll);
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, BN, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = 0; i < items; ++i) {
+                const uint32_t buf = i & 1;
+                mbar_wait(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.full(stage), phase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < kBK / 8; ++k) {
+                        const uint64_t bdesc = make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        const uint64_t adesc = make_smem_desc(sm.a(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        mma_tf32(tmem_base + buf * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    if (kCluster > 1) mma_commit_mc(sm.empty(stage), (uint16_t)((1u << kCluster) - 1u)); else mma_commit(sm.empty(stage));
+                    if (kb == KB - 1) mma_commit(sm.tmem_full(buf));
+                    if (++stage == kStages2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 2 && warp < 6) {
+        const int q = warp & 3;
+        uint32_t sit = 0;
+        int signalled = 0;                                                 // items whose completion this warp has announced
+        for (int i = 0; i < items; ++i) {
+            const ChainItem it = chain_item(i, ntiles, n, G);
+            const int m0 = ((cid + it.tile * ncl) * kCluster + rank) * 128;
+            const uint32_t buf = i & 1;
+            mbar_wait(sm.tmem_full(buf), (i >> 1) & 1);
+            tc_fence_after();
+            if (m0 < M)
+                epilogue_tma(sm, tmem_base + buf * 256, q, lane, &args.c[it.p], m0, M, 0, (BN + 31) / 32 * 32, args.bias[it.p], W,
+                             args.flags[it.p], sit, nullptr, 0, args.bits[it.p], (W + 31) / 32);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(sm.tmem_empty(buf));
+                // "stores complete" signals.  Waiting for item i's own stores here would idle this warp for the store
+                // latency on every item; instead item i - 1 is signalled now -- after item i's groups were committed,
+                // wait_group <groups of one item> leaves only those pending -- unless a nearby item depends on item i
+                // (groups of one or two tiles), which gets the full wait.
+                const bool urgent = it.g <= 2 && it.p + 1 < n;
+                if (urgent || i == items - 1) {
+                    tma_store_wait_all();
+                    for (; signalled <= i; ++signalled) mbar_arrive(sm.cdone(signalled % kChainSlots));
+                } else {
+                    tma_store_wait_pending((BN + 31) / 32);
+                    for (; signalled < i; ++signalled) mbar_arrive(sm.cdone(signalled % kChainSlots));
+                }
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (kCluster > 1) cluster_sync_all(); else __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
 // ------------------------------------------------------------------ PNAConv: aggregate -> first post Linear, ONE kernel
 // out[r, :] = act([mean | min | max | std | x](row r) W_eff(d_r)^T + b) for the degree-bucketed rows (degree_groups.cu).
 // Same pipeline as k_gemm_tf32_rows2 (weights by multicast TMA, tcgen05 accumulators ping-ponging in TMEM, TMA-store
@@ -1334,6 +1504,70 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
     for (int z = 0; z < n && rc == GNNX_OK; ++z)
         rc = splitk_reduce_launch((const float*)ws + z * stride, p.splits, (int)Mo, (int)No, C[z], ldc[z], nullptr, 0, nullptr, 0, st);
     return rc;
+}
+
+// ------------------------------------------------------------------ Linear chains (forward)
+bool tc_chain_ok(int n, int64_t M, int64_t W, const float* A, int64_t lda, const float* const* Wt, const int64_t* ldw,
+                 float* const* C, const int64_t* ldc) {
+    if (!encode_fn() || n < 2 || n > kChainMax) return false;
+    if (W < 32 || W > 256 || W % 32 || M < 768) return false;
+    if (!aligned16(A) || (lda & 3)) return false;
+    for (int p = 0; p < n; ++p)
+        if (!aligned16(Wt[p]) || !aligned16(C[p]) || (ldw[p] & 3) || (ldc[p] & 3)) return false;
+    return true;
+}
+
+int gemm_tc_chain(int n, const float* A, int64_t lda, const float* const* Wt, const int64_t* ldw, const float* const* bias,
+                  const int* flags, float* const* C, const int64_t* ldc, uint32_t* const* bits, int64_t M, int64_t W,
+                  cudaStream_t st) {
+    static std::atomic<uint64_t> attrs_done{0};
+    {
+        int rc = ensure_attrs(attrs_done, []() -> int {
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_chain<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemChain));
+            return GNNX_OK;
+        });
+        if (rc) return rc;
+    }
+    constexpr int cluster = 2;
+    ChainArgs args;
+    memset(&args, 0, sizeof args);
+    args.n = n;
+    for (int p = 0; p < n; ++p) {
+        const float* a = p == 0 ? A : C[p - 1];
+        const int64_t la = p == 0 ? lda : ldc[p - 1];
+        if (make_map_kmajor(&args.a[p], a, M, W, la, 128)) return GNNX_ERR_INVALID;
+        if (make_map_kmajor(&args.b[p], Wt[p], W, W, ldw[p], (int)W / cluster)) return GNNX_ERR_INVALID;
+        if (make_map_store(&args.c[p], C[p], M, W, ldc[p])) return GNNX_ERR_INVALID;
+        args.bias[p] = bias ? bias[p] : nullptr;
+        args.bits[p] = bits ? bits[p] : nullptr;
+        args.flags[p] = flags ? flags[p] : 0;
+    }
+    for (int p = n; p < kChainMax; ++p) { args.a[p] = args.a[0]; args.b[p] = args.b[0]; args.c[p] = args.c[0]; }
+    const int m_groups = ceil_div(ceil_div(M, 128), cluster);
+    const int max_cl = num_sms() / cluster;
+    int ncl = m_groups < max_cl ? m_groups : max_cl;
+    if (m_groups > max_cl) ncl = ceil_div(m_groups, ceil_div(m_groups, max_cl));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ncl * cluster);
+    cfg.blockDim = dim3(kThreads2);
+    cfg.dynamicSmemBytes = kSmemChain;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    static int group = 0;
+    // tiles per group: 6 = all row tiles of a cluster at cfg2 (138 us per 3-product chain against 142 at 3 or 4; three separate
+    // launches: 157).  GNNX_CHAIN_GROUP overrides.
+    if (group == 0) { const char* e = getenv("GNNX_CHAIN_GROUP"); group = e ? atoi(e) : 6; if (group < 1 || group > kChainGroupMax) group = 6; }
+    if (trace_on()) trace_before((const void*)k_gemm_tf32_chain<2>, st);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_gemm_tf32_chain<2>, args, (int)M, (int)W, group);
+    if (trace_on()) trace_after(st);
+    if (e != cudaSuccess) return set_error((int)e, "gemm_tf32_chain launch: %s", cudaGetErrorString(e));
+    count_tc_launches(1);
+    return check_launch("gemm_tf32_chain");
 }
 
 // ------------------------------------------------------------------ fused aggregate -> grouped post Linear (forward)

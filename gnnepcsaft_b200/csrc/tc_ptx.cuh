@@ -148,6 +148,19 @@ __device__ __forceinline__ void tma_store_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
 }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// until at most n (1..8) of this thread's most recent bulk groups are still in flight (complete, not just read)
+__device__ __forceinline__ void tma_store_wait_pending(int n) {
+    switch (n) {
+        case 1: asm volatile("cp.async.bulk.wait_group 1;" ::: "memory"); break;
+        case 2: asm volatile("cp.async.bulk.wait_group 2;" ::: "memory"); break;
+        case 3: asm volatile("cp.async.bulk.wait_group 3;" ::: "memory"); break;
+        case 4: asm volatile("cp.async.bulk.wait_group 4;" ::: "memory"); break;
+        case 5: asm volatile("cp.async.bulk.wait_group 5;" ::: "memory"); break;
+        case 6: asm volatile("cp.async.bulk.wait_group 6;" ::: "memory"); break;
+        case 7: asm volatile("cp.async.bulk.wait_group 7;" ::: "memory"); break;
+        default: asm volatile("cp.async.bulk.wait_group 8;" ::: "memory"); break;
+    }
+}
 // generic-proxy smem writes -> visible to the async proxy (TMA store source)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 

@@ -296,6 +296,32 @@ def gemm_dw_batched(dys, xs, precision: Optional[int] = None):
     return outs
 
 
+def gemm_chain(x: Tensor, layers, precision: Optional[int] = None):
+    """``layers`` = [(weight [W, W], bias | None, relu: bool, want_bits: bool), ...] applied in sequence to ``x`` [M, W]
+    (torch Linear layout) -> ``(outs, bits)``: every layer's output and, where asked for, its packed (out > 0) mask.
+    One launch on the tensor-core tier (``gnnx_gemm_chain``), the same numbers as ``gemm`` called layer by layer."""
+    import ctypes
+    n = len(layers)
+    M, W = x.shape
+    _chk(x, torch.float32, "x")
+    for w, b, _, _ in layers:
+        if w.shape != (W, W) or w.dtype != torch.float32 or not w.is_cuda or w.stride(1) != 1:
+            raise ValueError("gnnx.gemm_chain: every weight must be a CUDA float32 [W, W] matrix with unit inner stride")
+        if b is not None and (b.shape != (W,) or not b.is_contiguous()):
+            raise ValueError("gnnx.gemm_chain: bias must be a contiguous [W] vector")
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    outs = [torch.empty((M, W), dtype=torch.float32, device=x.device) for _ in range(n)]
+    bits = [torch.empty((M, (W + 31) // 32), dtype=torch.int32, device=x.device) if want else None for _, _, _, want in layers]
+    prec = _default_precision if precision is None else precision
+    vp, i64, i32 = ctypes.c_void_p * n, ctypes.c_int64 * n, ctypes.c_int32 * n
+    lib().call("gnnx_gemm_chain", n, x.data_ptr(), _ld(x), vp(*[w.data_ptr() for w, _, _, _ in layers]),
+               i64(*[_ld(w) for w, _, _, _ in layers]), vp(*[_p(b) for _, b, _, _ in layers]),
+               i32(*[GEMM_RELU if relu else 0 for _, _, relu, _ in layers]), vp(*[o.data_ptr() for o in outs]), i64(*[W] * n),
+               vp(*[_p(t) for t in bits]), M, W, prec, _stream())
+    return outs, bits
+
+
 def colsum(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
     if not x.is_cuda or x.dtype != torch.float32:
         raise RuntimeError("gnnx.colsum: needs a CUDA float32 tensor")

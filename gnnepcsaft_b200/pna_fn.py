@@ -244,11 +244,18 @@ class PNAConvFn(Function):
             ops.gemm(x, pk.wx, trans_b=True, out=z[:, :Ho], accumulate=True)
             o = ops.pna_post_combine_fwd(z, pk.b0, g.rowptr, meta.avg_deg_log, relu=relu0)
         wf, bf = prep.wf, prep.bf
-        if pk.post:
-            os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True, want_masks=train)
+        mids = pk.post[:-1] if pk.post else []
+        if mids and wf.shape[0] == wf.shape[1] == o.shape[1] and all(w.shape == wf.shape for w, _ in mids):
+            # post layers 1 .. and the fused (last post Linear o lin) as ONE launch: a row tile goes through all of them
+            # and its intermediates come back from L2 (ops.gemm_chain; layer-by-layer where the kernel does not apply)
+            couts, cbits = ops.gemm_chain(o, [(w, b, True, train) for w, b in mids] + [(wf, bf, False, False)])
+            os_, omasks, out = [o] + couts[:-1], [None] + cbits[:-1], couts[-1]
         else:
-            os_, omasks = [o], [None]
-        out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
+            if pk.post:
+                os_, omasks = _chain_fwd(o, pk.post[:-1], relu_last=True, want_masks=train)
+            else:
+                os_, omasks = [o], [None]
+            out = ops.gemm(os_[-1], wf, trans_b=True, bias=bf)
         if CAPTURE_AGG is not None:
             # ReLU'd activations inside the pre / post chains (tests teacher-force their sign pattern onto the oracle):
             # pre in dst-sorted slot order, post in node order

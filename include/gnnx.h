@@ -180,6 +180,17 @@ GNNX_API int gnnx_gemm_dw_batched(int32_t n, const float* const* dY, const int64
                          const int64_t* ld_x, float* const* dW, const int64_t* ld_dw, int64_t Mo, int64_t No,
                          int64_t R, int32_t precision, void* workspace, size_t workspace_bytes, void* stream);
 
+/* A chain of n (<= 4) square Linear layers applied row by row: C[0] = act(A W[0]^T + bias[0]), C[p] = act(C[p-1] W[p]^T +
+ * bias[p]) with W[p] [width, width] row-major (torch Linear layout), flags[p] = GNNX_GEMM_RELU or 0, optional packed
+ * (C[p] > 0) masks.  Every C[p] is written (the backward needs the intermediates).  On the tensor-core tier with
+ * width % 32 == 0, width <= 256 and M >= 768 this is ONE launch whose work items are ordered so that an intermediate
+ * tile is read back from L2 by the CTA that wrote it (PyG: the post_nn / pre_nn Sequential(Linear, ReLU, Linear, ...)
+ * of PNAConv, torch_geometric PNAConv.__init__ as built at models.py:445-457); otherwise n gnnx_gemm calls with the
+ * same results.  The pointer / stride arrays live in HOST memory. */
+GNNX_API int gnnx_gemm_chain(int32_t n, const float* A, int64_t lda, const float* const* W, const int64_t* ld_w,
+                    const float* const* bias, const int32_t* flags, float* const* C, const int64_t* ld_c,
+                    uint32_t* const* relu_bits_out, int64_t M, int64_t width, int32_t precision, void* stream);
+
 /* Column sums (bias gradients): out[c] = sum_r in[r, c], deterministic two-pass. */
 GNNX_API size_t gnnx_colsum_workspace_bytes(int64_t rows, int64_t cols);
 GNNX_API int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* out,

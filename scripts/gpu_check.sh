@@ -1,3 +1,6 @@
 #!/bin/bash
-python -m pytest tests/test_gpu_ops.py tests/test_gpu_model.py -m gpu -q 2>&1 | tail -2
-for b in 0 1 0 1; do echo "GNNX_GATHER8=$b"; GNNX_GATHER8=$b python scripts/kernel_trace.py --workload cfg2 --steps 2 2>/dev/null | grep -E "k_pna_gather_fwd" | cut -c1-150; done
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -4
+for w in cfg2 cfg3 transformer; do
+  timeout 400 python bench.py --workload $w > gpurun_out/bench_r2i_$w.json 2> gpurun_out/bench_r2i_$w.err; tail -c 1500 gpurun_out/bench_r2i_$w.json | cut -c1-700
+done
