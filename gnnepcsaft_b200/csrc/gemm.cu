@@ -51,7 +51,7 @@ size_t gnnx_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K, int32_t ta, in
     size_t s = simt_workspace_bytes(M, N, K);
     if (!ta) {                                             // room for colsum_a_out: per-CTA partials or the two-pass kernel's
         size_t c = gnnx_colsum_workspace_bytes(M, K);
-        size_t f = (size_t)num_sms() * K * sizeof(float);
+        size_t f = (size_t)num_sms() * 2 * K * sizeof(float);    // two column-sum warps per CTA (gemm_tc.cu kCsWarps)
         if (f > c) c = f;
         if (c > s) s = c;
     }

@@ -256,7 +256,8 @@ constexpr int kA2 = 128 * 128;                  // 16 KB
 constexpr int kB2 = 256 * 128;                  // 32 KB
 constexpr int kStage2 = kA2 + kB2;              // 48 KB
 constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes + 256;
-constexpr int kThreads2 = 224;                  // + warp 6: column sums of the A tiles (the bias gradient riding a dX product)
+constexpr int kThreads2 = 256;                  // + warps 6, 7: column sums of the A tiles (the bias gradient riding a dX product)
+constexpr int kCsWarps = 1;                     // column-sum warps per CTA (two, 64 rows each, were measured: no faster -- reading a stage is ~1 us of a 42 us product)
 constexpr int kBackoffFlag = 1 << 16;             // internal launch flag: waiting roles sleep between polls
 constexpr int kColsumMaxK = 256;                // columns the fused sum covers (8 k-blocks of accumulators in registers)
 
@@ -273,12 +274,78 @@ struct Smem2 {
     __device__ uint32_t* tmem_ptr() const { return reinterpret_cast<uint32_t*>(bars() + 2 * kStages2 + 4); }
 };
 
-// kEpi8: eight epilogue warps (warps 2-5 and 7-10, two per TMEM lane quadrant, alternate 32-column chunks) instead of
-// four: an epilogue warp walks its chunks one after the other (TMEM load -> registers -> staging tile -> bulk store), and
-// the epilogue of a CTA's LAST tile overlaps nothing, so its length is a fixed cost of every launch.
-constexpr int kThreads2E8 = 352;
-template <bool kBMN, int kCluster, bool kEpi8 = false>
-__global__ void __launch_bounds__(kEpi8 ? kThreads2E8 : kThreads2, 1)
+// The column-sum warp's tail: fold the four row lanes and write this warp's partial row.
+__device__ __forceinline__ void colsum_store_partial(float4 (&acc)[kColsumMaxK / kBK], int lane, int cw, int KB, int K,
+                                                    float* __restrict__ colsum_partial) {
+    const int cj = lane & 7, rr = lane >> 3;
+    const int my_row = (int)blockIdx.x * kCsWarps + cw;
+#pragma unroll
+    for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
+        float4 v = acc[kb];                                   // fold the four row lanes (fixed order)
+#pragma unroll
+        for (int o = 8; o <= 16; o <<= 1) {
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+            v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+        }
+        const int col = kb * kBK + cj * 4;
+        if (kb < KB && rr == 0 && col < K)                    // K % 4 == 0 (tc_supported: lda % 4, TMA box)
+            *reinterpret_cast<float4*>(colsum_partial + (long long)my_row * K + col) = v;
+    }
+    __threadfence();
+}
+
+// After the kernel's final CTA-wide sync: the CTA that arrives LAST at the ticket folds all partial rows with all of its
+// threads (no second launch for the bias gradient).  One warp doing this alone took 13 us of a 55 us product: ~150 KB
+// through 16 loads in flight.  Here thread t owns the float4 column t % (K / 4) and the row group t / (K / 4); a group
+// walks its rows g, g + G, ... sixteen at a time, the groups are then summed in group order through `scratch` (shared
+// memory, >= 4 KB, free by now).  Which CTA folds varies from run to run, the order of the sum does not.  The ticket is
+// left at 0.  Every thread of the CTA must call this.
+__device__ __forceinline__ void colsum_cta_fold(int K, const float* __restrict__ colsum_partial, float* __restrict__ colsum_out,
+                                               int* __restrict__ ticket, float* scratch, int* flag) {
+    if (threadIdx.x == 0) {
+        __threadfence();
+        *flag = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!*flag) return;
+    __threadfence();
+    const int nrows = (int)gridDim.x * kCsWarps;
+    const int nc4 = K >> 2;                                   // float4 columns (<= 64)
+    const int G = (int)blockDim.x / nc4;                      // row groups (>= 4 at 256 threads)
+    const int c4 = (int)threadIdx.x % nc4, g = (int)threadIdx.x / nc4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (g < G) {
+        const float4* base = reinterpret_cast<const float4*>(colsum_partial) + c4;
+        // sixteen rows in flight; past the end the loads are clamped to the last row and their values dropped
+        // (unconditional loads: a load under a branch would serialise the round trips)
+        for (int r = g; r < nrows; r += 16 * G) {
+            float4 t[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) t[j] = __ldcg(base + (long long)min(r + j * G, nrows - 1) * nc4);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const bool ok = r + j * G < nrows;
+                s.x += ok ? t[j].x : 0.f; s.y += ok ? t[j].y : 0.f; s.z += ok ? t[j].z : 0.f; s.w += ok ? t[j].w : 0.f;
+            }
+        }
+        reinterpret_cast<float4*>(scratch)[g * nc4 + c4] = s;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < nc4) {
+        float4 o = reinterpret_cast<const float4*>(scratch)[threadIdx.x];
+        for (int j = 1; j < G; ++j) {
+            const float4 t = reinterpret_cast<const float4*>(scratch)[j * nc4 + threadIdx.x];
+            o.x += t.x; o.y += t.y; o.z += t.z; o.w += t.w;
+        }
+        reinterpret_cast<float4*>(colsum_out)[threadIdx.x] = o;
+    }
+    if (threadIdx.x == 0) *ticket = 0;
+}
+
+// (An eight-epilogue-warp variant was measured and removed: dX products 84.0 us against 81.9, forward 72.2 against 71.7 --
+// the un-overlapped last epilogue is not what limits a launch.  DESIGN.md 8.1.)
+template <bool kBMN, int kCluster>
+__global__ void __launch_bounds__(kThreads2, 1)
 k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
                   const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
@@ -293,11 +360,11 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages2; ++s) {
             mbar_init(sm.full(s), 1);
-            mbar_init(sm.empty(s), kCluster + (colsum_partial ? 1 : 0));     // + this CTA's column-sum warp
+            mbar_init(sm.empty(s), kCluster + (colsum_partial ? kCsWarps : 0));     // + this CTA's column-sum warps
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(sm.tmem_full(b), 1);
-            mbar_init(sm.tmem_empty(b), kEpi8 ? 8 : 4);
+            mbar_init(sm.tmem_empty(b), 4);
         }
         mbar_fence_init();
     }
@@ -377,7 +444,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 }
             }
         }
-    } else if (warp == 6) {
+    } else if (warp >= 6 && warp < 6 + kCsWarps) {
         // Column sums of A over this CTA's row tiles: out[k] = sum_m A[m, k] (rows past M arrive as TMA zero fill).
         // Lane l reads the 16-byte chunk (l & 7) -- columns 4(l&7)..+3 of the k-block -- of rows (l >> 3), +4, +8, ...;
         // a stage is released to the producer only after this warp has read it.
@@ -385,7 +452,7 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             float4 acc[kColsumMaxK / kBK];
 #pragma unroll
             for (int j = 0; j < kColsumMaxK / kBK; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            const int cj = lane & 7, rr = lane >> 3;
+            const int cj = lane & 7, rr = (lane >> 3) + (warp - 6) * (128 / kCsWarps);
             int stage = 0;
             uint32_t phase = 0;
             for (int w = cid; w < work; w += ncl) {
@@ -397,8 +464,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                         if (first_n) {
                             const uint8_t* a = sm.base + stage * kStage2;
                             float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
-#pragma unroll 8
-                            for (int r = rr; r < 128; r += 8) {       // K-major SW128: 16-byte chunk index ^ (row & 7)
+#pragma unroll
+                            for (int r = rr; r < rr + 128 / kCsWarps; r += 8) {       // K-major SW128: 16-byte chunk index ^ (row & 7)
                                 const float4 v0 = *reinterpret_cast<const float4*>(a + r * 128 + ((cj ^ (r & 7)) << 4));
                                 const float4 v1 = *reinterpret_cast<const float4*>(a + (r + 4) * 128 + ((cj ^ ((r + 4) & 7)) << 4));
                                 s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
@@ -412,62 +479,10 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     }
                 }
             }
-#pragma unroll
-            for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
-                float4 v = acc[kb];                                   // fold the four row lanes (fixed order)
-#pragma unroll
-                for (int o = 8; o <= 16; o <<= 1) {
-                    v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
-                    v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
-                }
-                const int col = kb * kBK + cj * 4;
-                if (kb < KB && rr == 0 && col < K)                    // K % 4 == 0 (tc_supported: lda % 4, TMA box)
-                    *reinterpret_cast<float4*>(colsum_partial + (long long)blockIdx.x * K + col) = v;
-            }
-            // The CTA whose partial row lands last folds all of them, in CTA order (which CTA that is varies from run to
-            // run, the order of the sum does not): no second launch for the bias gradient.  The ticket is left at 0.
-            __threadfence();
-            __syncwarp();
-            int last = 0;
-            if (lane == 0) last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
-            last = __shfl_sync(0xffffffffu, last, 0);
-            if (last) {
-                __threadfence();
-                const int nb = (int)gridDim.x;
-                // lane l folds columns 4l..4l+3 and 128+4l..; 8 partial rows x 2 column groups = 16 loads in flight
-                const int c0 = lane * 4, c1 = c0 + 128;
-                const bool h0 = c0 < K, h1 = c1 < K;
-                float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
-                const float4 z = s0;
-                int b = 0;
-                for (; b + 8 <= nb; b += 8) {
-                    float4 t0[8], t1[8];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float* p = colsum_partial + (long long)(b + j) * K;
-                        t0[j] = h0 ? __ldcg(reinterpret_cast<const float4*>(p + c0)) : z;
-                        t1[j] = h1 ? __ldcg(reinterpret_cast<const float4*>(p + c1)) : z;
-                    }
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        s0.x += t0[j].x; s0.y += t0[j].y; s0.z += t0[j].z; s0.w += t0[j].w;
-                        s1.x += t1[j].x; s1.y += t1[j].y; s1.z += t1[j].z; s1.w += t1[j].w;
-                    }
-                }
-                for (; b < nb; ++b) {
-                    const float* p = colsum_partial + (long long)b * K;
-                    if (h0) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p + c0)); s0.x += t.x; s0.y += t.y; s0.z += t.z; s0.w += t.w; }
-                    if (h1) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p + c1)); s1.x += t.x; s1.y += t.y; s1.z += t.z; s1.w += t.w; }
-                }
-                if (h0) *reinterpret_cast<float4*>(colsum_out + c0) = s0;
-                if (h1) *reinterpret_cast<float4*>(colsum_out + c1) = s1;
-                if (lane == 0) *ticket = 0;
-            }
+            colsum_store_partial(acc, lane, warp - 6, KB, K, colsum_partial);
         }
-    } else {
+    } else if (warp < 6) {
         const int q = warp & 3;
-        const int second = kEpi8 && warp > 6 ? 1 : 0;                 // second epilogue warp of this quadrant
-        uint8_t* stage1 = kEpi8 ? reinterpret_cast<uint8_t*>(sm.epi(0)) + ((warp > 6 ? warp - 3 : warp - 2) * 4096) : nullptr;
         uint32_t it = 0, i = 0;
         const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask));
         if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
@@ -479,9 +494,8 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
                 if (use_tma)
-                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits,
-                                 kEpi8 ? 32 * second : 0, kEpi8 ? 64 : 32, stage1);
-                else if (!second)
+                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
+                else
                     epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags, mask, ldm);
             }
             tc_fence_before();
@@ -497,6 +511,198 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
     }
+    if (colsum_partial)                                              // staging tiles and the TMEM-pointer slot are free by now
+        colsum_cta_fold(K, colsum_partial, colsum_out, ticket, sm.epi(0), reinterpret_cast<int*>(sm.tmem_ptr()) + 1);
+}
+
+// ------------------------------------------------------------------ the same product on CTA PAIRS (cta_group::2)
+// k_gemm_tf32_rows2 stages the WHOLE weight tile in each CTA (48 KB stages: 16 KB of A rows, 32 KB of weights, 4 stages).
+// Measured: these products are bound by bytes in flight -- 64 KB of A per SM against a ~3.8 us
+// release -> refill loop is 17 KB/us, a 128-row tile per 7.7 us where HBM would allow 5.8.  A CTA pair issues ONE
+// tcgen05.mma.cta_group::2 (M = 256: 128 rows from each SM) that reads half of the weight tile from each CTA's shared
+// memory, so a stage is 16 KB + 16 KB and the same 192 KB hold SIX stages: 96 KB of A in flight per SM.  Each CTA loads
+// its own A rows and its own half of the weights (no multicast: half the L2 -> SM weight traffic of rows2<.., 2>); both
+// signal the LEADER's full barrier, the leader's MMA thread releases the stage in both CTAs with a multicast commit.
+// Same accumulation order over K as rows2, same epilogue: results are bit-identical (tests/test_gpu_gemm_pair.py).
+constexpr int kStagesP = 6;
+constexpr int kBP = 128 * 128;                  // this CTA's half of a weight stage (<= 128 rows / 4 chunks of 32 columns)
+constexpr int kStageP = kA2 + kBP;              // 32 KB
+constexpr int kSmemP = 1024 + kStagesP * kStageP + kEpiBytes + 256;
+
+struct SmemP {
+    uint8_t* base;
+    __device__ uint32_t a(int s) const { return smem_u32(base + s * kStageP); }
+    __device__ uint32_t b(int s) const { return smem_u32(base + s * kStageP + kA2); }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStagesP * kStageP + q * 8192); }
+    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStagesP * kStageP + kEpiBytes); }
+    __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }                       // used in the leader only
+    __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStagesP + s); }
+    __device__ uint32_t afull(int s) const { return smem_u32(bars() + 2 * kStagesP + s); }       // "stage landed", forwarded to the column-sum warps
+    __device__ uint32_t tmem_full(int b) const { return smem_u32(bars() + 3 * kStagesP + b); }
+    __device__ uint32_t tmem_empty(int b) const { return smem_u32(bars() + 3 * kStagesP + 2 + b); }   // used in the leader only
+    __device__ uint32_t* tmem_ptr() const { return reinterpret_cast<uint32_t*>(bars() + 3 * kStagesP + 4); }
+};
+
+template <bool kBMN>
+__global__ void __launch_bounds__(kThreads2, 1)
+k_gemm_tf32_pair(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, float* __restrict__ C, long long ldc, int M, int N, int K, int BN,
+                 const float* __restrict__ bias, int flags, const float* __restrict__ mask, long long ldm,
+                 uint32_t* __restrict__ bits_out, long long ldbits, float* __restrict__ colsum_partial,
+                 const int* __restrict__ bucket_ptr, int n_groups, int group_rows, float* __restrict__ colsum_out,
+                 int* __restrict__ ticket) {
+    extern __shared__ uint8_t smem_raw[];
+    SmemP sm;
+    sm.base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();                       // 0: the leader (issues the MMAs)
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStagesP; ++s) {
+            mbar_init(sm.full(s), 1);                                // the leader's expect_tx arrival; bytes of BOTH CTAs
+            mbar_init(sm.empty(s), 1 + (colsum_partial ? kCsWarps : 0));   // the pair's commit (+ this CTA's column-sum warps)
+            mbar_init(sm.afull(s), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(sm.tmem_full(b), 1);
+            mbar_init(sm.tmem_empty(b), 8);                          // four epilogue warps of each CTA
+        }
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc_pair(smem_u32(sm.tmem_ptr()), kTmemCols);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr();
+    pdl_enter();
+
+    const int n_tiles = (N + BN - 1) / BN;
+    const int m_groups = ((M + 127) / 128 + 1) / 2;
+    const int work = n_tiles * m_groups;
+    const int cid = blockIdx.x / 2, ncl = gridDim.x / 2;
+    const int KB = (K + kBK - 1) / kBK;
+    const int half = BN / 2;                                         // weight rows (K-major) / columns (MN-major) held by each CTA
+
+    if (warp == 0) {
+        if (lane == 0) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx = 2u * (kA2 + (uint32_t)half * 128u);
+            for (int w = cid; w < work; w += ncl) {
+                const int m0 = ((w / n_tiles) * 2 + rank) * 128, n0 = (w % n_tiles) * BN;
+                int goff = 0;
+                if (bucket_ptr) {
+                    const int mbase = (w / n_tiles) * 256;
+                    for (int d = 1; d < n_groups; ++d) goff += (mbase >= __ldg(bucket_ptr + d)) ? group_rows : 0;
+                }
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.empty(stage), phase ^ 1);
+                    const uint32_t lead_full = mapa_cluster(sm.full(stage), 0);
+                    if (rank == 0) mbar_expect_tx(sm.full(stage), tx);
+                    tma_load_2d_pair(sm.a(stage), &tmA, lead_full, kb * kBK, m0);
+                    if (kBMN) tma_load_3d_pair(sm.b(stage), &tmB, lead_full, 0, kb * kBK + goff, n0 / 32 + rank * (half / 32));
+                    else tma_load_2d_pair(sm.b(stage), &tmB, lead_full, kb * kBK, n0 + rank * half + goff);
+                    if (++stage == kStagesP) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            const uint32_t idesc = make_idesc_tf32(256, BN, 0, kBMN ? 1 : 0);
+            int stage = 0;
+            uint32_t phase = 0, i = 0;
+            for (int w = cid; w < work; w += ncl, ++i) {
+                const uint32_t buf = i & 1;
+                mbar_wait_cluster(sm.tmem_empty(buf), ((i >> 1) & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(sm.full(stage), phase);
+                    tc_fence_after();
+                    if (colsum_partial) {                            // the column-sum warps of both CTAs may read the stage now
+                        mbar_arrive(sm.afull(stage));
+                        mbar_arrive_cluster(mapa_cluster(sm.afull(stage), 1));
+                    }
+#pragma unroll
+                    for (int k = 0; k < kBK / 8; ++k) {
+                        const uint64_t bdesc = kBMN ? make_smem_desc(sm.b(stage) + k * 1024, 32 * 128, 512, kLayoutSw128B32)
+                                                    : make_smem_desc(sm.b(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        const uint64_t adesc = make_smem_desc(sm.a(stage) + k * 32, 16, 1024, kLayoutSw128);
+                        mma_tf32_pair(tmem_base + buf * 256, adesc, bdesc, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    mma_commit_pair(sm.empty(stage), 3);
+                    if (kb == KB - 1) mma_commit_pair(sm.tmem_full(buf), 3);
+                    if (++stage == kStagesP) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 6 && warp < 6 + kCsWarps) {
+        // column sums of this CTA's A tiles (see k_gemm_tf32_rows2); the "stage landed" signal comes from the leader's MMA thread
+        if (colsum_partial) {
+            float4 acc[kColsumMaxK / kBK];
+#pragma unroll
+            for (int j = 0; j < kColsumMaxK / kBK; ++j) acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int cj = lane & 7, rr = (lane >> 3) + (warp - 6) * (128 / kCsWarps);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int w = cid; w < work; w += ncl) {
+                const bool first_n = (w % n_tiles) == 0;
+#pragma unroll
+                for (int kb = 0; kb < kColsumMaxK / kBK; ++kb) {
+                    if (kb < KB) {
+                        mbar_wait_cluster(sm.afull(stage), phase);
+                        if (first_n) {
+                            const uint8_t* a = sm.base + stage * kStageP;
+                            float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+#pragma unroll
+                            for (int r = rr; r < rr + 128 / kCsWarps; r += 8) {
+                                const float4 v0 = *reinterpret_cast<const float4*>(a + r * 128 + ((cj ^ (r & 7)) << 4));
+                                const float4 v1 = *reinterpret_cast<const float4*>(a + (r + 4) * 128 + ((cj ^ ((r + 4) & 7)) << 4));
+                                s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+                                s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
+                            }
+                            acc[kb].x += s0.x + s1.x; acc[kb].y += s0.y + s1.y; acc[kb].z += s0.z + s1.z; acc[kb].w += s0.w + s1.w;
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(sm.empty(stage));
+                        if (++stage == kStagesP) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+            colsum_store_partial(acc, lane, warp - 6, KB, K, colsum_partial);
+        }
+    } else if (warp < 6) {
+        const int q = warp & 3;
+        uint32_t it = 0, i = 0;
+        const bool use_tma = !((flags & GNNX_GEMM_ACCUMULATE) && ((flags & GNNX_GEMM_RELU) || mask));
+        if (use_tma && lane == 0) tma_prefetch_desc(&tmC);
+        for (int w = cid; w < work; w += ncl, ++i) {
+            const int m0 = ((w / n_tiles) * 2 + rank) * 128, n0 = (w % n_tiles) * BN;
+            const uint32_t buf = i & 1;
+            mbar_wait_cluster(sm.tmem_full(buf), (i >> 1) & 1);
+            tc_fence_after();
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
+            if (m0 < M) {
+                if (use_tma)
+                    epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
+                else
+                    epilogue_acc(sm, tmem_base + buf * 256, q, lane, C, ldc, (long long)m0, M, n0, N, ncols, bias, flags, mask, ldm);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_cluster(sm.tmem_empty(buf), 0));   // both CTAs' epilogues free the pair's accumulator
+        }
+        if (use_tma && lane == 0) tma_store_wait_all();
+    }
+    tc_fence_before();
+    __syncwarp();
+    cluster_sync_all();                                              // no CTA may exit (or free TMEM) while the pair's MMAs / commits can reach it
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, kTmemCols);
+    }
+    if (colsum_partial)
+        colsum_cta_fold(K, colsum_partial, colsum_out, ticket, sm.epi(0), reinterpret_cast<int*>(sm.tmem_ptr()) + 1);
 }
 
 // ------------------------------------------------------------------ Linear -> ReLU -> Linear (-> ...) chains, ONE launch
@@ -1296,8 +1502,8 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
             GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
-            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_rows2<true, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_pair<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemP));
+            GNNX_CUDA(cudaFuncSetAttribute(k_gemm_tf32_pair<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemP));
             return GNNX_OK;
         });
         if (rc) return rc;
@@ -1380,26 +1586,25 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
         int* tk = nullptr;                               // arrival counter: the last CTA folds the partials in-kernel
         if (colsum_a_out) {
             GNNX_REQUIRE(K <= kColsumMaxK, "gemm_tc: fused column sums cover K <= %d", kColsumMaxK);
-            GNNX_REQUIRE(ws && ws_bytes >= (size_t)ncl * cluster * K * sizeof(float), "gemm_tc: workspace too small for the column-sum partials");
+            GNNX_REQUIRE(ws && ws_bytes >= (size_t)ncl * cluster * kCsWarps * K * sizeof(float), "gemm_tc: workspace too small for the column-sum partials");
             csp = (float*)ws;
             GNNX_REQUIRE(((uintptr_t)colsum_a_out & 15) == 0, "gemm_tc: colsum_a_out must be 16-byte aligned");
             tk = stream_ticket(st);
             if (!tk) return set_error(GNNX_ERR_INVALID, "gemm_tc: could not allocate the column-sum ticket");
         }
         cudaError_t e;
+        // CTA pairs (cta_group::2): read per call so that a test can compare both kernels in one process
+        const char* pe = getenv("GNNX_GEMM_PAIR");
+        const bool pair = cluster == 2 && BN % 64 == 0 && pe && pe[0] == '1';
         if (trace_on())
-            trace_before(cluster == 4 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 4> : (const void*)k_gemm_tf32_rows2<true, 4>)
+            trace_before(pair ? (tb ? (const void*)k_gemm_tf32_pair<false> : (const void*)k_gemm_tf32_pair<true>)
+                         : cluster == 4 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 4> : (const void*)k_gemm_tf32_rows2<true, 4>)
                          : cluster == 2 ? (tb ? (const void*)k_gemm_tf32_rows2<false, 2> : (const void*)k_gemm_tf32_rows2<true, 2>)
                                       : (tb ? (const void*)k_gemm_tf32_rows2<false, 1> : (const void*)k_gemm_tf32_rows2<true, 1>), st);
-        // GNNX_GEMM_EPI8=1: eight epilogue warps.  Measured on a B200 (cfg2): dX products 84.0 us against 81.9, forward 72.2
-        // against 71.7 -- the un-overlapped last epilogue is not what the fixed ~12 us per launch is made of.  Off.
-        static std::once_flag e8_once;
-        static int epi8 = 0;
-        std::call_once(e8_once, [] { const char* e = getenv("GNNX_GEMM_EPI8"); epi8 = (e && e[0] == '1') ? 1 : 0; });
-        if (epi8 && cluster == 2) {
-            cfg.blockDim = dim3(kThreads2E8);
-            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 2, true>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
-                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 2, true>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
+        if (pair) {
+            cfg.dynamicSmemBytes = kSmemP;
+            e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_pair<false>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
+                   : cudaLaunchKernelEx(&cfg, k_gemm_tf32_pair<true>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
         } else if (cluster == 4)
             e = tb ? cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<false, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk)
                    : cudaLaunchKernelEx(&cfg, k_gemm_tf32_rows2<true, 4>, mA, mB, mC, C, ldc_, Mi, Ni, Ki, BN, bias, flags, mask, ldm_, bits_out, ldbits, csp, bucket_ptr, n_groups, group_rows, colsum_a_out, tk);
