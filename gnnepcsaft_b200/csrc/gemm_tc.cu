@@ -49,6 +49,7 @@ constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + 128;
 constexpr int kTmemCols = 512;
 
 struct Smem {
+    static constexpr int kBufs = 2;                 // TMA-store staging tiles per epilogue warp
     uint8_t* base;      // 1024-aligned
     __device__ uint32_t a(int s) const { return smem_u32(base + s * kStageBytes); }
     __device__ uint32_t b(int s) const { return smem_u32(base + s * kStageBytes + kAStage); }
@@ -196,8 +197,8 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
         }
         float v[32];
         tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
-        uint8_t* buf = stage1 ? stage : stage + (it & 1) * 4096;
-        if (lane == 0) { if (stage1) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }   // the store that last read this buffer has drained it
+        uint8_t* buf = stage1 ? stage : stage + (it % SM::kBufs) * 4096;
+        if (lane == 0) { if (stage1) tma_store_wait_read<0>(); else tma_store_wait_read<SM::kBufs - 1>(); }   // the store that last read this buffer has drained it
         __syncwarp();
         tmem_ld_wait();
         if (bias) {
@@ -251,22 +252,32 @@ __device__ __forceinline__ void epilogue_tma(const SM& sm, uint32_t tmem_acc, in
 // (a thread-block cluster, adjacent row tiles, same N tile) each load HALF of every weight stage and multicast it to
 // both, so the L2 traffic per output element equals that of a 256-row tile.  A stage is released to the producers of
 // BOTH CTAs by a multicast tcgen05.commit (empty barriers count kCluster arrivals).
-constexpr int kStages2 = 4;
+#ifndef GNNX_ROWS2_STAGES
+#define GNNX_ROWS2_STAGES 4
+#endif
+#ifndef GNNX_ROWS2_BUFS
+#define GNNX_ROWS2_BUFS 2
+#endif
+constexpr int kStages2 = GNNX_ROWS2_STAGES;
+constexpr int kEpiBufs2 = GNNX_ROWS2_BUFS;      // TMA-store staging tiles (4 KB) per epilogue warp
+constexpr int kEpiBytes2 = 4 * kEpiBufs2 * 4096;
 constexpr int kA2 = 128 * 128;                  // 16 KB
 constexpr int kB2 = 256 * 128;                  // 32 KB
 constexpr int kStage2 = kA2 + kB2;              // 48 KB
-constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes + 256;
+constexpr int kSmem2 = 1024 + kStages2 * kStage2 + kEpiBytes2 + 256;
+static_assert(kSmem2 <= 232448, "rows2: shared memory");
 constexpr int kThreads2 = 256;                  // + warps 6, 7: column sums of the A tiles (the bias gradient riding a dX product)
 constexpr int kCsWarps = 1;                     // column-sum warps per CTA (two, 64 rows each, were measured: no faster -- reading a stage is ~1 us of a 42 us product)
 constexpr int kBackoffFlag = 1 << 16;             // internal launch flag: waiting roles sleep between polls
 constexpr int kColsumMaxK = 256;                // columns the fused sum covers (8 k-blocks of accumulators in registers)
 
 struct Smem2 {
+    static constexpr int kBufs = kEpiBufs2;
     uint8_t* base;
     __device__ uint32_t a(int s) const { return smem_u32(base + s * kStage2); }
     __device__ uint32_t b(int s) const { return smem_u32(base + s * kStage2 + kA2); }
-    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages2 * kStage2 + q * 8192); }
-    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStages2 * kStage2 + kEpiBytes); }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStages2 * kStage2 + q * kEpiBufs2 * 4096); }
+    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStages2 * kStage2 + kEpiBytes2); }
     __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }
     __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStages2 + s); }
     __device__ uint32_t tmem_full(int b) const { return smem_u32(bars() + 2 * kStages2 + b); }
@@ -489,9 +500,9 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int w = cid; w < work; w += ncl, ++i) {
             const int m0 = ((w / n_tiles) * kCluster + rank) * 128, n0 = (w % n_tiles) * BN;
             const uint32_t buf = i & 1;
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             wait(sm.tmem_full(buf), (i >> 1) & 1, 128);
             tc_fence_after();
-            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
                 if (use_tma)
                     epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
@@ -524,17 +535,27 @@ k_gemm_tf32_rows2(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // its own A rows and its own half of the weights (no multicast: half the L2 -> SM weight traffic of rows2<.., 2>); both
 // signal the LEADER's full barrier, the leader's MMA thread releases the stage in both CTAs with a multicast commit.
 // Same accumulation order over K as rows2, same epilogue: results are bit-identical (tests/test_gpu_gemm_pair.py).
-constexpr int kStagesP = 6;
+#ifndef GNNX_PAIR_STAGES
+#define GNNX_PAIR_STAGES 6
+#endif
+#ifndef GNNX_PAIR_BUFS
+#define GNNX_PAIR_BUFS 2
+#endif
+constexpr int kStagesP = GNNX_PAIR_STAGES;
+constexpr int kEpiBufsP = GNNX_PAIR_BUFS;
+constexpr int kEpiBytesP = 4 * kEpiBufsP * 4096;
 constexpr int kBP = 128 * 128;                  // this CTA's half of a weight stage (<= 128 rows / 4 chunks of 32 columns)
 constexpr int kStageP = kA2 + kBP;              // 32 KB
-constexpr int kSmemP = 1024 + kStagesP * kStageP + kEpiBytes + 256;
+constexpr int kSmemP = 1024 + kStagesP * kStageP + kEpiBytesP + 256;
+static_assert(kSmemP <= 232448, "pair: shared memory");
 
 struct SmemP {
+    static constexpr int kBufs = kEpiBufsP;
     uint8_t* base;
     __device__ uint32_t a(int s) const { return smem_u32(base + s * kStageP); }
     __device__ uint32_t b(int s) const { return smem_u32(base + s * kStageP + kA2); }
-    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStagesP * kStageP + q * 8192); }
-    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStagesP * kStageP + kEpiBytes); }
+    __device__ float* epi(int q) const { return reinterpret_cast<float*>(base + kStagesP * kStageP + q * kEpiBufsP * 4096); }
+    __device__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + kStagesP * kStageP + kEpiBytesP); }
     __device__ uint32_t full(int s) const { return smem_u32(bars() + s); }                       // used in the leader only
     __device__ uint32_t empty(int s) const { return smem_u32(bars() + kStagesP + s); }
     __device__ uint32_t afull(int s) const { return smem_u32(bars() + 2 * kStagesP + s); }       // "stage landed", forwarded to the column-sum warps
@@ -679,9 +700,9 @@ k_gemm_tf32_pair(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int w = cid; w < work; w += ncl, ++i) {
             const int m0 = ((w / n_tiles) * 2 + rank) * 128, n0 = (w % n_tiles) * BN;
             const uint32_t buf = i & 1;
+            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             mbar_wait_cluster(sm.tmem_full(buf), (i >> 1) & 1);
             tc_fence_after();
-            const int ncols = min(BN, ((N - n0) + 31) / 32 * 32);
             if (m0 < M) {
                 if (use_tma)
                     epilogue_tma(sm, tmem_base + buf * 256, q, lane, &tmC, m0, M, n0, ncols, bias, N, flags, it, mask, ldm, bits_out, ldbits);
