@@ -50,6 +50,7 @@ bool pdl_enabled();
 // Per-kernel device timeline (gnnx_trace_begin / gnnx_trace_end): while a trace is open every launch() is bracketed by
 // two CUDA events on its stream, so the report gives each kernel's in-situ duration (warm caches, real predecessors)
 // and the time the stream spent between gnnx kernels (other libraries' kernels, launch gaps).
+int* stream_ticket(cudaStream_t stream);   // gemm_tc.cu: 64 zero-initialised ints per (device, stream); every user leaves its ints at 0
 bool trace_on();
 void trace_before(const void* func, cudaStream_t st);
 void trace_after(cudaStream_t st);

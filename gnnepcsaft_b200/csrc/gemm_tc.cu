@@ -1462,7 +1462,7 @@ using namespace tc;
 // stream -- e.g. the capture stream of a CUDA graph -- involves no CUDA call at all (cudaMalloc / cudaMemset are not
 // allowed while a stream is being captured; the first tensor-core product of a process must therefore run eagerly,
 // which the usual warm-up step before a capture does anyway).
-static int* stream_ticket(cudaStream_t stream) {
+int* stream_ticket(cudaStream_t stream) {   // 64 ints per stream: [0] the GEMM column-sum ticket, [8..9] BatchNorm's grid barrier
     constexpr int kSlots = 1024, kStride = 64;             // ints: 256 B apart
     struct Pool { int* base = nullptr; int next = 0; std::map<cudaStream_t, int> slot; };
     static std::mutex mu;

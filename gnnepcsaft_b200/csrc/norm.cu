@@ -3,6 +3,8 @@
 // Reductions over rows are two-pass and deterministic: per-chunk partials (Welford/Chan for the
 // variance) merged in chunk order -- no atomics.
 #include "common.cuh"
+#include <atomic>
+#include <cstdlib>
 
 namespace gnnx {
 
@@ -183,6 +185,178 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
     }
 }
 
+// ------------------------------------------------------------------ training forward as ONE cooperative launch
+// statistics -> (grid barrier) -> per-channel finalisation, channel c by CTA c -> (grid barrier) -> normalise + ReLU.
+// Three launches become one, and the second pass re-reads rows this launch has just read: phase 1 loads them with the
+// default policy (they stay in L2 as far as its 126 MB go; [101 887 x 256] fp32 is 104 MB), phase 2 streams them,
+// each CTA walking its rows backwards (most recently read first).
+// The grid is sized by the host so that every CTA is resident (SMs x co-resident CTAs): the barrier is an arrival
+// counter in global memory that thread 0 of each CTA polls with acquire loads; a counter that never fills traps after
+// ~2 s instead of hanging the GPU.  counters[0] counts arrivals (nch per barrier), counters[1] exits; the last CTA out
+// zeroes both for the next launch on the stream.
+__device__ __forceinline__ void grid_barrier(int* counter, int target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1);
+        long long t0 = 0;
+        for (unsigned it = 0;; ++it) {
+            int v;
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            if (v >= target) break;
+            __nanosleep(40);
+            if ((it & 4095u) == 4095u) {
+                long long now = clock64();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 4000000000ll) __trap();
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+k_bn_fwd_coop(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial,
+              const int* __restrict__ row_node, float eps, float momentum, float* __restrict__ running_mean,
+              float* __restrict__ running_var, float* __restrict__ save_mean, float* __restrict__ save_rstd,
+              const float* __restrict__ weight, const float* __restrict__ bias, int relu, float* __restrict__ y,
+              NodeDropout drop, int* __restrict__ counters) {
+    pdl_enter();
+    __shared__ float sh[4][3][256 + 4];
+    const int nch = (int)gridDim.x;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int r0 = blockIdx.x * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    int rp = r0;                                          // pilot: a row of the batch (see k_bn_stats_partial)
+    if (row_node)
+        while (rp < r1 && __ldg(row_node + rp) < 0) ++rp;
+    // ---- phase 1: (n, mean, M2) of this CTA's rows, per column
+    for (int c0 = 0; c0 < C; c0 += 256) {
+        const int c = c0 + tx * 4;
+        F4 s, q, p;
+        s.q = q.q = p.q = make_float4(0.f, 0.f, 0.f, 0.f);
+        float n = 0.f;
+        if (c < C && rp < r1) {
+            p.q = ldg4(x + (long long)rp * C + c);
+            int r = r0 + ty;
+            for (; r + 12 < r1; r += 16) {
+                F4 v[4];
+                bool ok[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    v[u].q = ldg4(x + (long long)(r + 4 * u) * C + c);
+                    ok[u] = !row_node || row_node[r + 4 * u] >= 0;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { float d = ok[u] ? v[u].a[j] - p.a[j] : 0.f; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+                    n += ok[u] ? 1.f : 0.f;
+                }
+            }
+            for (; r < r1; r += 4) {
+                F4 v;
+                v.q = ldg4(x + (long long)r * C + c);
+                const bool ok = !row_node || row_node[r] >= 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { float d = ok ? v.a[j] - p.a[j] : 0.f; s.a[j] += d; q.a[j] = fmaf(d, d, q.a[j]); }
+                n += ok ? 1.f : 0.f;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float mean = n > 0.f ? p.a[j] + s.a[j] / n : 0.f;
+            float m2 = n > 0.f ? fmaxf(q.a[j] - s.a[j] * s.a[j] / n, 0.f) : 0.f;
+            sh[ty][0][tx * 4 + j] = n; sh[ty][1][tx * 4 + j] = mean; sh[ty][2][tx * 4 + j] = m2;
+        }
+        __syncthreads();
+        const int cc = c0 + threadIdx.x;
+        if (cc < C) {
+            Welford t = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                Welford o = {sh[i][0][threadIdx.x], sh[i][1][threadIdx.x], sh[i][2][threadIdx.x]};
+                welford_merge(t, o);
+            }
+            float* pp = partial + (long long)blockIdx.x * 3 * C;
+            pp[cc] = t.n; pp[C + cc] = t.mean; pp[2 * C + cc] = t.m2;
+        }
+        __syncthreads();
+    }
+    grid_barrier(counters, nch);
+    // ---- finalisation: channel c by CTA c (+ k * grid): thread t merges chunks t, t + 256, ... in order, then a fixed
+    // shuffle tree per warp and the eight warps in order
+    for (int c = blockIdx.x; c < C; c += nch) {
+        Welford t = {0.f, 0.f, 0.f};
+        for (int ch = threadIdx.x; ch < nch; ch += 256) {
+            const float* p = partial + (long long)ch * 3 * C;
+            Welford o = {__ldcg(p + c), __ldcg(p + C + c), __ldcg(p + 2 * C + c)};
+            welford_merge(t, o);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            Welford o = {__shfl_down_sync(0xffffffffu, t.n, off), __shfl_down_sync(0xffffffffu, t.mean, off),
+                         __shfl_down_sync(0xffffffffu, t.m2, off)};
+            welford_merge(t, o);
+        }
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { sh[0][0][threadIdx.x >> 5] = t.n; sh[0][1][threadIdx.x >> 5] = t.mean; sh[0][2][threadIdx.x >> 5] = t.m2; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            Welford a = {0.f, 0.f, 0.f};
+            for (int w = 0; w < 8; ++w) {
+                Welford o = {sh[0][0][w], sh[0][1][w], sh[0][2][w]};
+                welford_merge(a, o);
+            }
+            const float var = a.m2 / a.n;
+            save_mean[c] = a.mean;
+            save_rstd[c] = rsqrtf(var + eps);
+            if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * a.mean;
+            if (running_var) {
+                const float unbiased = a.n > 1.f ? a.m2 / (a.n - 1.f) : var;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+            }
+        }
+    }
+    grid_barrier(counters, 2 * nch);
+    // ---- phase 2: normalise this CTA's rows (the addresses phase 1 read)
+    for (int c0 = 0; c0 < C; c0 += 256) {
+        const int c = c0 + tx * 4;
+        if (c >= C) continue;
+        F4 mu, rs, w, b;
+        mu.q = __ldcg(reinterpret_cast<const float4*>(save_mean + c)); rs.q = __ldcg(reinterpret_cast<const float4*>(save_rstd + c));
+        w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        b.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        // last rows first: what phase 1 read most recently is what L2 still holds
+        for (int r = r0 + ty + 16 * max(0, (r1 - r0 - ty + 15) / 16 - 1); r >= r0 + ty; r -= 16) {
+            F4 v[4];
+            long long orow[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int rr = min(r + 4 * u, r1 - 1);                  // clamped: the loads stay unconditional
+                v[u].q = ldg4_stream(x + (long long)rr * C + c);
+                orow[u] = r + 4 * u < r1 ? (row_node ? (long long)row_node[rr] : (long long)rr) : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (orow[u] < 0) continue;
+                F4 o;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float t = bn_affine(v[u].a[j], mu.a[j], rs.a[j], w.a[j], b.a[j]);
+                    t = relu ? fmaxf(t, 0.f) : t;
+                    o.a[j] = drop_apply(drop, orow[u] * C + c + j, t);
+                }
+                stg4(y + orow[u] * C + c, o.q);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(counters + 1, 1) == nch - 1) { counters[0] = 0; counters[1] = 0; __threadfence(); }
+    }
+}
+
 // partial: [nchunks][2][C] = (sum dy', sum dy' * xhat); same thread layout as k_bn_stats_partial
 __global__ void __launch_bounds__(256)
 k_bn_bwd_partial(const float* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ y,
@@ -314,6 +488,132 @@ __global__ void k_bn_bwd_apply(const float* __restrict__ dy, const float* __rest
             o.a[j] = w.a[j] * rs.a[j] * (gg - db.a[j] * inv_n - xh * dw.a[j] * inv_n);
         }
         stg4(dx + i * 4, o.q);
+    }
+}
+
+// ------------------------------------------------------------------ backward as ONE cooperative launch (see k_bn_fwd_coop)
+// (sum dy', sum dy' xhat) per CTA -> barrier -> channel c folded by CTA c -> barrier -> dx of the same rows.
+__global__ void __launch_bounds__(256)
+k_bn_bwd_coop(const float* __restrict__ dy, const float* __restrict__ x, int rows, int C, const float* __restrict__ mean,
+              const float* __restrict__ rstd, int relu, int rows_per_chunk, float* __restrict__ partial,
+              const int* __restrict__ row_node, const float* __restrict__ weight, const float* __restrict__ bias,
+              NodeDropout drop, float* __restrict__ dweight, float* __restrict__ dbias, float* __restrict__ dx,
+              long long n_valid, int training, int* __restrict__ counters) {
+    pdl_enter();
+    __shared__ float sh[4][2][256 + 4];
+    const int nch = (int)gridDim.x;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int r0 = blockIdx.x * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    for (int c0 = 0; c0 < C; c0 += 256) {
+        const int c = c0 + tx * 4;
+        F4 s1, s2;
+        s1.q = s2.q = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < C) {
+            F4 mu, rs, wv, bv;
+            mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+            wv.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+            bv.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int r = r0 + ty; r < r1; r += 8) {
+                F4 g[2], xv[2];
+                bool off_row[2];
+                long long oi[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int rr = min(r + 4 * u, r1 - 1);              // clamped: unconditional loads
+                    xv[u].q = ldg4(x + (long long)rr * C + c);
+                    const int node = row_node ? row_node[rr] : rr;
+                    off_row[u] = r + 4 * u >= r1 || node < 0;
+                    oi[u] = (long long)max(node, 0) * C + c;
+                    g[u].q = ldg4(dy + oi[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const bool off = off_row[u] || (relu && !(bn_affine(xv[u].a[j], mu.a[j], rs.a[j], wv.a[j], bv.a[j]) > 0.f));
+                        const float gg = off ? 0.f : drop_apply(drop, oi[u] + j, g[u].a[j]);
+                        s1.a[j] += gg;
+                        s2.a[j] = fmaf(gg, (xv[u].a[j] - mu.a[j]) * rs.a[j], s2.a[j]);
+                    }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { sh[ty][0][tx * 4 + j] = s1.a[j]; sh[ty][1][tx * 4 + j] = s2.a[j]; }
+        __syncthreads();
+        const int cc = c0 + threadIdx.x;
+        if (cc < C) {
+            float a = 0.f, b = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a += sh[i][0][threadIdx.x]; b += sh[i][1][threadIdx.x]; }
+            partial[(long long)blockIdx.x * 2 * C + cc] = a;
+            partial[(long long)blockIdx.x * 2 * C + C + cc] = b;
+        }
+        __syncthreads();
+    }
+    grid_barrier(counters, nch);
+    for (int c = blockIdx.x; c < C; c += nch) {
+        float a = 0.f, b = 0.f;
+        for (int ch = threadIdx.x; ch < nch; ch += 256) {
+            a += __ldcg(partial + (long long)ch * 2 * C + c);
+            b += __ldcg(partial + (long long)ch * 2 * C + C + c);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            a += __shfl_down_sync(0xffffffffu, a, off);
+            b += __shfl_down_sync(0xffffffffu, b, off);
+        }
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { sh[0][0][threadIdx.x >> 5] = a; sh[0][1][threadIdx.x >> 5] = b; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float sa = 0.f, sb = 0.f;
+            for (int w = 0; w < 8; ++w) { sa += sh[0][0][w]; sb += sh[0][1][w]; }
+            dbias[c] = sa; dweight[c] = sb;
+        }
+    }
+    grid_barrier(counters, 2 * nch);
+    const float inv_n = training ? 1.f / (float)n_valid : 0.f;
+    for (int c0 = 0; c0 < C; c0 += 256) {
+        const int c = c0 + tx * 4;
+        if (c >= C) continue;
+        F4 mu, rs, w, bb, dw, db;
+        mu.q = ldg4(mean + c); rs.q = ldg4(rstd + c);
+        w.q = weight ? ldg4(weight + c) : make_float4(1.f, 1.f, 1.f, 1.f);
+        bb.q = bias ? ldg4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        dw.q = __ldcg(reinterpret_cast<const float4*>(dweight + c)); db.q = __ldcg(reinterpret_cast<const float4*>(dbias + c));
+        for (int r = r0 + ty + 8 * max(0, (r1 - r0 - ty + 7) / 8 - 1); r >= r0 + ty; r -= 8) {     // last rows first (L2)
+            F4 g[2], xv[2];
+            int node[2];
+            long long oi[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int rr = min(r + 4 * u, r1 - 1);
+                xv[u].q = ldg4_stream(x + (long long)rr * C + c);
+                node[u] = row_node ? row_node[rr] : rr;
+                oi[u] = (long long)max(node[u], 0) * C + c;
+                g[u].q = ldg4_stream(dy + oi[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (r + 4 * u >= r1) continue;
+                F4 o;
+                if (node[u] < 0) {
+                    o.q = make_float4(0.f, 0.f, 0.f, 0.f);               // padding rows carry no gradient
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float gg = (relu && !(bn_affine(xv[u].a[j], mu.a[j], rs.a[j], w.a[j], bb.a[j]) > 0.f)) ? 0.f : drop_apply(drop, oi[u] + j, g[u].a[j]);
+                        const float xh = (xv[u].a[j] - mu.a[j]) * rs.a[j];
+                        o.a[j] = w.a[j] * rs.a[j] * (gg - db.a[j] * inv_n - xh * dw.a[j] * inv_n);
+                    }
+                }
+                stg4(dx + (long long)(r + 4 * u) * C + c, o.q);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(counters + 1, 1) == nch - 1) { counters[0] = 0; counters[1] = 0; __threadfence(); }
     }
 }
 
@@ -450,6 +750,21 @@ size_t gnnx_bn_workspace_bytes(int64_t rows, int32_t C) {
     return ((size_t)bn_chunks(rows, C) * 3 * C + 2 * (size_t)C) * sizeof(float);
 }
 
+// co-resident CTAs per SM of the cooperative kernels (0: forward, 1: backward); -1: unavailable or disabled
+static int coop_ctas(int which) {
+    static std::atomic<int> cached[2] = {{0}, {0}};
+    int k = cached[which].load();
+    if (k == 0) {
+        const char* e = getenv("GNNX_BN_COOP");
+        int n = 0;
+        cudaError_t rc = which == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_bn_fwd_coop, 256, 0)
+                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_bn_bwd_coop, 256, 0);
+        if ((e && e[0] == '0') || rc != cudaSuccess || n < 1) { cudaGetLastError(); n = -1; }
+        cached[which].store(n); k = n;
+    }
+    return k;
+}
+
 static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int32_t* row_node, int32_t C, const float* weight,
                        const float* bias, float* running_mean, float* running_var, int32_t training, float momentum, float eps,
                        int32_t relu, float dropout_p, int64_t seed, float* y, float* save_mean, float* save_rstd, void* ws,
@@ -464,6 +779,17 @@ static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int3
         GNNX_REQUIRE(n_valid > 1, "bn_relu_fwd: training-mode batch norm needs more than one row");
         int nch = bn_chunks(rows, C);
         int rpc = ceil_div(rows, nch);
+        // one cooperative launch when every CTA of the grid can be resident (GNNX_BN_COOP=0: the three-kernel path)
+        const int k = coop_ctas(0);
+        if (k > 0 && rows < 0x7fffffff) {
+            int cn = min(nch, num_sms() * min(k, 4));
+            int* ctr = stream_ticket(st);
+            if (ctr) {
+                launch(k_bn_fwd_coop, cn, 256, 0, st, x, (int)rows, C, ceil_div(rows, cn), (float*)ws, row_node, eps, momentum, running_mean,
+                       running_var, save_mean, save_rstd, weight, bias, relu, y, node_dropout(dropout_p, seed), ctr + 8);
+                return check_launch("bn_relu_fwd", 1);
+            }
+        }
         launch(k_bn_stats_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, x, (int)rows, C, rpc, (float*)ws, row_node);
         launch(k_bn_stats_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, eps, momentum, running_mean, running_var, save_mean, save_rstd);
     } else {
@@ -502,6 +828,16 @@ static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t 
     cudaStream_t st = as_stream(stream);
     int nch = bn_chunks(rows, C);
     int rpc = ceil_div(rows, nch);
+    const int k = coop_ctas(1);
+    if (k > 0 && rows < 0x7fffffff) {
+        int cn = min(nch, num_sms() * min(k, 4));
+        int* ctr = stream_ticket(st);
+        if (ctr) {
+            launch(k_bn_bwd_coop, cn, 256, 0, st, dy, x, (int)rows, C, save_mean, save_rstd, relu, ceil_div(rows, cn), (float*)ws, row_node,
+                   weight, bias, drop, dweight, dbias, dx, (long long)n_valid, training, ctr + 8);
+            return check_launch("bn_relu_bwd", 1);
+        }
+    }
     launch(k_bn_bwd_partial, dim3(ceil_div(C, 256), nch), 256, 0, st, dy, x, y, (int)rows, C, save_mean, save_rstd, relu, rpc, (float*)ws, row_node, weight, bias, drop);
     launch(k_bn_bwd_final, ceil_div(C, 8), 256, 0, st, (const float*)ws, nch, C, dweight, dbias);
     launch(k_bn_bwd_apply, flat_grid(rows * (C / 4)), 256, 0, st, dy, x, y, rows, C, weight, save_mean, save_rstd, dweight, dbias, relu, dx, row_node, n_valid, bias, drop, training);

@@ -145,7 +145,12 @@ def test_pna_aggregate_in_degree_one_std_is_zero():
 
 
 # ------------------------------------------------------------------ BatchNorm / pooling / loss / optimizer
-@pytest.mark.parametrize("rows,C,relu", [(800, 64, True), (5000, 256, True), (33, 32, False)])
+# (150000, 256): the cooperative kernels' grid reaches its cap of SMs x co-resident CTAs; (2000, 640): three 256-column
+# slabs, the last one partial; (2, 8): fewer rows than row lanes.  The large case runs without the ReLU: among 38 M
+# outputs some land within rounding of zero, and a sign decided differently by the two implementations moves that entry's
+# gradient by its full value (an oracle property, not a kernel one; the small cases have no such entry).
+@pytest.mark.parametrize("rows,C,relu", [(800, 64, True), (5000, 256, True), (33, 32, False), (150000, 256, False),
+                                         (2000, 640, True), (2, 8, False)])
 def test_batchnorm_relu_fwd_bwd(rows, C, relu):
     x = torch.randn(rows, C) * 3 + 1.5
     bo = O.BatchNorm(C)
@@ -162,8 +167,10 @@ def test_batchnorm_relu_fwd_bwd(rows, C, relu):
     w = torch.randn_like(yo)
     (yo * w).sum().backward(); (yp * w.to(DEV)).sum().backward()
     assert_close(xp.grad, xo.grad, RTOL, ATOL, "bn dx")
-    assert_close(bp.module.weight.grad, bo.module.weight.grad, RTOL, ATOL, "bn dweight")
-    assert_close(bp.module.bias.grad, bo.module.bias.grad, RTOL, ATOL, "bn dbias")
+    # sums of `rows` terms of O(1) with cancellation: both fp32 results carry ~eps * sqrt(rows) * sum|terms|
+    rt = RTOL if rows < 50000 else 1e-4
+    assert_close(bp.module.weight.grad, bo.module.weight.grad, rt, ATOL, "bn dweight")
+    assert_close(bp.module.bias.grad, bo.module.bias.grad, rt, ATOL, "bn dbias")
     assert_close(bp.module.running_mean, bo.module.running_mean, RTOL, ATOL, "running_mean")
     assert_close(bp.module.running_var, bo.module.running_var, RTOL, ATOL, "running_var")
     assert int(bp.module.num_batches_tracked) == 1
