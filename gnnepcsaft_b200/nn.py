@@ -263,13 +263,19 @@ class PNAConv(Module):
         return PNAMeta(g, codes, self.towers, self.F_in, self.F_out, self.pre_layers, self.post_layers,
                        self.aggr_module.avg_deg_log_value(), prep)
 
-    def prepare(self, table: Optional[Tensor], g: GraphIndex):
+    def prepare(self, table: Optional[Tensor], g: GraphIndex, n_groups: Optional[int] = None):
         """The parameter-only part of a call (``pna_fn.PNAPrep``), computed ahead of it -- GNNePCSAFT queues this for
-        all its layers on the side stream.  ``table``: the factored bond-feature table, ``g``: the batch's index."""
+        all its layers on the side stream.  ``table``: the factored bond-feature table, ``g``: the batch's index;
+        ``n_groups``: the batch's degree-group count when the caller already has it (nothing of ``g`` is then touched:
+        the call is pure parameter arithmetic and can be captured into a CUDA graph)."""
         meta = self._meta(g, None)
-        bk = g.degree_buckets() if grouped_ok(meta) else None
+        if n_groups is None:
+            bk = g.degree_buckets() if grouped_ok(meta) else None
+            n_groups = bk.n_groups if bk is not None else 0
+        elif not grouped_ok(meta):
+            n_groups = 0
         with torch.no_grad():
-            return pna_prepare(meta, self._flat_params(), table, bk.n_groups if bk is not None else 0)
+            return pna_prepare(meta, self._flat_params(), table, n_groups)
 
     def bucket_rows(self, g: GraphIndex):
         """The batch's degree buckets when this layer takes the degree-grouped path on ``g`` (else ``None``)."""

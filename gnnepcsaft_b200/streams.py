@@ -3,8 +3,9 @@
 GNNePCSAFT can compute the parameter-only tensors of all its PNAConv layers (fused ``W_lin W_last`` weight, the
 60-row edge-term tables, the per-degree weights: ~5 tiny kernels per layer) before the layer loop.  In eval mode
 the result is cached until a parameter changes (bulk screening), so the stream only matters for the first batch; in
-training ``PREP_AHEAD`` is an opt-in: measured on B200 (cfg2) it takes 0.35 ms off the device-resident step but adds
-0.6 ms to a step that reads its loss back, because ~50 launches are front-loaded while the GPU waits for the host.
+training the work is replayed from ONE CUDA graph (``PREP_GRAPH``).  Measured on B200 (cfg2) with eager side-stream
+launches: 0.2-0.35 ms off the device-resident step, but +0.7 ms on a step that blocks on its loss, because ~50 launches
+are front-loaded while the GPU waits for the host; the graph makes the front-loading one copy and one launch.
 (The backward's weight-space chains were also tried on this stream: no gain -- a persistent GEMM CTA fills the SM's
 register file, so small kernels cannot run underneath it.)  Ordering is by events only: ``begin`` makes the side
 stream wait for everything already queued on the caller's stream, an event from ``mark`` makes the caller's stream
@@ -21,10 +22,11 @@ import torch
 import os
 
 ENABLED = os.environ.get("GNNX_SIDE_STREAM", "1") != "0"
-# Training forward: queue every layer's parameter-only work ahead of the layer loop.  Off by default: the persistent
-# GEMM CTAs fill the register file, so the small kernels mostly wait for gaps anyway, and front-loading ~50 launches
-# delays the first big kernel of a step whenever the host is the one being waited for (per-step loss readback).
-PREP_AHEAD = os.environ.get("GNNX_PREP_AHEAD", "0") == "1"
+# Training forward: queue every layer's parameter-only work ahead of the layer loop (GNNX_PREP_AHEAD=0: inline, per layer).
+PREP_AHEAD = os.environ.get("GNNX_PREP_AHEAD", "1") == "1"
+# ... and replay that work from ONE CUDA graph (GNNePCSAFT._prepare_convs_graph): the front-loading is then a copy and a
+# graph launch, so the blocking variants of the step no longer pay for it.  GNNX_PREP_GRAPH=0: eager side-stream launches.
+PREP_GRAPH = os.environ.get("GNNX_PREP_GRAPH", "1") != "0"
 _SIDES: dict = {}
 
 
