@@ -302,7 +302,8 @@ class GNNePCSAFT(Module):
         if ent["graph"] is None:
             ent["table"].copy_(table)
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=sd.stream):
+            # thread_local: a loader thread allocating pinned memory meanwhile must not invalidate the capture
+            with torch.cuda.graph(graph, stream=sd.stream, capture_error_mode="thread_local"):
                 ent["preps"] = [conv.prepare(ent["table"], g, n_groups=n_groups) for conv in self.convs]
             ent["graph"] = graph
         sd.begin()
