@@ -1,2 +1,3 @@
 #!/bin/bash
-timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_gpu_gatv2_pair.py -m gpu -q -x 2>&1 | tail -6
+for p in 0 1; do echo "GNNX_GATV2_PAIR=$p"; GNNX_GATV2_PAIR=$p timeout 300 python scripts/kernel_trace.py --workload cfg3 --steps 2 2>/dev/null | grep -E "^cfg3|k_gatv2_fwd" | cut -c1-150; done
