@@ -46,6 +46,33 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
 
+// Grid-wide barrier for kernels whose whole grid is resident (the host sizes the grid: SMs x co-resident CTAs): an
+// arrival counter in global memory that thread 0 of each CTA bumps and then polls with acquire loads.  `target` =
+// arrivals expected so far (grid size x barrier ordinal).  A counter that never fills traps after ~2 s of SM clocks
+// instead of hanging the GPU.  Used by the cooperative BatchNorm kernels (norm.cu) and the split fold of the weight-
+// gradient products (gemm_tc.cu); counters come from stream_ticket() and are left at 0 by the last CTA out.
+__device__ __forceinline__ void grid_barrier(int* counter, int target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1);
+        long long t0 = 0;
+        for (unsigned it = 0;; ++it) {
+            int v;
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            if (v >= target) break;
+            __nanosleep(40);
+            if ((it & 4095u) == 4095u) {
+                long long now = clock64();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 4000000000ll) __trap();
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 bool pdl_enabled();
 // Per-kernel device timeline (gnnx_trace_begin / gnnx_trace_end): while a trace is open every launch() is bracketed by
 // two CUDA events on its stream, so the report gives each kernel's in-situ duration (warm caches, real predecessors)

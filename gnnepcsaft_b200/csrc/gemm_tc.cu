@@ -1213,9 +1213,21 @@ k_pna_post_fused(const __grid_constant__ CUtensorMap tmB, const __grid_constant_
 }
 
 // ------------------------------------------------------------------ partial[z][Mo,No] = A[rows_z, Mo]^T * B[rows_z, No]
+// Fold of the row-split partials inside the product's own launch (C != null): after a grid barrier every CTA of a
+// problem sums a slice of the output over the splits, in split order, exactly as k_splitk_reduce does (bit-identical),
+// and applies bias / accumulate / ReLU.  The host enables it only when the whole grid is resident (<= one CTA per SM);
+// counters[0] / [1] are the barrier's arrival and exit counts (stream_ticket() + 16), left at 0.
+struct RedFold {
+    float* C;
+    long long ldc;
+    const float* bias;
+    int flags;
+    int* counters;
+};
+
 __device__ __forceinline__ void red_body(const CUtensorMap* tmA, const CUtensorMap* tmB, const CUtensorMap* tmP,
                                          float* __restrict__ partial, int Mo, int No, int R, int rows_per_split, int BM,
-                                         int BN, const int* __restrict__ split_table, const int split) {
+                                         int BN, const int* __restrict__ split_table, const int split, const RedFold fold) {
     extern __shared__ uint8_t smem_raw[];
     const Smem sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1279,7 +1291,10 @@ __device__ __forceinline__ void red_body(const CUtensorMap* tmA, const CUtensorM
             const int prow = split * Mo;
             for (int h = 0; h < halves; ++h)
                 epilogue_tma(sm, tmem_base + h * 256, q, lane, tmP, prow + m0 + h * 128, prow + Mo, n0, ncols, nullptr, No, 0, it);
-            if (lane == 0) tma_store_wait_all();
+            if (lane == 0) {
+                tma_store_wait_all();
+                if (fold.C) asm volatile("fence.proxy.async;" ::: "memory");     // bulk-store writes before the generic-proxy release below
+            }
         } else if (!split_table) {                 // empty row range: this split contributes zeros (the grouped reduce skips it)
             for (int h = 0; h < halves; ++h)
                 for (int r = q * 32 + lane; r < 128; r += 128) {
@@ -1295,27 +1310,63 @@ __device__ __forceinline__ void red_body(const CUtensorMap* tmA, const CUtensorM
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
     }
+    if (fold.C) {
+        const int nctas = (int)(gridDim.x * gridDim.y * gridDim.z);
+        grid_barrier(fold.counters, nctas);
+        asm volatile("fence.proxy.async;" ::: "memory");
+        const int ci = (int)(blockIdx.x + gridDim.x * blockIdx.y), nci = (int)(gridDim.x * gridDim.y);   // the CTAs of this problem
+        const int splits = (int)gridDim.y;
+        const long long total = (long long)Mo * No, total4 = total >> 2;                                 // Mo, No multiples of 32
+        const float4* p4 = reinterpret_cast<const float4*>(partial);
+        for (long long i = (long long)ci * kThreads + threadIdx.x; i < total4; i += (long long)nci * kThreads) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            int sp = 0;
+            for (; sp + 8 <= splits; sp += 8) {                 // 8 independent loads in flight, summed in split order
+                float4 t[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t[j] = __ldcg(p4 + (long long)(sp + j) * total4 + i);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { v.x += t[j].x; v.y += t[j].y; v.z += t[j].z; v.w += t[j].w; }
+            }
+            for (; sp < splits; ++sp) {
+                const float4 t = __ldcg(p4 + (long long)sp * total4 + i);
+                v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+            }
+            const long long e = i << 2;
+            const int m = (int)(e / No), n = (int)(e % No);
+            float* dst = fold.C + (long long)m * fold.ldc + n;
+            if (fold.bias) { const float4 b = __ldg(reinterpret_cast<const float4*>(fold.bias + n)); v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w; }
+            if (fold.flags & GNNX_GEMM_ACCUMULATE) { const float4 c = *reinterpret_cast<const float4*>(dst); v.x += c.x; v.y += c.y; v.z += c.z; v.w += c.w; }
+            if (fold.flags & GNNX_GEMM_RELU) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            *reinterpret_cast<float4*>(dst) = v;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (atomicAdd(fold.counters + 1, 1) == nctas - 1) { fold.counters[0] = 0; fold.counters[1] = 0; __threadfence(); }
+        }
+    }
 }
 
 
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_red(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmP, float* __restrict__ partial, int Mo, int No, int R,
-                int rows_per_split, int BM, int BN, const int* __restrict__ split_table) {
-    red_body(&tmA, &tmB, &tmP, partial, Mo, No, R, rows_per_split, BM, BN, split_table, (int)blockIdx.y);
+                int rows_per_split, int BM, int BN, const int* __restrict__ split_table, const RedFold fold) {
+    red_body(&tmA, &tmB, &tmP, partial, Mo, No, R, rows_per_split, BM, BN, split_table, (int)blockIdx.y, fold);
 }
 
 // Up to kRedBatch weight gradients of one shape in ONE launch (blockIdx.z = problem): the three post_nn products of a
 // PNAConv layer share the row count, so each gets a third of the CTAs, three times the rows per CTA (the prologue, the
 // un-overlapped 256 KB epilogue and the launch are paid once instead of three times) and a third of the partials.
 constexpr int kRedBatch = 4;
-struct RedBatch { CUtensorMap a[kRedBatch], b[kRedBatch], p[kRedBatch]; };
+struct RedBatch { CUtensorMap a[kRedBatch], b[kRedBatch], p[kRedBatch]; float* c[kRedBatch]; long long ldc[kRedBatch]; int* counters; };
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_tf32_red_batched(const __grid_constant__ RedBatch bt, float* __restrict__ partial, long long partial_stride, int Mo,
                         int No, int R, int rows_per_split, int BM, int BN) {
     const int z = blockIdx.z;
+    const RedFold fold = {bt.counters ? bt.c[z] : nullptr, bt.ldc[z], nullptr, 0, bt.counters};
     red_body(&bt.a[z], &bt.b[z], &bt.p[z], partial + z * partial_stride, Mo, No, R, rows_per_split, BM, BN, nullptr,
-             (int)blockIdx.y);
+             (int)blockIdx.y, fold);
 }
 
 // ------------------------------------------------------------------ host side
@@ -1480,6 +1531,11 @@ int* stream_ticket(cudaStream_t stream) {   // 64 ints per stream: [0] the GEMM 
     auto it = p.slot.find(stream);
     if (it == p.slot.end()) it = p.slot.emplace(stream, p.next++ % kSlots).first;     // > 1024 live streams would share
     return p.base + (size_t)it->second * kStride;
+}
+
+static bool red_fold_enabled() {
+    const char* e = getenv("GNNX_RED_FOLD");        // read per call: tests compare both paths in one process
+    return !(e && e[0] == '0');
 }
 
 bool tc_supported(int64_t M, int64_t N, int64_t K, int ta, int tb, int64_t lda, int64_t ldb, int64_t ldc, const void* A,
@@ -1647,12 +1703,17 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     if (make_map_mnmajor(&mA, A, K, M, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, K, N, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, (const float*)ws, (int64_t)p.splits * M, N, N)) return GNNX_ERR_INVALID;
+    // the ordered fold of the partials runs inside the same launch when the whole grid is resident (one CTA per SM) and
+    // no mask is applied; GNNX_RED_FOLD=0: always the separate k_splitk_reduce launch (same sums, same order)
+    int* ctr = nullptr;
+    if (!mask && red_fold_enabled() && (long long)p.tiles * p.splits <= num_sms()) ctr = stream_ticket(st);
+    const RedFold fold = {ctr ? C : nullptr, (long long)ldc, bias, flags, ctr ? ctr + 16 : nullptr};
     launch(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
-                                                                          p.rows_per_split, p.BM, p.BN, nullptr);
+                                                                          p.rows_per_split, p.BM, p.BN, nullptr, fold);
     count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
-    rc = splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
+    if (!ctr) rc = splitk_reduce_launch((const float*)ws, p.splits, (int)M, (int)N, C, ldc, bias, flags, mask, ldm, st);
     if (rc == GNNX_OK && bits_out) rc = pack_relu_bits_launch(C, ldc, (int)M, (int)N, bits_out, st);
     return rc;
 }
@@ -1678,7 +1739,8 @@ int gemm_tc_red_grouped(const float* A, int64_t lda, const float* B, int64_t ldb
     if (make_map_mnmajor(&mA, A, R, Mo, lda, p.BM / 32)) return GNNX_ERR_INVALID;
     if (make_map_mnmajor(&mB, B, R, No, ldb, p.BN / 32)) return GNNX_ERR_INVALID;
     if (make_map_store(&mC, partial, (int64_t)S * Mo, No, No)) return GNNX_ERR_INVALID;
-    launch(k_gemm_tf32_red, dim3(p.tiles, S), kThreads, kSmemBytes, st, mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table);
+    const RedFold none = {nullptr, 0, nullptr, 0, nullptr};             // folded by k_group_reduce with per-group coefficients
+    launch(k_gemm_tf32_red, dim3(p.tiles, S), kThreads, kSmemBytes, st, mA, mB, mC, partial, (int)Mo, (int)No, (int)R, 0, p.BM, p.BN, split_table, none);
     count_tc_launches(1);
     return check_launch("gemm_tf32_red(grouped)");
 }
@@ -1723,11 +1785,15 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
         if (make_map_store(&bt.p[z], (const float*)ws + z * stride, (int64_t)p.splits * Mo, No, No)) return GNNX_ERR_INVALID;
     }
     for (int z = n; z < kRedBatch; ++z) { bt.a[z] = bt.a[0]; bt.b[z] = bt.b[0]; bt.p[z] = bt.p[0]; }
+    int* ctr = nullptr;
+    if (red_fold_enabled() && (long long)p.tiles * p.splits * n <= num_sms()) ctr = stream_ticket(st);
+    for (int z = 0; z < kRedBatch; ++z) { bt.c[z] = C[z < n ? z : 0]; bt.ldc[z] = ldc[z < n ? z : 0]; }
+    bt.counters = ctr ? ctr + 16 : nullptr;
     launch(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
            (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
     count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red(batched)");
-    for (int z = 0; z < n && rc == GNNX_OK; ++z)
+    for (int z = 0; z < n && rc == GNNX_OK && !ctr; ++z)
         rc = splitk_reduce_launch((const float*)ws + z * stride, p.splits, (int)Mo, (int)No, C[z], ldc[z], nullptr, 0, nullptr, 0, st);
     return rc;
 }

@@ -194,28 +194,6 @@ __global__ void k_bn_apply(const float* __restrict__ x, long long rows, int C, c
 // counter in global memory that thread 0 of each CTA polls with acquire loads; a counter that never fills traps after
 // ~2 s instead of hanging the GPU.  counters[0] counts arrivals (nch per barrier), counters[1] exits; the last CTA out
 // zeroes both for the next launch on the stream.
-__device__ __forceinline__ void grid_barrier(int* counter, int target) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1);
-        long long t0 = 0;
-        for (unsigned it = 0;; ++it) {
-            int v;
-            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-            if (v >= target) break;
-            __nanosleep(40);
-            if ((it & 4095u) == 4095u) {
-                long long now = clock64();
-                if (t0 == 0) t0 = now;
-                else if (now - t0 > 4000000000ll) __trap();
-            }
-        }
-        __threadfence();
-    }
-    __syncthreads();
-}
-
 __global__ void __launch_bounds__(256)
 k_bn_fwd_coop(const float* __restrict__ x, int rows, int C, int rows_per_chunk, float* __restrict__ partial,
               const int* __restrict__ row_node, float eps, float momentum, float* __restrict__ running_mean,
