@@ -72,6 +72,7 @@ def _stale(dll) -> str:
 
 class _Lib:
     def __init__(self):
+        self.graph_replayed = 0          # gnnx kernels re-launched by CUDA-graph replays (see launch_count)
         if not LIB_PATH.exists():
             raise RuntimeError(
                 f"{LIB_PATH} is missing: build it with `python -m gnnepcsaft_b200.build` "
@@ -154,8 +155,10 @@ class _Lib:
         return rows
 
     def launch_count(self) -> int:
-        """Kernels launched by libgnnx so far in this process."""
-        return int(self._dll.gnnx_launch_count())
+        """Kernels launched by libgnnx so far in this process, those replayed from a CUDA graph of gnnx kernels included
+        (``graph_replayed``: the library counts a captured launch once, at capture time; the owner of the graph adds the
+        captured count at every replay)."""
+        return int(self._dll.gnnx_launch_count()) + self.graph_replayed
 
     def tc_launch_count(self) -> int:
         """Of those, tcgen05 tensor-core kernels (k_gemm_tf32_rows2 / k_gemm_tf32_red*)."""

@@ -16,6 +16,7 @@ import torch.nn.functional as F
 from torch import Tensor
 from torch.nn import BatchNorm1d, Dropout, Linear, Module, ModuleList, ReLU, Sequential
 
+from ._lib import lib
 from . import functional as Fn
 from . import nn as gnn
 from . import ops, streams
@@ -289,7 +290,7 @@ class GNNePCSAFT(Module):
             p.data_ptr() for m in (self.convs, self.edge_embed) for p in m.parameters())
         ent = self._prep_graph
         if ent is None or ent["key"] != key:
-            ent = self._prep_graph = dict(key=key, graph=None, table=torch.empty_like(table), preps=None)
+            ent = self._prep_graph = dict(key=key, graph=None, table=torch.empty_like(table), preps=None, launches=0)
             sd.begin()                                  # first step with this key: eager, on the side stream
             try:
                 preps = [conv.prepare(table, g, n_groups=n_groups) for conv in self.convs]
@@ -302,14 +303,17 @@ class GNNePCSAFT(Module):
         if ent["graph"] is None:
             ent["table"].copy_(table)
             graph = torch.cuda.CUDAGraph()
+            n0 = lib().launch_count()
             # thread_local: a loader thread allocating pinned memory meanwhile must not invalidate the capture
             with torch.cuda.graph(graph, stream=sd.stream, capture_error_mode="thread_local"):
                 ent["preps"] = [conv.prepare(ent["table"], g, n_groups=n_groups) for conv in self.convs]
             ent["graph"] = graph
+            ent["launches"] = lib().launch_count() - n0
         sd.begin()
         try:
             ent["table"].copy_(table)
             ent["graph"].replay()
+            lib().graph_replayed += ent["launches"]
             ev = sd.mark()
         finally:
             sd.end()
