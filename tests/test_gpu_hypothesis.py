@@ -102,3 +102,90 @@ def test_fused_multi_aggregator_against_scatter(case, H):
     assert bool((err[away] <= 1e-5 * want_var[away] + 4e-7 * ex2[away] + 1e-12).all())
     empty = torch.bincount(ei[1], minlength=n) == 0
     assert float(agg[empty].abs().sum()) == 0.0           # empty rows: 0 for all four
+
+
+# ------------------------------------------------------------------ kernels with grid barriers / cross-item dependencies
+FEW = dict(max_examples=15, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+
+
+@settings(**FEW)
+@given(st.integers(8, 4000), st.integers(1, 80), st.booleans(), st.integers(0, 2 ** 31 - 1))
+def test_cooperative_batchnorm_against_fp64(rows, c4, relu, seed):
+    """k_bn_fwd_coop / k_bn_bwd_coop on arbitrary row counts (grids from 1 CTA to the residency cap) and channel counts
+    (partial and multiple 256-column slabs): outputs, input gradient and parameter gradients against an fp64 evaluation
+    of the same formulas, with the ReLU mask taken from the kernel's own output sign."""
+    from gnnepcsaft_b200 import nn as gnn
+    C = 4 * c4
+    gen = torch.Generator().manual_seed(seed)
+    x = (torch.randn(rows, C, generator=gen) * 2 + 0.5).to(DEV).requires_grad_(True)
+    bn = gnn.BatchNorm(C).to(DEV).train()
+    with torch.no_grad():
+        bn.module.weight.uniform_(0.5, 1.5); bn.module.bias.normal_()
+    y = bn(x, relu=relu)
+    w = torch.randn(rows, C, generator=gen).to(DEV)
+    (y * w).sum().backward()
+    xd, wd, bd = x.detach().double(), bn.module.weight.detach().double(), bn.module.bias.detach().double()
+    mu, var = xd.mean(0), xd.var(0, unbiased=False)
+    xh = (xd - mu) / torch.sqrt(var + bn.module.eps)
+    pre = xh * wd + bd
+    keep = (y.detach() > 0).double() if relu else torch.ones_like(pre)
+    want = pre * keep
+    scale = float(want.abs().max()) + 1e-6
+    assert float((y.detach().double() - want).abs().max()) <= 5e-5 * scale + 1e-5
+    g = w.double() * keep
+    db, dw = g.sum(0), (g * xh).sum(0)
+    dx = (wd / torch.sqrt(var + bn.module.eps)) * (g - db / rows - xh * dw / rows)
+    tol = 1e-4 * (float(dx.abs().max()) + 1e-6) + 1e-5
+    assert float((x.grad.double() - dx).abs().max()) <= tol
+    assert float((bn.module.bias.grad.double() - db).abs().max()) <= 1e-4 * (float(g.abs().sum(0).max()) + 1e-6)
+    assert float((bn.module.weight.grad.double() - dw).abs().max()) <= 1e-4 * (float((g * xh).abs().sum(0).max()) + 1e-6)
+
+
+@settings(**FEW)
+@given(st.integers(768, 9000), st.sampled_from([32, 64, 96, 128, 256]), st.integers(2, 4), st.integers(0, 2 ** 31 - 1))
+def test_linear_chain_equals_layer_by_layer(M, W, n, seed):
+    ops.set_matmul_precision("tf32")
+    ops.FORCE_TC = True
+    try:
+        gen = torch.Generator().manual_seed(seed)
+        x = torch.randn(M, W, generator=gen).to(DEV)
+        layers = [((torch.randn(W, W, generator=gen) / W ** 0.5).to(DEV), (torch.randn(W, generator=gen) * 0.1).to(DEV), p < n - 1, p < n - 1)
+                  for p in range(n)]
+        outs, bits = ops.gemm_chain(x, layers)
+        a = x
+        for p, (w, b, relu, want) in enumerate(layers):
+            if want:
+                ref, rbits = ops.gemm(a, w, trans_b=True, bias=b, relu=relu, want_relu_bits=True)
+                assert torch.equal(bits[p], rbits)
+            else:
+                ref = ops.gemm(a, w, trans_b=True, bias=b, relu=relu)
+            assert torch.equal(outs[p], ref), f"layer {p} of {n}, M={M}, W={W}"
+            a = ref
+    finally:
+        ops.FORCE_TC = False
+        ops.set_matmul_precision("fp32")
+
+
+@settings(**FEW)
+@given(st.integers(300, 60000), st.integers(1, 16), st.integers(1, 12), st.integers(0, 2 ** 31 - 1))
+def test_weight_gradient_fold_equals_separate_reduce(R, mo32, no32, seed):
+    import os
+    ops.set_matmul_precision("tf32")
+    ops.FORCE_TC = True
+    was = os.environ.get("GNNX_RED_FOLD")
+    try:
+        gen = torch.Generator().manual_seed(seed)
+        a = torch.randn(R, 32 * mo32, generator=gen).to(DEV)
+        b = torch.randn(R, 32 * no32, generator=gen).to(DEV)
+        got = []
+        for fold in ("0", "1"):
+            os.environ["GNNX_RED_FOLD"] = fold
+            got.append(ops.gemm(a, b, trans_a=True))
+        assert torch.equal(*got), f"R={R}, Mo={32 * mo32}, No={32 * no32}"
+    finally:
+        ops.FORCE_TC = False
+        ops.set_matmul_precision("fp32")
+        if was is None:
+            os.environ.pop("GNNX_RED_FOLD", None)
+        else:
+            os.environ["GNNX_RED_FOLD"] = was
