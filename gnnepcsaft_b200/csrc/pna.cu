@@ -4,6 +4,8 @@
 // deterministic and atomic-free: one warp owns one (destination row, 128-column chunk), walks the
 // row's edges in edge order with float4 loads (several rows in flight), and writes each output once.
 #include <stdlib.h>
+#include <algorithm>
+#include <atomic>
 
 #include "common.cuh"
 
@@ -95,6 +97,99 @@ k_pna_gather_fwd(const float* __restrict__ pq, long long ld_pq, const float* __r
                 }
             }
         }
+    }
+}
+
+// ------------------------------------------------------------------ the same gather with the neighbour rows STAGED through
+// shared memory by the bulk-copy engine (opt-in GNNX_GATHER_BULK=1; hidden 256 only: one Q[src] row = 1 KB).
+// One warp per destination; lane 0 issues one cp.async.bulk per edge (up to kBulkRows per destination; longer rows
+// fall back to direct loads for the rest) into the warp's stage and arms its mbarrier with the byte count, the copies
+// of the NEXT destination are issued before this one is consumed (two stages per warp).  P[dst] and the 60-row
+// edge-term table are read directly (one row per destination / L1-resident).  Same arithmetic, bit-identical output.
+constexpr int kBulkRows = 4;
+constexpr int kBulkStage = kBulkRows * 1024;                     // bytes
+constexpr int kBulkSmem = 8 * 2 * kBulkStage + 8 * 2 * 8;        // 8 warps x 2 stages + 2 mbarriers per warp
+
+__device__ __forceinline__ uint32_t sm_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+template <typename RIdx>
+__global__ void __launch_bounds__(256)
+k_pna_gather_fwd_bulk(const float* __restrict__ pq, long long ld_pq, const float* __restrict__ r, long long ld_r,
+                      const RIdx* __restrict__ ridx, const int* __restrict__ rowptr, const int* __restrict__ csr_src,
+                      int N, int relu, float* __restrict__ h, uint32_t* __restrict__ bits) {
+    constexpr int H = 256;
+    extern __shared__ __align__(128) uint8_t bulk_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* my = bulk_smem + warp * 2 * kBulkStage;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(bulk_smem + 8 * 2 * kBulkStage) + warp * 2;
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(sm_u32(bars)) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(sm_u32(bars + 1)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    pdl_enter();
+    const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
+    const int c = lane * 4;
+    auto issue = [&](int node, int s) {                         // lane 0 only
+        const int b = rowptr[node], e = rowptr[node + 1];
+        const int cnt = min(e - b, kBulkRows);
+        if (cnt <= 0) return;
+        const uint32_t bar = sm_u32(bars + s);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(cnt * 1024) : "memory");
+        for (int j = 0; j < cnt; ++j) {
+            const float* src = pq + (long long)csr_src[b + j] * ld_pq + H;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             sm_u32(my + s * kBulkStage + j * 1024)),
+                         "l"(src), "r"(1024), "r"(bar)
+                         : "memory");
+        }
+    };
+    uint32_t phase[2] = {0u, 0u};
+    int s = 0;
+    int i = gw;
+    if (i < N && lane == 0) issue(i, 0);
+    for (; i < N; i += nw, s ^= 1) {
+        if (i + nw < N && lane == 0) issue(i + nw, s ^ 1);
+        const int b = rowptr[i], e = rowptr[i + 1];
+        if (b == e) continue;
+        F4 p[2];
+        p[0] = f4_ld(pq + (long long)i * ld_pq + c);
+        p[1] = f4_ld(pq + (long long)i * ld_pq + 128 + c);
+        const uint32_t bar = sm_u32(bars + s);
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(done) : "r"(bar), "r"(phase[s]) : "memory");
+        phase[s] ^= 1u;
+        for (int k = b; k < e; ++k) {
+            const long long rr = (long long)ridx[k];
+            F4 q[2], t[2];
+            if (k - b < kBulkRows) {
+                const float* st = reinterpret_cast<const float*>(my + s * kBulkStage + (k - b) * 1024);
+                q[0].q = *reinterpret_cast<const float4*>(st + c);
+                q[1].q = *reinterpret_cast<const float4*>(st + 128 + c);
+            } else {
+                const float* src = pq + (long long)csr_src[k] * ld_pq + H;
+                q[0] = f4_ld(src + c); q[1] = f4_ld(src + 128 + c);
+            }
+            t[0] = f4_ld(r + rr * ld_r + c); t[1] = f4_ld(r + rr * ld_r + 128 + c);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                F4 o;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    o.a[j] = p[v].a[j] + q[v].a[j] + t[v].a[j];
+                    if (relu) o.a[j] = fmaxf(o.a[j], 0.f);
+                }
+                stg4(h + (long long)k * H + c + 128 * v, o.q);
+                if (bits) {
+                    const uint32_t w = pack_relu_word(o, true, lane);
+                    if ((lane & 7) == 0) bits[(long long)k * (H / 32) + ((c + 128 * v) >> 5)] = w;
+                }
+            }
+        }
+        __syncwarp();                                           // every lane is done with stage s before it is refilled
     }
 }
 
@@ -519,6 +614,21 @@ int gnnx_pna_gather_fwd(const float* pq, int64_t ld_pq, const float* r, int64_t 
     if (wide < 0) { const char* e = getenv("GNNX_GATHER8"); wide = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1; }
     // 8 columns per lane pay in the backward (96.5 -> 79.5 us) but not here: three operand rows per edge at V = 2 need 64
     // registers, the lost occupancy eats the gain (94.5 us against 92.7).  GNNX_GATHER8=2 selects it all the same.
+    {   // opt-in: neighbour rows staged through shared memory by cp.async.bulk (measured)
+        const char* be = getenv("GNNX_GATHER_BULK");
+        if (be && be[0] == '1' && H == 256 && ((uintptr_t)pq & 15) == 0) {
+            static std::atomic<int> attr{0};
+            if (!attr.load()) {
+                GNNX_CUDA(cudaFuncSetAttribute(k_pna_gather_fwd_bulk<int>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkSmem));
+                GNNX_CUDA(cudaFuncSetAttribute(k_pna_gather_fwd_bulk<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkSmem));
+                attr.store(1);
+            }
+            int g = (int)std::min<long long>((N + 7) / 8, (long long)num_sms() * 3);
+            if (ridx_i32) launch(k_pna_gather_fwd_bulk<int>, g, 256, kBulkSmem, as_stream(stream), pq, ld_pq, r, ld_r, ridx_i32, rowptr, csr_src, (int)N, relu, h, relu_bits_out);
+            else launch(k_pna_gather_fwd_bulk<uint8_t>, g, 256, kBulkSmem, as_stream(stream), pq, ld_pq, r, ld_r, ridx_u8, rowptr, csr_src, (int)N, relu, h, relu_bits_out);
+            return check_launch("pna_gather_fwd(bulk)");
+        }
+    }
     const int V = (wide == 2 && H > 128) ? 2 : 1;
     const int chunks = (H + 128 * V - 1) / (128 * V);
     int grid = warp_grid((long long)N * chunks);
