@@ -276,3 +276,20 @@ def test_gather_fwd_bulk_staged_variant_is_bit_identical(relu, table):
         assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1])
     else:
         assert torch.equal(out[0], out[1])
+
+
+@pytest.mark.parametrize("rows,H,ncodes", [(207726, 256, 60), (5000, 128, 60), (777, 64, 12), (40000, 384, 60), (3, 256, 60), (0, 256, 60)])
+def test_code_segment_sum_against_index_add(rows, H, ncodes):
+    """dtable[code] = sum of the rows with that code (the edge-term table's gradient): float4 kernel (H % 128 == 0) and
+    scalar kernel against an fp64 index_add; deterministic."""
+    gen = torch.Generator().manual_seed(rows + H)
+    dh = torch.randn(rows, H, generator=gen).to(DEV)
+    codes = torch.randint(0, ncodes, (rows,), generator=gen).to(torch.uint8)
+    if rows > 100:
+        codes[: rows // 2] = 3                                # one dominant code, as single bonds are
+    codes = codes.to(DEV)
+    got = ops.code_segment_sum(dh, codes, ncodes)
+    want = torch.zeros(ncodes, H, dtype=torch.float64, device=DEV).index_add_(0, codes.long(), dh.double())
+    mag = torch.zeros(ncodes, H, dtype=torch.float64, device=DEV).index_add_(0, codes.long(), dh.double().abs())
+    assert bool(((got.double() - want).abs() <= 2e-6 * mag + 1e-6).all())
+    assert torch.equal(got, ops.code_segment_sum(dh, codes, ncodes))
