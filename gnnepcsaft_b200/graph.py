@@ -200,15 +200,9 @@ class DeviceGraphStore:
     """A whole dataset kept packed in HBM (uint8 features, int16 local endpoints) -- SURVEY §8(f) rank 2."""
 
     def __init__(self, packed, device):
-        # the packed store is validated ONCE on the host, so batches collated from it need no device-side check
-        n_of_edge = np.repeat(np.diff(packed.node_ptr).astype(np.int32), np.diff(packed.edge_ptr))
-        if packed.src.size and (packed.src.min() < 0 or packed.dst.min() < 0 or (packed.src >= n_of_edge).any()
-                                or (packed.dst >= n_of_edge).any()):
-            raise IndexError("packed store: an edge endpoint lies outside its molecule's node range")
-        if packed.x.size and (packed.x >= np.asarray(ATOM_FEATURE_DIMS, packed.x.dtype)).any():
-            raise IndexError("packed store: an atom feature id is outside its OGB vocabulary")
-        if packed.edge_attr.size and (packed.edge_attr >= np.asarray(BOND_FEATURE_DIMS, packed.edge_attr.dtype)).any():
-            raise IndexError("packed store: a bond feature id is outside its OGB vocabulary")
+        # Upload first, then validate ONCE on the device (batches collated from the store need no check of their own): for
+        # a 1.25 M-molecule screening shard the same checks in numpy (an [E] repeat, three [E] / [N, 9] comparisons, an
+        # [N]-bin bincount for the largest in-degree) took 2.3 s of host time against 0.3 s for the upload itself.
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)
         self.x, self.src, self.dst, self.edge_attr = t(packed.x), t(packed.src), t(packed.dst), t(packed.edge_attr)
         self.node_ptr, self.edge_ptr = t(packed.node_ptr), t(packed.edge_ptr)
@@ -216,10 +210,48 @@ class DeviceGraphStore:
         self.node_ptr_host, self.edge_ptr_host = packed.node_ptr, packed.edge_ptr   # numpy, for sizing on the host
         self.num_graphs = packed.num_graphs
         self.device = device
-        # largest in-degree of the dataset, known on the host: every batch buckets its nodes into the same degree classes
-        deg = np.bincount(np.repeat(packed.node_ptr[:-1], np.diff(packed.edge_ptr)) + packed.dst.astype(np.int64),
-                          minlength=int(packed.node_ptr[-1])) if packed.dst.size else np.zeros(1, np.int64)
-        self.max_degree = int(deg.max()) if deg.size else 0
+        bad_edge, bad_atom, bad_bond, max_deg = self._validate_on_device()
+        if bad_edge:
+            raise IndexError("packed store: an edge endpoint lies outside its molecule's node range")
+        if bad_atom:
+            raise IndexError("packed store: an atom feature id is outside its OGB vocabulary")
+        if bad_bond:
+            raise IndexError("packed store: a bond feature id is outside its OGB vocabulary")
+        # largest in-degree of the dataset: every batch buckets its nodes into the same degree classes
+        self.max_degree = max_deg
+
+    def _validate_on_device(self, edges_per_chunk: int = 1 << 24):
+        """Endpoint / vocabulary range checks and the largest in-degree, molecule chunks of <= ``edges_per_chunk`` edges at
+        a time (bounded temporaries), ONE host read at the end -> (bad_edge, bad_atom, bad_bond, max_degree)."""
+        dev = self.device
+        flags = torch.zeros(4, dtype=torch.int64, device=dev)          # bad edge / atom / bond counts, max in-degree
+        if self.x.numel():
+            lim = torch.tensor(ATOM_FEATURE_DIMS, dtype=self.x.dtype, device=dev)
+            flags[1] = (self.x >= lim).any().to(torch.int64)
+        if self.edge_attr.numel():
+            lim = torch.tensor(BOND_FEATURE_DIMS, dtype=self.edge_attr.dtype, device=dev)
+            flags[2] = (self.edge_attr >= lim).any().to(torch.int64)
+        ep, G = self.edge_ptr_host, self.num_graphs
+        g0 = 0
+        while g0 < G and self.src.numel():
+            g1 = int(np.searchsorted(ep, ep[g0] + edges_per_chunk, side="right")) - 1      # last molecule that still fits
+            g1 = min(G, max(g1, g0 + 1))
+            e0, e1 = int(ep[g0]), int(ep[g1])
+            n0, n1 = int(self.node_ptr_host[g0]), int(self.node_ptr_host[g1])
+            if e1 > e0:
+                ne = self.edge_ptr[g0 + 1:g1 + 1] - self.edge_ptr[g0:g1]
+                nn = (self.node_ptr[g0 + 1:g1 + 1] - self.node_ptr[g0:g1]).to(torch.int32)
+                n_of_edge = torch.repeat_interleave(nn, ne, output_size=e1 - e0)
+                src, dst = self.src[e0:e1].to(torch.int32), self.dst[e0:e1].to(torch.int32)
+                bad = (src < 0) | (dst < 0) | (src >= n_of_edge) | (dst >= n_of_edge)
+                flags[0] += bad.any().to(torch.int64)
+                off = torch.repeat_interleave((self.node_ptr[g0:g1] - n0).to(torch.int32), ne, output_size=e1 - e0)
+                tgt = (off + dst).clamp_(0, max(n1 - n0 - 1, 0)).to(torch.int64)             # clamped: a bad endpoint is reported above
+                deg = torch.bincount(tgt, minlength=max(n1 - n0, 1))
+                flags[3] = torch.maximum(flags[3], deg.max())
+            g0 = g1
+        f = flags.tolist()
+        return bool(f[0]), bool(f[1]), bool(f[2]), int(f[3])
 
     def collate(self, graph_ids: np.ndarray) -> Batch:
         """Block-diagonal batch of the selected molecules, built entirely on the device."""

@@ -254,3 +254,24 @@ def test_reference_file_to_device_batches(tmp_path):
         assert torch.equal(b.batch.cpu().long(), ref.batch) and torch.equal(b.para.cpu(), ref.para)
         seen += ids
     assert sorted(seen) == list(range(70)) and len(loader) == 5
+
+
+def test_packed_store_is_validated_on_the_device_and_reports_what_numpy_would():
+    """DeviceGraphStore uploads, then checks on the device in molecule chunks: a bad endpoint / atom id / bond id raises
+    the IndexError the host-side check used to raise, and the largest in-degree equals the numpy bincount -- also when
+    the chunk size forces many chunks."""
+    import copy
+    from gnnepcsaft_b200 import synth
+    packed = synth.pack(synth.make_graphs(300, 11, 5, 40, 0.0))
+    store = graph.DeviceGraphStore(packed, torch.device(DEV))
+    deg = np.bincount(np.repeat(packed.node_ptr[:-1], np.diff(packed.edge_ptr)) + packed.dst.astype(np.int64),
+                      minlength=int(packed.node_ptr[-1]))
+    assert store.max_degree == int(deg.max())
+    assert store._validate_on_device(edges_per_chunk=97) == (False, False, False, int(deg.max()))
+    for field, value, what in (("dst", 999, "edge endpoint"), ("src", -1, "edge endpoint"), ("x", 200, "atom feature"),
+                               ("edge_attr", 77, "bond feature")):
+        bad = copy.deepcopy(packed)
+        arr = getattr(bad, field)
+        arr.reshape(-1)[arr.size // 2] = value
+        with pytest.raises(IndexError, match=what):
+            graph.DeviceGraphStore(bad, torch.device(DEV))
