@@ -317,6 +317,102 @@ __global__ void k_sum_partials(const float* __restrict__ partial, int nchunks, l
         out[i] = s;
     }
 }
+// ------------------------------------------------------------------ the same sum over slots ORDERED BY CODE
+// `order` lists the slots sorted by code (stable), code_ptr[k] = first position of code k.  The per-batch ordering is
+// built once (ops.code_order) and shared by every layer.  Chunks of kCsRowsPerChunk consecutive positions never cross a
+// code boundary (chunk_ptr[k] = first chunk of code k), so a warp sums the rows of ONE code into registers -- a plain
+// gathered row sum with 512-byte loads, no shared-memory tables -- and writes one partial row; a second small kernel
+// adds each code's partial rows in chunk order.  Deterministic: fixed row order inside a chunk, fixed chunk order.
+constexpr int kCsRowsPerChunk = 256;
+__global__ void __launch_bounds__(256)
+k_code_sum_sorted(const float* __restrict__ dh, const int* __restrict__ order, const int* __restrict__ code_ptr,
+                  const int* __restrict__ chunk_ptr, int ncodes, int H, int max_chunks, float* __restrict__ partial) {
+    pdl_enter();
+    // block = (chunk, 128-column slab); warp y sums rows y * 32 .. + 31 of the chunk (8 loads in flight, row order), the
+    // eight warp sums are added in warp order.  One warp walking all 256 rows took 32 dependent round trips.
+    __shared__ float4 sh[8][32];
+    const int lane = threadIdx.x & 31, y = threadIdx.x >> 5;
+    const int slabs = (H + 127) / 128;
+    const int c = blockIdx.x / slabs;
+    const int col = (blockIdx.x % slabs) * 128 + lane * 4;
+    if (c >= __ldg(chunk_ptr + ncodes)) return;                   // chunks in use (<= max_chunks, the launch bound); block-uniform
+    (void)max_chunks;
+    int lo = 0, hi = ncodes;                                      // largest k with chunk_ptr[k] <= c
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(chunk_ptr + mid) <= c) lo = mid; else hi = mid;
+    }
+    const int cbeg = __ldg(code_ptr + lo) + (c - __ldg(chunk_ptr + lo)) * kCsRowsPerChunk;
+    const int cend = min(cbeg + kCsRowsPerChunk, __ldg(code_ptr + lo + 1));
+    const int begin = cbeg + y * (kCsRowsPerChunk / 8), end = min(begin + kCsRowsPerChunk / 8, cend);
+    F4 acc = f4_zero();
+    if (col < H) {
+        for (int p = begin; p < end; p += 8) {
+            F4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int row = __ldg(order + min(p + u, end - 1));             // clamped: loads stay unconditional
+                v[u] = f4_lds(dh + (long long)row * H + col);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (p + u < end) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc.a[j] += v[u].a[j];
+                }
+        }
+    }
+    sh[y][lane] = acc.q;
+    __syncthreads();
+    if (y == 0 && col < H) {
+        F4 s = f4_zero();
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            F4 t; t.q = sh[w][lane];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s.a[j] += t.a[j];
+        }
+        stg4(partial + (long long)c * H + col, s.q);
+    }
+}
+
+// dtable[code] = sum of the code's partial rows in chunk order: block = (code, 128-column slab), warp y takes chunks
+// y, y + 8, ... of the code, the eight warp sums are added in warp order.
+__global__ void __launch_bounds__(256)
+k_code_sum_fold(const float* __restrict__ partial, const int* __restrict__ chunk_ptr, int ncodes, int H, float* __restrict__ dtable) {
+    pdl_enter();
+    __shared__ float4 sh[8][32];
+    const int lane = threadIdx.x & 31, y = threadIdx.x >> 5;
+    const int code = blockIdx.y, col = blockIdx.x * 128 + lane * 4;
+    const int c0 = __ldg(chunk_ptr + code), c1 = __ldg(chunk_ptr + code + 1);
+    F4 acc = f4_zero();
+    if (col < H) {
+        for (int c = c0 + y; c < c1; c += 64) {
+            F4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = f4_ld(partial + (long long)min(c + 8 * u, c1 - 1) * H + col);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (c + 8 * u < c1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc.a[j] += v[u].a[j];
+                }
+        }
+    }
+    sh[y][lane] = acc.q;
+    __syncthreads();
+    if (y == 0 && col < H) {
+        F4 s = f4_zero();
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            F4 t; t.q = sh[w][lane];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s.a[j] += t.a[j];
+        }
+        stg4(dtable + (long long)code * H + col, s.q);
+    }
+}
+
 static int code_chunks(int64_t rows, int32_t H) {
     int slabs = ceil_div(H, 32);
     int target = max(1, (num_sms() * 3) / slabs);
@@ -681,6 +777,24 @@ int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, i
     launch(k_code_sum_partial, dim3(ceil_div(H, 32), nch), dim3(32, kCodeRows), smem, st, dh, codes, (int)rows, ncodes, H, rpc, (float*)ws);
     launch(k_sum_partials, flat_grid(count), 256, 0, st, (const float*)ws, nch, count, dtable);
     return check_launch("code_segment_sum", 2);
+}
+
+size_t gnnx_code_segment_sum_sorted_workspace_bytes(int64_t rows, int32_t num_codes, int32_t H) {
+    return (size_t)(rows / kCsRowsPerChunk + num_codes + 1) * H * sizeof(float);
+}
+
+int gnnx_code_segment_sum_sorted(const float* dh, const int32_t* order, const int32_t* code_ptr, const int32_t* chunk_ptr,
+                                 int64_t rows, int32_t ncodes, int32_t H, float* dtable, void* ws, size_t ws_bytes, void* stream) {
+    GNNX_REQUIRE(ncodes >= 1 && ncodes <= 65535, "code_segment_sum_sorted: num_codes must be in [1, 65535]");
+    GNNX_REQUIRE(H % 4 == 0 && ((uintptr_t)dh & 15) == 0, "code_segment_sum_sorted: hidden must be a multiple of 4 and dh 16-byte aligned");
+    GNNX_REQUIRE(ws_bytes >= gnnx_code_segment_sum_sorted_workspace_bytes(rows, ncodes, H), "code_segment_sum_sorted: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(dtable, 0, (size_t)ncodes * H * sizeof(float), st)); return GNNX_OK; }
+    const int max_chunks = (int)(rows / kCsRowsPerChunk + ncodes);          // sum_k ceil(n_k / R) <= rows / R + ncodes
+    const int slabs = ceil_div(H, 128);
+    launch(k_code_sum_sorted, max_chunks * slabs, 256, 0, st, dh, order, code_ptr, chunk_ptr, ncodes, H, max_chunks, (float*)ws);
+    launch(k_code_sum_fold, dim3(slabs, ncodes), 256, 0, st, (const float*)ws, chunk_ptr, ncodes, H, dtable);
+    return check_launch("code_segment_sum_sorted", 2);
 }
 
 int gnnx_pna_aggregate_fwd(const float* m, const int32_t* rowptr, int64_t N, int32_t T, int32_t F, float* agg, void* stream) {

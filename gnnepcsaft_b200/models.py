@@ -212,6 +212,8 @@ class GNNePCSAFT(Module):
         ea_u8 = b.edge_attr if b.edge_attr.dtype == torch.uint8 else ops.narrow_u8(
             b.edge_attr, gnn.BOND_FEATURE_DIMS, st[ops.ST_BOND:ops.ST_BOND + 1])
         edges = self.edge_embed.forward_table(ops.edge_codes(ea_u8.contiguous(), g.csr_eid, st[ops.ST_BOND:ops.ST_BOND + 1]))
+        if self.training and torch.is_grad_enabled():
+            ops.code_order_ahead(edges.codes, edges.table.shape[0])     # the backward's slot ordering, under the forward
         preps = self._prepare_convs(edges, g)
         # Dropout(p) in front of every conv (reference models.py:209) is fused into the kernel that PRODUCES that conv's
         # input: the embedding sum for layer 0, the BatchNorm+ReLU apply of layer l-1 for layer l.  No mask tensor: the

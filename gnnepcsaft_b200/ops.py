@@ -358,10 +358,63 @@ def pna_gather_bwd(dh: Tensor, g, want_dr_edge: bool):
     return dpq, dr
 
 
+CODE_SORTED_MIN_ROWS = 8192      # below this the table kernel's single pass is as fast and needs no ordering
+_code_order_cache: dict = {}
+
+
+def code_order(codes: Tensor, num_codes: int):
+    """Slots ordered by code, built ONCE per batch and shared by every layer's ``code_segment_sum``: ``(order, code_ptr,
+    chunk_ptr)`` = slot ids sorted by code (stable radix sort on the uint8 keys), first position of each code, and the
+    exclusive prefix sum of ceil(count / 256) (the 256-row chunks of ``gnnx_code_segment_sum_sorted`` never straddle
+    two codes).  Cached on the codes tensor's storage and version (one entry: a step has one edge-code tensor)."""
+    key = (codes.data_ptr(), codes.numel(), codes._version, num_codes, codes.device)
+    ent = _code_order_cache.get("last")
+    if ent is not None and ent[0] == key:
+        if ent[3] is not None:                               # built ahead on the side stream (code_order_ahead)
+            torch.cuda.current_stream().wait_event(ent[3])
+        return ent[1]
+    srt = torch.sort(codes, stable=True)                     # no host sync anywhere below: the call is graph-capturable
+    order = srt.indices.to(torch.int32)
+    ks = torch.arange(num_codes + 1, dtype=torch.int32, device=codes.device)
+    code_ptr = torch.searchsorted(srt.values.to(torch.int32), ks).to(torch.int32)        # first position with code >= k
+    cnt = code_ptr[1:] - code_ptr[:-1]
+    chunk_ptr = torch.cat([code_ptr[:1] * 0, torch.cumsum((cnt + 255) // 256, 0).to(torch.int32)])
+    res = (order, code_ptr, chunk_ptr)
+    _code_order_cache["last"] = (key, res, codes, None)     # keeps `codes` alive so that the address cannot be reused
+    return res
+
+
+def code_order_ahead(codes: Tensor, num_codes: int) -> None:
+    """Build the batch's code ordering NOW, on the side stream: only the backward needs it (the gradient of the edge-term
+    tables), so its ~8 small kernels run under the forward instead of in front of the first backward layer.  No-op for
+    batches below ``CODE_SORTED_MIN_ROWS`` and while a CUDA graph is being captured (the backward then builds it inline)."""
+    from . import streams
+    if codes.numel() < CODE_SORTED_MIN_ROWS or torch.cuda.is_current_stream_capturing():
+        return
+    sd = streams.side(codes.device)
+    if sd is None:
+        code_order(codes, num_codes)
+        return
+    sd.begin()
+    try:
+        code_order(codes, num_codes)
+        ev = sd.mark()
+    finally:
+        sd.end()
+    key, res, keep, _ = _code_order_cache["last"]
+    _code_order_cache["last"] = (key, res, keep, ev)
+
+
 def code_segment_sum(dh: Tensor, codes: Tensor, num_codes: int) -> Tensor:
     _chk(dh, torch.float32, "dh"); _chk(codes, torch.uint8, "codes")
     rows, H = dh.shape
     out = torch.empty((num_codes, H), dtype=torch.float32, device=dh.device)
+    if rows >= CODE_SORTED_MIN_ROWS and H % 4 == 0 and dh.is_contiguous():
+        order, code_ptr, chunk_ptr = code_order(codes, num_codes)
+        ws, nb = _ws(_query("gnnx_code_segment_sum_sorted_workspace_bytes", rows, num_codes, H), dh.device)
+        lib().call("gnnx_code_segment_sum_sorted", dh.data_ptr(), order.data_ptr(), code_ptr.data_ptr(), chunk_ptr.data_ptr(),
+                   rows, num_codes, H, out.data_ptr(), _p(ws), nb, _stream())
+        return out
     ws, nb = _ws(_query("gnnx_code_segment_sum_workspace_bytes", rows, num_codes, H), dh.device)
     lib().call("gnnx_code_segment_sum", dh.data_ptr(), codes.data_ptr(), rows, num_codes, H, out.data_ptr(), _p(ws), nb, _stream())
     return out

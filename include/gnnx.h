@@ -237,6 +237,14 @@ GNNX_API size_t gnnx_code_segment_sum_workspace_bytes(int64_t rows, int32_t num_
 GNNX_API int gnnx_code_segment_sum(const float* dh, const uint8_t* codes, int64_t rows, int32_t num_codes,
                           int32_t hidden, float* dtable, void* workspace, size_t workspace_bytes,
                           void* stream);
+/* The same sum with the slots ORDERED BY CODE once per batch: order[rows] = slot ids sorted by code (stable),
+ * code_ptr[num_codes + 1] = first position of each code, chunk_ptr[num_codes + 1] = exclusive prefix sum of
+ * ceil(count_k / 256).  A gathered row sum without shared-memory tables (the ordering is shared by all layers of a
+ * step); deterministic.  Replaces the same reference lines as gnnx_code_segment_sum. */
+GNNX_API size_t gnnx_code_segment_sum_sorted_workspace_bytes(int64_t rows, int32_t num_codes, int32_t hidden);
+GNNX_API int gnnx_code_segment_sum_sorted(const float* dh, const int32_t* order, const int32_t* code_ptr,
+                          const int32_t* chunk_ptr, int64_t rows, int32_t num_codes, int32_t hidden, float* dtable,
+                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Replaces DegreeScalerAggregation(MultiAggregation[mean,min,max,std]) (models.py:443-449):
  * one pass over the dst-sorted messages m [E, T*F]; agg is [N, T, 4, F] = PyG's [N,T,4F]

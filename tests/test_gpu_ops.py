@@ -293,3 +293,12 @@ def test_code_segment_sum_against_index_add(rows, H, ncodes):
     mag = torch.zeros(ncodes, H, dtype=torch.float64, device=DEV).index_add_(0, codes.long(), dh.double().abs())
     assert bool(((got.double() - want).abs() <= 2e-6 * mag + 1e-6).all())
     assert torch.equal(got, ops.code_segment_sum(dh, codes, ncodes))
+    # both kernels: rows ordered by code (>= ops.CODE_SORTED_MIN_ROWS rows) and per-warp shared-memory tables
+    was = ops.CODE_SORTED_MIN_ROWS
+    try:
+        for thr in (0, 1 << 40):
+            ops.CODE_SORTED_MIN_ROWS = thr
+            alt = ops.code_segment_sum(dh, codes, ncodes)
+            assert bool(((alt.double() - want).abs() <= 2e-6 * mag + 1e-6).all()), f"threshold {thr}"
+    finally:
+        ops.CODE_SORTED_MIN_ROWS = was
