@@ -5,6 +5,8 @@
 #include <mutex>
 
 #include "common.cuh"
+#include <atomic>
+#include <cstdlib>
 
 namespace gnnx {
 
@@ -400,6 +402,52 @@ int colsum_final_launch(const float* partial, int nchunks, int cols, float* out,
     launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, partial, nchunks, cols, out);
     return check_launch("colsum_final");
 }
+// partial sums, a grid barrier and the final fold in ONE launch (the host launches it only when the whole grid is
+// resident): same arithmetic as k_colsum_partial4 followed by k_colsum_final, so the result is bit-identical.
+__global__ void __launch_bounds__(256)
+k_colsum_coop4(const float* __restrict__ in, long long ld, int rows, int cols, int rows_per_chunk, float* __restrict__ partial,
+               float* __restrict__ out, int* __restrict__ counters) {
+    pdl_enter();
+    __shared__ float sh[4][256 + 4];
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+    const int c = (blockIdx.x * 64 + tx) * 4;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(rows, r0 + rows_per_chunk);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < cols) {
+        int r = r0 + ty;
+        for (; r + 12 < r1; r += 16) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = ldg4_stream(in + (long long)(r + 4 * u) * ld + c);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+        }
+        for (; r < r1; r += 4) {
+            float4 v = ldg4_stream(in + (long long)r * ld + c);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+    }
+    sh[ty][tx * 4 + 0] = s.x; sh[ty][tx * 4 + 1] = s.y; sh[ty][tx * 4 + 2] = s.z; sh[ty][tx * 4 + 3] = s.w;
+    __syncthreads();
+    const int cc = blockIdx.x * 256 + threadIdx.x;
+    if (cc < cols) partial[(long long)blockIdx.y * cols + cc] = (sh[0][threadIdx.x] + sh[1][threadIdx.x]) + (sh[2][threadIdx.x] + sh[3][threadIdx.x]);
+    const int nctas = (int)(gridDim.x * gridDim.y), nchunks = (int)gridDim.y;
+    grid_barrier(counters, nctas);
+    const int lane = threadIdx.x & 31;
+    const int nwarps = nctas * 8;
+    for (int col = ((int)(blockIdx.y * gridDim.x + blockIdx.x)) * 8 + (threadIdx.x >> 5); col < cols; col += nwarps) {
+        float a = 0.f;
+        for (int ch = lane; ch < nchunks; ch += 32) a += __ldcg(partial + (long long)ch * cols + col);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) a += __shfl_down_sync(0xffffffffu, a, off);
+        if (lane == 0) out[col] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(counters + 1, 1) == nctas - 1) { counters[0] = 0; counters[1] = 0; __threadfence(); }
+    }
+}
+
 int colsum_chunks(int64_t rows, int64_t cols) {
     int slabs = ceil_div(cols, 256);
     int target = max(1, (num_sms() * 4) / slabs);
@@ -425,8 +473,24 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
     if (rows == 0) { GNNX_CUDA(cudaMemsetAsync(out, 0, cols * sizeof(float), st)); return GNNX_OK; }
     int nch = colsum_chunks(rows, cols);
     int rpc = ceil_div(rows, nch);
-    if ((cols & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)in & 15) == 0)
+    if ((cols & 3) == 0 && (ld & 3) == 0 && ((uintptr_t)in & 15) == 0) {
+        // one cooperative launch when the whole grid is resident (GNNX_COLSUM_COOP=0: two launches, same bits)
+        static std::atomic<int> coop{0};                      // co-resident CTAs per SM; -1: unavailable
+        int k = coop.load();
+        if (k == 0) {
+            int n = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_colsum_coop4, 256, 0) != cudaSuccess || n < 1) { cudaGetLastError(); n = -1; }
+            coop.store(n); k = n;
+        }
+        const char* ce = getenv("GNNX_COLSUM_COOP");
+        const long long ctas = (long long)ceil_div(cols, 256) * nch;
+        int* ctr = (k > 0 && !(ce && ce[0] == '0') && ctas <= (long long)num_sms() * min(k, 4)) ? stream_ticket(st) : nullptr;
+        if (ctr) {
+            launch(k_colsum_coop4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws, out, ctr + 24);
+            return check_launch("colsum", 1);
+        }
         launch(k_colsum_partial4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);
+    }
     else
         launch(k_colsum_partial, dim3(ceil_div(cols, 32), nch), dim3(32, kCsRows), 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);
     launch(k_colsum_final, ceil_div(cols, 8), 256, 0, st, (const float*)ws, nch, (int)cols, out);

@@ -302,3 +302,26 @@ def test_code_segment_sum_against_index_add(rows, H, ncodes):
             assert bool(((alt.double() - want).abs() <= 2e-6 * mag + 1e-6).all()), f"threshold {thr}"
     finally:
         ops.CODE_SORTED_MIN_ROWS = was
+
+
+@pytest.mark.parametrize("rows,cols", [(101887, 256), (4096, 512), (70000, 8), (33, 1024), (205206, 128)])
+def test_colsum_cooperative_launch_equals_two_launches(rows, cols):
+    """gnnx_colsum as ONE cooperative launch (partials -> grid barrier -> fold) against partial + final kernels
+    (GNNX_COLSUM_COOP=0): same arithmetic, bit-identical; and against an fp64 sum."""
+    import os
+    x = torch.randn(rows, cols, device=DEV)
+    was = os.environ.get("GNNX_COLSUM_COOP")
+    try:
+        out = []
+        for mode in ("0", "1", "1"):
+            os.environ["GNNX_COLSUM_COOP"] = mode
+            out.append(ops.colsum(x))
+        torch.cuda.synchronize()
+    finally:
+        if was is None:
+            os.environ.pop("GNNX_COLSUM_COOP", None)
+        else:
+            os.environ["GNNX_COLSUM_COOP"] = was
+    assert torch.equal(out[0], out[1]) and torch.equal(out[1], out[2])
+    want = x.double().sum(0)
+    assert float((out[1].double() - want).abs().max()) <= 1e-5 * float(x.double().abs().sum(0).max())
