@@ -5,6 +5,7 @@
 // One warp owns one (destination row, head group) pair (attn.cuh) and gathers two edges per iteration.
 // Deterministic and atomic-free: the only cross-row reduction (d att) goes through ordered partials.
 #include "attn.cuh"
+#include <cstdlib>
 
 namespace gnnx {
 
@@ -168,6 +169,155 @@ k_gatv2_fwd(const float* __restrict__ xlr, const float* __restrict__ ee, long lo
                 const bool keep = drop_thr == 0u || attn_keep(seed, (long long)slot * heads + hd, drop_thr);
                 *ap = keep ? a : -a;
             }
+        }
+    }
+}
+
+// The same forward for C == 128 with an even number of heads: a HALF-warp owns a head (16 lanes x 8 columns), so a
+// warp advances two heads of a destination at once.  k_gatv2_fwd<1> at heads = 2 x C = 128 is instruction-bound (72 %
+// issue-active at 0.3 of the DRAM peak): with 8 columns per lane the per-edge index loads, the online-softmax scalar
+// work (one exp, compares, rescale factors) and the reduction shuffles (4 levels inside 16 lanes instead of 5 inside
+// 32) are issued once per PAIR of heads.  The reduction tree differs from k_gatv2_fwd<1>, so results agree to fp32
+// rounding, not bit for bit.  GNNX_GATV2_H2=0 selects the one-head-per-warp kernel.
+template <typename EIdx>
+__global__ void __launch_bounds__(256, 2)
+k_gatv2_fwd_h2(const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
+               const float* __restrict__ att, const float* __restrict__ bias, const int* __restrict__ rowptr,
+               const int* __restrict__ csr_src, int N, int E, int heads, int groups, float slope, int self_loops,
+               unsigned int drop_thr, float keep_scale, unsigned long long seed, float* __restrict__ out, float* alpha) {
+    pdl_enter();
+    const int H = heads * 128;
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const long long ld = 2ll * H;
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);
+    const int row_stride = (gridDim.x * wpb) / groups;
+    const int li = lane & 15;                                    // lane inside its head
+    const int head = (gw % groups) * 2 + (lane >> 4);
+    const int c0 = head * 128 + li * 4;                          // this lane's columns: c0 .. +3 and c0 + 64 .. +3
+    int i = gw / groups;
+    int nb = 0, ne = 0;
+    if (i < N) { nb = rowptr[i]; ne = rowptr[i + 1]; }
+    for (; i < N; i += row_stride) {
+        const int b = nb, e = ne;
+        if (i + row_stride < N) { nb = rowptr[i + row_stride]; ne = rowptr[i + row_stride + 1]; }
+        const int nreal = e - b;
+        const int nslots = nreal + (self_loops ? 1 : 0);
+        const bool spill = nslots > 16;                          // logits in registers (lane t of a head <- slot t) unless the row is longer
+        float mylg = 0.f;
+        F4 xr[2], av[2], acc[2], esum[2], xself[2];
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            const int c = c0 + 64 * v;
+            xr[v] = g4(xlr + (long long)i * ld + H + c);
+            xself[v] = self_loops ? g4(xlr + (long long)i * ld + c) : z4();
+            av[v] = g4(att + c);
+            acc[v] = z4(); esum[v] = z4();
+        }
+        float mx = -INFINITY, den = 0.f;
+        int cnt = 0;
+        auto step = [&](const F4 (&xl)[2], const F4 (&ev)[2], int slot, int tt) {
+            float part = 0.f;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float s = xr[v].a[j] + xl[v].a[j] + ev[v].a[j];
+                    s = s > 0.f ? s : s * slope;
+                    part = fmaf(s, av[v].a[j], part);
+                }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);      // inside the 16-lane half
+            const float lg = part;
+            if (spill) { if (li == 0) alpha[(long long)slot * heads + head] = lg; }
+            else if (li == tt) mylg = lg;
+            const float dl = lg - mx;
+            const float ex = expf(-fabsf(dl));
+            const float nm = fmaxf(mx, lg);
+            const float sc = dl > 0.f ? ex : 1.f;
+            const float wgt = dl > 0.f ? 1.f : ex;
+            den = den * sc + wgt;
+            const float wk = (drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr)) ? wgt : 0.f;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[v].a[j] = acc[v].a[j] * sc + wk * xl[v].a[j];
+            mx = nm;
+        };
+        for (int t = b; t < e; t += 2) {
+            const bool two = t + 1 < e;
+            const int s0 = csr_src[t], s1 = two ? csr_src[t + 1] : s0;
+            const long long r0 = (long long)eidx[t] * ld_e, r1 = two ? (long long)eidx[t + 1] * ld_e : r0;
+            F4 x0[2], e0[2], x1[2], e1[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int c = c0 + 64 * v;
+                x0[v] = g4(xlr + (long long)s0 * ld + c);
+                e0[v] = g4(ee + r0 + c);
+                x1[v] = g4(xlr + (long long)s1 * ld + c);
+                e1[v] = g4(ee + r1 + c);
+            }
+            if (!(self_loops && s0 == i)) {
+#pragma unroll
+                for (int v = 0; v < 2; ++v)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) esum[v].a[j] += e0[v].a[j];
+                ++cnt;
+                step(x0, e0, t, t - b);
+            } else if (!spill && li == t - b) {
+                mylg = INFINITY;                                 // marks a removed edge: alpha = 0
+            }
+            if (two) {
+                if (!(self_loops && s1 == i)) {
+#pragma unroll
+                    for (int v = 0; v < 2; ++v)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) esum[v].a[j] += e1[v].a[j];
+                    ++cnt;
+                    step(x1, e1, t + 1, t + 1 - b);
+                } else if (!spill && li == t + 1 - b) {
+                    mylg = INFINITY;
+                }
+            }
+        }
+        if (self_loops) {
+            const float inv_cnt = 1.f / (float)max(cnt, 1);
+            F4 ev[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) ev[v].a[j] = esum[v].a[j] * inv_cnt;
+            step(xself, ev, E + i, nreal);
+        }
+        const float inv = 1.f / (den + 1e-16f);
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            const int c = c0 + 64 * v;
+            F4 o, bv = bias ? g4(bias + c) : z4();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o.a[j] = acc[v].a[j] * (inv * keep_scale) + bv.a[j];
+            stg4(out + (long long)i * H + c, o.q);
+        }
+        if (!spill) {
+            if (li < nslots) {
+                const int slot = li < nreal ? b + li : E + i;
+                float a = 0.f;
+                if (mylg != INFINITY) {
+                    a = expf(mylg - mx) * inv;
+                    if (!(drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr))) a = -a;
+                }
+                alpha[(long long)slot * heads + head] = a;
+            }
+            continue;
+        }
+        __syncwarp();                                            // long rows: the 16 lanes of a head walk its slots
+        for (int t = li; t < nslots; t += 16) {
+            const int slot = t < nreal ? b + t : E + i;
+            float* ap = alpha + (long long)slot * heads + head;
+            if (t < nreal && self_loops && csr_src[slot] == i) { *ap = 0.f; continue; }     // removed self loop
+            const float a = expf(*ap - mx) * inv;
+            const bool keep = drop_thr == 0u || attn_keep(seed, (long long)slot * heads + head, drop_thr);
+            *ap = keep ? a : -a;
         }
     }
 }
@@ -440,6 +590,16 @@ int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t
     const unsigned int thr = attn_drop_threshold(dropout_p);
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
+    {   // a half-warp per head (GNNX_GATV2_H2=0: a warp per head); read per call so that a test can compare both
+        const char* pe = getenv("GNNX_GATV2_H2");
+        if (C == 128 && heads % 2 == 0 && !(pe && pe[0] == '0')) {
+            const int groups = heads / 2;
+            const int grid2 = attn_row_grid(N, groups, 8);
+            if (eidx_i32) launch(k_gatv2_fwd_h2<int>, grid2, 256, 0, st, xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, groups, slope, self_loops, thr, ks, sd, out, alpha);
+            else launch(k_gatv2_fwd_h2<uint8_t>, grid2, 256, 0, st, xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, groups, slope, self_loops, thr, ks, sd, out, alpha);
+            return check_launch("gatv2_fwd");
+        }
+    }
 #define CALL(NQ)                                                                                                              \
     if (eidx_i32) launch(k_gatv2_fwd<NQ, int>, grid, 256, 0, st, xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha); \
     else launch(k_gatv2_fwd<NQ, uint8_t>, grid, 256, 0, st, xlr, e, ld_e, eidx_u8, att, bias, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, thr, ks, sd, out, alpha)

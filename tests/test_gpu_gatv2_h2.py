@@ -1,0 +1,67 @@
+"""k_gatv2_fwd_h2 (C == 128, even head count: a half-warp owns a head, a warp two heads) against k_gatv2_fwd<1> (a warp
+per head, GNNX_GATV2_H2=0).  The reduction trees differ, so the comparison is to fp32 rounding: outputs within 2e-6 of the
+row scale, attention coefficients within 2e-6, the dropout outcome (sign bit of alpha) identical -- with self loops
+synthesised or not, attention dropout on or off, rows longer than 16 slots (logits spilled through alpha), isolated
+nodes and table-indexed edge terms.  Parity against the oracle is tests/test_gpu_model.py's job on whichever is default."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from gnnepcsaft_b200 import graph, ops
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(autouse=True)
+def _env():
+    was = os.environ.get("GNNX_GATV2_H2")
+    yield
+    if was is None:
+        os.environ.pop("GNNX_GATV2_H2", None)
+    else:
+        os.environ["GNNX_GATV2_H2"] = was
+
+
+def _graph(n, e, seed, hub):
+    rng = np.random.default_rng(seed)
+    ei = rng.integers(0, n, size=(2, e))
+    if hub:
+        ei[1, : min(e, 80)] = 3                      # one destination with far more than 16 slots
+    k = min(e, 5)
+    ei[1, :k] = ei[0, :k]                             # a few self loops to remove / keep
+    return graph.GraphIndex.build(torch.from_numpy(ei.astype(np.int64)).to(DEV), n)
+
+
+@pytest.mark.parametrize("heads", [2, 4])
+@pytest.mark.parametrize("n,e,hub", [(500, 1800, False), (300, 900, True), (64, 0, False), (20000, 41000, False)])
+@pytest.mark.parametrize("self_loops,p,table", [(True, 0.0, True), (False, 0.0, False), (True, 0.25, False)])
+def test_half_warp_per_head_agrees_with_warp_per_head(heads, n, e, hub, self_loops, p, table):
+    g = _graph(n, e, seed=n + e + heads, hub=hub)
+    C, H = 128, heads * 128
+    gen = torch.Generator().manual_seed(n + heads)
+    xlr = torch.randn(n, 2 * H, generator=gen).to(DEV)
+    att = (torch.randn(H, generator=gen) / C ** 0.5).to(DEV)
+    bias = torch.randn(H, generator=gen).to(DEV)
+    if table:                                          # 60-row edge-term table indexed by a u8 code per slot
+        ee = torch.randn(60, H, generator=gen).to(DEV)
+        eidx = torch.randint(0, 60, (max(e, 1),), generator=gen).to(torch.uint8).to(DEV)[:e]
+    else:
+        ee = torch.randn(max(e, 1), H, generator=gen).to(DEV)[:e]
+        eidx = g.csr_eid
+    res = []
+    for mode in ("0", "1"):
+        os.environ["GNNX_GATV2_H2"] = mode
+        res.append(ops.gatv2_fwd(xlr, ee, eidx, att, bias, g, heads, C, 0.2, self_loops, dropout_p=p, seed=1234))
+    torch.cuda.synchronize()
+    (o0, a0), (o1, a1) = res
+    rows = e + n if self_loops else e                  # without self loops the last N alpha rows are never written
+    if not self_loops:                                 # ... and destinations without edges keep bias only in both
+        pass
+    scale = float(o0.abs().max()) + 1e-6
+    assert float((o0 - o1).abs().max()) <= 4e-6 * scale, f"out: {float((o0 - o1).abs().max()):.3e} of {scale:.3g}"
+    a0, a1 = a0[:rows], a1[:rows]
+    assert float((a0.abs() - a1.abs()).abs().max() if rows else 0.0) <= 4e-6
+    assert torch.equal(torch.signbit(a0) & (a0 != 0), torch.signbit(a1) & (a1 != 0)), "dropout outcome (sign of alpha)"
