@@ -473,6 +473,150 @@ k_gatv2_bwd_dst(const float* __restrict__ dout, const float* __restrict__ out, c
         stg4(datt_partial + (long long)gw * (128 * NQ) + q * 128 + lane * 4, datt[q].q);
 }
 
+// k_gatv2_bwd_dst with a HALF-warp per head (C == 128, even head count; see k_gatv2_fwd_h2): 8 columns per lane, the
+// index / alpha loads, the per-slot scalar arithmetic and a 4-level reduction are issued once per pair of heads.  Warp gw
+// owns heads 2 (gw % groups), + 1 = 256 consecutive columns; its d att partial row is [256] (datt_partial + gw * 256).
+template <typename EIdx>
+__global__ void __launch_bounds__(256, 2)
+k_gatv2_bwd_dst_h2(const float* __restrict__ dout, const float* __restrict__ out, const float* __restrict__ bias,
+                   const float* __restrict__ xlr, const float* __restrict__ ee, long long ld_e, const EIdx* __restrict__ eidx,
+                   const float* __restrict__ att, const float* __restrict__ alpha, const int* __restrict__ rowptr,
+                   const int* __restrict__ csr_src, int N, int E, int heads, int groups, float slope, int self_loops,
+                   float keep_scale, float* __restrict__ dxlr, float* __restrict__ ds, float* __restrict__ datt_partial,
+                   float* __restrict__ de, const int* __restrict__ de_row) {
+    pdl_enter();
+    const int H = heads * 128;
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    const long long ld = 2ll * H;
+    const int gw = blockIdx.x * wpb + (threadIdx.x >> 5);
+    const int row_stride = (gridDim.x * wpb) / groups;
+    const int li = lane & 15;
+    const int cb = (gw % groups) * 256;
+    const int head = (cb >> 7) + (lane >> 4);
+    const int c0 = head * 128 + li * 4;                          // this lane's columns: c0 .. +3 and c0 + 64 .. +3
+    auto hsum = [](float v) {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    };
+    F4 av[2], datt[2], bv[2];
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+        const int c = c0 + 64 * v;
+        av[v] = g4(att + c);
+        bv[v] = bias ? g4(bias + c) : z4();
+        datt[v] = z4();
+    }
+    for (int i = gw / groups; i < N; i += row_stride) {
+        const int b = rowptr[i], e = rowptr[i + 1];
+        F4 xr[2], go[2], dxr[2], esum[2];
+        float sp = 0.f;
+#pragma unroll
+        for (int v = 0; v < 2; ++v) {
+            const int c = c0 + 64 * v;
+            xr[v] = g4(xlr + (long long)i * ld + H + c);
+            go[v] = g4(dout + (long long)i * H + c);
+            const F4 o = g4(out + (long long)i * H + c);
+            dxr[v] = z4(); esum[v] = z4();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) sp = fmaf(go[v].a[j], o.a[j] - bv[v].a[j], sp);
+        }
+        const float S = hsum(sp);
+        int cnt = 0;
+        F4 dl[2];
+        dl[0] = z4(); dl[1] = z4();
+        auto step = [&](const F4 (&xl)[2], const F4 (&ev)[2], float stored, int slot, bool is_loop, float loop_scale) {
+            float part = 0.f;
+#pragma unroll
+            for (int v = 0; v < 2; ++v)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) part = fmaf(go[v].a[j], xl[v].a[j], part);
+            const float kf = attn_dropped(stored) ? 0.f : keep_scale;
+            const float dlg = fabsf(stored) * (kf * hsum(part) - S);
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                F4 d;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float s = xr[v].a[j] + xl[v].a[j] + ev[v].a[j];
+                    const float a = s > 0.f ? s : s * slope;
+                    datt[v].a[j] = fmaf(dlg, a, datt[v].a[j]);
+                    d.a[j] = dlg * av[v].a[j] * (s > 0.f ? 1.f : slope);
+                    dxr[v].a[j] += d.a[j];
+                }
+                stg4(ds + (long long)slot * H + c0 + 64 * v, d.q);
+                if (is_loop) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dl[v].a[j] = d.a[j] * loop_scale;
+                } else if (de) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) d.a[j] += dl[v].a[j];
+                    const long long row = de_row ? de_row[slot] : slot;
+                    stg4(de + row * H + c0 + 64 * v, d.q);
+                }
+            }
+        };
+        auto zero_slot = [&](int slot) {
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                stg4(ds + (long long)slot * H + c0 + 64 * v, make_float4(0.f, 0.f, 0.f, 0.f));
+                if (de) stg4(de + (de_row ? (long long)de_row[slot] : (long long)slot) * H + c0 + 64 * v, make_float4(0.f, 0.f, 0.f, 0.f));
+            }
+        };
+        if (self_loops) {
+            for (int t = b; t < e; ++t) {
+                if (csr_src[t] == i) continue;
+                const long long r0 = (long long)eidx[t] * ld_e;
+#pragma unroll
+                for (int v = 0; v < 2; ++v) {
+                    const F4 ev = g4(ee + r0 + c0 + 64 * v);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) esum[v].a[j] += ev.a[j];
+                }
+                ++cnt;
+            }
+            const float inv_cnt = 1.f / (float)max(cnt, 1);
+            const float al = alpha[(long long)(E + i) * heads + head];
+            F4 xl[2], ev[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                xl[v] = g4(xlr + (long long)i * ld + c0 + 64 * v);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) ev[v].a[j] = esum[v].a[j] * inv_cnt;
+            }
+            step(xl, ev, al, E + i, true, inv_cnt);
+        }
+        for (int t = b; t < e; t += 2) {
+            const bool two = t + 1 < e;
+            const int s0 = csr_src[t], s1 = two ? csr_src[t + 1] : s0;
+            const long long r0 = (long long)eidx[t] * ld_e, r1 = two ? (long long)eidx[t + 1] * ld_e : r0;
+            const float a0 = alpha[(long long)t * heads + head];
+            const float a1 = two ? alpha[(long long)(t + 1) * heads + head] : 0.f;
+            F4 x0[2], e0[2], x1[2], e1[2];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int c = c0 + 64 * v;
+                x0[v] = g4(xlr + (long long)s0 * ld + c);
+                e0[v] = g4(ee + r0 + c);
+                x1[v] = g4(xlr + (long long)s1 * ld + c);
+                e1[v] = g4(ee + r1 + c);
+            }
+            if (!(self_loops && s0 == i)) step(x0, e0, a0, t, false, 0.f);
+            else zero_slot(t);
+            if (two) {
+                if (!(self_loops && s1 == i)) step(x1, e1, a1, t + 1, false, 0.f);
+                else zero_slot(t + 1);
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < 2; ++v) stg4(dxlr + (long long)i * ld + H + c0 + 64 * v, dxr[v].q);
+    }
+#pragma unroll
+    for (int v = 0; v < 2; ++v)
+        stg4(datt_partial + (long long)gw * 256 + (c0 - cb) + 64 * v, datt[v].q);
+}
+
 // Backward, source side: dxlr[j, 0:H] = sum_{edges j->i} (ds[pos] + alpha'[pos] * dout[i]) + loop term.
 // Warp per (source row, 128-column chunk), two out-edges per iteration.
 __global__ void __launch_bounds__(256)
@@ -572,6 +716,11 @@ using namespace gnnx;
     } while (0)
 
 static int gat_bwd_grid(int64_t N, int groups) { return attn_row_grid(N, groups, 8); }
+// half-warp-per-head kernels (C == 128, even head count); GNNX_GATV2_H2=0 selects the warp-per-head ones (read per call)
+static bool gat_h2(int heads, int C) {
+    const char* pe = getenv("GNNX_GATV2_H2");
+    return C == 128 && heads % 2 == 0 && !(pe && pe[0] == '0');
+}
 
 extern "C" {
 
@@ -591,8 +740,7 @@ int gnnx_gatv2_fwd(const float* xlr, const float* e, int64_t ld_e, const int32_t
     const float ks = 1.0f / (1.0f - dropout_p);
     const unsigned long long sd = (unsigned long long)seed;
     {   // a half-warp per head (GNNX_GATV2_H2=0: a warp per head); read per call so that a test can compare both
-        const char* pe = getenv("GNNX_GATV2_H2");
-        if (C == 128 && heads % 2 == 0 && !(pe && pe[0] == '0')) {
+        if (gat_h2(heads, C)) {
             const int groups = heads / 2;
             const int grid2 = attn_row_grid(N, groups, 8);
             if (eidx_i32) launch(k_gatv2_fwd_h2<int>, grid2, 256, 0, st, xlr, e, ld_e, eidx_i32, att, bias, rowptr, csr_src, (int)N, (int)E, heads, groups, slope, self_loops, thr, ks, sd, out, alpha);
@@ -616,7 +764,14 @@ size_t gnnx_gatv2_bwd_workspace_bytes(int64_t N, int64_t E, int32_t heads, int32
     // column sum that folds them
     const size_t part = (size_t)gat_bwd_grid(N, s.groups) * 8 * 128 * s.nq * sizeof(float);
     const int64_t rows = (int64_t)gat_bwd_grid(N, s.groups) * 8 / s.groups;
-    return part + gnnx_colsum_workspace_bytes(rows, (int64_t)heads * C);
+    size_t need = part + gnnx_colsum_workspace_bytes(rows, (int64_t)heads * C);
+    if (C == 128 && heads % 2 == 0) {                     // the half-warp-per-head layout: [256] per warp, heads / 2 groups
+        const int g2 = heads / 2;
+        const size_t part2 = (size_t)gat_bwd_grid(N, g2) * 8 * 256 * sizeof(float);
+        const size_t need2 = part2 + gnnx_colsum_workspace_bytes((int64_t)gat_bwd_grid(N, g2) * 8 / g2, (int64_t)heads * C);
+        if (need2 > need) need = need2;
+    }
+    return need;
 }
 
 int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const float* xlr, const float* e, int64_t ld_e,
@@ -633,8 +788,18 @@ int gnnx_gatv2_bwd(const float* dout, const float* out, const float* bias, const
     cudaStream_t st = as_stream(stream);
     if (N == 0) { GNNX_CUDA(cudaMemsetAsync(datt, 0, H * sizeof(float), st)); return GNNX_OK; }
     const AttnShape s = attn_shape(heads, C);
-    const int grid = gat_bwd_grid(N, s.groups);
     const float ks = 1.0f / (1.0f - dropout_p);
+    if (gat_h2(heads, C)) {
+        const int g2 = heads / 2, grid2 = gat_bwd_grid(N, g2);
+        if (eidx_i32) launch(k_gatv2_bwd_dst_h2<int>, grid2, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, g2, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row);
+        else launch(k_gatv2_bwd_dst_h2<uint8_t>, grid2, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, g2, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row);
+        launch(k_gatv2_bwd_src, attn_row_grid(N, (H + 127) / 128, 16), 256, 0, st, dout, ds, alpha, colptr, csc_pos, csc_dst, (int)N, (int)E, heads, C, ilog2(C), self_loops, ks, dxlr);
+        int rc2 = check_launch("gatv2_bwd", 2);
+        if (rc2) return rc2;
+        const size_t part2 = (size_t)grid2 * 8 * 256 * sizeof(float);
+        return gnnx_colsum((const float*)ws, (int64_t)g2 * 256, (int64_t)grid2 * 8 / g2, H, datt, (char*)ws + part2, ws_bytes - part2, stream);
+    }
+    const int grid = gat_bwd_grid(N, s.groups);
 #define CALL(NQ)                                                                                                              \
     if (eidx_i32) launch(k_gatv2_bwd_dst<NQ, int>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_i32, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row); \
     else launch(k_gatv2_bwd_dst<NQ, uint8_t>, grid, 256, 0, st, dout, out, bias, xlr, e, ld_e, eidx_u8, att, alpha, rowptr, csr_src, (int)N, (int)E, heads, C, ilog2(C), s.groups, slope, self_loops, ks, dxlr, ds, (float*)ws, de, de_row)
