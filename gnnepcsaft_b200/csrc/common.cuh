@@ -100,6 +100,34 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
     return e;
 }
 
+// Launch of a kernel that contains a grid barrier.  Default: like launch() -- the host has sized the grid so that every
+// CTA fits on the GPU at once, and a grid is dispatched whole before a later one starts.  With gang launch ON
+// (gnnx_set_gang_launch(1); train.Trainer turns it on for data-parallel runs, GNNX_GANG_LAUNCH=1 forces it) the kernel is
+// launched with cudaLaunchAttributeCooperative instead of the programmatic-serialisation attribute: the driver then
+// guarantees that all CTAs are co-resident before any runs, whatever another stream (NCCL's all-reduce kernel, launched
+// from inside the backward) is doing to the SMs at that moment -- a partially resident grid spinning at its barrier next
+// to a partially resident collective could otherwise wait for each other.  Costs the launch overlap (~2 us per kernel).
+bool gang_launch();
+void set_gang_launch(int on);
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_coop(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    if (!gang_launch()) return launch(kernel, grid, block, smem, st, static_cast<Args&&>(args)...);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (!trace_on()) return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    trace_before(reinterpret_cast<const void*>(kernel), st);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    trace_after(st);
+    return e;
+}
+
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

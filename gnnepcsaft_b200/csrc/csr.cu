@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include <atomic>
 
 namespace gnnx {
 
@@ -42,6 +43,15 @@ void trace_before(const void* func, cudaStream_t st) {
     g_trace_recs.push_back(r);
 }
 void trace_after(cudaStream_t st) { cudaEventRecord(g_trace_recs.back().e1, st); }
+
+// Gang launch of the kernels that contain a grid barrier (see launch_coop in common.cuh): -1 = read GNNX_GANG_LAUNCH once
+static std::atomic<int> g_gang{-1};
+bool gang_launch() {
+    int v = g_gang.load(std::memory_order_relaxed);
+    if (v < 0) { const char* e = getenv("GNNX_GANG_LAUNCH"); v = (e && e[0] == '1') ? 1 : 0; g_gang.store(v); }
+    return v == 1;
+}
+void set_gang_launch(int on) { g_gang.store(on ? 1 : 0); }
 
 bool pdl_enabled() {
     static int on = -1;
@@ -378,6 +388,7 @@ extern "C" {
 
 int gnnx_abi_version(void) { return GNNX_ABI_VERSION; }
 const char* gnnx_last_error(void) { return gnnx::g_err; }
+int gnnx_set_gang_launch(int32_t on) { gnnx::set_gang_launch(on); return GNNX_OK; }
 int64_t gnnx_launch_count(void) { return (int64_t)__atomic_load_n(&gnnx::g_launches, __ATOMIC_RELAXED); }
 int64_t gnnx_tc_launch_count(void) { return (int64_t)__atomic_load_n(&gnnx::g_tc_launches, __ATOMIC_RELAXED); }
 #ifndef GNNX_BUILD_DIGEST

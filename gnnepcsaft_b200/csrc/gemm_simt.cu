@@ -486,7 +486,7 @@ int gnnx_colsum(const float* in, int64_t ld, int64_t rows, int64_t cols, float* 
         const long long ctas = (long long)ceil_div(cols, 256) * nch;
         int* ctr = (k > 0 && !(ce && ce[0] == '0') && ctas <= (long long)num_sms() * min(k, 4)) ? stream_ticket(st) : nullptr;
         if (ctr) {
-            launch(k_colsum_coop4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws, out, ctr + 24);
+            launch_coop(k_colsum_coop4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws, out, ctr + 24);
             return check_launch("colsum", 1);
         }
         launch(k_colsum_partial4, dim3(ceil_div(cols, 256), nch), 256, 0, st, in, ld, (int)rows, (int)cols, rpc, (float*)ws);

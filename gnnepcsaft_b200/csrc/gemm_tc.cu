@@ -1708,8 +1708,10 @@ int gemm_tc(const float* A, int64_t lda, int ta, const float* B, int64_t ldb, in
     int* ctr = nullptr;
     if (!mask && red_fold_enabled() && (long long)p.tiles * p.splits <= num_sms()) ctr = stream_ticket(st);
     const RedFold fold = {ctr ? C : nullptr, (long long)ldc, bias, flags, ctr ? ctr + 16 : nullptr};
-    launch(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
-                                                                          p.rows_per_split, p.BM, p.BN, nullptr, fold);
+    if (ctr) launch_coop(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
+                         p.rows_per_split, p.BM, p.BN, nullptr, fold);
+    else launch(k_gemm_tf32_red, dim3(p.tiles, p.splits), kThreads, kSmemBytes, st, mA, mB, mC, (float*)ws, (int)M, (int)N, (int)K,
+                p.rows_per_split, p.BM, p.BN, nullptr, fold);
     count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red");
     if (rc) return rc;
@@ -1789,8 +1791,10 @@ int gemm_tc_red_batched(int n, const float* const* A, const int64_t* lda, const 
     if (red_fold_enabled() && (long long)p.tiles * p.splits * n <= num_sms()) ctr = stream_ticket(st);
     for (int z = 0; z < kRedBatch; ++z) { bt.c[z] = C[z < n ? z : 0]; bt.ldc[z] = ldc[z < n ? z : 0]; }
     bt.counters = ctr ? ctr + 16 : nullptr;
-    launch(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
-           (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
+    if (ctr) launch_coop(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
+                         (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
+    else launch(k_gemm_tf32_red_batched, dim3(p.tiles, p.splits, n), kThreads, kSmemBytes, st, bt, (float*)ws, stride, (int)Mo,
+                (int)No, (int)R, p.rows_per_split, p.BM, p.BN);
     count_tc_launches(1);
     int rc = check_launch("gemm_tf32_red(batched)");
     for (int z = 0; z < n && rc == GNNX_OK && !ctr; ++z)

@@ -763,7 +763,7 @@ static int bn_fwd_impl(const float* x, int64_t rows, int64_t n_valid, const int3
             int cn = min(nch, num_sms() * min(k, 4));
             int* ctr = stream_ticket(st);
             if (ctr) {
-                launch(k_bn_fwd_coop, cn, 256, 0, st, x, (int)rows, C, ceil_div(rows, cn), (float*)ws, row_node, eps, momentum, running_mean,
+                launch_coop(k_bn_fwd_coop, cn, 256, 0, st, x, (int)rows, C, ceil_div(rows, cn), (float*)ws, row_node, eps, momentum, running_mean,
                        running_var, save_mean, save_rstd, weight, bias, relu, y, node_dropout(dropout_p, seed), ctr + 8);
                 return check_launch("bn_relu_fwd", 1);
             }
@@ -811,7 +811,7 @@ static int bn_bwd_impl(const float* dy, const float* x, const float* y, int64_t 
         int cn = min(nch, num_sms() * min(k, 4));
         int* ctr = stream_ticket(st);
         if (ctr) {
-            launch(k_bn_bwd_coop, cn, 256, 0, st, dy, x, (int)rows, C, save_mean, save_rstd, relu, ceil_div(rows, cn), (float*)ws, row_node,
+            launch_coop(k_bn_bwd_coop, cn, 256, 0, st, dy, x, (int)rows, C, save_mean, save_rstd, relu, ceil_div(rows, cn), (float*)ws, row_node,
                    weight, bias, drop, dweight, dbias, dx, (long long)n_valid, training, ctr + 8);
             return check_launch("bn_relu_bwd", 1);
         }

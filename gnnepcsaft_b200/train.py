@@ -201,6 +201,11 @@ class Trainer:
         self.pg = process_group
         if self.distributed:                                  # identical replicas to start from
             dist.broadcast(self.flat.data, src=0, group=self.pg)
+        if self.world > 1 and torch.cuda.is_available() and self.flat.data.is_cuda:
+            # NCCL's kernels share the SMs with the backward from another stream: the kernels with a grid barrier are then
+            # launched as cooperative grids (all CTAs co-resident by the driver's guarantee, csrc/common.cuh: launch_coop)
+            from ._lib import lib
+            lib().call("gnnx_set_gang_launch", 1)
 
     def backward(self, pred: Tensor, dpred: Tensor) -> None:
         """``pred.backward(dpred)`` with the gradients landing in the flat buffer (and, data parallel, the all-reduce of

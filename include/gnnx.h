@@ -48,6 +48,10 @@ GNNX_API int gnnx_abi_version(void);
 GNNX_API const char* gnnx_build_digest(void);
 GNNX_API const char* gnnx_last_error(void);
 /* Total number of CUDA kernels launched by this library in this process (monotonic). */
+/* No counterpart in the reference (launch policy).  on != 0: the kernels that contain a grid barrier (cooperative BatchNorm,
+ * column sums, the weight-gradient split fold) are launched with cudaLaunchAttributeCooperative, i.e. the driver guarantees
+ * that all their CTAs are co-resident -- for processes that run collectives (NCCL) on another stream of the same GPU. */
+GNNX_API int gnnx_set_gang_launch(int32_t on); /* returns GNNX_OK */
 GNNX_API int64_t gnnx_launch_count(void);
 /* Of those, the tcgen05 tensor-core kernels (k_gemm_tf32_rows2 / k_gemm_tf32_red*): lets a caller verify that a
  * product really took the tensor path and not the fp32 CUDA-core fallback. */
